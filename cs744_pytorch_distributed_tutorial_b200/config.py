@@ -1,0 +1,110 @@
+"""Run configuration.
+
+The reference has exactly three flags (``--master-ip``, ``--num-nodes``,
+``--rank``; ref: master/part2a/part2a.py:137-141) and hard-codes everything else
+as literals.  Every literal becomes a field here whose *default is the reference
+value*, so running with only the three reference flags reproduces its setup
+(SURVEY.md 5.6).
+"""
+from __future__ import annotations
+
+import dataclasses
+import os
+from dataclasses import dataclass, field
+from typing import Optional
+
+MODES = ("part1", "part2a", "part2a_extra", "part2b", "part3")
+
+# MASTER_PORT literals (ref: master/part2a/part2a.py:83, master/part3/part3.py:72)
+REFERENCE_PORTS = {"part1": 29501, "part2a": 29501, "part2a_extra": 29501, "part2b": 29501, "part3": 29508}
+
+
+@dataclass
+class TrainConfig:
+    # --- the three reference flags -------------------------------------------------
+    master_ip: str = "127.0.0.1"
+    num_nodes: int = 1          # world size (one process per GPU / node)
+    rank: int = 0
+    # --- which of the tutorial's parts to run ---------------------------------------
+    mode: str = "part1"
+    # --- literals of the reference, now defaults -----------------------------------
+    global_batch: int = 256     # ref: 256 in part1 (part1.py:17), 4 x 64 elsewhere (part2a.py:20)
+    lr: float = 0.1             # ref: master/part1/part1.py:98
+    momentum: float = 0.9
+    weight_decay: float = 1e-4
+    seed: int = 5000            # ref: master/part2a/part2a.py:89
+    epochs: int = 1             # ref: master/part2a/part2a.py:130
+    port: Optional[int] = None  # default: the reference port of the mode
+    log_interval: int = 20      # ref: master/part2a/part2a.py:54
+    num_workers: int = 2        # ref: master/part2a/part2a.py:109
+    cpu_threads: int = 4        # ref: master/part2a/part2a.py:18
+    data_root: str = "../../data"
+    # --- new knobs -------------------------------------------------------------------
+    arch: str = "VGG11"
+    device: str = "auto"        # auto | cpu | cuda
+    dtype: str = "bf16"         # compute dtype of the native GPU path (fp32 master weights)
+    backend: str = "auto"       # auto | gloo | nccl | native  (native = in-kernel NVLink collectives)
+    sync_impl: str = "auto"     # auto | torch | native
+    bucket_plan: str = "layer"  # layer (8 buckets) | ddp (torch's 3 buckets) | single
+    fuse_optimizer: bool = True  # SGD in the collective epilogue where the mode allows it
+    cuda_graph: bool = True
+    iters: Optional[int] = None  # stop an epoch after this many iterations
+    train_size: int = 50000     # CIFAR-10 sizes; synthetic data uses the same counts by default
+    test_size: int = 10000
+    synthetic: bool = True
+    augment: bool = True
+    drop_last: bool = False     # the reference keeps the partial last batch
+    eval: bool = True
+    checkpoint: Optional[str] = None
+    resume: Optional[str] = None
+    json_metrics: bool = True
+    scaling: str = "strong"     # strong: global_batch fixed; weak: per_rank_batch fixed
+    per_rank_batch: Optional[int] = None
+    timeout_s: float = 120.0
+
+    def __post_init__(self) -> None:
+        if self.mode not in MODES:
+            raise ValueError(f"mode must be one of {MODES}, got {self.mode!r}")
+        if self.num_nodes < 1 or not (0 <= self.rank < self.num_nodes):
+            raise ValueError(f"need 0 <= rank < num_nodes, got rank={self.rank} num_nodes={self.num_nodes}")
+        if self.mode == "part1" and self.num_nodes != 1:
+            raise ValueError("part1 is the single-process mode; use part2a/part2b/part3 for num_nodes > 1")
+        if self.port is None:
+            self.port = REFERENCE_PORTS[self.mode]
+        if self.per_rank_batch is None:
+            if self.global_batch % self.num_nodes != 0:
+                raise ValueError(f"global batch {self.global_batch} is not divisible by {self.num_nodes} ranks")
+            self.per_rank_batch = self.global_batch // self.num_nodes
+        else:
+            self.global_batch = self.per_rank_batch * self.num_nodes
+
+    @property
+    def world_size(self) -> int:
+        return self.num_nodes
+
+    def resolved_device(self) -> str:
+        if self.device != "auto":
+            return self.device
+        import torch
+        return "cuda" if torch.cuda.is_available() else "cpu"
+
+    def replace(self, **kw) -> "TrainConfig":
+        d = dataclasses.asdict(self)
+        d.update(kw)
+        if "num_nodes" in kw or "global_batch" in kw:
+            d.setdefault("per_rank_batch", None)
+            if "per_rank_batch" not in kw:
+                d["per_rank_batch"] = None
+        return TrainConfig(**d)
+
+    @staticmethod
+    def from_env(**kw) -> "TrainConfig":
+        """Fill rank / world size / master address from torchrun-style environment variables."""
+        env = os.environ
+        base = dict(
+            master_ip=env.get("MASTER_ADDR", "127.0.0.1"),
+            num_nodes=int(env.get("WORLD_SIZE", "1")),
+            rank=int(env.get("RANK", "0")),
+        )
+        base.update(kw)
+        return TrainConfig(**base)

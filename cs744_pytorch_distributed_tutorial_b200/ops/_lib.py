@@ -1,0 +1,104 @@
+"""ctypes binding of ``libb200dp.so`` (the C ABI declared in ``include/b200dp.h``).
+
+The library is loaded lazily.  On a machine with a GPU a missing or unloadable
+library is a hard error -- there is no silent PyTorch fallback for the native
+ops (the CPU/gloo plumbing path never calls in here).
+"""
+from __future__ import annotations
+
+import ctypes
+from ctypes import c_char_p, c_float, c_int, c_longlong, c_void_p
+from typing import Optional
+
+import torch
+
+from . import _build
+
+_lib: Optional[ctypes.CDLL] = None
+
+P = c_void_p
+I = c_int
+F = c_float
+LL = c_longlong
+
+_PROTOTYPES = {
+    "b200dp_conv_igemm": [P, P, P, P, P, I, I, I, I, I, I, I, P],
+    "b200dp_conv_wgrad": [P, P, P, I, I, I, I, I, I, I, I, I, P],
+    "b200dp_im2col3x3_c3": [P, P, I, I, I, P],
+    "b200dp_bn_stats": [P, P, LL, I, P],
+    "b200dp_bn_relu_pool_fwd": [P, P, P, P, P, P, P, P, P, P, I, I, I, I, I, I, F, F, P],
+    "b200dp_bn_relu_pool_bwd_reduce": [P, P, P, P, P, P, P, I, I, I, I, I, P],
+    "b200dp_bn_relu_pool_bwd_apply": [P, P, P, P, P, P, P, P, P, P, I, I, I, I, I, P],
+    "b200dp_linear_fwd": [P, P, P, P, I, I, I, P],
+    "b200dp_cross_entropy": [P, P, P, P, P, I, I, F, P],
+    "b200dp_linear_bwd": [P, P, P, P, P, P, I, I, I, P],
+    "b200dp_sgd_momentum": [P, P, P, LL, F, F, F, F, P],
+    "b200dp_prep_conv_weights": [P, P, P, I, I, I, I, P],
+}
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+def lib() -> ctypes.CDLL:
+    """Load (building first if the sources changed) and return the library."""
+    global _lib
+    if _lib is None:
+        path = _build.build()
+        handle = ctypes.CDLL(str(path), mode=ctypes.RTLD_GLOBAL)
+        handle.b200dp_last_error.restype = c_char_p
+        handle.b200dp_version.restype = c_char_p
+        for name, argtypes in _PROTOTYPES.items():
+            fn = getattr(handle, name, None)
+            if fn is None:
+                continue  # declared here before the translation unit exists; call() reports it
+            fn.argtypes = argtypes
+            fn.restype = c_int
+        _lib = handle
+    return _lib
+
+
+def declare(name: str, argtypes: list) -> None:
+    """Register the prototype of an entry point defined in another module's domain
+    (collectives, runtime).  Safe to call before or after the library is loaded."""
+    _PROTOTYPES[name] = argtypes
+    if _lib is not None:
+        fn = getattr(_lib, name)
+        fn.argtypes = argtypes
+        fn.restype = c_int
+
+
+def available() -> bool:
+    try:
+        lib()
+        return True
+    except Exception:
+        return False
+
+
+def call(name: str, *args) -> None:
+    """Invoke an ``int``-returning entry point; raise NativeError on non-zero."""
+    fn = getattr(lib(), name, None)
+    if fn is None:
+        raise NativeError(f"{name} is not exported by libb200dp.so")
+    rc = fn(*args)
+    if rc != 0:
+        msg = lib().b200dp_last_error().decode(errors="replace")
+        raise NativeError(f"{name} failed (code {rc}): {msg}")
+
+
+def ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    """Device pointer of a tensor (None -> NULL)."""
+    if t is None:
+        return None
+    return t.data_ptr()
+
+
+def stream_ptr(stream: Optional[torch.cuda.Stream] = None) -> int:
+    s = stream if stream is not None else torch.cuda.current_stream()
+    return s.cuda_stream
+
+
+def version() -> str:
+    return lib().b200dp_version().decode()

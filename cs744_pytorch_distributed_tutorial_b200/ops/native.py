@@ -1,0 +1,127 @@
+"""Thin torch-tensor wrappers over the native sm_100a kernels.
+
+Each function validates dtypes/layouts, allocates nothing unless documented and
+launches on the current CUDA stream, so the whole step can be captured in a CUDA
+graph.  Activations are bf16 NHWC ``[B, H, W, C]``; see ``include/b200dp.h``.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from . import _lib
+from ._lib import call, ptr, stream_ptr
+
+BN_EPS = 1e-5
+BN_MOMENTUM = 0.1
+
+
+def _chk(t: torch.Tensor, dtype: torch.dtype, name: str) -> None:
+    if not t.is_cuda or t.dtype != dtype or not t.is_contiguous():
+        raise ValueError(f"{name}: expected contiguous CUDA {dtype} tensor, got {t.dtype} on {t.device} "
+                         f"contiguous={t.is_contiguous()}")
+
+
+def conv_igemm(act: torch.Tensor, wgt: torch.Tensor, bias: Optional[torch.Tensor], out: torch.Tensor,
+               stats: Optional[torch.Tensor] = None, taps: int = 9, block_n: int = 0) -> torch.Tensor:
+    """out[B,H,W,Cout] = conv3x3(act[B,H,W,Cin], wgt[Cout, taps*Cin]) + bias (tcgen05 implicit GEMM).
+
+    ref: master/part1/model.py:18-23.  Also the dgrad kernel when fed dY and the
+    flipped/transposed weights.
+    """
+    _chk(act, torch.bfloat16, "act")
+    _chk(wgt, torch.bfloat16, "wgt")
+    _chk(out, torch.bfloat16, "out")
+    B, H, W, Cin = act.shape
+    Cout = wgt.shape[0]
+    assert wgt.shape[1] == taps * Cin, (wgt.shape, taps, Cin)
+    assert out.shape == (B, H, W, Cout)
+    call("b200dp_conv_igemm", ptr(act), ptr(wgt), ptr(bias), ptr(out), ptr(stats), B, H, W, Cin, Cout, taps,
+         block_n, stream_ptr())
+    return out
+
+
+def conv_wgrad(dy: torch.Tensor, x: torch.Tensor, dw: torch.Tensor, taps: int = 9, cin_valid: Optional[int] = None,
+               split_k: int = 0, accumulate: bool = False) -> torch.Tensor:
+    """dw[Cout, taps, cin_valid] (fp32) (+)= sum_p dy[p, Cout] * x[p+tap, Cin].  With split-K or
+    ``accumulate`` the partial tiles are added onto ``dw`` (zero it first for a plain gradient)."""
+    _chk(dy, torch.bfloat16, "dy")
+    _chk(x, torch.bfloat16, "x")
+    _chk(dw, torch.float32, "dw")
+    B, H, W, Cout = dy.shape
+    Cin = x.shape[3]
+    cv = Cin if cin_valid is None else cin_valid
+    assert dw.numel() == Cout * taps * cv
+    call("b200dp_conv_wgrad", ptr(dy), ptr(x), ptr(dw), B, H, W, Cin, Cout, taps, cv, split_k, int(accumulate),
+         stream_ptr())
+    return dw
+
+
+def im2col3x3_c3(x_nchw: torch.Tensor, a0: torch.Tensor) -> torch.Tensor:
+    _chk(x_nchw, torch.float32, "x")
+    _chk(a0, torch.bfloat16, "a0")
+    B, C, H, W = x_nchw.shape
+    assert C == 3 and a0.numel() == B * H * W * 64
+    call("b200dp_im2col3x3_c3", ptr(x_nchw), ptr(a0), B, H, W, stream_ptr())
+    return a0
+
+
+def bn_stats(y: torch.Tensor, stats: torch.Tensor) -> torch.Tensor:
+    _chk(y, torch.bfloat16, "y")
+    _chk(stats, torch.float32, "stats")
+    C = y.shape[-1]
+    call("b200dp_bn_stats", ptr(y), ptr(stats), y.numel() // C, C, stream_ptr())
+    return stats
+
+
+def bn_relu_pool_fwd(y, stats, gamma, beta, running_mean, running_var, num_batches_tracked, save_mean, save_invstd,
+                     out, pool: bool, training: bool, momentum: float = BN_MOMENTUM, eps: float = BN_EPS):
+    B, H, W, C = y.shape
+    call("b200dp_bn_relu_pool_fwd", ptr(y), ptr(stats), ptr(gamma), ptr(beta), ptr(running_mean), ptr(running_var),
+         ptr(num_batches_tracked), ptr(save_mean), ptr(save_invstd), ptr(out), B, H, W, C, int(pool), int(training),
+         momentum, eps, stream_ptr())
+    return out
+
+
+def bn_relu_pool_bwd(y, dout, mean, invstd, gamma, beta, sums, dy, dgamma, dbeta, pool: bool):
+    """Two launches: per-channel reduction into ``sums`` (must be zero), then the dY pass."""
+    B, H, W, C = y.shape
+    call("b200dp_bn_relu_pool_bwd_reduce", ptr(y), ptr(dout), ptr(mean), ptr(invstd), ptr(gamma), ptr(beta),
+         ptr(sums), B, H, W, C, int(pool), stream_ptr())
+    call("b200dp_bn_relu_pool_bwd_apply", ptr(y), ptr(dout), ptr(mean), ptr(invstd), ptr(gamma), ptr(beta),
+         ptr(sums), ptr(dy), ptr(dgamma), ptr(dbeta), B, H, W, C, int(pool), stream_ptr())
+    return dy
+
+
+def linear_fwd(x, w, b, logits):
+    B, Fdim = x.shape[0], x.numel() // x.shape[0]
+    call("b200dp_linear_fwd", ptr(x), ptr(w), ptr(b), ptr(logits), B, Fdim, w.shape[0], stream_ptr())
+    return logits
+
+
+def cross_entropy(logits, target, loss=None, dlogits=None, correct=None, grad_scale: float = 1.0):
+    B, O = logits.shape
+    assert target.dtype == torch.int64
+    call("b200dp_cross_entropy", ptr(logits), ptr(target), ptr(loss), ptr(dlogits), ptr(correct), B, O,
+         float(grad_scale), stream_ptr())
+
+
+def linear_bwd(x, w, dlogits, dw, db, dx):
+    B, Fdim = x.shape[0], x.numel() // x.shape[0]
+    call("b200dp_linear_bwd", ptr(x), ptr(w), ptr(dlogits), ptr(dw), ptr(db), ptr(dx), B, Fdim, w.shape[0],
+         stream_ptr())
+
+
+def sgd_momentum(p, g, buf, lr: float, momentum: float, wd: float, grad_scale: float = 1.0):
+    """Fused SGD on flat fp32 buffers (ref: master/part1/part1.py:38,98-99)."""
+    assert p.numel() == g.numel() == buf.numel()
+    call("b200dp_sgd_momentum", ptr(p), ptr(g), ptr(buf), p.numel(), lr, momentum, wd, grad_scale, stream_ptr())
+
+
+def prep_conv_weights(master, wf, wd, Cout: int, Cin: int, taps: int, kpad: int):
+    call("b200dp_prep_conv_weights", ptr(master), ptr(wf), ptr(wd), Cout, Cin, taps, kpad, stream_ptr())
+
+
+def version() -> str:
+    return _lib.version()

@@ -1,0 +1,615 @@
+// tcgen05 / TMEM / TMA implicit-GEMM kernels for the VGG conv layers.
+//
+//   conv_igemm_kernel  : forward conv3x3(pad 1) and dgrad.  GEMM view
+//        D[pixels, Cout] = sum_{tap, cin-block}  A_tap[pixels, 64] * W[Cout, tap*Cin + 64-block]^T
+//     The A tile of a tap is fetched by ONE 4-D TMA box over the NHWC activation
+//     tensor, shifted by (dr, ds); rows/columns that fall outside the image are
+//     zero-filled by the TMA unit, which is exactly the pad-1 halo.  The box lands
+//     in shared memory as 128 rows x 128 bytes with the 128-byte swizzle, i.e.
+//     already in the canonical K-major UMMA operand layout -- no im2col buffer.
+//   conv_wgrad_kernel  : dW[Cout, tap, Cin] = sum_pixels dY[p, Cout] * X[p+tap, Cin].
+//     Both operands are consumed MN-major directly from NHWC (the contraction runs
+//     over pixels), split-K over pixel blocks fills the 148 SMs, partial tiles are
+//     combined with vector red.global.add.
+//
+// Warp roles per CTA (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner +
+// single-thread tcgen05.mma issuer, warps 2..5 = epilogue (tcgen05.ld -> registers
+// -> bias / BatchNorm statistics -> global).
+//
+// Replaces what the reference gets from ATen/oneDNN through nn.Conv2d
+// (ref: master/part1/model.py:18-23) and its autograd (ref: master/part1/part1.py:37).
+#include <cuda.h>
+#include <cudaTypedefs.h>
+#include <stdio.h>
+
+#include "../include/b200dp.h"
+#include "common.cuh"
+#include "host_util.h"
+
+namespace b200dp {
+
+constexpr int kBlockM = 128;
+constexpr int kBlockK = 64;  // 64 bf16 = 128 bytes = one SW128 swizzle span
+constexpr int kUmmaK = 16;
+constexpr int kAStageBytes = kBlockM * kBlockK * 2;  // 16 KiB
+constexpr int kNumThreads = 192;
+
+struct IgemmParams {
+  int H, W, TH, TN;  // image dims; an M tile is TN images x TH rows x W columns = 128 pixels
+  int taps;          // 9 (3x3 pad 1) or 1
+  int cin_blocks;    // Cin / 64
+  int m_total;       // valid output rows (B*H*W)
+  int n_total;       // Cout
+  const float* bias;
+  __nv_bfloat16* out;
+  float* stats;  // optional [2][Cout]: sum, sum of squares
+};
+
+// Sum v[j] over the 32 lanes of the warp for every j; lane l returns the total of column l.
+// 31 shuffles instead of 160 (butterfly that halves the live set each stage).
+B200DP_DEVINL float warp_transpose_sum(float (&v)[32], int lane) {
+#pragma unroll
+  for (int off = 16, n = 32; off >= 1; off >>= 1, n >>= 1) {
+    const bool upper = (lane & off) != 0;
+#pragma unroll
+    for (int i = 0; i < n / 2; ++i) {
+      const float send = upper ? v[i] : v[i + n / 2];
+      const float keep = upper ? v[i + n / 2] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+    }
+  }
+  return v[0];
+}
+
+template <int BLOCK_N, int STAGES>
+__global__ void __launch_bounds__(kNumThreads)
+    conv_igemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                      const IgemmParams p) {
+  constexpr int kBStageBytes = BLOCK_N * kBlockK * 2;
+  constexpr int kStageBytes = kAStageBytes + kBStageBytes;
+  constexpr uint32_t kTmemCols = BLOCK_N < 32 ? 32 : BLOCK_N;
+  constexpr uint32_t kIdesc = umma_idesc_bf16(kBlockM, BLOCK_N, 0, 0);
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * kStageBytes);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full_bar = empty_bar + STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int m_tile = blockIdx.x;
+  const int n_tile = blockIdx.y;
+  const int num_kb = p.taps * p.cin_blocks;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(tmem_full_bar, 1);
+    mbar_fence_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, kTmemCols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      int n0, h0;
+      if (p.TN == 1) {
+        const int tiles_per_img = p.H / p.TH;
+        n0 = m_tile / tiles_per_img;
+        h0 = (m_tile - n0 * tiles_per_img) * p.TH;
+      } else {
+        n0 = m_tile * p.TN;
+        h0 = 0;
+      }
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        mbar_arrive_expect_tx(&full_bar[stage], kStageBytes);
+        const int tap = kb / p.cin_blocks;
+        const int cb = kb - tap * p.cin_blocks;
+        int dr = 0, ds = 0;
+        if (p.taps == 9) {
+          dr = tap / 3 - 1;
+          ds = tap % 3 - 1;
+        }
+        uint8_t* a_dst = smem + stage * kStageBytes;
+        tma_load_4d(a_dst, &tmA, &full_bar[stage], cb * kBlockK, ds, h0 + dr, n0);
+        tma_load_2d(a_dst + kAStageBytes, &tmB, &full_bar[stage], kb * kBlockK, n_tile * BLOCK_N);
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(smem + stage * kStageBytes);
+        const uint32_t b_addr = a_addr + kAStageBytes;
+#pragma unroll
+        for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+          // K-major SW128: 8-row groups are 1024 B apart; a K step of 16 bf16 is +32 B inside the span.
+          const uint64_t da = umma_smem_desc(a_addr + k * kUmmaK * 2, 16, 1024);
+          const uint64_t db = umma_smem_desc(b_addr + k * kUmmaK * 2, 16, 1024);
+          umma_bf16(tmem_base, da, db, kIdesc, (kb | k) != 0);
+        }
+        umma_commit(&empty_bar[stage]);
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+      umma_commit(tmem_full_bar);
+    }
+  } else {
+    // Epilogue: warp w may only touch TMEM lanes [32*(w%4), 32*(w%4)+32).
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    const long m = static_cast<long>(m_tile) * kBlockM + row;
+    const bool valid = m < p.m_total;
+    mbar_wait(tmem_full_bar, 0);
+    tc_fence_after();
+    __nv_bfloat16* out_row = p.out + m * p.n_total + n_tile * BLOCK_N;
+#pragma unroll 1
+    for (int c = 0; c < BLOCK_N; c += 32) {
+      uint32_t v[32];
+      tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + c, v);
+      tmem_ld_wait();
+      float f[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+      if (p.bias != nullptr) {
+        const float* b = p.bias + n_tile * BLOCK_N + c;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) f[j] += __ldg(b + j);
+      }
+      uint32_t packed[16];
+#pragma unroll
+      for (int j = 0; j < 16; ++j) packed[j] = pack_bf16x2(f[2 * j], f[2 * j + 1]);
+      if (valid) {
+        uint4* dst = reinterpret_cast<uint4*>(out_row + c);
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          dst[j] = make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
+      }
+      if (p.stats != nullptr) {
+        // statistics of the values as stored (bf16-rounded), so that the
+        // normalisation that follows is exactly centred on what it reads.
+        float s1[32], s2[32];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const float2 r = unpack_bf16x2(packed[j]);
+          s1[2 * j] = valid ? r.x : 0.f;
+          s1[2 * j + 1] = valid ? r.y : 0.f;
+          s2[2 * j] = s1[2 * j] * s1[2 * j];
+          s2[2 * j + 1] = s1[2 * j + 1] * s1[2 * j + 1];
+        }
+        const float t1 = warp_transpose_sum(s1, lane);
+        const float t2 = warp_transpose_sum(s2, lane);
+        const int ch = n_tile * BLOCK_N + c + lane;
+        atomicAdd(p.stats + ch, t1);
+        atomicAdd(p.stats + p.n_total + ch, t2);
+      }
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, kTmemCols);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// weight gradient
+// ---------------------------------------------------------------------------
+struct WgradParams {
+  int H, W, TH, TN;  // a K block is TN images x TH rows x W columns = 64 pixels
+  int taps;
+  int cin, cout;
+  int co_tiles, ci_tiles;
+  int a_boxes;  // 64-channel dY boxes that really exist in this M tile (1 when Cout == 64, else 2)
+  int kblocks_total, kblocks_per_split;
+  int ld_out, cin_valid;
+  int use_red;
+  float* out;
+};
+
+B200DP_DEVINL void red_add_v4(float* addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)
+               : "memory");
+}
+
+template <int BLOCK_N, int STAGES>
+__global__ void __launch_bounds__(kNumThreads)
+    conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ CUtensorMap tmX,
+                      const WgradParams p) {
+  constexpr int kSubTileBytes = 64 * 64 * 2;  // one (64 channels x 64 pixels) box, 8 KiB
+  constexpr int kABytes = 2 * kSubTileBytes;
+  constexpr int kBBytes = (BLOCK_N / 64) * kSubTileBytes;
+  constexpr int kStageBytes = kABytes + kBBytes;
+  constexpr uint32_t kTmemCols = BLOCK_N < 32 ? 32 : BLOCK_N;
+  constexpr uint32_t kIdesc = umma_idesc_bf16(kBlockM, BLOCK_N, 1, 1);
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * kStageBytes);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full_bar = empty_bar + STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  int t = blockIdx.x;
+  const int ci_tile = t % p.ci_tiles;
+  t /= p.ci_tiles;
+  const int co_tile = t % p.co_tiles;
+  const int tap = t / p.co_tiles;
+  const int kb_begin = blockIdx.y * p.kblocks_per_split;
+  const int kb_end = min(kb_begin + p.kblocks_per_split, p.kblocks_total);
+  const int num_kb = kb_end - kb_begin;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmDY);
+    tma_prefetch_desc(&tmX);
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(tmem_full_bar, 1);
+    mbar_fence_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, kTmemCols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (num_kb > 0) {
+    if (warp == 0) {
+      if (elect_one()) {
+        int dr = 0, ds = 0;
+        if (p.taps == 9) {
+          dr = tap / 3 - 1;
+          ds = tap % 3 - 1;
+        }
+        const int blocks_per_img = (p.TN == 1) ? (p.H / p.TH) : 1;
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int kb = kb_begin; kb < kb_end; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          mbar_arrive_expect_tx(&full_bar[stage], kStageBytes);
+          int n0, h0;
+          if (p.TN == 1) {
+            n0 = kb / blocks_per_img;
+            h0 = (kb - n0 * blocks_per_img) * p.TH;
+          } else {
+            n0 = kb * p.TN;
+            h0 = 0;
+          }
+          uint8_t* a_dst = smem + stage * kStageBytes;
+          // dY tile: [64 pixels][64 channels] per box, pixels kb*64 .. +63
+#pragma unroll
+          for (int j = 0; j < 2; ++j) {
+            const int co = co_tile * kBlockM + (j < p.a_boxes ? j * 64 : 0);
+            tma_load_2d(a_dst + j * kSubTileBytes, &tmDY, &full_bar[stage], co, kb * 64);
+          }
+          uint8_t* b_dst = a_dst + kABytes;
+#pragma unroll
+          for (int j = 0; j < BLOCK_N / 64; ++j)
+            tma_load_4d(b_dst + j * kSubTileBytes, &tmX, &full_bar[stage], ci_tile * BLOCK_N + j * 64, ds,
+                        h0 + dr, n0);
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    } else if (warp == 1) {
+      if (elect_one()) {
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(smem + stage * kStageBytes);
+          const uint32_t b_addr = a_addr + kABytes;
+#pragma unroll
+          for (int k = 0; k < 64 / kUmmaK; ++k) {
+            // MN-major SW128: rows are pixels (K), 128 B each; 8-pixel groups are 1024 B apart (SBO),
+            // 64-channel column blocks are one sub-tile apart (LBO); 16 pixels per MMA = +2048 B.
+            const uint64_t da = umma_smem_desc(a_addr + k * kUmmaK * 128, kSubTileBytes, 1024);
+            const uint64_t db = umma_smem_desc(b_addr + k * kUmmaK * 128, kSubTileBytes, 1024);
+            umma_bf16(tmem_base, da, db, kIdesc, (kb | k) != 0);
+          }
+          umma_commit(&empty_bar[stage]);
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit(tmem_full_bar);
+      }
+    } else {
+      const int q = warp & 3;
+      const int row = q * 32 + lane;
+      const int co = co_tile * kBlockM + row;
+      const bool valid = co < p.cout;
+      mbar_wait(tmem_full_bar, 0);
+      tc_fence_after();
+      float* out_row = p.out + static_cast<long>(co) * p.ld_out + tap * p.cin_valid + ci_tile * BLOCK_N;
+      const int col_limit = p.cin_valid - ci_tile * BLOCK_N;  // columns >= this are padding
+#pragma unroll 1
+      for (int c = 0; c < BLOCK_N; c += 32) {
+        uint32_t v[32];
+        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + c, v);
+        tmem_ld_wait();
+        if (valid) {
+          if (c + 32 <= col_limit && (p.ld_out & 3) == 0 && (p.cin_valid & 3) == 0) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              float* dst = out_row + c + j;
+              if (p.use_red) {
+                red_add_v4(dst, __uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]),
+                           __uint_as_float(v[j + 3]));
+              } else {
+                *reinterpret_cast<float4*>(dst) =
+                    make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]),
+                                __uint_as_float(v[j + 3]));
+              }
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              if (c + j < col_limit) {
+                if (p.use_red)
+                  atomicAdd(out_row + c + j, __uint_as_float(v[j]));
+                else
+                  out_row[c + j] = __uint_as_float(v[j]);
+              }
+            }
+          }
+        }
+      }
+      tc_fence_before();
+    }
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, kTmemCols);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------
+static PFN_cuTensorMapEncodeTiled_v12000 get_encode_fn() {
+  static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
+  if (fn == nullptr) {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres);
+    if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || ptr == nullptr) {
+      set_error("cuTensorMapEncodeTiled is not available from the CUDA driver (%s)", cudaGetErrorString(e));
+      return nullptr;
+    }
+    fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(ptr);
+  }
+  return fn;
+}
+
+// bf16 tensor map, 128-byte swizzle, out-of-bounds elements read as zero.
+static int make_tmap(CUtensorMap* tm, const void* base, int rank, const uint64_t* dims, const uint32_t* box) {
+  auto fn = get_encode_fn();
+  if (fn == nullptr) return B200DP_ENOSYS;
+  cuuint64_t gdim[4];
+  cuuint64_t gstride[3];
+  cuuint32_t bdim[4];
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  uint64_t stride = 2;
+  for (int i = 0; i < rank; ++i) {
+    gdim[i] = dims[i];
+    bdim[i] = box[i];
+    stride *= dims[i];
+    if (i < rank - 1) gstride[i] = stride;
+  }
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), gdim, gstride, bdim, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed with CUresult %d (rank %d dims %llu %llu box %u %u)", (int)r, rank,
+              (unsigned long long)dims[0], (unsigned long long)dims[1], box[0], box[1]);
+    return B200DP_EINVAL;
+  }
+  return 0;
+}
+
+// Split `pixels_per_tile` output pixels into TN images x TH rows x W columns.
+static int tile_geometry(int H, int W, int pixels_per_tile, int* TH, int* TN) {
+  if (W <= 0 || H <= 0 || pixels_per_tile % W != 0) return -1;
+  const int rows = pixels_per_tile / W;
+  if (rows <= H) {
+    if (H % rows != 0) return -1;
+    *TH = rows;
+    *TN = 1;
+  } else {
+    if (rows % H != 0) return -1;
+    *TH = H;
+    *TN = rows / H;
+  }
+  return 0;
+}
+
+template <int BLOCK_N, int STAGES>
+static int launch_igemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const IgemmParams& p, int m_tiles,
+                        cudaStream_t stream) {
+  constexpr int smem = STAGES * (kAStageBytes + BLOCK_N * kBlockK * 2) + 1024 + 256;
+  static bool configured = false;
+  auto kern = conv_igemm_kernel<BLOCK_N, STAGES>;
+  if (!configured) {
+    B200DP_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured = true;
+  }
+  dim3 grid(m_tiles, p.n_total / BLOCK_N);
+  kern<<<grid, kNumThreads, smem, stream>>>(tmA, tmB, p);
+  B200DP_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+template <int BLOCK_N, int STAGES>
+static int launch_wgrad(const CUtensorMap& tmDY, const CUtensorMap& tmX, const WgradParams& p, int tiles,
+                        int splits, cudaStream_t stream) {
+  constexpr int smem = STAGES * (2 * 8192 + (BLOCK_N / 64) * 8192) + 1024 + 256;
+  static bool configured = false;
+  auto kern = conv_wgrad_kernel<BLOCK_N, STAGES>;
+  if (!configured) {
+    B200DP_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured = true;
+  }
+  dim3 grid(tiles, splits);
+  kern<<<grid, kNumThreads, smem, stream>>>(tmDY, tmX, p);
+  B200DP_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace b200dp
+
+using namespace b200dp;
+
+extern "C" int b200dp_conv_igemm(const void* act, const void* wgt, const float* bias, void* out, float* stats,
+                                 int B, int H, int W, int Cin, int Cout, int taps, int block_n,
+                                 b200dp_stream_t stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if ((taps != 9 && taps != 1) || Cin % 64 != 0 || Cout % 32 != 0 || B <= 0) {
+    set_error("conv_igemm: unsupported shape B=%d H=%d W=%d Cin=%d Cout=%d taps=%d", B, H, W, Cin, Cout, taps);
+    return B200DP_EINVAL;
+  }
+  IgemmParams p{};
+  p.H = H;
+  p.W = W;
+  if (tile_geometry(H, W, kBlockM, &p.TH, &p.TN) != 0) {
+    set_error("conv_igemm: H=%d W=%d cannot be tiled into 128-pixel blocks", H, W);
+    return B200DP_EINVAL;
+  }
+  p.taps = taps;
+  p.cin_blocks = Cin / 64;
+  p.m_total = B * H * W;
+  p.n_total = Cout;
+  p.bias = bias;
+  p.out = static_cast<__nv_bfloat16*>(out);
+  p.stats = stats;
+  const int m_tiles = (p.m_total + kBlockM - 1) / kBlockM;
+  if (block_n == 0) {
+    // largest N tile that still yields about one CTA per SM
+    const int cands[4] = {256, 128, 64, 32};
+    block_n = 32;
+    for (int c : cands) {
+      if (Cout % c == 0 && static_cast<long>(m_tiles) * (Cout / c) >= 120) {
+        block_n = c;
+        break;
+      }
+    }
+    if (Cout % block_n != 0) block_n = (Cout % 64 == 0) ? 64 : 32;
+  }
+  if (Cout % block_n != 0) {
+    set_error("conv_igemm: Cout=%d is not a multiple of block_n=%d", Cout, block_n);
+    return B200DP_EINVAL;
+  }
+  CUtensorMap tmA, tmB;
+  {
+    const uint64_t dims[4] = {(uint64_t)Cin, (uint64_t)W, (uint64_t)H, (uint64_t)B};
+    const uint32_t box[4] = {64, (uint32_t)W, (uint32_t)p.TH, (uint32_t)p.TN};
+    int rc = make_tmap(&tmA, act, 4, dims, box);
+    if (rc) return rc;
+  }
+  {
+    const uint64_t dims[2] = {(uint64_t)taps * Cin, (uint64_t)Cout};
+    const uint32_t box[2] = {64, (uint32_t)block_n};
+    int rc = make_tmap(&tmB, wgt, 2, dims, box);
+    if (rc) return rc;
+  }
+  switch (block_n) {
+    case 256: return launch_igemm<256, 4>(tmA, tmB, p, m_tiles, stream);
+    case 128: return launch_igemm<128, 3>(tmA, tmB, p, m_tiles, stream);
+    case 64: return launch_igemm<64, 4>(tmA, tmB, p, m_tiles, stream);
+    case 32: return launch_igemm<32, 4>(tmA, tmB, p, m_tiles, stream);
+    default: set_error("conv_igemm: block_n=%d not in {32,64,128,256}", block_n); return B200DP_EINVAL;
+  }
+}
+
+extern "C" int b200dp_conv_wgrad(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin,
+                                 int Cout, int taps, int cin_valid, int split_k, int accumulate,
+                                 b200dp_stream_t stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if ((taps != 9 && taps != 1) || Cin % 64 != 0 || (Cout % 128 != 0 && Cout != 64) || B <= 0 || cin_valid > Cin ||
+      cin_valid <= 0) {
+    set_error("conv_wgrad: unsupported shape B=%d H=%d W=%d Cin=%d Cout=%d taps=%d", B, H, W, Cin, Cout, taps);
+    return B200DP_EINVAL;
+  }
+  WgradParams p{};
+  p.H = H;
+  p.W = W;
+  if (tile_geometry(H, W, 64, &p.TH, &p.TN) != 0 || (static_cast<long>(B) * H * W) % 64 != 0) {
+    set_error("conv_wgrad: B=%d H=%d W=%d cannot be tiled into 64-pixel blocks", B, H, W);
+    return B200DP_EINVAL;
+  }
+  const int block_n = (Cin % 128 == 0) ? 128 : 64;
+  p.taps = taps;
+  p.cin = Cin;
+  p.cout = Cout;
+  p.co_tiles = (Cout + kBlockM - 1) / kBlockM;
+  p.ci_tiles = Cin / block_n;
+  p.a_boxes = (Cout >= 128) ? 2 : 1;
+  p.kblocks_total = (B * H * W) / 64;
+  const int tiles = taps * p.co_tiles * p.ci_tiles;
+  if (split_k <= 0) {
+    split_k = (148 + tiles - 1) / tiles;
+    if (split_k > p.kblocks_total) split_k = p.kblocks_total;
+    // keep at least 4 K blocks per CTA so the pipeline prologue is amortised
+    while (split_k > 1 && p.kblocks_total / split_k < 4) --split_k;
+  }
+  if (split_k > p.kblocks_total) split_k = p.kblocks_total;
+  p.kblocks_per_split = (p.kblocks_total + split_k - 1) / split_k;
+  split_k = (p.kblocks_total + p.kblocks_per_split - 1) / p.kblocks_per_split;
+  p.cin_valid = cin_valid;
+  p.ld_out = taps * cin_valid;
+  p.use_red = (split_k > 1 || accumulate) ? 1 : 0;
+  p.out = dw;
+  CUtensorMap tmDY, tmX;
+  {
+    const uint64_t dims[2] = {(uint64_t)Cout, (uint64_t)B * H * W};
+    const uint32_t box[2] = {64, 64};
+    int rc = make_tmap(&tmDY, dy, 2, dims, box);
+    if (rc) return rc;
+  }
+  {
+    const uint64_t dims[4] = {(uint64_t)Cin, (uint64_t)W, (uint64_t)H, (uint64_t)B};
+    const uint32_t box[4] = {64, (uint32_t)W, (uint32_t)p.TH, (uint32_t)p.TN};
+    int rc = make_tmap(&tmX, x, 4, dims, box);
+    if (rc) return rc;
+  }
+  if (block_n == 128) return launch_wgrad<128, 4>(tmDY, tmX, p, tiles, split_k, stream);
+  return launch_wgrad<64, 4>(tmDY, tmX, p, tiles, split_k, stream);
+}

@@ -1,0 +1,667 @@
+// Bandwidth-bound kernels of the VGG step: layer-0 patch gather, BatchNorm(train)
+// statistics, fused BN + ReLU (+ 2x2 max-pool) forward and backward, the
+// 512->10 classifier with softmax cross-entropy, weight re-layout and the SGD
+// update.  All activations are bf16 NHWC; every thread works on 8 channels
+// (one 16-byte vector) so that loads and stores are fully coalesced.
+//
+// Semantics follow the torch modules the reference instantiates
+// (ref: master/part1/model.py:16,24-25,40; master/part1/part1.py:94,98-99):
+// BatchNorm2d eps 1e-5 / momentum 0.1 / biased batch variance for normalisation,
+// unbiased for running_var; MaxPool2d(2,2) routes the gradient to the first
+// maximum in scan order; CrossEntropyLoss(mean); SGD lr/momentum/weight_decay
+// with dampening 0 and weight decay on every parameter.
+#include <stdio.h>
+
+#include "../include/b200dp.h"
+#include "common.cuh"
+#include "host_util.h"
+
+namespace b200dp {
+
+struct Vec8 {
+  float v[8];
+};
+
+B200DP_DEVINL Vec8 load_bf16x8(const __nv_bfloat16* p) {
+  const uint4 u = *reinterpret_cast<const uint4*>(p);
+  Vec8 r;
+  float2 f;
+  f = unpack_bf16x2(u.x); r.v[0] = f.x; r.v[1] = f.y;
+  f = unpack_bf16x2(u.y); r.v[2] = f.x; r.v[3] = f.y;
+  f = unpack_bf16x2(u.z); r.v[4] = f.x; r.v[5] = f.y;
+  f = unpack_bf16x2(u.w); r.v[6] = f.x; r.v[7] = f.y;
+  return r;
+}
+
+B200DP_DEVINL void store_bf16x8(__nv_bfloat16* p, const Vec8& r) {
+  uint4 u;
+  u.x = pack_bf16x2(r.v[0], r.v[1]);
+  u.y = pack_bf16x2(r.v[2], r.v[3]);
+  u.z = pack_bf16x2(r.v[4], r.v[5]);
+  u.w = pack_bf16x2(r.v[6], r.v[7]);
+  *reinterpret_cast<uint4*>(p) = u;
+}
+
+B200DP_DEVINL Vec8 load_f32x8(const float* p) {
+  const float4 a = *reinterpret_cast<const float4*>(p);
+  const float4 b = *reinterpret_cast<const float4*>(p + 4);
+  Vec8 r;
+  r.v[0] = a.x; r.v[1] = a.y; r.v[2] = a.z; r.v[3] = a.w;
+  r.v[4] = b.x; r.v[5] = b.y; r.v[6] = b.z; r.v[7] = b.w;
+  return r;
+}
+
+// ---------------------------------------------------------------------------
+// layer 0: gather 3x3x3 patches of the fp32 NCHW input into a bf16 [pixels][64]
+// matrix (27 real columns, k = (r*3+s)*3 + c, the rest zero) so that the first
+// conv is a plain K=64 GEMM for the tcgen05 kernel.
+// ---------------------------------------------------------------------------
+__global__ void im2col_c3_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ a0, int B, int H, int W) {
+  const long total = static_cast<long>(B) * H * W * 8;
+  for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long>(gridDim.x) * blockDim.x) {
+    const int chunk = static_cast<int>(i & 7);
+    const long pix = i >> 3;
+    Vec8 r;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) r.v[j] = 0.f;
+    if (chunk < 4) {
+      const int w = static_cast<int>(pix % W);
+      const int h = static_cast<int>((pix / W) % H);
+      const long n = pix / (static_cast<long>(W) * H);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int k = chunk * 8 + j;
+        if (k < 27) {
+          const int tap = k / 3, c = k - tap * 3;
+          const int hh = h + tap / 3 - 1, ww = w + tap % 3 - 1;
+          if (hh >= 0 && hh < H && ww >= 0 && ww < W) r.v[j] = __ldg(x + ((n * 3 + c) * H + hh) * W + ww);
+        }
+      }
+    }
+    store_bf16x8(a0 + i * 8, r);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// per-channel sum / sum of squares of a bf16 [P][C] matrix (stand-alone variant;
+// the conv epilogue can produce the same numbers fused).
+// ---------------------------------------------------------------------------
+__global__ void bn_stats_kernel(const __nv_bfloat16* __restrict__ y, float* __restrict__ stats, long P, int C) {
+  extern __shared__ float red[];  // [rows_per_block][C] x 2
+  const int chunks = C / 8;
+  const int rows_per_block = blockDim.x / chunks;
+  const int chunk = threadIdx.x % chunks;
+  const int rl = threadIdx.x / chunks;
+  Vec8 s1, s2;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s1.v[j] = s2.v[j] = 0.f;
+  if (rl < rows_per_block) {
+    for (long r = static_cast<long>(blockIdx.x) * rows_per_block + rl; r < P;
+         r += static_cast<long>(gridDim.x) * rows_per_block) {
+      const Vec8 v = load_bf16x8(y + r * C + chunk * 8);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        s1.v[j] += v.v[j];
+        s2.v[j] += v.v[j] * v.v[j];
+      }
+    }
+  }
+  float* r1 = red;
+  float* r2 = red + rows_per_block * C;
+  if (rl < rows_per_block) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      r1[rl * C + chunk * 8 + j] = s1.v[j];
+      r2[rl * C + chunk * 8 + j] = s2.v[j];
+    }
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float a = 0.f, b = 0.f;
+    for (int r = 0; r < rows_per_block; ++r) {
+      a += r1[r * C + c];
+      b += r2[r * C + c];
+    }
+    atomicAdd(stats + c, a);
+    atomicAdd(stats + C + c, b);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// BN(train or eval) + ReLU (+ 2x2/2 max-pool) forward
+// ---------------------------------------------------------------------------
+struct BnFwdParams {
+  const __nv_bfloat16* y;
+  const float* stats;  // [2][C] sum, sumsq over P = B*H*W (training only)
+  const float* gamma;
+  const float* beta;
+  float* running_mean;
+  float* running_var;
+  long long* num_batches_tracked;
+  float* save_mean;
+  float* save_invstd;
+  __nv_bfloat16* out;
+  int B, H, W, C, pool, training;
+  float momentum, eps;
+};
+
+__global__ void bn_relu_pool_fwd_kernel(const BnFwdParams p) {
+  const int chunks = p.C / 8;
+  const int Ho = p.pool ? p.H / 2 : p.H, Wo = p.pool ? p.W / 2 : p.W;
+  const long total = static_cast<long>(p.B) * Ho * Wo * chunks;
+  const float count = static_cast<float>(static_cast<long>(p.B) * p.H * p.W);
+  for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long>(gridDim.x) * blockDim.x) {
+    const int chunk = static_cast<int>(i % chunks);
+    const long q = i / chunks;
+    const int c0 = chunk * 8;
+    Vec8 scale, shift;
+    const Vec8 g = load_f32x8(p.gamma + c0), b = load_f32x8(p.beta + c0);
+    if (p.training) {
+      const Vec8 s1 = load_f32x8(p.stats + c0), s2 = load_f32x8(p.stats + p.C + c0);
+      Vec8 mean, var, invstd;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        mean.v[j] = s1.v[j] / count;
+        var.v[j] = fmaxf(s2.v[j] / count - mean.v[j] * mean.v[j], 0.f);
+        invstd.v[j] = rsqrtf(var.v[j] + p.eps);
+        scale.v[j] = g.v[j] * invstd.v[j];
+        shift.v[j] = b.v[j] - mean.v[j] * scale.v[j];
+      }
+      if (q == 0) {
+        // one thread per channel chunk owns the side outputs and the running statistics
+        const float unbias = count > 1.f ? count / (count - 1.f) : 1.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          p.save_mean[c0 + j] = mean.v[j];
+          p.save_invstd[c0 + j] = invstd.v[j];
+          p.running_mean[c0 + j] = (1.f - p.momentum) * p.running_mean[c0 + j] + p.momentum * mean.v[j];
+          p.running_var[c0 + j] = (1.f - p.momentum) * p.running_var[c0 + j] + p.momentum * var.v[j] * unbias;
+        }
+        if (chunk == 0 && p.num_batches_tracked != nullptr) *p.num_batches_tracked += 1;
+      }
+    } else {
+      const Vec8 rm = load_f32x8(p.running_mean + c0), rv = load_f32x8(p.running_var + c0);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        scale.v[j] = g.v[j] * rsqrtf(rv.v[j] + p.eps);
+        shift.v[j] = b.v[j] - rm.v[j] * scale.v[j];
+      }
+    }
+    Vec8 o;
+    if (p.pool) {
+      const int wo = static_cast<int>(q % Wo);
+      const int ho = static_cast<int>((q / Wo) % Ho);
+      const long n = q / (static_cast<long>(Wo) * Ho);
+      const __nv_bfloat16* base = p.y + ((n * p.H + 2 * ho) * p.W + 2 * wo) * p.C + c0;
+      const Vec8 a = load_bf16x8(base), bq = load_bf16x8(base + p.C);
+      const Vec8 c = load_bf16x8(base + static_cast<long>(p.W) * p.C),
+                 d = load_bf16x8(base + static_cast<long>(p.W) * p.C + p.C);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float za = fmaf(a.v[j], scale.v[j], shift.v[j]), zb = fmaf(bq.v[j], scale.v[j], shift.v[j]);
+        const float zc = fmaf(c.v[j], scale.v[j], shift.v[j]), zd = fmaf(d.v[j], scale.v[j], shift.v[j]);
+        o.v[j] = fmaxf(fmaxf(fmaxf(za, zb), fmaxf(zc, zd)), 0.f);
+      }
+    } else {
+      const Vec8 a = load_bf16x8(p.y + q * p.C + c0);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o.v[j] = fmaxf(fmaf(a.v[j], scale.v[j], shift.v[j]), 0.f);
+    }
+    store_bf16x8(p.out + q * p.C + c0, o);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// BN + ReLU (+ pool) backward.  Pass 1 reduces sum(dz) and sum(dz * xhat) per
+// channel; pass 2 recomputes dz and writes dY = gamma*invstd*(dz - S1/P - xhat*S2/P).
+// dz is the gradient reaching the BN output: the incoming gradient routed through
+// the pool arg-max (first maximum in scan order) and masked by ReLU.
+// ---------------------------------------------------------------------------
+struct BnBwdParams {
+  const __nv_bfloat16* y;
+  const __nv_bfloat16* dout;
+  const float* mean;
+  const float* invstd;
+  const float* gamma;
+  const float* beta;
+  float* sums;  // [2][C]: S1 = sum dz, S2 = sum dz*xhat
+  __nv_bfloat16* dy;
+  float* dgamma;
+  float* dbeta;
+  int B, H, W, C, pool;
+};
+
+template <bool APPLY>
+__global__ void bn_relu_pool_bwd_kernel(const BnBwdParams p) {
+  extern __shared__ float red[];
+  const int chunks = p.C / 8;
+  const int rows_per_block = blockDim.x / chunks;
+  const int chunk = threadIdx.x % chunks;
+  const int rl = threadIdx.x / chunks;
+  const int c0 = chunk * 8;
+  const int Ho = p.pool ? p.H / 2 : p.H, Wo = p.pool ? p.W / 2 : p.W;
+  const long Q = static_cast<long>(p.B) * Ho * Wo;
+  const float inv_count = 1.f / static_cast<float>(static_cast<long>(p.B) * p.H * p.W);
+
+  const Vec8 mean = load_f32x8(p.mean + c0), invstd = load_f32x8(p.invstd + c0);
+  const Vec8 g = load_f32x8(p.gamma + c0), b = load_f32x8(p.beta + c0);
+  Vec8 k1, k2;  // S1/P and S2/P (APPLY only)
+  if (APPLY) {
+    const Vec8 s1 = load_f32x8(p.sums + c0), s2 = load_f32x8(p.sums + p.C + c0);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      k1.v[j] = s1.v[j] * inv_count;
+      k2.v[j] = s2.v[j] * inv_count;
+    }
+    if (blockIdx.x == 0 && rl == 0 && p.dgamma != nullptr) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        p.dgamma[c0 + j] = s2.v[j];
+        p.dbeta[c0 + j] = s1.v[j];
+      }
+    }
+  }
+  Vec8 a1, a2;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) a1.v[j] = a2.v[j] = 0.f;
+
+  if (rl < rows_per_block) {
+    for (long q = static_cast<long>(blockIdx.x) * rows_per_block + rl; q < Q;
+         q += static_cast<long>(gridDim.x) * rows_per_block) {
+      const Vec8 go = load_bf16x8(p.dout + q * p.C + c0);
+      if (p.pool) {
+        const int wo = static_cast<int>(q % Wo);
+        const int ho = static_cast<int>((q / Wo) % Ho);
+        const long n = q / (static_cast<long>(Wo) * Ho);
+        const long off = ((n * p.H + 2 * ho) * p.W + 2 * wo) * p.C + c0;
+        const long offs[4] = {off, off + p.C, off + static_cast<long>(p.W) * p.C,
+                              off + static_cast<long>(p.W) * p.C + p.C};
+        Vec8 xh[4];
+        int win[8];
+        float zmax[8];
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+          const Vec8 yv = load_bf16x8(p.y + offs[t]);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            xh[t].v[j] = (yv.v[j] - mean.v[j]) * invstd.v[j];
+            // same arithmetic as the forward pass so that the winner is identical
+            const float scale = g.v[j] * invstd.v[j];
+            const float z = fmaf(yv.v[j], scale, b.v[j] - mean.v[j] * scale);
+            const float a = fmaxf(z, 0.f);
+            if (t == 0 || a > zmax[j]) {
+              zmax[j] = a;
+              win[j] = t;
+            }
+          }
+        }
+        if (APPLY) {
+#pragma unroll
+          for (int t = 0; t < 4; ++t) {
+            Vec8 o;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float dz = (win[j] == t && zmax[j] > 0.f) ? go.v[j] : 0.f;
+              o.v[j] = g.v[j] * invstd.v[j] * (dz - k1.v[j] - xh[t].v[j] * k2.v[j]);
+            }
+            store_bf16x8(p.dy + offs[t], o);
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            if (zmax[j] > 0.f) {
+              float xw = xh[0].v[j];
+              xw = win[j] == 1 ? xh[1].v[j] : xw;
+              xw = win[j] == 2 ? xh[2].v[j] : xw;
+              xw = win[j] == 3 ? xh[3].v[j] : xw;
+              a1.v[j] += go.v[j];
+              a2.v[j] += go.v[j] * xw;
+            }
+          }
+        }
+      } else {
+        const Vec8 yv = load_bf16x8(p.y + q * p.C + c0);
+        Vec8 o;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float xhat = (yv.v[j] - mean.v[j]) * invstd.v[j];
+          const float scale = g.v[j] * invstd.v[j];
+          const float z = fmaf(yv.v[j], scale, b.v[j] - mean.v[j] * scale);
+          const float dz = z > 0.f ? go.v[j] : 0.f;
+          if (APPLY) {
+            o.v[j] = g.v[j] * invstd.v[j] * (dz - k1.v[j] - xhat * k2.v[j]);
+          } else {
+            a1.v[j] += dz;
+            a2.v[j] += dz * xhat;
+          }
+        }
+        if (APPLY) store_bf16x8(p.dy + q * p.C + c0, o);
+      }
+    }
+  }
+  if (!APPLY) {
+    float* r1 = red;
+    float* r2 = red + rows_per_block * p.C;
+    if (rl < rows_per_block) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        r1[rl * p.C + c0 + j] = a1.v[j];
+        r2[rl * p.C + c0 + j] = a2.v[j];
+      }
+    }
+    __syncthreads();
+    for (int c = threadIdx.x; c < p.C; c += blockDim.x) {
+      float s = 0.f, t = 0.f;
+      for (int r = 0; r < rows_per_block; ++r) {
+        s += r1[r * p.C + c];
+        t += r2[r * p.C + c];
+      }
+      atomicAdd(p.sums + c, s);
+      atomicAdd(p.sums + p.C + c, t);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// classifier: logits = x W^T + b ; softmax cross-entropy (mean) ; backward
+// ---------------------------------------------------------------------------
+__global__ void linear_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w,
+                                  const float* __restrict__ bias, float* __restrict__ logits, int B, int F, int O) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (warp >= B) return;
+  const __nv_bfloat16* xr = x + static_cast<long>(warp) * F;
+  for (int o = 0; o < O; ++o) {
+    float acc = 0.f;
+    for (int f = lane * 8; f < F; f += 256) {
+      const Vec8 xv = load_bf16x8(xr + f);
+      const Vec8 wv = load_f32x8(w + static_cast<long>(o) * F + f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc = fmaf(xv.v[j], wv.v[j], acc);
+    }
+    acc = warp_sum(acc);
+    if (lane == 0) logits[static_cast<long>(warp) * O + o] = acc + bias[o];
+  }
+}
+
+// one block; loss is the batch mean; dlogits = (softmax - onehot) * grad_scale / B
+__global__ void cross_entropy_kernel(const float* __restrict__ logits, const long long* __restrict__ target,
+                                     float* __restrict__ loss, float* __restrict__ dlogits, int* __restrict__ correct,
+                                     int B, int O, float grad_scale) {
+  __shared__ float s_loss[32];
+  __shared__ int s_corr[32];
+  float my_loss = 0.f;
+  int my_corr = 0;
+  for (int i = threadIdx.x; i < B; i += blockDim.x) {
+    const float* l = logits + static_cast<long>(i) * O;
+    float mx = l[0];
+    int am = 0;
+    for (int o = 1; o < O; ++o) {
+      if (l[o] > mx) {
+        mx = l[o];
+        am = o;
+      }
+    }
+    float se = 0.f;
+    for (int o = 0; o < O; ++o) se += expf(l[o] - mx);
+    const float lse = logf(se) + mx;
+    const int t = static_cast<int>(target[i]);
+    my_loss += lse - l[t];
+    my_corr += (am == t);
+    if (dlogits != nullptr) {
+      const float sc = grad_scale / static_cast<float>(B);
+      for (int o = 0; o < O; ++o)
+        dlogits[static_cast<long>(i) * O + o] = (expf(l[o] - lse) - (o == t ? 1.f : 0.f)) * sc;
+    }
+  }
+  my_loss = warp_sum(my_loss);
+  for (int o = 16; o > 0; o >>= 1) my_corr += __shfl_xor_sync(0xffffffffu, my_corr, o);
+  if ((threadIdx.x & 31) == 0) {
+    s_loss[threadIdx.x >> 5] = my_loss;
+    s_corr[threadIdx.x >> 5] = my_corr;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float tl = 0.f;
+    int tc = 0;
+    for (int w = 0; w < (blockDim.x + 31) / 32; ++w) {
+      tl += s_loss[w];
+      tc += s_corr[w];
+    }
+    if (loss != nullptr) *loss = tl / static_cast<float>(B);
+    if (correct != nullptr) *correct = tc;
+  }
+}
+
+// blocks [0, nW): dW (and db); blocks [nW, ...): dX
+__global__ void linear_bwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w,
+                                  const float* __restrict__ dlogits, float* __restrict__ dw, float* __restrict__ db,
+                                  __nv_bfloat16* __restrict__ dx, int B, int F, int O, int nW) {
+  if (static_cast<int>(blockIdx.x) < nW) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx < O * F) {
+      const int o = idx / F, f = idx - o * F;
+      float acc = 0.f;
+      for (int i = 0; i < B; ++i)
+        acc = fmaf(dlogits[static_cast<long>(i) * O + o], __bfloat162float(x[static_cast<long>(i) * F + f]), acc);
+      dw[idx] = acc;
+    }
+    if (idx < O) {
+      float acc = 0.f;
+      for (int i = 0; i < B; ++i) acc += dlogits[static_cast<long>(i) * O + idx];
+      db[idx] = acc;
+    }
+  } else {
+    const long idx = static_cast<long>(blockIdx.x - nW) * blockDim.x + threadIdx.x;
+    if (idx < static_cast<long>(B) * F) {
+      const int i = static_cast<int>(idx / F), f = static_cast<int>(idx - static_cast<long>(i) * F);
+      float acc = 0.f;
+      for (int o = 0; o < O; ++o) acc = fmaf(dlogits[static_cast<long>(i) * O + o], w[static_cast<long>(o) * F + f], acc);
+      dx[idx] = __float2bfloat16(acc);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// optimizer and weight re-layout
+// ---------------------------------------------------------------------------
+// d = g*gscale + wd*p ; buf = mom*buf + d ; p -= lr*buf.  With buf zero-initialised the
+// first step gives buf = d, which is torch.optim.SGD's first-step rule (dampening 0).
+__global__ void sgd_momentum_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ buf,
+                                    long n, float lr, float momentum, float wd, float gscale) {
+  const long n4 = n >> 2;
+  const long stride = static_cast<long>(gridDim.x) * blockDim.x;
+  for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < n4; i += stride) {
+    float4 pv = reinterpret_cast<float4*>(p)[i];
+    const float4 gv = reinterpret_cast<const float4*>(g)[i];
+    float4 bv = reinterpret_cast<float4*>(buf)[i];
+    bv.x = fmaf(momentum, bv.x, fmaf(wd, pv.x, gv.x * gscale));
+    bv.y = fmaf(momentum, bv.y, fmaf(wd, pv.y, gv.y * gscale));
+    bv.z = fmaf(momentum, bv.z, fmaf(wd, pv.z, gv.z * gscale));
+    bv.w = fmaf(momentum, bv.w, fmaf(wd, pv.w, gv.w * gscale));
+    pv.x = fmaf(-lr, bv.x, pv.x);
+    pv.y = fmaf(-lr, bv.y, pv.y);
+    pv.z = fmaf(-lr, bv.z, pv.z);
+    pv.w = fmaf(-lr, bv.w, pv.w);
+    reinterpret_cast<float4*>(buf)[i] = bv;
+    reinterpret_cast<float4*>(p)[i] = pv;
+  }
+  for (long i = (n4 << 2) + blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < n; i += stride) {
+    const float b = fmaf(momentum, buf[i], fmaf(wd, p[i], g[i] * gscale));
+    buf[i] = b;
+    p[i] = fmaf(-lr, b, p[i]);
+  }
+}
+
+// master fp32 [Cout][taps][Cin] -> Wf bf16 [Cout][kpad] (zero padded past taps*Cin)
+//                               -> Wd bf16 [Cin][taps*Cout] with taps flipped (dgrad operand), optional
+__global__ void prep_conv_weights_kernel(const float* __restrict__ master, __nv_bfloat16* __restrict__ wf,
+                                         __nv_bfloat16* __restrict__ wd, int Cout, int Cin, int taps, int kpad) {
+  const long nf = static_cast<long>(Cout) * kpad;
+  const long nd = wd != nullptr ? static_cast<long>(Cin) * taps * Cout : 0;
+  const int kvalid = taps * Cin;
+  const long stride = static_cast<long>(gridDim.x) * blockDim.x;
+  for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < nf + nd; i += stride) {
+    if (i < nf) {
+      const int co = static_cast<int>(i / kpad), k = static_cast<int>(i - static_cast<long>(co) * kpad);
+      wf[i] = __float2bfloat16(k < kvalid ? master[static_cast<long>(co) * kvalid + k] : 0.f);
+    } else {
+      const long j = i - nf;
+      const int co = static_cast<int>(j % Cout);
+      const int tap = static_cast<int>((j / Cout) % taps);
+      const int ci = static_cast<int>(j / (static_cast<long>(Cout) * taps));
+      wd[j] = __float2bfloat16(master[(static_cast<long>(co) * taps + (taps - 1 - tap)) * Cin + ci]);
+    }
+  }
+}
+
+static inline int grid_for(long work_items, int threads, int max_blocks = 148 * 16) {
+  long b = (work_items + threads - 1) / threads;
+  if (b > max_blocks) b = max_blocks;
+  if (b < 1) b = 1;
+  return static_cast<int>(b);
+}
+
+}  // namespace b200dp
+
+using namespace b200dp;
+
+extern "C" int b200dp_im2col3x3_c3(const float* x_nchw, void* a0, int B, int H, int W, b200dp_stream_t s) {
+  const long total = static_cast<long>(B) * H * W * 8;
+  im2col_c3_kernel<<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(s)>>>(
+      x_nchw, static_cast<__nv_bfloat16*>(a0), B, H, W);
+  B200DP_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200dp_bn_stats(const void* y, float* stats, long long P, int C, b200dp_stream_t s) {
+  if (C % 8 != 0 || C > 2048) {
+    set_error("bn_stats: C=%d unsupported", C);
+    return B200DP_EINVAL;
+  }
+  const int threads = 256;
+  const int rows_per_block = threads / (C / 8);
+  if (rows_per_block < 1) {
+    set_error("bn_stats: C=%d too wide for a 256-thread block", C);
+    return B200DP_EINVAL;
+  }
+  const size_t smem = 2 * rows_per_block * C * sizeof(float);
+  int blocks = grid_for(P, rows_per_block * 8, 148 * 4);
+  bn_stats_kernel<<<blocks, threads, smem, static_cast<cudaStream_t>(s)>>>(static_cast<const __nv_bfloat16*>(y),
+                                                                          stats, P, C);
+  B200DP_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200dp_bn_relu_pool_fwd(const void* y, const float* stats, const float* gamma, const float* beta,
+                                       float* running_mean, float* running_var, long long* num_batches_tracked,
+                                       float* save_mean, float* save_invstd, void* out, int B, int H, int W, int C,
+                                       int pool, int training, float momentum, float eps, b200dp_stream_t s) {
+  if (C % 8 != 0 || (pool && ((H | W) & 1))) {
+    set_error("bn_relu_pool_fwd: unsupported shape H=%d W=%d C=%d pool=%d", H, W, C, pool);
+    return B200DP_EINVAL;
+  }
+  BnFwdParams p{static_cast<const __nv_bfloat16*>(y), stats, gamma, beta, running_mean, running_var,
+                num_batches_tracked, save_mean, save_invstd, static_cast<__nv_bfloat16*>(out),
+                B, H, W, C, pool, training, momentum, eps};
+  const long total = static_cast<long>(B) * (pool ? H / 2 : H) * (pool ? W / 2 : W) * (C / 8);
+  bn_relu_pool_fwd_kernel<<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(s)>>>(p);
+  B200DP_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+static int launch_bn_bwd(bool apply, const BnBwdParams& p, cudaStream_t s) {
+  if (p.C % 8 != 0 || p.C > 2048 || (p.pool && ((p.H | p.W) & 1))) {
+    set_error("bn_relu_pool_bwd: unsupported shape H=%d W=%d C=%d pool=%d", p.H, p.W, p.C, p.pool);
+    return B200DP_EINVAL;
+  }
+  const int threads = 256;
+  const int rows_per_block = threads / (p.C / 8);
+  const size_t smem = apply ? 0 : 2 * rows_per_block * p.C * sizeof(float);
+  const long Q = static_cast<long>(p.B) * (p.pool ? p.H / 2 : p.H) * (p.pool ? p.W / 2 : p.W);
+  const int blocks = grid_for(Q, rows_per_block * (apply ? 2 : 4), 148 * 8);
+  if (apply)
+    bn_relu_pool_bwd_kernel<true><<<blocks, threads, smem, s>>>(p);
+  else
+    bn_relu_pool_bwd_kernel<false><<<blocks, threads, smem, s>>>(p);
+  B200DP_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200dp_bn_relu_pool_bwd_reduce(const void* y, const void* dout, const float* mean,
+                                              const float* invstd, const float* gamma, const float* beta,
+                                              float* sums, int B, int H, int W, int C, int pool,
+                                              b200dp_stream_t s) {
+  BnBwdParams p{static_cast<const __nv_bfloat16*>(y), static_cast<const __nv_bfloat16*>(dout), mean, invstd, gamma,
+                beta, sums, nullptr, nullptr, nullptr, B, H, W, C, pool};
+  return launch_bn_bwd(false, p, static_cast<cudaStream_t>(s));
+}
+
+extern "C" int b200dp_bn_relu_pool_bwd_apply(const void* y, const void* dout, const float* mean,
+                                             const float* invstd, const float* gamma, const float* beta,
+                                             const float* sums, void* dy, float* dgamma, float* dbeta, int B, int H,
+                                             int W, int C, int pool, b200dp_stream_t s) {
+  BnBwdParams p{static_cast<const __nv_bfloat16*>(y), static_cast<const __nv_bfloat16*>(dout), mean, invstd, gamma,
+                beta, const_cast<float*>(sums), static_cast<__nv_bfloat16*>(dy), dgamma, dbeta, B, H, W, C, pool};
+  return launch_bn_bwd(true, p, static_cast<cudaStream_t>(s));
+}
+
+extern "C" int b200dp_linear_fwd(const void* x, const float* w, const float* b, float* logits, int B, int F, int O,
+                                 b200dp_stream_t s) {
+  if (F % 8 != 0) {
+    set_error("linear_fwd: F=%d must be a multiple of 8", F);
+    return B200DP_EINVAL;
+  }
+  const int threads = 256;
+  const int blocks = (B * 32 + threads - 1) / threads;
+  linear_fwd_kernel<<<blocks, threads, 0, static_cast<cudaStream_t>(s)>>>(static_cast<const __nv_bfloat16*>(x), w, b,
+                                                                         logits, B, F, O);
+  B200DP_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200dp_cross_entropy(const float* logits, const long long* target, float* loss, float* dlogits,
+                                    int* correct, int B, int O, float grad_scale, b200dp_stream_t s) {
+  cross_entropy_kernel<<<1, 256, 0, static_cast<cudaStream_t>(s)>>>(logits, target, loss, dlogits, correct, B, O,
+                                                                    grad_scale);
+  B200DP_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200dp_linear_bwd(const void* x, const float* w, const float* dlogits, float* dw, float* db, void* dx,
+                                 int B, int F, int O, b200dp_stream_t s) {
+  const int threads = 256;
+  const int nW = (O * F + threads - 1) / threads;
+  const int nX = static_cast<int>((static_cast<long>(B) * F + threads - 1) / threads);
+  linear_bwd_kernel<<<nW + nX, threads, 0, static_cast<cudaStream_t>(s)>>>(
+      static_cast<const __nv_bfloat16*>(x), w, dlogits, dw, db, static_cast<__nv_bfloat16*>(dx), B, F, O, nW);
+  B200DP_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200dp_sgd_momentum(float* p, const float* g, float* buf, long long n, float lr, float momentum,
+                                   float wd, float grad_scale, b200dp_stream_t s) {
+  if ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(buf)) & 15) {
+    set_error("sgd_momentum: buffers must be 16-byte aligned");
+    return B200DP_EINVAL;
+  }
+  sgd_momentum_kernel<<<grid_for(n / 4 + 1, 256, 148 * 8), 256, 0, static_cast<cudaStream_t>(s)>>>(
+      p, g, buf, n, lr, momentum, wd, grad_scale);
+  B200DP_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200dp_prep_conv_weights(const float* master, void* wf, void* wd, int Cout, int Cin, int taps,
+                                        int kpad, b200dp_stream_t s) {
+  if (kpad < taps * Cin) {
+    set_error("prep_conv_weights: kpad=%d < taps*Cin=%d", kpad, taps * Cin);
+    return B200DP_EINVAL;
+  }
+  const long n = static_cast<long>(Cout) * kpad + (wd ? static_cast<long>(Cin) * taps * Cout : 0);
+  prep_conv_weights_kernel<<<grid_for(n, 256), 256, 0, static_cast<cudaStream_t>(s)>>>(
+      master, static_cast<__nv_bfloat16*>(wf), static_cast<__nv_bfloat16*>(wd), Cout, Cin, taps, kpad);
+  B200DP_CUDA_TRY(cudaGetLastError());
+  return 0;
+}

@@ -1,0 +1,124 @@
+/*
+ * b200dp -- C ABI of the native B200 (sm_100a) library.
+ *
+ * Every entry point is `extern "C"`, takes raw device pointers plus a CUDA
+ * stream, launches asynchronously on that stream and returns 0 on success or a
+ * non-zero code (a cudaError_t value, or a negative B200DP_E* code) with a
+ * human-readable message available from b200dp_last_error().  Python reaches
+ * these through ctypes (cs744_pytorch_distributed_tutorial_b200/ops/_lib.py);
+ * C/C++ callers can link libb200dp.so directly.
+ *
+ * Layout conventions (internal to the framework; converted at the
+ * state_dict boundary):
+ *   activations   bf16, NHWC  [B][H][W][C]
+ *   conv weights  fp32 master in KRSC [Cout][3][3][Cin]; bf16 shadows
+ *                 Wf [Cout][9*Cin] (forward) and Wd [Cin][9*Cout] (dgrad, taps flipped)
+ *   gradients     fp32, same layout as the master parameters, in one flat buffer
+ *
+ * Citations of the form (ref: path:line) point into the reference repository
+ * kkyyhh96/CS744_PyTorch_Distributed_Tutorial and name the behaviour the entry
+ * point reproduces; none of its code is reused.
+ */
+#ifndef B200DP_H_
+#define B200DP_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* b200dp_stream_t; /* cudaStream_t */
+
+#define B200DP_EINVAL (-22)
+#define B200DP_ENOSYS (-38)
+#define B200DP_ETIMEDOUT (-110)
+
+/* Last error message recorded on the calling thread ("" if none). */
+const char* b200dp_last_error(void);
+/* Library version / build string (contains "sm_100a"). */
+const char* b200dp_version(void);
+
+/* ------------------------------------------------------------------------
+ * tcgen05 / TMEM / TMA implicit-GEMM convolution
+ * (ref: master/part1/model.py:18-23 nn.Conv2d(k=3,s=1,p=1,bias=True) and its autograd)
+ * ------------------------------------------------------------------------ */
+
+/* out[B,H,W,Cout] (bf16) = conv3x3_pad1(act[B,H,W,Cin] bf16, wgt[Cout][taps*Cin] bf16) + bias.
+ * taps = 9 (3x3, pad 1) or 1 (pointwise GEMM on a pre-gathered matrix, used for layer 0).
+ * Cin % 64 == 0, Cout % block_n == 0, block_n in {32,64,128,256} or 0 = choose.
+ * The same entry point computes dgrad when given dY as `act` and the
+ * tap-flipped transposed weights Wd as `wgt` (bias = NULL).
+ * If stats != NULL (2*Cout floats, zero on entry) the epilogue also adds the
+ * per-channel sum and sum of squares of the bf16-rounded outputs into
+ * stats[0..Cout) and stats[Cout..2Cout) (fused BatchNorm statistics). */
+int b200dp_conv_igemm(const void* act, const void* wgt, const float* bias, void* out, float* stats, int B,
+                      int H, int W, int Cin, int Cout, int taps, int block_n, b200dp_stream_t stream);
+
+/* dW[Cout][taps][cin_valid] (fp32) += sum over pixels dY[p][Cout] * X[p + tap][Cin].
+ * dy: bf16 [B,H,W,Cout]; x: bf16 [B,H,W,Cin].  Both operands are consumed
+ * MN-major straight from their NHWC layout.  split_k = 0 chooses a split that
+ * fills the 148 SMs; with split_k > 1 partial tiles are combined with
+ * red.global.add, so dw must be zero (or hold the value to accumulate onto).
+ * cin_valid <= Cin restricts which input-channel columns are written (layer 0:
+ * 27 of the 64 padded im2col columns). */
+int b200dp_conv_wgrad(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin, int Cout,
+                      int taps, int cin_valid, int split_k, int accumulate, b200dp_stream_t stream);
+
+/* ------------------------------------------------------------------------
+ * Bandwidth-bound layer kernels (bf16 NHWC activations, 8 channels per thread)
+ * ------------------------------------------------------------------------ */
+
+/* Layer 0 patch gather: x fp32 NCHW [B,3,H,W] -> a0 bf16 [B*H*W][64]; column
+ * k = (r*3+s)*3 + c for k < 27, zero above.  Turns the 3-channel conv into a
+ * K=64 GEMM for b200dp_conv_igemm(taps=1).  (ref: master/part1/model.py:13,18) */
+int b200dp_im2col3x3_c3(const float* x_nchw, void* a0, int B, int H, int W, b200dp_stream_t stream);
+
+/* stats[0..C) += sum_p y[p][c], stats[C..2C) += sum_p y[p][c]^2 (stats zero on entry). */
+int b200dp_bn_stats(const void* y, float* stats, long long P, int C, b200dp_stream_t stream);
+
+/* out = maxpool2x2?(relu(batchnorm(y))).  training=1: batch statistics from `stats`
+ * (count B*H*W), saves mean / invstd, updates running_mean / running_var (unbiased)
+ * / num_batches_tracked exactly like nn.BatchNorm2d.  training=0: running stats.
+ * (ref: master/part1/model.py:16,24-25) */
+int b200dp_bn_relu_pool_fwd(const void* y, const float* stats, const float* gamma, const float* beta,
+                            float* running_mean, float* running_var, long long* num_batches_tracked,
+                            float* save_mean, float* save_invstd, void* out, int B, int H, int W, int C,
+                            int pool, int training, float momentum, float eps, b200dp_stream_t stream);
+
+/* Backward of the fused block, pass 1: sums[0..C) += sum dz, sums[C..2C) += sum dz*xhat. */
+int b200dp_bn_relu_pool_bwd_reduce(const void* y, const void* dout, const float* mean, const float* invstd,
+                                   const float* gamma, const float* beta, float* sums, int B, int H, int W,
+                                   int C, int pool, b200dp_stream_t stream);
+/* pass 2: dy = gamma*invstd*(dz - S1/P - xhat*S2/P); dgamma = S2, dbeta = S1 (either may be NULL). */
+int b200dp_bn_relu_pool_bwd_apply(const void* y, const void* dout, const float* mean, const float* invstd,
+                                  const float* gamma, const float* beta, const float* sums, void* dy,
+                                  float* dgamma, float* dbeta, int B, int H, int W, int C, int pool,
+                                  b200dp_stream_t stream);
+
+/* Classifier and loss (ref: master/part1/model.py:40,45; master/part1/part1.py:36,94). */
+int b200dp_linear_fwd(const void* x_bf16, const float* w, const float* b, float* logits, int B, int F, int O,
+                      b200dp_stream_t stream);
+/* loss = mean CE; dlogits = (softmax - onehot) * grad_scale / B; correct = #argmax==target.
+ * loss, dlogits and correct may each be NULL. */
+int b200dp_cross_entropy(const float* logits, const long long* target, float* loss, float* dlogits,
+                         int* correct, int B, int O, float grad_scale, b200dp_stream_t stream);
+int b200dp_linear_bwd(const void* x_bf16, const float* w, const float* dlogits, float* dw, float* db,
+                      void* dx_bf16, int B, int F, int O, b200dp_stream_t stream);
+
+/* SGD with momentum and weight decay on flat fp32 buffers:
+ * d = g*grad_scale + wd*p; buf = momentum*buf + d; p -= lr*buf.  buf starts at zero,
+ * which reproduces torch.optim.SGD's first step.  (ref: master/part1/part1.py:38,98-99) */
+int b200dp_sgd_momentum(float* p, const float* g, float* buf, long long n, float lr, float momentum, float wd,
+                        float grad_scale, b200dp_stream_t stream);
+
+/* fp32 master [Cout][taps][Cin] -> bf16 Wf [Cout][kpad] (zero padded) and, if wd != NULL,
+ * bf16 Wd [Cin][taps*Cout] with the taps flipped (the dgrad operand). */
+int b200dp_prep_conv_weights(const float* master, void* wf, void* wd, int Cout, int Cin, int taps, int kpad,
+                             b200dp_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200DP_H_ */

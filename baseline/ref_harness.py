@@ -1,0 +1,166 @@
+"""Runs the UNMODIFIED reference scripts from ``baseline/_ref`` for the benchmark's reference arm.
+
+What is the reference's and what is harness:
+  * reference code, executed as is: ``model.py`` (``VGG11``) and the ``train_model`` function of
+    ``master/<part>/<script>.py`` (rank 0) or ``slave/...`` (other ranks) -- its loop, its
+    ``.to(device)``, ``zero_grad``, forward, loss, backward, gradient-sync block, ``optimizer.step``
+    and ``.item()`` prints.
+  * harness, mirroring the few lines of the reference's ``vgg_model`` / ``init_process`` that cannot
+    run here: process-group init (nccl instead of gloo), ``VGG11().to(device)``, ``DDP(model)`` for
+    part3, ``optim.SGD(lr 0.1, momentum 0.9, wd 1e-4)``, ``CrossEntropyLoss`` -- and a loader that
+    serves synthetic CIFAR-shaped batches and brackets exactly K iterations with CUDA events.
+  * parameterisation applied IN MEMORY at load time (files on disk stay byte-identical, checked
+    against the install manifest): the module global ``device`` -> "cuda"; for part2a / part2a_extra
+    / part2b the hard-coded world size 4 (``[0, 1, 2, 3]``, ``range(4)``, ``/ 4``, peers 1..3) ->
+    the actual world size.  part3 needs no source parameterisation.
+"""
+from __future__ import annotations
+
+import contextlib
+import hashlib
+import io
+import json
+import os
+import re
+import sys
+import types
+from pathlib import Path
+from typing import List, Optional, Tuple
+
+import torch
+
+REF_ROOT = Path(__file__).resolve().parent / "_ref"
+
+SCRIPTS = {
+    "part1": ("part1", "part1.py"),
+    "part2a": ("part2a", "part2a.py"),
+    "part2a_extra": ("part2a", "part2a_extra.py"),
+    "part2b": ("part2b", "part2b.py"),
+    "part3": ("part3", "part3.py"),
+}
+
+
+def available() -> Optional[str]:
+    """None if the reference can run, else a one-line reason."""
+    if not (REF_ROOT / "MANIFEST.json").exists():
+        return "baseline/_ref is missing (run baseline/install_reference.py where /root/reference is mounted)"
+    try:
+        import torchvision  # noqa: F401  (the reference imports it at module level)
+    except Exception as e:  # pragma: no cover
+        return f"torchvision not importable: {e}"
+    return None
+
+
+def _verify(path: Path) -> None:
+    manifest = json.loads((REF_ROOT / "MANIFEST.json").read_text())["sha256"]
+    rel = str(path.relative_to(REF_ROOT))
+    got = hashlib.sha256(path.read_bytes()).hexdigest()
+    if manifest.get(rel) != got:
+        raise RuntimeError(f"{rel} differs from the installed reference (sha256 mismatch)")
+
+
+def _parameterise_world(src: str, world: int, script: str) -> str:
+    """The reference hard-codes 4 ranks in its sync blocks; substitute the real world size."""
+    if world == 4:
+        return src
+    src = src.replace("dist.new_group([0, 1, 2, 3])", f"dist.new_group(list(range({world})))")
+    src = src.replace("range(4)", f"range({world})")
+    src = re.sub(r"/ 4\b", f"/ {world}", src)
+    if script == "part2a_extra.py":
+        raise NotImplementedError("part2a_extra unrolls peers 1,2,3 by hand; only world_size 4 runs unmodified")
+    return src
+
+
+def load_reference(mode: str, rank: int, world: int, device: str) -> types.ModuleType:
+    part, script = SCRIPTS[mode]
+    role = "master" if (rank == 0 or mode == "part1") else "slave"
+    path = REF_ROOT / role / part / script
+    _verify(path)
+    _verify(path.parent / "model.py")
+    src = _parameterise_world(path.read_text(), world, script)
+    sys.dont_write_bytecode = True
+    sys.path.insert(0, str(path.parent))
+    sys.modules.pop("model", None)
+    try:
+        mod = types.ModuleType(f"reference_{mode}_{role}")
+        mod.__file__ = str(path)
+        exec(compile(src, str(path), "exec"), mod.__dict__)
+    finally:
+        sys.path.remove(str(path.parent))
+    mod.device = device
+    return mod
+
+
+class TimedLoader:
+    """Serves ``warmup + steps`` batches and brackets the last ``steps`` with CUDA events.
+
+    ``__next__`` of iteration i runs after iteration i-1 has been fully enqueued, so recording the
+    start event when batch ``warmup`` is requested and the end event when the loader is exhausted
+    times exactly ``steps`` iterations of the reference's own loop.
+    """
+
+    def __init__(self, batches: List[Tuple[torch.Tensor, torch.Tensor]], warmup: int, steps: int, world: int):
+        self.batches, self.warmup, self.steps, self.world = batches, warmup, steps, world
+        self.start = torch.cuda.Event(enable_timing=True)
+        self.end = torch.cuda.Event(enable_timing=True)
+        self.elapsed_ms: Optional[float] = None
+        self.on_timed_region = None  # optional callbacks (clock sampling)
+        self.on_timed_region_end = None
+
+    def __len__(self) -> int:
+        return self.warmup + self.steps
+
+    def __iter__(self):
+        import torch.distributed as dist
+        for i in range(self.warmup + self.steps):
+            if i == self.warmup:
+                if self.world > 1:
+                    dist.barrier()
+                torch.cuda.synchronize()
+                if self.on_timed_region:
+                    self.on_timed_region()
+                self.start.record()
+            yield self.batches[i % len(self.batches)]
+        self.end.record()
+        torch.cuda.synchronize()
+        if self.on_timed_region_end:
+            self.on_timed_region_end()
+        self.elapsed_ms = self.start.elapsed_time(self.end)
+
+
+def run_reference(mode: str, rank: int, world: int, local_rank: int, per_rank_batch: int, steps: int, warmup: int,
+                  host_inputs: bool, n_distinct_batches: int = 8, quiet: bool = True,
+                  on_timed_region=None, on_timed_region_end=None) -> dict:
+    """Time ``steps`` iterations of the reference's ``train_model``.  Returns ms per step (this rank)."""
+    import torch.distributed as dist
+    import torch.nn as nn
+    import torch.optim as optim
+    torch.cuda.set_device(local_rank)
+    device = "cuda"
+    if world > 1 and not dist.is_initialized():
+        dist.init_process_group("nccl", rank=rank, world_size=world)
+    ref = load_reference(mode, rank, world, device)
+    torch.manual_seed(5000)            # ref: master/part3/part3.py:78
+    model = ref.mdl.VGG11()
+    model.to(device)
+    if mode == "part3":
+        model = ref.DDP(model)         # ref: master/part3/part3.py:116
+    optimizer = optim.SGD(model.parameters(), lr=0.1, momentum=0.9, weight_decay=0.0001)
+    criterion = nn.CrossEntropyLoss().to(device)
+    g = torch.Generator().manual_seed(1234 + rank)
+    batches = []
+    for _ in range(n_distinct_batches):
+        x = torch.randn(per_rank_batch, 3, 32, 32, generator=g)
+        y = torch.randint(0, 10, (per_rank_batch,), generator=g)
+        if host_inputs:
+            batches.append((x.pin_memory(), y.pin_memory()))
+        else:
+            batches.append((x.cuda(), y.cuda()))
+    loader = TimedLoader(batches, warmup, steps, world)
+    loader.on_timed_region, loader.on_timed_region_end = on_timed_region, on_timed_region_end
+    sink = io.StringIO()
+    with contextlib.redirect_stdout(sink) if quiet else contextlib.nullcontext():
+        ref.train_model(model, loader, optimizer, criterion, 0, rank)
+    ms = loader.elapsed_ms / steps
+    h2d = per_rank_batch * (3 * 32 * 32 * 4 + 8) if host_inputs else 0
+    return {"ms_per_step": ms, "h2d_bytes_per_step": h2d, "stdout_tail": sink.getvalue()[-400:]}

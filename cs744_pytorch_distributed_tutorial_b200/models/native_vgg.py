@@ -1,0 +1,356 @@
+"""sm_100a executor for the VGG family: flat parameter/gradient/momentum buffers and a
+static forward/backward kernel schedule.
+
+Design:
+  * All parameters live in ONE flat fp32 buffer, gradients in a second, SGD momentum in
+    a third.  ``module.weight.data`` / ``.grad`` are *views* into them, so the kernels
+    write gradients straight into (optionally peer-visible) memory and the collectives
+    and the fused optimizer work on contiguous ranges -- no copy in or out.
+  * The flat order is the *gradient-ready* order (reverse definition order), so that every
+    bucket of the overlap reducer is one contiguous range.
+  * Conv weights are stored KRSC ``[Cout][3][3][Cin]``; the module sees them as OIHW
+    tensors with channels_last strides, which keeps ``state_dict`` compatibility
+     without a layout conversion in the hot path.
+  * Activations are bf16 NHWC in pre-allocated workspaces; the step allocates nothing and
+    never synchronises with the host, so it can be captured in a CUDA graph.
+
+The kernel schedule replaces what the reference gets from ``model(data)`` /
+``loss.backward()`` (ref: master/part1/part1.py:35-37).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Callable, Dict, List, Optional, Sequence, Tuple
+
+import torch
+import torch.nn as nn
+
+from ..ops import native as K
+
+ALIGN = 4  # floats; every tensor starts on a 16-byte boundary inside the flat buffers
+
+
+@dataclass
+class FlatEntry:
+    name: str
+    offset: int      # in floats
+    numel: int
+    shape: Tuple[int, ...]      # logical (state_dict) shape
+    kind: str        # "conv_w" | "other"
+
+
+@dataclass
+class Bucket:
+    index: int
+    start: int       # float offset into the flat buffers (inclusive)
+    end: int         # exclusive; padded to ALIGN
+    names: List[str]
+
+    @property
+    def numel(self) -> int:
+        return self.end - self.start
+
+    @property
+    def nbytes(self) -> int:
+        return 4 * self.numel
+
+
+class FlatLayout:
+    """Offsets of every parameter in gradient-ready order plus the bucket plans."""
+
+    def __init__(self, named_params: Sequence[Tuple[str, torch.Tensor]], pad_to: int = 1024):
+        self.entries: List[FlatEntry] = []
+        off = 0
+        for name, p in reversed(list(named_params)):
+            kind = "conv_w" if p.dim() == 4 else "other"
+            self.entries.append(FlatEntry(name, off, p.numel(), tuple(p.shape), kind))
+            off += (p.numel() + ALIGN - 1) // ALIGN * ALIGN
+        self.used = off
+        self.total = (off + pad_to - 1) // pad_to * pad_to
+        self.by_name: Dict[str, FlatEntry] = {e.name: e for e in self.entries}
+
+    def buckets(self, plan: str = "layer") -> List[Bucket]:
+        """``layer``: one bucket per conv layer in gradient-ready order, the small tensors
+        folded into the neighbouring conv's bucket.  ``ddp``: torch DDP's size
+        caps (1 MiB first bucket, 25 MiB afterwards; ref: master/part3/part3.py:116 and the
+        probe in SURVEY.md 2.9).  ``single``: everything in one bucket (DDP's first iteration)."""
+        groups: List[List[FlatEntry]] = []
+        if plan == "single":
+            groups = [list(self.entries)]
+        elif plan == "layer":
+            cur: List[FlatEntry] = []
+            for e in self.entries:
+                cur.append(e)
+                if e.kind == "conv_w":
+                    groups.append(cur)
+                    cur = []
+            if cur:
+                groups[-1].extend(cur)
+        elif plan == "ddp":
+            cap, cur, size = 1 << 20, [], 0
+            for e in self.entries:
+                cur.append(e)
+                size += 4 * e.numel
+                if size >= cap:
+                    groups.append(cur)
+                    cur, size, cap = [], 0, 25 << 20
+            if cur:
+                groups.append(cur)
+        else:
+            raise ValueError(f"unknown bucket plan {plan!r}")
+        out: List[Bucket] = []
+        for i, g in enumerate(groups):
+            start = g[0].offset
+            end = self.total if i == len(groups) - 1 else groups[i + 1][0].offset
+            out.append(Bucket(i, start, end, [e.name for e in g]))
+        return out
+
+
+class _Block:
+    """Workspaces and parameter views of one conv -> BN -> ReLU (-> pool) block."""
+    pass
+
+
+class NativeVGG:
+    def __init__(self, module: nn.Module, max_batch: int, heap=None, conv_stats_fused: bool = True):
+        dev = next(module.parameters()).device
+        if dev.type != "cuda":
+            raise RuntimeError("NativeVGG needs the module on a CUDA device")
+        if not K._lib.available():
+            raise RuntimeError("libb200dp.so is not available; the native sm_100a path cannot run")
+        self.module = module
+        self.device = dev
+        self.max_batch = max_batch
+        self.heap = heap
+        self.conv_stats_fused = conv_stats_fused
+        self.specs = module.block_specs()
+        self.layout = FlatLayout(list(module.named_parameters()))
+        alloc = (lambda n, dt=torch.float32: heap.zeros(n, dt)) if heap is not None else \
+                (lambda n, dt=torch.float32: torch.zeros(n, device=dev, dtype=dt))
+        self._alloc = alloc
+        n = self.layout.total
+        self.flat_params = alloc(n)
+        self.flat_grads = alloc(n)
+        self.flat_momentum = alloc(n)
+        # BatchNorm buffers, flat so that one kernel can broadcast them (part3 semantics)
+        self.bn_channels = [s.cout for s in self.specs]
+        self.flat_bn = alloc(2 * sum(self.bn_channels))
+        self.flat_nbt_padded = alloc((len(self.specs) + 1) // 2 * 2, torch.int64)  # 16-byte multiple
+        self.flat_nbt = self.flat_nbt_padded[: len(self.specs)]
+        self.on_bucket_ready: Optional[Callable[[int], None]] = None
+        self._bucket_of_block: Dict[int, List[int]] = {}
+        self._adopt_parameters()
+        self._alloc_workspaces()
+        self.refresh_shadows()
+
+    # ------------------------------------------------------------------ parameters
+    def _view(self, flat: torch.Tensor, e: FlatEntry) -> torch.Tensor:
+        t = flat[e.offset: e.offset + e.numel]
+        if e.kind == "conv_w":
+            co, ci, kh, kw = e.shape
+            return t.view(co, kh, kw, ci).permute(0, 3, 1, 2)  # OIHW shape, KRSC memory
+        return t.view(e.shape)
+
+    def _adopt_parameters(self) -> None:
+        """Copy the module's values into the flat buffers and re-point .data/.grad at views."""
+        params = dict(self.module.named_parameters())
+        with torch.no_grad():
+            for e in self.layout.entries:
+                p = params[e.name]
+                v = self._view(self.flat_params, e)
+                v.copy_(p.data)
+                p.data = v
+                p.grad = self._view(self.flat_grads, e)
+            off = 0
+            for i, s in enumerate(self.specs):
+                bn = self.module.layers[s.bn_idx]
+                rm = self.flat_bn[off: off + s.cout]
+                rv = self.flat_bn[off + s.cout: off + 2 * s.cout]
+                rm.copy_(bn.running_mean)
+                rv.copy_(bn.running_var)
+                bn.running_mean.data = rm
+                bn.running_var.data = rv
+                self.flat_nbt[i].copy_(bn.num_batches_tracked)
+                bn.num_batches_tracked.data = self.flat_nbt[i]
+                off += 2 * s.cout
+
+    def refresh_from_module(self) -> None:
+        """Call after parameters were changed from outside (load_state_dict)."""
+        self.refresh_shadows()
+
+    def grad_views_intact(self) -> bool:
+        params = dict(self.module.named_parameters())
+        return all(params[e.name].grad is not None and
+                   params[e.name].grad.data_ptr() == self.flat_grads.data_ptr() + 4 * e.offset
+                   for e in self.layout.entries)
+
+    def restore_grad_views(self) -> None:
+        params = dict(self.module.named_parameters())
+        for e in self.layout.entries:
+            params[e.name].grad = self._view(self.flat_grads, e)
+
+    # ------------------------------------------------------------------ workspaces
+    def _alloc_workspaces(self) -> None:
+        B, dev = self.max_batch, self.device
+        bf = torch.bfloat16
+        L = self.layout
+        self.blocks: List[_Block] = []
+        zero_floats = sum(4 * s.cout for s in self.specs)
+        self.zero_region = torch.zeros(zero_floats, device=dev)  # conv stats + bn-bwd sums, cleared per step
+        zoff = 0
+        for i, s in enumerate(self.specs):
+            b = _Block()
+            b.spec = s
+            b.first = (i == 0)
+            b.kin = 64 if b.first else s.cin           # GEMM K per tap (layer 0: 27 -> 64 padded, 1 tap)
+            b.taps = 1 if b.first else 9
+            hw = s.hw
+            b.x_in = torch.zeros(B, hw, hw, b.kin, device=dev, dtype=bf) if b.first else self.blocks[-1].out
+            b.y = torch.empty(B, hw, hw, s.cout, device=dev, dtype=bf)
+            ho = hw // 2 if s.pool else hw
+            b.out = torch.empty(B, ho, ho, s.cout, device=dev, dtype=bf)
+            b.dy = torch.empty_like(b.y)
+            b.dout = torch.empty_like(b.out)            # gradient w.r.t. the block output
+            b.stats = self.zero_region[zoff: zoff + 2 * s.cout]
+            b.sums = self.zero_region[zoff + 2 * s.cout: zoff + 4 * s.cout]
+            zoff += 4 * s.cout
+            b.mean = torch.empty(s.cout, device=dev)
+            b.invstd = torch.empty(s.cout, device=dev)
+            kpad = b.taps * b.kin
+            b.wf = torch.empty(s.cout, kpad, device=dev, dtype=bf)
+            b.wd = None if b.first else torch.empty(s.cin, 9 * s.cout, device=dev, dtype=bf)
+            ew, eb = L.by_name[f"layers.{s.conv_idx}.weight"], L.by_name[f"layers.{s.conv_idx}.bias"]
+            eg, ebt = L.by_name[f"layers.{s.bn_idx}.weight"], L.by_name[f"layers.{s.bn_idx}.bias"]
+            fp, fg = self.flat_params, self.flat_grads
+            sl = lambda flat, e: flat[e.offset: e.offset + e.numel]
+            b.w_master, b.bias, b.gamma, b.beta = sl(fp, ew), sl(fp, eb), sl(fp, eg), sl(fp, ebt)
+            b.g_w, b.g_bias, b.g_gamma, b.g_beta = sl(fg, ew), sl(fg, eb), sl(fg, eg), sl(fg, ebt)
+            bn = self.module.layers[s.bn_idx]
+            b.running_mean, b.running_var, b.nbt = bn.running_mean.data, bn.running_var.data, self.flat_nbt[i:i + 1]
+            self.blocks.append(b)
+        efw, efb = L.by_name["fc1.weight"], L.by_name["fc1.bias"]
+        self.fc_w = self.flat_params[efw.offset: efw.offset + efw.numel].view(efw.shape)
+        self.fc_b = self.flat_params[efb.offset: efb.offset + efb.numel]
+        self.g_fc_w = self.flat_grads[efw.offset: efw.offset + efw.numel].view(efw.shape)
+        self.g_fc_b = self.flat_grads[efb.offset: efb.offset + efb.numel]
+        nc = efw.shape[0]
+        self.logits = torch.zeros(B, nc, device=dev)
+        self.dlogits = torch.zeros(B, nc, device=dev)
+        self.loss = torch.zeros((), device=dev)
+        self.correct = torch.zeros((), device=dev, dtype=torch.int32)
+
+    def set_bucket_plan(self, buckets: Sequence[Bucket]) -> None:
+        """Tell the executor which bucket becomes complete after which block's weight gradient."""
+        self._bucket_of_block = {}
+        L = self.layout
+
+        def block_of(name: str) -> int:
+            if name.startswith("layers."):
+                idx = int(name.split(".")[1])
+                for i, b in enumerate(self.blocks):
+                    if idx in (b.spec.conv_idx, b.spec.bn_idx):
+                        return i
+            return len(self.blocks) - 1  # fc1.* gradients exist before the last block's backward
+
+        for bk in buckets:
+            # complete once the lowest layer that owns a tensor of the bucket has run its backward
+            self._bucket_of_block.setdefault(min(block_of(n) for n in bk.names), []).append(bk.index)
+        self.buckets = list(buckets)
+
+    # ------------------------------------------------------------------ weight shadows
+    def refresh_shadows(self) -> None:
+        """bf16 operand copies of the fp32 master weights: Wf (forward) and Wd (dgrad)."""
+        for b in self.blocks:
+            s = b.spec
+            K.prep_conv_weights(b.w_master, b.wf, b.wd, s.cout, s.cin, 9, b.taps * b.kin)
+
+    # ------------------------------------------------------------------ forward
+    def forward(self, x: torch.Tensor, training: bool = True) -> torch.Tensor:
+        """x: fp32 NCHW [B,3,32,32] on the device.  Returns the logits workspace view [B,10]."""
+        B = x.shape[0]
+        if B > self.max_batch:
+            raise ValueError(f"batch {B} exceeds the executor's max_batch {self.max_batch}")
+        self._B = B
+        if training:
+            self.zero_region.zero_()
+        for b in self.blocks:
+            s = b.spec
+            x_in = b.x_in[:B]
+            if b.first:
+                K.im2col3x3_c3(x.contiguous(), x_in)
+            y = b.y[:B]
+            fused = training and self.conv_stats_fused
+            K.conv_igemm(x_in, b.wf, b.bias, y, stats=b.stats if fused else None, taps=b.taps)
+            if training and not fused:
+                K.bn_stats(y, b.stats)
+            K.bn_relu_pool_fwd(y, b.stats, b.gamma, b.beta, b.running_mean, b.running_var, b.nbt, b.mean, b.invstd,
+                               b.out[:B], s.pool, training)
+        feat = self.blocks[-1].out[:B]
+        K.linear_fwd(feat, self.fc_w, self.fc_b, self.logits[:B])
+        return self.logits[:B]
+
+    def loss_fwd_bwd(self, target: torch.Tensor, grad_scale: float = 1.0, need_grad: bool = True) -> torch.Tensor:
+        """Mean cross-entropy of the last forward's logits; fills dlogits = dL/dlogits * grad_scale."""
+        B = self._B
+        K.cross_entropy(self.logits[:B], target, self.loss, self.dlogits[:B] if need_grad else None, self.correct,
+                        grad_scale)
+        return self.loss
+
+    # ------------------------------------------------------------------ backward
+    def backward(self, dlogits: Optional[torch.Tensor] = None) -> None:
+        """Back-propagate from dlogits (default: the buffer filled by ``loss_fwd_bwd``) and write
+        every parameter gradient into ``flat_grads``.  Calls ``on_bucket_ready(k)`` as soon as the
+        last gradient of bucket k has been *launched* on the current stream."""
+        B = self._B
+        dl = self.dlogits[:B] if dlogits is None else dlogits
+        last = self.blocks[-1]
+        self.flat_grads.zero_()  # split-K weight gradients are accumulated with red.global.add
+        K.linear_bwd(last.out[:B], self.fc_w, dl, self.g_fc_w, self.g_fc_b, last.dout[:B])
+        for i in range(len(self.blocks) - 1, -1, -1):
+            b = self.blocks[i]
+            s = b.spec
+            K.bn_relu_pool_bwd(b.y[:B], b.dout[:B], b.mean, b.invstd, b.gamma, b.beta, b.sums, b.dy[:B], b.g_gamma,
+                               b.g_beta, s.pool)
+            # the conv bias feeds a training-mode BatchNorm, so its exact gradient is zero:
+            # it simply keeps the zero written by the flat_grads clear at the top of backward().
+            K.conv_wgrad(b.dy[:B], b.x_in[:B], b.g_w, taps=b.taps, cin_valid=(27 if b.first else None))
+            if self.on_bucket_ready is not None:
+                for k in self._bucket_of_block.get(i, ()):
+                    self.on_bucket_ready(k)
+            if i > 0:
+                K.conv_igemm(b.dy[:B], b.wd, None, self.blocks[i - 1].dout[:B])
+
+    # ------------------------------------------------------------------ torch.autograd bridge
+    def autograd_forward(self, x: torch.Tensor, training: bool) -> torch.Tensor:
+        params = [p for _, p in self.module.named_parameters()]
+        return _NativeVGGFunction.apply(x, self, training, *params)
+
+
+class _NativeVGGFunction(torch.autograd.Function):
+    """Lets ``loss.backward()`` drive the native backward.  Gradients are *written* into the
+    flat gradient buffer (the tutorial zeroes gradients every iteration, so overwrite ==
+    accumulate-after-zero; ref: master/part1/part1.py:34)."""
+
+    @staticmethod
+    def forward(ctx, x, native: NativeVGG, training: bool, *params):
+        ctx.native = native
+        ctx.training = training
+        logits = native.forward(x, training)
+        return logits.clone()
+
+    @staticmethod
+    def backward(ctx, dlogits):
+        native: NativeVGG = ctx.native
+        if not ctx.training:
+            raise RuntimeError("backward through an eval-mode native forward is not supported")
+        native.backward(dlogits.contiguous().float())
+        grads = []
+        params = dict(native.module.named_parameters())
+        for name, p in native.module.named_parameters():
+            e = native.layout.by_name[name]
+            view = native._view(native.flat_grads, e)
+            if p.grad is not None and p.grad.data_ptr() == view.data_ptr():
+                grads.append(None)      # already in place; returning it would double it
+            else:
+                grads.append(view)      # autograd installs the view as p.grad
+        return (None, None, None, *grads)

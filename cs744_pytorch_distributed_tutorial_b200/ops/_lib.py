@@ -41,6 +41,14 @@ class NativeError(RuntimeError):
     pass
 
 
+# Entry points that do not launch a kernel (bookkeeping); everything else launches exactly one.
+_NON_LAUNCHING = {"b200dp_store_create", "b200dp_store_set", "b200dp_store_get", "b200dp_store_add",
+                  "b200dp_store_barrier", "b200dp_store_destroy", "b200dp_comm_create", "b200dp_comm_destroy",
+                  "b200dp_comm_heap", "b200dp_comm_peer_base", "b200dp_comm_set_timeout", "b200dp_reducer_create",
+                  "b200dp_reducer_set_lr", "b200dp_reducer_finalize", "b200dp_reducer_destroy"}
+launch_count = 0  # kernels of this library launched (or captured) by this process so far
+
+
 def lib() -> ctypes.CDLL:
     """Load (building first if the sources changed) and return the library."""
     global _lib
@@ -83,6 +91,9 @@ def call(name: str, *args) -> None:
     if fn is None:
         raise NativeError(f"{name} is not exported by libb200dp.so")
     rc = fn(*args)
+    if name not in _NON_LAUNCHING:
+        global launch_count
+        launch_count += 1
     if rc != 0:
         msg = lib().b200dp_last_error().decode(errors="replace")
         raise NativeError(f"{name} failed (code {rc}): {msg}")

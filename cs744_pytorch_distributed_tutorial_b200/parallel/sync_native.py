@@ -1,0 +1,177 @@
+"""Gradient synchronisation + optimizer strategies of the B200 path.
+
+Each strategy is the block the tutorial puts between ``backward()`` and the end of
+``optimizer.step()``, implemented with the in-kernel NVLink collectives of
+``csrc/collectives.cu`` on the executor's flat symmetric buffers:
+
+  part1         -> ``LocalSGD``: one fused SGD kernel (ref: master/part1/part1.py:38).
+  part2a        -> ``ParamServerSync``: rank 0 pulls every rank's gradients over NVLink, sums in
+                   rank order, divides by W and pushes the mean back; then the local SGD kernel
+                   (ref: master/part2a/part2a.py:42-53).
+  part2a_extra  -> the same with ``push=True``: workers store into rank 0's staging area first,
+                   the isend/irecv data flow (ref: master/part2a/part2a_extra.py:41-58).
+  part2b        -> ``AllReduceSync``: pre-divide, all-reduce, SGD -- by default ONE two-shot kernel
+                   that reduce-scatters, applies SGD to the owned slice and all-gathers updated
+                   parameters (ref: master/part2b/part2b.py:43-46).
+  part3         -> ``BucketedOverlapSync``: the same fused kernel per bucket, launched on a side
+                   stream the moment a bucket's last gradient is enqueued, overlapping the rest of
+                   backward; BatchNorm buffers broadcast from rank 0 before every forward
+                   (ref: master/part3/part3.py:116-117).
+
+All calls are stream-ordered and host-sync free, hence capturable in the step's CUDA graph.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from ..ops import native as K
+from .comm import CH_BUCKET, CH_MAIN, BucketReducer, Communicator
+
+
+class NativeSync:
+    name = "none"
+    syncs_buffers = False
+
+    def __init__(self, native, comm: Optional[Communicator], lr: float, momentum: float, weight_decay: float,
+                 fuse_optimizer: bool = True):
+        self.native, self.comm = native, comm
+        self.lr, self.momentum, self.weight_decay = lr, momentum, weight_decay
+        self.fuse_optimizer = fuse_optimizer
+        self.world = comm.world if comm is not None else 1
+        self.n = native.layout.total
+
+    def _local_sgd(self) -> None:
+        nv = self.native
+        K.sgd_momentum(nv.flat_params, nv.flat_grads, nv.flat_momentum, self.lr, self.momentum, self.weight_decay)
+
+    def on_init(self) -> None:
+        """Run once after construction, outside any graph capture."""
+
+    def pre_forward(self) -> None:
+        pass
+
+    def sync_and_step(self) -> None:
+        """Synchronise gradients and update parameters (everything after backward())."""
+        raise NotImplementedError
+
+    def sync_only(self) -> None:
+        """Synchronise gradients into ``flat_grads`` without touching the parameters."""
+        raise NotImplementedError
+
+    def close(self) -> None:
+        pass
+
+
+class LocalSGD(NativeSync):
+    name = "none"
+
+    def sync_only(self) -> None:
+        return
+
+    def sync_and_step(self) -> None:
+        self._local_sgd()
+
+
+class ParamServerSync(NativeSync):
+    name = "gather_scatter"
+
+    def __init__(self, *a, push: bool = False, blocks: int = 64, **kw):
+        super().__init__(*a, **kw)
+        self.push = push
+        self.blocks = blocks
+        self.staging = None
+        if push:
+            self.name = "p2p_param_server"
+            self.staging = self.comm.zeros((self.world - 1) * self.n)
+
+    def sync_only(self) -> None:
+        self.comm.ps_reduce_bcast(self.native.flat_grads, 0, self.n, root=0, staging=self.staging, blocks=self.blocks,
+                                  channel=CH_MAIN)
+
+    def sync_and_step(self) -> None:
+        self.sync_only()
+        self._local_sgd()
+
+
+class AllReduceSync(NativeSync):
+    name = "allreduce"
+
+    def __init__(self, *a, blocks: int = 64, algo: int = 0, **kw):
+        super().__init__(*a, **kw)
+        self.blocks, self.algo = blocks, algo
+
+    def sync_only(self) -> None:
+        self.comm.allreduce(self.native.flat_grads, 0, self.n, prescale=True, algo=self.algo, blocks=self.blocks,
+                            channel=CH_MAIN)
+
+    def sync_and_step(self) -> None:
+        nv = self.native
+        if self.fuse_optimizer:
+            self.comm.allreduce(nv.flat_grads, 0, self.n, params=nv.flat_params, momentum_buf=nv.flat_momentum,
+                                lr=self.lr, momentum=self.momentum, weight_decay=self.weight_decay, prescale=True,
+                                algo=self.algo, blocks=self.blocks, channel=CH_MAIN)
+        else:
+            self.sync_only()
+            self._local_sgd()
+
+
+class BucketedOverlapSync(NativeSync):
+    name = "ddp_bucketed"
+    syncs_buffers = True
+
+    def __init__(self, *a, bucket_plan: str = "layer", blocks: int = 16, **kw):
+        super().__init__(*a, **kw)
+        nv = self.native
+        self.buckets = nv.layout.buckets(bucket_plan)
+        nv.set_bucket_plan(self.buckets)
+        fuse = self.fuse_optimizer
+        self.reducer = BucketReducer(self.comm, self.buckets, nv.flat_grads, nv.flat_params if fuse else None,
+                                     nv.flat_momentum if fuse else None, self.lr, self.momentum, self.weight_decay,
+                                     prescale=True, blocks=blocks, channel=CH_BUCKET)
+        nv.on_bucket_ready = self.reducer.bucket_ready
+        self.launch_log = []
+
+    def on_init(self) -> None:
+        # DDP constructor: replicas start identical to rank 0
+        nv = self.native
+        if self.world > 1:
+            self.comm.broadcast(nv.flat_params, root=0, channel=CH_MAIN)
+            self.comm.broadcast(nv.flat_bn, root=0, channel=CH_MAIN)
+            nv.refresh_shadows()
+
+    def pre_forward(self) -> None:
+        # DDP _sync_buffers: rank 0's BatchNorm statistics overwrite everyone's before each forward
+        if self.world > 1:
+            nv = self.native
+            self.comm.broadcast(nv.flat_bn, root=0, blocks=2, channel=CH_MAIN)
+            self.comm.broadcast(nv.flat_nbt_padded, root=0, blocks=1, channel=CH_MAIN)
+
+    def sync_only(self) -> None:
+        self.reducer.finalize()
+
+    def sync_and_step(self) -> None:
+        self.reducer.finalize()
+        if not self.fuse_optimizer:
+            self._local_sgd()
+
+    def close(self) -> None:
+        self.native.on_bucket_ready = None
+        self.reducer.close()
+
+
+def make_native_sync(mode: str, native, comm: Optional[Communicator], cfg) -> NativeSync:
+    kw = dict(lr=cfg.lr, momentum=cfg.momentum, weight_decay=cfg.weight_decay, fuse_optimizer=cfg.fuse_optimizer)
+    world = comm.world if comm is not None else 1
+    if mode == "part1" or (world == 1 and mode != "part3"):
+        return LocalSGD(native, comm, **kw)
+    if mode == "part2a":
+        return ParamServerSync(native, comm, **kw)
+    if mode == "part2a_extra":
+        return ParamServerSync(native, comm, push=True, **kw)
+    if mode == "part2b":
+        return AllReduceSync(native, comm, **kw)
+    if mode == "part3":
+        return BucketedOverlapSync(native, comm, bucket_plan=cfg.bucket_plan, **kw)
+    raise ValueError(mode)

@@ -1,0 +1,644 @@
+// In-kernel NVLink collectives over a symmetric heap (one process per GPU).
+//
+// Memory model: every rank cudaMalloc's one heap of identical size, exports it with CUDA IPC
+// through the rendezvous store and maps every peer's heap; an object allocated at byte offset
+// `o` on one rank lives at `o` on all of them, so a kernel reaches rank r's copy at
+// peer_base[r] + o with plain ld/st.global over NVLink 5 / NVSwitch.  A small signal pad at
+// the start of the heap holds per-(channel, slot, source rank, block) 32-bit flags that are
+// written with st.release.sys and polled with ld.acquire.sys; values are launch epochs that
+// only grow, so the pad never has to be cleared.
+//
+// Kernels:
+//   allreduce_twoshot  reduce-scatter by P2P loads of my 1/W slice from every rank, 1/W scale,
+//                      optional SGD(momentum, weight decay) epilogue on the slice, all-gather by
+//                      P2P stores of the mean gradient or of the UPDATED PARAMETERS.
+//                      (ref: master/part2b/part2b.py:43-45 all_reduce; part3 DDP buckets)
+//   allreduce_oneshot  every rank loads all W copies and reduces locally (latency-optimal for
+//                      small buckets), optional fused SGD.
+//   ps_reduce_bcast    parameter server: rank 0 pulls every rank's gradient, sums in rank order
+//                      starting from zero, divides by W and pushes the mean to every rank
+//                      (ref: master/part2a/part2a.py:42-52); `push` variant: workers store their
+//                      gradients into rank 0's staging area first (the isend/irecv flavour,
+//                      ref: master/part2a/part2a_extra.py:41-58).
+//   broadcast          rank `root` pushes a range to every rank (DDP buffer / module-state sync,
+//                      SURVEY.md 2.6 C11-C12).
+//
+// Every wait is bounded: after `timeout_ns` a block reports which peer / slot / block it was
+// waiting for and traps, so a dead rank surfaces as a CUDA error instead of a hang.
+#include <stdio.h>
+#include <string.h>
+
+#include <string>
+#include <vector>
+
+#include "../include/b200dp.h"
+#include "common.cuh"
+#include "host_util.h"
+
+extern "C" int b200dp_store_set(void* h, const char* key, const void* data, int len);
+extern "C" int b200dp_store_get(void* h, const char* key, void* buf, int cap, int* out_len);
+extern "C" int b200dp_store_barrier(void* h, const char* name);
+
+namespace b200dp {
+
+constexpr int kMaxWorld = 8;
+constexpr int kMaxBlocks = 256;
+constexpr int kNumChannels = 4;
+constexpr int kSlotsPerChannel = 2;  // 0 = entry barrier, 1 = exit barrier
+constexpr size_t kSignalPadBytes =
+    sizeof(uint32_t) * kNumChannels * kSlotsPerChannel * kMaxWorld * kMaxBlocks + 4096;
+
+struct PeerTable {
+  char* base[kMaxWorld];  // peer-mapped heap base addresses, index = rank
+};
+
+struct Comm {
+  int rank = 0, world = 1, device = 0;
+  void* store = nullptr;
+  char* local_base = nullptr;
+  size_t heap_bytes = 0;
+  PeerTable peers{};
+  uint32_t* epochs = nullptr;       // [kNumChannels] launch epoch per channel (device memory, local)
+  uint32_t* done_blocks = nullptr;  // [kNumChannels] finished-block counters
+  unsigned long long timeout_ns = 20ull * 1000 * 1000 * 1000;
+  bool ipc_opened[kMaxWorld] = {false};
+};
+
+struct CommDev {
+  PeerTable peers;
+  int rank, world;
+  uint32_t* epochs;
+  uint32_t* done_blocks;
+  unsigned long long timeout_ns;
+};
+
+B200DP_DEVINL uint32_t* flag_addr(char* heap_base, int channel, int slot, int src_rank, int block) {
+  return reinterpret_cast<uint32_t*>(heap_base) +
+         ((static_cast<size_t>(channel) * kSlotsPerChannel + slot) * kMaxWorld + src_rank) * kMaxBlocks + block;
+}
+
+// All-to-all barrier between block `blockIdx.x` of every rank.  Thread t < world talks to peer t.
+B200DP_DEVINL void rank_barrier(const CommDev& c, int channel, int slot, uint32_t epoch) {
+  __syncthreads();
+  if (threadIdx.x < c.world) {
+    const int peer = threadIdx.x;
+    __threadfence_system();
+    st_release_sys(flag_addr(c.peers.base[peer], channel, slot, c.rank, blockIdx.x), epoch);
+    const uint32_t* mine = flag_addr(c.peers.base[c.rank], channel, slot, peer, blockIdx.x);
+    const uint64_t t0 = globaltimer_ns();
+    while (static_cast<int32_t>(ld_acquire_sys(mine) - epoch) < 0) {
+      if (globaltimer_ns() - t0 > c.timeout_ns) {
+        printf("b200dp: rank %d block %d timed out waiting for rank %d (channel %d slot %d epoch %u, saw %u)\n",
+               c.rank, blockIdx.x, peer, channel, slot, epoch, ld_relaxed_sys(mine));
+        __trap();
+      }
+    }
+  }
+  __syncthreads();
+}
+
+B200DP_DEVINL uint32_t begin_collective(const CommDev& c, int channel) {
+  return *reinterpret_cast<volatile uint32_t*>(c.epochs + channel) + 1;
+}
+
+// The last block to finish publishes the new epoch for the next launch on this channel.
+B200DP_DEVINL void end_collective(const CommDev& c, int channel, uint32_t epoch) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const uint32_t prev = atomicAdd(c.done_blocks + channel, 1u);
+    if (prev == gridDim.x - 1) {
+      c.done_blocks[channel] = 0;
+      __threadfence();
+      *reinterpret_cast<volatile uint32_t*>(c.epochs + channel) = epoch;
+    }
+  }
+}
+
+B200DP_DEVINL float4 ld_peer_f4(const float* p) { return __ldcg(reinterpret_cast<const float4*>(p)); }
+B200DP_DEVINL void st_peer_f4(float* p, const float4& v) { __stcg(reinterpret_cast<float4*>(p), v); }
+
+struct SgdHyper {
+  float lr, momentum, weight_decay;
+};
+
+B200DP_DEVINL float4 sgd4(float4 g, float4& p, float4& m, const SgdHyper& h) {
+  m.x = fmaf(h.momentum, m.x, fmaf(h.weight_decay, p.x, g.x));
+  m.y = fmaf(h.momentum, m.y, fmaf(h.weight_decay, p.y, g.y));
+  m.z = fmaf(h.momentum, m.z, fmaf(h.weight_decay, p.z, g.z));
+  m.w = fmaf(h.momentum, m.w, fmaf(h.weight_decay, p.w, g.w));
+  p.x = fmaf(-h.lr, m.x, p.x);
+  p.y = fmaf(-h.lr, m.y, p.y);
+  p.z = fmaf(-h.lr, m.z, p.z);
+  p.w = fmaf(-h.lr, m.w, p.w);
+  return p;
+}
+
+struct RangeArgs {
+  size_t grad_off;   // byte offset of the flat gradient buffer inside the heap
+  size_t param_off;  // byte offset of the flat parameter buffer (fused SGD)
+  size_t mom_off;    // byte offset of the flat momentum buffer (fused SGD)
+  size_t stage_off;  // byte offset of the parameter-server staging area (push variant)
+  long start, end;   // element range [start, end) of the flat buffers; multiples of 4
+  int channel;
+  int root;
+  SgdHyper sgd;
+};
+
+// ---------------------------------------------------------------------------
+// two-shot all-reduce: reduce-scatter -> (scale, SGD) -> all-gather
+// ---------------------------------------------------------------------------
+template <bool FUSE_SGD, bool PRESCALE>
+__global__ void __launch_bounds__(512) allreduce_twoshot_kernel(const CommDev c, const RangeArgs a) {
+  const uint32_t epoch = begin_collective(c, a.channel);
+  rank_barrier(c, a.channel, 0, epoch);
+  const int W = c.world;
+  const long n4 = (a.end - a.start) >> 2;           // float4 elements in the bucket
+  const long per = (n4 + W - 1) / W;                // slice length per rank
+  const long lo = min(per * c.rank, n4), hi = min(lo + per, n4);
+  const float inv_w = 1.f / static_cast<float>(W);
+  for (long i = lo + blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < hi;
+       i += static_cast<long>(gridDim.x) * blockDim.x) {
+    const size_t eoff = static_cast<size_t>(a.start + (i << 2)) * sizeof(float);
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int r = 0; r < kMaxWorld; ++r) {
+      if (r < W) {
+        float4 v = ld_peer_f4(reinterpret_cast<const float*>(c.peers.base[r] + a.grad_off + eoff));
+        if (PRESCALE) {  // divide-then-sum, the order of part2b / DDP
+          v.x *= inv_w; v.y *= inv_w; v.z *= inv_w; v.w *= inv_w;
+        }
+        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+      }
+    }
+    if (!PRESCALE) {
+      acc.x *= inv_w; acc.y *= inv_w; acc.z *= inv_w; acc.w *= inv_w;
+    }
+    if (FUSE_SGD) {
+      char* me = c.peers.base[c.rank];
+      float4 p = *reinterpret_cast<const float4*>(me + a.param_off + eoff);
+      float4 m = *reinterpret_cast<const float4*>(me + a.mom_off + eoff);
+      const float4 np = sgd4(acc, p, m, a.sgd);
+      *reinterpret_cast<float4*>(me + a.mom_off + eoff) = m;
+      *reinterpret_cast<float4*>(me + a.grad_off + eoff) = acc;  // owner keeps the mean gradient
+#pragma unroll
+      for (int r = 0; r < kMaxWorld; ++r)
+        if (r < W) st_peer_f4(reinterpret_cast<float*>(c.peers.base[r] + a.param_off + eoff), np);
+    } else {
+#pragma unroll
+      for (int r = 0; r < kMaxWorld; ++r)
+        if (r < W) st_peer_f4(reinterpret_cast<float*>(c.peers.base[r] + a.grad_off + eoff), acc);
+    }
+  }
+  rank_barrier(c, a.channel, 1, epoch);
+  end_collective(c, a.channel, epoch);
+}
+
+// ---------------------------------------------------------------------------
+// one-shot all-reduce: every rank reduces the whole range locally.  The range must fit in one
+// pass (gridDim.x * blockDim.x float4's) so that the read and write phases are separated by a
+// single barrier.
+// ---------------------------------------------------------------------------
+template <bool FUSE_SGD, bool PRESCALE>
+__global__ void __launch_bounds__(512) allreduce_oneshot_kernel(const CommDev c, const RangeArgs a) {
+  const uint32_t epoch = begin_collective(c, a.channel);
+  rank_barrier(c, a.channel, 0, epoch);
+  const int W = c.world;
+  const long n4 = (a.end - a.start) >> 2;
+  const long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x;
+  const float inv_w = 1.f / static_cast<float>(W);
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  const size_t eoff = static_cast<size_t>(a.start + (i << 2)) * sizeof(float);
+  if (i < n4) {
+#pragma unroll
+    for (int r = 0; r < kMaxWorld; ++r) {
+      if (r < W) {
+        float4 v = ld_peer_f4(reinterpret_cast<const float*>(c.peers.base[r] + a.grad_off + eoff));
+        if (PRESCALE) {
+          v.x *= inv_w; v.y *= inv_w; v.z *= inv_w; v.w *= inv_w;
+        }
+        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+      }
+    }
+    if (!PRESCALE) {
+      acc.x *= inv_w; acc.y *= inv_w; acc.z *= inv_w; acc.w *= inv_w;
+    }
+  }
+  // every rank has finished reading block-partition `blockIdx.x` of every peer before anyone overwrites it
+  rank_barrier(c, a.channel, 1, epoch);
+  if (i < n4) {
+    char* me = c.peers.base[c.rank];
+    *reinterpret_cast<float4*>(me + a.grad_off + eoff) = acc;
+    if (FUSE_SGD) {
+      float4 p = *reinterpret_cast<const float4*>(me + a.param_off + eoff);
+      float4 m = *reinterpret_cast<const float4*>(me + a.mom_off + eoff);
+      sgd4(acc, p, m, a.sgd);
+      *reinterpret_cast<float4*>(me + a.mom_off + eoff) = m;
+      *reinterpret_cast<float4*>(me + a.param_off + eoff) = p;
+    }
+  }
+  end_collective(c, a.channel, epoch);
+}
+
+// ---------------------------------------------------------------------------
+// parameter server (rank `root` reduces, everyone receives the mean)
+// ---------------------------------------------------------------------------
+template <bool PUSH>
+__global__ void __launch_bounds__(512) ps_reduce_bcast_kernel(const CommDev c, const RangeArgs a) {
+  const uint32_t epoch = begin_collective(c, a.channel);
+  const int W = c.world;
+  const long n4 = (a.end - a.start) >> 2;
+  const long stride = static_cast<long>(gridDim.x) * blockDim.x;
+  const long first = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x;
+  if (PUSH && c.rank != a.root) {
+    // worker "isend": store my gradient into my slot of the root's staging area
+    const int slot = c.rank < a.root ? c.rank : c.rank - 1;
+    char* dst = c.peers.base[a.root] + a.stage_off + static_cast<size_t>(slot) * (n4 << 4);
+    const char* src = c.peers.base[c.rank] + a.grad_off + static_cast<size_t>(a.start) * sizeof(float);
+    for (long i = first; i < n4; i += stride)
+      st_peer_f4(reinterpret_cast<float*>(dst + (i << 4)), *reinterpret_cast<const float4*>(src + (i << 4)));
+  }
+  rank_barrier(c, a.channel, 0, epoch);
+  if (c.rank == a.root) {
+    const float wf = static_cast<float>(W);
+    for (long i = first; i < n4; i += stride) {
+      const size_t eoff = static_cast<size_t>(a.start + (i << 2)) * sizeof(float);
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int r = 0; r < kMaxWorld; ++r) {
+        if (r < W) {
+          float4 v;
+          if (PUSH && r != a.root) {
+            const int slot = r < a.root ? r : r - 1;
+            v = *reinterpret_cast<const float4*>(c.peers.base[a.root] + a.stage_off +
+                                                 static_cast<size_t>(slot) * (n4 << 4) + (i << 4));
+          } else {
+            v = ld_peer_f4(reinterpret_cast<const float*>(c.peers.base[r] + a.grad_off + eoff));
+          }
+          acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+        }
+      }
+      // sum first, then a true division, exactly like `grad_sum / 4`
+      acc.x /= wf; acc.y /= wf; acc.z /= wf; acc.w /= wf;
+#pragma unroll
+      for (int r = 0; r < kMaxWorld; ++r)
+        if (r < W) st_peer_f4(reinterpret_cast<float*>(c.peers.base[r] + a.grad_off + eoff), acc);
+    }
+  }
+  rank_barrier(c, a.channel, 1, epoch);
+  end_collective(c, a.channel, epoch);
+}
+
+// ---------------------------------------------------------------------------
+// broadcast of a byte range (multiple of 16) at heap offset grad_off from `root`
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(512) broadcast_kernel(const CommDev c, const RangeArgs a) {
+  const uint32_t epoch = begin_collective(c, a.channel);
+  rank_barrier(c, a.channel, 0, epoch);
+  if (c.rank == a.root) {
+    const long n4 = (a.end - a.start) >> 2;
+    const long stride = static_cast<long>(gridDim.x) * blockDim.x;
+    for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < n4; i += stride) {
+      const size_t eoff = static_cast<size_t>(a.start + (i << 2)) * sizeof(float);
+      const float4 v = *reinterpret_cast<const float4*>(c.peers.base[c.rank] + a.grad_off + eoff);
+      for (int r = 0; r < c.world; ++r)
+        if (r != c.rank) st_peer_f4(reinterpret_cast<float*>(c.peers.base[r] + a.grad_off + eoff), v);
+    }
+  }
+  rank_barrier(c, a.channel, 1, epoch);
+  end_collective(c, a.channel, epoch);
+}
+
+__global__ void barrier_kernel(const CommDev c, int channel) {
+  const uint32_t epoch = begin_collective(c, channel);
+  rank_barrier(c, channel, 0, epoch);
+  end_collective(c, channel, epoch);
+}
+
+static CommDev dev_view(const Comm* c) {
+  CommDev d;
+  d.peers = c->peers;
+  d.rank = c->rank;
+  d.world = c->world;
+  d.epochs = c->epochs;
+  d.done_blocks = c->done_blocks;
+  d.timeout_ns = c->timeout_ns;
+  return d;
+}
+
+static int check_range(const Comm* c, long start, long end, int blocks, int channel, const char* what) {
+  if (!c) {
+    set_error("%s: null communicator", what);
+    return B200DP_EINVAL;
+  }
+  if (start < 0 || end < start || (start & 3) || (end & 3)) {
+    set_error("%s: element range [%ld, %ld) must be non-negative and a multiple of 4", what, start, end);
+    return B200DP_EINVAL;
+  }
+  if (blocks < 1 || blocks > kMaxBlocks) {
+    set_error("%s: blocks=%d outside [1, %d]", what, blocks, kMaxBlocks);
+    return B200DP_EINVAL;
+  }
+  if (channel < 0 || channel >= kNumChannels) {
+    set_error("%s: channel=%d outside [0, %d)", what, channel, kNumChannels);
+    return B200DP_EINVAL;
+  }
+  return 0;
+}
+
+}  // namespace b200dp
+
+using namespace b200dp;
+
+// ---------------------------------------------------------------------------
+// communicator / symmetric heap
+// ---------------------------------------------------------------------------
+extern "C" int b200dp_comm_create(void* store, int rank, int world, int device, long long heap_bytes,
+                                  void** out_comm) {
+  if (world < 1 || world > kMaxWorld || rank < 0 || rank >= world || heap_bytes <= 0 || !out_comm) {
+    set_error("comm_create: bad arguments (rank %d, world %d, heap %lld bytes; world <= %d)", rank, world,
+              heap_bytes, kMaxWorld);
+    return B200DP_EINVAL;
+  }
+  if (world > 1 && store == nullptr) {
+    set_error("comm_create: a rendezvous store is required for world > 1");
+    return B200DP_EINVAL;
+  }
+  B200DP_CUDA_TRY(cudaSetDevice(device));
+  auto* c = new Comm();
+  c->rank = rank;
+  c->world = world;
+  c->device = device;
+  c->store = store;
+  c->heap_bytes = ((static_cast<size_t>(heap_bytes) + kSignalPadBytes + (2u << 20) - 1) >> 21) << 21;
+  B200DP_CUDA_TRY(cudaMalloc(reinterpret_cast<void**>(&c->local_base), c->heap_bytes));
+  B200DP_CUDA_TRY(cudaMemset(c->local_base, 0, c->heap_bytes));
+  B200DP_CUDA_TRY(cudaMalloc(reinterpret_cast<void**>(&c->epochs), 2 * kNumChannels * sizeof(uint32_t)));
+  B200DP_CUDA_TRY(cudaMemset(c->epochs, 0, 2 * kNumChannels * sizeof(uint32_t)));
+  c->done_blocks = c->epochs + kNumChannels;
+  B200DP_CUDA_TRY(cudaDeviceSynchronize());
+  c->peers.base[rank] = c->local_base;
+  if (world > 1) {
+    cudaIpcMemHandle_t mine;
+    B200DP_CUDA_TRY(cudaIpcGetMemHandle(&mine, c->local_base));
+    static int generation = 0;
+    const std::string prefix = "heap/" + std::to_string(generation++) + "/";
+    int rc = b200dp_store_set(store, (prefix + std::to_string(rank)).c_str(), &mine, sizeof(mine));
+    if (rc) return rc;
+    for (int r = 0; r < world; ++r) {
+      if (r == rank) continue;
+      cudaIpcMemHandle_t h;
+      int len = 0;
+      rc = b200dp_store_get(store, (prefix + std::to_string(r)).c_str(), &h, sizeof(h), &len);
+      if (rc) return rc;
+      void* p = nullptr;
+      cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+      if (e != cudaSuccess) {
+        set_error("comm_create: rank %d cannot map rank %d's heap over CUDA IPC: %s", rank, r,
+                  cudaGetErrorString(e));
+        return static_cast<int>(e);
+      }
+      c->peers.base[r] = static_cast<char*>(p);
+      c->ipc_opened[r] = true;
+    }
+    rc = b200dp_store_barrier(store, "comm_create");
+    if (rc) return rc;
+  }
+  *out_comm = c;
+  return 0;
+}
+
+extern "C" int b200dp_comm_destroy(void* comm) {
+  auto* c = static_cast<Comm*>(comm);
+  if (!c) return 0;
+  cudaSetDevice(c->device);
+  cudaDeviceSynchronize();
+  if (c->world > 1 && c->store) b200dp_store_barrier(c->store, "comm_destroy");
+  for (int r = 0; r < c->world; ++r)
+    if (c->ipc_opened[r]) cudaIpcCloseMemHandle(c->peers.base[r]);
+  if (c->world > 1 && c->store) b200dp_store_barrier(c->store, "comm_destroy2");
+  cudaFree(c->local_base);
+  cudaFree(c->epochs);
+  delete c;
+  return 0;
+}
+
+/* Local address of the first usable byte of the heap (after the signal pad) and its size. */
+extern "C" int b200dp_comm_heap(void* comm, void** base, long long* usable_bytes, long long* data_offset) {
+  auto* c = static_cast<Comm*>(comm);
+  if (!c) return B200DP_EINVAL;
+  if (base) *base = c->local_base;
+  if (data_offset) *data_offset = static_cast<long long>(kSignalPadBytes);
+  if (usable_bytes) *usable_bytes = static_cast<long long>(c->heap_bytes - kSignalPadBytes);
+  return 0;
+}
+
+extern "C" int b200dp_comm_peer_base(void* comm, int rank, void** base) {
+  auto* c = static_cast<Comm*>(comm);
+  if (!c || rank < 0 || rank >= c->world) return B200DP_EINVAL;
+  *base = c->peers.base[rank];
+  return 0;
+}
+
+extern "C" int b200dp_comm_set_timeout(void* comm, double seconds) {
+  auto* c = static_cast<Comm*>(comm);
+  if (!c || seconds <= 0) return B200DP_EINVAL;
+  c->timeout_ns = static_cast<unsigned long long>(seconds * 1e9);
+  return 0;
+}
+
+extern "C" int b200dp_comm_barrier(void* comm, int channel, b200dp_stream_t stream) {
+  auto* c = static_cast<Comm*>(comm);
+  int rc = check_range(c, 0, 0, 1, channel, "comm_barrier");
+  if (rc) return rc;
+  barrier_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(dev_view(c), channel);
+  B200DP_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+// algo: 0 = choose, 1 = one-shot, 2 = two-shot
+extern "C" int b200dp_allreduce(void* comm, long long grad_off, long long param_off, long long mom_off,
+                                long long start, long long end, int fuse_sgd, int prescale, float lr,
+                                float momentum, float weight_decay, int algo, int blocks, int channel,
+                                b200dp_stream_t stream_) {
+  auto* c = static_cast<Comm*>(comm);
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  const int threads = 512;
+  const long n4 = (end - start) >> 2;
+  if (algo == 0) algo = (n4 * 16 <= 256 * 1024) ? 1 : 2;
+  if (algo == 1) {
+    blocks = static_cast<int>((n4 + threads - 1) / threads);
+    if (blocks < 1) blocks = 1;
+    if (blocks > kMaxBlocks) algo = 2;  // does not fit in one pass
+  }
+  if (algo == 2 && blocks <= 0) blocks = 64;
+  int rc = check_range(c, start, end, blocks, channel, "allreduce");
+  if (rc) return rc;
+  RangeArgs a{};
+  a.grad_off = static_cast<size_t>(grad_off);
+  a.param_off = static_cast<size_t>(param_off);
+  a.mom_off = static_cast<size_t>(mom_off);
+  a.start = start;
+  a.end = end;
+  a.channel = channel;
+  a.sgd = SgdHyper{lr, momentum, weight_decay};
+  const CommDev d = dev_view(c);
+#define B200DP_LAUNCH_AR(KERN)                                                       \
+  do {                                                                               \
+    if (fuse_sgd && prescale) KERN<true, true><<<blocks, threads, 0, stream>>>(d, a); \
+    else if (fuse_sgd) KERN<true, false><<<blocks, threads, 0, stream>>>(d, a);       \
+    else if (prescale) KERN<false, true><<<blocks, threads, 0, stream>>>(d, a);       \
+    else KERN<false, false><<<blocks, threads, 0, stream>>>(d, a);                    \
+  } while (0)
+  if (algo == 1)
+    B200DP_LAUNCH_AR(allreduce_oneshot_kernel);
+  else
+    B200DP_LAUNCH_AR(allreduce_twoshot_kernel);
+#undef B200DP_LAUNCH_AR
+  B200DP_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200dp_ps_reduce_bcast(void* comm, long long grad_off, long long stage_off, long long start,
+                                      long long end, int root, int push, int blocks, int channel,
+                                      b200dp_stream_t stream_) {
+  auto* c = static_cast<Comm*>(comm);
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (blocks <= 0) blocks = 64;
+  int rc = check_range(c, start, end, blocks, channel, "ps_reduce_bcast");
+  if (rc) return rc;
+  if (root < 0 || root >= c->world) {
+    set_error("ps_reduce_bcast: root %d outside the world of %d", root, c->world);
+    return B200DP_EINVAL;
+  }
+  RangeArgs a{};
+  a.grad_off = static_cast<size_t>(grad_off);
+  a.stage_off = static_cast<size_t>(stage_off);
+  a.start = start;
+  a.end = end;
+  a.channel = channel;
+  a.root = root;
+  const CommDev d = dev_view(c);
+  if (push)
+    ps_reduce_bcast_kernel<true><<<blocks, 512, 0, stream>>>(d, a);
+  else
+    ps_reduce_bcast_kernel<false><<<blocks, 512, 0, stream>>>(d, a);
+  B200DP_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200dp_broadcast(void* comm, long long byte_off, long long nbytes, int root, int blocks,
+                                int channel, b200dp_stream_t stream_) {
+  auto* c = static_cast<Comm*>(comm);
+  if (blocks <= 0) blocks = nbytes > (1 << 20) ? 64 : 4;
+  if (nbytes & 15) {
+    set_error("broadcast: nbytes=%lld must be a multiple of 16", nbytes);
+    return B200DP_EINVAL;
+  }
+  int rc = check_range(c, 0, nbytes / 4, blocks, channel, "broadcast");
+  if (rc) return rc;
+  RangeArgs a{};
+  a.grad_off = static_cast<size_t>(byte_off);
+  a.start = 0;
+  a.end = nbytes / 4;
+  a.channel = channel;
+  a.root = root;
+  broadcast_kernel<<<blocks, 512, 0, static_cast<cudaStream_t>(stream_)>>>(dev_view(c), a);
+  B200DP_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+// ---------------------------------------------------------------------------
+// Bucket reducer: the framework-owned counterpart of DDP's C++ Reducer
+// (ref: master/part3/part3.py:116).  Gradients already live in the flat
+// symmetric buffer, so "mark ready" is just: record an event on the compute stream, make the
+// high-priority side stream wait on it, and launch that bucket's fused all-reduce(+SGD) there
+// with a capped number of CTAs so that the backward GEMMs keep most of the SMs.  finalize()
+// joins the side stream back into the compute stream.  All of it is stream-ordered and
+// capturable in a CUDA graph (fork = event record + wait, join = the reverse).
+// ---------------------------------------------------------------------------
+namespace b200dp {
+struct Reducer {
+  Comm* comm = nullptr;
+  std::vector<long long> start, end;
+  long long grad_off = 0, param_off = 0, mom_off = 0;
+  int fuse_sgd = 0, prescale = 1, blocks = 16, channel = 1;
+  float lr = 0.1f, momentum = 0.9f, weight_decay = 1e-4f;
+  cudaStream_t side = nullptr;
+  std::vector<cudaEvent_t> ready;
+  cudaEvent_t done = nullptr;
+  int launched = 0;
+};
+}  // namespace b200dp
+
+extern "C" int b200dp_reducer_create(void* comm, int n_buckets, const long long* starts, const long long* ends,
+                                     long long grad_off, long long param_off, long long mom_off, int fuse_sgd,
+                                     int prescale, float lr, float momentum, float weight_decay, int blocks,
+                                     int channel, void** out) {
+  if (!comm || n_buckets < 1 || !starts || !ends || !out) {
+    set_error("reducer_create: bad arguments");
+    return B200DP_EINVAL;
+  }
+  auto* r = new Reducer();
+  r->comm = static_cast<Comm*>(comm);
+  r->start.assign(starts, starts + n_buckets);
+  r->end.assign(ends, ends + n_buckets);
+  r->grad_off = grad_off;
+  r->param_off = param_off;
+  r->mom_off = mom_off;
+  r->fuse_sgd = fuse_sgd;
+  r->prescale = prescale;
+  r->lr = lr;
+  r->momentum = momentum;
+  r->weight_decay = weight_decay;
+  r->blocks = blocks > 0 ? blocks : 16;
+  r->channel = channel;
+  int lo = 0, hi = 0;
+  B200DP_CUDA_TRY(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+  B200DP_CUDA_TRY(cudaStreamCreateWithPriority(&r->side, cudaStreamNonBlocking, hi));
+  r->ready.resize(n_buckets);
+  for (auto& e : r->ready) B200DP_CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  B200DP_CUDA_TRY(cudaEventCreateWithFlags(&r->done, cudaEventDisableTiming));
+  *out = r;
+  return 0;
+}
+
+extern "C" int b200dp_reducer_set_lr(void* reducer, float lr) {
+  auto* r = static_cast<Reducer*>(reducer);
+  if (!r) return B200DP_EINVAL;
+  r->lr = lr;
+  return 0;
+}
+
+extern "C" int b200dp_reducer_bucket_ready(void* reducer, int k, b200dp_stream_t compute_stream) {
+  auto* r = static_cast<Reducer*>(reducer);
+  if (!r || k < 0 || k >= static_cast<int>(r->ready.size())) {
+    set_error("reducer_bucket_ready: bucket %d out of range", k);
+    return B200DP_EINVAL;
+  }
+  B200DP_CUDA_TRY(cudaEventRecord(r->ready[k], static_cast<cudaStream_t>(compute_stream)));
+  B200DP_CUDA_TRY(cudaStreamWaitEvent(r->side, r->ready[k], 0));
+  ++r->launched;
+  return b200dp_allreduce(r->comm, r->grad_off, r->param_off, r->mom_off, r->start[k], r->end[k], r->fuse_sgd,
+                          r->prescale, r->lr, r->momentum, r->weight_decay, 0, r->blocks, r->channel, r->side);
+}
+
+extern "C" int b200dp_reducer_finalize(void* reducer, b200dp_stream_t compute_stream) {
+  auto* r = static_cast<Reducer*>(reducer);
+  if (!r) return B200DP_EINVAL;
+  B200DP_CUDA_TRY(cudaEventRecord(r->done, r->side));
+  B200DP_CUDA_TRY(cudaStreamWaitEvent(static_cast<cudaStream_t>(compute_stream), r->done, 0));
+  r->launched = 0;
+  return 0;
+}
+
+extern "C" int b200dp_reducer_destroy(void* reducer) {
+  auto* r = static_cast<Reducer*>(reducer);
+  if (!r) return 0;
+  cudaStreamSynchronize(r->side);
+  for (auto& e : r->ready) cudaEventDestroy(e);
+  cudaEventDestroy(r->done);
+  cudaStreamDestroy(r->side);
+  delete r;
+  return 0;
+}

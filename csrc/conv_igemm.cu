@@ -571,7 +571,7 @@ extern "C" int b200dp_conv_wgrad(const void* dy, const void* x, float* dw, int B
   WgradParams p{};
   p.H = H;
   p.W = W;
-  if (tile_geometry(H, W, 64, &p.TH, &p.TN) != 0 || (static_cast<long>(B) * H * W) % 64 != 0) {
+  if (tile_geometry(H, W, 64, &p.TH, &p.TN) != 0) {
     set_error("conv_wgrad: B=%d H=%d W=%d cannot be tiled into 64-pixel blocks", B, H, W);
     return B200DP_EINVAL;
   }
@@ -582,7 +582,9 @@ extern "C" int b200dp_conv_wgrad(const void* dy, const void* x, float* dw, int B
   p.co_tiles = (Cout + kBlockM - 1) / kBlockM;
   p.ci_tiles = Cin / block_n;
   p.a_boxes = (Cout >= 128) ? 2 : 1;
-  p.kblocks_total = (B * H * W) / 64;
+  // A K block is 64 pixels; when a block spans whole images (TN > 1) the last one may hang over
+  // the end of the batch -- the tensor maps are sized to B, so TMA zero-fills the overhang.
+  p.kblocks_total = (p.TN > 1) ? (B + p.TN - 1) / p.TN : (B * H * W) / 64;
   const int tiles = taps * p.co_tiles * p.ci_tiles;
   if (split_k <= 0) {
     split_k = (148 + tiles - 1) / tiles;

@@ -118,6 +118,67 @@ int b200dp_sgd_momentum(float* p, const float* g, float* buf, long long n, float
 int b200dp_prep_conv_weights(const float* master, void* wf, void* wd, int Cout, int Cin, int taps, int kpad,
                              b200dp_stream_t stream);
 
+/* ------------------------------------------------------------------------
+ * Rendezvous store (TCP key-value, rank 0 hosts it on master_ip:port)
+ * (ref: master/part2a/part2a.py:80-85 init_process_group via MASTER_ADDR/MASTER_PORT)
+ * ------------------------------------------------------------------------ */
+int b200dp_store_create(const char* master_ip, int port, int rank, int world, int timeout_ms, void** out_store);
+int b200dp_store_set(void* store, const char* key, const void* data, int len);
+/* Blocks until the key exists (or the store's timeout expires -> B200DP_ETIMEDOUT). */
+int b200dp_store_get(void* store, const char* key, void* buf, int cap, int* out_len);
+int b200dp_store_add(void* store, const char* key, long long delta, long long* result);
+int b200dp_store_barrier(void* store, const char* name);
+int b200dp_store_destroy(void* store);
+
+/* ------------------------------------------------------------------------
+ * Communicator: symmetric heap mapped into every rank over CUDA IPC + signal pad.
+ * Offsets passed to the collectives are BYTE offsets from the heap base and are
+ * identical on every rank.  `channel` (0..3) selects an independent set of flags
+ * and epoch counter; launches on one channel must be stream-ordered on each rank
+ * and issued in the same order by all ranks.
+ * ------------------------------------------------------------------------ */
+int b200dp_comm_create(void* store, int rank, int world, int device, long long heap_bytes, void** out_comm);
+int b200dp_comm_destroy(void* comm);
+int b200dp_comm_heap(void* comm, void** base, long long* usable_bytes, long long* data_offset);
+int b200dp_comm_peer_base(void* comm, int rank, void** base);
+int b200dp_comm_set_timeout(void* comm, double seconds);
+int b200dp_comm_barrier(void* comm, int channel, b200dp_stream_t stream);
+
+/* Gradient all-reduce (mean) over elements [start, end) of the flat fp32 gradient buffer at
+ * byte offset grad_off (ref: master/part2b/part2b.py:43-45; DDP buckets master/part3/part3.py:116).
+ * algo 0 = choose by size, 1 = one-shot (every rank reduces everything), 2 = two-shot
+ * (reduce-scatter + all-gather).  prescale=1 divides before summing (part2b / DDP order).
+ * fuse_sgd=1 applies SGD(momentum, weight decay) in the epilogue to the parameters at
+ * param_off / momentum at mom_off; the two-shot variant then all-gathers updated PARAMETERS. */
+int b200dp_allreduce(void* comm, long long grad_off, long long param_off, long long mom_off, long long start,
+                     long long end, int fuse_sgd, int prescale, float lr, float momentum, float weight_decay,
+                     int algo, int blocks, int channel, b200dp_stream_t stream);
+
+/* Parameter server: `root` sums every rank's gradient in rank order starting from zero, divides
+ * by the world size and stores the mean into every rank's gradient buffer
+ * (ref: master/part2a/part2a.py:42-52).  push=1: workers first store their gradients into the
+ * root's staging area at stage_off ((world-1) * range bytes), the isend/irecv data flow of
+ * master/part2a/part2a_extra.py:41-58. */
+int b200dp_ps_reduce_bcast(void* comm, long long grad_off, long long stage_off, long long start, long long end,
+                           int root, int push, int blocks, int channel, b200dp_stream_t stream);
+
+/* Copy nbytes (multiple of 16) at heap byte offset byte_off from `root` to every rank
+ * (DDP module-state and per-forward BatchNorm buffer sync). */
+int b200dp_broadcast(void* comm, long long byte_off, long long nbytes, int root, int blocks, int channel,
+                     b200dp_stream_t stream);
+
+/* Bucket reducer (the role of DDP's C++ Reducer, ref: master/part3/part3.py:116): per-bucket
+ * all-reduce(+SGD) on a high-priority side stream with a capped CTA count, forked from and
+ * joined back into the compute stream with events (CUDA-graph capturable). */
+int b200dp_reducer_create(void* comm, int n_buckets, const long long* starts, const long long* ends,
+                          long long grad_off, long long param_off, long long mom_off, int fuse_sgd,
+                          int prescale, float lr, float momentum, float weight_decay, int blocks, int channel,
+                          void** out_reducer);
+int b200dp_reducer_set_lr(void* reducer, float lr);
+int b200dp_reducer_bucket_ready(void* reducer, int bucket, b200dp_stream_t compute_stream);
+int b200dp_reducer_finalize(void* reducer, b200dp_stream_t compute_stream);
+int b200dp_reducer_destroy(void* reducer);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,286 @@
+#!/usr/bin/env python
+"""Headline benchmark: VGG-11 / CIFAR-10-shaped training throughput (images/s) on N B200s.
+
+    python bench.py --gpus 1 --steps 50 --warmup 5                       # this framework
+    python bench.py --impl reference --gpus 1 --steps 50 --warmup 5      # the tutorial's own code
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 \
+        --master-port 29511 bench.py --gpus 8 --steps 50 --warmup 5
+
+Metric and config are the ones BASELINE.json names: VGG-11, synthetic CIFAR-10-shaped data,
+random-init weights, SGD(lr 0.1, momentum 0.9, wd 1e-4), mode part3 (bucketed all-reduce overlapped
+with backward).  Default scaling is *weak* at 256 images per GPU, bf16 compute with fp32 master
+weights (BASELINE.json config 5); ``--scaling strong`` fixes the global batch at 256 instead.
+
+One JSON line is printed by rank 0.  ``value`` is the device-timed whole-job images/s over exactly
+K steps (CUDA events, barrier + synchronize on both sides, max over ranks); ``e2e`` repeats the
+measurement through ``Trainer.train_step`` with a pinned-host -> device copy of every step's batch
+and a device -> host read of every step's loss inside the timed region.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks during the timed region (NVML; same fields as the nvidia-smi query of the profiling recipe)
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    REASONS = {
+        0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
+        0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+        0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting",
+    }
+
+    def __init__(self, index: int, period_s: float = 0.02):
+        self.samples, self.reasons = [], set()
+        self.max_mhz = None
+        self._stop = threading.Event()
+        self._thread = None
+        self.period = period_s
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _sample(self):
+        try:
+            self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+            mask = self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+            for bit, name in self.REASONS.items():
+                if mask & bit and name != "gpu_idle":
+                    self.reasons.add(name)
+        except Exception:
+            pass
+
+    def start(self):
+        if self.nv is None:
+            return
+        self._stop.clear()
+
+        def loop():
+            while not self._stop.is_set():
+                self._sample()
+                time.sleep(self.period)
+        self._thread = threading.Thread(target=loop, daemon=True)
+        self._thread.start()
+
+    def stop(self):
+        if self._thread is not None:
+            self._sample()
+            self._stop.set()
+            self._thread.join()
+            self._thread = None
+
+    def summary(self) -> dict:
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+        return {"sm_mhz": statistics.median(self.samples), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(self.samples)}
+
+
+def env_int(name: str, default: int) -> int:
+    return int(os.environ.get(name, default))
+
+
+def parse_args():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=50)
+    p.add_argument("--warmup", type=int, default=5)
+    p.add_argument("--impl", choices=("native", "reference"), default="native")
+    p.add_argument("--mode", default="part3", choices=("part1", "part2a", "part2a_extra", "part2b", "part3"))
+    p.add_argument("--scaling", choices=("weak", "strong"), default="weak")
+    p.add_argument("--per-gpu-batch", type=int, default=256)
+    p.add_argument("--global-batch", type=int, default=256, help="used with --scaling strong")
+    p.add_argument("--bucket-plan", default="layer")
+    p.add_argument("--no-e2e", action="store_true")
+    p.add_argument("--port", type=int, default=None)
+    return p.parse_args()
+
+
+def working_set_mb(arch_blocks, batch: int) -> float:
+    """Bytes a training step streams through (activations bf16 fwd+bwd, weights/grads/momentum fp32)."""
+    act = 0
+    for s in arch_blocks:
+        hw = s.hw * s.hw
+        act += batch * hw * s.cout * 2 * 2                      # y and dy
+        act += batch * (hw // 4 if s.pool else hw) * s.cout * 2 * 2  # out and dout
+    params = 9_231_114 * 4 * 3 + 9_231_114 * 2 * 2               # fp32 p/g/m + bf16 Wf/Wd
+    return (act + params) / 1e6
+
+
+def run_native(args) -> dict:
+    from cs744_pytorch_distributed_tutorial_b200.config import TrainConfig
+    from cs744_pytorch_distributed_tutorial_b200.engine import Trainer
+    from cs744_pytorch_distributed_tutorial_b200.ops import _lib
+
+    world = env_int("WORLD_SIZE", 1)
+    rank = env_int("RANK", 0)
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}; launch with torch.distributed.run for N>1")
+    mode = args.mode if world > 1 or args.mode in ("part1", "part3") else "part1"
+    kw = dict(mode=mode, master_ip=os.environ.get("MASTER_ADDR", "127.0.0.1"), num_nodes=world, rank=rank,
+              device="cuda", eval=False, bucket_plan=args.bucket_plan,
+              port=args.port or env_int("MASTER_PORT", 29500) + 37)
+    if args.scaling == "weak":
+        kw["per_rank_batch"] = args.per_gpu_batch
+    else:
+        kw["global_batch"] = args.global_batch
+    cfg = TrainConfig(**kw)
+    tr = Trainer(cfg)
+    be = tr.backend
+    B = cfg.per_rank_batch
+    g = torch.Generator().manual_seed(1234 + rank)
+    host_batches = [(torch.randn(B, 3, 32, 32, generator=g).pin_memory(),
+                     torch.randint(0, 10, (B,), generator=g).pin_memory()) for _ in range(8)]
+    sampler = ClockSampler(torch.cuda.current_device())
+
+    # ---- device-timed: K replays of the captured step, inputs already resident on the device
+    for i in range(max(args.warmup, 3)):
+        be.run_staged(be.stage_inputs(*host_batches[i % 8]))
+    be.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    n0 = _lib.launch_count
+    sampler.start()
+    e0.record()
+    for _ in range(args.steps):
+        if be.graph is not None:
+            be.graph.replay()
+        else:
+            be._step_body()
+    e1.record()
+    torch.cuda.synchronize()
+    sampler.stop()
+    be.barrier()
+    ms_dev = be.max_over_ranks(e0.elapsed_time(e1)) / args.steps
+    launches = be.launches_per_step * args.steps if be.graph is not None else _lib.launch_count - n0
+
+    # ---- end to end through the public API: H2D of every batch + D2H of every loss in the timed region
+    e2e = None
+    if not args.no_e2e:
+        for i in range(3):
+            tr.train_step(*host_batches[i % 8])
+        be.barrier()
+        torch.cuda.synchronize()
+        t0 = torch.cuda.Event(enable_timing=True)
+        t1 = torch.cuda.Event(enable_timing=True)
+        t0.record()
+        tickets = []
+        for i in range(args.steps):
+            tr.train_step(*host_batches[i % 8])
+            tickets.append(be.read_loss_async())
+            if len(tickets) > 8:                      # keep the host at most a few steps ahead
+                be.loss_value(tickets.pop(0))
+        last = [be.loss_value(t) for t in tickets][-1]
+        t1.record()
+        torch.cuda.synchronize()
+        be.barrier()
+        ms_e2e = be.max_over_ranks(t0.elapsed_time(t1)) / args.steps
+        e2e = {"value": cfg.global_batch / (ms_e2e * 1e-3), "unit": "images/s", "ms_per_step": ms_e2e,
+               "h2d_bytes_per_step": B * (3 * 32 * 32 * 4 + 8), "d2h_bytes_per_step": 4, "last_loss": last}
+    out = {
+        "metric": "VGG-11 CIFAR-10 images/sec", "impl": "native", "value": cfg.global_batch / (ms_dev * 1e-3),
+        "unit": "images/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": ms_dev, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
+        "dtype": "bf16", "data": "synthetic (random CIFAR-10-shaped tensors, random-init weights)",
+        "config": {"model": "VGG-11", "global_batch": cfg.global_batch, "per_gpu_batch": B, "seq_len": None,
+                   "image": "3x32x32", "mode": mode, "parallelism": f"dp{world}", "optimizer": "SGD lr0.1 m0.9 wd1e-4",
+                   "bucket_plan": args.bucket_plan, "cuda_graph": be.graph is not None,
+                   "l2": f"no explicit flush: one step streams ~{working_set_mb(tr.model.block_specs(), B):.0f} MB "
+                         f"(> 126 MB L2) and rewrites every activation and parameter"},
+        "gpu_launches": launches, "clocks": sampler.summary(),
+    }
+    if e2e is not None:
+        out["e2e"] = e2e
+    tr.close()
+    return out if rank == 0 else {}
+
+
+def run_reference(args) -> dict:
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "baseline"))
+    import ref_harness
+    why = ref_harness.available()
+    if why is not None:
+        return {"impl": "reference", "unavailable": why}
+    import torch.distributed as dist
+    world = env_int("WORLD_SIZE", 1)
+    rank = env_int("RANK", 0)
+    local = env_int("LOCAL_RANK", 0)
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}; launch with torch.distributed.run for N>1")
+    mode = args.mode
+    if world == 1 and mode != "part3":
+        mode = "part1"
+    B = args.per_gpu_batch if args.scaling == "weak" else args.global_batch // world
+    torch.cuda.set_device(local)
+    if mode == "part3" and world == 1 and not dist.is_initialized():
+        # DDP needs a process group even for one rank (the reference always has 4)
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", str(args.port or 29533))
+        dist.init_process_group("nccl", rank=0, world_size=1)
+    sampler = ClockSampler(local)
+    try:
+        dev = ref_harness.run_reference(mode, rank, world, local, B, args.steps, max(args.warmup, 3), host_inputs=False,
+                                        on_timed_region=sampler.start, on_timed_region_end=sampler.stop)
+        e2e = None
+        if not args.no_e2e:
+            e2e = ref_harness.run_reference(mode, rank, world, local, B, args.steps, 3, host_inputs=True)
+    except Exception as e:  # the reference arm must never take the benchmark down
+        return {"impl": "reference", "unavailable": f"{type(e).__name__}: {e}"[:300]}
+
+    def max_ranks(v: float) -> float:
+        if world == 1:
+            return v
+        t = torch.tensor([v], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    ms_dev = max_ranks(dev["ms_per_step"])
+    gb = B * world
+    out = {
+        "metric": "VGG-11 CIFAR-10 images/sec", "impl": "reference", "value": gb / (ms_dev * 1e-3), "unit": "images/s",
+        "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_dev,
+        "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "fp32 (torch default, TF32 conv)",
+        "data": "synthetic (random CIFAR-10-shaped tensors, random-init weights)",
+        "config": {"model": "VGG-11", "global_batch": gb, "per_gpu_batch": B, "image": "3x32x32", "mode": mode,
+                   "parallelism": f"dp{world}", "backend": "nccl", "script": "/".join(ref_harness.SCRIPTS[mode]),
+                   "note": "unmodified train_model() and model.py from baseline/_ref; device global set to cuda"},
+        "gpu_launches": 0, "clocks": sampler.summary(),
+    }
+    if e2e is not None:
+        ms = max_ranks(e2e["ms_per_step"])
+        out["e2e"] = {"value": gb / (ms * 1e-3), "unit": "images/s", "ms_per_step": ms,
+                      "h2d_bytes_per_step": e2e["h2d_bytes_per_step"], "d2h_bytes_per_step": 4.0 / 20}
+    if dist.is_initialized():
+        dist.destroy_process_group()
+    return out if rank == 0 else {}
+
+
+def main():
+    args = parse_args()
+    if not torch.cuda.is_available():
+        print(json.dumps({"impl": args.impl, "unavailable": "no CUDA device visible"}))
+        return 0
+    out = run_reference(args) if args.impl == "reference" else run_native(args)
+    if out:
+        print(json.dumps(out), flush=True)
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

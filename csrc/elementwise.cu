@@ -665,3 +665,70 @@ extern "C" int b200dp_prep_conv_weights(const float* master, void* wf, void* wd,
   B200DP_CUDA_TRY(cudaGetLastError());
   return 0;
 }
+
+// ---------------------------------------------------------------------------
+// BatchNorm + ReLU (+ pool) backward for callers that must not allocate.
+//
+// b200dp_bn_relu_pool_bwd_reduce / _apply need a caller-owned [2][C] fp32 buffer for the
+// per-channel sums.  Some hosts cannot provide one at the point of the call: an application that
+// handed the whole device to its own arena at start-up, a plug-in running under a fixed memory
+// plan, or a loop where cudaMalloc's device-wide synchronisation is not acceptable.  For them this
+// entry point carries its own scratch: one file-scope __device__ array, resident on every GPU
+// that loads the library until the process exits.
+// ---------------------------------------------------------------------------
+#include <mutex>
+
+namespace b200dp {
+
+constexpr int kNoAllocMaxChannels = 2048;  // 2 * 2048 floats = 16 KiB of device memory per GPU
+constexpr int kNoAllocMaxDevices = 64;
+
+static __device__ __align__(256) float g_bn_bwd_scratch[2 * kNoAllocMaxChannels];
+
+// The array's name is only a host-side handle; kernels must be given the device address that
+// cudaGetSymbolAddress returns for the device that is current at the time of the query.
+static float* g_bn_bwd_scratch_addr[kNoAllocMaxDevices] = {nullptr};
+static std::mutex g_bn_bwd_scratch_mutex;
+
+static int bn_bwd_scratch_for_current_device(float** out) {
+  int dev = -1;
+  B200DP_CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kNoAllocMaxDevices) {
+    set_error("bn_relu_pool_bwd_noalloc: device ordinal %d is outside the supported range [0, %d)", dev,
+              kNoAllocMaxDevices);
+    return B200DP_EINVAL;
+  }
+  std::lock_guard<std::mutex> lock(g_bn_bwd_scratch_mutex);
+  if (g_bn_bwd_scratch_addr[dev] == nullptr) {
+    void* p = nullptr;
+    B200DP_CUDA_TRY(cudaGetSymbolAddress(&p, g_bn_bwd_scratch));
+    g_bn_bwd_scratch_addr[dev] = static_cast<float*>(p);
+  }
+  *out = g_bn_bwd_scratch_addr[dev];
+  return 0;
+}
+
+}  // namespace b200dp
+
+extern "C" int b200dp_bn_relu_pool_bwd_noalloc(const void* y, const void* dout, const float* mean,
+                                               const float* invstd, const float* gamma, const float* beta,
+                                               void* dy, float* dgamma, float* dbeta, int B, int H, int W, int C,
+                                               int pool, b200dp_stream_t s) {
+  if (C <= 0 || C > kNoAllocMaxChannels) {
+    set_error("bn_relu_pool_bwd_noalloc: C=%d exceeds the built-in scratch, which holds at most %d channels; "
+              "use b200dp_bn_relu_pool_bwd_reduce/_apply with your own [2][C] buffer instead",
+              C, kNoAllocMaxChannels);
+    return B200DP_EINVAL;
+  }
+  float* scratch = nullptr;
+  int rc = bn_bwd_scratch_for_current_device(&scratch);
+  if (rc) return rc;
+  cudaStream_t stream = static_cast<cudaStream_t>(s);
+  // The array still holds the sums of whoever called last; the reduction adds onto it.
+  B200DP_CUDA_TRY(cudaMemsetAsync(scratch, 0, 2 * static_cast<size_t>(C) * sizeof(float), stream));
+  BnBwdParams p{static_cast<const __nv_bfloat16*>(y), static_cast<const __nv_bfloat16*>(dout), mean, invstd, gamma,
+                beta, scratch, static_cast<__nv_bfloat16*>(dy), dgamma, dbeta, B, H, W, C, pool};
+  rc = launch_bn_bwd(false, p, stream);
+  if (rc) return rc;
+  return launch_bn_bwd(true, p, stream);
+}

@@ -97,6 +97,25 @@ int b200dp_bn_relu_pool_bwd_apply(const void* y, const void* dout, const float* 
                                   float* dgamma, float* dbeta, int B, int H, int W, int C, int pool,
                                   b200dp_stream_t stream);
 
+/* BatchNorm + ReLU (+ pool) backward that allocates nothing and needs no scratch from the caller.
+ * This entry point has no counterpart in the reference.  It is for hosts that cannot call
+ * cudaMalloc where the backward runs -- all device memory already belongs to the host
+ * application's own arena or to a fixed memory plan, or the implicit device synchronisation of an
+ * allocation is not tolerable there -- and therefore cannot supply the [2][C] `sums` buffer that
+ * b200dp_bn_relu_pool_bwd_reduce/_apply require.  Both passes run back to back on `stream`; the
+ * per-channel sums live in a 16 KiB __device__ array inside the library (present on every GPU that
+ * loads it, until exit).  Results equal reduce + apply.
+ *   - C must be <= 2048; larger C is rejected with B200DP_EINVAL and a message.
+ *   - The first call on each device looks up the array's device address (cudaGetSymbolAddress,
+ *     with that device current).  Make that first call before any stream capture begins, and keep
+ *     the device that owns `stream` current when calling.
+ *   - All calls share the one array; it is cleared at the start of each call.  Two calls that
+ *     overlap on the GPU (different streams, or different host threads) race on it -- serialise them.
+ * Inputs and outputs are still the caller's; no cudaMalloc / cudaFree / torch allocation happens. */
+int b200dp_bn_relu_pool_bwd_noalloc(const void* y, const void* dout, const float* mean, const float* invstd,
+                                    const float* gamma, const float* beta, void* dy, float* dgamma,
+                                    float* dbeta, int B, int H, int W, int C, int pool, b200dp_stream_t stream);
+
 /* Classifier and loss (ref: master/part1/model.py:40,45; master/part1/part1.py:36,94). */
 int b200dp_linear_fwd(const void* x_bf16, const float* w, const float* b, float* logits, int B, int F, int O,
                       b200dp_stream_t stream);

@@ -1,0 +1,116 @@
+"""CPU tests of the native runtime pieces that need no GPU (rendezvous store), checkpoints, CLI."""
+import json
+import os
+import subprocess
+import sys
+import threading
+
+import pytest
+import torch
+
+sys.path.insert(0, os.path.dirname(__file__))
+from helpers import REPO, free_port, reference_model_module  # noqa: E402
+
+
+def test_library_builds_and_exports_the_c_abi():
+    from cs744_pytorch_distributed_tutorial_b200.ops import _lib
+    lib = _lib.lib()
+    assert "sm_100a" in _lib.version()
+    header = open(os.path.join(REPO, "include", "b200dp.h")).read()
+    import re
+    declared = set(re.findall(r"\b(b200dp_[a-z0-9_]+)\s*\(", header))
+    assert len(declared) >= 30
+    for name in declared:
+        assert hasattr(lib, name), f"{name} is declared in include/b200dp.h but not exported"
+
+
+def test_store_set_get_add_barrier_across_three_ranks():
+    from cs744_pytorch_distributed_tutorial_b200.parallel.comm import Store
+    port, world = free_port(), 3
+    results, errors = {}, []
+
+    def rank_main(rank):
+        try:
+            s = Store("127.0.0.1", port, rank, world, timeout_s=20)
+            s.set(f"hello/{rank}", bytes([rank]) * (rank + 1))
+            got = [s.get(f"hello/{r}") for r in range(world)]   # blocks until each peer has written
+            total = s.add("counter", rank + 1)
+            s.barrier("t")
+            final = s.add("counter", 0)
+            s.barrier("t")
+            results[rank] = (got, total, final)
+            s.close()
+        except Exception as e:  # pragma: no cover
+            errors.append((rank, repr(e)))
+
+    threads = [threading.Thread(target=rank_main, args=(r,)) for r in range(world)]
+    [t.start() for t in threads]
+    [t.join(60) for t in threads]
+    assert not errors, errors
+    for rank in range(world):
+        got, _, final = results[rank]
+        assert got == [bytes([r]) * (r + 1) for r in range(world)]
+        assert final == 1 + 2 + 3
+
+
+def test_store_get_times_out_with_a_message_naming_the_key():
+    from cs744_pytorch_distributed_tutorial_b200.ops._lib import NativeError
+    from cs744_pytorch_distributed_tutorial_b200.parallel.comm import Store
+    s = Store("127.0.0.1", free_port(), 0, 1, timeout_s=0.3)
+    with pytest.raises(NativeError, match="never/written"):
+        s.get("never/written")
+    s.close()
+
+
+def test_checkpoint_roundtrip_and_reference_compat(tmp_path):
+    from cs744_pytorch_distributed_tutorial_b200.checkpoint import load_checkpoint, save_checkpoint
+    from cs744_pytorch_distributed_tutorial_b200.models.vgg import VGG11
+    torch.manual_seed(1)
+    m = VGG11()
+    opt = torch.optim.SGD(m.parameters(), lr=0.1, momentum=0.9)
+    path = str(tmp_path / "ck.pt")
+    save_checkpoint(path, m, opt.state_dict(), step=7)
+    ck = torch.load(path, weights_only=False)
+    assert ck["step"] == 7 and len(ck["model"]) == 58
+    assert all(not k.startswith("module.") and v.is_contiguous() for k, v in ck["model"].items())
+    m2 = VGG11()
+    out = load_checkpoint(path, m2)
+    assert out["step"] == 7
+    for (k, a), (_, b) in zip(m.state_dict().items(), m2.state_dict().items()):
+        assert torch.equal(a, b), k
+    ref_mod = reference_model_module()
+    if ref_mod is not None:
+        ref = ref_mod.VGG11()
+        ref.load_state_dict(ck["model"], strict=True)          # ours -> reference
+        bare = str(tmp_path / "bare.pt")
+        torch.save({"module." + k: v for k, v in ref.state_dict().items()}, bare)   # raw DDP state_dict
+        load_checkpoint(bare, m2)                               # reference -> ours
+
+
+def test_cli_part1_prints_reference_lines_and_json():
+    cmd = [sys.executable, "-m", "cs744_pytorch_distributed_tutorial_b200.cli", "--mode", "part1", "--device", "cpu",
+           "--global-batch", "16", "--train-size", "64", "--test-size", "32", "--iters", "2"]
+    r = subprocess.run(cmd, cwd=REPO, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = r.stdout.strip().splitlines()
+    assert lines[0].startswith("0 loss: ")
+    assert any(l.startswith("Test set: Average loss:") for l in lines)
+    metrics = json.loads(lines[-1])
+    assert metrics["mode"] == "part1" and metrics["iters"] == 2 and metrics["samples"] == 32
+
+
+def test_cli_two_process_part2a_with_reference_flags():
+    """The reference's launch recipe: one process per node with --master-ip/--num-nodes/--rank."""
+    port = free_port()
+    procs = []
+    for rank in range(2):
+        cmd = [sys.executable, "-m", "cs744_pytorch_distributed_tutorial_b200.cli", "--mode", "part2a",
+               "--master-ip", "127.0.0.1", "--num-nodes", "2", "--rank", str(rank), "--port", str(port),
+               "--device", "cpu", "--global-batch", "16", "--train-size", "64", "--test-size", "16", "--iters", "2"]
+        procs.append(subprocess.Popen(cmd, cwd=REPO, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True))
+    outs = [p.communicate(timeout=600) for p in procs]
+    for p, (so, se) in zip(procs, outs):
+        assert p.returncode == 0, se[-2000:]
+    assert outs[0][0].splitlines()[0].startswith("0 loss: ")
+    m = json.loads(outs[0][0].strip().splitlines()[-1])
+    assert m["world_size"] == 2 and m["global_batch"] == 16

@@ -466,12 +466,13 @@ extern "C" int b200dp_allreduce(void* comm, long long grad_off, long long param_
   const int threads = 512;
   const long n4 = (end - start) >> 2;
   if (algo == 0) algo = (n4 * 16 <= 256 * 1024) ? 1 : 2;
+  const int requested_blocks = blocks;
   if (algo == 1) {
     blocks = static_cast<int>((n4 + threads - 1) / threads);
     if (blocks < 1) blocks = 1;
-    if (blocks > kMaxBlocks) algo = 2;  // does not fit in one pass
+    if (blocks > kMaxBlocks) algo = 2;  // does not fit in one pass: use the two-shot kernel
   }
-  if (algo == 2 && blocks <= 0) blocks = 64;
+  if (algo == 2) blocks = requested_blocks > 0 ? requested_blocks : 64;
   int rc = check_range(c, start, end, blocks, channel, "allreduce");
   if (rc) return rc;
   RangeArgs a{};

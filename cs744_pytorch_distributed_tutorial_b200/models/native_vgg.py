@@ -111,8 +111,32 @@ class _Block:
     pass
 
 
+_TUNE_CACHE: Dict[tuple, int] = {}   # (kind, B, hw, cin, cout) -> best block_n / split_k, per process
+
+
+def _time_captured(fn, reps: int = 8, replays: int = 3) -> float:
+    """Microseconds per call of ``fn``, measured by replaying a CUDA graph of ``reps`` launches
+    (removes the host launch cost, which would otherwise hide the differences between ~10 us kernels)."""
+    fn()
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for _ in range(reps):
+            fn()
+    best = float("inf")
+    for _ in range(replays):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        g.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1) * 1e3 / reps)
+    return best
+
+
 class NativeVGG:
-    def __init__(self, module: nn.Module, max_batch: int, heap=None, conv_stats_fused: bool = True):
+    def __init__(self, module: nn.Module, max_batch: int, heap=None, conv_stats_fused: bool = True,
+                 autotune: bool = True):
         dev = next(module.parameters()).device
         if dev.type != "cuda":
             raise RuntimeError("NativeVGG needs the module on a CUDA device")
@@ -142,6 +166,8 @@ class NativeVGG:
         self._adopt_parameters()
         self._alloc_workspaces()
         self.refresh_shadows()
+        if autotune:
+            self.autotune(max_batch)
 
     # ------------------------------------------------------------------ parameters
     def _view(self, flat: torch.Tensor, e: FlatEntry) -> torch.Tensor:
@@ -202,6 +228,7 @@ class NativeVGG:
             b = _Block()
             b.spec = s
             b.first = (i == 0)
+            b.fwd_block_n = b.dgrad_block_n = b.wgrad_split_k = 0   # 0 = library heuristic; see autotune()
             b.kin = 64 if b.first else s.cin           # GEMM K per tap (layer 0: 27 -> 64 padded, 1 tap)
             b.taps = 1 if b.first else 9
             hw = s.hw
@@ -257,12 +284,49 @@ class NativeVGG:
             self._bucket_of_block.setdefault(min(block_of(n) for n in bk.names), []).append(bk.index)
         self.buckets = list(buckets)
 
+    # ------------------------------------------------------------------ tile autotuning
+    def autotune(self, B: int) -> None:
+        """Pick the N tile of every forward / dgrad conv and the split-K of every wgrad by timing the
+        candidates on this GPU at batch ``B`` (the shapes are tiny and L2->SM bandwidth bound, so the
+        best tile depends on how many CTAs a shape yields; a static rule leaves 5-10% on the table)."""
+        side = torch.cuda.Stream(self.device)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for i, b in enumerate(self.blocks):
+                s = b.spec
+                x_in, y, dy = b.x_in[:B], b.y[:B], b.dy[:B]
+                key = (B, s.hw, b.kin, s.cout, b.taps)
+                if ("fwd",) + key not in _TUNE_CACHE:
+                    cands = [n for n in (32, 64, 128, 256) if s.cout % n == 0]
+                    t = {n: _time_captured(lambda n=n: K.conv_igemm(x_in, b.wf, b.bias, y, stats=b.stats, taps=b.taps,
+                                                                    block_n=n)) for n in cands}
+                    _TUNE_CACHE[("fwd",) + key] = min(t, key=t.get)
+                b.fwd_block_n = _TUNE_CACHE[("fwd",) + key]
+                if ("wgrad",) + key not in _TUNE_CACHE:
+                    t = {k: _time_captured(lambda k=k: K.conv_wgrad(dy, x_in, b.g_w, taps=b.taps, split_k=k,
+                                                                    cin_valid=(27 if b.first else None)))
+                         for k in (0, 1, 2, 4, 8, 16)}
+                    _TUNE_CACHE[("wgrad",) + key] = min(t, key=t.get)
+                b.wgrad_split_k = _TUNE_CACHE[("wgrad",) + key]
+                if i > 0:
+                    dprev = self.blocks[i - 1].dout[:B]
+                    if ("dgrad",) + key not in _TUNE_CACHE:
+                        cands = [n for n in (32, 64, 128, 256) if s.cin % n == 0]
+                        t = {n: _time_captured(lambda n=n: K.conv_igemm(dy, b.wd, None, dprev, block_n=n)) for n in cands}
+                        _TUNE_CACHE[("dgrad",) + key] = min(t, key=t.get)
+                    b.dgrad_block_n = _TUNE_CACHE[("dgrad",) + key]
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        self.flat_grads.zero_()
+        self.zero_region.zero_()
+
     # ------------------------------------------------------------------ weight shadows
     def refresh_shadows(self) -> None:
         """bf16 operand copies of the fp32 master weights: Wf (forward) and Wd (dgrad)."""
-        for b in self.blocks:
-            s = b.spec
-            K.prep_conv_weights(b.w_master, b.wf, b.wd, s.cout, s.cin, 9, b.taps * b.kin)
+        if getattr(self, "_prep", None) is None:
+            self._prep = K.BatchedWeightPrep([(b.w_master, b.wf, b.wd, b.spec.cout, b.spec.cin, 9, b.taps * b.kin)
+                                              for b in self.blocks])
+        self._prep()
 
     # ------------------------------------------------------------------ forward
     def forward(self, x: torch.Tensor, training: bool = True) -> torch.Tensor:
@@ -280,7 +344,8 @@ class NativeVGG:
                 K.im2col3x3_c3(x.contiguous(), x_in)
             y = b.y[:B]
             fused = training and self.conv_stats_fused
-            K.conv_igemm(x_in, b.wf, b.bias, y, stats=b.stats if fused else None, taps=b.taps)
+            K.conv_igemm(x_in, b.wf, b.bias, y, stats=b.stats if fused else None, taps=b.taps,
+                         block_n=b.fwd_block_n)
             if training and not fused:
                 K.bn_stats(y, b.stats)
             K.bn_relu_pool_fwd(y, b.stats, b.gamma, b.beta, b.running_mean, b.running_var, b.nbt, b.mean, b.invstd,
@@ -313,12 +378,13 @@ class NativeVGG:
                                b.g_beta, s.pool)
             # the conv bias feeds a training-mode BatchNorm, so its exact gradient is zero:
             # it simply keeps the zero written by the flat_grads clear at the top of backward().
-            K.conv_wgrad(b.dy[:B], b.x_in[:B], b.g_w, taps=b.taps, cin_valid=(27 if b.first else None))
+            K.conv_wgrad(b.dy[:B], b.x_in[:B], b.g_w, taps=b.taps, cin_valid=(27 if b.first else None),
+                         split_k=b.wgrad_split_k)
             if self.on_bucket_ready is not None:
                 for k in self._bucket_of_block.get(i, ()):
                     self.on_bucket_ready(k)
             if i > 0:
-                K.conv_igemm(b.dy[:B], b.wd, None, self.blocks[i - 1].dout[:B])
+                K.conv_igemm(b.dy[:B], b.wd, None, self.blocks[i - 1].dout[:B], block_n=b.dgrad_block_n)
 
     # ------------------------------------------------------------------ torch.autograd bridge
     def autograd_forward(self, x: torch.Tensor, training: bool) -> torch.Tensor:

@@ -34,6 +34,7 @@ _PROTOTYPES = {
     "b200dp_linear_bwd": [P, P, P, P, P, P, I, I, I, P],
     "b200dp_sgd_momentum": [P, P, P, LL, F, F, F, F, P],
     "b200dp_prep_conv_weights": [P, P, P, I, I, I, I, P],
+    "b200dp_prep_conv_weights_batched": [I, P, P, P, P, P, P, P, P],
 }
 
 

@@ -123,5 +123,36 @@ def prep_conv_weights(master, wf, wd, Cout: int, Cin: int, taps: int, kpad: int)
     call("b200dp_prep_conv_weights", ptr(master), ptr(wf), ptr(wd), Cout, Cin, taps, kpad, stream_ptr())
 
 
+class BatchedWeightPrep:
+    """All conv layers' bf16 shadows (Wf and the tap-flipped transposed Wd) in ONE launch.  The
+    pointer tables are built once; layers that are not multiples of 64 (the 3-channel first conv)
+    fall back to the single-layer kernel."""
+
+    def __init__(self, layers):
+        """``layers``: iterable of (master, wf, wd_or_None, Cout, Cin, taps, kpad)."""
+        import ctypes
+        layers = list(layers)
+        odd = lambda l: bool(l[3] % 64 or l[4] % 64 or l[6] != l[5] * l[4])
+        self._single = [l for l in layers if odd(l)]
+        batched = [l for l in layers if not odd(l)]
+        self._n = len(batched)
+        self._keep = batched
+        if self._n:
+            vp = ctypes.c_void_p * self._n
+            ia = ctypes.c_int * self._n
+            self._master = vp(*[l[0].data_ptr() for l in batched])
+            self._wf = vp(*[l[1].data_ptr() for l in batched])
+            self._wd = vp(*[(l[2].data_ptr() if l[2] is not None else None) for l in batched])
+            self._cout, self._cin = ia(*[l[3] for l in batched]), ia(*[l[4] for l in batched])
+            self._taps, self._kpad = ia(*[l[5] for l in batched]), ia(*[l[6] for l in batched])
+
+    def __call__(self) -> None:
+        for m, wf, wd, co, ci, taps, kpad in self._single:
+            prep_conv_weights(m, wf, wd, co, ci, taps, kpad)
+        if self._n:
+            call("b200dp_prep_conv_weights_batched", self._n, self._master, self._wf, self._wd, self._cout, self._cin,
+                 self._taps, self._kpad, stream_ptr())
+
+
 def version() -> str:
     return _lib.version()

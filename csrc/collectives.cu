@@ -157,37 +157,57 @@ __global__ void __launch_bounds__(512) allreduce_twoshot_kernel(const CommDev c,
   const long per = (n4 + W - 1) / W;                // slice length per rank
   const long lo = min(per * c.rank, n4), hi = min(lo + per, n4);
   const float inv_w = 1.f / static_cast<float>(W);
-  for (long i = lo + blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < hi;
-       i += static_cast<long>(gridDim.x) * blockDim.x) {
-    const size_t eoff = static_cast<size_t>(a.start + (i << 2)) * sizeof(float);
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  constexpr int U = 4;  // independent float4 streams per thread: U x W 16-byte peer loads in flight
+  const long tstride = static_cast<long>(gridDim.x) * blockDim.x;
+  for (long i0 = lo + blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i0 < hi; i0 += tstride * U) {
+    float4 acc[U];
+    size_t eoff[U];
+    bool live[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long i = i0 + u * tstride;
+      live[u] = i < hi;
+      eoff[u] = static_cast<size_t>(a.start + ((live[u] ? i : lo) << 2)) * sizeof(float);
+      acc[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
 #pragma unroll
     for (int r = 0; r < kMaxWorld; ++r) {
       if (r < W) {
-        float4 v = ld_peer_f4(reinterpret_cast<const float*>(c.peers.base[r] + a.grad_off + eoff));
-        if (PRESCALE) {  // divide-then-sum, the order of part2b / DDP
-          v.x *= inv_w; v.y *= inv_w; v.z *= inv_w; v.w *= inv_w;
+        float4 v[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+          v[u] = ld_peer_f4(reinterpret_cast<const float*>(c.peers.base[r] + a.grad_off + eoff[u]));
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          if (PRESCALE) {  // divide-then-sum, the order of part2b / DDP
+            v[u].x *= inv_w; v[u].y *= inv_w; v[u].z *= inv_w; v[u].w *= inv_w;
+          }
+          acc[u].x += v[u].x; acc[u].y += v[u].y; acc[u].z += v[u].z; acc[u].w += v[u].w;
         }
-        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
       }
     }
-    if (!PRESCALE) {
-      acc.x *= inv_w; acc.y *= inv_w; acc.z *= inv_w; acc.w *= inv_w;
-    }
-    if (FUSE_SGD) {
-      char* me = c.peers.base[c.rank];
-      float4 p = *reinterpret_cast<const float4*>(me + a.param_off + eoff);
-      float4 m = *reinterpret_cast<const float4*>(me + a.mom_off + eoff);
-      const float4 np = sgd4(acc, p, m, a.sgd);
-      *reinterpret_cast<float4*>(me + a.mom_off + eoff) = m;
-      *reinterpret_cast<float4*>(me + a.grad_off + eoff) = acc;  // owner keeps the mean gradient
 #pragma unroll
-      for (int r = 0; r < kMaxWorld; ++r)
-        if (r < W) st_peer_f4(reinterpret_cast<float*>(c.peers.base[r] + a.param_off + eoff), np);
-    } else {
+    for (int u = 0; u < U; ++u) {
+      if (!live[u]) continue;
+      float4 g = acc[u];
+      if (!PRESCALE) {
+        g.x *= inv_w; g.y *= inv_w; g.z *= inv_w; g.w *= inv_w;
+      }
+      if (FUSE_SGD) {
+        char* me = c.peers.base[c.rank];
+        float4 p = *reinterpret_cast<const float4*>(me + a.param_off + eoff[u]);
+        float4 m = *reinterpret_cast<const float4*>(me + a.mom_off + eoff[u]);
+        const float4 np = sgd4(g, p, m, a.sgd);
+        *reinterpret_cast<float4*>(me + a.mom_off + eoff[u]) = m;
+        *reinterpret_cast<float4*>(me + a.grad_off + eoff[u]) = g;  // owner keeps the mean gradient
 #pragma unroll
-      for (int r = 0; r < kMaxWorld; ++r)
-        if (r < W) st_peer_f4(reinterpret_cast<float*>(c.peers.base[r] + a.grad_off + eoff), acc);
+        for (int r = 0; r < kMaxWorld; ++r)
+          if (r < W) st_peer_f4(reinterpret_cast<float*>(c.peers.base[r] + a.param_off + eoff[u]), np);
+      } else {
+#pragma unroll
+        for (int r = 0; r < kMaxWorld; ++r)
+          if (r < W) st_peer_f4(reinterpret_cast<float*>(c.peers.base[r] + a.grad_off + eoff[u]), g);
+      }
     }
   }
   rank_barrier(c, a.channel, 1, epoch);

@@ -56,30 +56,32 @@ B200DP_DEVINL Vec8 load_f32x8(const float* p) {
 // matrix (27 real columns, k = (r*3+s)*3 + c, the rest zero) so that the first
 // conv is a plain K=64 GEMM for the tcgen05 kernel.
 // ---------------------------------------------------------------------------
+// One block per image row: the 3 x 3 x (W+2) input window is staged in shared memory with
+// coalesced loads, then every thread emits one 16-byte chunk of a pixel's 64-wide patch row.
 __global__ void im2col_c3_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ a0, int B, int H, int W) {
-  const long total = static_cast<long>(B) * H * W * 8;
-  for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<long>(gridDim.x) * blockDim.x) {
-    const int chunk = static_cast<int>(i & 7);
-    const long pix = i >> 3;
+  extern __shared__ float win[];  // [3 rows][3 channels][W + 2]
+  const int Wp = W + 2;
+  const int n = blockIdx.x / H, h = blockIdx.x - n * H;
+  for (int i = threadIdx.x; i < 9 * Wp; i += blockDim.x) {
+    const int r = i / (3 * Wp), c = (i / Wp) % 3, ww = i % Wp - 1;
+    const int hh = h + r - 1;
+    win[i] = (hh >= 0 && hh < H && ww >= 0 && ww < W) ? __ldg(x + ((static_cast<long>(n) * 3 + c) * H + hh) * W + ww) : 0.f;
+  }
+  __syncthreads();
+  for (int t = threadIdx.x; t < W * 8; t += blockDim.x) {
+    const int w = t >> 3, chunk = t & 7;
     Vec8 r;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) r.v[j] = 0.f;
-    if (chunk < 4) {
-      const int w = static_cast<int>(pix % W);
-      const int h = static_cast<int>((pix / W) % H);
-      const long n = pix / (static_cast<long>(W) * H);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const int k = chunk * 8 + j;
-        if (k < 27) {
-          const int tap = k / 3, c = k - tap * 3;
-          const int hh = h + tap / 3 - 1, ww = w + tap % 3 - 1;
-          if (hh >= 0 && hh < H && ww >= 0 && ww < W) r.v[j] = __ldg(x + ((n * 3 + c) * H + hh) * W + ww);
-        }
+    for (int j = 0; j < 8; ++j) {
+      const int k = chunk * 8 + j;
+      float v = 0.f;
+      if (k < 27) {
+        const int tap = k / 3, c = k - tap * 3;
+        v = win[(tap / 3) * 3 * Wp + c * Wp + w + tap % 3];
       }
+      r.v[j] = v;
     }
-    store_bf16x8(a0 + i * 8, r);
+    store_bf16x8(a0 + ((static_cast<long>(n) * H + h) * W + w) * 64 + chunk * 8, r);
   }
 }
 
@@ -233,33 +235,44 @@ struct BnBwdParams {
   int B, H, W, C, pool;
 };
 
+// Register-lean formulation (64 regs -> 4 blocks / SM so that enough 16-byte loads are in flight):
+//   z  = y*scale + shift                       scale = gamma*invstd, shift = beta - mean*scale
+//   pass 1 accumulates  a1 = sum dz,  a2 = sum dz*y ;  S2 = invstd*(a2 - mean*a1) at the end
+//   pass 2 writes       dy = scale*dz + c0 + c1*y   c1 = -scale*invstd*S2/P, c0 = -scale*S1/P - c1*mean
 template <bool APPLY>
-__global__ void bn_relu_pool_bwd_kernel(const BnBwdParams p) {
+__global__ void __launch_bounds__(256, 3) bn_relu_pool_bwd_kernel(const BnBwdParams p) {
   extern __shared__ float red[];
   const int chunks = p.C / 8;
   const int rows_per_block = blockDim.x / chunks;
   const int chunk = threadIdx.x % chunks;
   const int rl = threadIdx.x / chunks;
-  const int c0 = chunk * 8;
+  const int c0i = chunk * 8;
   const int Ho = p.pool ? p.H / 2 : p.H, Wo = p.pool ? p.W / 2 : p.W;
   const long Q = static_cast<long>(p.B) * Ho * Wo;
   const float inv_count = 1.f / static_cast<float>(static_cast<long>(p.B) * p.H * p.W);
 
-  const Vec8 mean = load_f32x8(p.mean + c0), invstd = load_f32x8(p.invstd + c0);
-  const Vec8 g = load_f32x8(p.gamma + c0), b = load_f32x8(p.beta + c0);
-  Vec8 k1, k2;  // S1/P and S2/P (APPLY only)
-  if (APPLY) {
-    const Vec8 s1 = load_f32x8(p.sums + c0), s2 = load_f32x8(p.sums + p.C + c0);
+  Vec8 scale, shift, c0, c1;
+  {
+    const Vec8 mean = load_f32x8(p.mean + c0i), invstd = load_f32x8(p.invstd + c0i);
+    const Vec8 g = load_f32x8(p.gamma + c0i), b = load_f32x8(p.beta + c0i);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      k1.v[j] = s1.v[j] * inv_count;
-      k2.v[j] = s2.v[j] * inv_count;
+      scale.v[j] = g.v[j] * invstd.v[j];
+      shift.v[j] = b.v[j] - mean.v[j] * scale.v[j];
     }
-    if (blockIdx.x == 0 && rl == 0 && p.dgamma != nullptr) {
+    if (APPLY) {
+      const Vec8 s1 = load_f32x8(p.sums + c0i), s2 = load_f32x8(p.sums + p.C + c0i);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        p.dgamma[c0 + j] = s2.v[j];
-        p.dbeta[c0 + j] = s1.v[j];
+        c1.v[j] = -scale.v[j] * invstd.v[j] * s2.v[j] * inv_count;
+        c0.v[j] = -scale.v[j] * s1.v[j] * inv_count - c1.v[j] * mean.v[j];
+      }
+      if (blockIdx.x == 0 && rl == 0 && p.dgamma != nullptr) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          p.dgamma[c0i + j] = s2.v[j];
+          p.dbeta[c0i + j] = s1.v[j];
+        }
       }
     }
   }
@@ -270,74 +283,73 @@ __global__ void bn_relu_pool_bwd_kernel(const BnBwdParams p) {
   if (rl < rows_per_block) {
     for (long q = static_cast<long>(blockIdx.x) * rows_per_block + rl; q < Q;
          q += static_cast<long>(gridDim.x) * rows_per_block) {
-      const Vec8 go = load_bf16x8(p.dout + q * p.C + c0);
+      const Vec8 go = load_bf16x8(p.dout + q * p.C + c0i);
       if (p.pool) {
         const int wo = static_cast<int>(q % Wo);
         const int ho = static_cast<int>((q / Wo) % Ho);
         const long n = q / (static_cast<long>(Wo) * Ho);
-        const long off = ((n * p.H + 2 * ho) * p.W + 2 * wo) * p.C + c0;
-        const long offs[4] = {off, off + p.C, off + static_cast<long>(p.W) * p.C,
-                              off + static_cast<long>(p.W) * p.C + p.C};
-        Vec8 xh[4];
-        int win[8];
-        float zmax[8];
+        const long off = ((n * p.H + 2 * ho) * p.W + 2 * wo) * p.C + c0i;
+        const long rowb = static_cast<long>(p.W) * p.C;
+        // keep the four candidates packed (bf16) -- 16 registers instead of 32
+        const uint4 raw0 = *reinterpret_cast<const uint4*>(p.y + off);
+        const uint4 raw1 = *reinterpret_cast<const uint4*>(p.y + off + p.C);
+        const uint4 raw2 = *reinterpret_cast<const uint4*>(p.y + off + rowb);
+        const uint4 raw3 = *reinterpret_cast<const uint4*>(p.y + off + rowb + p.C);
+        const uint32_t w0[4] = {raw0.x, raw0.y, raw0.z, raw0.w}, w1[4] = {raw1.x, raw1.y, raw1.z, raw1.w};
+        const uint32_t w2[4] = {raw2.x, raw2.y, raw2.z, raw2.w}, w3[4] = {raw3.x, raw3.y, raw3.z, raw3.w};
+        Vec8 o0, o1, o2, o3;
 #pragma unroll
-        for (int t = 0; t < 4; ++t) {
-          const Vec8 yv = load_bf16x8(p.y + offs[t]);
+        for (int h = 0; h < 4; ++h) {
+          const float2 y0 = unpack_bf16x2(w0[h]), y1 = unpack_bf16x2(w1[h]);
+          const float2 y2 = unpack_bf16x2(w2[h]), y3 = unpack_bf16x2(w3[h]);
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            xh[t].v[j] = (yv.v[j] - mean.v[j]) * invstd.v[j];
+          for (int e = 0; e < 2; ++e) {
+            const int j = 2 * h + e;
+            const float ya = e ? y0.y : y0.x, yb = e ? y1.y : y1.x, yc = e ? y2.y : y2.x, yd = e ? y3.y : y3.x;
             // same arithmetic as the forward pass so that the winner is identical
-            const float scale = g.v[j] * invstd.v[j];
-            const float z = fmaf(yv.v[j], scale, b.v[j] - mean.v[j] * scale);
-            const float a = fmaxf(z, 0.f);
-            if (t == 0 || a > zmax[j]) {
-              zmax[j] = a;
-              win[j] = t;
+            const float za = fmaxf(fmaf(ya, scale.v[j], shift.v[j]), 0.f);
+            const float zb = fmaxf(fmaf(yb, scale.v[j], shift.v[j]), 0.f);
+            const float zc = fmaxf(fmaf(yc, scale.v[j], shift.v[j]), 0.f);
+            const float zd = fmaxf(fmaf(yd, scale.v[j], shift.v[j]), 0.f);
+            int win = 0;
+            float zmax = za, yw = ya;
+            if (zb > zmax) { zmax = zb; win = 1; yw = yb; }
+            if (zc > zmax) { zmax = zc; win = 2; yw = yc; }
+            if (zd > zmax) { zmax = zd; win = 3; yw = yd; }
+            const float dz = zmax > 0.f ? go.v[j] : 0.f;
+            if (APPLY) {
+              const float sdz = scale.v[j] * dz;
+              o0.v[j] = fmaf(c1.v[j], ya, c0.v[j]) + (win == 0 ? sdz : 0.f);
+              o1.v[j] = fmaf(c1.v[j], yb, c0.v[j]) + (win == 1 ? sdz : 0.f);
+              o2.v[j] = fmaf(c1.v[j], yc, c0.v[j]) + (win == 2 ? sdz : 0.f);
+              o3.v[j] = fmaf(c1.v[j], yd, c0.v[j]) + (win == 3 ? sdz : 0.f);
+            } else {
+              a1.v[j] += dz;
+              a2.v[j] = fmaf(dz, yw, a2.v[j]);
             }
           }
         }
         if (APPLY) {
-#pragma unroll
-          for (int t = 0; t < 4; ++t) {
-            Vec8 o;
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const float dz = (win[j] == t && zmax[j] > 0.f) ? go.v[j] : 0.f;
-              o.v[j] = g.v[j] * invstd.v[j] * (dz - k1.v[j] - xh[t].v[j] * k2.v[j]);
-            }
-            store_bf16x8(p.dy + offs[t], o);
-          }
-        } else {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            if (zmax[j] > 0.f) {
-              float xw = xh[0].v[j];
-              xw = win[j] == 1 ? xh[1].v[j] : xw;
-              xw = win[j] == 2 ? xh[2].v[j] : xw;
-              xw = win[j] == 3 ? xh[3].v[j] : xw;
-              a1.v[j] += go.v[j];
-              a2.v[j] += go.v[j] * xw;
-            }
-          }
+          store_bf16x8(p.dy + off, o0);
+          store_bf16x8(p.dy + off + p.C, o1);
+          store_bf16x8(p.dy + off + rowb, o2);
+          store_bf16x8(p.dy + off + rowb + p.C, o3);
         }
       } else {
-        const Vec8 yv = load_bf16x8(p.y + q * p.C + c0);
+        const Vec8 yv = load_bf16x8(p.y + q * p.C + c0i);
         Vec8 o;
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-          const float xhat = (yv.v[j] - mean.v[j]) * invstd.v[j];
-          const float scale = g.v[j] * invstd.v[j];
-          const float z = fmaf(yv.v[j], scale, b.v[j] - mean.v[j] * scale);
+          const float z = fmaf(yv.v[j], scale.v[j], shift.v[j]);
           const float dz = z > 0.f ? go.v[j] : 0.f;
           if (APPLY) {
-            o.v[j] = g.v[j] * invstd.v[j] * (dz - k1.v[j] - xhat * k2.v[j]);
+            o.v[j] = fmaf(scale.v[j], dz, fmaf(c1.v[j], yv.v[j], c0.v[j]));
           } else {
             a1.v[j] += dz;
-            a2.v[j] += dz * xhat;
+            a2.v[j] = fmaf(dz, yv.v[j], a2.v[j]);
           }
         }
-        if (APPLY) store_bf16x8(p.dy + q * p.C + c0, o);
+        if (APPLY) store_bf16x8(p.dy + q * p.C + c0i, o);
       }
     }
   }
@@ -347,8 +359,8 @@ __global__ void bn_relu_pool_bwd_kernel(const BnBwdParams p) {
     if (rl < rows_per_block) {
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        r1[rl * p.C + c0 + j] = a1.v[j];
-        r2[rl * p.C + c0 + j] = a2.v[j];
+        r1[rl * p.C + c0i + j] = a1.v[j];
+        r2[rl * p.C + c0i + j] = a2.v[j];
       }
     }
     __syncthreads();
@@ -358,8 +370,10 @@ __global__ void bn_relu_pool_bwd_kernel(const BnBwdParams p) {
         s += r1[r * p.C + c];
         t += r2[r * p.C + c];
       }
+      // S2 = sum dz*xhat = invstd * (sum dz*y - mean * sum dz)
+      const float m = p.mean[c], is = p.invstd[c];
       atomicAdd(p.sums + c, s);
-      atomicAdd(p.sums + p.C + c, t);
+      atomicAdd(p.sums + p.C + c, is * (t - m * s));
     }
   }
 }
@@ -435,24 +449,53 @@ __global__ void cross_entropy_kernel(const float* __restrict__ logits, const lon
   }
 }
 
-// blocks [0, nW): dW (and db); blocks [nW, ...): dX
-__global__ void linear_bwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w,
-                                  const float* __restrict__ dlogits, float* __restrict__ dw, float* __restrict__ db,
-                                  __nv_bfloat16* __restrict__ dx, int B, int F, int O, int nW) {
+// blocks [0, nW): dW (and db) for a tile of 64 features; blocks [nW, ...): dX.
+// dW[o][f] = sum_b dl[b][o] * x[b][f]: 64 feature lanes x 4 batch groups per block, the dl tile
+// staged in shared memory, O accumulators per thread, batch groups combined through smem.
+constexpr int kLinMaxO = 16;
+constexpr int kLinTileB = 256;
+
+__global__ void __launch_bounds__(256) linear_bwd_kernel(const __nv_bfloat16* __restrict__ x,
+                                                         const float* __restrict__ w,
+                                                         const float* __restrict__ dlogits, float* __restrict__ dw,
+                                                         float* __restrict__ db, __nv_bfloat16* __restrict__ dx,
+                                                         int B, int F, int O, int nW) {
+  __shared__ float s_dl[kLinTileB * kLinMaxO];
+  __shared__ float s_red[4][kLinMaxO][64];
   if (static_cast<int>(blockIdx.x) < nW) {
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx < O * F) {
-      const int o = idx / F, f = idx - o * F;
-      float acc = 0.f;
-      for (int i = 0; i < B; ++i)
-        acc = fmaf(dlogits[static_cast<long>(i) * O + o], __bfloat162float(x[static_cast<long>(i) * F + f]), acc);
-      dw[idx] = acc;
+    const int fl = threadIdx.x & 63, bg = threadIdx.x >> 6;
+    const int f = blockIdx.x * 64 + fl;
+    float acc[kLinMaxO];
+#pragma unroll
+    for (int o = 0; o < kLinMaxO; ++o) acc[o] = 0.f;
+    float dbacc = 0.f;
+    for (int b0 = 0; b0 < B; b0 += kLinTileB) {
+      const int nb = min(kLinTileB, B - b0);
+      __syncthreads();
+      for (int i = threadIdx.x; i < nb * O; i += blockDim.x) s_dl[i] = dlogits[static_cast<long>(b0) * O + i];
+      __syncthreads();
+      if (f < F) {
+#pragma unroll 4
+        for (int b = bg; b < nb; b += 4) {
+          const float xv = __bfloat162float(x[static_cast<long>(b0 + b) * F + f]);
+#pragma unroll
+          for (int o = 0; o < kLinMaxO; ++o)
+            if (o < O) acc[o] = fmaf(s_dl[b * O + o], xv, acc[o]);
+        }
+      }
+      if (blockIdx.x == 0 && threadIdx.x < O)
+        for (int b = 0; b < nb; ++b) dbacc += s_dl[b * O + threadIdx.x];
     }
-    if (idx < O) {
-      float acc = 0.f;
-      for (int i = 0; i < B; ++i) acc += dlogits[static_cast<long>(i) * O + idx];
-      db[idx] = acc;
+#pragma unroll
+    for (int o = 0; o < kLinMaxO; ++o)
+      if (o < O) s_red[bg][o][fl] = acc[o];
+    __syncthreads();
+    if (bg == 0 && f < F) {
+#pragma unroll
+      for (int o = 0; o < kLinMaxO; ++o)
+        if (o < O) dw[static_cast<long>(o) * F + f] = s_red[0][o][fl] + s_red[1][o][fl] + s_red[2][o][fl] + s_red[3][o][fl];
     }
+    if (blockIdx.x == 0 && threadIdx.x < O) db[threadIdx.x] = dbacc;
   } else {
     const long idx = static_cast<long>(blockIdx.x - nW) * blockDim.x + threadIdx.x;
     if (idx < static_cast<long>(B) * F) {
@@ -517,6 +560,58 @@ __global__ void prep_conv_weights_kernel(const float* __restrict__ master, __nv_
   }
 }
 
+// All conv layers in ONE launch: 64(co) x 64(ci) tiles of one tap are read with coalesced float4
+// loads, written to Wf as bf16 and transposed through shared memory into Wd (tap flipped).
+constexpr int kPrepMaxLayers = 20;
+struct PrepLayer {
+  const float* master;
+  __nv_bfloat16* wf;
+  __nv_bfloat16* wd;
+  int cout, cin, taps, kpad;
+  int tile_begin;  // first global tile index of this layer
+  int ci_tiles;
+};
+struct PrepTable {
+  PrepLayer l[kPrepMaxLayers];
+  int n;
+};
+
+__global__ void __launch_bounds__(256) prep_conv_weights_batched_kernel(const PrepTable t) {
+  __shared__ float tile[64][65];
+  int li = 0;
+  while (li + 1 < t.n && static_cast<int>(blockIdx.x) >= t.l[li + 1].tile_begin) ++li;
+  const PrepLayer L = t.l[li];
+  int tidx = blockIdx.x - L.tile_begin;
+  const int ci_t = tidx % L.ci_tiles;
+  tidx /= L.ci_tiles;
+  const int tap = tidx % L.taps;
+  const int co_t = tidx / L.taps;
+  const int co0 = co_t * 64, ci0 = ci_t * 64;
+  const int kvalid = L.taps * L.cin;
+  const int c4 = (threadIdx.x & 15) * 4;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int r = (threadIdx.x >> 4) + 16 * k;
+    const float4 v = *reinterpret_cast<const float4*>(L.master + static_cast<long>(co0 + r) * kvalid + tap * L.cin + ci0 + c4);
+    tile[r][c4] = v.x; tile[r][c4 + 1] = v.y; tile[r][c4 + 2] = v.z; tile[r][c4 + 3] = v.w;
+    uint2 o;
+    o.x = pack_bf16x2(v.x, v.y);
+    o.y = pack_bf16x2(v.z, v.w);
+    *reinterpret_cast<uint2*>(L.wf + static_cast<long>(co0 + r) * L.kpad + tap * L.cin + ci0 + c4) = o;
+  }
+  if (L.wd == nullptr) return;
+  __syncthreads();
+  const int ftap = L.taps - 1 - tap;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int ci = (threadIdx.x >> 4) + 16 * k;
+    uint2 o;
+    o.x = pack_bf16x2(tile[c4][ci], tile[c4 + 1][ci]);
+    o.y = pack_bf16x2(tile[c4 + 2][ci], tile[c4 + 3][ci]);
+    *reinterpret_cast<uint2*>(L.wd + (static_cast<long>(ci0 + ci) * L.taps + ftap) * L.cout + co0 + c4) = o;
+  }
+}
+
 static inline int grid_for(long work_items, int threads, int max_blocks = 148 * 16) {
   long b = (work_items + threads - 1) / threads;
   if (b > max_blocks) b = max_blocks;
@@ -529,9 +624,9 @@ static inline int grid_for(long work_items, int threads, int max_blocks = 148 * 
 using namespace b200dp;
 
 extern "C" int b200dp_im2col3x3_c3(const float* x_nchw, void* a0, int B, int H, int W, b200dp_stream_t s) {
-  const long total = static_cast<long>(B) * H * W * 8;
-  im2col_c3_kernel<<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(s)>>>(
-      x_nchw, static_cast<__nv_bfloat16*>(a0), B, H, W);
+  const size_t smem = 9 * (W + 2) * sizeof(float);
+  im2col_c3_kernel<<<B * H, 256, smem, static_cast<cudaStream_t>(s)>>>(x_nchw, static_cast<__nv_bfloat16*>(a0), B, H,
+                                                                       W);
   B200DP_CUDA_TRY(cudaGetLastError());
   return 0;
 }
@@ -632,8 +727,12 @@ extern "C" int b200dp_cross_entropy(const float* logits, const long long* target
 
 extern "C" int b200dp_linear_bwd(const void* x, const float* w, const float* dlogits, float* dw, float* db, void* dx,
                                  int B, int F, int O, b200dp_stream_t s) {
+  if (O > kLinMaxO) {
+    set_error("linear_bwd: O=%d exceeds the supported %d outputs", O, kLinMaxO);
+    return B200DP_EINVAL;
+  }
   const int threads = 256;
-  const int nW = (O * F + threads - 1) / threads;
+  const int nW = (F + 63) / 64;
   const int nX = static_cast<int>((static_cast<long>(B) * F + threads - 1) / threads);
   linear_bwd_kernel<<<nW + nX, threads, 0, static_cast<cudaStream_t>(s)>>>(
       static_cast<const __nv_bfloat16*>(x), w, dlogits, dw, db, static_cast<__nv_bfloat16*>(dx), B, F, O, nW);
@@ -731,4 +830,31 @@ extern "C" int b200dp_bn_relu_pool_bwd_noalloc(const void* y, const void* dout, 
   rc = launch_bn_bwd(false, p, stream);
   if (rc) return rc;
   return launch_bn_bwd(true, p, stream);
+}
+
+/* Batched form of b200dp_prep_conv_weights: all layers in one launch.  Arrays have n entries;
+ * layers need Cout % 64 == 0 and Cin % 64 == 0 (others: use the single-layer entry point). */
+extern "C" int b200dp_prep_conv_weights_batched(int n, const float* const* master, void* const* wf, void* const* wd,
+                                                const int* cout, const int* cin, const int* taps, const int* kpad,
+                                                b200dp_stream_t s) {
+  if (n < 1 || n > kPrepMaxLayers) {
+    set_error("prep_conv_weights_batched: n=%d outside [1, %d]", n, kPrepMaxLayers);
+    return B200DP_EINVAL;
+  }
+  PrepTable t{};
+  t.n = n;
+  int tiles = 0;
+  for (int i = 0; i < n; ++i) {
+    if (cout[i] % 64 || cin[i] % 64 || kpad[i] != taps[i] * cin[i]) {
+      set_error("prep_conv_weights_batched: layer %d (Cout=%d Cin=%d kpad=%d) needs multiples of 64 and no padding",
+                i, cout[i], cin[i], kpad[i]);
+      return B200DP_EINVAL;
+    }
+    t.l[i] = PrepLayer{master[i], static_cast<__nv_bfloat16*>(wf[i]), static_cast<__nv_bfloat16*>(wd[i]), cout[i],
+                       cin[i], taps[i], kpad[i], tiles, cin[i] / 64};
+    tiles += (cout[i] / 64) * taps[i] * (cin[i] / 64);
+  }
+  prep_conv_weights_batched_kernel<<<tiles, 256, 0, static_cast<cudaStream_t>(s)>>>(t);
+  B200DP_CUDA_TRY(cudaGetLastError());
+  return 0;
 }

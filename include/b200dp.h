@@ -136,6 +136,11 @@ int b200dp_sgd_momentum(float* p, const float* g, float* buf, long long n, float
  * bf16 Wd [Cin][taps*Cout] with the taps flipped (the dgrad operand). */
 int b200dp_prep_conv_weights(const float* master, void* wf, void* wd, int Cout, int Cin, int taps, int kpad,
                              b200dp_stream_t stream);
+/* The same for n layers in ONE launch (tiled, coalesced, transposed through shared memory);
+ * every layer needs Cout % 64 == 0, Cin % 64 == 0 and kpad == taps*Cin. */
+int b200dp_prep_conv_weights_batched(int n, const float* const* master, void* const* wf, void* const* wd,
+                                     const int* cout, const int* cin, const int* taps, const int* kpad,
+                                     b200dp_stream_t stream);
 
 /* ------------------------------------------------------------------------
  * Rendezvous store (TCP key-value, rank 0 hosts it on master_ip:port)

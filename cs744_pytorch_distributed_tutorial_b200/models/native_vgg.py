@@ -111,6 +111,10 @@ class _Block:
     pass
 
 
+def self_first_is_64(module: nn.Module) -> bool:
+    return module.block_specs()[0].cout == 64
+
+
 _TUNE_CACHE: Dict[tuple, int] = {}   # (kind, B, hw, cin, cout) -> best block_n / split_k, per process
 
 
@@ -136,7 +140,7 @@ def _time_captured(fn, reps: int = 8, replays: int = 3) -> float:
 
 class NativeVGG:
     def __init__(self, module: nn.Module, max_batch: int, heap=None, conv_stats_fused: bool = True,
-                 autotune: bool = True):
+                 autotune: bool = True, direct_first_layer: bool = False):
         dev = next(module.parameters()).device
         if dev.type != "cuda":
             raise RuntimeError("NativeVGG needs the module on a CUDA device")
@@ -147,6 +151,9 @@ class NativeVGG:
         self.max_batch = max_batch
         self.heap = heap
         self.conv_stats_fused = conv_stats_fused
+        # layer 0 (3 input channels): optional direct CUDA-core conv instead of patch gather + K=64
+        # tcgen05 GEMM.  Measured slower on B200 at B=256 (LDS-bound: 122 us vs 33 + 44 us), so off.
+        self.direct_first_layer = direct_first_layer and self_first_is_64(module)
         self.specs = module.block_specs()
         self.layout = FlatLayout(list(module.named_parameters()))
         alloc = (lambda n, dt=torch.float32: heap.zeros(n, dt)) if heap is not None else \
@@ -232,7 +239,10 @@ class NativeVGG:
             b.kin = 64 if b.first else s.cin           # GEMM K per tap (layer 0: 27 -> 64 padded, 1 tap)
             b.taps = 1 if b.first else 9
             hw = s.hw
-            b.x_in = torch.zeros(B, hw, hw, b.kin, device=dev, dtype=bf) if b.first else self.blocks[-1].out
+            if b.first:
+                b.x_in = None if self.direct_first_layer else torch.zeros(B, hw, hw, b.kin, device=dev, dtype=bf)
+            else:
+                b.x_in = self.blocks[-1].out
             b.y = torch.empty(B, hw, hw, s.cout, device=dev, dtype=bf)
             ho = hw // 2 if s.pool else hw
             b.out = torch.empty(B, ho, ho, s.cout, device=dev, dtype=bf)
@@ -244,6 +254,7 @@ class NativeVGG:
             b.mean = torch.empty(s.cout, device=dev)
             b.invstd = torch.empty(s.cout, device=dev)
             kpad = b.taps * b.kin
+            b.direct = b.first and self.direct_first_layer
             b.wf = torch.empty(s.cout, kpad, device=dev, dtype=bf)
             b.wd = None if b.first else torch.empty(s.cin, 9 * s.cout, device=dev, dtype=bf)
             ew, eb = L.by_name[f"layers.{s.conv_idx}.weight"], L.by_name[f"layers.{s.conv_idx}.bias"]
@@ -293,6 +304,8 @@ class NativeVGG:
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):
             for i, b in enumerate(self.blocks):
+                if b.direct:
+                    continue
                 s = b.spec
                 x_in, y, dy = b.x_in[:B], b.y[:B], b.dy[:B]
                 key = (B, s.hw, b.kin, s.cout, b.taps)
@@ -325,7 +338,7 @@ class NativeVGG:
         """bf16 operand copies of the fp32 master weights: Wf (forward) and Wd (dgrad)."""
         if getattr(self, "_prep", None) is None:
             self._prep = K.BatchedWeightPrep([(b.w_master, b.wf, b.wd, b.spec.cout, b.spec.cin, 9, b.taps * b.kin)
-                                              for b in self.blocks])
+                                              for b in self.blocks if not b.direct])
         self._prep()
 
     # ------------------------------------------------------------------ forward
@@ -339,13 +352,17 @@ class NativeVGG:
             self.zero_region.zero_()
         for b in self.blocks:
             s = b.spec
-            x_in = b.x_in[:B]
-            if b.first:
-                K.im2col3x3_c3(x.contiguous(), x_in)
             y = b.y[:B]
             fused = training and self.conv_stats_fused
-            K.conv_igemm(x_in, b.wf, b.bias, y, stats=b.stats if fused else None, taps=b.taps,
-                         block_n=b.fwd_block_n)
+            if b.direct:
+                self._x_first = x if x.is_contiguous() else x.contiguous()
+                K.conv3x3_c3_fwd(self._x_first, b.w_master, b.bias, y, stats=b.stats if fused else None)
+            else:
+                x_in = b.x_in[:B]
+                if b.first:
+                    K.im2col3x3_c3(x.contiguous(), x_in)
+                K.conv_igemm(x_in, b.wf, b.bias, y, stats=b.stats if fused else None, taps=b.taps,
+                             block_n=b.fwd_block_n)
             if training and not fused:
                 K.bn_stats(y, b.stats)
             K.bn_relu_pool_fwd(y, b.stats, b.gamma, b.beta, b.running_mean, b.running_var, b.nbt, b.mean, b.invstd,
@@ -378,8 +395,11 @@ class NativeVGG:
                                b.g_beta, s.pool)
             # the conv bias feeds a training-mode BatchNorm, so its exact gradient is zero:
             # it simply keeps the zero written by the flat_grads clear at the top of backward().
-            K.conv_wgrad(b.dy[:B], b.x_in[:B], b.g_w, taps=b.taps, cin_valid=(27 if b.first else None),
-                         split_k=b.wgrad_split_k)
+            if b.direct:
+                K.conv3x3_c3_wgrad(b.dy[:B], self._x_first, b.g_w)
+            else:
+                K.conv_wgrad(b.dy[:B], b.x_in[:B], b.g_w, taps=b.taps, cin_valid=(27 if b.first else None),
+                             split_k=b.wgrad_split_k)
             if self.on_bucket_ready is not None:
                 for k in self._bucket_of_block.get(i, ()):
                     self.on_bucket_ready(k)

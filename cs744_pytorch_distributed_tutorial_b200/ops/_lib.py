@@ -25,10 +25,13 @@ _PROTOTYPES = {
     "b200dp_conv_igemm": [P, P, P, P, P, I, I, I, I, I, I, I, P],
     "b200dp_conv_wgrad": [P, P, P, I, I, I, I, I, I, I, I, I, P],
     "b200dp_im2col3x3_c3": [P, P, I, I, I, P],
+    "b200dp_conv3x3_c3_fwd": [P, P, P, P, P, I, I, I, P],
+    "b200dp_conv3x3_c3_wgrad": [P, P, P, I, I, I, P],
     "b200dp_bn_stats": [P, P, LL, I, P],
     "b200dp_bn_relu_pool_fwd": [P, P, P, P, P, P, P, P, P, P, I, I, I, I, I, I, F, F, P],
     "b200dp_bn_relu_pool_bwd_reduce": [P, P, P, P, P, P, P, I, I, I, I, I, P],
     "b200dp_bn_relu_pool_bwd_apply": [P, P, P, P, P, P, P, P, P, P, I, I, I, I, I, P],
+    "b200dp_bn_relu_pool_bwd_fused": [P, P, P, P, P, P, P, P, P, P, I, I, I, I, I, P],
     "b200dp_linear_fwd": [P, P, P, P, I, I, I, P],
     "b200dp_cross_entropy": [P, P, P, P, P, I, I, F, P],
     "b200dp_linear_bwd": [P, P, P, P, P, P, I, I, I, P],

@@ -13,6 +13,11 @@ import torch
 from . import _lib
 from ._lib import call, ptr, stream_ptr
 
+import os
+
+# one cooperative launch (grid barrier) vs reduce + apply; measured on B200: the two-pass form with a
+# full 444-block wave is ~3% faster per step than the co-residency-capped cooperative grid, so off.
+BN_BWD_FUSED = os.environ.get("B200DP_BN_BWD_FUSED", "0") != "0"
 BN_EPS = 1e-5
 BN_MOMENTUM = 0.1
 
@@ -67,6 +72,27 @@ def im2col3x3_c3(x_nchw: torch.Tensor, a0: torch.Tensor) -> torch.Tensor:
     return a0
 
 
+def conv3x3_c3_fwd(x_nchw: torch.Tensor, w: torch.Tensor, bias: torch.Tensor, y: torch.Tensor,
+                   stats: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """First layer as a direct conv: x fp32 NCHW [B,3,H,W], w fp32 [64, 27] (KRSC), y bf16 NHWC [B,H,W,64]."""
+    _chk(x_nchw, torch.float32, "x")
+    _chk(y, torch.bfloat16, "y")
+    B, C, H, W = x_nchw.shape
+    assert C == 3 and w.numel() == 64 * 27 and y.shape == (B, H, W, 64)
+    call("b200dp_conv3x3_c3_fwd", ptr(x_nchw), ptr(w), ptr(bias), ptr(y), ptr(stats), B, H, W, stream_ptr())
+    return y
+
+
+def conv3x3_c3_wgrad(dy: torch.Tensor, x_nchw: torch.Tensor, dw: torch.Tensor) -> torch.Tensor:
+    """dw[64, 27] += sum_p dy[p] (x) patch(x)[p]; ``dw`` must be zeroed by the caller."""
+    _chk(dy, torch.bfloat16, "dy")
+    _chk(x_nchw, torch.float32, "x")
+    B, C, H, W = x_nchw.shape
+    assert C == 3 and dw.numel() == 64 * 27 and dy.shape == (B, H, W, 64)
+    call("b200dp_conv3x3_c3_wgrad", ptr(dy), ptr(x_nchw), ptr(dw), B, H, W, stream_ptr())
+    return dw
+
+
 def bn_stats(y: torch.Tensor, stats: torch.Tensor) -> torch.Tensor:
     _chk(y, torch.bfloat16, "y")
     _chk(stats, torch.float32, "stats")
@@ -84,9 +110,14 @@ def bn_relu_pool_fwd(y, stats, gamma, beta, running_mean, running_var, num_batch
     return out
 
 
-def bn_relu_pool_bwd(y, dout, mean, invstd, gamma, beta, sums, dy, dgamma, dbeta, pool: bool):
-    """Two launches: per-channel reduction into ``sums`` (must be zero), then the dY pass."""
+def bn_relu_pool_bwd(y, dout, mean, invstd, gamma, beta, sums, dy, dgamma, dbeta, pool: bool, fused: Optional[bool] = None):
+    """Per-channel reduction into ``sums`` (must be zero), then the dY pass -- in one cooperative
+    launch with a grid-wide barrier (``fused``) or as two launches."""
     B, H, W, C = y.shape
+    if BN_BWD_FUSED if fused is None else fused:
+        call("b200dp_bn_relu_pool_bwd_fused", ptr(y), ptr(dout), ptr(mean), ptr(invstd), ptr(gamma), ptr(beta),
+             ptr(sums), ptr(dy), ptr(dgamma), ptr(dbeta), B, H, W, C, int(pool), stream_ptr())
+        return dy
     call("b200dp_bn_relu_pool_bwd_reduce", ptr(y), ptr(dout), ptr(mean), ptr(invstd), ptr(gamma), ptr(beta),
          ptr(sums), B, H, W, C, int(pool), stream_ptr())
     call("b200dp_bn_relu_pool_bwd_apply", ptr(y), ptr(dout), ptr(mean), ptr(invstd), ptr(gamma), ptr(beta),

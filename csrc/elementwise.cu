@@ -10,6 +10,7 @@
 // unbiased for running_var; MaxPool2d(2,2) routes the gradient to the first
 // maximum in scan order; CrossEntropyLoss(mean); SGD lr/momentum/weight_decay
 // with dampening 0 and weight decay on every parameter.
+#include <cooperative_groups.h>
 #include <stdio.h>
 
 #include "../include/b200dp.h"
@@ -56,20 +57,27 @@ B200DP_DEVINL Vec8 load_f32x8(const float* p) {
 // matrix (27 real columns, k = (r*3+s)*3 + c, the rest zero) so that the first
 // conv is a plain K=64 GEMM for the tcgen05 kernel.
 // ---------------------------------------------------------------------------
-// One block per image row: the 3 x 3 x (W+2) input window is staged in shared memory with
-// coalesced loads, then every thread emits one 16-byte chunk of a pixel's 64-wide patch row.
-__global__ void im2col_c3_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ a0, int B, int H, int W) {
-  extern __shared__ float win[];  // [3 rows][3 channels][W + 2]
+// One block per group of kIm2colRows image rows: the (rows+2) x 3 x (W+2) input window is staged in
+// shared memory with coalesced loads, then every thread emits 16-byte chunks of the 64-wide patch rows.
+constexpr int kIm2colRows = 4;
+
+__global__ void __launch_bounds__(256) im2col_c3_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ a0,
+                                                        int B, int H, int W) {
+  extern __shared__ float win[];  // [rows + 2][3 channels][W + 2]
   const int Wp = W + 2;
-  const int n = blockIdx.x / H, h = blockIdx.x - n * H;
-  for (int i = threadIdx.x; i < 9 * Wp; i += blockDim.x) {
-    const int r = i / (3 * Wp), c = (i / Wp) % 3, ww = i % Wp - 1;
-    const int hh = h + r - 1;
+  const int groups = (H + kIm2colRows - 1) / kIm2colRows;
+  const int n = blockIdx.x / groups, h0 = (blockIdx.x - n * groups) * kIm2colRows;
+  const int rows = min(kIm2colRows, H - h0);
+  for (int i = threadIdx.x; i < (rows + 2) * 3 * Wp; i += blockDim.x) {
+    const int r = i / (3 * Wp), rem = i - r * 3 * Wp;
+    const int c = rem / Wp, ww = rem - c * Wp - 1;
+    const int hh = h0 + r - 1;
     win[i] = (hh >= 0 && hh < H && ww >= 0 && ww < W) ? __ldg(x + ((static_cast<long>(n) * 3 + c) * H + hh) * W + ww) : 0.f;
   }
   __syncthreads();
-  for (int t = threadIdx.x; t < W * 8; t += blockDim.x) {
-    const int w = t >> 3, chunk = t & 7;
+  for (int t = threadIdx.x; t < rows * W * 8; t += blockDim.x) {
+    const int chunk = t & 7, pix = t >> 3;
+    const int pr = pix / W, w = pix - pr * W;
     Vec8 r;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
@@ -77,11 +85,11 @@ __global__ void im2col_c3_kernel(const float* __restrict__ x, __nv_bfloat16* __r
       float v = 0.f;
       if (k < 27) {
         const int tap = k / 3, c = k - tap * 3;
-        v = win[(tap / 3) * 3 * Wp + c * Wp + w + tap % 3];
+        v = win[(pr + tap / 3) * 3 * Wp + c * Wp + w + tap % 3];
       }
       r.v[j] = v;
     }
-    store_bf16x8(a0 + ((static_cast<long>(n) * H + h) * W + w) * 64 + chunk * 8, r);
+    store_bf16x8(a0 + ((static_cast<long>(n) * H + h0 + pr) * W + w) * 64 + chunk * 8, r);
   }
 }
 
@@ -148,17 +156,29 @@ struct BnFwdParams {
   float momentum, eps;
 };
 
-__global__ void bn_relu_pool_fwd_kernel(const BnFwdParams p) {
+B200DP_DEVINL Vec8 unpack8(const uint4& u) {
+  Vec8 r;
+  float2 f;
+  f = unpack_bf16x2(u.x); r.v[0] = f.x; r.v[1] = f.y;
+  f = unpack_bf16x2(u.y); r.v[2] = f.x; r.v[3] = f.y;
+  f = unpack_bf16x2(u.z); r.v[4] = f.x; r.v[5] = f.y;
+  f = unpack_bf16x2(u.w); r.v[6] = f.x; r.v[7] = f.y;
+  return r;
+}
+
+// Each thread owns 8 channels (scale/shift stay in registers) and walks output pixels two at a
+// time so that up to eight 16-byte loads are in flight per thread.
+__global__ void __launch_bounds__(256, 3) bn_relu_pool_fwd_kernel(const BnFwdParams p) {
   const int chunks = p.C / 8;
+  const int rows_per_block = blockDim.x / chunks;
+  const int chunk = threadIdx.x % chunks;
+  const int rl = threadIdx.x / chunks;
+  const int c0 = chunk * 8;
   const int Ho = p.pool ? p.H / 2 : p.H, Wo = p.pool ? p.W / 2 : p.W;
-  const long total = static_cast<long>(p.B) * Ho * Wo * chunks;
+  const long Q = static_cast<long>(p.B) * Ho * Wo;
   const float count = static_cast<float>(static_cast<long>(p.B) * p.H * p.W);
-  for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<long>(gridDim.x) * blockDim.x) {
-    const int chunk = static_cast<int>(i % chunks);
-    const long q = i / chunks;
-    const int c0 = chunk * 8;
-    Vec8 scale, shift;
+  Vec8 scale, shift;
+  {
     const Vec8 g = load_f32x8(p.gamma + c0), b = load_f32x8(p.beta + c0);
     if (p.training) {
       const Vec8 s1 = load_f32x8(p.stats + c0), s2 = load_f32x8(p.stats + p.C + c0);
@@ -171,7 +191,7 @@ __global__ void bn_relu_pool_fwd_kernel(const BnFwdParams p) {
         scale.v[j] = g.v[j] * invstd.v[j];
         shift.v[j] = b.v[j] - mean.v[j] * scale.v[j];
       }
-      if (q == 0) {
+      if (blockIdx.x == 0 && rl == 0) {
         // one thread per channel chunk owns the side outputs and the running statistics
         const float unbias = count > 1.f ? count / (count - 1.f) : 1.f;
 #pragma unroll
@@ -191,27 +211,57 @@ __global__ void bn_relu_pool_fwd_kernel(const BnFwdParams p) {
         shift.v[j] = b.v[j] - rm.v[j] * scale.v[j];
       }
     }
-    Vec8 o;
+  }
+  if (rl >= rows_per_block) return;
+  const long stride = static_cast<long>(gridDim.x) * rows_per_block;
+  const long rowb = static_cast<long>(p.W) * p.C;
+  for (long qa = static_cast<long>(blockIdx.x) * rows_per_block + rl; qa < Q; qa += 2 * stride) {
+    const long qb = qa + stride;
+    const bool hasb = qb < Q;
     if (p.pool) {
-      const int wo = static_cast<int>(q % Wo);
-      const int ho = static_cast<int>((q / Wo) % Ho);
-      const long n = q / (static_cast<long>(Wo) * Ho);
-      const __nv_bfloat16* base = p.y + ((n * p.H + 2 * ho) * p.W + 2 * wo) * p.C + c0;
-      const Vec8 a = load_bf16x8(base), bq = load_bf16x8(base + p.C);
-      const Vec8 c = load_bf16x8(base + static_cast<long>(p.W) * p.C),
-                 d = load_bf16x8(base + static_cast<long>(p.W) * p.C + p.C);
+      long off[2];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const float za = fmaf(a.v[j], scale.v[j], shift.v[j]), zb = fmaf(bq.v[j], scale.v[j], shift.v[j]);
-        const float zc = fmaf(c.v[j], scale.v[j], shift.v[j]), zd = fmaf(d.v[j], scale.v[j], shift.v[j]);
-        o.v[j] = fmaxf(fmaxf(fmaxf(za, zb), fmaxf(zc, zd)), 0.f);
+      for (int u = 0; u < 2; ++u) {
+        const long q = (u == 0 || hasb) ? (u == 0 ? qa : qb) : qa;
+        const int wo = static_cast<int>(q % Wo);
+        const int ho = static_cast<int>((q / Wo) % Ho);
+        const long n = q / (static_cast<long>(Wo) * Ho);
+        off[u] = ((n * p.H + 2 * ho) * p.W + 2 * wo) * p.C + c0;
+      }
+      uint4 raw[2][4];
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        raw[u][0] = *reinterpret_cast<const uint4*>(p.y + off[u]);
+        raw[u][1] = *reinterpret_cast<const uint4*>(p.y + off[u] + p.C);
+        raw[u][2] = *reinterpret_cast<const uint4*>(p.y + off[u] + rowb);
+        raw[u][3] = *reinterpret_cast<const uint4*>(p.y + off[u] + rowb + p.C);
+      }
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        if (u == 1 && !hasb) break;
+        const Vec8 a = unpack8(raw[u][0]), bq = unpack8(raw[u][1]), c = unpack8(raw[u][2]), d = unpack8(raw[u][3]);
+        Vec8 o;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float za = fmaf(a.v[j], scale.v[j], shift.v[j]), zb = fmaf(bq.v[j], scale.v[j], shift.v[j]);
+          const float zc = fmaf(c.v[j], scale.v[j], shift.v[j]), zd = fmaf(d.v[j], scale.v[j], shift.v[j]);
+          o.v[j] = fmaxf(fmaxf(fmaxf(za, zb), fmaxf(zc, zd)), 0.f);
+        }
+        store_bf16x8(p.out + (u == 0 ? qa : qb) * p.C + c0, o);
       }
     } else {
-      const Vec8 a = load_bf16x8(p.y + q * p.C + c0);
+      const uint4 ra = *reinterpret_cast<const uint4*>(p.y + qa * p.C + c0);
+      const uint4 rb = *reinterpret_cast<const uint4*>(p.y + (hasb ? qb : qa) * p.C + c0);
+      const Vec8 a = unpack8(ra), b2 = unpack8(rb);
+      Vec8 oa, ob;
 #pragma unroll
-      for (int j = 0; j < 8; ++j) o.v[j] = fmaxf(fmaf(a.v[j], scale.v[j], shift.v[j]), 0.f);
+      for (int j = 0; j < 8; ++j) {
+        oa.v[j] = fmaxf(fmaf(a.v[j], scale.v[j], shift.v[j]), 0.f);
+        ob.v[j] = fmaxf(fmaf(b2.v[j], scale.v[j], shift.v[j]), 0.f);
+      }
+      store_bf16x8(p.out + qa * p.C + c0, oa);
+      if (hasb) store_bf16x8(p.out + qb * p.C + c0, ob);
     }
-    store_bf16x8(p.out + q * p.C + c0, o);
   }
 }
 
@@ -240,8 +290,7 @@ struct BnBwdParams {
 //   pass 1 accumulates  a1 = sum dz,  a2 = sum dz*y ;  S2 = invstd*(a2 - mean*a1) at the end
 //   pass 2 writes       dy = scale*dz + c0 + c1*y   c1 = -scale*invstd*S2/P, c0 = -scale*S1/P - c1*mean
 template <bool APPLY>
-__global__ void __launch_bounds__(256, 3) bn_relu_pool_bwd_kernel(const BnBwdParams p) {
-  extern __shared__ float red[];
+B200DP_DEVINL void bn_relu_pool_bwd_body(const BnBwdParams& p, float* red) {
   const int chunks = p.C / 8;
   const int rows_per_block = blockDim.x / chunks;
   const int chunk = threadIdx.x % chunks;
@@ -261,7 +310,13 @@ __global__ void __launch_bounds__(256, 3) bn_relu_pool_bwd_kernel(const BnBwdPar
       shift.v[j] = b.v[j] - mean.v[j] * scale.v[j];
     }
     if (APPLY) {
-      const Vec8 s1 = load_f32x8(p.sums + c0i), s2 = load_f32x8(p.sums + p.C + c0i);
+      // L2 loads: in the fused kernel these sums were produced by atomics earlier in the same launch
+      Vec8 s1, s2;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        s1.v[j] = __ldcg(p.sums + c0i + j);
+        s2.v[j] = __ldcg(p.sums + p.C + c0i + j);
+      }
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         c1.v[j] = -scale.v[j] * invstd.v[j] * s2.v[j] * inv_count;
@@ -378,25 +433,57 @@ __global__ void __launch_bounds__(256, 3) bn_relu_pool_bwd_kernel(const BnBwdPar
   }
 }
 
+template <bool APPLY>
+__global__ void __launch_bounds__(256, 3) bn_relu_pool_bwd_kernel(const BnBwdParams p) {
+  extern __shared__ float red[];
+  bn_relu_pool_bwd_body<APPLY>(p, red);
+}
+
+// Both passes in one cooperative launch: reduce, grid-wide barrier, apply.  The second pass finds
+// y and dout still in L2, and a layer costs one launch instead of two.
+__global__ void __launch_bounds__(256, 3) bn_relu_pool_bwd_fused_kernel(const BnBwdParams p) {
+  extern __shared__ float red[];
+  bn_relu_pool_bwd_body<false>(p, red);
+  __threadfence();
+  cooperative_groups::this_grid().sync();
+  bn_relu_pool_bwd_body<true>(p, red);
+}
+
 // ---------------------------------------------------------------------------
 // classifier: logits = x W^T + b ; softmax cross-entropy (mean) ; backward
 // ---------------------------------------------------------------------------
-__global__ void linear_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w,
-                                  const float* __restrict__ bias, float* __restrict__ logits, int B, int F, int O) {
+constexpr int kLinMaxO = 16;
+constexpr int kLinTileB = 256;
+
+// one warp per sample: the 16 activations of a lane are loaded once, all O dot products run as
+// independent chains, then O warp reductions
+__global__ void __launch_bounds__(128) linear_fwd_kernel(const __nv_bfloat16* __restrict__ x,
+                                                         const float* __restrict__ w, const float* __restrict__ bias,
+                                                         float* __restrict__ logits, int B, int F, int O) {
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (warp >= B) return;
   const __nv_bfloat16* xr = x + static_cast<long>(warp) * F;
-  for (int o = 0; o < O; ++o) {
-    float acc = 0.f;
-    for (int f = lane * 8; f < F; f += 256) {
-      const Vec8 xv = load_bf16x8(xr + f);
-      const Vec8 wv = load_f32x8(w + static_cast<long>(o) * F + f);
+  float acc[kLinMaxO];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) acc = fmaf(xv.v[j], wv.v[j], acc);
+  for (int o = 0; o < kLinMaxO; ++o) acc[o] = 0.f;
+  for (int f = lane * 8; f < F; f += 256) {
+    const Vec8 xv = load_bf16x8(xr + f);
+#pragma unroll
+    for (int o = 0; o < kLinMaxO; ++o) {
+      if (o < O) {
+        const Vec8 wv = load_f32x8(w + static_cast<long>(o) * F + f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[o] = fmaf(xv.v[j], wv.v[j], acc[o]);
+      }
     }
-    acc = warp_sum(acc);
-    if (lane == 0) logits[static_cast<long>(warp) * O + o] = acc + bias[o];
+  }
+#pragma unroll
+  for (int o = 0; o < kLinMaxO; ++o) {
+    if (o < O) {
+      const float t = warp_sum(acc[o]);
+      if (lane == 0) logits[static_cast<long>(warp) * O + o] = t + bias[o];
+    }
   }
 }
 
@@ -452,9 +539,6 @@ __global__ void cross_entropy_kernel(const float* __restrict__ logits, const lon
 // blocks [0, nW): dW (and db) for a tile of 64 features; blocks [nW, ...): dX.
 // dW[o][f] = sum_b dl[b][o] * x[b][f]: 64 feature lanes x 4 batch groups per block, the dl tile
 // staged in shared memory, O accumulators per thread, batch groups combined through smem.
-constexpr int kLinMaxO = 16;
-constexpr int kLinTileB = 256;
-
 __global__ void __launch_bounds__(256) linear_bwd_kernel(const __nv_bfloat16* __restrict__ x,
                                                          const float* __restrict__ w,
                                                          const float* __restrict__ dlogits, float* __restrict__ dw,
@@ -463,28 +547,27 @@ __global__ void __launch_bounds__(256) linear_bwd_kernel(const __nv_bfloat16* __
   __shared__ float s_dl[kLinTileB * kLinMaxO];
   __shared__ float s_red[4][kLinMaxO][64];
   if (static_cast<int>(blockIdx.x) < nW) {
+    // nW = feature tiles x batch slices; partial sums are combined with atomics (dw, db zero on entry)
+    const int ftiles = (F + 63) / 64;
+    const int ft = blockIdx.x % ftiles, slice = blockIdx.x / ftiles, nslices = nW / ftiles;
     const int fl = threadIdx.x & 63, bg = threadIdx.x >> 6;
-    const int f = blockIdx.x * 64 + fl;
+    const int f = ft * 64 + fl;
+    const int per = (B + nslices - 1) / nslices;
+    const int b_lo = slice * per, b_hi = min(B, b_lo + per);
     float acc[kLinMaxO];
 #pragma unroll
     for (int o = 0; o < kLinMaxO; ++o) acc[o] = 0.f;
-    float dbacc = 0.f;
-    for (int b0 = 0; b0 < B; b0 += kLinTileB) {
-      const int nb = min(kLinTileB, B - b0);
-      __syncthreads();
-      for (int i = threadIdx.x; i < nb * O; i += blockDim.x) s_dl[i] = dlogits[static_cast<long>(b0) * O + i];
-      __syncthreads();
-      if (f < F) {
+    const int nb = max(b_hi - b_lo, 0);
+    for (int i = threadIdx.x; i < nb * O; i += blockDim.x) s_dl[i] = dlogits[static_cast<long>(b_lo) * O + i];
+    __syncthreads();
+    if (f < F) {
 #pragma unroll 4
-        for (int b = bg; b < nb; b += 4) {
-          const float xv = __bfloat162float(x[static_cast<long>(b0 + b) * F + f]);
+      for (int b = bg; b < nb; b += 4) {
+        const float xv = __bfloat162float(x[static_cast<long>(b_lo + b) * F + f]);
 #pragma unroll
-          for (int o = 0; o < kLinMaxO; ++o)
-            if (o < O) acc[o] = fmaf(s_dl[b * O + o], xv, acc[o]);
-        }
+        for (int o = 0; o < kLinMaxO; ++o)
+          if (o < O) acc[o] = fmaf(s_dl[b * O + o], xv, acc[o]);
       }
-      if (blockIdx.x == 0 && threadIdx.x < O)
-        for (int b = 0; b < nb; ++b) dbacc += s_dl[b * O + threadIdx.x];
     }
 #pragma unroll
     for (int o = 0; o < kLinMaxO; ++o)
@@ -493,9 +576,15 @@ __global__ void __launch_bounds__(256) linear_bwd_kernel(const __nv_bfloat16* __
     if (bg == 0 && f < F) {
 #pragma unroll
       for (int o = 0; o < kLinMaxO; ++o)
-        if (o < O) dw[static_cast<long>(o) * F + f] = s_red[0][o][fl] + s_red[1][o][fl] + s_red[2][o][fl] + s_red[3][o][fl];
+        if (o < O)
+          atomicAdd(dw + static_cast<long>(o) * F + f,
+                    s_red[0][o][fl] + s_red[1][o][fl] + s_red[2][o][fl] + s_red[3][o][fl]);
     }
-    if (blockIdx.x == 0 && threadIdx.x < O) db[threadIdx.x] = dbacc;
+    if (ft == 0 && threadIdx.x < O) {
+      float dbacc = 0.f;
+      for (int b = 0; b < nb; ++b) dbacc += s_dl[b * O + threadIdx.x];
+      atomicAdd(db + threadIdx.x, dbacc);
+    }
   } else {
     const long idx = static_cast<long>(blockIdx.x - nW) * blockDim.x + threadIdx.x;
     if (idx < static_cast<long>(B) * F) {
@@ -624,9 +713,10 @@ static inline int grid_for(long work_items, int threads, int max_blocks = 148 * 
 using namespace b200dp;
 
 extern "C" int b200dp_im2col3x3_c3(const float* x_nchw, void* a0, int B, int H, int W, b200dp_stream_t s) {
-  const size_t smem = 9 * (W + 2) * sizeof(float);
-  im2col_c3_kernel<<<B * H, 256, smem, static_cast<cudaStream_t>(s)>>>(x_nchw, static_cast<__nv_bfloat16*>(a0), B, H,
-                                                                       W);
+  const size_t smem = (kIm2colRows + 2) * 3 * (W + 2) * sizeof(float);
+  const int groups = (H + kIm2colRows - 1) / kIm2colRows;
+  im2col_c3_kernel<<<B * groups, 256, smem, static_cast<cudaStream_t>(s)>>>(
+      x_nchw, static_cast<__nv_bfloat16*>(a0), B, H, W);
   B200DP_CUDA_TRY(cudaGetLastError());
   return 0;
 }
@@ -661,8 +751,14 @@ extern "C" int b200dp_bn_relu_pool_fwd(const void* y, const float* stats, const 
   BnFwdParams p{static_cast<const __nv_bfloat16*>(y), stats, gamma, beta, running_mean, running_var,
                 num_batches_tracked, save_mean, save_invstd, static_cast<__nv_bfloat16*>(out),
                 B, H, W, C, pool, training, momentum, eps};
-  const long total = static_cast<long>(B) * (pool ? H / 2 : H) * (pool ? W / 2 : W) * (C / 8);
-  bn_relu_pool_fwd_kernel<<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(s)>>>(p);
+  if (C > 2048) {
+    set_error("bn_relu_pool_fwd: C=%d too wide for a 256-thread block", C);
+    return B200DP_EINVAL;
+  }
+  const long Q = static_cast<long>(B) * (pool ? H / 2 : H) * (pool ? W / 2 : W);
+  const int rows_per_block = 256 / (C / 8);
+  // two output pixels per thread per iteration; at most one resident wave (3 blocks / SM)
+  bn_relu_pool_fwd_kernel<<<grid_for(Q, rows_per_block * 2, 148 * 3), 256, 0, static_cast<cudaStream_t>(s)>>>(p);
   B200DP_CUDA_TRY(cudaGetLastError());
   return 0;
 }
@@ -676,12 +772,51 @@ static int launch_bn_bwd(bool apply, const BnBwdParams& p, cudaStream_t s) {
   const int rows_per_block = threads / (p.C / 8);
   const size_t smem = apply ? 0 : 2 * rows_per_block * p.C * sizeof(float);
   const long Q = static_cast<long>(p.B) * (p.pool ? p.H / 2 : p.H) * (p.pool ? p.W / 2 : p.W);
-  const int blocks = grid_for(Q, rows_per_block * (apply ? 2 : 4), 148 * 8);
+  // at most one resident wave (3 blocks / SM): a grid-stride loop balances better than a ragged tail
+  const int blocks = grid_for(Q, rows_per_block, 148 * 3);
   if (apply)
     bn_relu_pool_bwd_kernel<true><<<blocks, threads, smem, s>>>(p);
   else
     bn_relu_pool_bwd_kernel<false><<<blocks, threads, smem, s>>>(p);
   B200DP_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+/* reduce + apply in ONE cooperative launch (sums must be zero on entry, as for the two-pass form). */
+extern "C" int b200dp_bn_relu_pool_bwd_fused(const void* y, const void* dout, const float* mean, const float* invstd,
+                                             const float* gamma, const float* beta, float* sums, void* dy,
+                                             float* dgamma, float* dbeta, int B, int H, int W, int C, int pool,
+                                             b200dp_stream_t s) {
+  BnBwdParams p{static_cast<const __nv_bfloat16*>(y), static_cast<const __nv_bfloat16*>(dout), mean, invstd, gamma,
+                beta, sums, static_cast<__nv_bfloat16*>(dy), dgamma, dbeta, B, H, W, C, pool};
+  if (p.C % 8 != 0 || p.C > 2048 || (p.pool && ((p.H | p.W) & 1))) {
+    set_error("bn_relu_pool_bwd_fused: unsupported shape H=%d W=%d C=%d pool=%d", p.H, p.W, p.C, p.pool);
+    return B200DP_EINVAL;
+  }
+  const int threads = 256;
+  const int rows_per_block = threads / (p.C / 8);
+  const size_t smem = 2 * rows_per_block * p.C * sizeof(float);
+  static int max_blocks = 0;  // co-resident limit for the cooperative grid
+  if (max_blocks == 0) {
+    int per_sm = 0, sms = 0, dev = 0;
+    B200DP_CUDA_TRY(cudaGetDevice(&dev));
+    B200DP_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    B200DP_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bn_relu_pool_bwd_fused_kernel, threads, smem));
+    if (per_sm < 1) {
+      set_error("bn_relu_pool_bwd_fused: kernel does not fit on an SM");
+      return B200DP_EINVAL;
+    }
+    // two blocks per SM: leaves room for a communication kernel to stay co-resident on a side stream
+    max_blocks = sms * (per_sm < 2 ? per_sm : 2);
+  }
+  const long Q = static_cast<long>(p.B) * (p.pool ? p.H / 2 : p.H) * (p.pool ? p.W / 2 : p.W);
+  long blocks = (Q + rows_per_block - 1) / rows_per_block;
+  if (blocks > max_blocks) blocks = max_blocks;
+  if (blocks < 1) blocks = 1;
+  void* args[] = {&p};
+  B200DP_CUDA_TRY(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(bn_relu_pool_bwd_fused_kernel),
+                                              dim3(static_cast<unsigned>(blocks)), dim3(threads), args, smem,
+                                              static_cast<cudaStream_t>(s)));
   return 0;
 }
 
@@ -709,7 +844,11 @@ extern "C" int b200dp_linear_fwd(const void* x, const float* w, const float* b, 
     set_error("linear_fwd: F=%d must be a multiple of 8", F);
     return B200DP_EINVAL;
   }
-  const int threads = 256;
+  if (O > kLinMaxO) {
+    set_error("linear_fwd: O=%d exceeds the supported %d outputs", O, kLinMaxO);
+    return B200DP_EINVAL;
+  }
+  const int threads = 128;
   const int blocks = (B * 32 + threads - 1) / threads;
   linear_fwd_kernel<<<blocks, threads, 0, static_cast<cudaStream_t>(s)>>>(static_cast<const __nv_bfloat16*>(x), w, b,
                                                                          logits, B, F, O);
@@ -732,8 +871,15 @@ extern "C" int b200dp_linear_bwd(const void* x, const float* w, const float* dlo
     return B200DP_EINVAL;
   }
   const int threads = 256;
-  const int nW = (F + 63) / 64;
+  const int nslices = (B + 31) / 32 < 16 ? (B + 31) / 32 : 16;   // <= kLinTileB rows per slice
+  if ((B + nslices - 1) / nslices > kLinTileB) {
+    set_error("linear_bwd: batch %d too large for the staged dlogits tile", B);
+    return B200DP_EINVAL;
+  }
+  const int nW = ((F + 63) / 64) * nslices;
   const int nX = static_cast<int>((static_cast<long>(B) * F + threads - 1) / threads);
+  B200DP_CUDA_TRY(cudaMemsetAsync(dw, 0, sizeof(float) * O * F, static_cast<cudaStream_t>(s)));
+  B200DP_CUDA_TRY(cudaMemsetAsync(db, 0, sizeof(float) * O, static_cast<cudaStream_t>(s)));
   linear_bwd_kernel<<<nW + nX, threads, 0, static_cast<cudaStream_t>(s)>>>(
       static_cast<const __nv_bfloat16*>(x), w, dlogits, dw, db, static_cast<__nv_bfloat16*>(dx), B, F, O, nW);
   B200DP_CUDA_TRY(cudaGetLastError());
@@ -855,6 +1001,213 @@ extern "C" int b200dp_prep_conv_weights_batched(int n, const float* const* maste
     tiles += (cout[i] / 64) * taps[i] * (cin[i] / 64);
   }
   prep_conv_weights_batched_kernel<<<tiles, 256, 0, static_cast<cudaStream_t>(s)>>>(t);
+  B200DP_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+// ---------------------------------------------------------------------------
+// First layer (3 input channels) as a direct convolution on the CUDA cores.
+// K = 27 is too thin for the tensor cores (the GEMM route pads it to 64 and needs a patch-gather
+// pass); here every thread owns one output pixel x 16 channels, the 4-row input window and the
+// [27][64] weights sit in shared memory, operands are rounded to bf16 exactly like the tcgen05
+// path, BatchNorm statistics are accumulated in registers across a persistent block's tiles.
+// (ref: master/part1/model.py:13,18-23 -- the in_channels=3 Conv2d)
+// ---------------------------------------------------------------------------
+namespace b200dp {
+
+B200DP_DEVINL float round_bf16(float v) { return __bfloat162float(__float2bfloat16(v)); }
+
+__global__ void __launch_bounds__(256) conv3x3_c3_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
+                                                             const float* __restrict__ bias,
+                                                             __nv_bfloat16* __restrict__ y, float* __restrict__ stats,
+                                                             int B, int H, int W) {
+  extern __shared__ float smem_f[];
+  const int Wp = W + 2;
+  float* s_w = smem_f;                 // [27][64]
+  float* s_win = s_w + 27 * 64;        // [4][3][Wp]
+  float* s_red = s_win + 12 * Wp;      // [8 warps][2][64]
+  for (int i = threadIdx.x; i < 27 * 64; i += blockDim.x) {
+    const int k = i >> 6, co = i & 63;
+    s_w[i] = round_bf16(w[co * 27 + k]);
+  }
+  const int cg = threadIdx.x & 3;       // channels cg*16 .. +15
+  const int pl = threadIdx.x >> 2;      // pixel within the tile (2 rows x W, W <= 32)
+  const int pr = pl / W, pw = pl - pr * W;
+  float bsum[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) bsum[j] = bias[cg * 16 + j];
+  float s1[16], s2[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) s1[j] = s2[j] = 0.f;
+  const int tiles = B * (H / 2);
+  for (int t = blockIdx.x; t < tiles; t += gridDim.x) {
+    const int n = t / (H / 2), h0 = (t - n * (H / 2)) * 2;
+    __syncthreads();
+    for (int i = threadIdx.x; i < 12 * Wp; i += blockDim.x) {
+      const int r = i / (3 * Wp), c = (i / Wp) % 3, ww = i % Wp - 1;
+      const int hh = h0 + r - 1;
+      s_win[i] = (hh >= 0 && hh < H && ww >= 0 && ww < W)
+                     ? round_bf16(__ldg(x + ((static_cast<long>(n) * 3 + c) * H + hh) * W + ww)) : 0.f;
+    }
+    __syncthreads();
+    if (pl < 2 * W) {
+      float acc[16];
+#pragma unroll
+      for (int j = 0; j < 16; ++j) acc[j] = 0.f;
+#pragma unroll
+      for (int k = 0; k < 27; ++k) {
+        const int tap = k / 3, c = k - tap * 3;
+        const float xv = s_win[(pr + tap / 3) * 3 * Wp + c * Wp + pw + tap % 3];
+        const float4* wr = reinterpret_cast<const float4*>(s_w + k * 64 + cg * 16);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const float4 wv = wr[q];
+          acc[4 * q] = fmaf(xv, wv.x, acc[4 * q]);
+          acc[4 * q + 1] = fmaf(xv, wv.y, acc[4 * q + 1]);
+          acc[4 * q + 2] = fmaf(xv, wv.z, acc[4 * q + 2]);
+          acc[4 * q + 3] = fmaf(xv, wv.w, acc[4 * q + 3]);
+        }
+      }
+      uint32_t packed[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        packed[j] = pack_bf16x2(acc[2 * j] + bsum[2 * j], acc[2 * j + 1] + bsum[2 * j + 1]);
+        const float2 r = unpack_bf16x2(packed[j]);
+        s1[2 * j] += r.x; s1[2 * j + 1] += r.y;
+        s2[2 * j] = fmaf(r.x, r.x, s2[2 * j]); s2[2 * j + 1] = fmaf(r.y, r.y, s2[2 * j + 1]);
+      }
+      uint4* dst = reinterpret_cast<uint4*>(y + ((static_cast<long>(n) * H + h0 + pr) * W + pw) * 64 + cg * 16);
+      dst[0] = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+      dst[1] = make_uint4(packed[4], packed[5], packed[6], packed[7]);
+    }
+  }
+  if (stats != nullptr) {
+    // lanes that share cg (lane % 4) hold the same channels: fold the 8 pixels of the warp
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+#pragma unroll
+      for (int o = 4; o < 32; o <<= 1) {
+        s1[j] += __shfl_xor_sync(0xffffffffu, s1[j], o);
+        s2[j] += __shfl_xor_sync(0xffffffffu, s2[j], o);
+      }
+    }
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    __syncthreads();
+    if (lane < 4) {
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        s_red[(warp * 2) * 64 + lane * 16 + j] = s1[j];
+        s_red[(warp * 2 + 1) * 64 + lane * 16 + j] = s2[j];
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x < 128) {
+      const int which = threadIdx.x >> 6, ch = threadIdx.x & 63;
+      float tot = 0.f;
+      for (int wv = 0; wv < 8; ++wv) tot += s_red[(wv * 2 + which) * 64 + ch];
+      atomicAdd(stats + which * 64 + ch, tot);
+    }
+  }
+}
+
+// dW[co][k] += sum_p dY[p][co] * patch[p][k], k = (r*3+s)*3 + c.  256 threads = 4 pixel groups x
+// 16 groups of 4 output channels x 4 groups of 7 patch columns; 28 accumulators per thread.
+__global__ void __launch_bounds__(256) conv3x3_c3_wgrad_kernel(const __nv_bfloat16* __restrict__ dy,
+                                                               const float* __restrict__ x, float* __restrict__ dw,
+                                                               int B, int H, int W) {
+  extern __shared__ float smem_f[];
+  const int Wp = W + 2;
+  float* s_win = smem_f;                                        // [4][3][Wp]
+  __nv_bfloat16* s_dy = reinterpret_cast<__nv_bfloat16*>(s_win + 12 * Wp + ((12 * Wp) & 1));  // [2W][64]
+  const int kg = threadIdx.x & 3, cog = (threadIdx.x >> 2) & 15, pg = threadIdx.x >> 6;
+  float acc[4][7];
+#pragma unroll
+  for (int a = 0; a < 4; ++a)
+#pragma unroll
+    for (int i = 0; i < 7; ++i) acc[a][i] = 0.f;
+  int koff[7];  // window offset of patch column k relative to the pixel's (row, col)
+#pragma unroll
+  for (int i = 0; i < 7; ++i) {
+    const int k = kg * 7 + i;
+    const int tap = k / 3, c = k - tap * 3;
+    koff[i] = k < 27 ? (tap / 3) * 3 * Wp + c * Wp + tap % 3 : -1;
+  }
+  const int tiles = B * (H / 2);
+  const int npix = 2 * W;
+  for (int t = blockIdx.x; t < tiles; t += gridDim.x) {
+    const int n = t / (H / 2), h0 = (t - n * (H / 2)) * 2;
+    __syncthreads();
+    for (int i = threadIdx.x; i < 12 * Wp; i += blockDim.x) {
+      const int r = i / (3 * Wp), c = (i / Wp) % 3, ww = i % Wp - 1;
+      const int hh = h0 + r - 1;
+      s_win[i] = (hh >= 0 && hh < H && ww >= 0 && ww < W)
+                     ? round_bf16(__ldg(x + ((static_cast<long>(n) * 3 + c) * H + hh) * W + ww)) : 0.f;
+    }
+    const uint4* src = reinterpret_cast<const uint4*>(dy + (static_cast<long>(n) * H + h0) * W * 64);
+    for (int i = threadIdx.x; i < npix * 8; i += blockDim.x) reinterpret_cast<uint4*>(s_dy)[i] = src[i];
+    __syncthreads();
+    for (int p = pg; p < npix; p += 4) {
+      const int pr = p / W, pw = p - pr * W;
+      const uint2 dq = *reinterpret_cast<const uint2*>(s_dy + p * 64 + cog * 4);
+      const float2 d01 = unpack_bf16x2(dq.x), d23 = unpack_bf16x2(dq.y);
+      const float* base = s_win + pr * 3 * Wp + pw;
+#pragma unroll
+      for (int i = 0; i < 7; ++i) {
+        const float xv = koff[i] >= 0 ? base[koff[i]] : 0.f;
+        acc[0][i] = fmaf(d01.x, xv, acc[0][i]);
+        acc[1][i] = fmaf(d01.y, xv, acc[1][i]);
+        acc[2][i] = fmaf(d23.x, xv, acc[2][i]);
+        acc[3][i] = fmaf(d23.y, xv, acc[3][i]);
+      }
+    }
+  }
+  // combine the 4 pixel groups through shared memory, then one atomic per (co, k) per block
+  __syncthreads();
+  float* s_acc = smem_f;  // reuse: [4 pg][64 co][28]
+#pragma unroll
+  for (int a = 0; a < 4; ++a)
+#pragma unroll
+    for (int i = 0; i < 7; ++i) s_acc[(pg * 64 + cog * 4 + a) * 28 + kg * 7 + i] = acc[a][i];
+  __syncthreads();
+  for (int i = threadIdx.x; i < 64 * 27; i += blockDim.x) {
+    const int co = i / 27, k = i - co * 27;
+    const float v = s_acc[(0 * 64 + co) * 28 + k] + s_acc[(1 * 64 + co) * 28 + k] + s_acc[(2 * 64 + co) * 28 + k] +
+                    s_acc[(3 * 64 + co) * 28 + k];
+    atomicAdd(dw + i, v);
+  }
+}
+
+}  // namespace b200dp
+
+extern "C" int b200dp_conv3x3_c3_fwd(const float* x_nchw, const float* w, const float* bias, void* y, float* stats,
+                                     int B, int H, int W, b200dp_stream_t s) {
+  if (W > 32 || (H & 1) || W < 1) {
+    set_error("conv3x3_c3_fwd: needs even H and W <= 32 (got H=%d W=%d)", H, W);
+    return B200DP_EINVAL;
+  }
+  const size_t smem = (27 * 64 + 12 * (W + 2) + 8 * 2 * 64) * sizeof(float);
+  const int tiles = B * (H / 2);
+  const int blocks = tiles < 148 * 4 ? tiles : 148 * 4;
+  conv3x3_c3_fwd_kernel<<<blocks, 256, smem, static_cast<cudaStream_t>(s)>>>(
+      x_nchw, w, bias, static_cast<__nv_bfloat16*>(y), stats, B, H, W);
+  B200DP_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200dp_conv3x3_c3_wgrad(const void* dy, const float* x_nchw, float* dw, int B, int H, int W,
+                                       b200dp_stream_t s) {
+  if (W > 32 || (H & 1) || W < 1) {
+    set_error("conv3x3_c3_wgrad: needs even H and W <= 32 (got H=%d W=%d)", H, W);
+    return B200DP_EINVAL;
+  }
+  size_t win_floats = 12 * (W + 2) + ((12 * (W + 2)) & 1);
+  size_t smem = win_floats * sizeof(float) + 2 * W * 64 * sizeof(__nv_bfloat16);
+  const size_t red = 4 * 64 * 28 * sizeof(float);
+  if (smem < red) smem = red;
+  const int tiles = B * (H / 2);
+  const int blocks = tiles < 148 * 2 ? tiles : 148 * 2;
+  conv3x3_c3_wgrad_kernel<<<blocks, 256, smem, static_cast<cudaStream_t>(s)>>>(
+      static_cast<const __nv_bfloat16*>(dy), x_nchw, dw, B, H, W);
   B200DP_CUDA_TRY(cudaGetLastError());
   return 0;
 }

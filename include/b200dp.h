@@ -75,6 +75,16 @@ int b200dp_conv_wgrad(const void* dy, const void* x, float* dw, int B, int H, in
  * K=64 GEMM for b200dp_conv_igemm(taps=1).  (ref: master/part1/model.py:13,18) */
 int b200dp_im2col3x3_c3(const float* x_nchw, void* a0, int B, int H, int W, b200dp_stream_t stream);
 
+/* First conv (3 input channels) as a direct convolution on the CUDA cores -- K = 27 is too thin
+ * for tcgen05.  y[B,H,W,64] (bf16) = conv3x3(x fp32 NCHW, w fp32 [64][27], k = (r*3+s)*3+c) + bias,
+ * operands rounded to bf16 like the tensor-core path; optional fused BatchNorm statistics
+ * (stats[2][64], zero on entry).  H even, W <= 32.  (ref: master/part1/model.py:13,18-23) */
+int b200dp_conv3x3_c3_fwd(const float* x_nchw, const float* w, const float* bias, void* y, float* stats, int B,
+                          int H, int W, b200dp_stream_t stream);
+/* dw[64][27] (fp32) += sum_p dy[p][64] * patch(x)[p][27]; dw must be zero (or hold the value to add to). */
+int b200dp_conv3x3_c3_wgrad(const void* dy, const float* x_nchw, float* dw, int B, int H, int W,
+                            b200dp_stream_t stream);
+
 /* stats[0..C) += sum_p y[p][c], stats[C..2C) += sum_p y[p][c]^2 (stats zero on entry). */
 int b200dp_bn_stats(const void* y, float* stats, long long P, int C, b200dp_stream_t stream);
 
@@ -96,6 +106,11 @@ int b200dp_bn_relu_pool_bwd_apply(const void* y, const void* dout, const float* 
                                   const float* gamma, const float* beta, const float* sums, void* dy,
                                   float* dgamma, float* dbeta, int B, int H, int W, int C, int pool,
                                   b200dp_stream_t stream);
+
+/* Both passes in one cooperative launch (grid-wide barrier in between); same contract as the pair. */
+int b200dp_bn_relu_pool_bwd_fused(const void* y, const void* dout, const float* mean, const float* invstd,
+                                  const float* gamma, const float* beta, float* sums, void* dy, float* dgamma,
+                                  float* dbeta, int B, int H, int W, int C, int pool, b200dp_stream_t stream);
 
 /* BatchNorm + ReLU (+ pool) backward that allocates nothing and needs no scratch from the caller.
  * This entry point has no counterpart in the reference.  It is for hosts that cannot call

@@ -244,3 +244,31 @@ def test_sgd_momentum_matches_torch(n):
         opt.step()
     torch.cuda.synchronize()
     torch.testing.assert_close(p, pr.detach(), rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("B,H,W", [(8, 32, 32), (3, 16, 16), (256, 32, 32)])
+def test_first_layer_direct_conv(B, H, W):
+    """3-channel conv on the CUDA cores: forward (+ fused statistics) and weight gradient."""
+    native = _native()
+    g = torch.Generator(device=DEV).manual_seed(8)
+    x = torch.randn(B, 3, H, W, device=DEV, generator=g)
+    w = (torch.randn(64, 3, 3, 3, device=DEV, generator=g) / 5).contiguous()   # KRSC: [co][r][s][c]
+    bias = torch.randn(64, device=DEV, generator=g)
+    y = torch.empty(B, H, W, 64, device=DEV, dtype=torch.bfloat16)
+    stats = torch.zeros(2, 64, device=DEV)
+    native.conv3x3_c3_fwd(x, w, bias, y, stats)
+    torch.cuda.synchronize()
+    xb, wb = x.bfloat16().float(), w.bfloat16().float().permute(0, 3, 1, 2)
+    ref = F.conv2d(xb, wb, bias, padding=1).permute(0, 2, 3, 1)
+    assert _rel_err(y, ref) < 4e-3
+    y32 = y.float().view(-1, 64)
+    torch.testing.assert_close(stats[0], y32.sum(0), rtol=2e-3, atol=5e-2)
+    torch.testing.assert_close(stats[1], (y32 * y32).sum(0), rtol=2e-3, atol=5e-2)
+    dy = (torch.randn(B, H, W, 64, device=DEV, generator=g) / 30).bfloat16()
+    dw = torch.zeros(64, 27, device=DEV)
+    native.conv3x3_c3_wgrad(dy, x, dw)
+    torch.cuda.synchronize()
+    wr = torch.zeros(64, 3, 3, 3, device=DEV, requires_grad=True)
+    F.conv2d(xb, wr, None, padding=1).backward(dy.float().permute(0, 3, 1, 2))
+    ref_dw = wr.grad.permute(0, 2, 3, 1).reshape(64, 27)
+    assert _rel_err(dw, ref_dw) < 2e-3

@@ -108,6 +108,8 @@ def parse_args():
     p.add_argument("--global-batch", type=int, default=256, help="used with --scaling strong")
     p.add_argument("--bucket-plan", default="layer")
     p.add_argument("--no-e2e", action="store_true")
+    p.add_argument("--comm-blocks", type=int, default=None)
+    p.add_argument("--sync-blocks", type=int, default=None)
     p.add_argument("--port", type=int, default=None)
     return p.parse_args()
 
@@ -136,6 +138,10 @@ def run_native(args) -> dict:
     kw = dict(mode=mode, master_ip=os.environ.get("MASTER_ADDR", "127.0.0.1"), num_nodes=world, rank=rank,
               device="cuda", eval=False, bucket_plan=args.bucket_plan,
               port=args.port or env_int("MASTER_PORT", 29500) + 37)
+    if args.comm_blocks:
+        kw["comm_blocks"] = args.comm_blocks
+    if args.sync_blocks:
+        kw["sync_blocks"] = args.sync_blocks
     if args.scaling == "weak":
         kw["per_rank_batch"] = args.per_gpu_batch
     else:

@@ -47,6 +47,8 @@ class TrainConfig:
     sync_impl: str = "auto"     # auto | torch | native
     bucket_plan: str = "layer"  # layer (8 buckets) | ddp (torch's 3 buckets) | single
     fuse_optimizer: bool = True  # SGD in the collective epilogue where the mode allows it
+    comm_blocks: int = 16       # CTAs of a side-stream bucket kernel (part3); the GEMMs keep the other SMs
+    sync_blocks: int = 64       # CTAs of a collective issued after backward (part2a / part2b)
     cuda_graph: bool = True
     iters: Optional[int] = None  # stop an epoch after this many iterations
     train_size: int = 50000     # CIFAR-10 sizes; synthetic data uses the same counts by default

@@ -115,7 +115,21 @@ def self_first_is_64(module: nn.Module) -> bool:
     return module.block_specs()[0].cout == 64
 
 
-_TUNE_CACHE: Dict[tuple, int] = {}   # (kind, B, hw, cin, cout) -> best block_n / split_k, per process
+_TUNE_CACHE: Dict[tuple, object] = {}   # (kind, B, hw, cin, cout, taps) -> best tile config, per process
+
+
+def _igemm_candidates(m_tiles: int, n_total: int, total_kb: int):
+    """(block_n, split_k) pairs worth timing: every N tile, plus K splits while the grid is small."""
+    out = []
+    for bn in (32, 64, 128, 256):
+        if n_total % bn:
+            continue
+        tiles = m_tiles * (n_total // bn)
+        out.append((bn, 1))
+        for sk in (2, 3, 4, 6, 9):
+            if tiles < 148 and tiles * sk <= 640 and total_kb // sk >= 4 and bn >= 64:
+                out.append((bn, sk))
+    return out
 
 
 def _time_captured(fn, reps: int = 8, replays: int = 3) -> float:
@@ -228,6 +242,10 @@ class NativeVGG:
         bf = torch.bfloat16
         L = self.layout
         self.blocks: List[_Block] = []
+        # fp32 partial-tile workspace of the split-K convs (kept zero by their finalize kernel)
+        need = [B * s.hw * s.hw * max(s.cout, s.cin if i else 0) for i, s in enumerate(self.specs)
+                if (B * s.hw * s.hw + 127) // 128 < 148]      # only grids below one wave are ever split
+        self.splitk_ws = torch.zeros(max(need + [8]), device=dev)
         zero_floats = sum(4 * s.cout for s in self.specs)
         self.zero_region = torch.zeros(zero_floats, device=dev)  # conv stats + bn-bwd sums, cleared per step
         zoff = 0
@@ -236,6 +254,7 @@ class NativeVGG:
             b.spec = s
             b.first = (i == 0)
             b.fwd_block_n = b.dgrad_block_n = b.wgrad_split_k = 0   # 0 = library heuristic; see autotune()
+            b.fwd_split_k = b.dgrad_split_k = 1
             b.kin = 64 if b.first else s.cin           # GEMM K per tap (layer 0: 27 -> 64 padded, 1 tap)
             b.taps = 1 if b.first else 9
             hw = s.hw
@@ -309,12 +328,13 @@ class NativeVGG:
                 s = b.spec
                 x_in, y, dy = b.x_in[:B], b.y[:B], b.dy[:B]
                 key = (B, s.hw, b.kin, s.cout, b.taps)
+                m_tiles = (B * s.hw * s.hw + 127) // 128
                 if ("fwd",) + key not in _TUNE_CACHE:
-                    cands = [n for n in (32, 64, 128, 256) if s.cout % n == 0]
-                    t = {n: _time_captured(lambda n=n: K.conv_igemm(x_in, b.wf, b.bias, y, stats=b.stats, taps=b.taps,
-                                                                    block_n=n)) for n in cands}
+                    t = {c: _time_captured(lambda c=c: K.conv_igemm(x_in, b.wf, b.bias, y, stats=b.stats, taps=b.taps,
+                                                                    block_n=c[0], split_k=c[1], workspace=self.splitk_ws))
+                         for c in _igemm_candidates(m_tiles, s.cout, b.taps * b.kin // 64)}
                     _TUNE_CACHE[("fwd",) + key] = min(t, key=t.get)
-                b.fwd_block_n = _TUNE_CACHE[("fwd",) + key]
+                b.fwd_block_n, b.fwd_split_k = _TUNE_CACHE[("fwd",) + key]
                 if ("wgrad",) + key not in _TUNE_CACHE:
                     t = {k: _time_captured(lambda k=k: K.conv_wgrad(dy, x_in, b.g_w, taps=b.taps, split_k=k,
                                                                     cin_valid=(27 if b.first else None)))
@@ -324,10 +344,11 @@ class NativeVGG:
                 if i > 0:
                     dprev = self.blocks[i - 1].dout[:B]
                     if ("dgrad",) + key not in _TUNE_CACHE:
-                        cands = [n for n in (32, 64, 128, 256) if s.cin % n == 0]
-                        t = {n: _time_captured(lambda n=n: K.conv_igemm(dy, b.wd, None, dprev, block_n=n)) for n in cands}
+                        t = {c: _time_captured(lambda c=c: K.conv_igemm(dy, b.wd, None, dprev, block_n=c[0],
+                                                                        split_k=c[1], workspace=self.splitk_ws))
+                             for c in _igemm_candidates(m_tiles, s.cin, 9 * s.cout // 64)}
                         _TUNE_CACHE[("dgrad",) + key] = min(t, key=t.get)
-                    b.dgrad_block_n = _TUNE_CACHE[("dgrad",) + key]
+                    b.dgrad_block_n, b.dgrad_split_k = _TUNE_CACHE[("dgrad",) + key]
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
         self.flat_grads.zero_()
@@ -362,7 +383,7 @@ class NativeVGG:
                 if b.first:
                     K.im2col3x3_c3(x.contiguous(), x_in)
                 K.conv_igemm(x_in, b.wf, b.bias, y, stats=b.stats if fused else None, taps=b.taps,
-                             block_n=b.fwd_block_n)
+                             block_n=b.fwd_block_n, split_k=b.fwd_split_k, workspace=self.splitk_ws)
             if training and not fused:
                 K.bn_stats(y, b.stats)
             K.bn_relu_pool_fwd(y, b.stats, b.gamma, b.beta, b.running_mean, b.running_var, b.nbt, b.mean, b.invstd,
@@ -404,7 +425,8 @@ class NativeVGG:
                 for k in self._bucket_of_block.get(i, ()):
                     self.on_bucket_ready(k)
             if i > 0:
-                K.conv_igemm(b.dy[:B], b.wd, None, self.blocks[i - 1].dout[:B], block_n=b.dgrad_block_n)
+                K.conv_igemm(b.dy[:B], b.wd, None, self.blocks[i - 1].dout[:B], block_n=b.dgrad_block_n,
+                             split_k=b.dgrad_split_k, workspace=self.splitk_ws)
 
     # ------------------------------------------------------------------ torch.autograd bridge
     def autograd_forward(self, x: torch.Tensor, training: bool) -> torch.Tensor:

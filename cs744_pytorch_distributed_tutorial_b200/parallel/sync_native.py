@@ -167,11 +167,11 @@ def make_native_sync(mode: str, native, comm: Optional[Communicator], cfg) -> Na
     if mode == "part1" or (world == 1 and mode != "part3"):
         return LocalSGD(native, comm, **kw)
     if mode == "part2a":
-        return ParamServerSync(native, comm, **kw)
+        return ParamServerSync(native, comm, blocks=cfg.sync_blocks, **kw)
     if mode == "part2a_extra":
-        return ParamServerSync(native, comm, push=True, **kw)
+        return ParamServerSync(native, comm, push=True, blocks=cfg.sync_blocks, **kw)
     if mode == "part2b":
-        return AllReduceSync(native, comm, **kw)
+        return AllReduceSync(native, comm, blocks=cfg.sync_blocks, **kw)
     if mode == "part3":
-        return BucketedOverlapSync(native, comm, bucket_plan=cfg.bucket_plan, **kw)
+        return BucketedOverlapSync(native, comm, bucket_plan=cfg.bucket_plan, blocks=cfg.comm_blocks, **kw)
     raise ValueError(mode)

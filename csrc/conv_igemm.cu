@@ -43,6 +43,10 @@ struct IgemmParams {
   const float* bias;
   __nv_bfloat16* out;
   float* stats;  // optional [2][Cout]: sum, sum of squares
+  // split-K: gridDim.z CTAs share one output tile, each reduces kb_per_split K blocks and adds its
+  // fp32 partial tile into `partial` ([M][Cout], zero on entry); a finalize kernel produces `out`.
+  float* partial;
+  int kb_per_split;
 };
 
 // Sum v[j] over the 32 lanes of the warp for every j; lane l returns the total of column l.
@@ -59,6 +63,11 @@ B200DP_DEVINL float warp_transpose_sum(float (&v)[32], int lane) {
     }
   }
   return v[0];
+}
+
+B200DP_DEVINL void red_add_v4(float* addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)
+               : "memory");
 }
 
 template <int BLOCK_N, int STAGES>
@@ -81,7 +90,10 @@ __global__ void __launch_bounds__(kNumThreads)
   const int lane = threadIdx.x & 31;
   const int m_tile = blockIdx.x;
   const int n_tile = blockIdx.y;
-  const int num_kb = p.taps * p.cin_blocks;
+  const int total_kb = p.taps * p.cin_blocks;
+  const int kb_begin = blockIdx.z * p.kb_per_split;
+  const int kb_end = min(kb_begin + p.kb_per_split, total_kb);
+  const int num_kb = kb_end - kb_begin;  // >= 1 by construction of the grid
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -115,7 +127,7 @@ __global__ void __launch_bounds__(kNumThreads)
       }
       int stage = 0;
       uint32_t phase = 0;
-      for (int kb = 0; kb < num_kb; ++kb) {
+      for (int kb = kb_begin; kb < kb_end; ++kb) {
         mbar_wait(&empty_bar[stage], phase ^ 1);
         mbar_arrive_expect_tx(&full_bar[stage], kStageBytes);
         const int tap = kb / p.cin_blocks;
@@ -172,6 +184,16 @@ __global__ void __launch_bounds__(kNumThreads)
       uint32_t v[32];
       tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + c, v);
       tmem_ld_wait();
+      if (p.partial != nullptr) {
+        if (valid) {
+          float* dst = p.partial + m * p.n_total + n_tile * BLOCK_N + c;
+#pragma unroll
+          for (int j = 0; j < 32; j += 4)
+            red_add_v4(dst + j, __uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]),
+                       __uint_as_float(v[j + 3]));
+        }
+        continue;
+      }
       float f[32];
 #pragma unroll
       for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
@@ -217,6 +239,69 @@ __global__ void __launch_bounds__(kNumThreads)
   }
 }
 
+// Split-K epilogue: partial fp32 [M][N] -> (+bias) -> bf16 out, fused BatchNorm statistics of the
+// rounded values, and the workspace is cleared again for its next user.
+__global__ void __launch_bounds__(256) splitk_finalize_kernel(float* __restrict__ partial,
+                                                              const float* __restrict__ bias,
+                                                              __nv_bfloat16* __restrict__ out,
+                                                              float* __restrict__ stats, long M, int N) {
+  extern __shared__ float red[];  // [rows_per_block][N] x 2 (only with stats)
+  const int chunks = N / 8;
+  const int rows_per_block = blockDim.x / chunks;
+  const int chunk = threadIdx.x % chunks, rl = threadIdx.x / chunks, c0 = chunk * 8;
+  float b[8], s1[8], s2[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    b[j] = bias != nullptr ? bias[c0 + j] : 0.f;
+    s1[j] = s2[j] = 0.f;
+  }
+  if (rl < rows_per_block) {
+    for (long r = static_cast<long>(blockIdx.x) * rows_per_block + rl; r < M;
+         r += static_cast<long>(gridDim.x) * rows_per_block) {
+      float4* src = reinterpret_cast<float4*>(partial + r * N + c0);
+      const float4 lo = src[0], hi = src[1];
+      src[0] = make_float4(0.f, 0.f, 0.f, 0.f);
+      src[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+      uint4 o;
+      o.x = pack_bf16x2(lo.x + b[0], lo.y + b[1]);
+      o.y = pack_bf16x2(lo.z + b[2], lo.w + b[3]);
+      o.z = pack_bf16x2(hi.x + b[4], hi.y + b[5]);
+      o.w = pack_bf16x2(hi.z + b[6], hi.w + b[7]);
+      *reinterpret_cast<uint4*>(out + r * N + c0) = o;
+      if (stats != nullptr) {
+        const float2 r0 = unpack_bf16x2(o.x), r1 = unpack_bf16x2(o.y), r2 = unpack_bf16x2(o.z), r3 = unpack_bf16x2(o.w);
+        const float vals[8] = {r0.x, r0.y, r1.x, r1.y, r2.x, r2.y, r3.x, r3.y};
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          s1[j] += vals[j];
+          s2[j] = fmaf(vals[j], vals[j], s2[j]);
+        }
+      }
+    }
+  }
+  if (stats != nullptr) {
+    float* r1 = red;
+    float* r2 = red + rows_per_block * N;
+    if (rl < rows_per_block) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        r1[rl * N + c0 + j] = s1[j];
+        r2[rl * N + c0 + j] = s2[j];
+      }
+    }
+    __syncthreads();
+    for (int c = threadIdx.x; c < N; c += blockDim.x) {
+      float a = 0.f, t = 0.f;
+      for (int r = 0; r < rows_per_block; ++r) {
+        a += r1[r * N + c];
+        t += r2[r * N + c];
+      }
+      atomicAdd(stats + c, a);
+      atomicAdd(stats + N + c, t);
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------
 // weight gradient
 // ---------------------------------------------------------------------------
@@ -231,11 +316,6 @@ struct WgradParams {
   int use_red;
   float* out;
 };
-
-B200DP_DEVINL void red_add_v4(float* addr, float a, float b, float c, float d) {
-  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)
-               : "memory");
-}
 
 template <int BLOCK_N, int STAGES>
 __global__ void __launch_bounds__(kNumThreads)
@@ -464,7 +544,7 @@ static int tile_geometry(int H, int W, int pixels_per_tile, int* TH, int* TN) {
 
 template <int BLOCK_N, int STAGES>
 static int launch_igemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const IgemmParams& p, int m_tiles,
-                        cudaStream_t stream) {
+                        int splits, cudaStream_t stream) {
   constexpr int smem = STAGES * (kAStageBytes + BLOCK_N * kBlockK * 2) + 1024 + 256;
   static bool configured = false;
   auto kern = conv_igemm_kernel<BLOCK_N, STAGES>;
@@ -472,7 +552,7 @@ static int launch_igemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Ig
     B200DP_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     configured = true;
   }
-  dim3 grid(m_tiles, p.n_total / BLOCK_N);
+  dim3 grid(m_tiles, p.n_total / BLOCK_N, splits);
   kern<<<grid, kNumThreads, smem, stream>>>(tmA, tmB, p);
   B200DP_CUDA_TRY(cudaGetLastError());
   return 0;
@@ -498,10 +578,9 @@ static int launch_wgrad(const CUtensorMap& tmDY, const CUtensorMap& tmX, const W
 
 using namespace b200dp;
 
-extern "C" int b200dp_conv_igemm(const void* act, const void* wgt, const float* bias, void* out, float* stats,
-                                 int B, int H, int W, int Cin, int Cout, int taps, int block_n,
-                                 b200dp_stream_t stream_) {
-  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+static int conv_igemm_impl(const void* act, const void* wgt, const float* bias, void* out, float* stats,
+                           float* workspace, int B, int H, int W, int Cin, int Cout, int taps, int block_n, int split_k,
+                           cudaStream_t stream) {
   if ((taps != 9 && taps != 1) || Cin % 64 != 0 || Cout % 32 != 0 || B <= 0) {
     set_error("conv_igemm: unsupported shape B=%d H=%d W=%d Cin=%d Cout=%d taps=%d", B, H, W, Cin, Cout, taps);
     return B200DP_EINVAL;
@@ -537,6 +616,19 @@ extern "C" int b200dp_conv_igemm(const void* act, const void* wgt, const float* 
     set_error("conv_igemm: Cout=%d is not a multiple of block_n=%d", Cout, block_n);
     return B200DP_EINVAL;
   }
+  const int total_kb = taps * p.cin_blocks;
+  if (split_k < 1) split_k = 1;
+  if (split_k > total_kb) split_k = total_kb;
+  p.kb_per_split = (total_kb + split_k - 1) / split_k;
+  split_k = (total_kb + p.kb_per_split - 1) / p.kb_per_split;
+  if (split_k > 1) {
+    if (workspace == nullptr || Cout % 8 != 0 || Cout > 2048) {
+      set_error("conv_igemm: split_k=%d needs an fp32 workspace of B*H*W*Cout floats (zeroed) and Cout <= 2048",
+                split_k);
+      return B200DP_EINVAL;
+    }
+    p.partial = workspace;
+  }
   CUtensorMap tmA, tmB;
   {
     const uint64_t dims[4] = {(uint64_t)Cin, (uint64_t)W, (uint64_t)H, (uint64_t)B};
@@ -550,13 +642,39 @@ extern "C" int b200dp_conv_igemm(const void* act, const void* wgt, const float* 
     int rc = make_tmap(&tmB, wgt, 2, dims, box);
     if (rc) return rc;
   }
+  int rc;
   switch (block_n) {
-    case 256: return launch_igemm<256, 4>(tmA, tmB, p, m_tiles, stream);
-    case 128: return launch_igemm<128, 3>(tmA, tmB, p, m_tiles, stream);
-    case 64: return launch_igemm<64, 4>(tmA, tmB, p, m_tiles, stream);
-    case 32: return launch_igemm<32, 4>(tmA, tmB, p, m_tiles, stream);
+    case 256: rc = launch_igemm<256, 4>(tmA, tmB, p, m_tiles, split_k, stream); break;
+    case 128: rc = launch_igemm<128, 3>(tmA, tmB, p, m_tiles, split_k, stream); break;
+    case 64: rc = launch_igemm<64, 4>(tmA, tmB, p, m_tiles, split_k, stream); break;
+    case 32: rc = launch_igemm<32, 4>(tmA, tmB, p, m_tiles, split_k, stream); break;
     default: set_error("conv_igemm: block_n=%d not in {32,64,128,256}", block_n); return B200DP_EINVAL;
   }
+  if (rc || split_k == 1) return rc;
+  const int threads = 256;
+  const int rows_per_block = threads / (Cout / 8);
+  const size_t smem = stats != nullptr ? 2 * rows_per_block * Cout * sizeof(float) : 0;
+  long blocks = (static_cast<long>(p.m_total) + rows_per_block * 2 - 1) / (rows_per_block * 2);
+  if (blocks > 148 * 4) blocks = 148 * 4;
+  if (blocks < 1) blocks = 1;
+  splitk_finalize_kernel<<<static_cast<unsigned>(blocks), threads, smem, stream>>>(
+      workspace, bias, static_cast<__nv_bfloat16*>(out), stats, p.m_total, Cout);
+  B200DP_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200dp_conv_igemm(const void* act, const void* wgt, const float* bias, void* out, float* stats,
+                                 int B, int H, int W, int Cin, int Cout, int taps, int block_n,
+                                 b200dp_stream_t stream_) {
+  return conv_igemm_impl(act, wgt, bias, out, stats, nullptr, B, H, W, Cin, Cout, taps, block_n, 1,
+                         static_cast<cudaStream_t>(stream_));
+}
+
+extern "C" int b200dp_conv_igemm_splitk(const void* act, const void* wgt, const float* bias, void* out, float* stats,
+                                        float* workspace, int B, int H, int W, int Cin, int Cout, int taps,
+                                        int block_n, int split_k, b200dp_stream_t stream_) {
+  return conv_igemm_impl(act, wgt, bias, out, stats, workspace, B, H, W, Cin, Cout, taps, block_n, split_k,
+                         static_cast<cudaStream_t>(stream_));
 }
 
 extern "C" int b200dp_conv_wgrad(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin,

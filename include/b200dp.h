@@ -56,6 +56,14 @@ const char* b200dp_version(void);
 int b200dp_conv_igemm(const void* act, const void* wgt, const float* bias, void* out, float* stats, int B,
                       int H, int W, int Cin, int Cout, int taps, int block_n, b200dp_stream_t stream);
 
+/* The same with the K loop (taps x Cin/64 blocks) split over split_k CTAs per output tile -- for the
+ * small-spatial layers whose pixel count yields too few tiles to fill 148 SMs.  Partial tiles are
+ * combined with red.global.add in `workspace` (B*H*W*Cout floats, ZERO on entry; left zero on exit),
+ * then a finalize kernel adds the bias, rounds to bf16 and takes the BatchNorm statistics. */
+int b200dp_conv_igemm_splitk(const void* act, const void* wgt, const float* bias, void* out, float* stats,
+                             float* workspace, int B, int H, int W, int Cin, int Cout, int taps, int block_n,
+                             int split_k, b200dp_stream_t stream);
+
 /* dW[Cout][taps][cin_valid] (fp32) += sum over pixels dY[p][Cout] * X[p + tap][Cin].
  * dy: bf16 [B,H,W,Cout]; x: bf16 [B,H,W,Cin].  Both operands are consumed
  * MN-major straight from their NHWC layout.  split_k = 0 chooses a split that

@@ -272,3 +272,29 @@ def test_first_layer_direct_conv(B, H, W):
     F.conv2d(xb, wr, None, padding=1).backward(dy.float().permute(0, 3, 1, 2))
     ref_dw = wr.grad.permute(0, 2, 3, 1).reshape(64, 27)
     assert _rel_err(dw, ref_dw) < 2e-3
+
+
+@pytest.mark.parametrize("shape,block_n,split_k", [((64, 2, 2, 512, 512), 128, 4), ((64, 2, 2, 512, 512), 64, 9),
+                                                   ((32, 4, 4, 256, 512), 256, 3), ((32, 8, 8, 128, 256), 128, 2)])
+def test_conv_fwd_split_k(shape, block_n, split_k):
+    """K loop split across CTAs: partial tiles meet in an fp32 workspace, the finalize kernel adds the
+    bias, rounds, takes the statistics and leaves the workspace zero for the next call."""
+    native = _native()
+    B, H, W, Cin, Cout = shape
+    g = torch.Generator(device=DEV).manual_seed(9)
+    x = torch.randn(B, H, W, Cin, device=DEV, generator=g).bfloat16()
+    w = (torch.randn(Cout, 3, 3, Cin, device=DEV, generator=g) / (3 * Cin ** 0.5)).bfloat16()
+    bias = torch.randn(Cout, device=DEV, generator=g)
+    ws = torch.zeros(B * H * W * Cout, device=DEV)
+    ref = _conv_ref(x, w, bias)
+    for _ in range(2):   # twice: the second call relies on the workspace having been re-zeroed
+        out = torch.empty(B, H, W, Cout, device=DEV, dtype=torch.bfloat16)
+        stats = torch.zeros(2, Cout, device=DEV)
+        native.conv_igemm(x, w.view(Cout, 9 * Cin), bias, out, stats=stats, block_n=block_n, split_k=split_k,
+                          workspace=ws)
+        torch.cuda.synchronize()
+        assert _rel_err(out, ref) < 6e-3
+        o32 = out.float().view(-1, Cout)
+        torch.testing.assert_close(stats[0], o32.sum(0), rtol=2e-3, atol=2e-2)
+        torch.testing.assert_close(stats[1], (o32 * o32).sum(0), rtol=2e-3, atol=2e-2)
+        assert ws.abs().max().item() == 0

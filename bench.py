@@ -111,6 +111,8 @@ def parse_args():
     p.add_argument("--comm-blocks", type=int, default=None)
     p.add_argument("--sync-blocks", type=int, default=None)
     p.add_argument("--port", type=int, default=None)
+    p.add_argument("--single-rank-collectives", action="store_true",
+                   help="at --gpus 1 still run the bucket reducer and comm kernels (default: fused local SGD)")
     return p.parse_args()
 
 
@@ -138,6 +140,7 @@ def run_native(args) -> dict:
     kw = dict(mode=mode, master_ip=os.environ.get("MASTER_ADDR", "127.0.0.1"), num_nodes=world, rank=rank,
               device="cuda", eval=False, bucket_plan=args.bucket_plan,
               port=args.port or env_int("MASTER_PORT", 29500) + 37)
+    kw["single_rank_collectives"] = args.single_rank_collectives
     if args.comm_blocks:
         kw["comm_blocks"] = args.comm_blocks
     if args.sync_blocks:
@@ -213,6 +216,26 @@ def run_native(args) -> dict:
     }
     if e2e is not None:
         out["e2e"] = e2e
+    if world > 1:
+        # exposed communication = step time - the same step with the sync block replaced by the local
+        # fused SGD, measured on every rank with an identical no-communication trainer
+        local = Trainer(TrainConfig(mode="part1", num_nodes=1, rank=0, device="cuda", eval=False, per_rank_batch=B))
+        lb = local.backend
+        for i in range(3):
+            lb.run_staged(lb.stage_inputs(*host_batches[i % 8]))
+        be.barrier()
+        torch.cuda.synchronize()
+        l0, l1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0.record()
+        for _ in range(args.steps):
+            lb.graph.replay()
+        l1.record()
+        torch.cuda.synchronize()
+        ms_local = be.max_over_ranks(l0.elapsed_time(l1)) / args.steps
+        local.close()
+        out["compute_only_ms_per_step"] = ms_local
+        out["exposed_comm_ms_per_step"] = ms_dev - ms_local
+        out["exposed_comm_fraction"] = (ms_dev - ms_local) / ms_dev
     tr.close()
     return out if rank == 0 else {}
 

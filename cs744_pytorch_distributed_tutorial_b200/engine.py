@@ -152,7 +152,7 @@ class NativeBackend:
         self.store = None
         self.comm = None
         W = cfg.world_size
-        need_comm = W > 1 or cfg.mode == "part3"
+        need_comm = W > 1 or (cfg.mode == "part3" and cfg.single_rank_collectives)
         if W > 1:
             self.store = Store(cfg.master_ip, cfg.port, cfg.rank, W, timeout_s=cfg.timeout_s)
         heap = None

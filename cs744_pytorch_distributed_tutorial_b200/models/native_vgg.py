@@ -132,7 +132,7 @@ def _igemm_candidates(m_tiles: int, n_total: int, total_kb: int):
     return out
 
 
-def _time_captured(fn, reps: int = 8, replays: int = 3) -> float:
+def _time_captured(fn, reps: int = 10, replays: int = 5) -> float:
     """Microseconds per call of ``fn``, measured by replaying a CUDA graph of ``reps`` launches
     (removes the host launch cost, which would otherwise hide the differences between ~10 us kernels)."""
     fn()
@@ -255,6 +255,7 @@ class NativeVGG:
             b.first = (i == 0)
             b.fwd_block_n = b.dgrad_block_n = b.wgrad_split_k = 0   # 0 = library heuristic; see autotune()
             b.fwd_split_k = b.dgrad_split_k = 1
+            b.wgrad_block_n = 0
             b.kin = 64 if b.first else s.cin           # GEMM K per tap (layer 0: 27 -> 64 padded, 1 tap)
             b.taps = 1 if b.first else 9
             hw = s.hw
@@ -336,11 +337,13 @@ class NativeVGG:
                     _TUNE_CACHE[("fwd",) + key] = min(t, key=t.get)
                 b.fwd_block_n, b.fwd_split_k = _TUNE_CACHE[("fwd",) + key]
                 if ("wgrad",) + key not in _TUNE_CACHE:
-                    t = {k: _time_captured(lambda k=k: K.conv_wgrad(dy, x_in, b.g_w, taps=b.taps, split_k=k,
-                                                                    cin_valid=(27 if b.first else None)))
-                         for k in (0, 1, 2, 4, 8, 16)}
+                    tiles_n = [0] + ([256] if b.kin % 256 == 0 else [])
+                    t = {(k, n): _time_captured(lambda k=k, n=n: K.conv_wgrad(dy, x_in, b.g_w, taps=b.taps, split_k=k,
+                                                                              cin_valid=(27 if b.first else None),
+                                                                              block_n=n))
+                         for k in (0, 1, 2, 4, 8, 16) for n in tiles_n}
                     _TUNE_CACHE[("wgrad",) + key] = min(t, key=t.get)
-                b.wgrad_split_k = _TUNE_CACHE[("wgrad",) + key]
+                b.wgrad_split_k, b.wgrad_block_n = _TUNE_CACHE[("wgrad",) + key]
                 if i > 0:
                     dprev = self.blocks[i - 1].dout[:B]
                     if ("dgrad",) + key not in _TUNE_CACHE:
@@ -420,7 +423,7 @@ class NativeVGG:
                 K.conv3x3_c3_wgrad(b.dy[:B], self._x_first, b.g_w)
             else:
                 K.conv_wgrad(b.dy[:B], b.x_in[:B], b.g_w, taps=b.taps, cin_valid=(27 if b.first else None),
-                             split_k=b.wgrad_split_k)
+                             split_k=b.wgrad_split_k, block_n=b.wgrad_block_n)
             if self.on_bucket_ready is not None:
                 for k in self._bucket_of_block.get(i, ()):
                     self.on_bucket_ready(k)

@@ -55,7 +55,7 @@ def conv_igemm(act: torch.Tensor, wgt: torch.Tensor, bias: Optional[torch.Tensor
 
 
 def conv_wgrad(dy: torch.Tensor, x: torch.Tensor, dw: torch.Tensor, taps: int = 9, cin_valid: Optional[int] = None,
-               split_k: int = 0, accumulate: bool = False) -> torch.Tensor:
+               split_k: int = 0, accumulate: bool = False, block_n: int = 0) -> torch.Tensor:
     """dw[Cout, taps, cin_valid] (fp32) (+)= sum_p dy[p, Cout] * x[p+tap, Cin].  With split-K or
     ``accumulate`` the partial tiles are added onto ``dw`` (zero it first for a plain gradient)."""
     _chk(dy, torch.bfloat16, "dy")
@@ -65,8 +65,8 @@ def conv_wgrad(dy: torch.Tensor, x: torch.Tensor, dw: torch.Tensor, taps: int = 
     Cin = x.shape[3]
     cv = Cin if cin_valid is None else cin_valid
     assert dw.numel() == Cout * taps * cv
-    call("b200dp_conv_wgrad", ptr(dy), ptr(x), ptr(dw), B, H, W, Cin, Cout, taps, cv, split_k, int(accumulate),
-         stream_ptr())
+    call("b200dp_conv_wgrad_tiled", ptr(dy), ptr(x), ptr(dw), B, H, W, Cin, Cout, taps, cv, split_k, int(accumulate),
+         block_n, stream_ptr())
     return dw
 
 

@@ -164,7 +164,10 @@ class BucketedOverlapSync(NativeSync):
 def make_native_sync(mode: str, native, comm: Optional[Communicator], cfg) -> NativeSync:
     kw = dict(lr=cfg.lr, momentum=cfg.momentum, weight_decay=cfg.weight_decay, fuse_optimizer=cfg.fuse_optimizer)
     world = comm.world if comm is not None else 1
-    if mode == "part1" or (world == 1 and mode != "part3"):
+    # one rank: a mean over one gradient is the gradient -- no kernel needs to touch peer memory, so every
+    # mode degenerates to the fused local SGD.  `single_rank_collectives` keeps the reducer / collective
+    # path alive at world size 1 (tests, profiling of the comm kernels on one GPU).
+    if mode == "part1" or (world == 1 and not (mode == "part3" and cfg.single_rank_collectives)):
         return LocalSGD(native, comm, **kw)
     if mode == "part2a":
         return ParamServerSync(native, comm, blocks=cfg.sync_blocks, **kw)

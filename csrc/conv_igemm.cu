@@ -677,10 +677,8 @@ extern "C" int b200dp_conv_igemm_splitk(const void* act, const void* wgt, const 
                          static_cast<cudaStream_t>(stream_));
 }
 
-extern "C" int b200dp_conv_wgrad(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin,
-                                 int Cout, int taps, int cin_valid, int split_k, int accumulate,
-                                 b200dp_stream_t stream_) {
-  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+static int conv_wgrad_impl(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin, int Cout, int taps,
+                           int cin_valid, int split_k, int accumulate, int block_n_req, cudaStream_t stream) {
   if ((taps != 9 && taps != 1) || Cin % 64 != 0 || (Cout % 128 != 0 && Cout != 64) || B <= 0 || cin_valid > Cin ||
       cin_valid <= 0) {
     set_error("conv_wgrad: unsupported shape B=%d H=%d W=%d Cin=%d Cout=%d taps=%d", B, H, W, Cin, Cout, taps);
@@ -693,7 +691,9 @@ extern "C" int b200dp_conv_wgrad(const void* dy, const void* x, float* dw, int B
     set_error("conv_wgrad: B=%d H=%d W=%d cannot be tiled into 64-pixel blocks", B, H, W);
     return B200DP_EINVAL;
   }
-  const int block_n = (Cin % 128 == 0) ? 128 : 64;
+  int block_n = (Cin % 128 == 0) ? 128 : 64;
+  if (block_n_req == 256 && Cin % 256 == 0) block_n = 256;
+  if (block_n_req == 64) block_n = 64;
   p.taps = taps;
   p.cin = Cin;
   p.cout = Cout;
@@ -730,6 +730,22 @@ extern "C" int b200dp_conv_wgrad(const void* dy, const void* x, float* dw, int B
     int rc = make_tmap(&tmX, x, 4, dims, box);
     if (rc) return rc;
   }
+  if (block_n == 256) return launch_wgrad<256, 4>(tmDY, tmX, p, tiles, split_k, stream);
   if (block_n == 128) return launch_wgrad<128, 4>(tmDY, tmX, p, tiles, split_k, stream);
   return launch_wgrad<64, 4>(tmDY, tmX, p, tiles, split_k, stream);
+}
+
+extern "C" int b200dp_conv_wgrad(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin,
+                                 int Cout, int taps, int cin_valid, int split_k, int accumulate,
+                                 b200dp_stream_t stream_) {
+  return conv_wgrad_impl(dy, x, dw, B, H, W, Cin, Cout, taps, cin_valid, split_k, accumulate, 0,
+                         static_cast<cudaStream_t>(stream_));
+}
+
+/* As b200dp_conv_wgrad with an explicit input-channel tile (64, 128 or 256; 0 = default). */
+extern "C" int b200dp_conv_wgrad_tiled(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin,
+                                       int Cout, int taps, int cin_valid, int split_k, int accumulate, int block_n,
+                                       b200dp_stream_t stream_) {
+  return conv_wgrad_impl(dy, x, dw, B, H, W, Cin, Cout, taps, cin_valid, split_k, accumulate, block_n,
+                         static_cast<cudaStream_t>(stream_));
 }

@@ -74,6 +74,11 @@ int b200dp_conv_igemm_splitk(const void* act, const void* wgt, const float* bias
 int b200dp_conv_wgrad(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin, int Cout,
                       int taps, int cin_valid, int split_k, int accumulate, b200dp_stream_t stream);
 
+/* As b200dp_conv_wgrad with an explicit input-channel (GEMM N) tile: 64, 128 or 256; 0 = default. */
+int b200dp_conv_wgrad_tiled(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin, int Cout,
+                            int taps, int cin_valid, int split_k, int accumulate, int block_n,
+                            b200dp_stream_t stream);
+
 /* ------------------------------------------------------------------------
  * Bandwidth-bound layer kernels (bf16 NHWC activations, 8 channels per thread)
  * ------------------------------------------------------------------------ */

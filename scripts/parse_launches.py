@@ -4,7 +4,8 @@ path = sys.argv[1] if len(sys.argv) > 1 else "gpurun_out/launches.csv"
 lines = [l for l in open(path) if not l.startswith("==")]
 rows = list(csv.DictReader(lines))
 names = [r["Kernel Name"] for r in rows]
-start = max(i for i, n in enumerate(names) if "im2col" in n)
+firsts = [i for i, n in enumerate(names) if "im2col" in n or "conv3x3_c3_fwd" in n]
+start = max(firsts) if firsts else 0
 agg = collections.OrderedDict()
 total = 0.0
 verbose = "-v" in sys.argv

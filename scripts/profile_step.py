@@ -24,7 +24,8 @@ ap.add_argument("--warmup", type=int, default=3)
 ap.add_argument("--events", action="store_true")
 a = ap.parse_args()
 
-cfg = TrainConfig(mode=a.mode, per_rank_batch=a.batch, device="cuda", eval=False, cuda_graph=False)
+cfg = TrainConfig(mode=a.mode, per_rank_batch=a.batch, device="cuda", eval=False, cuda_graph=False,
+                  single_rank_collectives=True)
 tr = Trainer(cfg)
 be = tr.backend
 x = torch.randn(a.batch, 3, 32, 32).pin_memory()
@@ -66,7 +67,10 @@ if a.events:
         print(f"{per_step:9.1f} us/step  x{len(v) // a.steps:<3d} {k}")
     print(f"{total:9.1f} us/step  total (serialised, event-bracketed)")
 else:
+    # with `ncu --profile-from-start off` only these steps are captured (not the autotuner's runs)
+    torch.cuda.profiler.start()
     for _ in range(a.steps):
         tr.train_step(x, y)
     torch.cuda.synchronize()
+    torch.cuda.profiler.stop()
 tr.close()

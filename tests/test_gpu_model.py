@@ -220,7 +220,8 @@ def test_part3_single_gpu_reducer_matches_part1(plan):
     from cs744_pytorch_distributed_tutorial_b200.engine import Trainer
     out = {}
     for mode in ("part1", "part3"):
-        cfg = TrainConfig(mode=mode, global_batch=32, device="cuda", eval=False, bucket_plan=plan, lr=0.01)
+        cfg = TrainConfig(mode=mode, global_batch=32, device="cuda", eval=False, bucket_plan=plan, lr=0.01,
+                          single_rank_collectives=True)
         tr = Trainer(cfg)
         g = torch.Generator().manual_seed(4)
         for _ in range(2):

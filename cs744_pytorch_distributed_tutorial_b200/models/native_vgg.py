@@ -119,16 +119,19 @@ _TUNE_CACHE: Dict[tuple, object] = {}   # (kind, B, hw, cin, cout, taps) -> best
 
 
 def _igemm_candidates(m_tiles: int, n_total: int, total_kb: int):
-    """(block_n, split_k) pairs worth timing: every N tile, plus K splits while the grid is small."""
+    """(block_n, split_k, cta_pair) triples worth timing: every N tile, K splits while the grid is
+    small, and the tcgen05 cta_group::2 kernel wherever the tile count allows pairing."""
     out = []
     for bn in (32, 64, 128, 256):
         if n_total % bn:
             continue
         tiles = m_tiles * (n_total // bn)
-        out.append((bn, 1))
-        for sk in (2, 3, 4, 6, 9):
-            if tiles < 148 and tiles * sk <= 640 and total_kb // sk >= 4 and bn >= 64:
-                out.append((bn, sk))
+        pairs = (False, True) if (m_tiles % 2 == 0 and bn >= 64) else (False,)
+        for pair in pairs:
+            out.append((bn, 1, pair))
+            for sk in (2, 3, 4, 6, 9):
+                if tiles < 148 and tiles * sk <= 640 and total_kb // sk >= 4 and bn >= 64:
+                    out.append((bn, sk, pair))
     return out
 
 
@@ -256,6 +259,7 @@ class NativeVGG:
             b.fwd_block_n = b.dgrad_block_n = b.wgrad_split_k = 0   # 0 = library heuristic; see autotune()
             b.fwd_split_k = b.dgrad_split_k = 1
             b.wgrad_block_n = 0
+            b.fwd_pair = b.dgrad_pair = False
             b.kin = 64 if b.first else s.cin           # GEMM K per tap (layer 0: 27 -> 64 padded, 1 tap)
             b.taps = 1 if b.first else 9
             hw = s.hw
@@ -332,10 +336,11 @@ class NativeVGG:
                 m_tiles = (B * s.hw * s.hw + 127) // 128
                 if ("fwd",) + key not in _TUNE_CACHE:
                     t = {c: _time_captured(lambda c=c: K.conv_igemm(x_in, b.wf, b.bias, y, stats=b.stats, taps=b.taps,
-                                                                    block_n=c[0], split_k=c[1], workspace=self.splitk_ws))
+                                                                    block_n=c[0], split_k=c[1], cta_pair=c[2],
+                                                                    workspace=self.splitk_ws))
                          for c in _igemm_candidates(m_tiles, s.cout, b.taps * b.kin // 64)}
                     _TUNE_CACHE[("fwd",) + key] = min(t, key=t.get)
-                b.fwd_block_n, b.fwd_split_k = _TUNE_CACHE[("fwd",) + key]
+                b.fwd_block_n, b.fwd_split_k, b.fwd_pair = _TUNE_CACHE[("fwd",) + key]
                 if ("wgrad",) + key not in _TUNE_CACHE:
                     tiles_n = [0] + ([256] if b.kin % 256 == 0 else [])
                     t = {(k, n): _time_captured(lambda k=k, n=n: K.conv_wgrad(dy, x_in, b.g_w, taps=b.taps, split_k=k,
@@ -348,10 +353,11 @@ class NativeVGG:
                     dprev = self.blocks[i - 1].dout[:B]
                     if ("dgrad",) + key not in _TUNE_CACHE:
                         t = {c: _time_captured(lambda c=c: K.conv_igemm(dy, b.wd, None, dprev, block_n=c[0],
-                                                                        split_k=c[1], workspace=self.splitk_ws))
+                                                                        split_k=c[1], cta_pair=c[2],
+                                                                        workspace=self.splitk_ws))
                              for c in _igemm_candidates(m_tiles, s.cin, 9 * s.cout // 64)}
                         _TUNE_CACHE[("dgrad",) + key] = min(t, key=t.get)
-                    b.dgrad_block_n, b.dgrad_split_k = _TUNE_CACHE[("dgrad",) + key]
+                    b.dgrad_block_n, b.dgrad_split_k, b.dgrad_pair = _TUNE_CACHE[("dgrad",) + key]
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
         self.flat_grads.zero_()
@@ -386,7 +392,8 @@ class NativeVGG:
                 if b.first:
                     K.im2col3x3_c3(x.contiguous(), x_in)
                 K.conv_igemm(x_in, b.wf, b.bias, y, stats=b.stats if fused else None, taps=b.taps,
-                             block_n=b.fwd_block_n, split_k=b.fwd_split_k, workspace=self.splitk_ws)
+                             block_n=b.fwd_block_n, split_k=b.fwd_split_k, cta_pair=b.fwd_pair,
+                             workspace=self.splitk_ws)
             if training and not fused:
                 K.bn_stats(y, b.stats)
             K.bn_relu_pool_fwd(y, b.stats, b.gamma, b.beta, b.running_mean, b.running_var, b.nbt, b.mean, b.invstd,
@@ -429,7 +436,7 @@ class NativeVGG:
                     self.on_bucket_ready(k)
             if i > 0:
                 K.conv_igemm(b.dy[:B], b.wd, None, self.blocks[i - 1].dout[:B], block_n=b.dgrad_block_n,
-                             split_k=b.dgrad_split_k, workspace=self.splitk_ws)
+                             split_k=b.dgrad_split_k, cta_pair=b.dgrad_pair, workspace=self.splitk_ws)
 
     # ------------------------------------------------------------------ torch.autograd bridge
     def autograd_forward(self, x: torch.Tensor, training: bool) -> torch.Tensor:

@@ -30,7 +30,7 @@ def _chk(t: torch.Tensor, dtype: torch.dtype, name: str) -> None:
 
 def conv_igemm(act: torch.Tensor, wgt: torch.Tensor, bias: Optional[torch.Tensor], out: torch.Tensor,
                stats: Optional[torch.Tensor] = None, taps: int = 9, block_n: int = 0, split_k: int = 1,
-               workspace: Optional[torch.Tensor] = None) -> torch.Tensor:
+               workspace: Optional[torch.Tensor] = None, cta_pair: bool = False) -> torch.Tensor:
     """out[B,H,W,Cout] = conv3x3(act[B,H,W,Cin], wgt[Cout, taps*Cin]) + bias (tcgen05 implicit GEMM).
 
     ref: master/part1/model.py:18-23.  Also the dgrad kernel when fed dY and the
@@ -43,6 +43,13 @@ def conv_igemm(act: torch.Tensor, wgt: torch.Tensor, bias: Optional[torch.Tensor
     Cout = wgt.shape[0]
     assert wgt.shape[1] == taps * Cin, (wgt.shape, taps, Cin)
     assert out.shape == (B, H, W, Cout)
+    if cta_pair:
+        # tcgen05 cta_group::2: a 256 x block_n tile per pair of SMs, each staging half of the weight tile
+        if split_k > 1:
+            assert workspace is not None and workspace.numel() >= out.numel()
+        call("b200dp_conv_igemm_pair", ptr(act), ptr(wgt), ptr(bias), ptr(out), ptr(stats),
+             ptr(workspace) if split_k > 1 else None, B, H, W, Cin, Cout, taps, block_n, split_k, stream_ptr())
+        return out
     if split_k > 1:
         # K loop split over several CTAs per tile; `workspace` (fp32, >= B*H*W*Cout, zero) holds the partials
         assert workspace is not None and workspace.dtype == torch.float32 and workspace.numel() >= out.numel()

@@ -70,6 +70,73 @@ B200DP_DEVINL void red_add_v4(float* addr, float a, float b, float c, float d) {
                : "memory");
 }
 
+// Epilogue shared by the 1-CTA and 2-CTA kernels: TMEM -> registers -> (+bias, bf16, statistics) -> global,
+// or fp32 red.add into the split-K workspace.  Warp w may only touch TMEM lanes [32*(w%4), 32*(w%4)+32).
+template <int BLOCK_N>
+B200DP_DEVINL void igemm_epilogue(const IgemmParams& p, uint32_t tmem_base, uint64_t* tmem_full_bar, int warp,
+                                  int lane, int m_tile, int n_tile) {
+  // Epilogue: warp w may only touch TMEM lanes [32*(w%4), 32*(w%4)+32).
+  const int q = warp & 3;
+  const int row = q * 32 + lane;
+  const long m = static_cast<long>(m_tile) * kBlockM + row;
+  const bool valid = m < p.m_total;
+  mbar_wait(tmem_full_bar, 0);
+  tc_fence_after();
+  __nv_bfloat16* out_row = p.out + m * p.n_total + n_tile * BLOCK_N;
+#pragma unroll 1
+  for (int c = 0; c < BLOCK_N; c += 32) {
+    uint32_t v[32];
+    tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + c, v);
+    tmem_ld_wait();
+    if (p.partial != nullptr) {
+      if (valid) {
+        float* dst = p.partial + m * p.n_total + n_tile * BLOCK_N + c;
+#pragma unroll
+        for (int j = 0; j < 32; j += 4)
+          red_add_v4(dst + j, __uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]),
+                     __uint_as_float(v[j + 3]));
+      }
+      continue;
+    }
+    float f[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+    if (p.bias != nullptr) {
+      const float* b = p.bias + n_tile * BLOCK_N + c;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) f[j] += __ldg(b + j);
+    }
+    uint32_t packed[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) packed[j] = pack_bf16x2(f[2 * j], f[2 * j + 1]);
+    if (valid) {
+      uint4* dst = reinterpret_cast<uint4*>(out_row + c);
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        dst[j] = make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
+    }
+    if (p.stats != nullptr) {
+      // statistics of the values as stored (bf16-rounded), so that the
+      // normalisation that follows is exactly centred on what it reads.
+      float s1[32], s2[32];
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const float2 r = unpack_bf16x2(packed[j]);
+        s1[2 * j] = valid ? r.x : 0.f;
+        s1[2 * j + 1] = valid ? r.y : 0.f;
+        s2[2 * j] = s1[2 * j] * s1[2 * j];
+        s2[2 * j + 1] = s1[2 * j + 1] * s1[2 * j + 1];
+      }
+      const float t1 = warp_transpose_sum(s1, lane);
+      const float t2 = warp_transpose_sum(s2, lane);
+      const int ch = n_tile * BLOCK_N + c + lane;
+      atomicAdd(p.stats + ch, t1);
+      atomicAdd(p.stats + p.n_total + ch, t2);
+    }
+  }
+  tc_fence_before();
+}
+
 template <int BLOCK_N, int STAGES>
 __global__ void __launch_bounds__(kNumThreads)
     conv_igemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -171,71 +238,137 @@ __global__ void __launch_bounds__(kNumThreads)
       umma_commit(tmem_full_bar);
     }
   } else {
-    // Epilogue: warp w may only touch TMEM lanes [32*(w%4), 32*(w%4)+32).
-    const int q = warp & 3;
-    const int row = q * 32 + lane;
-    const long m = static_cast<long>(m_tile) * kBlockM + row;
-    const bool valid = m < p.m_total;
-    mbar_wait(tmem_full_bar, 0);
-    tc_fence_after();
-    __nv_bfloat16* out_row = p.out + m * p.n_total + n_tile * BLOCK_N;
-#pragma unroll 1
-    for (int c = 0; c < BLOCK_N; c += 32) {
-      uint32_t v[32];
-      tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + c, v);
-      tmem_ld_wait();
-      if (p.partial != nullptr) {
-        if (valid) {
-          float* dst = p.partial + m * p.n_total + n_tile * BLOCK_N + c;
-#pragma unroll
-          for (int j = 0; j < 32; j += 4)
-            red_add_v4(dst + j, __uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]),
-                       __uint_as_float(v[j + 3]));
-        }
-        continue;
-      }
-      float f[32];
-#pragma unroll
-      for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
-      if (p.bias != nullptr) {
-        const float* b = p.bias + n_tile * BLOCK_N + c;
-#pragma unroll
-        for (int j = 0; j < 32; ++j) f[j] += __ldg(b + j);
-      }
-      uint32_t packed[16];
-#pragma unroll
-      for (int j = 0; j < 16; ++j) packed[j] = pack_bf16x2(f[2 * j], f[2 * j + 1]);
-      if (valid) {
-        uint4* dst = reinterpret_cast<uint4*>(out_row + c);
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
-          dst[j] = make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
-      }
-      if (p.stats != nullptr) {
-        // statistics of the values as stored (bf16-rounded), so that the
-        // normalisation that follows is exactly centred on what it reads.
-        float s1[32], s2[32];
-#pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const float2 r = unpack_bf16x2(packed[j]);
-          s1[2 * j] = valid ? r.x : 0.f;
-          s1[2 * j + 1] = valid ? r.y : 0.f;
-          s2[2 * j] = s1[2 * j] * s1[2 * j];
-          s2[2 * j + 1] = s1[2 * j + 1] * s1[2 * j + 1];
-        }
-        const float t1 = warp_transpose_sum(s1, lane);
-        const float t2 = warp_transpose_sum(s2, lane);
-        const int ch = n_tile * BLOCK_N + c + lane;
-        atomicAdd(p.stats + ch, t1);
-        atomicAdd(p.stats + p.n_total + ch, t2);
-      }
-    }
-    tc_fence_before();
+    igemm_epilogue<BLOCK_N>(p, tmem_base, tmem_full_bar, warp, lane, m_tile, n_tile);
   }
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, kTmemCols);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// CTA-pair variant: tcgen05.mma.cta_group::2, one 256(M) x BLOCK_N tile per pair of SMs.
+// Each CTA stages its own 128 pixel rows of A and only HALF of the weight tile (BLOCK_N/2 rows);
+// the tensor core reads the other half from the partner SM.  Per k-block an SM therefore ingests
+// 16 KiB + BLOCK_N*64 B instead of 16 KiB + BLOCK_N*128 B -- these shapes are bound by L2->SM
+// delivery (ncu: xbar2l1tex ~8 TB/s, tensor pipe ~40%), so fewer bytes per FLOP is the lever.
+// Protocol: both CTAs run a TMA producer whose loads complete on the LEADER's full barrier
+// (expect_tx counts both halves); the leader's single MMA thread issues for the pair and commits
+// with a cluster multicast to the empty / tmem-full barriers of both CTAs; each CTA drains its own
+// TMEM half in its epilogue warps.
+// ---------------------------------------------------------------------------
+template <int BLOCK_N, int STAGES>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads)
+    conv_igemm_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                           const IgemmParams p) {
+  constexpr int kBHalfBytes = (BLOCK_N / 2) * kBlockK * 2;
+  constexpr int kStageBytes = kAStageBytes + kBHalfBytes;
+  constexpr uint32_t kTmemCols = BLOCK_N < 32 ? 32 : BLOCK_N;
+  constexpr uint32_t kIdesc = umma_idesc_bf16(2 * kBlockM, BLOCK_N, 0, 0);
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * kStageBytes);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full_bar = empty_bar + STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t cta_rank = cluster_ctarank();
+  const bool leader = cta_rank == 0;
+  const int m_tile = blockIdx.x;  // the pair owns m tiles (2i, 2i+1)
+  const int n_tile = blockIdx.y;
+  const int total_kb = p.taps * p.cin_blocks;
+  const int kb_begin = blockIdx.z * p.kb_per_split;
+  const int kb_end = min(kb_begin + p.kb_per_split, total_kb);
+  const int num_kb = kb_end - kb_begin;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);   // leader: its own arrive.expect_tx; tx bytes of both CTAs
+      mbar_init(&empty_bar[s], 1);  // one multicast commit from the leader's MMA thread
+    }
+    mbar_init(tmem_full_bar, 1);
+    mbar_fence_init();
+  }
+  if (warp == 1) {
+    tmem_alloc_2cta(tmem_slot, kTmemCols);
+    tmem_relinquish_2cta();
+  }
+  tc_fence_before();
+  cluster_sync_all();  // the partner's barriers must be initialised before anything can arrive on them
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      int n0, h0;
+      if (p.TN == 1) {
+        const int tiles_per_img = p.H / p.TH;
+        n0 = m_tile / tiles_per_img;
+        h0 = (m_tile - n0 * tiles_per_img) * p.TH;
+      } else {
+        n0 = m_tile * p.TN;
+        h0 = 0;
+      }
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = kb_begin; kb < kb_end; ++kb) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        if (leader) mbar_arrive_expect_tx(&full_bar[stage], 2 * kStageBytes);
+        const int tap = kb / p.cin_blocks;
+        const int cb = kb - tap * p.cin_blocks;
+        int dr = 0, ds = 0;
+        if (p.taps == 9) {
+          dr = tap / 3 - 1;
+          ds = tap % 3 - 1;
+        }
+        uint8_t* a_dst = smem + stage * kStageBytes;
+        tma_load_4d_2cta(a_dst, &tmA, &full_bar[stage], cb * kBlockK, ds, h0 + dr, n0);
+        tma_load_2d_2cta(a_dst + kAStageBytes, &tmB, &full_bar[stage], kb * kBlockK,
+                         n_tile * BLOCK_N + static_cast<int>(cta_rank) * (BLOCK_N / 2));
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (leader && elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(smem + stage * kStageBytes);
+        const uint32_t b_addr = a_addr + kAStageBytes;
+#pragma unroll
+        for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+          const uint64_t da = umma_smem_desc(a_addr + k * kUmmaK * 2, 16, 1024);
+          const uint64_t db = umma_smem_desc(b_addr + k * kUmmaK * 2, 16, 1024);
+          umma_bf16_2cta(tmem_base, da, db, kIdesc, (kb | k) != 0);
+        }
+        umma_commit_2cta(&empty_bar[stage], 0b11);
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+      umma_commit_2cta(tmem_full_bar, 0b11);
+    }
+  } else {
+    igemm_epilogue<BLOCK_N>(p, tmem_base, tmem_full_bar, warp, lane, m_tile, n_tile);
+  }
+  __syncthreads();
+  tc_fence_before();
+  cluster_sync_all();  // neither CTA may free TMEM or exit while the pair's MMAs / arrives are in flight
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc_2cta(tmem_base, kTmemCols);
   }
 }
 
@@ -559,6 +692,22 @@ static int launch_igemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Ig
 }
 
 template <int BLOCK_N, int STAGES>
+static int launch_igemm_2cta(const CUtensorMap& tmA, const CUtensorMap& tmB, const IgemmParams& p, int m_tiles,
+                             int splits, cudaStream_t stream) {
+  constexpr int smem = STAGES * (kAStageBytes + (BLOCK_N / 2) * kBlockK * 2) + 1024 + 256;
+  static bool configured = false;
+  auto kern = conv_igemm_2cta_kernel<BLOCK_N, STAGES>;
+  if (!configured) {
+    B200DP_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured = true;
+  }
+  dim3 grid(m_tiles, p.n_total / BLOCK_N, splits);  // m_tiles is even; __cluster_dims__(2,1,1) pairs them
+  kern<<<grid, kNumThreads, smem, stream>>>(tmA, tmB, p);
+  B200DP_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+template <int BLOCK_N, int STAGES>
 static int launch_wgrad(const CUtensorMap& tmDY, const CUtensorMap& tmX, const WgradParams& p, int tiles,
                         int splits, cudaStream_t stream) {
   constexpr int smem = STAGES * (2 * 8192 + (BLOCK_N / 64) * 8192) + 1024 + 256;
@@ -580,7 +729,7 @@ using namespace b200dp;
 
 static int conv_igemm_impl(const void* act, const void* wgt, const float* bias, void* out, float* stats,
                            float* workspace, int B, int H, int W, int Cin, int Cout, int taps, int block_n, int split_k,
-                           cudaStream_t stream) {
+                           int cta_pair, cudaStream_t stream) {
   if ((taps != 9 && taps != 1) || Cin % 64 != 0 || Cout % 32 != 0 || B <= 0) {
     set_error("conv_igemm: unsupported shape B=%d H=%d W=%d Cin=%d Cout=%d taps=%d", B, H, W, Cin, Cout, taps);
     return B200DP_EINVAL;
@@ -636,13 +785,26 @@ static int conv_igemm_impl(const void* act, const void* wgt, const float* bias, 
     int rc = make_tmap(&tmA, act, 4, dims, box);
     if (rc) return rc;
   }
+  if (cta_pair && ((m_tiles & 1) || block_n < 64)) {
+    set_error("conv_igemm: the CTA-pair kernel needs an even number of 128-pixel tiles (got %d) and block_n >= 64",
+              m_tiles);
+    return B200DP_EINVAL;
+  }
   {
     const uint64_t dims[2] = {(uint64_t)taps * Cin, (uint64_t)Cout};
-    const uint32_t box[2] = {64, (uint32_t)block_n};
+    const uint32_t box[2] = {64, (uint32_t)(cta_pair ? block_n / 2 : block_n)};
     int rc = make_tmap(&tmB, wgt, 2, dims, box);
     if (rc) return rc;
   }
   int rc;
+  if (cta_pair) {
+    switch (block_n) {
+      case 256: rc = launch_igemm_2cta<256, 6>(tmA, tmB, p, m_tiles, split_k, stream); break;
+      case 128: rc = launch_igemm_2cta<128, 6>(tmA, tmB, p, m_tiles, split_k, stream); break;
+      case 64: rc = launch_igemm_2cta<64, 6>(tmA, tmB, p, m_tiles, split_k, stream); break;
+      default: set_error("conv_igemm: block_n=%d not in {64,128,256} for the CTA-pair kernel", block_n); return B200DP_EINVAL;
+    }
+  } else
   switch (block_n) {
     case 256: rc = launch_igemm<256, 4>(tmA, tmB, p, m_tiles, split_k, stream); break;
     case 128: rc = launch_igemm<128, 3>(tmA, tmB, p, m_tiles, split_k, stream); break;
@@ -666,14 +828,24 @@ static int conv_igemm_impl(const void* act, const void* wgt, const float* bias, 
 extern "C" int b200dp_conv_igemm(const void* act, const void* wgt, const float* bias, void* out, float* stats,
                                  int B, int H, int W, int Cin, int Cout, int taps, int block_n,
                                  b200dp_stream_t stream_) {
-  return conv_igemm_impl(act, wgt, bias, out, stats, nullptr, B, H, W, Cin, Cout, taps, block_n, 1,
+  return conv_igemm_impl(act, wgt, bias, out, stats, nullptr, B, H, W, Cin, Cout, taps, block_n, 1, 0,
                          static_cast<cudaStream_t>(stream_));
 }
 
 extern "C" int b200dp_conv_igemm_splitk(const void* act, const void* wgt, const float* bias, void* out, float* stats,
                                         float* workspace, int B, int H, int W, int Cin, int Cout, int taps,
                                         int block_n, int split_k, b200dp_stream_t stream_) {
-  return conv_igemm_impl(act, wgt, bias, out, stats, workspace, B, H, W, Cin, Cout, taps, block_n, split_k,
+  return conv_igemm_impl(act, wgt, bias, out, stats, workspace, B, H, W, Cin, Cout, taps, block_n, split_k, 0,
+                         static_cast<cudaStream_t>(stream_));
+}
+
+/* CTA-pair (tcgen05 cta_group::2) variant: 256 x block_n tile per pair of SMs, each SM stages half of
+ * the weight tile.  Needs an even number of 128-pixel tiles and block_n in {64,128,256}; split_k and
+ * workspace as for b200dp_conv_igemm_splitk (split_k = 1: workspace may be NULL). */
+extern "C" int b200dp_conv_igemm_pair(const void* act, const void* wgt, const float* bias, void* out, float* stats,
+                                      float* workspace, int B, int H, int W, int Cin, int Cout, int taps,
+                                      int block_n, int split_k, b200dp_stream_t stream_) {
+  return conv_igemm_impl(act, wgt, bias, out, stats, workspace, B, H, W, Cin, Cout, taps, block_n, split_k, 1,
                          static_cast<cudaStream_t>(stream_));
 }
 

@@ -64,6 +64,14 @@ int b200dp_conv_igemm_splitk(const void* act, const void* wgt, const float* bias
                              float* workspace, int B, int H, int W, int Cin, int Cout, int taps, int block_n,
                              int split_k, b200dp_stream_t stream);
 
+/* CTA-pair variant (tcgen05.mma.cta_group::2): one 256-pixel x block_n tile per pair of SMs; each SM
+ * stages its own 128 pixel rows and only half of the weight tile, the pair's single MMA thread issues
+ * for both and commits by cluster multicast.  Needs an even number of 128-pixel tiles and block_n in
+ * {64,128,256}; split_k / workspace as above (split_k = 1: workspace may be NULL). */
+int b200dp_conv_igemm_pair(const void* act, const void* wgt, const float* bias, void* out, float* stats,
+                           float* workspace, int B, int H, int W, int Cin, int Cout, int taps, int block_n,
+                           int split_k, b200dp_stream_t stream);
+
 /* dW[Cout][taps][cin_valid] (fp32) += sum over pixels dY[p][Cout] * X[p + tap][Cin].
  * dy: bf16 [B,H,W,Cout]; x: bf16 [B,H,W,Cin].  Both operands are consumed
  * MN-major straight from their NHWC layout.  split_k = 0 chooses a split that

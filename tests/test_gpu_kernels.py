@@ -298,3 +298,29 @@ def test_conv_fwd_split_k(shape, block_n, split_k):
         torch.testing.assert_close(stats[0], o32.sum(0), rtol=2e-3, atol=2e-2)
         torch.testing.assert_close(stats[1], (o32 * o32).sum(0), rtol=2e-3, atol=2e-2)
         assert ws.abs().max().item() == 0
+
+
+@pytest.mark.parametrize("shape", [(32, 16, 16, 64, 128), (32, 8, 8, 256, 256), (32, 4, 4, 512, 512),
+                                   (64, 2, 2, 512, 512), (2, 32, 32, 64, 64)])
+@pytest.mark.parametrize("block_n,split_k", [(64, 1), (128, 1), (256, 1), (128, 3)])
+def test_conv_fwd_cta_pair(shape, block_n, split_k):
+    """tcgen05.mma.cta_group::2: two CTAs share one 256-row tile, each staging half of the weights."""
+    native = _native()
+    B, H, W, Cin, Cout = shape
+    if Cout % block_n or ((B * H * W) // 128) % 2:
+        pytest.skip("shape not tileable by the CTA-pair kernel")
+    g = torch.Generator(device=DEV).manual_seed(10)
+    x = torch.randn(B, H, W, Cin, device=DEV, generator=g).bfloat16()
+    w = (torch.randn(Cout, 3, 3, Cin, device=DEV, generator=g) / (3 * Cin ** 0.5)).bfloat16()
+    bias = torch.randn(Cout, device=DEV, generator=g)
+    out = torch.empty(B, H, W, Cout, device=DEV, dtype=torch.bfloat16)
+    stats = torch.zeros(2, Cout, device=DEV)
+    ws = torch.zeros(out.numel(), device=DEV) if split_k > 1 else None
+    native.conv_igemm(x, w.view(Cout, 9 * Cin), bias, out, stats=stats, block_n=block_n, split_k=split_k,
+                      workspace=ws, cta_pair=True)
+    torch.cuda.synchronize()
+    ref = _conv_ref(x, w, bias)
+    assert _rel_err(out, ref) < 6e-3
+    o32 = out.float().view(-1, Cout)
+    torch.testing.assert_close(stats[0], o32.sum(0), rtol=2e-3, atol=2e-2)
+    torch.testing.assert_close(stats[1], (o32 * o32).sum(0), rtol=2e-3, atol=2e-2)

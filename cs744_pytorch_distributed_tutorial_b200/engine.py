@@ -189,16 +189,19 @@ class NativeBackend:
         nv = self.native
         self.sync.pre_forward()
         nv.forward(self.x, training=True)
+        self.sync.post_forward()
         nv.loss_fwd_bwd(self.y)
         nv.backward()
         self.sync.sync_and_step()
         nv.refresh_shadows()
+        # within a captured step the auxiliary stream must be joined before the capture ends
+        self.sync.pre_forward()
 
     def _capture(self) -> None:
         # warm up outside capture (module loading, lazy attribute setup), on a side stream as
         # torch requires; the warm-up steps train on zeros, so restore the state afterwards.
         nv = self.native
-        keep = [t.clone() for t in (nv.flat_params, nv.flat_momentum, nv.flat_bn, nv.flat_nbt_padded)]
+        keep = [t.clone() for t in (nv.flat_params, nv.flat_momentum, nv.bn_state)]
         s = torch.cuda.Stream(self.device)
         s.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(s):
@@ -213,7 +216,7 @@ class NativeBackend:
             self._step_body()
         self.launches_per_step = _lib.launch_count - n0
         torch.cuda.synchronize(self.device)
-        for dst, src in zip((nv.flat_params, nv.flat_momentum, nv.flat_bn, nv.flat_nbt_padded), keep):
+        for dst, src in zip((nv.flat_params, nv.flat_momentum, nv.bn_state), keep):
             dst.copy_(src)
         nv.refresh_shadows()
         torch.cuda.synchronize(self.device)
@@ -232,6 +235,7 @@ class NativeBackend:
         return slot
 
     def run_staged(self, slot: int) -> torch.Tensor:
+        self._eval_synced = False
         cur = torch.cuda.current_stream()
         cur.wait_event(self._copy_done[slot])
         self.x.copy_(self._stage_x[slot], non_blocking=True)
@@ -256,10 +260,12 @@ class NativeBackend:
         y = target.to(self.device, non_blocking=True)
         self.sync.pre_forward()
         nv.forward(x, training=True)
+        self.sync.post_forward()
         nv.loss_fwd_bwd(y)
         nv.backward()
         self.sync.sync_and_step()
         nv.refresh_shadows()
+        self.sync.pre_forward()
         self.steps_done += 1
         return nv.loss
 
@@ -282,8 +288,10 @@ class NativeBackend:
         nv = self.native
         x = data.to(self.device, non_blocking=True).float()
         y = target.to(self.device, non_blocking=True)
-        if self.sync.syncs_buffers:
-            self.sync.pre_forward()
+        if self.sync.syncs_buffers and not getattr(self, "_eval_synced", False):
+            # DDP broadcasts buffers on eval forwards too; they cannot change during evaluation, so once
+            self.sync.resync_buffers()
+            self._eval_synced = True
         nv.forward(x, training=False)
         nv.loss_fwd_bwd(y, need_grad=False)
         return nv.loss.clone(), int(nv.correct.item())

@@ -182,8 +182,13 @@ class NativeVGG:
         self.flat_momentum = alloc(n)
         # BatchNorm buffers, flat so that one kernel can broadcast them (part3 semantics)
         self.bn_channels = [s.cout for s in self.specs]
-        self.flat_bn = alloc(2 * sum(self.bn_channels))
-        self.flat_nbt_padded = alloc((len(self.specs) + 1) // 2 * 2, torch.int64)  # 16-byte multiple
+        # running_mean / running_var of every layer followed by the int64 num_batches_tracked counters, in
+        # ONE region so that a single kernel broadcasts all BatchNorm state
+        n_bn = 2 * sum(self.bn_channels)
+        n_nbt = (len(self.specs) + 1) // 2 * 2              # keeps the region a multiple of 16 bytes
+        self.bn_state = alloc(n_bn + 2 * n_nbt)             # fp32 words; the tail is viewed as int64
+        self.flat_bn = self.bn_state[:n_bn]
+        self.flat_nbt_padded = self.bn_state[n_bn:].view(torch.int64)
         self.flat_nbt = self.flat_nbt_padded[: len(self.specs)]
         self.on_bucket_ready: Optional[Callable[[int], None]] = None
         self._bucket_of_block: Dict[int, List[int]] = {}

@@ -27,7 +27,7 @@ from typing import Optional
 import torch
 
 from ..ops import native as K
-from .comm import CH_BUCKET, CH_MAIN, BucketReducer, Communicator
+from .comm import CH_AUX, CH_BUCKET, CH_MAIN, BucketReducer, Communicator
 
 
 class NativeSync:
@@ -50,6 +50,12 @@ class NativeSync:
         """Run once after construction, outside any graph capture."""
 
     def pre_forward(self) -> None:
+        pass
+
+    def post_forward(self) -> None:
+        pass
+
+    def resync_buffers(self) -> None:
         pass
 
     def sync_and_step(self) -> None:
@@ -138,15 +144,36 @@ class BucketedOverlapSync(NativeSync):
         nv = self.native
         if self.world > 1:
             self.comm.broadcast(nv.flat_params, root=0, channel=CH_MAIN)
-            self.comm.broadcast(nv.flat_bn, root=0, channel=CH_MAIN)
+            self.comm.broadcast(nv.bn_state, root=0, channel=CH_MAIN)
             nv.refresh_shadows()
+            self._aux_stream = torch.cuda.Stream(nv.device)
+            self._aux_fork = torch.cuda.Event()
+            self._aux_join = torch.cuda.Event()
+            self._aux_pending = False
 
     def pre_forward(self) -> None:
-        # DDP _sync_buffers: rank 0's BatchNorm statistics overwrite everyone's before each forward
+        """DDP ``_sync_buffers``: every forward starts from rank 0's BatchNorm state.  That state was
+        final when rank 0 finished its *previous* forward, so the broadcast is issued there
+        (``post_forward``) on an auxiliary stream and only joined here -- same values, no exposed wait."""
+        if self.world > 1 and self._aux_pending:
+            torch.cuda.current_stream().wait_event(self._aux_join)
+            self._aux_pending = False
+
+    def post_forward(self) -> None:
         if self.world > 1:
             nv = self.native
-            self.comm.broadcast(nv.flat_bn, root=0, blocks=2, channel=CH_MAIN)
-            self.comm.broadcast(nv.flat_nbt_padded, root=0, blocks=1, channel=CH_MAIN)
+            cur = torch.cuda.current_stream()
+            self._aux_fork.record(cur)
+            self._aux_stream.wait_event(self._aux_fork)
+            self.comm.broadcast(nv.bn_state, root=0, blocks=2, channel=CH_AUX, stream=self._aux_stream)
+            self._aux_join.record(self._aux_stream)
+            self._aux_pending = True
+
+    def resync_buffers(self) -> None:
+        """Synchronous form (evaluation after training, tests)."""
+        if self.world > 1:
+            self.pre_forward()
+            self.comm.broadcast(self.native.bn_state, root=0, blocks=2, channel=CH_MAIN)
 
     def sync_only(self) -> None:
         self.reducer.finalize()

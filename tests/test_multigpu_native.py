@@ -143,7 +143,7 @@ def _mode_worker(rank, world, mode, fuse, port, outdir):
         y = torch.randint(0, 10, (32,), generator=g).pin_memory()
         losses.append(float(tr.train_step(x, y).item()))
     # DDP semantics: buffers are re-synchronised from rank 0 at the start of the next forward
-    tr.backend.sync.pre_forward()
+    tr.backend.sync.resync_buffers()
     torch.cuda.synchronize()
     torch.save({"params": nv.flat_params.cpu(), "init": init, "bn": nv.flat_bn.cpu(), "losses": losses},
                os.path.join(outdir, f"{mode}_{int(fuse)}_{rank}.pt"))

@@ -111,6 +111,7 @@ def parse_args():
     p.add_argument("--comm-blocks", type=int, default=None)
     p.add_argument("--sync-blocks", type=int, default=None)
     p.add_argument("--port", type=int, default=None)
+    p.add_argument("--nvls", action="store_true", help="multicast heap; large all-reduces reduce inside the NVSwitch")
     p.add_argument("--single-rank-collectives", action="store_true",
                    help="at --gpus 1 still run the bucket reducer and comm kernels (default: fused local SGD)")
     return p.parse_args()
@@ -141,6 +142,7 @@ def run_native(args) -> dict:
               device="cuda", eval=False, bucket_plan=args.bucket_plan,
               port=args.port or env_int("MASTER_PORT", 29500) + 37)
     kw["single_rank_collectives"] = args.single_rank_collectives
+    kw["nvls"] = args.nvls
     if args.comm_blocks:
         kw["comm_blocks"] = args.comm_blocks
     if args.sync_blocks:

@@ -49,6 +49,7 @@ class TrainConfig:
     fuse_optimizer: bool = True  # SGD in the collective epilogue where the mode allows it
     comm_blocks: int = 16       # CTAs of a side-stream bucket kernel (part3); the GEMMs keep the other SMs
     sync_blocks: int = 64       # CTAs of a collective issued after backward (part2a / part2b)
+    nvls: bool = False          # VMM heap + NVSwitch multicast; large all-reduces run in the switch (multimem)
     single_rank_collectives: bool = False  # world_size 1: still run the bucket reducer / comm kernels
     cuda_graph: bool = True
     iters: Optional[int] = None  # stop an epoch after this many iterations

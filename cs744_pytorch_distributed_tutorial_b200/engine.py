@@ -161,7 +161,10 @@ class NativeBackend:
             flat = (n_params + 4 * 64 + 1023) // 1024 * 1024 + 4096
             staging = (W - 1) * flat if cfg.mode == "part2a_extra" else 0
             heap_bytes = 4 * (3 * flat + staging) + (8 << 20)
-            self.comm = Communicator(self.store, cfg.rank, W, device.index or 0, heap_bytes, timeout_s=cfg.timeout_s)
+            self.comm = Communicator(self.store, cfg.rank, W, device.index or 0, heap_bytes, timeout_s=cfg.timeout_s,
+                                     multicast=cfg.nvls and W > 1)
+            if cfg.nvls and W > 1:
+                self.comm.prefer_nvls(True)
             heap = self.comm
         self.native = model.enable_native(max_batch=B, heap=heap)
         self.sync = make_native_sync(cfg.mode, self.native, self.comm, cfg)

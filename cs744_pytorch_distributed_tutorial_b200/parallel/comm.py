@@ -27,6 +27,9 @@ _lib.declare("b200dp_store_add", [P, c_char_p, LL, POINTER(c_longlong)])
 _lib.declare("b200dp_store_barrier", [P, c_char_p])
 _lib.declare("b200dp_store_destroy", [P])
 _lib.declare("b200dp_comm_create", [P, I, I, I, LL, POINTER(c_void_p)])
+_lib.declare("b200dp_comm_create_ex", [P, I, I, I, LL, I, POINTER(c_void_p)])
+_lib.declare("b200dp_comm_has_multicast", [P])
+_lib.declare("b200dp_comm_prefer_nvls", [P, I])
 _lib.declare("b200dp_comm_destroy", [P])
 _lib.declare("b200dp_comm_heap", [P, POINTER(c_void_p), POINTER(c_longlong), POINTER(c_longlong)])
 _lib.declare("b200dp_comm_peer_base", [P, I, POINTER(c_void_p)])
@@ -106,13 +109,16 @@ class Communicator:
     """Symmetric heap + collectives for one rank.  ``world == 1`` works without a store."""
 
     def __init__(self, store: Optional[Store], rank: int, world: int, device: int, heap_bytes: int,
-                 timeout_s: float = 20.0):
+                 timeout_s: float = 20.0, multicast: bool = False):
+        """``multicast=True`` allocates the heap through the CUDA virtual-memory API and maps an NVSwitch
+        multicast view of it (NVLS all-reduce, ``algo=3``); the default heap is cudaMalloc + CUDA IPC."""
         self.rank, self.world, self.device = rank, world, device
         self.store = store
         h = c_void_p()
-        call("b200dp_comm_create", store.handle if store is not None else None, rank, world, device, heap_bytes,
-             byref(h))
+        call("b200dp_comm_create_ex", store.handle if store is not None else None, rank, world, device, heap_bytes,
+             1 if multicast else 0, byref(h))
         self._h = h
+        self.has_multicast = bool(_lib.lib().b200dp_comm_has_multicast(h))
         base, usable, data_off = c_void_p(), c_longlong(), c_longlong()
         call("b200dp_comm_heap", self._h, byref(base), byref(usable), byref(data_off))
         self.base_ptr = base.value
@@ -122,6 +128,10 @@ class Communicator:
         self._bytes = torch.as_tensor(self._blob, device=torch.device("cuda", device))
         call("b200dp_comm_set_timeout", self._h, float(timeout_s))
         self._keep: List[torch.Tensor] = []
+
+    def prefer_nvls(self, on: bool = True) -> None:
+        """Large all-reduces (and the bucket reducer's) use the in-switch multimem kernel."""
+        call("b200dp_comm_prefer_nvls", self._h, int(on))
 
     # -- allocation --------------------------------------------------------------------
     def zeros(self, numel: int, dtype: torch.dtype = torch.float32, align: int = 256) -> torch.Tensor:

@@ -25,8 +25,12 @@
 //
 // Every wait is bounded: after `timeout_ns` a block reports which peer / slot / block it was
 // waiting for and traps, so a dead rank surfaces as a CUDA error instead of a hang.
+#include <cuda.h>
+#include <cudaTypedefs.h>
 #include <stdio.h>
 #include <string.h>
+#include <time.h>
+#include <unistd.h>
 
 #include <string>
 #include <vector>
@@ -40,6 +44,9 @@ extern "C" int b200dp_store_get(void* h, const char* key, void* buf, int cap, in
 extern "C" int b200dp_store_barrier(void* h, const char* name);
 
 namespace b200dp {
+int fd_listen(const std::string& name);
+int fd_send(const std::string& name, int fd, int tag, int timeout_ms);
+int fd_recv(int listen_fd, int* tag);
 
 constexpr int kMaxWorld = 8;
 constexpr int kMaxBlocks = 256;
@@ -62,10 +69,19 @@ struct Comm {
   uint32_t* done_blocks = nullptr;  // [kNumChannels] finished-block counters
   unsigned long long timeout_ns = 20ull * 1000 * 1000 * 1000;
   bool ipc_opened[kMaxWorld] = {false};
+  // virtual-memory-management heap (cuMemCreate + POSIX fd exchange) with an NVSwitch multicast
+  // mapping: mc_base + offset addresses the copies of ALL ranks at once (multimem.* instructions)
+  bool vmm = false;
+  CUmemGenericAllocationHandle mem_handle = 0;
+  CUmemGenericAllocationHandle peer_handle[kMaxWorld] = {0};
+  CUmemGenericAllocationHandle mc_handle = 0;
+  char* mc_base = nullptr;
+  bool prefer_nvls = false;  // algo 0 ("choose") picks the NVLS kernel for large ranges
 };
 
 struct CommDev {
   PeerTable peers;
+  char* mc_base;  // multicast address of the heap (NULL without NVLS)
   int rank, world;
   uint32_t* epochs;
   uint32_t* done_blocks;
@@ -261,6 +277,69 @@ __global__ void __launch_bounds__(512) allreduce_oneshot_kernel(const CommDev c,
 }
 
 // ---------------------------------------------------------------------------
+// NVLS all-reduce: the reduction happens INSIDE the NVSwitch.  Each rank owns 1/W of the range;
+// one multimem.ld_reduce returns the sum over all ranks' copies of 16 bytes, the 1/W scale (and the
+// SGD update of the owned slice) runs in registers, and one multimem.st writes the result into every
+// rank's copy.  Per rank that is S/W bytes in and S/W bytes out over NVLink instead of the two-shot
+// kernel's (W-1)/W * S each way.  
+// ---------------------------------------------------------------------------
+B200DP_DEVINL float4 multimem_ld_reduce_add_f4(const float* mc_addr) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(mc_addr)
+               : "memory");
+  return v;
+}
+B200DP_DEVINL void multimem_st_f4(float* mc_addr, const float4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc_addr), "f"(v.x), "f"(v.y),
+               "f"(v.z), "f"(v.w)
+               : "memory");
+}
+
+template <bool FUSE_SGD>
+__global__ void __launch_bounds__(512) allreduce_nvls_kernel(const CommDev c, const RangeArgs a) {
+  const uint32_t epoch = begin_collective(c, a.channel);
+  rank_barrier(c, a.channel, 0, epoch);
+  const int W = c.world;
+  const long n4 = (a.end - a.start) >> 2;
+  const long per = (n4 + W - 1) / W;
+  const long lo = min(per * c.rank, n4), hi = min(lo + per, n4);
+  const float inv_w = 1.f / static_cast<float>(W);
+  constexpr int U = 4;
+  const long tstride = static_cast<long>(gridDim.x) * blockDim.x;
+  for (long i0 = lo + blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i0 < hi; i0 += tstride * U) {
+    float4 g[U];
+    size_t eoff[U];
+    bool live[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long i = i0 + u * tstride;
+      live[u] = i < hi;
+      eoff[u] = static_cast<size_t>(a.start + ((live[u] ? i : lo) << 2)) * sizeof(float);
+      g[u] = multimem_ld_reduce_add_f4(reinterpret_cast<const float*>(c.mc_base + a.grad_off + eoff[u]));
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (!live[u]) continue;
+      g[u].x *= inv_w; g[u].y *= inv_w; g[u].z *= inv_w; g[u].w *= inv_w;
+      if (FUSE_SGD) {
+        char* me = c.peers.base[c.rank];
+        float4 p = *reinterpret_cast<const float4*>(me + a.param_off + eoff[u]);
+        float4 m = *reinterpret_cast<const float4*>(me + a.mom_off + eoff[u]);
+        const float4 np = sgd4(g[u], p, m, a.sgd);
+        *reinterpret_cast<float4*>(me + a.mom_off + eoff[u]) = m;
+        multimem_st_f4(reinterpret_cast<float*>(c.mc_base + a.param_off + eoff[u]), np);
+      } else {
+        multimem_st_f4(reinterpret_cast<float*>(c.mc_base + a.grad_off + eoff[u]), g[u]);
+      }
+    }
+  }
+  rank_barrier(c, a.channel, 1, epoch);
+  end_collective(c, a.channel, epoch);
+}
+
+// ---------------------------------------------------------------------------
 // parameter server (rank `root` reduces, everyone receives the mean)
 // ---------------------------------------------------------------------------
 template <bool PUSH>
@@ -335,9 +414,16 @@ __global__ void barrier_kernel(const CommDev c, int channel) {
   end_collective(c, channel, epoch);
 }
 
+static long long globaltimer_host() {
+  timespec ts;
+  clock_gettime(CLOCK_REALTIME, &ts);
+  return static_cast<long long>(ts.tv_sec) * 1000000000ll + ts.tv_nsec;
+}
+
 static CommDev dev_view(const Comm* c) {
   CommDev d;
   d.peers = c->peers;
+  d.mc_base = c->mc_base;
   d.rank = c->rank;
   d.world = c->world;
   d.epochs = c->epochs;
@@ -373,8 +459,198 @@ using namespace b200dp;
 // ---------------------------------------------------------------------------
 // communicator / symmetric heap
 // ---------------------------------------------------------------------------
-extern "C" int b200dp_comm_create(void* store, int rank, int world, int device, long long heap_bytes,
-                                  void** out_comm) {
+namespace b200dp {
+
+#define B200DP_CU_TRY(expr)                                                                     \
+  do {                                                                                          \
+    CUresult _r = (expr);                                                                       \
+    if (_r != CUDA_SUCCESS) {                                                                   \
+      set_error("%s:%d: %s -> CUresult %d", __FILE__, __LINE__, #expr, static_cast<int>(_r));   \
+      return B200DP_EINVAL;                                                                     \
+    }                                                                                           \
+  } while (0)
+
+template <typename Fn>
+static Fn driver_fn(const char* name) {
+  void* ptr = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  if (cudaGetDriverEntryPoint(name, &ptr, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess)
+    return nullptr;
+  return reinterpret_cast<Fn>(ptr);
+}
+
+struct DriverApi {
+  PFN_cuMemCreate_v10020 memCreate;
+  PFN_cuMemRelease_v10020 memRelease;
+  PFN_cuMemAddressReserve_v10020 addrReserve;
+  PFN_cuMemAddressFree_v10020 addrFree;
+  PFN_cuMemMap_v10020 memMap;
+  PFN_cuMemUnmap_v10020 memUnmap;
+  PFN_cuMemSetAccess_v10020 setAccess;
+  PFN_cuMemExportToShareableHandle_v10020 exportHandle;
+  PFN_cuMemImportFromShareableHandle_v10020 importHandle;
+  PFN_cuMulticastCreate_v12010 mcCreate;
+  PFN_cuMulticastAddDevice_v12010 mcAddDevice;
+  PFN_cuMulticastBindMem_v12010 mcBindMem;
+  bool ok;
+};
+
+static const DriverApi& driver_api() {
+  static DriverApi a = [] {
+    DriverApi d{};
+    d.memCreate = driver_fn<PFN_cuMemCreate_v10020>("cuMemCreate");
+    d.memRelease = driver_fn<PFN_cuMemRelease_v10020>("cuMemRelease");
+    d.addrReserve = driver_fn<PFN_cuMemAddressReserve_v10020>("cuMemAddressReserve");
+    d.addrFree = driver_fn<PFN_cuMemAddressFree_v10020>("cuMemAddressFree");
+    d.memMap = driver_fn<PFN_cuMemMap_v10020>("cuMemMap");
+    d.memUnmap = driver_fn<PFN_cuMemUnmap_v10020>("cuMemUnmap");
+    d.setAccess = driver_fn<PFN_cuMemSetAccess_v10020>("cuMemSetAccess");
+    d.exportHandle = driver_fn<PFN_cuMemExportToShareableHandle_v10020>("cuMemExportToShareableHandle");
+    d.importHandle = driver_fn<PFN_cuMemImportFromShareableHandle_v10020>("cuMemImportFromShareableHandle");
+    d.mcCreate = driver_fn<PFN_cuMulticastCreate_v12010>("cuMulticastCreate");
+    d.mcAddDevice = driver_fn<PFN_cuMulticastAddDevice_v12010>("cuMulticastAddDevice");
+    d.mcBindMem = driver_fn<PFN_cuMulticastBindMem_v12010>("cuMulticastBindMem");
+    d.ok = d.memCreate && d.memRelease && d.addrReserve && d.addrFree && d.memMap && d.memUnmap && d.setAccess &&
+           d.exportHandle && d.importHandle && d.mcCreate && d.mcAddDevice && d.mcBindMem;
+    return d;
+  }();
+  return a;
+}
+
+static int map_handle(const DriverApi& d, CUmemGenericAllocationHandle h, size_t bytes, int device, char** out) {
+  CUdeviceptr va = 0;
+  B200DP_CU_TRY(d.addrReserve(&va, bytes, 2u << 20, 0, 0));
+  B200DP_CU_TRY(d.memMap(va, bytes, 0, h, 0));
+  CUmemAccessDesc acc{};
+  acc.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+  acc.location.id = device;
+  acc.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+  B200DP_CU_TRY(d.setAccess(va, bytes, &acc, 1));
+  *out = reinterpret_cast<char*>(va);
+  return 0;
+}
+
+// Heap through the virtual-memory-management API so that it can be bound to an NVSwitch multicast
+// object: cuMemCreate -> export as POSIX fd -> every peer imports and maps it; rank 0 creates the
+// multicast object, everyone adds its device, binds its allocation and maps the multicast address.
+static int create_vmm_heap(Comm* c) {
+  const DriverApi& d = driver_api();
+  if (!d.ok) {
+    set_error("comm_create: the CUDA driver lacks the VMM / multicast entry points");
+    return B200DP_ENOSYS;
+  }
+  int mc_supported = 0;
+  {
+    auto devGet = driver_fn<PFN_cuDeviceGet_v2000>("cuDeviceGet");
+    auto getAttr = driver_fn<PFN_cuDeviceGetAttribute_v2000>("cuDeviceGetAttribute");
+    CUdevice dv = 0;
+    if (!devGet || !getAttr) return B200DP_ENOSYS;
+    B200DP_CU_TRY(devGet(&dv, c->device));
+    B200DP_CU_TRY(getAttr(&mc_supported, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, dv));
+  }
+  if (!mc_supported) {
+    set_error("comm_create: device %d does not support NVSwitch multicast", c->device);
+    return B200DP_ENOSYS;
+  }
+  CUmemAllocationProp prop{};
+  prop.type = CU_MEM_ALLOCATION_TYPE_PINNED;
+  prop.requestedHandleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+  prop.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+  prop.location.id = c->device;
+  B200DP_CU_TRY(d.memCreate(&c->mem_handle, c->heap_bytes, &prop, 0));
+  int rc = map_handle(d, c->mem_handle, c->heap_bytes, c->device, &c->local_base);
+  if (rc) return rc;
+  B200DP_CUDA_TRY(cudaMemset(c->local_base, 0, c->heap_bytes));
+  c->peers.base[c->rank] = c->local_base;
+  c->vmm = true;
+  if (c->world == 1) return 0;
+
+  // ---- agree on a socket-name token, open the listening sockets, exchange descriptors
+  static int generation = 0;
+  const std::string gen = std::to_string(generation++);
+  long long token = 0;
+  if (c->rank == 0) {
+    token = (static_cast<long long>(getpid()) << 20) ^ static_cast<long long>(globaltimer_host());
+    rc = b200dp_store_set(c->store, ("vmm/token/" + gen).c_str(), &token, sizeof(token));
+    if (rc) return rc;
+  }
+  int len = 0;
+  rc = b200dp_store_get(c->store, ("vmm/token/" + gen).c_str(), &token, sizeof(token), &len);
+  if (rc) return rc;
+  auto sock_name = [&](int r) { return "b200dp-" + std::to_string(token) + "-" + gen + "-" + std::to_string(r); };
+  const int lfd = fd_listen(sock_name(c->rank));
+  if (lfd < 0) {
+    set_error("comm_create: rank %d cannot open its descriptor-passing socket", c->rank);
+    return B200DP_EINVAL;
+  }
+  rc = b200dp_store_barrier(c->store, "vmm_listen");
+  if (rc) return rc;
+  int my_fd = -1;
+  B200DP_CU_TRY(d.exportHandle(&my_fd, c->mem_handle, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0));
+  for (int r = 0; r < c->world; ++r)
+    if (r != c->rank && fd_send(sock_name(r), my_fd, c->rank, 30000) != 0) {
+      set_error("comm_create: rank %d could not pass its heap descriptor to rank %d", c->rank, r);
+      return B200DP_ETIMEDOUT;
+    }
+  int mc_fd = -1;
+  if (c->rank == 0) {
+    CUmulticastObjectProp mp{};
+    mp.numDevices = c->world;
+    mp.size = c->heap_bytes;
+    mp.handleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+    B200DP_CU_TRY(d.mcCreate(&c->mc_handle, &mp));
+    B200DP_CU_TRY(d.exportHandle(&mc_fd, c->mc_handle, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0));
+    for (int r = 1; r < c->world; ++r)
+      if (fd_send(sock_name(r), mc_fd, 100, 30000) != 0) {
+        set_error("comm_create: rank 0 could not pass the multicast descriptor to rank %d", r);
+        return B200DP_ETIMEDOUT;
+      }
+  }
+  const int expect = (c->world - 1) + (c->rank == 0 ? 0 : 1);
+  for (int k = 0; k < expect; ++k) {
+    int tag = -1;
+    const int fd = fd_recv(lfd, &tag);
+    if (fd < 0) {
+      set_error("comm_create: rank %d failed to receive a descriptor", c->rank);
+      return B200DP_EINVAL;
+    }
+    if (tag == 100) {
+      B200DP_CU_TRY(d.importHandle(&c->mc_handle, reinterpret_cast<void*>(static_cast<intptr_t>(fd)),
+                                   CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR));
+    } else if (tag >= 0 && tag < c->world && tag != c->rank) {
+      B200DP_CU_TRY(d.importHandle(&c->peer_handle[tag], reinterpret_cast<void*>(static_cast<intptr_t>(fd)),
+                                   CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR));
+      rc = map_handle(d, c->peer_handle[tag], c->heap_bytes, c->device, &c->peers.base[tag]);
+      if (rc) return rc;
+    }
+    ::close(fd);
+  }
+  ::close(lfd);
+  ::close(my_fd);
+  if (mc_fd >= 0) ::close(mc_fd);
+  // ---- multicast: add devices, then bind memory, then map (each step is collective)
+  CUdevice cudev = 0;
+  {
+    auto devGet = driver_fn<PFN_cuDeviceGet_v2000>("cuDeviceGet");
+    if (!devGet) return B200DP_ENOSYS;
+    B200DP_CU_TRY(devGet(&cudev, c->device));
+  }
+  B200DP_CU_TRY(d.mcAddDevice(c->mc_handle, cudev));
+  rc = b200dp_store_barrier(c->store, "mc_add");
+  if (rc) return rc;
+  B200DP_CU_TRY(d.mcBindMem(c->mc_handle, 0, c->mem_handle, 0, c->heap_bytes, 0));
+  rc = b200dp_store_barrier(c->store, "mc_bind");
+  if (rc) return rc;
+  rc = map_handle(d, c->mc_handle, c->heap_bytes, c->device, &c->mc_base);
+  if (rc) return rc;
+  return b200dp_store_barrier(c->store, "mc_map");
+}
+
+}  // namespace b200dp
+
+// flags bit 0: allocate the heap with the VMM API and map an NVSwitch multicast view of it (NVLS)
+extern "C" int b200dp_comm_create_ex(void* store, int rank, int world, int device, long long heap_bytes, int flags,
+                                     void** out_comm) {
   if (world < 1 || world > kMaxWorld || rank < 0 || rank >= world || heap_bytes <= 0 || !out_comm) {
     set_error("comm_create: bad arguments (rank %d, world %d, heap %lld bytes; world <= %d)", rank, world,
               heap_bytes, kMaxWorld);
@@ -385,17 +661,29 @@ extern "C" int b200dp_comm_create(void* store, int rank, int world, int device, 
     return B200DP_EINVAL;
   }
   B200DP_CUDA_TRY(cudaSetDevice(device));
+  B200DP_CUDA_TRY(cudaFree(nullptr));  // make sure the primary context exists before driver-API calls
   auto* c = new Comm();
   c->rank = rank;
   c->world = world;
   c->device = device;
   c->store = store;
   c->heap_bytes = ((static_cast<size_t>(heap_bytes) + kSignalPadBytes + (2u << 20) - 1) >> 21) << 21;
-  B200DP_CUDA_TRY(cudaMalloc(reinterpret_cast<void**>(&c->local_base), c->heap_bytes));
-  B200DP_CUDA_TRY(cudaMemset(c->local_base, 0, c->heap_bytes));
   B200DP_CUDA_TRY(cudaMalloc(reinterpret_cast<void**>(&c->epochs), 2 * kNumChannels * sizeof(uint32_t)));
   B200DP_CUDA_TRY(cudaMemset(c->epochs, 0, 2 * kNumChannels * sizeof(uint32_t)));
   c->done_blocks = c->epochs + kNumChannels;
+  if (flags & 1) {
+    int rc = create_vmm_heap(c);
+    if (rc) return rc;
+    B200DP_CUDA_TRY(cudaDeviceSynchronize());
+    if (world > 1) {
+      rc = b200dp_store_barrier(store, "comm_create");
+      if (rc) return rc;
+    }
+    *out_comm = c;
+    return 0;
+  }
+  B200DP_CUDA_TRY(cudaMalloc(reinterpret_cast<void**>(&c->local_base), c->heap_bytes));
+  B200DP_CUDA_TRY(cudaMemset(c->local_base, 0, c->heap_bytes));
   B200DP_CUDA_TRY(cudaDeviceSynchronize());
   c->peers.base[rank] = c->local_base;
   if (world > 1) {
@@ -428,6 +716,29 @@ extern "C" int b200dp_comm_create(void* store, int rank, int world, int device, 
   return 0;
 }
 
+extern "C" int b200dp_comm_create(void* store, int rank, int world, int device, long long heap_bytes,
+                                  void** out_comm) {
+  return b200dp_comm_create_ex(store, rank, world, device, heap_bytes, 0, out_comm);
+}
+
+/* Make "algo 0" choose the in-switch (NVLS) kernel for ranges above 256 KiB. */
+extern "C" int b200dp_comm_prefer_nvls(void* comm, int on) {
+  auto* c = static_cast<Comm*>(comm);
+  if (!c) return B200DP_EINVAL;
+  if (on && c->mc_base == nullptr) {
+    set_error("comm_prefer_nvls: this communicator has no multicast mapping");
+    return B200DP_EINVAL;
+  }
+  c->prefer_nvls = on != 0;
+  return 0;
+}
+
+/* 1 if the communicator has an NVSwitch multicast mapping of its heap (NVLS collectives usable). */
+extern "C" int b200dp_comm_has_multicast(void* comm) {
+  auto* c = static_cast<Comm*>(comm);
+  return (c != nullptr && c->mc_base != nullptr) ? 1 : 0;
+}
+
 extern "C" int b200dp_comm_destroy(void* comm) {
   auto* c = static_cast<Comm*>(comm);
   if (!c) return 0;
@@ -436,6 +747,27 @@ extern "C" int b200dp_comm_destroy(void* comm) {
   if (c->world > 1 && c->store) b200dp_store_barrier(c->store, "comm_destroy");
   for (int r = 0; r < c->world; ++r)
     if (c->ipc_opened[r]) cudaIpcCloseMemHandle(c->peers.base[r]);
+  if (c->vmm) {
+    const DriverApi& d = driver_api();
+    if (c->mc_base) {
+      d.memUnmap(reinterpret_cast<CUdeviceptr>(c->mc_base), c->heap_bytes);
+      d.addrFree(reinterpret_cast<CUdeviceptr>(c->mc_base), c->heap_bytes);
+    }
+    for (int r = 0; r < c->world; ++r) {
+      if (r == c->rank || c->peers.base[r] == nullptr) continue;
+      d.memUnmap(reinterpret_cast<CUdeviceptr>(c->peers.base[r]), c->heap_bytes);
+      d.addrFree(reinterpret_cast<CUdeviceptr>(c->peers.base[r]), c->heap_bytes);
+      if (c->peer_handle[r]) d.memRelease(c->peer_handle[r]);
+    }
+    if (c->world > 1 && c->store) b200dp_store_barrier(c->store, "comm_destroy2");
+    if (c->mc_handle) d.memRelease(c->mc_handle);
+    d.memUnmap(reinterpret_cast<CUdeviceptr>(c->local_base), c->heap_bytes);
+    d.addrFree(reinterpret_cast<CUdeviceptr>(c->local_base), c->heap_bytes);
+    d.memRelease(c->mem_handle);
+    cudaFree(c->epochs);
+    delete c;
+    return 0;
+  }
   if (c->world > 1 && c->store) b200dp_store_barrier(c->store, "comm_destroy2");
   cudaFree(c->local_base);
   cudaFree(c->epochs);
@@ -485,14 +817,18 @@ extern "C" int b200dp_allreduce(void* comm, long long grad_off, long long param_
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   const int threads = 512;
   const long n4 = (end - start) >> 2;
-  if (algo == 0) algo = (n4 * 16 <= 256 * 1024) ? 1 : 2;
+  if (algo == 3 && c != nullptr && c->mc_base == nullptr) {
+    set_error("allreduce: algo 3 (NVLS) needs a communicator created with the multicast heap");
+    return B200DP_EINVAL;
+  }
+  if (algo == 0) algo = (n4 * 16 <= 256 * 1024) ? 1 : ((c != nullptr && c->prefer_nvls && c->mc_base) ? 3 : 2);
   const int requested_blocks = blocks;
   if (algo == 1) {
     blocks = static_cast<int>((n4 + threads - 1) / threads);
     if (blocks < 1) blocks = 1;
     if (blocks > kMaxBlocks) algo = 2;  // does not fit in one pass: use the two-shot kernel
   }
-  if (algo == 2) blocks = requested_blocks > 0 ? requested_blocks : 64;
+  if (algo == 2 || algo == 3) blocks = requested_blocks > 0 ? requested_blocks : 64;
   int rc = check_range(c, start, end, blocks, channel, "allreduce");
   if (rc) return rc;
   RangeArgs a{};
@@ -511,7 +847,12 @@ extern "C" int b200dp_allreduce(void* comm, long long grad_off, long long param_
     else if (prescale) KERN<false, true><<<blocks, threads, 0, stream>>>(d, a);       \
     else KERN<false, false><<<blocks, threads, 0, stream>>>(d, a);                    \
   } while (0)
-  if (algo == 1)
+  if (algo == 3) {
+    if (fuse_sgd)
+      allreduce_nvls_kernel<true><<<blocks, threads, 0, stream>>>(d, a);
+    else
+      allreduce_nvls_kernel<false><<<blocks, threads, 0, stream>>>(d, a);
+  } else if (algo == 1)
     B200DP_LAUNCH_AR(allreduce_oneshot_kernel);
   else
     B200DP_LAUNCH_AR(allreduce_twoshot_kernel);

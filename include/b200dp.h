@@ -198,6 +198,13 @@ int b200dp_store_destroy(void* store);
  * and issued in the same order by all ranks.
  * ------------------------------------------------------------------------ */
 int b200dp_comm_create(void* store, int rank, int world, int device, long long heap_bytes, void** out_comm);
+/* flags bit 0: allocate the heap with the CUDA virtual-memory API (cuMemCreate, POSIX-fd exchange over
+ * Unix sockets) and map an NVSwitch MULTICAST view of it, which enables the NVLS all-reduce (algo 3). */
+int b200dp_comm_create_ex(void* store, int rank, int world, int device, long long heap_bytes, int flags,
+                          void** out_comm);
+int b200dp_comm_has_multicast(void* comm);
+/* Let algo 0 of b200dp_allreduce (and the bucket reducer) pick the NVLS kernel for ranges > 256 KiB. */
+int b200dp_comm_prefer_nvls(void* comm, int on);
 int b200dp_comm_destroy(void* comm);
 int b200dp_comm_heap(void* comm, void** base, long long* usable_bytes, long long* data_offset);
 int b200dp_comm_peer_base(void* comm, int rank, void** base);
@@ -207,7 +214,8 @@ int b200dp_comm_barrier(void* comm, int channel, b200dp_stream_t stream);
 /* Gradient all-reduce (mean) over elements [start, end) of the flat fp32 gradient buffer at
  * byte offset grad_off (ref: master/part2b/part2b.py:43-45; DDP buckets master/part3/part3.py:116).
  * algo 0 = choose by size, 1 = one-shot (every rank reduces everything), 2 = two-shot
- * (reduce-scatter + all-gather).  prescale=1 divides before summing (part2b / DDP order).
+ * (reduce-scatter + all-gather), 3 = NVLS: multimem.ld_reduce sums the owned slice inside the
+ * NVSwitch and multimem.st writes the result to every rank (needs a multicast communicator).  prescale=1 divides before summing (part2b / DDP order).
  * fuse_sgd=1 applies SGD(momentum, weight decay) in the epilogue to the parameters at
  * param_off / momentum at mom_off; the two-shot variant then all-gathers updated PARAMETERS. */
 int b200dp_allreduce(void* comm, long long grad_off, long long param_off, long long mom_off, long long start,

@@ -188,3 +188,63 @@ def test_part3_broadcasts_batchnorm_buffers_but_part2b_does_not(mode_results):
     assert all(torch.equal(p3[0]["bn"], r["bn"]) for r in p3[1:])
     p2 = mode_results[("part2b", True)]
     assert not torch.equal(p2[0]["bn"], p2[1]["bn"])      # per-rank statistics
+
+
+def _nvls_worker(rank, world, port, outdir):
+    from cs744_pytorch_distributed_tutorial_b200.parallel.comm import Communicator, Store
+    torch.cuda.set_device(rank)
+    store = Store("127.0.0.1", port, rank, world, timeout_s=60)
+    N = 1_200_000
+    comm = Communicator(store, rank, world, rank, heap_bytes=4 * 3 * N + (1 << 20), timeout_s=30, multicast=True)
+    failures = []
+    if not comm.has_multicast:
+        failures.append(f"rank {rank}: multicast mapping missing")
+    grads, params, mom = comm.zeros(N), comm.zeros(N), comm.zeros(N)
+
+    def check(name, got, want, **kw):
+        try:
+            torch.testing.assert_close(got.cpu(), want, **kw)
+        except AssertionError as e:
+            failures.append(f"rank {rank} {name}: {str(e)[:300]}")
+
+    for case, (start, end) in enumerate([(0, 16), (0, 4100), (1024, N - 2048), (0, N)]):
+        mine = _rank_data(rank, N, 300 + case)
+        grads.copy_(mine)
+        torch.cuda.synchronize()
+        comm.allreduce(grads, start, end, algo=3, blocks=32)      # in-switch reduction (multimem)
+        torch.cuda.synchronize()
+        mean = sum(_rank_data(r, N, 300 + case) for r in range(world)) / world
+        want = mine.clone()
+        want[start:end] = mean[start:end]
+        check(f"nvls allreduce case{case}", grads, want, rtol=1e-5, atol=1e-6)
+    # fused SGD through the multicast store of the updated parameters
+    p0, m0 = _rank_data(99, N, 8), _rank_data(98, N, 8) * 0.1
+    params.copy_(p0); mom.copy_(m0)
+    grads.copy_(_rank_data(rank, N, 350))
+    torch.cuda.synchronize()
+    comm.allreduce(grads, 0, N, params=params, momentum_buf=mom, lr=0.1, momentum=0.9, weight_decay=1e-4, algo=3,
+                   blocks=32)
+    torch.cuda.synchronize()
+    g = sum(_rank_data(r, N, 350) for r in range(world)) / world
+    m1 = 0.9 * m0 + (g + 1e-4 * p0)
+    check("nvls fused sgd params", params, p0 - 0.1 * m1, rtol=1e-5, atol=1e-6)
+    # the peer-mapped (unicast) view of the same VMM heap keeps working: two-shot on it
+    grads.copy_(_rank_data(rank, N, 360))
+    torch.cuda.synchronize()
+    comm.allreduce(grads, 0, N, algo=2, blocks=32)
+    torch.cuda.synchronize()
+    check("two-shot on the VMM heap", grads, sum(_rank_data(r, N, 360) / world for r in range(world)), rtol=1e-5,
+          atol=1e-6)
+    with open(os.path.join(outdir, f"fail_{rank}.txt"), "w") as f:
+        f.write("\n".join(failures))
+    comm.close()
+    store.close()
+
+
+def test_nvls_multimem_allreduce():
+    """NVSwitch in-switch reduction (multimem.ld_reduce / multimem.st) over a multicast-mapped heap."""
+    world = _world()
+    with tempfile.TemporaryDirectory() as d:
+        mp.spawn(_nvls_worker, args=(world, free_port(), d), nprocs=world, join=True)
+        fails = [open(os.path.join(d, f"fail_{r}.txt")).read() for r in range(world)]
+    assert not any(fails), "\n".join(f for f in fails if f)

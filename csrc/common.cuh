@@ -47,6 +47,12 @@ B200DP_DEVINL bool elect_one() {
 }
 
 // ---------------------------------------------------------------------------
+// programmatic dependent launch (no-ops unless the launch carried the attribute)
+// ---------------------------------------------------------------------------
+B200DP_DEVINL void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+B200DP_DEVINL void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+// ---------------------------------------------------------------------------
 // mbarrier
 // ---------------------------------------------------------------------------
 B200DP_DEVINL void mbar_init(uint64_t* bar, uint32_t count) {

@@ -155,6 +155,7 @@ __global__ void __launch_bounds__(kNumThreads)
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  pdl_launch_dependents();  // let the next kernel's CTAs start their prologue as SMs free up
   const int m_tile = blockIdx.x;
   const int n_tile = blockIdx.y;
   const int total_kb = p.taps * p.cin_blocks;
@@ -180,6 +181,7 @@ __global__ void __launch_bounds__(kNumThreads)
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();  // everything above overlapped the previous kernel's tail; global memory only from here on
 
   if (warp == 0) {
     if (elect_one()) {
@@ -276,6 +278,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads)
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  pdl_launch_dependents();  // let the next kernel's CTAs start their prologue as SMs free up
   const uint32_t cta_rank = cluster_ctarank();
   const bool leader = cta_rank == 0;
   const int m_tile = blockIdx.x;  // the pair owns m tiles (2i, 2i+1)
@@ -303,6 +306,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads)
   cluster_sync_all();  // the partner's barriers must be initialised before anything can arrive on them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();  // everything above overlapped the previous kernel's tail; global memory only from here on
 
   if (warp == 0) {
     if (elect_one()) {
@@ -379,6 +383,8 @@ __global__ void __launch_bounds__(256) splitk_finalize_kernel(float* __restrict_
                                                               __nv_bfloat16* __restrict__ out,
                                                               float* __restrict__ stats, long M, int N) {
   extern __shared__ float red[];  // [rows_per_block][N] x 2 (only with stats)
+  pdl_launch_dependents();
+  pdl_wait();
   const int chunks = N / 8;
   const int rows_per_block = blockDim.x / chunks;
   const int chunk = threadIdx.x % chunks, rl = threadIdx.x / chunks, c0 = chunk * 8;
@@ -470,6 +476,7 @@ __global__ void __launch_bounds__(kNumThreads)
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  pdl_launch_dependents();  // let the next kernel's CTAs start their prologue as SMs free up
 
   int t = blockIdx.x;
   const int ci_tile = t % p.ci_tiles;
@@ -498,6 +505,7 @@ __global__ void __launch_bounds__(kNumThreads)
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();  // everything above overlapped the previous kernel's tail; global memory only from here on
 
   if (num_kb > 0) {
     if (warp == 0) {
@@ -686,8 +694,7 @@ static int launch_igemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Ig
     configured = true;
   }
   dim3 grid(m_tiles, p.n_total / BLOCK_N, splits);
-  kern<<<grid, kNumThreads, smem, stream>>>(tmA, tmB, p);
-  B200DP_CUDA_TRY(cudaGetLastError());
+  B200DP_CUDA_TRY(launch_pdl(kern, grid, dim3(kNumThreads), smem, stream, tmA, tmB, p));
   return 0;
 }
 
@@ -702,8 +709,7 @@ static int launch_igemm_2cta(const CUtensorMap& tmA, const CUtensorMap& tmB, con
     configured = true;
   }
   dim3 grid(m_tiles, p.n_total / BLOCK_N, splits);  // m_tiles is even; __cluster_dims__(2,1,1) pairs them
-  kern<<<grid, kNumThreads, smem, stream>>>(tmA, tmB, p);
-  B200DP_CUDA_TRY(cudaGetLastError());
+  B200DP_CUDA_TRY(launch_pdl(kern, grid, dim3(kNumThreads), smem, stream, tmA, tmB, p));
   return 0;
 }
 
@@ -718,8 +724,7 @@ static int launch_wgrad(const CUtensorMap& tmDY, const CUtensorMap& tmX, const W
     configured = true;
   }
   dim3 grid(tiles, splits);
-  kern<<<grid, kNumThreads, smem, stream>>>(tmDY, tmX, p);
-  B200DP_CUDA_TRY(cudaGetLastError());
+  B200DP_CUDA_TRY(launch_pdl(kern, grid, dim3(kNumThreads), smem, stream, tmDY, tmX, p));
   return 0;
 }
 
@@ -819,9 +824,9 @@ static int conv_igemm_impl(const void* act, const void* wgt, const float* bias, 
   long blocks = (static_cast<long>(p.m_total) + rows_per_block * 2 - 1) / (rows_per_block * 2);
   if (blocks > 148 * 4) blocks = 148 * 4;
   if (blocks < 1) blocks = 1;
-  splitk_finalize_kernel<<<static_cast<unsigned>(blocks), threads, smem, stream>>>(
-      workspace, bias, static_cast<__nv_bfloat16*>(out), stats, p.m_total, Cout);
-  B200DP_CUDA_TRY(cudaGetLastError());
+  B200DP_CUDA_TRY(launch_pdl(splitk_finalize_kernel, dim3(static_cast<unsigned>(blocks)), dim3(threads), smem, stream,
+                             workspace, bias, static_cast<__nv_bfloat16*>(out), stats, static_cast<long>(p.m_total),
+                             Cout));
   return 0;
 }
 

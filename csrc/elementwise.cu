@@ -63,6 +63,8 @@ constexpr int kIm2colRows = 4;
 
 __global__ void __launch_bounds__(256) im2col_c3_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ a0,
                                                         int B, int H, int W) {
+  pdl_launch_dependents();
+  pdl_wait();
   extern __shared__ float win[];  // [rows + 2][3 channels][W + 2]
   const int Wp = W + 2;
   const int groups = (H + kIm2colRows - 1) / kIm2colRows;
@@ -98,6 +100,8 @@ __global__ void __launch_bounds__(256) im2col_c3_kernel(const float* __restrict_
 // the conv epilogue can produce the same numbers fused).
 // ---------------------------------------------------------------------------
 __global__ void bn_stats_kernel(const __nv_bfloat16* __restrict__ y, float* __restrict__ stats, long P, int C) {
+  pdl_launch_dependents();
+  pdl_wait();
   extern __shared__ float red[];  // [rows_per_block][C] x 2
   const int chunks = C / 8;
   const int rows_per_block = blockDim.x / chunks;
@@ -169,6 +173,8 @@ B200DP_DEVINL Vec8 unpack8(const uint4& u) {
 // Each thread owns 8 channels (scale/shift stay in registers) and walks output pixels two at a
 // time so that up to eight 16-byte loads are in flight per thread.
 __global__ void __launch_bounds__(256, 3) bn_relu_pool_fwd_kernel(const BnFwdParams p) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int chunks = p.C / 8;
   const int rows_per_block = blockDim.x / chunks;
   const int chunk = threadIdx.x % chunks;
@@ -435,6 +441,8 @@ B200DP_DEVINL void bn_relu_pool_bwd_body(const BnBwdParams& p, float* red) {
 
 template <bool APPLY>
 __global__ void __launch_bounds__(256, 3) bn_relu_pool_bwd_kernel(const BnBwdParams p) {
+  pdl_launch_dependents();
+  pdl_wait();
   extern __shared__ float red[];
   bn_relu_pool_bwd_body<APPLY>(p, red);
 }
@@ -460,6 +468,8 @@ constexpr int kLinTileB = 256;
 __global__ void __launch_bounds__(128) linear_fwd_kernel(const __nv_bfloat16* __restrict__ x,
                                                          const float* __restrict__ w, const float* __restrict__ bias,
                                                          float* __restrict__ logits, int B, int F, int O) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (warp >= B) return;
@@ -491,6 +501,8 @@ __global__ void __launch_bounds__(128) linear_fwd_kernel(const __nv_bfloat16* __
 __global__ void cross_entropy_kernel(const float* __restrict__ logits, const long long* __restrict__ target,
                                      float* __restrict__ loss, float* __restrict__ dlogits, int* __restrict__ correct,
                                      int B, int O, float grad_scale) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float s_loss[32];
   __shared__ int s_corr[32];
   float my_loss = 0.f;
@@ -544,6 +556,8 @@ __global__ void __launch_bounds__(256) linear_bwd_kernel(const __nv_bfloat16* __
                                                          const float* __restrict__ dlogits, float* __restrict__ dw,
                                                          float* __restrict__ db, __nv_bfloat16* __restrict__ dx,
                                                          int B, int F, int O, int nW) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float s_dl[kLinTileB * kLinMaxO];
   __shared__ float s_red[4][kLinMaxO][64];
   if (static_cast<int>(blockIdx.x) < nW) {
@@ -603,6 +617,8 @@ __global__ void __launch_bounds__(256) linear_bwd_kernel(const __nv_bfloat16* __
 // first step gives buf = d, which is torch.optim.SGD's first-step rule (dampening 0).
 __global__ void sgd_momentum_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ buf,
                                     long n, float lr, float momentum, float wd, float gscale) {
+  pdl_launch_dependents();
+  pdl_wait();
   const long n4 = n >> 2;
   const long stride = static_cast<long>(gridDim.x) * blockDim.x;
   for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < n4; i += stride) {
@@ -631,6 +647,8 @@ __global__ void sgd_momentum_kernel(float* __restrict__ p, const float* __restri
 //                               -> Wd bf16 [Cin][taps*Cout] with taps flipped (dgrad operand), optional
 __global__ void prep_conv_weights_kernel(const float* __restrict__ master, __nv_bfloat16* __restrict__ wf,
                                          __nv_bfloat16* __restrict__ wd, int Cout, int Cin, int taps, int kpad) {
+  pdl_launch_dependents();
+  pdl_wait();
   const long nf = static_cast<long>(Cout) * kpad;
   const long nd = wd != nullptr ? static_cast<long>(Cin) * taps * Cout : 0;
   const int kvalid = taps * Cin;
@@ -666,6 +684,8 @@ struct PrepTable {
 };
 
 __global__ void __launch_bounds__(256) prep_conv_weights_batched_kernel(const PrepTable t) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float tile[64][65];
   int li = 0;
   while (li + 1 < t.n && static_cast<int>(blockIdx.x) >= t.l[li + 1].tile_begin) ++li;
@@ -715,9 +735,8 @@ using namespace b200dp;
 extern "C" int b200dp_im2col3x3_c3(const float* x_nchw, void* a0, int B, int H, int W, b200dp_stream_t s) {
   const size_t smem = (kIm2colRows + 2) * 3 * (W + 2) * sizeof(float);
   const int groups = (H + kIm2colRows - 1) / kIm2colRows;
-  im2col_c3_kernel<<<B * groups, 256, smem, static_cast<cudaStream_t>(s)>>>(
-      x_nchw, static_cast<__nv_bfloat16*>(a0), B, H, W);
-  B200DP_CUDA_TRY(cudaGetLastError());
+  B200DP_CUDA_TRY(launch_pdl(im2col_c3_kernel, dim3(B * groups), dim3(256), smem, static_cast<cudaStream_t>(s), x_nchw,
+                             static_cast<__nv_bfloat16*>(a0), B, H, W));
   return 0;
 }
 
@@ -758,8 +777,8 @@ extern "C" int b200dp_bn_relu_pool_fwd(const void* y, const float* stats, const 
   const long Q = static_cast<long>(B) * (pool ? H / 2 : H) * (pool ? W / 2 : W);
   const int rows_per_block = 256 / (C / 8);
   // two output pixels per thread per iteration; at most one resident wave (3 blocks / SM)
-  bn_relu_pool_fwd_kernel<<<grid_for(Q, rows_per_block * 2, 148 * 3), 256, 0, static_cast<cudaStream_t>(s)>>>(p);
-  B200DP_CUDA_TRY(cudaGetLastError());
+  B200DP_CUDA_TRY(launch_pdl(bn_relu_pool_fwd_kernel, dim3(grid_for(Q, rows_per_block * 2, 148 * 3)), dim3(256), 0,
+                             static_cast<cudaStream_t>(s), p));
   return 0;
 }
 
@@ -777,10 +796,9 @@ static int launch_bn_bwd(bool apply, const BnBwdParams& p, cudaStream_t s) {
   // and many short blocks.
   const int blocks = apply ? grid_for(Q, rows_per_block * 2, 148 * 8) : grid_for(Q, rows_per_block, 148 * 3);
   if (apply)
-    bn_relu_pool_bwd_kernel<true><<<blocks, threads, smem, s>>>(p);
+    B200DP_CUDA_TRY(launch_pdl(bn_relu_pool_bwd_kernel<true>, dim3(blocks), dim3(threads), smem, s, p));
   else
-    bn_relu_pool_bwd_kernel<false><<<blocks, threads, smem, s>>>(p);
-  B200DP_CUDA_TRY(cudaGetLastError());
+    B200DP_CUDA_TRY(launch_pdl(bn_relu_pool_bwd_kernel<false>, dim3(blocks), dim3(threads), smem, s, p));
   return 0;
 }
 
@@ -852,17 +870,15 @@ extern "C" int b200dp_linear_fwd(const void* x, const float* w, const float* b, 
   }
   const int threads = 128;
   const int blocks = (B * 32 + threads - 1) / threads;
-  linear_fwd_kernel<<<blocks, threads, 0, static_cast<cudaStream_t>(s)>>>(static_cast<const __nv_bfloat16*>(x), w, b,
-                                                                         logits, B, F, O);
-  B200DP_CUDA_TRY(cudaGetLastError());
+  B200DP_CUDA_TRY(launch_pdl(linear_fwd_kernel, dim3(blocks), dim3(threads), 0, static_cast<cudaStream_t>(s),
+                             static_cast<const __nv_bfloat16*>(x), w, b, logits, B, F, O));
   return 0;
 }
 
 extern "C" int b200dp_cross_entropy(const float* logits, const long long* target, float* loss, float* dlogits,
                                     int* correct, int B, int O, float grad_scale, b200dp_stream_t s) {
-  cross_entropy_kernel<<<1, 256, 0, static_cast<cudaStream_t>(s)>>>(logits, target, loss, dlogits, correct, B, O,
-                                                                    grad_scale);
-  B200DP_CUDA_TRY(cudaGetLastError());
+  B200DP_CUDA_TRY(launch_pdl(cross_entropy_kernel, dim3(1), dim3(256), 0, static_cast<cudaStream_t>(s), logits, target,
+                             loss, dlogits, correct, B, O, grad_scale));
   return 0;
 }
 
@@ -882,9 +898,9 @@ extern "C" int b200dp_linear_bwd(const void* x, const float* w, const float* dlo
   const int nX = static_cast<int>((static_cast<long>(B) * F + threads - 1) / threads);
   B200DP_CUDA_TRY(cudaMemsetAsync(dw, 0, sizeof(float) * O * F, static_cast<cudaStream_t>(s)));
   B200DP_CUDA_TRY(cudaMemsetAsync(db, 0, sizeof(float) * O, static_cast<cudaStream_t>(s)));
-  linear_bwd_kernel<<<nW + nX, threads, 0, static_cast<cudaStream_t>(s)>>>(
-      static_cast<const __nv_bfloat16*>(x), w, dlogits, dw, db, static_cast<__nv_bfloat16*>(dx), B, F, O, nW);
-  B200DP_CUDA_TRY(cudaGetLastError());
+  B200DP_CUDA_TRY(launch_pdl(linear_bwd_kernel, dim3(nW + nX), dim3(threads), 0, static_cast<cudaStream_t>(s),
+                             static_cast<const __nv_bfloat16*>(x), w, dlogits, dw, db, static_cast<__nv_bfloat16*>(dx),
+                             B, F, O, nW));
   return 0;
 }
 
@@ -894,9 +910,9 @@ extern "C" int b200dp_sgd_momentum(float* p, const float* g, float* buf, long lo
     set_error("sgd_momentum: buffers must be 16-byte aligned");
     return B200DP_EINVAL;
   }
-  sgd_momentum_kernel<<<grid_for(n / 4 + 1, 256, 148 * 8), 256, 0, static_cast<cudaStream_t>(s)>>>(
-      p, g, buf, n, lr, momentum, wd, grad_scale);
-  B200DP_CUDA_TRY(cudaGetLastError());
+  B200DP_CUDA_TRY(launch_pdl(sgd_momentum_kernel, dim3(grid_for(n / 4 + 1, 256, 148 * 8)), dim3(256), 0,
+                             static_cast<cudaStream_t>(s), p, g, buf, static_cast<long>(n), lr, momentum, wd,
+                             grad_scale));
   return 0;
 }
 
@@ -1002,8 +1018,8 @@ extern "C" int b200dp_prep_conv_weights_batched(int n, const float* const* maste
                        cin[i], taps[i], kpad[i], tiles, cin[i] / 64};
     tiles += (cout[i] / 64) * taps[i] * (cin[i] / 64);
   }
-  prep_conv_weights_batched_kernel<<<tiles, 256, 0, static_cast<cudaStream_t>(s)>>>(t);
-  B200DP_CUDA_TRY(cudaGetLastError());
+  B200DP_CUDA_TRY(launch_pdl(prep_conv_weights_batched_kernel, dim3(tiles), dim3(256), 0, static_cast<cudaStream_t>(s),
+                             t));
   return 0;
 }
 

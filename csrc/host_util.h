@@ -20,6 +20,32 @@ inline void set_error(const char* fmt, ...) {
 
 }  // namespace b200dp
 
+namespace b200dp {
+
+// Programmatic dependent launch: the kernel may start (and run its prologue: barrier init, TMEM
+// allocation, descriptor prefetch) while the previous kernel on the stream is still draining; inside
+// the kernel griddepcontrol.wait blocks before the first access to global memory.  Captured into a
+// CUDA graph this becomes a programmatic dependency edge.  B200DP_PDL=0 turns it off (A/B runs).
+bool pdl_enabled();
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
+}  // namespace b200dp
+
 #define B200DP_CUDA_TRY(expr)                                                                              \
   do {                                                                                                     \
     cudaError_t _e = (expr);                                                                               \

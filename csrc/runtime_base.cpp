@@ -1,11 +1,20 @@
 // Error buffer + version string of libb200dp.so.
 #include "../include/b200dp.h"
+#include <stdlib.h>
+
 #include "host_util.h"
 
 namespace b200dp {
 char* error_buffer() {
   static thread_local char buf[kErrorBufferSize] = {0};
   return buf;
+}
+bool pdl_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("B200DP_PDL");
+    return e == nullptr || e[0] != '0';
+  }();
+  return on;
 }
 }  // namespace b200dp
 

@@ -111,7 +111,8 @@ def parse_args():
     p.add_argument("--comm-blocks", type=int, default=None)
     p.add_argument("--sync-blocks", type=int, default=None)
     p.add_argument("--port", type=int, default=None)
-    p.add_argument("--nvls", action="store_true", help="multicast heap; large all-reduces reduce inside the NVSwitch")
+    p.add_argument("--nvls", choices=("auto", "on", "off"), default="auto",
+                   help="multicast heap; large all-reduces reduce inside the NVSwitch (auto: on for world > 1)")
     p.add_argument("--single-rank-collectives", action="store_true",
                    help="at --gpus 1 still run the bucket reducer and comm kernels (default: fused local SGD)")
     return p.parse_args()
@@ -142,7 +143,7 @@ def run_native(args) -> dict:
               device="cuda", eval=False, bucket_plan=args.bucket_plan,
               port=args.port or env_int("MASTER_PORT", 29500) + 37)
     kw["single_rank_collectives"] = args.single_rank_collectives
-    kw["nvls"] = args.nvls
+    kw["nvls"] = {"auto": None, "on": True, "off": False}[args.nvls]
     if args.comm_blocks:
         kw["comm_blocks"] = args.comm_blocks
     if args.sync_blocks:
@@ -211,7 +212,7 @@ def run_native(args) -> dict:
         "dtype": "bf16", "data": "synthetic (random CIFAR-10-shaped tensors, random-init weights)",
         "config": {"model": "VGG-11", "global_batch": cfg.global_batch, "per_gpu_batch": B, "seq_len": None,
                    "image": "3x32x32", "mode": mode, "parallelism": f"dp{world}", "optimizer": "SGD lr0.1 m0.9 wd1e-4",
-                   "bucket_plan": args.bucket_plan, "cuda_graph": be.graph is not None,
+                   "bucket_plan": args.bucket_plan, "cuda_graph": be.graph is not None, "nvls": cfg.use_nvls,
                    "l2": f"no explicit flush: one step streams ~{working_set_mb(tr.model.block_specs(), B):.0f} MB "
                          f"(> 126 MB L2) and rewrites every activation and parameter"},
         "gpu_launches": launches, "clocks": sampler.summary(),

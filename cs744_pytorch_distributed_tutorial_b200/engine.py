@@ -162,8 +162,8 @@ class NativeBackend:
             staging = (W - 1) * flat if cfg.mode == "part2a_extra" else 0
             heap_bytes = 4 * (3 * flat + staging) + (8 << 20)
             self.comm = Communicator(self.store, cfg.rank, W, device.index or 0, heap_bytes, timeout_s=cfg.timeout_s,
-                                     multicast=cfg.nvls and W > 1)
-            if cfg.nvls and W > 1:
+                                     multicast=cfg.use_nvls)
+            if cfg.use_nvls:
                 self.comm.prefer_nvls(True)
             heap = self.comm
         self.native = model.enable_native(max_batch=B, heap=heap)

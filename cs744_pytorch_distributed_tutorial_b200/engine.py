@@ -161,10 +161,23 @@ class NativeBackend:
             flat = (n_params + 4 * 64 + 1023) // 1024 * 1024 + 4096
             staging = (W - 1) * flat if cfg.mode == "part2a_extra" else 0
             heap_bytes = 4 * (3 * flat + staging) + (8 << 20)
-            self.comm = Communicator(self.store, cfg.rank, W, device.index or 0, heap_bytes, timeout_s=cfg.timeout_s,
-                                     multicast=cfg.use_nvls)
+            from .ops._lib import NativeError
+            self.comm = None
             if cfg.use_nvls:
-                self.comm.prefer_nvls(True)
+                # The multicast heap needs NVSwitch multicast + VMM support; the capability check fails
+                # before any rank has talked to another, so every rank falls back together.
+                try:
+                    self.comm = Communicator(self.store, cfg.rank, W, device.index or 0, heap_bytes,
+                                             timeout_s=cfg.timeout_s, multicast=True)
+                    self.comm.prefer_nvls(True)
+                except NativeError as e:
+                    if cfg.nvls:      # explicitly requested: do not hide the failure
+                        raise
+                    if cfg.rank == 0:
+                        print(f"b200dp: NVLS unavailable ({e}); using the CUDA-IPC heap and P2P collectives", flush=True)
+                    self.comm = None
+            if self.comm is None:
+                self.comm = Communicator(self.store, cfg.rank, W, device.index or 0, heap_bytes, timeout_s=cfg.timeout_s)
             heap = self.comm
         self.native = model.enable_native(max_batch=B, heap=heap)
         self.sync = make_native_sync(cfg.mode, self.native, self.comm, cfg)

@@ -138,3 +138,8 @@ def test_config_defaults_are_reference_literals_and_validated():
         TrainConfig(mode="part1", num_nodes=2, rank=0)
     with pytest.raises(ValueError):
         TrainConfig(mode="part9")
+    # NVLS: automatic for multi-rank runs, never for a single rank, overridable
+    assert TrainConfig(mode="part3", num_nodes=8, rank=0).use_nvls
+    assert not TrainConfig(mode="part3", num_nodes=1, rank=0).use_nvls
+    assert not TrainConfig(mode="part3", num_nodes=8, rank=0, nvls=False).use_nvls
+    assert not TrainConfig(mode="part1", nvls=True).use_nvls

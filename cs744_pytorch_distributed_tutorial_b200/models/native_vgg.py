@@ -428,7 +428,7 @@ class NativeVGG:
             b = self.blocks[i]
             s = b.spec
             K.bn_relu_pool_bwd(b.y[:B], b.dout[:B], b.mean, b.invstd, b.gamma, b.beta, b.sums, b.dy[:B], b.g_gamma,
-                               b.g_beta, s.pool)
+                               b.g_beta, s.pool, out=b.out[:B])
             # the conv bias feeds a training-mode BatchNorm, so its exact gradient is zero:
             # it simply keeps the zero written by the flat_grads clear at the top of backward().
             if b.direct:

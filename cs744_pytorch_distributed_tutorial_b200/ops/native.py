@@ -18,6 +18,7 @@ import os
 # one cooperative launch (grid barrier) vs reduce + apply; measured on B200: the two-pass form with a
 # full 444-block wave is ~3% faster per step than the co-residency-capped cooperative grid, so off.
 BN_BWD_FUSED = os.environ.get("B200DP_BN_BWD_FUSED", "0") != "0"
+BN_REDUCE_FROM_OUT = os.environ.get("B200DP_BN_REDUCE_FROM_OUT", "1") != "0"
 BN_EPS = 1e-5
 BN_MOMENTUM = 0.1
 
@@ -124,7 +125,8 @@ def bn_relu_pool_fwd(y, stats, gamma, beta, running_mean, running_var, num_batch
     return out
 
 
-def bn_relu_pool_bwd(y, dout, mean, invstd, gamma, beta, sums, dy, dgamma, dbeta, pool: bool, fused: Optional[bool] = None):
+def bn_relu_pool_bwd(y, dout, mean, invstd, gamma, beta, sums, dy, dgamma, dbeta, pool: bool, fused: Optional[bool] = None,
+                     out: Optional[torch.Tensor] = None):
     """Per-channel reduction into ``sums`` (must be zero), then the dY pass -- in one cooperative
     launch with a grid-wide barrier (``fused``) or as two launches."""
     B, H, W, C = y.shape
@@ -132,8 +134,13 @@ def bn_relu_pool_bwd(y, dout, mean, invstd, gamma, beta, sums, dy, dgamma, dbeta
         call("b200dp_bn_relu_pool_bwd_fused", ptr(y), ptr(dout), ptr(mean), ptr(invstd), ptr(gamma), ptr(beta),
              ptr(sums), ptr(dy), ptr(dgamma), ptr(dbeta), B, H, W, C, int(pool), stream_ptr())
         return dy
-    call("b200dp_bn_relu_pool_bwd_reduce", ptr(y), ptr(dout), ptr(mean), ptr(invstd), ptr(gamma), ptr(beta),
-         ptr(sums), B, H, W, C, int(pool), stream_ptr())
+    if out is not None and BN_REDUCE_FROM_OUT:
+        # reduction from the stored block output: 2.5x fewer bytes on pooled layers, no arg-max search
+        call("b200dp_bn_relu_pool_bwd_reduce_from_out", ptr(out), ptr(dout), ptr(gamma), ptr(beta), ptr(sums),
+             dout.numel() // C, C, stream_ptr())
+    else:
+        call("b200dp_bn_relu_pool_bwd_reduce", ptr(y), ptr(dout), ptr(mean), ptr(invstd), ptr(gamma), ptr(beta),
+             ptr(sums), B, H, W, C, int(pool), stream_ptr())
     call("b200dp_bn_relu_pool_bwd_apply", ptr(y), ptr(dout), ptr(mean), ptr(invstd), ptr(gamma), ptr(beta),
          ptr(sums), ptr(dy), ptr(dgamma), ptr(dbeta), B, H, W, C, int(pool), stream_ptr())
     return dy

@@ -457,6 +457,74 @@ __global__ void __launch_bounds__(256, 3) bn_relu_pool_bwd_fused_kernel(const Bn
   bn_relu_pool_bwd_body<true>(p, red);
 }
 
+// Reduction pass from the block OUTPUT instead of the conv output.  With a = relu(z) (max-pooled or
+// not) and g the gradient arriving at a: dz is g where a > 0 and lands on the element whose z equals
+// a, so  S1 = sum_{a>0} g  and  S2 = sum dz*xhat = sum_{a>0} g * (a - beta) / gamma.  For pooled
+// layers this reads two quarter-size tensors instead of the full-resolution y (2.5x fewer bytes) and
+// needs no arg-max search; `a` is the stored bf16 value, i.e. z rounded to 8 bits of mantissa, whose
+// error averages out over the B*H*W terms of the sums.
+__global__ void __launch_bounds__(256, 4) bn_bwd_reduce_from_out_kernel(const __nv_bfloat16* __restrict__ out,
+                                                                        const __nv_bfloat16* __restrict__ dout,
+                                                                        const float* __restrict__ gamma,
+                                                                        const float* __restrict__ beta,
+                                                                        float* __restrict__ sums, long Q, int C) {
+  extern __shared__ float red[];
+  pdl_launch_dependents();
+  pdl_wait();
+  const int chunks = C / 8;
+  const int rows_per_block = blockDim.x / chunks;
+  const int chunk = threadIdx.x % chunks, rl = threadIdx.x / chunks, c0 = chunk * 8;
+  Vec8 bt, ig;
+  {
+    const Vec8 g = load_f32x8(gamma + c0);
+    bt = load_f32x8(beta + c0);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) ig.v[j] = fabsf(g.v[j]) > 1e-20f ? 1.f / g.v[j] : 0.f;
+  }
+  Vec8 a1, a2;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) a1.v[j] = a2.v[j] = 0.f;
+  if (rl < rows_per_block) {
+    const long stride = static_cast<long>(gridDim.x) * rows_per_block;
+    for (long qa = static_cast<long>(blockIdx.x) * rows_per_block + rl; qa < Q; qa += 2 * stride) {
+      const long qb = qa + stride;
+      const bool hasb = qb < Q;
+      const uint4 oa = *reinterpret_cast<const uint4*>(out + qa * C + c0);
+      const uint4 ga = *reinterpret_cast<const uint4*>(dout + qa * C + c0);
+      const uint4 ob = *reinterpret_cast<const uint4*>(out + (hasb ? qb : qa) * C + c0);
+      const uint4 gb = *reinterpret_cast<const uint4*>(dout + (hasb ? qb : qa) * C + c0);
+      const Vec8 o1 = unpack8(oa), g1 = unpack8(ga), o2 = unpack8(ob), g2 = unpack8(gb);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float d1 = o1.v[j] > 0.f ? g1.v[j] : 0.f;
+        const float d2 = (hasb && o2.v[j] > 0.f) ? g2.v[j] : 0.f;
+        a1.v[j] += d1 + d2;
+        a2.v[j] = fmaf(d1, (o1.v[j] - bt.v[j]) * ig.v[j], a2.v[j]);
+        a2.v[j] = fmaf(d2, (o2.v[j] - bt.v[j]) * ig.v[j], a2.v[j]);
+      }
+    }
+  }
+  float* r1 = red;
+  float* r2 = red + rows_per_block * C;
+  if (rl < rows_per_block) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      r1[rl * C + c0 + j] = a1.v[j];
+      r2[rl * C + c0 + j] = a2.v[j];
+    }
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float sa = 0.f, sb = 0.f;
+    for (int r = 0; r < rows_per_block; ++r) {
+      sa += r1[r * C + c];
+      sb += r2[r * C + c];
+    }
+    atomicAdd(sums + c, sa);
+    atomicAdd(sums + C + c, sb);
+  }
+}
+
 // ---------------------------------------------------------------------------
 // classifier: logits = x W^T + b ; softmax cross-entropy (mean) ; backward
 // ---------------------------------------------------------------------------
@@ -847,6 +915,25 @@ extern "C" int b200dp_bn_relu_pool_bwd_reduce(const void* y, const void* dout, c
   BnBwdParams p{static_cast<const __nv_bfloat16*>(y), static_cast<const __nv_bfloat16*>(dout), mean, invstd, gamma,
                 beta, sums, nullptr, nullptr, nullptr, B, H, W, C, pool};
   return launch_bn_bwd(false, p, static_cast<cudaStream_t>(s));
+}
+
+/* Pass 1 computed from the block's stored OUTPUT (`out`, the same shape as `dout`) instead of the conv
+ * output: fewer bytes for pooled layers, no arg-max search.  Same `sums` contract as _reduce. */
+extern "C" int b200dp_bn_relu_pool_bwd_reduce_from_out(const void* out, const void* dout, const float* gamma,
+                                                       const float* beta, float* sums, long long Q, int C,
+                                                       b200dp_stream_t s) {
+  if (C % 8 != 0 || C > 2048 || Q <= 0) {
+    set_error("bn_relu_pool_bwd_reduce_from_out: unsupported shape Q=%lld C=%d", Q, C);
+    return B200DP_EINVAL;
+  }
+  const int threads = 256;
+  const int rows_per_block = threads / (C / 8);
+  const size_t smem = 2 * rows_per_block * C * sizeof(float);
+  const int blocks = grid_for(Q, rows_per_block * 2, 148 * 4);
+  B200DP_CUDA_TRY(launch_pdl(bn_bwd_reduce_from_out_kernel, dim3(blocks), dim3(threads), smem,
+                             static_cast<cudaStream_t>(s), static_cast<const __nv_bfloat16*>(out),
+                             static_cast<const __nv_bfloat16*>(dout), gamma, beta, sums, static_cast<long>(Q), C));
+  return 0;
 }
 
 extern "C" int b200dp_bn_relu_pool_bwd_apply(const void* y, const void* dout, const float* mean,

@@ -122,6 +122,12 @@ int b200dp_bn_relu_pool_fwd(const void* y, const float* stats, const float* gamm
 int b200dp_bn_relu_pool_bwd_reduce(const void* y, const void* dout, const float* mean, const float* invstd,
                                    const float* gamma, const float* beta, float* sums, int B, int H, int W,
                                    int C, int pool, b200dp_stream_t stream);
+/* pass 1 from the block OUTPUT `out` (= maxpool?(relu(bn(y))), same shape as dout; Q = its pixel count):
+ * S1 = sum_{out>0} dout, S2 = sum_{out>0} dout*(out-beta)/gamma.  Reads two quarter-size tensors on
+ * pooled layers instead of the full-resolution y. */
+int b200dp_bn_relu_pool_bwd_reduce_from_out(const void* out, const void* dout, const float* gamma,
+                                            const float* beta, float* sums, long long Q, int C,
+                                            b200dp_stream_t stream);
 /* pass 2: dy = gamma*invstd*(dz - S1/P - xhat*S2/P); dgamma = S2, dbeta = S1 (either may be NULL). */
 int b200dp_bn_relu_pool_bwd_apply(const void* y, const void* dout, const float* mean, const float* invstd,
                                   const float* gamma, const float* beta, const float* sums, void* dy,

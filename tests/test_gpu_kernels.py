@@ -188,6 +188,17 @@ def test_bn_relu_pool_fwd_bwd(C, H, W, pool):
     assert _rel_err(dbeta, br.grad) < 2e-3
     assert _rel_err(dy, yr.grad.permute(0, 2, 3, 1)) < 8e-3
 
+    # the same backward with the reduction taken from the stored block output (the executor's default)
+    sums2 = torch.zeros(2, C, device=DEV)
+    dy2 = torch.empty_like(y)
+    dgamma2 = torch.empty(C, device=DEV)
+    dbeta2 = torch.empty(C, device=DEV)
+    native.bn_relu_pool_bwd(y, dout, mean, invstd, gamma, beta, sums2, dy2, dgamma2, dbeta2, pool, out=out)
+    torch.cuda.synchronize()
+    assert _rel_err(dbeta2, br.grad) < 2e-3
+    assert _rel_err(dgamma2, gr.grad) < 5e-3       # xhat recovered from the bf16-rounded output
+    assert _rel_err(dy2, yr.grad.permute(0, 2, 3, 1)) < 8e-3
+
     # eval mode uses the running statistics
     out_e = torch.empty_like(out)
     native.bn_relu_pool_fwd(y, None, gamma, beta, rm, rv, None, None, None, out_e, pool, False)

@@ -19,6 +19,8 @@ The kernel schedule replaces what the reference gets from ``model(data)`` /
 """
 from __future__ import annotations
 
+import contextlib
+import os
 from dataclasses import dataclass
 from typing import Callable, Dict, List, Optional, Sequence, Tuple
 
@@ -26,6 +28,9 @@ import torch
 import torch.nn as nn
 
 from ..ops import native as K
+
+# weight gradients on a second stream, concurrently with the dgrad / BatchNorm-backward chain
+WGRAD_ON_SIDE_STREAM = os.environ.get("B200DP_WGRAD_STREAM", "1") != "0"
 
 ALIGN = 4  # floats; every tensor starts on a 16-byte boundary inside the flat buffers
 
@@ -192,6 +197,9 @@ class NativeVGG:
         self.flat_nbt = self.flat_nbt_padded[: len(self.specs)]
         self.on_bucket_ready: Optional[Callable[[int], None]] = None
         self._bucket_of_block: Dict[int, List[int]] = {}
+        self._wgrad_stream = torch.cuda.Stream(dev)
+        self._wgrad_fork = [torch.cuda.Event() for _ in self.specs]
+        self._wgrad_join = torch.cuda.Event()
         self._adopt_parameters()
         self._alloc_workspaces()
         self.refresh_shadows()
@@ -422,6 +430,8 @@ class NativeVGG:
         B = self._B
         dl = self.dlogits[:B] if dlogits is None else dlogits
         last = self.blocks[-1]
+        main = torch.cuda.current_stream()
+        side = self._wgrad_stream if WGRAD_ON_SIDE_STREAM else None
         self.flat_grads.zero_()  # split-K weight gradients are accumulated with red.global.add
         K.linear_bwd(last.out[:B], self.fc_w, dl, self.g_fc_w, self.g_fc_b, last.dout[:B])
         for i in range(len(self.blocks) - 1, -1, -1):
@@ -431,17 +441,28 @@ class NativeVGG:
                                b.g_beta, s.pool, out=b.out[:B])
             # the conv bias feeds a training-mode BatchNorm, so its exact gradient is zero:
             # it simply keeps the zero written by the flat_grads clear at the top of backward().
-            if b.direct:
-                K.conv3x3_c3_wgrad(b.dy[:B], self._x_first, b.g_w)
-            else:
-                K.conv_wgrad(b.dy[:B], b.x_in[:B], b.g_w, taps=b.taps, cin_valid=(27 if b.first else None),
-                             split_k=b.wgrad_split_k, block_n=b.wgrad_block_n)
-            if self.on_bucket_ready is not None:
-                for k in self._bucket_of_block.get(i, ()):
-                    self.on_bucket_ready(k)
+            #
+            # wgrad(i) and dgrad(i) both only read dy(i) and are independent: the weight gradient goes to
+            # a second stream so that it runs next to the data-gradient chain (each of these GEMMs keeps
+            # the tensor pipe ~40% busy on its own).  The bucket-ready signal is recorded on that stream.
+            if side is not None:
+                self._wgrad_fork[i].record(main)
+                side.wait_event(self._wgrad_fork[i])
+            with torch.cuda.stream(side) if side is not None else contextlib.nullcontext():
+                if b.direct:
+                    K.conv3x3_c3_wgrad(b.dy[:B], self._x_first, b.g_w)
+                else:
+                    K.conv_wgrad(b.dy[:B], b.x_in[:B], b.g_w, taps=b.taps, cin_valid=(27 if b.first else None),
+                                 split_k=b.wgrad_split_k, block_n=b.wgrad_block_n)
+                if self.on_bucket_ready is not None:
+                    for k in self._bucket_of_block.get(i, ()):
+                        self.on_bucket_ready(k)
             if i > 0:
                 K.conv_igemm(b.dy[:B], b.wd, None, self.blocks[i - 1].dout[:B], block_n=b.dgrad_block_n,
                              split_k=b.dgrad_split_k, cta_pair=b.dgrad_pair, workspace=self.splitk_ws)
+        if side is not None:
+            self._wgrad_join.record(side)
+            main.wait_event(self._wgrad_join)
 
     # ------------------------------------------------------------------ torch.autograd bridge
     def autograd_forward(self, x: torch.Tensor, training: bool) -> torch.Tensor:

@@ -907,8 +907,10 @@ static int conv_wgrad_impl(const void* dy, const void* x, float* dw, int B, int 
     int rc = make_tmap(&tmX, x, 4, dims, box);
     if (rc) return rc;
   }
-  if (block_n == 256) return launch_wgrad<256, 4>(tmDY, tmX, p, tiles, split_k, stream);
-  if (block_n == 128) return launch_wgrad<128, 4>(tmDY, tmX, p, tiles, split_k, stream);
+  // 3 stages (96 / 144 / 72 KiB): the 128-wide kernel then fits on an SM next to a 3-stage dgrad CTA
+  // (99 KiB), which matters because weight and data gradients run on two streams concurrently
+  if (block_n == 256) return launch_wgrad<256, 3>(tmDY, tmX, p, tiles, split_k, stream);
+  if (block_n == 128) return launch_wgrad<128, 3>(tmDY, tmX, p, tiles, split_k, stream);
   return launch_wgrad<64, 4>(tmDY, tmX, p, tiles, split_k, stream);
 }
 

@@ -209,7 +209,8 @@ class NativeBackend:
         nv.loss_fwd_bwd(self.y)
         nv.backward()
         self.sync.sync_and_step()
-        nv.refresh_shadows()
+        if not self.sync.handles_shadows:
+            nv.refresh_shadows()
         # within a captured step the auxiliary stream must be joined before the capture ends
         self.sync.pre_forward()
 
@@ -280,7 +281,8 @@ class NativeBackend:
         nv.loss_fwd_bwd(y)
         nv.backward()
         self.sync.sync_and_step()
-        nv.refresh_shadows()
+        if not self.sync.handles_shadows:
+            nv.refresh_shadows()
         self.sync.pre_forward()
         self.steps_done += 1
         return nv.loss

@@ -200,6 +200,8 @@ class NativeVGG:
         self._wgrad_stream = torch.cuda.Stream(dev)
         self._wgrad_fork = [torch.cuda.Event() for _ in self.specs]
         self._wgrad_join = torch.cuda.Event()
+        self._dgrad_done = [torch.cuda.Event() for _ in self.specs]
+        self._block_prep = None
         self._adopt_parameters()
         self._alloc_workspaces()
         self.refresh_shadows()
@@ -384,6 +386,20 @@ class NativeVGG:
                                               for b in self.blocks if not b.direct])
         self._prep()
 
+    def prep_block(self, i: int) -> None:
+        """Refresh the bf16 weight copies of block ``i`` on the current stream, after the data gradient
+        of that block (the last reader of the old copies in this step) has finished."""
+        if self._block_prep is None:
+            self._block_prep = [None if b.direct else
+                                K.BatchedWeightPrep([(b.w_master, b.wf, b.wd, b.spec.cout, b.spec.cin, 9, b.taps * b.kin)])
+                                for b in self.blocks]
+        torch.cuda.current_stream().wait_event(self._dgrad_done[i])
+        if self._block_prep[i] is not None:
+            self._block_prep[i]()
+
+    def blocks_of_bucket(self, k: int) -> List[int]:
+        return [i for i, ks in self._bucket_of_block.items() if k in ks]
+
     # ------------------------------------------------------------------ forward
     def forward(self, x: torch.Tensor, training: bool = True) -> torch.Tensor:
         """x: fp32 NCHW [B,3,32,32] on the device.  Returns the logits workspace view [B,10]."""
@@ -447,6 +463,11 @@ class NativeVGG:
             # the tensor pipe ~40% busy on its own).  The bucket-ready signal is recorded on that stream.
             if side is not None:
                 self._wgrad_fork[i].record(main)
+            if i > 0:
+                K.conv_igemm(b.dy[:B], b.wd, None, self.blocks[i - 1].dout[:B], block_n=b.dgrad_block_n,
+                             split_k=b.dgrad_split_k, cta_pair=b.dgrad_pair, workspace=self.splitk_ws)
+            self._dgrad_done[i].record(main)   # after this the layer's bf16 weight copies may be rewritten
+            if side is not None:
                 side.wait_event(self._wgrad_fork[i])
             with torch.cuda.stream(side) if side is not None else contextlib.nullcontext():
                 if b.direct:
@@ -457,9 +478,6 @@ class NativeVGG:
                 if self.on_bucket_ready is not None:
                     for k in self._bucket_of_block.get(i, ()):
                         self.on_bucket_ready(k)
-            if i > 0:
-                K.conv_igemm(b.dy[:B], b.wd, None, self.blocks[i - 1].dout[:B], block_n=b.dgrad_block_n,
-                             split_k=b.dgrad_split_k, cta_pair=b.dgrad_pair, workspace=self.splitk_ws)
         if side is not None:
             self._wgrad_join.record(side)
             main.wait_event(self._wgrad_join)

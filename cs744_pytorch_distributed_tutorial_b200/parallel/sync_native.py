@@ -33,6 +33,7 @@ from .comm import CH_AUX, CH_BUCKET, CH_MAIN, BucketReducer, Communicator
 class NativeSync:
     name = "none"
     syncs_buffers = False
+    handles_shadows = False   # True: the strategy refreshes the bf16 weight copies itself
 
     def __init__(self, native, comm: Optional[Communicator], lr: float, momentum: float, weight_decay: float,
                  fuse_optimizer: bool = True):
@@ -71,13 +72,43 @@ class NativeSync:
 
 
 class LocalSGD(NativeSync):
+    """One rank: one fused SGD kernel after backward.  ``overlap`` (off; B200DP_LOCAL_OVERLAP=1): every
+    bucket (one conv layer + its small tensors) is updated and re-laid-out on the weight-gradient
+    stream as soon as its gradients exist -- the single-GPU analogue of part3's per-bucket fused
+    all-reduce+SGD.  Measured on B200 at batch 256: 0.784 ms/step against 0.771 for the single
+    kernel (sixteen more launches competing with backward for HBM), hence not the default."""
+
     name = "none"
+
+    def __init__(self, *a, overlap: bool = False, **kw):
+        super().__init__(*a, **kw)
+        from ..models.native_vgg import WGRAD_ON_SIDE_STREAM
+        import os
+        self.overlap = (overlap or os.environ.get("B200DP_LOCAL_OVERLAP", "0") == "1") and WGRAD_ON_SIDE_STREAM
+        if self.overlap:
+            nv = self.native
+            self.buckets = nv.layout.buckets("layer")
+            nv.set_bucket_plan(self.buckets)
+            nv.on_bucket_ready = self._bucket_ready
+            self.handles_shadows = True
+
+    def _bucket_ready(self, k: int) -> None:
+        nv, bk = self.native, self.buckets[k]
+        K.sgd_momentum(nv.flat_params[bk.start:bk.end], nv.flat_grads[bk.start:bk.end],
+                       nv.flat_momentum[bk.start:bk.end], self.lr, self.momentum, self.weight_decay)
+        for i in nv.blocks_of_bucket(k):
+            nv.prep_block(i)
 
     def sync_only(self) -> None:
         return
 
     def sync_and_step(self) -> None:
-        self._local_sgd()
+        if not self.overlap:
+            self._local_sgd()
+
+    def close(self) -> None:
+        if self.overlap:
+            self.native.on_bucket_ready = None
 
 
 class ParamServerSync(NativeSync):

@@ -176,7 +176,9 @@ def test_modes_agree_with_each_other(mode_results):
     d0 = base["params"] - base["init"]
     for key, ranks in mode_results.items():
         assert torch.equal(ranks[0]["init"], base["init"])
-        assert abs(ranks[0]["losses"][0] - base["losses"][0]) < 2e-3, key
+        # the first loss precedes any exchange; runs differ only through the autotuner's tile choices
+        # (accumulation order of bf16 products), i.e. by bf16 rounding noise
+        assert abs(ranks[0]["losses"][0] - base["losses"][0]) < 1e-2, key
         d = ranks[0]["params"] - ranks[0]["init"]
         cos = torch.nn.functional.cosine_similarity(d, d0, dim=0).item()
         assert cos > 0.97, f"{key} vs part2b: update cosine {cos}"

@@ -72,39 +72,65 @@ class NativeSync:
 
 
 class LocalSGD(NativeSync):
-    """One rank: one fused SGD kernel after backward.  ``overlap`` (off; B200DP_LOCAL_OVERLAP=1): every
-    bucket (one conv layer + its small tensors) is updated and re-laid-out on the weight-gradient
-    stream as soon as its gradients exist -- the single-GPU analogue of part3's per-bucket fused
-    all-reduce+SGD.  Measured on B200 at batch 256: 0.784 ms/step against 0.771 for the single
-    kernel (sixteen more launches competing with backward for HBM), hence not the default."""
+    """One rank.  The optimizer runs in two phases: as soon as the gradients of the last ``split``
+    conv layers exist (95 % of all parameters live there and they are ready after about half of
+    backward) one fused SGD kernel updates that range and one kernel refreshes their bf16 copies on
+    the weight-gradient stream, in the shadow of the remaining backward; the small remainder follows
+    after backward.  ``B200DP_LOCAL_OVERLAP``: ``2`` (default) two-phase, ``1`` per-bucket (measured
+    slower: sixteen more launches competing with backward), ``0`` one kernel after backward."""
 
     name = "none"
 
-    def __init__(self, *a, overlap: bool = False, **kw):
+    def __init__(self, *a, overlap: Optional[int] = None, **kw):
         super().__init__(*a, **kw)
-        from ..models.native_vgg import WGRAD_ON_SIDE_STREAM
         import os
-        self.overlap = (overlap or os.environ.get("B200DP_LOCAL_OVERLAP", "0") == "1") and WGRAD_ON_SIDE_STREAM
+        from ..models.native_vgg import WGRAD_ON_SIDE_STREAM
+        mode = int(os.environ.get("B200DP_LOCAL_OVERLAP", "2")) if overlap is None else int(overlap)
+        self.overlap = mode if WGRAD_ON_SIDE_STREAM else 0
+        nv = self.native
         if self.overlap:
-            nv = self.native
             self.buckets = nv.layout.buckets("layer")
             nv.set_bucket_plan(self.buckets)
             nv.on_bucket_ready = self._bucket_ready
             self.handles_shadows = True
+        if self.overlap == 2:
+            # phase 1 covers the buckets of the deepest blocks down to (and including) `first_block`
+            n = len(nv.blocks)
+            self.first_block = max(n - 5, 1)            # VGG-11: blocks 3..7 = 35.3 of 36.9 MB
+            self.split_bucket = max(k for k in range(len(self.buckets)) if self.first_block in nv.blocks_of_bucket(k))
+            self.split_end = self.buckets[self.split_bucket].end
+            self._prep_hi = K.BatchedWeightPrep([(b.w_master, b.wf, b.wd, b.spec.cout, b.spec.cin, 9, b.taps * b.kin)
+                                                 for b in nv.blocks[self.first_block:] if not b.direct])
+            self._prep_lo = K.BatchedWeightPrep([(b.w_master, b.wf, b.wd, b.spec.cout, b.spec.cin, 9, b.taps * b.kin)
+                                                 for b in nv.blocks[:self.first_block] if not b.direct])
+
+    def _sgd_range(self, lo: int, hi: int) -> None:
+        nv = self.native
+        K.sgd_momentum(nv.flat_params[lo:hi], nv.flat_grads[lo:hi], nv.flat_momentum[lo:hi], self.lr, self.momentum,
+                       self.weight_decay)
 
     def _bucket_ready(self, k: int) -> None:
-        nv, bk = self.native, self.buckets[k]
-        K.sgd_momentum(nv.flat_params[bk.start:bk.end], nv.flat_grads[bk.start:bk.end],
-                       nv.flat_momentum[bk.start:bk.end], self.lr, self.momentum, self.weight_decay)
-        for i in nv.blocks_of_bucket(k):
-            nv.prep_block(i)
+        nv = self.native
+        if self.overlap == 1:
+            self._sgd_range(self.buckets[k].start, self.buckets[k].end)
+            for i in nv.blocks_of_bucket(k):
+                nv.prep_block(i)
+        elif k == self.split_bucket:
+            # runs on the weight-gradient stream, right after wgrad(first_block); the data gradient of
+            # that block (last reader of the old bf16 copies of blocks >= first_block) is already queued
+            self._sgd_range(0, self.split_end)
+            torch.cuda.current_stream().wait_event(nv._dgrad_done[self.first_block])
+            self._prep_hi()
 
     def sync_only(self) -> None:
         return
 
     def sync_and_step(self) -> None:
-        if not self.overlap:
+        if self.overlap == 0:
             self._local_sgd()
+        elif self.overlap == 2:
+            self._sgd_range(self.split_end, self.n)
+            self._prep_lo()
 
     def close(self) -> None:
         if self.overlap:

@@ -1,0 +1,82 @@
+"""CPU tests of the benchmark plumbing: both arms degrade cleanly without a GPU, and the reference
+harness loads the unmodified tutorial sources (hash-checked) with only the documented parameterisation."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+sys.path.insert(0, os.path.dirname(__file__))
+from helpers import REPO  # noqa: E402
+
+sys.path.insert(0, os.path.join(REPO, "baseline"))
+
+needs_ref = pytest.mark.skipif(not os.path.exists(os.path.join(REPO, "baseline", "_ref", "MANIFEST.json")),
+                               reason="baseline/_ref not installed (run baseline/install_reference.py)")
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU behaviour")
+@pytest.mark.parametrize("impl", ["native", "reference"])
+def test_bench_without_gpu_prints_one_json_line_and_exits_zero(impl):
+    r = subprocess.run([sys.executable, "bench.py", "--impl", impl, "--steps", "2", "--warmup", "1"], cwd=REPO,
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-1000:]
+    out = json.loads(r.stdout.strip().splitlines()[-1])
+    assert out["impl"] == impl and "unavailable" in out
+
+
+@needs_ref
+def test_reference_sources_are_byte_identical_to_the_manifest():
+    import hashlib
+    import ref_harness
+    manifest = json.load(open(os.path.join(REPO, "baseline", "_ref", "MANIFEST.json")))["sha256"]
+    assert len(manifest) == 17
+    for rel, digest in manifest.items():
+        data = open(os.path.join(REPO, "baseline", "_ref", rel), "rb").read()
+        assert hashlib.sha256(data).hexdigest() == digest, rel
+        if os.path.exists(os.path.join("/root/reference", rel)):
+            assert data == open(os.path.join("/root/reference", rel), "rb").read(), rel
+    assert ref_harness.available() is None
+
+
+@needs_ref
+def test_reference_module_loads_and_only_world_literals_are_parameterised():
+    import ref_harness
+    src = open(os.path.join(REPO, "baseline", "_ref", "master", "part2b", "part2b.py")).read()
+    assert ref_harness._parameterise_world(src, 4, "part2b.py") == src          # world 4: untouched
+    p8 = ref_harness._parameterise_world(src, 8, "part2b.py")
+    assert "dist.new_group(list(range(8)))" in p8 and "p.grad / 8" in p8 and "[0, 1, 2, 3]" not in p8
+    # everything else is character-for-character the reference
+    import difflib
+    changed = [l for l in difflib.unified_diff(src.splitlines(), p8.splitlines(), lineterm="", n=0)
+               if l[:1] in "+-" and l[:3] not in ("+++", "---")]
+    assert len(changed) == 4, changed
+    with pytest.raises(NotImplementedError):
+        ref_harness._parameterise_world("x", 8, "part2a_extra.py")
+    mod = ref_harness.load_reference("part3", rank=0, world=1, device="cpu")
+    assert mod.device == "cpu" and callable(mod.train_model) and hasattr(mod, "DDP")
+    m = mod.mdl.VGG11()
+    assert sum(p.numel() for p in m.parameters()) == 9_231_114
+    slave = ref_harness.load_reference("part2b", rank=1, world=4, device="cpu")
+    assert slave.__file__.endswith(os.path.join("slave", "part2b", "part2b.py"))
+
+
+@needs_ref
+def test_reference_train_model_runs_on_cpu_through_the_harness_loader():
+    """The reference's own loop, driven with two synthetic batches (part1: no process group needed)."""
+    import contextlib
+    import io
+    import ref_harness
+    mod = ref_harness.load_reference("part1", rank=0, world=1, device="cpu")
+    torch.manual_seed(5000)
+    model = mod.mdl.VGG11()
+    opt = torch.optim.SGD(model.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4)
+    crit = torch.nn.CrossEntropyLoss()
+    g = torch.Generator().manual_seed(0)
+    batches = [(torch.randn(4, 3, 32, 32, generator=g), torch.randint(0, 10, (4,), generator=g)) for _ in range(2)]
+    buf = io.StringIO()
+    with contextlib.redirect_stdout(buf):
+        mod.train_model(model, batches, opt, crit, 0)
+    assert buf.getvalue().startswith("0 loss: ")

@@ -18,6 +18,9 @@ import os
 # one cooperative launch (grid barrier) vs reduce + apply; measured on B200: the two-pass form with a
 # full 444-block wave is ~3% faster per step than the co-residency-capped cooperative grid, so off.
 BN_BWD_FUSED = os.environ.get("B200DP_BN_BWD_FUSED", "0") != "0"
+# tensors of at most this many elements take the one-launch cooperative kernel even when the flag
+# above is off: on the 2x2 / 4x4 layers both passes are launch-latency bound (0 = never)
+BN_BWD_FUSED_MAX_ELEMS = int(os.environ.get("B200DP_BN_BWD_FUSED_MAX", "0"))
 BN_REDUCE_FROM_OUT = os.environ.get("B200DP_BN_REDUCE_FROM_OUT", "1") != "0"
 BN_EPS = 1e-5
 BN_MOMENTUM = 0.1
@@ -130,7 +133,7 @@ def bn_relu_pool_bwd(y, dout, mean, invstd, gamma, beta, sums, dy, dgamma, dbeta
     """Per-channel reduction into ``sums`` (must be zero), then the dY pass -- in one cooperative
     launch with a grid-wide barrier (``fused``) or as two launches."""
     B, H, W, C = y.shape
-    if BN_BWD_FUSED if fused is None else fused:
+    if (BN_BWD_FUSED or y.numel() <= BN_BWD_FUSED_MAX_ELEMS) if fused is None else fused:
         call("b200dp_bn_relu_pool_bwd_fused", ptr(y), ptr(dout), ptr(mean), ptr(invstd), ptr(gamma), ptr(beta),
              ptr(sums), ptr(dy), ptr(dgamma), ptr(dbeta), B, H, W, C, int(pool), stream_ptr())
         return dy

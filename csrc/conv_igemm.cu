@@ -21,6 +21,7 @@
 #include <cuda.h>
 #include <cudaTypedefs.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "../include/b200dp.h"
 #include "common.cuh"
@@ -47,6 +48,9 @@ struct IgemmParams {
   // fp32 partial tile into `partial` ([M][Cout], zero on entry); a finalize kernel produces `out`.
   float* partial;
   int kb_per_split;
+  // 1: the four epilogue warps combine their statistics in shared memory (the drained stage-0 operand
+  // buffer) and issue one atomic per channel per CTA instead of one per warp (B200DP_STATS_SMEM=0: off)
+  int stats_via_smem;
 };
 
 // Sum v[j] over the 32 lanes of the warp for every j; lane l returns the total of column l.
@@ -74,7 +78,7 @@ B200DP_DEVINL void red_add_v4(float* addr, float a, float b, float c, float d) {
 // or fp32 red.add into the split-K workspace.  Warp w may only touch TMEM lanes [32*(w%4), 32*(w%4)+32).
 template <int BLOCK_N>
 B200DP_DEVINL void igemm_epilogue(const IgemmParams& p, uint32_t tmem_base, uint64_t* tmem_full_bar, int warp,
-                                  int lane, int m_tile, int n_tile) {
+                                  int lane, int m_tile, int n_tile, float* scratch) {
   // Epilogue: warp w may only touch TMEM lanes [32*(w%4), 32*(w%4)+32).
   const int q = warp & 3;
   const int row = q * 32 + lane;
@@ -129,16 +133,33 @@ B200DP_DEVINL void igemm_epilogue(const IgemmParams& p, uint32_t tmem_base, uint
       }
       const float t1 = warp_transpose_sum(s1, lane);
       const float t2 = warp_transpose_sum(s2, lane);
-      const int ch = n_tile * BLOCK_N + c + lane;
-      atomicAdd(p.stats + ch, t1);
-      atomicAdd(p.stats + p.n_total + ch, t2);
+      if (p.stats_via_smem) {
+        // scratch is operand memory: every MMA that read it has completed (tmem_full_bar fired)
+        scratch[q * 2 * BLOCK_N + c + lane] = t1;
+        scratch[q * 2 * BLOCK_N + BLOCK_N + c + lane] = t2;
+      } else {
+        const int ch = n_tile * BLOCK_N + c + lane;
+        atomicAdd(p.stats + ch, t1);
+        atomicAdd(p.stats + p.n_total + ch, t2);
+      }
+    }
+  }
+  if (p.partial == nullptr && p.stats != nullptr && p.stats_via_smem) {
+    asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps only
+    for (int i = static_cast<int>(threadIdx.x) - 64; i < 2 * BLOCK_N; i += 128) {
+      const float t = scratch[i] + scratch[2 * BLOCK_N + i] + scratch[4 * BLOCK_N + i] + scratch[6 * BLOCK_N + i];
+      const int half = i / BLOCK_N;
+      atomicAdd(p.stats + half * p.n_total + n_tile * BLOCK_N + (i - half * BLOCK_N), t);
     }
   }
   tc_fence_before();
 }
 
+// STAGES == 1 is the single-K-block case (layer 0: one 64-wide K block per tile).  Such a CTA is a pure
+// latency chain (TMA -> one MMA group -> epilogue), so it is compiled for 5 CTAs per SM (25 KiB of
+// shared memory, 64 TMEM columns each) instead of the 2 that a 4-stage ring allows.
 template <int BLOCK_N, int STAGES>
-__global__ void __launch_bounds__(kNumThreads)
+__global__ void __launch_bounds__(kNumThreads, STAGES == 1 ? 5 : 1)
     conv_igemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                       const IgemmParams p) {
   constexpr int kBStageBytes = BLOCK_N * kBlockK * 2;
@@ -240,7 +261,7 @@ __global__ void __launch_bounds__(kNumThreads)
       umma_commit(tmem_full_bar);
     }
   } else {
-    igemm_epilogue<BLOCK_N>(p, tmem_base, tmem_full_bar, warp, lane, m_tile, n_tile);
+    igemm_epilogue<BLOCK_N>(p, tmem_base, tmem_full_bar, warp, lane, m_tile, n_tile, reinterpret_cast<float*>(smem));
   }
   __syncthreads();
   if (warp == 1) {
@@ -365,7 +386,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads)
       umma_commit_2cta(tmem_full_bar, 0b11);
     }
   } else {
-    igemm_epilogue<BLOCK_N>(p, tmem_base, tmem_full_bar, warp, lane, m_tile, n_tile);
+    igemm_epilogue<BLOCK_N>(p, tmem_base, tmem_full_bar, warp, lane, m_tile, n_tile, reinterpret_cast<float*>(smem));
   }
   __syncthreads();
   tc_fence_before();
@@ -683,6 +704,15 @@ static int tile_geometry(int H, int W, int pixels_per_tile, int* TH, int* TN) {
   return 0;
 }
 
+// B200DP_IGEMM_SHORTK=0 keeps single-K-block GEMMs on the 4-stage kernel (A/B runs).
+static bool short_k_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("B200DP_IGEMM_SHORTK");
+    return e == nullptr || e[0] != '0';
+  }();
+  return on;
+}
+
 template <int BLOCK_N, int STAGES>
 static int launch_igemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const IgemmParams& p, int m_tiles,
                         int splits, cudaStream_t stream) {
@@ -753,6 +783,11 @@ static int conv_igemm_impl(const void* act, const void* wgt, const float* bias, 
   p.bias = bias;
   p.out = static_cast<__nv_bfloat16*>(out);
   p.stats = stats;
+  static const bool stats_smem = [] {
+    const char* e = getenv("B200DP_STATS_SMEM");
+    return e == nullptr || e[0] != '0';
+  }();
+  p.stats_via_smem = stats_smem ? 1 : 0;
   const int m_tiles = (p.m_total + kBlockM - 1) / kBlockM;
   if (block_n == 0) {
     // largest N tile that still yields about one CTA per SM
@@ -813,7 +848,10 @@ static int conv_igemm_impl(const void* act, const void* wgt, const float* bias, 
   switch (block_n) {
     case 256: rc = launch_igemm<256, 4>(tmA, tmB, p, m_tiles, split_k, stream); break;
     case 128: rc = launch_igemm<128, 3>(tmA, tmB, p, m_tiles, split_k, stream); break;
-    case 64: rc = launch_igemm<64, 4>(tmA, tmB, p, m_tiles, split_k, stream); break;
+    case 64:
+      rc = (p.kb_per_split == 1 && short_k_enabled()) ? launch_igemm<64, 1>(tmA, tmB, p, m_tiles, split_k, stream)
+                                                      : launch_igemm<64, 4>(tmA, tmB, p, m_tiles, split_k, stream);
+      break;
     case 32: rc = launch_igemm<32, 4>(tmA, tmB, p, m_tiles, split_k, stream); break;
     default: set_error("conv_igemm: block_n=%d not in {32,64,128,256}", block_n); return B200DP_EINVAL;
   }

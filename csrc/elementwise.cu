@@ -96,6 +96,57 @@ __global__ void __launch_bounds__(256) im2col_c3_kernel(const float* __restrict_
   }
 }
 
+// Same result, cheaper address arithmetic: blockDim is a multiple of 8, so a thread emits the same
+// 16-byte chunk of every patch row it touches.  The (tap, channel) -> window offset decode of its 8
+// columns is done once, outside the pixel loop; the upper half of the row (columns 32..63) is a
+// constant zero store.  B200DP_IM2COL_V2=0 selects the kernel above (A/B runs).
+__global__ void __launch_bounds__(256) im2col_c3_v2_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ a0,
+                                                           int B, int H, int W) {
+  pdl_launch_dependents();
+  pdl_wait();
+  extern __shared__ float win[];  // [rows + 2][3 channels][W + 2]
+  const int Wp = W + 2;
+  const int groups = (H + kIm2colRows - 1) / kIm2colRows;
+  const int n = blockIdx.x / groups, h0 = (blockIdx.x - n * groups) * kIm2colRows;
+  const int rows = min(kIm2colRows, H - h0);
+  for (int i = threadIdx.x; i < (rows + 2) * 3 * Wp; i += blockDim.x) {
+    const int r = i / (3 * Wp), rem = i - r * 3 * Wp;
+    const int c = rem / Wp, ww = rem - c * Wp - 1;
+    const int hh = h0 + r - 1;
+    win[i] = (hh >= 0 && hh < H && ww >= 0 && ww < W) ? __ldg(x + ((static_cast<long>(n) * 3 + c) * H + hh) * W + ww) : 0.f;
+  }
+  const int chunk = threadIdx.x & 7;
+  int off[8];
+  unsigned live = 0;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int k = chunk * 8 + j;  // k = (r*3 + s)*3 + c
+    const bool real = k < 27;
+    off[j] = real ? (k / 9) * 3 * Wp + (k % 3) * Wp + (k / 3) % 3 : 0;
+    live |= static_cast<unsigned>(real) << j;
+  }
+  __syncthreads();
+  __nv_bfloat16* dst_base = a0 + (static_cast<long>(n) * H + h0) * W * 64 + chunk * 8;
+  for (int pix = threadIdx.x >> 3; pix < rows * W; pix += blockDim.x >> 3) {
+    uint4 o = make_uint4(0u, 0u, 0u, 0u);
+    if (live != 0) {
+      const int pr = pix / W, w = pix - pr * W;
+      const float* base = win + pr * 3 * Wp + w;
+      float v[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float t = base[off[j]];
+        v[j] = ((live >> j) & 1u) ? t : 0.f;
+      }
+      o.x = pack_bf16x2(v[0], v[1]);
+      o.y = pack_bf16x2(v[2], v[3]);
+      o.z = pack_bf16x2(v[4], v[5]);
+      o.w = pack_bf16x2(v[6], v[7]);
+    }
+    *reinterpret_cast<uint4*>(dst_base + static_cast<long>(pix) * 64) = o;
+  }
+}
+
 // ---------------------------------------------------------------------------
 // per-channel sum / sum of squares of a bf16 [P][C] matrix (stand-alone variant;
 // the conv epilogue can produce the same numbers fused).
@@ -953,8 +1004,12 @@ using namespace b200dp;
 extern "C" int b200dp_im2col3x3_c3(const float* x_nchw, void* a0, int B, int H, int W, b200dp_stream_t s) {
   const size_t smem = (kIm2colRows + 2) * 3 * (W + 2) * sizeof(float);
   const int groups = (H + kIm2colRows - 1) / kIm2colRows;
-  B200DP_CUDA_TRY(launch_pdl(im2col_c3_kernel, dim3(B * groups), dim3(256), smem, static_cast<cudaStream_t>(s), x_nchw,
-                             static_cast<__nv_bfloat16*>(a0), B, H, W));
+  static const bool v2 = [] {
+    const char* e = getenv("B200DP_IM2COL_V2");
+    return e == nullptr || e[0] != '0';
+  }();
+  B200DP_CUDA_TRY(launch_pdl(v2 ? im2col_c3_v2_kernel : im2col_c3_kernel, dim3(B * groups), dim3(256), smem,
+                             static_cast<cudaStream_t>(s), x_nchw, static_cast<__nv_bfloat16*>(a0), B, H, W));
   return 0;
 }
 

@@ -47,7 +47,10 @@ class TrainConfig:
     sync_impl: str = "auto"     # auto | torch | native
     bucket_plan: str = "layer"  # layer (8 buckets) | ddp (torch's 3 buckets) | single
     fuse_optimizer: bool = True  # SGD in the collective epilogue where the mode allows it
-    comm_blocks: int = 16       # CTAs of a side-stream bucket kernel (part3); the GEMMs keep the other SMs
+    # CTAs of a side-stream bucket kernel (part3); the GEMMs keep the other SMs.  Three 9.4 MB buckets
+    # become ready in the first ~100 us of backward; 16 CTAs could not drain them before backward ended
+    # (2 GPUs: 0.857 ms/step with 16, 0.771 with 32, 0.769 with 48 -- profiles/RESULTS.md section 0)
+    comm_blocks: int = 32
     sync_blocks: int = 64       # CTAs of a collective issued after backward (part2a / part2b)
     # VMM heap + NVSwitch multicast; large all-reduces run in the switch (multimem).  None = automatic:
     # on whenever world_size > 1 (measured, part3 ms/step with NVLS vs the two-shot P2P kernel: 0.95 vs

@@ -114,3 +114,26 @@ def test_cli_two_process_part2a_with_reference_flags():
     assert outs[0][0].splitlines()[0].startswith("0 loss: ")
     m = json.loads(outs[0][0].strip().splitlines()[-1])
     assert m["world_size"] == 2 and m["global_batch"] == 16
+
+
+@pytest.mark.parametrize("part", ["part1", "part2a", "part2a_extra", "part2b", "part3"])
+def test_example_scripts_keep_the_reference_command_line(part):
+    """examples/partX.py accept exactly the tutorial's flags (ref: master/part2a/part2a.py:136-143) and
+    preset the mode; `--help` must not need a GPU or a rendezvous."""
+    script = os.path.join(REPO, "examples", part + ".py")
+    r = subprocess.run([sys.executable, script, "--help"], cwd=REPO, capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr[-2000:]
+    for flag in ("--master-ip", "--num-nodes", "--rank"):
+        assert flag in r.stdout
+    src = open(script).read()
+    assert f'"--mode", "{part}"' in src
+
+
+def test_example_launcher_runs_two_ranks_of_part3_on_cpu():
+    env = dict(os.environ, PORT=str(free_port()))
+    cmd = ["bash", os.path.join(REPO, "examples", "launch_local.sh"), "part3", "2", "--device", "cpu",
+           "--global-batch", "16", "--train-size", "64", "--test-size", "16", "--iters", "2"]
+    r = subprocess.run(cmd, cwd=REPO, capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0, r.stderr[-2000:]
+    m = json.loads(r.stdout.strip().splitlines()[-1])
+    assert m["mode"] == "part3" and m["world_size"] == 2

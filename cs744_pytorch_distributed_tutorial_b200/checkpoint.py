@@ -23,7 +23,8 @@ def save_checkpoint(path: str, model, optimizer_state: Optional[dict] = None, st
 
 
 def load_checkpoint(path: str, model, strict: bool = True) -> dict:
-    ck = torch.load(path, map_location="cpu", weights_only=False)
+    # tensors, numbers and plain containers only: the restricted unpickler is enough and refuses code
+    ck = torch.load(path, map_location="cpu", weights_only=True)
     sd = ck["model"] if isinstance(ck, dict) and "model" in ck else ck  # also accept a bare state_dict
     if hasattr(model, "load_portable_state_dict"):
         model.load_portable_state_dict(sd, strict=strict)

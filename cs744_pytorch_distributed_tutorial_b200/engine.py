@@ -403,7 +403,7 @@ class Trainer:
         """One pass over ``loader`` with the reference's console output plus device-side timing."""
         cfg = self.cfg
         clock = StepClock(self.device)
-        ref_now = None
+        ref_first = time.time()
         last_loss = float("nan")
         n_iters = 0
         for batch_idx, (data, target) in enumerate(loader):
@@ -416,9 +416,8 @@ class Trainer:
             if batch_idx % cfg.log_interval == 0:
                 last_loss = float(loss.item())
                 print(batch_idx, "loss: ", last_loss, flush=True)
-                ref_now = time.time()
                 if batch_idx == 0:
-                    ref_first = ref_now
+                    ref_first = time.time()
             if batch_idx == 10:
                 # the reference divides a 10-iteration span by 9; we print the same
                 # label but the unbiased value

@@ -36,6 +36,10 @@ WGRAD_ON_SIDE_STREAM = os.environ.get("B200DP_WGRAD_STREAM", "1") != "0"
 # backward; measured neutral at batch 256 (0.7435 vs 0.7422 ms), so off unless asked for
 ZERO_GRADS_EARLY = os.environ.get("B200DP_ZERO_GRADS_EARLY", "0") != "0"
 
+# experimental (not yet validated on hardware): the dgrad epilogue of block i also accumulates the
+# BatchNorm-backward sums of block i-1, which then skips its reduction launch
+DGRAD_BN_REDUCE = os.environ.get("B200DP_DGRAD_BN_REDUCE", "0") != "0"
+
 ALIGN = 4  # floats; every tensor starts on a 16-byte boundary inside the flat buffers
 
 
@@ -468,11 +472,13 @@ class NativeVGG:
         else:
             self.flat_grads.zero_()  # split-K weight gradients are accumulated with red.global.add
         K.linear_bwd(last.out[:B], self.fc_w, dl, self.g_fc_w, self.g_fc_b, last.dout[:B])
+        reduced = False   # True: the dgrad of the block above already accumulated this block's sums
         for i in range(len(self.blocks) - 1, -1, -1):
             b = self.blocks[i]
             s = b.spec
             K.bn_relu_pool_bwd(b.y[:B], b.dout[:B], b.mean, b.invstd, b.gamma, b.beta, b.sums, b.dy[:B], b.g_gamma,
-                               b.g_beta, s.pool, out=b.out[:B])
+                               b.g_beta, s.pool, out=b.out[:B], skip_reduce=reduced)
+            reduced = False
             # the conv bias feeds a training-mode BatchNorm, so its exact gradient is zero:
             # it simply keeps the zero written by the flat_grads clear at the top of backward().
             #
@@ -481,7 +487,13 @@ class NativeVGG:
             # the tensor pipe ~40% busy on its own).  The bucket-ready signal is recorded on that stream.
             if side is not None:
                 self._wgrad_fork[i].record(main)
-            if i > 0:
+            if i > 0 and DGRAD_BN_REDUCE:
+                prev = self.blocks[i - 1]
+                K.conv_dgrad_bn_reduce(b.dy[:B], b.wd, prev.dout[:B], prev.out[:B], prev.gamma, prev.beta, prev.sums,
+                                       block_n=b.dgrad_block_n, split_k=b.dgrad_split_k, cta_pair=b.dgrad_pair,
+                                       workspace=self.splitk_ws)
+                reduced = True
+            elif i > 0:
                 K.conv_igemm(b.dy[:B], b.wd, None, self.blocks[i - 1].dout[:B], block_n=b.dgrad_block_n,
                              split_k=b.dgrad_split_k, cta_pair=b.dgrad_pair, workspace=self.splitk_ws)
             self._dgrad_done[i].record(main)   # after this the layer's bf16 weight copies may be rewritten

@@ -111,10 +111,6 @@ class VGG(nn.Module):
             self._native.refresh_from_module()
         return missing
 
-    def state_dict(self, *args, **kwargs):
-        sd = super().state_dict(*args, **kwargs)
-        return sd
-
 
 def VGG11() -> VGG:
     """Factory with the reference's name (ref: master/part1/model.py:49-50)."""

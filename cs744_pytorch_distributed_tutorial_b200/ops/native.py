@@ -65,6 +65,30 @@ def conv_igemm(act: torch.Tensor, wgt: torch.Tensor, bias: Optional[torch.Tensor
     return out
 
 
+def conv_dgrad_bn_reduce(dy: torch.Tensor, wd: torch.Tensor, dout_prev: torch.Tensor, out_prev: torch.Tensor,
+                         gamma: torch.Tensor, beta: torch.Tensor, sums: torch.Tensor, block_n: int = 0,
+                         split_k: int = 1, workspace: Optional[torch.Tensor] = None,
+                         cta_pair: bool = False) -> torch.Tensor:
+    """Data gradient of a 3x3 conv fused with the BatchNorm-backward reduction of the block below:
+    ``dout_prev = dgrad(dy, wd)`` and ``sums += [sum_{a>0} g, sum_{a>0} g*(a-beta)/gamma]`` where
+    ``a = out_prev`` is that block's stored output.  Saves the ``bn_bwd_reduce_from_out`` launch and its
+    read of ``dout_prev`` (ref: the autograd of master/part1/model.py:18-23 run by part1.py:37)."""
+    _chk(dy, torch.bfloat16, "dy")
+    _chk(wd, torch.bfloat16, "wd")
+    _chk(dout_prev, torch.bfloat16, "dout_prev")
+    _chk(out_prev, torch.bfloat16, "out_prev")
+    B, H, W, Cin = dy.shape
+    Cout = wd.shape[0]
+    assert wd.shape[1] == 9 * Cin and dout_prev.shape == (B, H, W, Cout) and out_prev.shape == dout_prev.shape
+    assert sums.numel() >= 2 * Cout and gamma.numel() == Cout and beta.numel() == Cout
+    if split_k > 1:
+        assert workspace is not None and workspace.dtype == torch.float32 and workspace.numel() >= dout_prev.numel()
+    call("b200dp_conv_dgrad_bn_reduce", ptr(dy), ptr(wd), ptr(dout_prev), ptr(workspace) if split_k > 1 else None,
+         ptr(out_prev), ptr(gamma), ptr(beta), ptr(sums), B, H, W, Cin, Cout, 9, block_n, split_k, int(cta_pair),
+         stream_ptr())
+    return dout_prev
+
+
 def conv_wgrad(dy: torch.Tensor, x: torch.Tensor, dw: torch.Tensor, taps: int = 9, cin_valid: Optional[int] = None,
                split_k: int = 0, accumulate: bool = False, block_n: int = 0) -> torch.Tensor:
     """dw[Cout, taps, cin_valid] (fp32) (+)= sum_p dy[p, Cout] * x[p+tap, Cin].  With split-K or
@@ -129,10 +153,15 @@ def bn_relu_pool_fwd(y, stats, gamma, beta, running_mean, running_var, num_batch
 
 
 def bn_relu_pool_bwd(y, dout, mean, invstd, gamma, beta, sums, dy, dgamma, dbeta, pool: bool, fused: Optional[bool] = None,
-                     out: Optional[torch.Tensor] = None):
+                     out: Optional[torch.Tensor] = None, skip_reduce: bool = False):
     """Per-channel reduction into ``sums`` (must be zero), then the dY pass -- in one cooperative
-    launch with a grid-wide barrier (``fused``) or as two launches."""
+    launch with a grid-wide barrier (``fused``) or as two launches.  ``skip_reduce``: ``sums`` already
+    holds the reduction (``conv_dgrad_bn_reduce`` of the block above produced it), only apply."""
     B, H, W, C = y.shape
+    if skip_reduce:
+        call("b200dp_bn_relu_pool_bwd_apply", ptr(y), ptr(dout), ptr(mean), ptr(invstd), ptr(gamma), ptr(beta),
+             ptr(sums), ptr(dy), ptr(dgamma), ptr(dbeta), B, H, W, C, int(pool), stream_ptr())
+        return dy
     if (BN_BWD_FUSED or y.numel() <= BN_BWD_FUSED_MAX_ELEMS) if fused is None else fused:
         call("b200dp_bn_relu_pool_bwd_fused", ptr(y), ptr(dout), ptr(mean), ptr(invstd), ptr(gamma), ptr(beta),
              ptr(sums), ptr(dy), ptr(dgamma), ptr(dbeta), B, H, W, C, int(pool), stream_ptr())

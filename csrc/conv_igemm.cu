@@ -51,6 +51,14 @@ struct IgemmParams {
   // 1: the four epilogue warps combine their statistics in shared memory (the drained stage-0 operand
   // buffer) and issue one atomic per channel per CTA instead of one per warp (B200DP_STATS_SMEM=0: off)
   int stats_via_smem;
+  // dgrad only (conv_dgrad_bnr kernels): the tile just computed is dL/da for a = relu(bn(z)) of the
+  // PREVIOUS block (max-pooled or not).  With `bnr_a` = that block's stored output, the epilogue also
+  // accumulates its BatchNorm-backward sums  S1 = sum_{a>0} g,  S2 = sum_{a>0} g*(a-beta)/gamma  into
+  // bnr_sums[0..N) / [N..2N) -- what bn_bwd_reduce_from_out_kernel computes in a separate pass.
+  const __nv_bfloat16* bnr_a;
+  const float* bnr_gamma;
+  const float* bnr_beta;
+  float* bnr_sums;
 };
 
 // Sum v[j] over the 32 lanes of the warp for every j; lane l returns the total of column l.
@@ -76,7 +84,7 @@ B200DP_DEVINL void red_add_v4(float* addr, float a, float b, float c, float d) {
 
 // Epilogue shared by the 1-CTA and 2-CTA kernels: TMEM -> registers -> (+bias, bf16, statistics) -> global,
 // or fp32 red.add into the split-K workspace.  Warp w may only touch TMEM lanes [32*(w%4), 32*(w%4)+32).
-template <int BLOCK_N>
+template <int BLOCK_N, bool BNR = false>
 B200DP_DEVINL void igemm_epilogue(const IgemmParams& p, uint32_t tmem_base, uint64_t* tmem_full_bar, int warp,
                                   int lane, int m_tile, int n_tile, float* scratch) {
   // Epilogue: warp w may only touch TMEM lanes [32*(w%4), 32*(w%4)+32).
@@ -91,6 +99,14 @@ B200DP_DEVINL void igemm_epilogue(const IgemmParams& p, uint32_t tmem_base, uint
   for (int c = 0; c < BLOCK_N; c += 32) {
     uint32_t v[32];
     tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + c, v);
+    uint4 act[4];
+    if constexpr (BNR) {
+      // the previous block's output row, same [M][N] layout as the gradient being written; in flight
+      // while the TMEM load completes
+      const uint4* a_row = reinterpret_cast<const uint4*>(p.bnr_a + m * p.n_total + n_tile * BLOCK_N + c);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) act[j] = (valid && p.partial == nullptr) ? __ldg(a_row + j) : make_uint4(0u, 0u, 0u, 0u);
+    }
     tmem_ld_wait();
     if (p.partial != nullptr) {
       if (valid) {
@@ -119,7 +135,30 @@ B200DP_DEVINL void igemm_epilogue(const IgemmParams& p, uint32_t tmem_base, uint
       for (int j = 0; j < 4; ++j)
         dst[j] = make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
     }
-    if (p.stats != nullptr) {
+    if constexpr (BNR) {
+      // T1 = sum_{a>0} g and T2 = sum_{a>0} g*a over the 32 rows of this warp; beta and gamma enter once
+      // per channel afterwards: S2 = (T2 - beta*T1) / gamma.  g is the value as stored (bf16-rounded).
+      const uint32_t aw[16] = {act[0].x, act[0].y, act[0].z, act[0].w, act[1].x, act[1].y, act[1].z, act[1].w,
+                               act[2].x, act[2].y, act[2].z, act[2].w, act[3].x, act[3].y, act[3].z, act[3].w};
+      float s1[32], s2[32];
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const float2 g = unpack_bf16x2(packed[j]);
+        const float2 a = unpack_bf16x2(aw[j]);
+        s1[2 * j] = (valid && a.x > 0.f) ? g.x : 0.f;
+        s1[2 * j + 1] = (valid && a.y > 0.f) ? g.y : 0.f;
+        s2[2 * j] = s1[2 * j] * a.x;
+        s2[2 * j + 1] = s1[2 * j + 1] * a.y;
+      }
+      const float t1 = warp_transpose_sum(s1, lane);
+      const float t2 = warp_transpose_sum(s2, lane);
+      const int ch = n_tile * BLOCK_N + c + lane;
+      const float gam = __ldg(p.bnr_gamma + ch);
+      const float ig = fabsf(gam) > 1e-20f ? 1.f / gam : 0.f;
+      const float u2 = (t2 - __ldg(p.bnr_beta + ch) * t1) * ig;
+      scratch[q * 2 * BLOCK_N + c + lane] = t1;
+      scratch[q * 2 * BLOCK_N + BLOCK_N + c + lane] = u2;
+    } else if (p.stats != nullptr) {
       // statistics of the values as stored (bf16-rounded), so that the
       // normalisation that follows is exactly centred on what it reads.
       float s1[32], s2[32];
@@ -144,7 +183,16 @@ B200DP_DEVINL void igemm_epilogue(const IgemmParams& p, uint32_t tmem_base, uint
       }
     }
   }
-  if (p.partial == nullptr && p.stats != nullptr && p.stats_via_smem) {
+  if constexpr (BNR) {
+    if (p.partial == nullptr) {
+      asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps only
+      for (int i = static_cast<int>(threadIdx.x) - 64; i < 2 * BLOCK_N; i += 128) {
+        const float t = scratch[i] + scratch[2 * BLOCK_N + i] + scratch[4 * BLOCK_N + i] + scratch[6 * BLOCK_N + i];
+        const int half = i / BLOCK_N;
+        atomicAdd(p.bnr_sums + half * p.n_total + n_tile * BLOCK_N + (i - half * BLOCK_N), t);
+      }
+    }
+  } else if (p.partial == nullptr && p.stats != nullptr && p.stats_via_smem) {
     asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps only
     for (int i = static_cast<int>(threadIdx.x) - 64; i < 2 * BLOCK_N; i += 128) {
       const float t = scratch[i] + scratch[2 * BLOCK_N + i] + scratch[4 * BLOCK_N + i] + scratch[6 * BLOCK_N + i];
@@ -158,10 +206,8 @@ B200DP_DEVINL void igemm_epilogue(const IgemmParams& p, uint32_t tmem_base, uint
 // STAGES == 1 is the single-K-block case (layer 0: one 64-wide K block per tile).  Such a CTA is a pure
 // latency chain (TMA -> one MMA group -> epilogue), so it is compiled for 5 CTAs per SM (25 KiB of
 // shared memory, 64 TMEM columns each) instead of the 2 that a 4-stage ring allows.
-template <int BLOCK_N, int STAGES>
-__global__ void __launch_bounds__(kNumThreads, STAGES == 1 ? 5 : 1)
-    conv_igemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                      const IgemmParams p) {
+template <int BLOCK_N, int STAGES, bool BNR>
+B200DP_DEVINL void conv_igemm_body(const CUtensorMap& tmA, const CUtensorMap& tmB, const IgemmParams& p) {
   constexpr int kBStageBytes = BLOCK_N * kBlockK * 2;
   constexpr int kStageBytes = kAStageBytes + kBStageBytes;
   constexpr uint32_t kTmemCols = BLOCK_N < 32 ? 32 : BLOCK_N;
@@ -261,13 +307,28 @@ __global__ void __launch_bounds__(kNumThreads, STAGES == 1 ? 5 : 1)
       umma_commit(tmem_full_bar);
     }
   } else {
-    igemm_epilogue<BLOCK_N>(p, tmem_base, tmem_full_bar, warp, lane, m_tile, n_tile, reinterpret_cast<float*>(smem));
+    igemm_epilogue<BLOCK_N, BNR>(p, tmem_base, tmem_full_bar, warp, lane, m_tile, n_tile, reinterpret_cast<float*>(smem));
   }
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, kTmemCols);
   }
+}
+
+template <int BLOCK_N, int STAGES>
+__global__ void __launch_bounds__(kNumThreads, STAGES == 1 ? 5 : 1)
+    conv_igemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                      const IgemmParams p) {
+  conv_igemm_body<BLOCK_N, STAGES, false>(tmA, tmB, p);
+}
+
+// dgrad whose epilogue also accumulates the previous block's BatchNorm-backward sums (IgemmParams::bnr_*)
+template <int BLOCK_N, int STAGES>
+__global__ void __launch_bounds__(kNumThreads)
+    conv_dgrad_bnr_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                          const IgemmParams p) {
+  conv_igemm_body<BLOCK_N, STAGES, true>(tmA, tmB, p);
 }
 
 // ---------------------------------------------------------------------------
@@ -281,10 +342,8 @@ __global__ void __launch_bounds__(kNumThreads, STAGES == 1 ? 5 : 1)
 // with a cluster multicast to the empty / tmem-full barriers of both CTAs; each CTA drains its own
 // TMEM half in its epilogue warps.
 // ---------------------------------------------------------------------------
-template <int BLOCK_N, int STAGES>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads)
-    conv_igemm_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                           const IgemmParams p) {
+template <int BLOCK_N, int STAGES, bool BNR>
+B200DP_DEVINL void conv_igemm_2cta_body(const CUtensorMap& tmA, const CUtensorMap& tmB, const IgemmParams& p) {
   constexpr int kBHalfBytes = (BLOCK_N / 2) * kBlockK * 2;
   constexpr int kStageBytes = kAStageBytes + kBHalfBytes;
   constexpr uint32_t kTmemCols = BLOCK_N < 32 ? 32 : BLOCK_N;
@@ -386,7 +445,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads)
       umma_commit_2cta(tmem_full_bar, 0b11);
     }
   } else {
-    igemm_epilogue<BLOCK_N>(p, tmem_base, tmem_full_bar, warp, lane, m_tile, n_tile, reinterpret_cast<float*>(smem));
+    igemm_epilogue<BLOCK_N, BNR>(p, tmem_base, tmem_full_bar, warp, lane, m_tile, n_tile, reinterpret_cast<float*>(smem));
   }
   __syncthreads();
   tc_fence_before();
@@ -395,6 +454,20 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads)
     tc_fence_after();
     tmem_dealloc_2cta(tmem_base, kTmemCols);
   }
+}
+
+template <int BLOCK_N, int STAGES>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads)
+    conv_igemm_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                           const IgemmParams p) {
+  conv_igemm_2cta_body<BLOCK_N, STAGES, false>(tmA, tmB, p);
+}
+
+template <int BLOCK_N, int STAGES>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads)
+    conv_dgrad_bnr_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                               const IgemmParams p) {
+  conv_igemm_2cta_body<BLOCK_N, STAGES, true>(tmA, tmB, p);
 }
 
 // Split-K epilogue: partial fp32 [M][N] -> (+bias) -> bf16 out, fused BatchNorm statistics of the
@@ -459,6 +532,72 @@ __global__ void __launch_bounds__(256) splitk_finalize_kernel(float* __restrict_
       atomicAdd(stats + c, a);
       atomicAdd(stats + N + c, t);
     }
+  }
+}
+
+// Split-K epilogue of a dgrad that also feeds the previous block's BatchNorm backward: partial fp32
+// [M][N] -> bf16 dL/da, workspace cleared, and S1 / S2 of IgemmParams::bnr_* from the rounded values.
+__global__ void __launch_bounds__(256) splitk_finalize_bnr_kernel(float* __restrict__ partial,
+                                                                  __nv_bfloat16* __restrict__ out,
+                                                                  const __nv_bfloat16* __restrict__ act,
+                                                                  const float* __restrict__ gamma,
+                                                                  const float* __restrict__ beta,
+                                                                  float* __restrict__ sums, long M, int N) {
+  extern __shared__ float red[];  // [rows_per_block][N] x 2
+  pdl_launch_dependents();
+  pdl_wait();
+  const int chunks = N / 8;
+  const int rows_per_block = blockDim.x / chunks;
+  const int chunk = threadIdx.x % chunks, rl = threadIdx.x / chunks, c0 = chunk * 8;
+  float s1[8], s2[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s1[j] = s2[j] = 0.f;
+  if (rl < rows_per_block) {
+    for (long r = static_cast<long>(blockIdx.x) * rows_per_block + rl; r < M;
+         r += static_cast<long>(gridDim.x) * rows_per_block) {
+      float4* src = reinterpret_cast<float4*>(partial + r * N + c0);
+      const float4 lo = src[0], hi = src[1];
+      const uint4 a = __ldg(reinterpret_cast<const uint4*>(act + r * N + c0));
+      src[0] = make_float4(0.f, 0.f, 0.f, 0.f);
+      src[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+      uint4 o;
+      o.x = pack_bf16x2(lo.x, lo.y);
+      o.y = pack_bf16x2(lo.z, lo.w);
+      o.z = pack_bf16x2(hi.x, hi.y);
+      o.w = pack_bf16x2(hi.z, hi.w);
+      *reinterpret_cast<uint4*>(out + r * N + c0) = o;
+      const float2 g0 = unpack_bf16x2(o.x), g1 = unpack_bf16x2(o.y), g2 = unpack_bf16x2(o.z), g3 = unpack_bf16x2(o.w);
+      const float2 a0 = unpack_bf16x2(a.x), a1 = unpack_bf16x2(a.y), a2 = unpack_bf16x2(a.z), a3 = unpack_bf16x2(a.w);
+      const float g[8] = {g0.x, g0.y, g1.x, g1.y, g2.x, g2.y, g3.x, g3.y};
+      const float av[8] = {a0.x, a0.y, a1.x, a1.y, a2.x, a2.y, a3.x, a3.y};
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float d = av[j] > 0.f ? g[j] : 0.f;
+        s1[j] += d;
+        s2[j] = fmaf(d, av[j], s2[j]);
+      }
+    }
+  }
+  float* r1 = red;
+  float* r2 = red + rows_per_block * N;
+  if (rl < rows_per_block) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      r1[rl * N + c0 + j] = s1[j];
+      r2[rl * N + c0 + j] = s2[j];
+    }
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < N; c += blockDim.x) {
+    float t1 = 0.f, t2 = 0.f;
+    for (int r = 0; r < rows_per_block; ++r) {
+      t1 += r1[r * N + c];
+      t2 += r2[r * N + c];
+    }
+    const float gam = gamma[c];
+    const float ig = fabsf(gam) > 1e-20f ? 1.f / gam : 0.f;
+    atomicAdd(sums + c, t1);
+    atomicAdd(sums + N + c, (t2 - beta[c] * t1) * ig);
   }
 }
 
@@ -744,6 +883,36 @@ static int launch_igemm_2cta(const CUtensorMap& tmA, const CUtensorMap& tmB, con
 }
 
 template <int BLOCK_N, int STAGES>
+static int launch_dgrad_bnr(const CUtensorMap& tmA, const CUtensorMap& tmB, const IgemmParams& p, int m_tiles,
+                            int splits, cudaStream_t stream) {
+  constexpr int smem = STAGES * (kAStageBytes + BLOCK_N * kBlockK * 2) + 1024 + 256;
+  static bool configured = false;
+  auto kern = conv_dgrad_bnr_kernel<BLOCK_N, STAGES>;
+  if (!configured) {
+    B200DP_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured = true;
+  }
+  dim3 grid(m_tiles, p.n_total / BLOCK_N, splits);
+  B200DP_CUDA_TRY(launch_pdl(kern, grid, dim3(kNumThreads), smem, stream, tmA, tmB, p));
+  return 0;
+}
+
+template <int BLOCK_N, int STAGES>
+static int launch_dgrad_bnr_2cta(const CUtensorMap& tmA, const CUtensorMap& tmB, const IgemmParams& p, int m_tiles,
+                                 int splits, cudaStream_t stream) {
+  constexpr int smem = STAGES * (kAStageBytes + (BLOCK_N / 2) * kBlockK * 2) + 1024 + 256;
+  static bool configured = false;
+  auto kern = conv_dgrad_bnr_2cta_kernel<BLOCK_N, STAGES>;
+  if (!configured) {
+    B200DP_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured = true;
+  }
+  dim3 grid(m_tiles, p.n_total / BLOCK_N, splits);
+  B200DP_CUDA_TRY(launch_pdl(kern, grid, dim3(kNumThreads), smem, stream, tmA, tmB, p));
+  return 0;
+}
+
+template <int BLOCK_N, int STAGES>
 static int launch_wgrad(const CUtensorMap& tmDY, const CUtensorMap& tmX, const WgradParams& p, int tiles,
                         int splits, cudaStream_t stream) {
   constexpr int smem = STAGES * (2 * 8192 + (BLOCK_N / 64) * 8192) + 1024 + 256;
@@ -762,9 +931,17 @@ static int launch_wgrad(const CUtensorMap& tmDY, const CUtensorMap& tmX, const W
 
 using namespace b200dp;
 
+// Optional second job of a dgrad launch: BatchNorm-backward sums of the block that produced `act_out`.
+struct BnReduceArgs {
+  const void* act_out;
+  const float* gamma;
+  const float* beta;
+  float* sums;
+};
+
 static int conv_igemm_impl(const void* act, const void* wgt, const float* bias, void* out, float* stats,
                            float* workspace, int B, int H, int W, int Cin, int Cout, int taps, int block_n, int split_k,
-                           int cta_pair, cudaStream_t stream) {
+                           int cta_pair, cudaStream_t stream, const BnReduceArgs* bnr = nullptr) {
   if ((taps != 9 && taps != 1) || Cin % 64 != 0 || Cout % 32 != 0 || B <= 0) {
     set_error("conv_igemm: unsupported shape B=%d H=%d W=%d Cin=%d Cout=%d taps=%d", B, H, W, Cin, Cout, taps);
     return B200DP_EINVAL;
@@ -837,6 +1014,43 @@ static int conv_igemm_impl(const void* act, const void* wgt, const float* bias, 
     if (rc) return rc;
   }
   int rc;
+  if (bnr != nullptr) {
+    if (bias != nullptr || stats != nullptr || Cout % 32 != 0) {
+      set_error("conv_dgrad_bn_reduce: bias / forward statistics cannot be combined with the BatchNorm-backward sums");
+      return B200DP_EINVAL;
+    }
+    p.bnr_a = static_cast<const __nv_bfloat16*>(bnr->act_out);
+    p.bnr_gamma = bnr->gamma;
+    p.bnr_beta = bnr->beta;
+    p.bnr_sums = bnr->sums;
+    if (cta_pair) {
+      switch (block_n) {
+        case 256: rc = launch_dgrad_bnr_2cta<256, 6>(tmA, tmB, p, m_tiles, split_k, stream); break;
+        case 128: rc = launch_dgrad_bnr_2cta<128, 6>(tmA, tmB, p, m_tiles, split_k, stream); break;
+        case 64: rc = launch_dgrad_bnr_2cta<64, 6>(tmA, tmB, p, m_tiles, split_k, stream); break;
+        default: set_error("conv_dgrad_bn_reduce: block_n=%d not in {64,128,256} for the CTA-pair kernel", block_n); return B200DP_EINVAL;
+      }
+    } else {
+      switch (block_n) {
+        case 256: rc = launch_dgrad_bnr<256, 4>(tmA, tmB, p, m_tiles, split_k, stream); break;
+        case 128: rc = launch_dgrad_bnr<128, 3>(tmA, tmB, p, m_tiles, split_k, stream); break;
+        case 64: rc = launch_dgrad_bnr<64, 4>(tmA, tmB, p, m_tiles, split_k, stream); break;
+        case 32: rc = launch_dgrad_bnr<32, 4>(tmA, tmB, p, m_tiles, split_k, stream); break;
+        default: set_error("conv_dgrad_bn_reduce: block_n=%d not in {32,64,128,256}", block_n); return B200DP_EINVAL;
+      }
+    }
+    if (rc || split_k == 1) return rc;
+    const int threads = 256;
+    const int rows_per_block = threads / (Cout / 8);
+    const size_t smem = 2 * rows_per_block * Cout * sizeof(float);
+    long blocks = (static_cast<long>(p.m_total) + rows_per_block * 2 - 1) / (rows_per_block * 2);
+    if (blocks > 148 * 4) blocks = 148 * 4;
+    if (blocks < 1) blocks = 1;
+    B200DP_CUDA_TRY(launch_pdl(splitk_finalize_bnr_kernel, dim3(static_cast<unsigned>(blocks)), dim3(threads), smem,
+                               stream, workspace, static_cast<__nv_bfloat16*>(out), p.bnr_a, p.bnr_gamma, p.bnr_beta,
+                               p.bnr_sums, static_cast<long>(p.m_total), Cout));
+    return 0;
+  }
   if (cta_pair) {
     switch (block_n) {
       case 256: rc = launch_igemm_2cta<256, 6>(tmA, tmB, p, m_tiles, split_k, stream); break;
@@ -890,6 +1104,26 @@ extern "C" int b200dp_conv_igemm_pair(const void* act, const void* wgt, const fl
                                       int block_n, int split_k, b200dp_stream_t stream_) {
   return conv_igemm_impl(act, wgt, bias, out, stats, workspace, B, H, W, Cin, Cout, taps, block_n, split_k, 1,
                          static_cast<cudaStream_t>(stream_));
+}
+
+/* Data gradient of a 3x3 conv (act = dY, wgt = tap-flipped transposed weights, as for the other entry
+ * points) that ALSO accumulates the BatchNorm-backward sums of the block below it: `bn_out` is that
+ * block's stored output a = relu(bn(z)) (max-pooled or not), same [B,H,W,Cout] shape as `out`; on return
+ * sums[0..Cout) += sum_{a>0} g and sums[Cout..2Cout) += sum_{a>0} g*(a-beta)/gamma with g the gradient just
+ * written to `out` -- the contract of b200dp_bn_relu_pool_bwd_reduce_from_out, without its extra pass.
+ * cta_pair / split_k / workspace as for b200dp_conv_igemm_pair / _splitk.  Experimental: off by default
+ * in the executor (B200DP_DGRAD_BN_REDUCE=1). */
+extern "C" int b200dp_conv_dgrad_bn_reduce(const void* act, const void* wgt, void* out, float* workspace,
+                                           const void* bn_out, const float* gamma, const float* beta, float* sums,
+                                           int B, int H, int W, int Cin, int Cout, int taps, int block_n, int split_k,
+                                           int cta_pair, b200dp_stream_t stream_) {
+  if (bn_out == nullptr || gamma == nullptr || beta == nullptr || sums == nullptr) {
+    set_error("conv_dgrad_bn_reduce: bn_out, gamma, beta and sums are required");
+    return B200DP_EINVAL;
+  }
+  const BnReduceArgs bnr{bn_out, gamma, beta, sums};
+  return conv_igemm_impl(act, wgt, nullptr, out, nullptr, workspace, B, H, W, Cin, Cout, taps, block_n, split_k,
+                         cta_pair, static_cast<cudaStream_t>(stream_), &bnr);
 }
 
 static int conv_wgrad_impl(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin, int Cout, int taps,

@@ -72,6 +72,18 @@ int b200dp_conv_igemm_pair(const void* act, const void* wgt, const float* bias, 
                            float* workspace, int B, int H, int W, int Cin, int Cout, int taps, int block_n,
                            int split_k, b200dp_stream_t stream);
 
+/* Data gradient that also produces the BatchNorm-backward sums of the block below it.  act = dY of
+ * this conv, wgt = its tap-flipped transposed weights, out = dL/da for the previous block's output
+ * a = relu(bn(z)) (max-pooled or not).  bn_out is that stored output (same [B,H,W,Cout] shape as out);
+ * on return  sums[0..Cout) += sum_{a>0} g  and  sums[Cout..2Cout) += sum_{a>0} g*(a-beta)/gamma  with g
+ * the gradient just written -- exactly what b200dp_bn_relu_pool_bwd_reduce_from_out computes, fused into
+ * the GEMM epilogue (split_k > 1: into the finalize kernel).  No bias, no forward statistics.
+ * block_n in {32,64,128,256} ({64,128,256} with cta_pair); workspace as for b200dp_conv_igemm_splitk.
+ * Experimental in round 1: the executor uses it only with B200DP_DGRAD_BN_REDUCE=1. */
+int b200dp_conv_dgrad_bn_reduce(const void* act, const void* wgt, void* out, float* workspace, const void* bn_out,
+                                const float* gamma, const float* beta, float* sums, int B, int H, int W, int Cin,
+                                int Cout, int taps, int block_n, int split_k, int cta_pair, b200dp_stream_t stream);
+
 /* dW[Cout][taps][cin_valid] (fp32) += sum over pixels dY[p][Cout] * X[p + tap][Cin].
  * dy: bf16 [B,H,W,Cout]; x: bf16 [B,H,W,Cin].  Both operands are consumed
  * MN-major straight from their NHWC layout.  split_k = 0 chooses a split that

@@ -1,0 +1,101 @@
+"""Kernels written at the end of round 1 after the GPU budget was spent: compiled, SASS-checked, not yet
+run on hardware.  They are off by default in the executor; these tests are their acceptance checks and
+run only with ``B200DP_EXPERIMENTAL=1`` so that an unvalidated path cannot turn the suite red.
+
+    B200DP_EXPERIMENTAL=1 python -m pytest tests/test_gpu_experimental.py -m gpu -x -q
+"""
+import os
+
+import pytest
+import torch
+
+pytestmark = [pytest.mark.gpu,
+              pytest.mark.skipif(os.environ.get("B200DP_EXPERIMENTAL", "0") == "0",
+                                 reason="experimental kernels: set B200DP_EXPERIMENTAL=1")]
+
+DEV = "cuda"
+
+
+def _native():
+    from cs744_pytorch_distributed_tutorial_b200.ops import native
+    return native
+
+
+# (B, H, W, C_dy = Cout of the conv, C_prev = Cin of the conv = channels of the block below)
+DGRAD_SHAPES = [
+    (32, 16, 16, 128, 64),
+    (32, 8, 8, 256, 128),
+    (32, 8, 8, 256, 256),
+    (32, 4, 4, 512, 256),
+    (32, 4, 4, 512, 512),
+    (32, 2, 2, 512, 512),
+    (30, 2, 2, 512, 512),    # last 128-row tile only partly valid
+]
+
+
+@pytest.mark.parametrize("shape", DGRAD_SHAPES)
+@pytest.mark.parametrize("cfg", [(0, 1, False), (32, 1, False), (64, 1, False), (128, 1, False), (256, 1, False),
+                                 (64, 1, True), (128, 1, True), (256, 1, True), (64, 3, False), (128, 4, True)])
+def test_dgrad_with_bn_reduce_matches_the_two_pass_path(shape, cfg):
+    """Same dL/da bits as the plain dgrad kernel, and the same sums as bn_bwd_reduce_from_out on it."""
+    native = _native()
+    from cs744_pytorch_distributed_tutorial_b200.ops._lib import call, ptr, stream_ptr
+    B, H, W, C, Cp = shape
+    block_n, split_k, pair = cfg
+    if block_n and Cp % block_n:
+        pytest.skip("block_n does not divide the channel count")
+    m_tiles = (B * H * W + 127) // 128
+    if pair and m_tiles % 2:
+        pytest.skip("the CTA-pair kernel needs an even number of tiles")
+    g = torch.Generator(device=DEV).manual_seed(11)
+    dy = torch.randn(B, H, W, C, device=DEV, generator=g).bfloat16()
+    wd = (torch.randn(Cp, 9 * C, device=DEV, generator=g) / (3 * C ** 0.5)).bfloat16()
+    a = torch.relu(torch.randn(B, H, W, Cp, device=DEV, generator=g)).bfloat16()   # about half zeros
+    gamma = torch.rand(Cp, device=DEV, generator=g) + 0.5
+    gamma[0] = 0.0                                                                   # guarded division
+    beta = torch.randn(Cp, device=DEV, generator=g) * 0.1
+    ws = torch.zeros(B * H * W * Cp, device=DEV)
+
+    ref = torch.empty(B, H, W, Cp, device=DEV, dtype=torch.bfloat16)
+    native.conv_igemm(dy, wd, None, ref, block_n=block_n, split_k=split_k, cta_pair=pair, workspace=ws)
+    sums_ref = torch.zeros(2 * Cp, device=DEV)
+    call("b200dp_bn_relu_pool_bwd_reduce_from_out", ptr(a), ptr(ref), ptr(gamma), ptr(beta), ptr(sums_ref),
+         B * H * W, Cp, stream_ptr())
+
+    out = torch.full_like(ref, float("nan"))
+    sums = torch.zeros(2 * Cp, device=DEV)
+    native.conv_dgrad_bn_reduce(dy, wd, out, a, gamma, beta, sums, block_n=block_n, split_k=split_k,
+                                workspace=ws, cta_pair=pair)
+    torch.cuda.synchronize()
+    if split_k == 1:
+        assert torch.equal(out, ref)
+    else:   # fp32 atomics: order-dependent last bit before the bf16 rounding
+        assert ((out.float() - ref.float()).norm() / ref.float().norm()).item() < 2e-3
+    assert float(ws.abs().max()) == 0.0          # split-K workspace handed back clean
+    scale = sums_ref.abs().max().item() + 1e-6
+    assert (sums - sums_ref).abs().max().item() < 2e-3 * scale, (sums[:8], sums_ref[:8])
+    assert sums[Cp].item() == 0.0                # gamma == 0 channel contributes nothing to S2
+
+
+def test_training_step_with_fused_dgrad_reduction_matches_the_default(monkeypatch):
+    """Whole backward with B200DP_DGRAD_BN_REDUCE on vs off: same gradients up to atomics ordering."""
+    from cs744_pytorch_distributed_tutorial_b200.models import native_vgg
+    from cs744_pytorch_distributed_tutorial_b200.models.vgg import VGG
+    torch.manual_seed(0)
+    x = torch.randn(64, 3, 32, 32, device=DEV)
+    y = torch.randint(0, 10, (64,), device=DEV)
+    grads = []
+    for flag in (False, True):
+        monkeypatch.setattr(native_vgg, "DGRAD_BN_REDUCE", flag)
+        torch.manual_seed(1)
+        model = VGG("VGG11").to(DEV)
+        nv = model.enable_native(max_batch=64)
+        nv.forward(x, training=True)
+        nv.loss_fwd_bwd(y)
+        nv.backward()
+        torch.cuda.synchronize()
+        grads.append(nv.flat_grads.clone())
+    a, b = grads
+    cos = torch.nn.functional.cosine_similarity(a, b, dim=0).item()
+    assert cos > 0.9995, cos
+    assert ((a - b).norm() / b.norm()).item() < 2e-2

@@ -41,6 +41,8 @@ _lib.declare("b200dp_broadcast", [P, LL, LL, I, I, I, P])
 _lib.declare("b200dp_reducer_create", [P, I, POINTER(c_longlong), POINTER(c_longlong), LL, LL, LL, I, I, F, F, F,
                                        I, I, POINTER(c_void_p)])
 _lib.declare("b200dp_reducer_set_lr", [P, F])
+_lib.declare("b200dp_reducer_stream", [P, POINTER(c_void_p)])
+_lib.declare("b200dp_reducer_set_blocks", [P, I])
 _lib.declare("b200dp_reducer_bucket_ready", [P, I, P])
 _lib.declare("b200dp_reducer_finalize", [P, P])
 _lib.declare("b200dp_reducer_destroy", [P])
@@ -218,6 +220,17 @@ class BucketReducer:
 
     def set_lr(self, lr: float) -> None:
         call("b200dp_reducer_set_lr", self._h, lr)
+
+    def set_blocks(self, blocks: int) -> None:
+        """CTAs per bucket collective from the next ``bucket_ready`` on (re-capture the step afterwards)."""
+        call("b200dp_reducer_set_blocks", self._h, int(blocks))
+
+    def stream(self, device) -> torch.cuda.Stream:
+        """The reducer's side stream as a torch stream: kernels queued on it after ``bucket_ready(k)``
+        run behind bucket k's collective and are joined by ``finalize``."""
+        s = c_void_p()
+        call("b200dp_reducer_stream", self._h, byref(s))
+        return torch.cuda.ExternalStream(s.value, device=device)
 
     def close(self) -> None:
         if self._h is not None:

@@ -195,6 +195,33 @@ class BucketedOverlapSync(NativeSync):
                                      prescale=True, blocks=blocks, channel=CH_BUCKET)
         nv.on_bucket_ready = self.reducer.bucket_ready
         self.launch_log = []
+        # Experimental (B200DP_PART3_PREP_OVERLAP=1, not yet run on hardware): the fused collective of a
+        # bucket leaves new fp32 weights behind; re-lay the bf16 copies of the deep blocks (95 % of the
+        # bytes) on the reducer's stream right behind the bucket that completes them instead of after
+        # finalize().  Same two-phase split as LocalSGD.
+        import os
+        from ..models.native_vgg import WGRAD_ON_SIDE_STREAM
+        self._prep_overlap = (os.environ.get("B200DP_PART3_PREP_OVERLAP", "0") != "0" and fuse
+                              and bucket_plan == "layer" and WGRAD_ON_SIDE_STREAM and len(nv.blocks) > 2)
+        if self._prep_overlap:
+            n = len(nv.blocks)
+            self.first_block = max(n - 5, 1)
+            self.split_bucket = max(k for k in range(len(self.buckets)) if self.first_block in nv.blocks_of_bucket(k))
+            spec = lambda b: (b.w_master, b.wf, b.wd, b.spec.cout, b.spec.cin, 9, b.taps * b.kin)
+            self._prep_hi = K.BatchedWeightPrep([spec(b) for b in nv.blocks[self.first_block:] if not b.direct])
+            self._prep_lo = K.BatchedWeightPrep([spec(b) for b in nv.blocks[:self.first_block] if not b.direct])
+            self._reducer_stream = self.reducer.stream(nv.device)
+            self.handles_shadows = True
+            nv.on_bucket_ready = self._bucket_ready
+
+    def _bucket_ready(self, k: int) -> None:
+        self.reducer.bucket_ready(k)
+        if k == self.split_bucket:
+            # buckets 0..k (every block >= first_block) have been queued on the reducer stream; the data
+            # gradient of first_block is the last reader of the old bf16 copies of those blocks
+            with torch.cuda.stream(self._reducer_stream):
+                self._reducer_stream.wait_event(self.native._dgrad_done[self.first_block])
+                self._prep_hi()
 
     def on_init(self) -> None:
         # DDP constructor: replicas start identical to rank 0
@@ -239,6 +266,8 @@ class BucketedOverlapSync(NativeSync):
         self.reducer.finalize()
         if not self.fuse_optimizer:
             self._local_sgd()
+        if self._prep_overlap:
+            self._prep_lo()
 
     def close(self) -> None:
         self.native.on_bucket_ready = None

@@ -972,6 +972,26 @@ extern "C" int b200dp_reducer_set_lr(void* reducer, float lr) {
   return 0;
 }
 
+/* The reducer's side stream (a cudaStream_t), so that the caller can queue work behind a bucket's
+ * collective -- e.g. the bf16 re-layout of the weights that bucket just updated. */
+extern "C" int b200dp_reducer_stream(void* reducer, void** stream_out) {
+  auto* r = static_cast<Reducer*>(reducer);
+  if (!r || !stream_out) return B200DP_EINVAL;
+  *stream_out = r->side;
+  return 0;
+}
+
+/* CTAs per bucket collective from the next bucket_ready() on (takes effect when the step is re-captured). */
+extern "C" int b200dp_reducer_set_blocks(void* reducer, int blocks) {
+  auto* r = static_cast<Reducer*>(reducer);
+  if (!r || blocks < 1) {
+    set_error("reducer_set_blocks: need a reducer and blocks >= 1");
+    return B200DP_EINVAL;
+  }
+  r->blocks = blocks;
+  return 0;
+}
+
 extern "C" int b200dp_reducer_bucket_ready(void* reducer, int k, b200dp_stream_t compute_stream) {
   auto* r = static_cast<Reducer*>(reducer);
   if (!r || k < 0 || k >= static_cast<int>(r->ready.size())) {

@@ -264,6 +264,11 @@ int b200dp_reducer_set_lr(void* reducer, float lr);
 int b200dp_reducer_bucket_ready(void* reducer, int bucket, b200dp_stream_t compute_stream);
 int b200dp_reducer_finalize(void* reducer, b200dp_stream_t compute_stream);
 int b200dp_reducer_destroy(void* reducer);
+/* The reducer's side stream (cudaStream_t): work queued on it after bucket_ready(k) runs behind bucket
+ * k's collective and is joined by finalize(). */
+int b200dp_reducer_stream(void* reducer, void** stream_out);
+/* CTAs per bucket collective for subsequent bucket_ready() calls (re-capture the step afterwards). */
+int b200dp_reducer_set_blocks(void* reducer, int blocks);
 
 #ifdef __cplusplus
 }

@@ -99,3 +99,33 @@ def test_training_step_with_fused_dgrad_reduction_matches_the_default(monkeypatc
     cos = torch.nn.functional.cosine_similarity(a, b, dim=0).item()
     assert cos > 0.9995, cos
     assert ((a - b).norm() / b.norm()).item() < 2e-2
+
+
+def test_part3_weight_relayout_behind_the_buckets(monkeypatch):
+    """B200DP_PART3_PREP_OVERLAP=1: after a few captured part3 steps (collective kernels alive on one rank)
+    the bf16 operand copies must be exactly the re-layout of the current fp32 weights."""
+    monkeypatch.setenv("B200DP_PART3_PREP_OVERLAP", "1")
+    from cs744_pytorch_distributed_tutorial_b200.config import TrainConfig
+    from cs744_pytorch_distributed_tutorial_b200.engine import Trainer
+    cfg = TrainConfig(mode="part3", device="cuda", per_rank_batch=64, eval=False, lr=0.01,
+                      single_rank_collectives=True)
+    tr = Trainer(cfg)
+    try:
+        assert tr.backend.sync._prep_overlap and tr.backend.sync.handles_shadows
+        g = torch.Generator().manual_seed(5)
+        for _ in range(3):
+            x = torch.randn(64, 3, 32, 32, generator=g).pin_memory()
+            y = torch.randint(0, 10, (64,), generator=g).pin_memory()
+            loss = tr.train_step(x, y)
+        torch.cuda.synchronize()
+        assert torch.isfinite(loss).item()
+        nv = tr.backend.native
+        got = [(b.wf.clone(), None if b.wd is None else b.wd.clone()) for b in nv.blocks]
+        nv.refresh_shadows()
+        torch.cuda.synchronize()
+        for b, (wf, wd) in zip(nv.blocks, got):
+            assert torch.equal(b.wf, wf)
+            if wd is not None:
+                assert torch.equal(b.wd, wd)
+    finally:
+        tr.close()

@@ -180,6 +180,8 @@ class NativeBackend:
                 self.comm = Communicator(self.store, cfg.rank, W, device.index or 0, heap_bytes, timeout_s=cfg.timeout_s)
             heap = self.comm
         self.native = model.enable_native(max_batch=B, heap=heap)
+        from .models.native_vgg import HEAD_FUSED
+        self.native.defer_head = HEAD_FUSED   # this backend always calls loss_fwd_bwd() after a training forward
         self.sync = make_native_sync(cfg.mode, self.native, self.comm, cfg)
         self.sync.on_init()
         # static step inputs / outputs

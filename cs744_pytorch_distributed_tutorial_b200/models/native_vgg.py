@@ -40,6 +40,10 @@ ZERO_GRADS_EARLY = os.environ.get("B200DP_ZERO_GRADS_EARLY", "0") != "0"
 # BatchNorm-backward sums of block i-1, which then skips its reduction launch
 DGRAD_BN_REDUCE = os.environ.get("B200DP_DGRAD_BN_REDUCE", "0") != "0"
 
+# experimental (not yet validated on hardware): linear_fwd + cross_entropy + linear_bwd as one launch in
+# the engine's training step (NativeVGG.defer_head)
+HEAD_FUSED = os.environ.get("B200DP_HEAD_FUSED", "0") != "0"
+
 ALIGN = 4  # floats; every tensor starts on a 16-byte boundary inside the flat buffers
 
 
@@ -181,6 +185,9 @@ class NativeVGG:
         self.max_batch = max_batch
         self.heap = heap
         self.conv_stats_fused = conv_stats_fused
+        self.defer_head = False       # set by the engine when every training forward is followed by loss_fwd_bwd
+        self._head_pending = False
+        self._head_done = False
         # layer 0 (3 input channels): optional direct CUDA-core conv instead of patch gather + K=64
         # tcgen05 GEMM.  Measured slower on B200 at B=256 (LDS-bound: 122 us vs 33 + 44 us), so off.
         self.direct_first_layer = direct_first_layer and self_first_is_64(module)
@@ -446,15 +453,36 @@ class NativeVGG:
             K.bn_relu_pool_fwd(y, b.stats, b.gamma, b.beta, b.running_mean, b.running_var, b.nbt, b.mean, b.invstd,
                                b.out[:B], s.pool, training)
         feat = self.blocks[-1].out[:B]
-        K.linear_fwd(feat, self.fc_w, self.fc_b, self.logits[:B])
+        if training and self.defer_head:
+            self._head_pending = True     # the caller promises loss_fwd_bwd(): the fused head fills the logits
+        else:
+            self._head_pending = False
+            K.linear_fwd(feat, self.fc_w, self.fc_b, self.logits[:B])
         return self.logits[:B]
 
     def loss_fwd_bwd(self, target: torch.Tensor, grad_scale: float = 1.0, need_grad: bool = True) -> torch.Tensor:
         """Mean cross-entropy of the last forward's logits; fills dlogits = dL/dlogits * grad_scale."""
         B = self._B
+        if self._head_pending:
+            self._head_pending = False
+            last = self.blocks[-1]
+            if need_grad:
+                self._clear_grads()
+                K.head_fwd_bwd(last.out[:B], self.fc_w, self.fc_b, target, self.logits[:B], self.loss, self.correct,
+                               self.dlogits[:B], last.dout[:B], self.g_fc_w, self.g_fc_b, grad_scale)
+                self._head_done = True
+                return self.loss
+            K.linear_fwd(last.out[:B], self.fc_w, self.fc_b, self.logits[:B])
         K.cross_entropy(self.logits[:B], target, self.loss, self.dlogits[:B] if need_grad else None, self.correct,
                         grad_scale)
         return self.loss
+
+    def _clear_grads(self) -> None:
+        if getattr(self, "_grads_cleared", False):
+            torch.cuda.current_stream().wait_event(self._zero_done)   # cleared during forward on the wgrad stream
+            self._grads_cleared = False
+        else:
+            self.flat_grads.zero_()  # split-K weight gradients are accumulated with red.global.add
 
     # ------------------------------------------------------------------ backward
     def backward(self, dlogits: Optional[torch.Tensor] = None) -> None:
@@ -466,12 +494,12 @@ class NativeVGG:
         last = self.blocks[-1]
         main = torch.cuda.current_stream()
         side = self._wgrad_stream if WGRAD_ON_SIDE_STREAM else None
-        if getattr(self, "_grads_cleared", False):
-            main.wait_event(self._zero_done)   # cleared during forward on the weight-gradient stream
-            self._grads_cleared = False
+        if self._head_done and dlogits is None:
+            self._head_done = False     # the fused head already cleared the gradients and ran the fc backward
         else:
-            self.flat_grads.zero_()  # split-K weight gradients are accumulated with red.global.add
-        K.linear_bwd(last.out[:B], self.fc_w, dl, self.g_fc_w, self.g_fc_b, last.dout[:B])
+            self._head_done = False
+            self._clear_grads()
+            K.linear_bwd(last.out[:B], self.fc_w, dl, self.g_fc_w, self.g_fc_b, last.dout[:B])
         reduced = False   # True: the dgrad of the block above already accumulated this block's sums
         for i in range(len(self.blocks) - 1, -1, -1):
             b = self.blocks[i]

@@ -40,6 +40,7 @@ _PROTOTYPES = {
     "b200dp_linear_fwd": [P, P, P, P, I, I, I, P],
     "b200dp_cross_entropy": [P, P, P, P, P, I, I, F, P],
     "b200dp_linear_bwd": [P, P, P, P, P, P, I, I, I, P],
+    "b200dp_head_fwd_bwd": [P, P, P, P, P, P, P, P, P, P, P, I, I, I, F, P],
     "b200dp_sgd_momentum": [P, P, P, LL, F, F, F, F, P],
     "b200dp_prep_conv_weights": [P, P, P, I, I, I, I, P],
     "b200dp_prep_conv_weights_batched": [I, P, P, P, P, P, P, P, P],

@@ -191,6 +191,15 @@ def cross_entropy(logits, target, loss=None, dlogits=None, correct=None, grad_sc
          float(grad_scale), stream_ptr())
 
 
+def head_fwd_bwd(x, w, b, target, logits, loss, correct, dlogits, dx, dw, db, grad_scale: float = 1.0):
+    """Classifier head of a training step in one launch: ``linear_fwd`` + ``cross_entropy`` + ``linear_bwd``
+    (ref: master/part1/model.py:44-46 and part1.py:35-37).  ``dw`` / ``db`` are accumulated onto."""
+    B, Fdim = x.shape[0], x.numel() // x.shape[0]
+    assert target.dtype == torch.int64
+    call("b200dp_head_fwd_bwd", ptr(x), ptr(w), ptr(b), ptr(target), ptr(logits), ptr(loss), ptr(correct),
+         ptr(dlogits), ptr(dx), ptr(dw), ptr(db), B, Fdim, w.shape[0], float(grad_scale), stream_ptr())
+
+
 def linear_bwd(x, w, dlogits, dw, db, dx):
     B, Fdim = x.shape[0], x.numel() // x.shape[0]
     call("b200dp_linear_bwd", ptr(x), ptr(w), ptr(dlogits), ptr(dw), ptr(db), ptr(dx), B, Fdim, w.shape[0],

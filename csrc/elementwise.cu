@@ -880,6 +880,164 @@ __global__ void __launch_bounds__(256) linear_bwd_kernel(const __nv_bfloat16* __
 }
 
 // ---------------------------------------------------------------------------
+// classifier head of a training step in ONE launch: logits, mean softmax cross-entropy, top-1 count,
+// dlogits, dX and this block's share of dW / db (experimental, B200DP_HEAD_FUSED=1).  One warp per
+// sample; the block's activations and dlogits are parked in shared memory so that dW needs one atomic
+// per (class, feature) per block.  Loss and count are combined by the last block to finish, so neither
+// needs clearing and the result does not depend on the order of atomics.
+// ---------------------------------------------------------------------------
+constexpr int kHeadWarps = 16;
+constexpr int kHeadMaxBlocks = 256;
+__device__ float g_head_loss_part[kHeadMaxBlocks];
+__device__ int g_head_corr_part[kHeadMaxBlocks];
+__device__ unsigned int g_head_blocks_done = 0;
+
+__global__ void __launch_bounds__(kHeadWarps * 32)
+    head_fwd_bwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w,
+                        const float* __restrict__ bias, const long long* __restrict__ target,
+                        float* __restrict__ logits, float* __restrict__ loss, int* __restrict__ correct,
+                        float* __restrict__ dlogits, __nv_bfloat16* __restrict__ dx, float* __restrict__ dw,
+                        float* __restrict__ db, int B, int F, int O, float grad_scale) {
+  pdl_launch_dependents();
+  pdl_wait();
+  extern __shared__ float head_sm[];
+  float* xs = head_sm;                    // [kHeadWarps][F]
+  float* dls = head_sm + kHeadWarps * F;  // [kHeadWarps][kLinMaxO]
+  __shared__ float s_loss[kHeadWarps];
+  __shared__ int s_corr[kHeadWarps];
+  __shared__ bool s_last;
+  const int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int i = blockIdx.x * kHeadWarps + wib;  // sample of this warp
+  const bool live = i < B;
+  if (lane < kLinMaxO) dls[wib * kLinMaxO + lane] = 0.f;
+  float my_loss = 0.f;
+  int my_corr = 0;
+  if (live) {
+    const __nv_bfloat16* xr = x + static_cast<long>(i) * F;
+    float acc[kLinMaxO];
+#pragma unroll
+    for (int o = 0; o < kLinMaxO; ++o) acc[o] = 0.f;
+    for (int f = lane * 8; f < F; f += 256) {
+      const Vec8 xv = load_bf16x8(xr + f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) xs[wib * F + f + j] = xv.v[j];
+#pragma unroll
+      for (int o = 0; o < kLinMaxO; ++o) {
+        if (o < O) {
+          const Vec8 wv = load_f32x8(w + static_cast<long>(o) * F + f);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[o] = fmaf(xv.v[j], wv.v[j], acc[o]);
+        }
+      }
+    }
+    // every lane ends up with every logit (butterfly), so the softmax below needs no broadcast
+    float l[kLinMaxO];
+#pragma unroll
+    for (int o = 0; o < kLinMaxO; ++o) {
+      float t = acc[o];
+#pragma unroll
+      for (int d = 16; d > 0; d >>= 1) t += __shfl_xor_sync(0xffffffffu, t, d);
+      l[o] = o < O ? t + bias[o] : -INFINITY;
+    }
+    float mx = l[0];
+    int am = 0;
+#pragma unroll
+    for (int o = 1; o < kLinMaxO; ++o) {
+      if (o < O && l[o] > mx) {
+        mx = l[o];
+        am = o;
+      }
+    }
+    float se = 0.f;
+#pragma unroll
+    for (int o = 0; o < kLinMaxO; ++o)
+      if (o < O) se += expf(l[o] - mx);
+    const float lse = logf(se) + mx;
+    const int t = static_cast<int>(target[i]);
+    const float sc = grad_scale / static_cast<float>(B);
+    float dl[kLinMaxO], lt = 0.f, mine_l = 0.f, mine_d = 0.f;
+#pragma unroll
+    for (int o = 0; o < kLinMaxO; ++o) {
+      dl[o] = o < O ? (expf(l[o] - lse) - (o == t ? 1.f : 0.f)) * sc : 0.f;
+      lt = (o == t) ? l[o] : lt;
+      mine_l = (o == lane) ? l[o] : mine_l;
+      mine_d = (o == lane) ? dl[o] : mine_d;
+    }
+    my_loss = lse - lt;
+    my_corr = (am == t) ? 1 : 0;
+    if (lane < O) {
+      logits[static_cast<long>(i) * O + lane] = mine_l;
+      if (dlogits != nullptr) dlogits[static_cast<long>(i) * O + lane] = mine_d;
+      dls[wib * kLinMaxO + lane] = mine_d;
+    }
+    for (int f = lane * 8; f < F; f += 256) {
+      Vec8 a;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) a.v[j] = 0.f;
+#pragma unroll
+      for (int o = 0; o < kLinMaxO; ++o) {
+        if (o < O) {
+          const Vec8 wv = load_f32x8(w + static_cast<long>(o) * F + f);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) a.v[j] = fmaf(dl[o], wv.v[j], a.v[j]);
+        }
+      }
+      store_bf16x8(dx + static_cast<long>(i) * F + f, a);
+    }
+  } else {
+    for (int f = lane; f < F; f += 32) xs[wib * F + f] = 0.f;
+  }
+  if (lane == 0) {
+    s_loss[wib] = my_loss;
+    s_corr[wib] = my_corr;
+  }
+  __syncthreads();
+  // dW / db of the block's samples: one atomic per (class, feature) per block
+  for (int f = threadIdx.x; f < F; f += blockDim.x) {
+#pragma unroll
+    for (int o = 0; o < kLinMaxO; ++o) {
+      if (o < O) {
+        float a = 0.f;
+#pragma unroll
+        for (int sidx = 0; sidx < kHeadWarps; ++sidx) a = fmaf(dls[sidx * kLinMaxO + o], xs[sidx * F + f], a);
+        atomicAdd(dw + static_cast<long>(o) * F + f, a);
+      }
+    }
+  }
+  if (static_cast<int>(threadIdx.x) < O) {
+    float a = 0.f;
+    for (int sidx = 0; sidx < kHeadWarps; ++sidx) a += dls[sidx * kLinMaxO + threadIdx.x];
+    atomicAdd(db + threadIdx.x, a);
+  }
+  // loss / count: per-block partials, summed in block order by whichever block finishes last
+  if (threadIdx.x == 0) {
+    float tl = 0.f;
+    int tc = 0;
+    for (int k = 0; k < kHeadWarps; ++k) {
+      tl += s_loss[k];
+      tc += s_corr[k];
+    }
+    g_head_loss_part[blockIdx.x] = tl;
+    g_head_corr_part[blockIdx.x] = tc;
+    __threadfence();
+    s_last = atomicAdd(&g_head_blocks_done, 1u) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (s_last && threadIdx.x == 0) {
+    __threadfence();
+    float tl = 0.f;
+    int tc = 0;
+    for (unsigned k = 0; k < gridDim.x; ++k) {
+      tl += *(volatile float*)&g_head_loss_part[k];
+      tc += *(volatile int*)&g_head_corr_part[k];
+    }
+    if (loss != nullptr) *loss = tl / static_cast<float>(B);
+    if (correct != nullptr) *correct = tc;
+    g_head_blocks_done = 0;  // ready for the next launch (stream order, graph replays)
+  }
+}
+
+// ---------------------------------------------------------------------------
 // optimizer and weight re-layout
 // ---------------------------------------------------------------------------
 // d = g*gscale + wd*p ; buf = mom*buf + d ; p -= lr*buf.  With buf zero-initialised the
@@ -1207,6 +1365,32 @@ extern "C" int b200dp_linear_bwd(const void* x, const float* w, const float* dlo
   B200DP_CUDA_TRY(launch_pdl(linear_bwd_kernel, dim3(nW + nX), dim3(threads), 0, static_cast<cudaStream_t>(s),
                              static_cast<const __nv_bfloat16*>(x), w, dlogits, dw, db, static_cast<__nv_bfloat16*>(dx),
                              B, F, O, nW));
+  return 0;
+}
+
+/* Training-step classifier head in one launch (experimental): logits = x W^T + b, mean softmax
+ * cross-entropy into *loss, top-1 count into *correct, dlogits (may be NULL), dx = dlogits W (bf16), and
+ * dw += dlogits^T x, db += sum dlogits (dw / db must be zero or hold the value to accumulate onto --
+ * unlike b200dp_linear_bwd this entry point does not clear them).  F % 8 == 0, F <= 2048, O <= 16,
+ * B <= 4096.  Launches on one stream only (it keeps its block counter in a device global). */
+extern "C" int b200dp_head_fwd_bwd(const void* x, const float* w, const float* bias, const long long* target,
+                                   float* logits, float* loss, int* correct, float* dlogits, void* dx, float* dw,
+                                   float* db, int B, int F, int O, float grad_scale, b200dp_stream_t s) {
+  if (F % 8 != 0 || F > 2048 || O > kLinMaxO || O < 1 || B < 1 || B > kHeadWarps * kHeadMaxBlocks) {
+    set_error("head_fwd_bwd: unsupported shape B=%d F=%d O=%d", B, F, O);
+    return B200DP_EINVAL;
+  }
+  const int blocks = (B + kHeadWarps - 1) / kHeadWarps;
+  const size_t smem = (static_cast<size_t>(kHeadWarps) * F + kHeadWarps * kLinMaxO) * sizeof(float);
+  static bool configured = false;
+  if (!configured) {
+    B200DP_CUDA_TRY(cudaFuncSetAttribute(head_fwd_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         static_cast<int>((kHeadWarps * 2048 + kHeadWarps * kLinMaxO) * sizeof(float))));
+    configured = true;
+  }
+  B200DP_CUDA_TRY(launch_pdl(head_fwd_bwd_kernel, dim3(blocks), dim3(kHeadWarps * 32), smem, static_cast<cudaStream_t>(s),
+                             static_cast<const __nv_bfloat16*>(x), w, bias, target, logits, loss, correct, dlogits,
+                             static_cast<__nv_bfloat16*>(dx), dw, db, B, F, O, grad_scale));
   return 0;
 }
 

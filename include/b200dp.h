@@ -179,6 +179,13 @@ int b200dp_cross_entropy(const float* logits, const long long* target, float* lo
                          int* correct, int B, int O, float grad_scale, b200dp_stream_t stream);
 int b200dp_linear_bwd(const void* x_bf16, const float* w, const float* dlogits, float* dw, float* db,
                       void* dx_bf16, int B, int F, int O, b200dp_stream_t stream);
+/* The three calls above as ONE launch for a training step (experimental; the executor uses it with
+ * B200DP_HEAD_FUSED=1): logits, mean cross-entropy, top-1 count, dlogits (may be NULL), dx, and
+ * dw += dlogits^T x, db += sum dlogits.  dw / db are accumulated onto (zero them first), loss / correct
+ * are overwritten.  F % 8 == 0, F <= 2048, O <= 16, B <= 4096; one stream at a time. */
+int b200dp_head_fwd_bwd(const void* x_bf16, const float* w, const float* bias, const long long* target,
+                        float* logits, float* loss, int* correct, float* dlogits, void* dx_bf16, float* dw,
+                        float* db, int B, int F, int O, float grad_scale, b200dp_stream_t stream);
 
 /* SGD with momentum and weight decay on flat fp32 buffers:
  * d = g*grad_scale + wd*p; buf = momentum*buf + d; p -= lr*buf.  buf starts at zero,

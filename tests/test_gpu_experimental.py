@@ -129,3 +129,63 @@ def test_part3_weight_relayout_behind_the_buckets(monkeypatch):
                 assert torch.equal(b.wd, wd)
     finally:
         tr.close()
+
+
+@pytest.mark.parametrize("B", [256, 64, 37, 1])
+def test_fused_head_matches_the_three_kernel_path(B):
+    """b200dp_head_fwd_bwd vs linear_fwd + cross_entropy + linear_bwd, and vs torch fp32."""
+    native = _native()
+    Fd, O = 512, 10
+    g = torch.Generator(device=DEV).manual_seed(3)
+    x = torch.randn(B, 1, 1, Fd, device=DEV, generator=g).bfloat16()
+    w = torch.randn(O, Fd, device=DEV, generator=g) * 0.05
+    b = torch.randn(O, device=DEV, generator=g) * 0.1
+    t = torch.randint(0, O, (B,), device=DEV, generator=g)
+    # reference: the three validated kernels
+    logits0 = torch.empty(B, O, device=DEV); dl0 = torch.empty(B, O, device=DEV)
+    loss0 = torch.zeros((), device=DEV); corr0 = torch.zeros((), device=DEV, dtype=torch.int32)
+    dw0 = torch.zeros(O, Fd, device=DEV); db0 = torch.zeros(O, device=DEV)
+    dx0 = torch.empty_like(x)
+    native.linear_fwd(x, w, b, logits0)
+    native.cross_entropy(logits0, t, loss0, dl0, corr0, 1.0)
+    native.linear_bwd(x, w, dl0, dw0, db0, dx0)
+    for rep in range(2):      # twice: the block counter must have been reset by the first launch
+        logits = torch.full((B, O), float("nan"), device=DEV); dl = torch.full((B, O), float("nan"), device=DEV)
+        loss = torch.full((), float("nan"), device=DEV); corr = torch.full((), -7, device=DEV, dtype=torch.int32)
+        dw = torch.zeros(O, Fd, device=DEV); db = torch.zeros(O, device=DEV)
+        dx = torch.full_like(x, float("nan"))
+        native.head_fwd_bwd(x, w, b, t, logits, loss, corr, dl, dx, dw, db, 1.0)
+        torch.cuda.synchronize()
+        torch.testing.assert_close(logits, logits0, rtol=1e-5, atol=1e-5)
+        torch.testing.assert_close(dl, dl0, rtol=1e-4, atol=1e-7)
+        torch.testing.assert_close(loss, loss0, rtol=1e-5, atol=1e-6)
+        assert int(corr) == int(corr0)
+        torch.testing.assert_close(dx.float(), dx0.float(), rtol=2e-2, atol=1e-6)
+        torch.testing.assert_close(dw, dw0, rtol=1e-4, atol=1e-6)
+        torch.testing.assert_close(db, db0, rtol=1e-4, atol=1e-7)
+    # and the plain fp32 definition
+    ref_logits = x.float().view(B, Fd) @ w.t() + b
+    torch.testing.assert_close(logits, ref_logits, rtol=1e-4, atol=1e-4)
+    torch.testing.assert_close(loss, torch.nn.functional.cross_entropy(ref_logits, t), rtol=1e-4, atol=1e-5)
+
+
+def test_training_step_with_fused_head_matches_the_default():
+    from cs744_pytorch_distributed_tutorial_b200.models.vgg import VGG
+    torch.manual_seed(0)
+    x = torch.randn(64, 3, 32, 32, device=DEV)
+    y = torch.randint(0, 10, (64,), device=DEV)
+    res = []
+    for defer in (False, True):
+        torch.manual_seed(1)
+        model = VGG("VGG11").to(DEV)
+        nv = model.enable_native(max_batch=64)
+        nv.defer_head = defer
+        for _ in range(2):      # second pass: flags and gradient clearing must have been reset
+            nv.forward(x, training=True)
+            nv.loss_fwd_bwd(y)
+            nv.backward()
+        torch.cuda.synchronize()
+        res.append((float(nv.loss), int(nv.correct), nv.flat_grads.clone()))
+    (l0, c0, g0), (l1, c1, g1) = res
+    assert abs(l0 - l1) < 1e-4 and c0 == c1
+    assert torch.nn.functional.cosine_similarity(g0, g1, dim=0).item() > 0.9995

@@ -185,6 +185,7 @@ class NativeVGG:
         self.max_batch = max_batch
         self.heap = heap
         self.conv_stats_fused = conv_stats_fused
+        self.wgrad_push = None        # {block index: conv_wgrad_push arguments}, set by BucketedOverlapSync
         self.defer_head = False       # set by the engine when every training forward is followed by loss_fwd_bwd
         self._head_pending = False
         self._head_done = False
@@ -530,6 +531,10 @@ class NativeVGG:
             with torch.cuda.stream(side) if side is not None else contextlib.nullcontext():
                 if b.direct:
                     K.conv3x3_c3_wgrad(b.dy[:B], self._x_first, b.g_w)
+                elif self.wgrad_push is not None and i in self.wgrad_push:
+                    # experimental: GEMM + transfer half of the reduce-scatter in one kernel
+                    K.conv_wgrad_push(b.dy[:B], b.x_in[:B], b.g_w, split_k=b.wgrad_split_k, block_n=b.wgrad_block_n,
+                                      **self.wgrad_push[i])
                 else:
                     K.conv_wgrad(b.dy[:B], b.x_in[:B], b.g_w, taps=b.taps, cin_valid=(27 if b.first else None),
                                  split_k=b.wgrad_split_k, block_n=b.wgrad_block_n)

@@ -28,6 +28,7 @@ _PROTOTYPES = {
     "b200dp_conv_dgrad_bn_reduce": [P, P, P, P, P, P, P, P, I, I, I, I, I, I, I, I, I, P],
     "b200dp_conv_wgrad": [P, P, P, I, I, I, I, I, I, I, I, I, P],
     "b200dp_conv_wgrad_tiled": [P, P, P, I, I, I, I, I, I, I, I, I, I, P],
+    "b200dp_conv_wgrad_push": [P, P, P, I, I, I, I, I, I, I, I, P, I, I, I, P, LL, LL, LL, LL, P],
     "b200dp_im2col3x3_c3": [P, P, I, I, I, P],
     "b200dp_conv3x3_c3_fwd": [P, P, P, P, P, I, I, I, P],
     "b200dp_conv3x3_c3_wgrad": [P, P, P, I, I, I, P],
@@ -56,7 +57,8 @@ _NON_LAUNCHING = {"b200dp_store_create", "b200dp_store_set", "b200dp_store_get",
                   "b200dp_store_barrier", "b200dp_store_destroy", "b200dp_comm_create", "b200dp_comm_destroy",
                   "b200dp_comm_heap", "b200dp_comm_peer_base", "b200dp_comm_set_timeout", "b200dp_reducer_create",
                   "b200dp_comm_create_ex", "b200dp_comm_prefer_nvls", "b200dp_comm_has_multicast",
-                  "b200dp_reducer_set_lr", "b200dp_reducer_finalize", "b200dp_reducer_destroy"}
+                  "b200dp_reducer_set_lr", "b200dp_reducer_finalize", "b200dp_reducer_destroy",
+                  "b200dp_reducer_stream", "b200dp_reducer_set_blocks", "b200dp_reducer_set_staged"}
 launch_count = 0  # kernels of this library launched (or captured) by this process so far
 
 

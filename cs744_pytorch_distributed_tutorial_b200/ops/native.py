@@ -105,6 +105,24 @@ def conv_wgrad(dy: torch.Tensor, x: torch.Tensor, dw: torch.Tensor, taps: int = 
     return dw
 
 
+def conv_wgrad_push(dy: torch.Tensor, x: torch.Tensor, dw: torch.Tensor, *, counters: torch.Tensor, world: int,
+                    rank: int, peer_stage, flat_off: int, own_start: int, own_len: int, stage_base: int,
+                    split_k: int = 0, block_n: int = 0) -> torch.Tensor:
+    """Weight gradient whose epilogue also forwards every finished tile to the rank that owns it in the
+    data-parallel reduce-scatter (``peer_stage``: ctypes array of ``world`` staging-buffer pointers).
+    ``dw`` must be zero on entry and sit at element ``flat_off`` of the flat gradient buffer."""
+    _chk(dy, torch.bfloat16, "dy")
+    _chk(x, torch.bfloat16, "x")
+    _chk(dw, torch.float32, "dw")
+    assert counters.dtype == torch.int32 and counters.is_cuda
+    B, H, W, Cout = dy.shape
+    Cin = x.shape[3]
+    assert dw.numel() == Cout * 9 * Cin
+    call("b200dp_conv_wgrad_push", ptr(dy), ptr(x), ptr(dw), B, H, W, Cin, Cout, 9, split_k, block_n, ptr(counters),
+         counters.numel(), world, rank, peer_stage, flat_off, own_start, own_len, stage_base, stream_ptr())
+    return dw
+
+
 def im2col3x3_c3(x_nchw: torch.Tensor, a0: torch.Tensor) -> torch.Tensor:
     _chk(x_nchw, torch.float32, "x")
     _chk(a0, torch.bfloat16, "a0")

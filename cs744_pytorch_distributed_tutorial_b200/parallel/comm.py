@@ -43,6 +43,8 @@ _lib.declare("b200dp_reducer_create", [P, I, POINTER(c_longlong), POINTER(c_long
 _lib.declare("b200dp_reducer_set_lr", [P, F])
 _lib.declare("b200dp_reducer_stream", [P, POINTER(c_void_p)])
 _lib.declare("b200dp_reducer_set_blocks", [P, I])
+_lib.declare("b200dp_reducer_set_staged", [P, LL, POINTER(c_longlong), POINTER(c_longlong), POINTER(c_longlong)])
+_lib.declare("b200dp_reduce_staged_sgd", [P, LL, LL, LL, LL, LL, LL, LL, LL, LL, F, F, F, I, I, I, P])
 _lib.declare("b200dp_reducer_bucket_ready", [P, I, P])
 _lib.declare("b200dp_reducer_finalize", [P, P])
 _lib.declare("b200dp_reducer_destroy", [P])
@@ -224,6 +226,13 @@ class BucketReducer:
     def set_blocks(self, blocks: int) -> None:
         """CTAs per bucket collective from the next ``bucket_ready`` on (re-capture the step afterwards)."""
         call("b200dp_reducer_set_blocks", self._h, int(blocks))
+
+    def set_staged(self, stage_buf_off: int, pushed_lo, pushed_hi, stage_base) -> None:
+        """Experimental: buckets whose conv weight gradient arrives through ``conv_wgrad_push`` staging run
+        the owner-side ``reduce_staged_sgd`` kernel instead of the all-reduce."""
+        n = self.n_buckets
+        arr = lambda v: (c_longlong * n)(*[int(x) for x in v])
+        call("b200dp_reducer_set_staged", self._h, int(stage_buf_off), arr(pushed_lo), arr(pushed_hi), arr(stage_base))
 
     def stream(self, device) -> torch.cuda.Stream:
         """The reducer's side stream as a torch stream: kernels queued on it after ``bucket_ready(k)``

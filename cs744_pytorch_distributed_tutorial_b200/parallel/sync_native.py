@@ -214,6 +214,45 @@ class BucketedOverlapSync(NativeSync):
             self.handles_shadows = True
             nv.on_bucket_ready = self._bucket_ready
 
+        # Experimental (B200DP_WGRAD_PUSH=1, not yet run on hardware): the weight-gradient GEMM of every
+        # 3x3 layer forwards its finished tiles to the owning rank's staging slots as they complete
+        # (GEMM -> reduce-scatter in one kernel); the bucket kernel on the reducer stream then only sums
+        # local memory, applies SGD and broadcasts the parameters.
+        self._wgrad_push = (os.environ.get("B200DP_WGRAD_PUSH", "0") != "0" and fuse and bucket_plan == "layer"
+                            and self.world > 1 and self.world <= 8)
+        if self._wgrad_push:
+            self._setup_wgrad_push()
+
+    def _setup_wgrad_push(self) -> None:
+        import ctypes
+        nv, W, comm = self.native, self.world, self.comm
+        per4 = [(((b.end - b.start) // 4) + W - 1) // W for b in self.buckets]
+        stage_base, total = [], 0
+        for p4 in per4:
+            stage_base.append(total)
+            total += W * p4 * 4
+        self._stage = comm.zeros(max(total, 4))
+        stage_off = comm.offset_of(self._stage)
+        self._peer_stage = (ctypes.c_void_p * W)(*[comm.peer_ptr(r) + stage_off for r in range(W)])
+        pushed_lo = [b.start for b in self.buckets]
+        pushed_hi = [b.start for b in self.buckets]
+        nv.wgrad_push = {}
+        self._push_counters = []
+        for i, blk in enumerate(nv.blocks):
+            if blk.first or blk.direct:
+                continue          # Cin = 3: 27 columns, not 16-byte rows; stays on the all-reduce
+            e = nv.layout.by_name[f"layers.{blk.spec.conv_idx}.weight"]
+            k = next(j for j, b in enumerate(self.buckets) if b.start <= e.offset < b.end)
+            bk = self.buckets[k]
+            tiles = 9 * ((blk.spec.cout + 127) // 128) * (blk.spec.cin // 64)
+            counters = torch.zeros(tiles, dtype=torch.int32, device=nv.device)
+            self._push_counters.append(counters)
+            nv.wgrad_push[i] = dict(counters=counters, world=W, rank=comm.rank, peer_stage=self._peer_stage,
+                                    flat_off=e.offset, own_start=bk.start, own_len=bk.end - bk.start,
+                                    stage_base=stage_base[k])
+            pushed_lo[k], pushed_hi[k] = e.offset, e.offset + e.numel
+        self.reducer.set_staged(stage_off, pushed_lo, pushed_hi, stage_base)
+
     def _bucket_ready(self, k: int) -> None:
         self.reducer.bucket_ready(k)
         if k == self.split_bucket:
@@ -271,6 +310,7 @@ class BucketedOverlapSync(NativeSync):
 
     def close(self) -> None:
         self.native.on_bucket_ready = None
+        self.native.wgrad_push = None
         self.reducer.close()
 
 

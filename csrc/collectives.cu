@@ -340,6 +340,78 @@ __global__ void __launch_bounds__(512) allreduce_nvls_kernel(const CommDev c, co
 }
 
 // ---------------------------------------------------------------------------
+// Owner-side half of the fused "weight-gradient GEMM -> reduce-scatter" path (experimental).
+// The conv_wgrad_push kernels of every rank have already stored their finished tiles of this bucket
+// into the owner's staging slots (conv_igemm.cu), so the owner reads only LOCAL memory here: its own
+// gradient plus W-1 staged copies.  Tensors that are not produced by a wgrad GEMM (biases, BatchNorm
+// weights, the classifier) are outside [pushed_lo, pushed_hi) and are pulled from the peers as in the
+// two-shot kernel.  Then 1/W, SGD on the owned slice, and the updated parameters go to every rank
+// (P2P stores, or one multimem.st through the switch).
+// ---------------------------------------------------------------------------
+struct StagedArgs {
+  RangeArgs r;
+  size_t stage_buf_off;       // byte offset of the staging buffer inside the heap
+  long pushed_lo, pushed_hi;  // absolute element range (multiples of 4) whose gradients arrive by push
+  long stage_base;            // element offset of this bucket's area inside the staging buffer
+};
+
+template <bool NVLS>
+__global__ void __launch_bounds__(512) reduce_staged_sgd_kernel(const CommDev c, const StagedArgs s) {
+  const RangeArgs& a = s.r;
+  const uint32_t epoch = begin_collective(c, a.channel);
+  // every rank has launched this collective, i.e. its wgrad kernels of this bucket (earlier in stream
+  // order) have completed and their staged tiles are visible
+  rank_barrier(c, a.channel, 0, epoch);
+  const int W = c.world;
+  const long n4 = (a.end - a.start) >> 2;
+  const long per = (n4 + W - 1) / W;
+  const long lo = min(per * c.rank, n4), hi = min(lo + per, n4);
+  const float inv_w = 1.f / static_cast<float>(W);
+  char* me = c.peers.base[c.rank];
+  const float* stage = reinterpret_cast<const float*>(me + s.stage_buf_off) + s.stage_base;
+  const long tstride = static_cast<long>(gridDim.x) * blockDim.x;
+  for (long i = lo + blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < hi; i += tstride) {
+    const long e = a.start + (i << 2);
+    const size_t eoff = static_cast<size_t>(e) * sizeof(float);
+    float4 g;
+    if (e >= s.pushed_lo && e < s.pushed_hi) {
+      g = __ldcg(reinterpret_cast<const float4*>(me + a.grad_off + eoff));
+#pragma unroll
+      for (int r = 0; r < kMaxWorld; ++r) {
+        if (r < W && r != c.rank) {
+          const float4 v = __ldcg(reinterpret_cast<const float4*>(stage + ((r * per + (i - lo)) << 2)));
+          g.x += v.x; g.y += v.y; g.z += v.z; g.w += v.w;
+        }
+      }
+    } else {
+      g = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int r = 0; r < kMaxWorld; ++r) {
+        if (r < W) {
+          const float4 v = ld_peer_f4(reinterpret_cast<const float*>(c.peers.base[r] + a.grad_off + eoff));
+          g.x += v.x; g.y += v.y; g.z += v.z; g.w += v.w;
+        }
+      }
+    }
+    g.x *= inv_w; g.y *= inv_w; g.z *= inv_w; g.w *= inv_w;
+    float4 p = *reinterpret_cast<const float4*>(me + a.param_off + eoff);
+    float4 m = *reinterpret_cast<const float4*>(me + a.mom_off + eoff);
+    const float4 np = sgd4(g, p, m, a.sgd);
+    *reinterpret_cast<float4*>(me + a.mom_off + eoff) = m;
+    *reinterpret_cast<float4*>(me + a.grad_off + eoff) = g;  // the owner keeps the mean gradient
+    if (NVLS) {
+      multimem_st_f4(reinterpret_cast<float*>(c.mc_base + a.param_off + eoff), np);
+    } else {
+#pragma unroll
+      for (int r = 0; r < kMaxWorld; ++r)
+        if (r < W) st_peer_f4(reinterpret_cast<float*>(c.peers.base[r] + a.param_off + eoff), np);
+    }
+  }
+  rank_barrier(c, a.channel, 1, epoch);
+  end_collective(c, a.channel, epoch);
+}
+
+// ---------------------------------------------------------------------------
 // parameter server (rank `root` reduces, everyone receives the mean)
 // ---------------------------------------------------------------------------
 template <bool PUSH>
@@ -861,6 +933,53 @@ extern "C" int b200dp_allreduce(void* comm, long long grad_off, long long param_
   return 0;
 }
 
+/* Owner-side half of the fused wgrad -> reduce-scatter path (experimental; see conv_wgrad_push):
+ * for the bucket [start, end): mean gradient of my slice = (own gradient + W-1 staged copies) / W inside
+ * [pushed_lo, pushed_hi), pulled from the peers elsewhere; SGD; updated parameters to every rank.
+ * stage_buf_off: byte offset of the staging buffer in the heap, stage_base: element offset of this
+ * bucket's area in it (source rank s at stage_base + s * per4 * 4).  nvls = 1 broadcasts the parameters
+ * with multimem.st (multicast heap required). */
+extern "C" int b200dp_reduce_staged_sgd(void* comm, long long grad_off, long long param_off, long long mom_off,
+                                        long long stage_buf_off, long long start, long long end,
+                                        long long pushed_lo, long long pushed_hi, long long stage_base, float lr,
+                                        float momentum, float weight_decay, int nvls, int blocks, int channel,
+                                        b200dp_stream_t stream_) {
+  auto* c = static_cast<Comm*>(comm);
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (blocks <= 0) blocks = 32;
+  int rc = check_range(c, start, end, blocks, channel, "reduce_staged_sgd");
+  if (rc) return rc;
+  if ((pushed_lo & 3) || (pushed_hi & 3) || (stage_base & 3) || pushed_lo < start || pushed_hi > end ||
+      pushed_lo > pushed_hi) {
+    set_error("reduce_staged_sgd: pushed range [%lld, %lld) must be 4-aligned and inside [%lld, %lld)", pushed_lo,
+              pushed_hi, start, end);
+    return B200DP_EINVAL;
+  }
+  if (nvls && c->mc_base == nullptr) {
+    set_error("reduce_staged_sgd: nvls=1 needs a communicator created with the multicast heap");
+    return B200DP_EINVAL;
+  }
+  StagedArgs s{};
+  s.r.grad_off = static_cast<size_t>(grad_off);
+  s.r.param_off = static_cast<size_t>(param_off);
+  s.r.mom_off = static_cast<size_t>(mom_off);
+  s.r.start = start;
+  s.r.end = end;
+  s.r.channel = channel;
+  s.r.sgd = SgdHyper{lr, momentum, weight_decay};
+  s.stage_buf_off = static_cast<size_t>(stage_buf_off);
+  s.pushed_lo = pushed_lo;
+  s.pushed_hi = pushed_hi;
+  s.stage_base = stage_base;
+  const CommDev d = dev_view(c);
+  if (nvls)
+    reduce_staged_sgd_kernel<true><<<blocks, 512, 0, stream>>>(d, s);
+  else
+    reduce_staged_sgd_kernel<false><<<blocks, 512, 0, stream>>>(d, s);
+  B200DP_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
 extern "C" int b200dp_ps_reduce_bcast(void* comm, long long grad_off, long long stage_off, long long start,
                                       long long end, int root, int push, int blocks, int channel,
                                       b200dp_stream_t stream_) {
@@ -930,6 +1049,10 @@ struct Reducer {
   std::vector<cudaEvent_t> ready;
   cudaEvent_t done = nullptr;
   int launched = 0;
+  // experimental: buckets whose conv weight gradient arrives through conv_wgrad_push staging
+  bool staged = false;
+  long long stage_buf_off = 0;
+  std::vector<long long> pushed_lo, pushed_hi, stage_base;
 };
 }  // namespace b200dp
 
@@ -1001,8 +1124,31 @@ extern "C" int b200dp_reducer_bucket_ready(void* reducer, int k, b200dp_stream_t
   B200DP_CUDA_TRY(cudaEventRecord(r->ready[k], static_cast<cudaStream_t>(compute_stream)));
   B200DP_CUDA_TRY(cudaStreamWaitEvent(r->side, r->ready[k], 0));
   ++r->launched;
+  if (r->staged && r->pushed_hi[k] > r->pushed_lo[k])
+    return b200dp_reduce_staged_sgd(r->comm, r->grad_off, r->param_off, r->mom_off, r->stage_buf_off, r->start[k],
+                                    r->end[k], r->pushed_lo[k], r->pushed_hi[k], r->stage_base[k], r->lr, r->momentum,
+                                    r->weight_decay, (r->comm->prefer_nvls && r->comm->mc_base) ? 1 : 0, r->blocks,
+                                    r->channel, r->side);
   return b200dp_allreduce(r->comm, r->grad_off, r->param_off, r->mom_off, r->start[k], r->end[k], r->fuse_sgd,
                           r->prescale, r->lr, r->momentum, r->weight_decay, 0, r->blocks, r->channel, r->side);
+}
+
+/* Experimental: tell the reducer which part of every bucket is delivered by conv_wgrad_push
+ * (pushed_lo[k] == pushed_hi[k]: none, the bucket keeps the plain all-reduce).  Needs fuse_sgd. */
+extern "C" int b200dp_reducer_set_staged(void* reducer, long long stage_buf_off, const long long* pushed_lo,
+                                         const long long* pushed_hi, const long long* stage_base) {
+  auto* r = static_cast<Reducer*>(reducer);
+  if (!r || !pushed_lo || !pushed_hi || !stage_base || !r->fuse_sgd) {
+    set_error("reducer_set_staged: needs a reducer with the fused optimizer and three arrays of n_buckets entries");
+    return B200DP_EINVAL;
+  }
+  const size_t n = r->start.size();
+  r->pushed_lo.assign(pushed_lo, pushed_lo + n);
+  r->pushed_hi.assign(pushed_hi, pushed_hi + n);
+  r->stage_base.assign(stage_base, stage_base + n);
+  r->stage_buf_off = stage_buf_off;
+  r->staged = true;
+  return 0;
 }
 
 extern "C" int b200dp_reducer_finalize(void* reducer, b200dp_stream_t compute_stream) {

@@ -616,10 +616,24 @@ struct WgradParams {
   float* out;
 };
 
-template <int BLOCK_N, int STAGES>
-__global__ void __launch_bounds__(kNumThreads)
-    conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ CUtensorMap tmX,
-                      const WgradParams p) {
+struct WgradPushParams : WgradParams {
+  // conv_wgrad_push kernels only (GEMM -> reduce-scatter in one kernel): when the last of the `splits`
+  // CTAs of an output tile has added its partial, that CTA forwards the finished tile to the rank that
+  // owns it, with plain vector stores over NVLink into the owner's staging slot for this rank.  The
+  // owner later sums its own gradient and the W-1 staged copies inside the fused SGD kernel -- no
+  // cross-GPU atomics, no reduce-scatter phase in the collective.
+  unsigned int* tile_counters;  // one per output tile (gridDim.x), zero on entry, left zero
+  int splits;
+  int world, rank;
+  long long flat_off;    // element offset of out[0] in the flat gradient buffer (multiple of 4)
+  long long own_start;   // first element of the bucket this tensor belongs to (multiple of 4)
+  long long per4;        // float4s of the bucket owned by each rank: owner(e) = ((e - own_start) / 4) / per4
+  long long stage_base;  // element offset of the bucket's staging area inside `peer_stage[r]`
+  float* peer_stage[8];  // every rank's staging buffer: slot of source rank s starts at stage_base + s*per4*4
+};
+
+template <int BLOCK_N, int STAGES, bool PUSH, typename ParamsT>
+B200DP_DEVINL void conv_wgrad_body(const CUtensorMap& tmDY, const CUtensorMap& tmX, const ParamsT& p) {
   constexpr int kSubTileBytes = 64 * 64 * 2;  // one (64 channels x 64 pixels) box, 8 KiB
   constexpr int kABytes = 2 * kSubTileBytes;
   constexpr int kBBytes = (BLOCK_N / 64) * kSubTileBytes;
@@ -773,6 +787,43 @@ __global__ void __launch_bounds__(kNumThreads)
           }
         }
       }
+      if constexpr (PUSH) {
+        // Tile hand-off.  Every split has added (or stored) its partial above; the fence orders those
+        // writes before the counter increment, so whoever draws the last ticket sees the complete tile.
+        uint32_t* last_flag = tmem_slot + 1;
+        __threadfence();
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (threadIdx.x == 64) {
+          const unsigned int ticket = atomicAdd(p.tile_counters + blockIdx.x, 1u);
+          const bool last = ticket == static_cast<unsigned int>(p.splits) - 1u;
+          if (last) p.tile_counters[blockIdx.x] = 0u;  // nobody else touches it before the next launch
+          *last_flag = last ? 1u : 0u;
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (*last_flag != 0u) {
+          __threadfence();
+          // warp-cooperative: the 32 lanes walk one output row at a time, so every store instruction
+          // sends 512 contiguous bytes over NVLink
+          const int ncols4 = min(BLOCK_N, col_limit) >> 2;  // the host enables PUSH only for multiples of 4
+          for (int rr = 0; rr < 32; ++rr) {
+            const int co_r = co_tile * kBlockM + q * 32 + rr;
+            if (co_r >= p.cout) break;
+            const long long row_off = static_cast<long long>(co_r) * p.ld_out + tap * p.cin_valid + ci_tile * BLOCK_N;
+            const float* src_row = p.out + row_off;
+            const long long i4_row = (p.flat_off + row_off - p.own_start) >> 2;
+            for (int c4 = lane; c4 < ncols4; c4 += 32) {
+              const long long i4 = i4_row + c4;
+              const int owner = static_cast<int>(i4 / p.per4);
+              if (owner != p.rank) {
+                const float4 v = __ldcg(reinterpret_cast<const float4*>(src_row) + c4);
+                float* dst = p.peer_stage[owner] + p.stage_base +
+                             ((static_cast<long long>(p.rank) * p.per4 + (i4 - owner * p.per4)) << 2);
+                *reinterpret_cast<float4*>(dst) = v;
+              }
+            }
+          }
+        }
+      }
       tc_fence_before();
     }
   }
@@ -781,6 +832,21 @@ __global__ void __launch_bounds__(kNumThreads)
     tc_fence_after();
     tmem_dealloc(tmem_base, kTmemCols);
   }
+}
+
+template <int BLOCK_N, int STAGES>
+__global__ void __launch_bounds__(kNumThreads)
+    conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ CUtensorMap tmX,
+                      const WgradParams p) {
+  conv_wgrad_body<BLOCK_N, STAGES, false, WgradParams>(tmDY, tmX, p);
+}
+
+// Weight gradient + the transfer half of the gradient reduce-scatter (WgradParams::peer_stage ...).
+template <int BLOCK_N, int STAGES>
+__global__ void __launch_bounds__(kNumThreads)
+    conv_wgrad_push_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ CUtensorMap tmX,
+                           const WgradPushParams p) {
+  conv_wgrad_body<BLOCK_N, STAGES, true, WgradPushParams>(tmDY, tmX, p);
 }
 
 // ---------------------------------------------------------------------------
@@ -926,6 +992,30 @@ static int launch_wgrad(const CUtensorMap& tmDY, const CUtensorMap& tmX, const W
   B200DP_CUDA_TRY(launch_pdl(kern, grid, dim3(kNumThreads), smem, stream, tmDY, tmX, p));
   return 0;
 }
+
+template <int BLOCK_N, int STAGES>
+static int launch_wgrad_push(const CUtensorMap& tmDY, const CUtensorMap& tmX, const WgradPushParams& p, int tiles,
+                             int splits, cudaStream_t stream) {
+  constexpr int smem = STAGES * (2 * 8192 + (BLOCK_N / 64) * 8192) + 1024 + 256;
+  static bool configured = false;
+  auto kern = conv_wgrad_push_kernel<BLOCK_N, STAGES>;
+  if (!configured) {
+    B200DP_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured = true;
+  }
+  dim3 grid(tiles, splits);
+  B200DP_CUDA_TRY(launch_pdl(kern, grid, dim3(kNumThreads), smem, stream, tmDY, tmX, p));
+  return 0;
+}
+
+// What the push flavour of the weight-gradient kernel needs to know about the data-parallel group.
+struct WgradPushArgs {
+  unsigned int* tile_counters;
+  int n_counters;
+  int world, rank;
+  void* const* peer_stage;  // `world` device pointers: every rank's staging buffer
+  long long flat_off, own_start, own_len, stage_base;
+};
 
 }  // namespace b200dp
 
@@ -1127,7 +1217,8 @@ extern "C" int b200dp_conv_dgrad_bn_reduce(const void* act, const void* wgt, voi
 }
 
 static int conv_wgrad_impl(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin, int Cout, int taps,
-                           int cin_valid, int split_k, int accumulate, int block_n_req, cudaStream_t stream) {
+                           int cin_valid, int split_k, int accumulate, int block_n_req, cudaStream_t stream,
+                           const WgradPushArgs* push = nullptr) {
   if ((taps != 9 && taps != 1) || Cin % 64 != 0 || (Cout % 128 != 0 && Cout != 64) || B <= 0 || cin_valid > Cin ||
       cin_valid <= 0) {
     set_error("conv_wgrad: unsupported shape B=%d H=%d W=%d Cin=%d Cout=%d taps=%d", B, H, W, Cin, Cout, taps);
@@ -1181,6 +1272,35 @@ static int conv_wgrad_impl(const void* dy, const void* x, float* dw, int B, int 
   }
   // 3 stages (96 / 144 / 72 KiB): the 128-wide kernel then fits on an SM next to a 3-stage dgrad CTA
   // (99 KiB), which matters because weight and data gradients run on two streams concurrently
+  if (push != nullptr) {
+    if (push->world < 2 || push->world > 8 || push->rank < 0 || push->rank >= push->world ||
+        push->peer_stage == nullptr || push->tile_counters == nullptr || push->n_counters < tiles) {
+      set_error("conv_wgrad_push: need 2..8 ranks, their staging pointers and >= %d tile counters", tiles);
+      return B200DP_EINVAL;
+    }
+    if (cin_valid != Cin || (p.ld_out & 3) != 0 || (push->flat_off & 3) != 0 || (push->own_start & 3) != 0 ||
+        (push->own_len & 3) != 0 || (push->stage_base & 3) != 0 || push->flat_off < push->own_start ||
+        push->flat_off + static_cast<long long>(Cout) * p.ld_out > push->own_start + push->own_len) {
+      set_error("conv_wgrad_push: the weight tensor must be unpadded, 16-byte aligned and inside its bucket");
+      return B200DP_EINVAL;
+    }
+    WgradPushParams pp{};
+    static_cast<WgradParams&>(pp) = p;
+    pp.tile_counters = push->tile_counters;
+    pp.splits = split_k;
+    pp.world = push->world;
+    pp.rank = push->rank;
+    pp.flat_off = push->flat_off;
+    pp.own_start = push->own_start;
+    const long long n4 = push->own_len >> 2;
+    pp.per4 = (n4 + push->world - 1) / push->world;
+    pp.stage_base = push->stage_base;
+    for (int r = 0; r < 8; ++r)
+      pp.peer_stage[r] = r < push->world ? static_cast<float*>(push->peer_stage[r]) : nullptr;
+    if (block_n == 256) return launch_wgrad_push<256, 3>(tmDY, tmX, pp, tiles, split_k, stream);
+    if (block_n == 128) return launch_wgrad_push<128, 3>(tmDY, tmX, pp, tiles, split_k, stream);
+    return launch_wgrad_push<64, 4>(tmDY, tmX, pp, tiles, split_k, stream);
+  }
   if (block_n == 256) return launch_wgrad<256, 3>(tmDY, tmX, p, tiles, split_k, stream);
   if (block_n == 128) return launch_wgrad<128, 3>(tmDY, tmX, p, tiles, split_k, stream);
   return launch_wgrad<64, 4>(tmDY, tmX, p, tiles, split_k, stream);
@@ -1191,6 +1311,26 @@ extern "C" int b200dp_conv_wgrad(const void* dy, const void* x, float* dw, int B
                                  b200dp_stream_t stream_) {
   return conv_wgrad_impl(dy, x, dw, B, H, W, Cin, Cout, taps, cin_valid, split_k, accumulate, 0,
                          static_cast<cudaStream_t>(stream_));
+}
+
+/* Weight gradient fused with the transfer half of the data-parallel reduce-scatter (experimental).
+ * As b200dp_conv_wgrad_tiled (dw zero on entry, full Cin columns), plus: the tensor lives at element
+ * flat_off of the flat gradient buffer, inside the bucket [own_start, own_start + own_len) that the
+ * ranks own in `world` equal float4 slices (the slicing of the two-shot all-reduce).  Whenever an output
+ * tile is complete on this rank, its float4s owned by another rank r are stored -- over NVLink, as the
+ * GEMM tiles finish -- into peer_stage[r] at  stage_base + (rank * per4 + j) * 4,  j = index inside
+ * r's slice, per4 = ceil(own_len / 4 / world).  The owner adds the W-1 staged copies to its own gradient
+ * in b200dp_reduce_staged_sgd.  tile_counters: >= taps * ceil(Cout/128) * Cin/block_n zeroed uints (left
+ * zero).  peer_stage: host array of `world` device pointers. */
+extern "C" int b200dp_conv_wgrad_push(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin,
+                                      int Cout, int taps, int split_k, int block_n, unsigned int* tile_counters,
+                                      int n_counters, int world, int rank, void* const* peer_stage,
+                                      long long flat_off, long long own_start, long long own_len,
+                                      long long stage_base, b200dp_stream_t stream_) {
+  const WgradPushArgs push{tile_counters, n_counters, world, rank, peer_stage, flat_off, own_start, own_len,
+                           stage_base};
+  return conv_wgrad_impl(dy, x, dw, B, H, W, Cin, Cout, taps, Cin, split_k, 0, block_n,
+                         static_cast<cudaStream_t>(stream_), &push);
 }
 
 /* As b200dp_conv_wgrad with an explicit input-channel tile (64, 128 or 256; 0 = default). */

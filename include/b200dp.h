@@ -94,6 +94,19 @@ int b200dp_conv_dgrad_bn_reduce(const void* act, const void* wgt, void* out, flo
 int b200dp_conv_wgrad(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin, int Cout,
                       int taps, int cin_valid, int split_k, int accumulate, b200dp_stream_t stream);
 
+/* Weight gradient fused with the transfer half of the data-parallel reduce-scatter (experimental, never
+ * run in round 1).  As b200dp_conv_wgrad_tiled (dw zero on entry, all Cin columns), plus: the tensor sits
+ * at element flat_off of the flat gradient buffer, inside the bucket [own_start, own_start + own_len) that
+ * the ranks own in `world` equal float4 slices (the slicing of the two-shot all-reduce).  When an output
+ * tile is complete on this rank its float4s owned by rank r are stored over NVLink into peer_stage[r] at
+ * stage_base + (rank * per4 + j) * 4, j = index inside r's slice, per4 = ceil(own_len / 4 / world).
+ * tile_counters: >= taps * ceil(Cout/128) * Cin/block_n zeroed uints (left zero); peer_stage: host array
+ * of `world` device pointers.  The owner finishes the reduction in b200dp_reduce_staged_sgd. */
+int b200dp_conv_wgrad_push(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin, int Cout,
+                           int taps, int split_k, int block_n, unsigned int* tile_counters, int n_counters,
+                           int world, int rank, void* const* peer_stage, long long flat_off, long long own_start,
+                           long long own_len, long long stage_base, b200dp_stream_t stream);
+
 /* As b200dp_conv_wgrad with an explicit input-channel (GEMM N) tile: 64, 128 or 256; 0 = default. */
 int b200dp_conv_wgrad_tiled(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin, int Cout,
                             int taps, int cin_valid, int split_k, int accumulate, int block_n,
@@ -247,6 +260,14 @@ int b200dp_allreduce(void* comm, long long grad_off, long long param_off, long l
                      long long end, int fuse_sgd, int prescale, float lr, float momentum, float weight_decay,
                      int algo, int blocks, int channel, b200dp_stream_t stream);
 
+/* Owner-side half of the fused wgrad -> reduce-scatter path (experimental): bucket [start, end); inside
+ * [pushed_lo, pushed_hi) the mean gradient of my slice is (own + W-1 staged copies) / W, elsewhere it is
+ * pulled from the peers; then SGD and the updated parameters go to every rank (nvls = 1: multimem.st). */
+int b200dp_reduce_staged_sgd(void* comm, long long grad_off, long long param_off, long long mom_off,
+                             long long stage_buf_off, long long start, long long end, long long pushed_lo,
+                             long long pushed_hi, long long stage_base, float lr, float momentum,
+                             float weight_decay, int nvls, int blocks, int channel, b200dp_stream_t stream);
+
 /* Parameter server: `root` sums every rank's gradient in rank order starting from zero, divides
  * by the world size and stores the mean into every rank's gradient buffer
  * (ref: master/part2a/part2a.py:42-52).  push=1: workers first store their gradients into the
@@ -276,6 +297,10 @@ int b200dp_reducer_destroy(void* reducer);
 int b200dp_reducer_stream(void* reducer, void** stream_out);
 /* CTAs per bucket collective for subsequent bucket_ready() calls (re-capture the step afterwards). */
 int b200dp_reducer_set_blocks(void* reducer, int blocks);
+/* Experimental: per bucket, the element range delivered by b200dp_conv_wgrad_push and its staging area;
+ * such buckets run b200dp_reduce_staged_sgd instead of the all-reduce (pushed_lo == pushed_hi: unchanged). */
+int b200dp_reducer_set_staged(void* reducer, long long stage_buf_off, const long long* pushed_lo,
+                              const long long* pushed_hi, const long long* stage_base);
 
 #ifdef __cplusplus
 }

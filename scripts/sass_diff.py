@@ -18,7 +18,7 @@ def functions(path):
                 out[name] = body
             name, body = m.group(1), []
         elif name and "/*" in line:
-            body.append(line.strip())
+            body.append(" ".join(line.split()))   # column padding depends on the longest line of the dump
     if name:
         out[name] = body
     return out

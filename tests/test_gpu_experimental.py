@@ -189,3 +189,57 @@ def test_training_step_with_fused_head_matches_the_default():
     (l0, c0, g0), (l1, c1, g1) = res
     assert abs(l0 - l1) < 1e-4 and c0 == c1
     assert torch.nn.functional.cosine_similarity(g0, g1, dim=0).item() > 0.9995
+
+
+# ---------------------------------------------------------------------------------------------------
+# >= 2 GPUs: weight-gradient GEMM -> reduce-scatter in one kernel (B200DP_WGRAD_PUSH=1)
+# ---------------------------------------------------------------------------------------------------
+def _push_worker(rank, world, push, port, outdir):
+    import os as _os
+    _os.environ["B200DP_WGRAD_PUSH"] = "1" if push else "0"
+    _os.environ["LOCAL_RANK"] = str(rank)
+    from cs744_pytorch_distributed_tutorial_b200.config import TrainConfig
+    from cs744_pytorch_distributed_tutorial_b200.engine import Trainer
+    torch.cuda.set_device(rank)
+    cfg = TrainConfig(mode="part3", master_ip="127.0.0.1", num_nodes=world, rank=rank, port=port, device="cuda",
+                      per_rank_batch=32, eval=False, lr=0.01, timeout_s=60)
+    tr = Trainer(cfg)
+    nv = tr.backend.native
+    assert (nv.wgrad_push is not None) == bool(push)
+    init = nv.flat_params.cpu()
+    g = torch.Generator().manual_seed(300 + rank)
+    losses = []
+    for _ in range(3):
+        x = torch.randn(32, 3, 32, 32, generator=g).pin_memory()
+        y = torch.randint(0, 10, (32,), generator=g).pin_memory()
+        losses.append(float(tr.train_step(x, y).item()))
+    torch.cuda.synchronize()
+    torch.save({"params": nv.flat_params.cpu(), "init": init, "losses": losses},
+               _os.path.join(outdir, f"push{int(push)}_{rank}.pt"))
+    tr.close()
+
+
+@pytest.mark.multigpu
+def test_wgrad_push_reduce_scatter_matches_the_bucket_allreduce():
+    import sys
+    import tempfile
+    import torch.multiprocessing as mp
+    sys.path.insert(0, os.path.dirname(__file__))
+    from helpers import free_port
+    n = torch.cuda.device_count()
+    world = 8 if n >= 8 else 4 if n >= 4 else 2
+    res = {}
+    with tempfile.TemporaryDirectory() as d:
+        for push in (False, True):
+            mp.spawn(_push_worker, args=(world, push, free_port(), d), nprocs=world, join=True)
+            res[push] = [torch.load(os.path.join(d, f"push{int(push)}_{r}.pt")) for r in range(world)]
+    for push, ranks in res.items():
+        for r in ranks[1:]:
+            assert torch.equal(ranks[0]["params"], r["params"]), f"push={push}: replicas differ"
+    a, b = res[False][0], res[True][0]
+    assert torch.equal(a["init"], b["init"])
+    assert abs(a["losses"][0] - b["losses"][0]) < 1e-2
+    da, db = a["params"] - a["init"], b["params"] - b["init"]
+    cos = torch.nn.functional.cosine_similarity(da, db, dim=0).item()
+    assert cos > 0.97, cos
+    assert abs(db.norm().item() / da.norm().item() - 1) < 0.05

@@ -4,6 +4,7 @@
 // listens on "\0b200dp-<token>-<rank>" and peers connect, send one descriptor plus an integer tag,
 // and close.  (No counterpart in the reference: its gloo backend moves bytes over TCP only.)
 #include <errno.h>
+#include <poll.h>
 #include <stdio.h>
 #include <string.h>
 #include <sys/socket.h>
@@ -72,7 +73,17 @@ int fd_send(const std::string& name, int fd, int tag, int timeout_ms) {
 }
 
 // Accept one connection on `listen_fd` and return the descriptor it carries (tag through *tag).
-int fd_recv(int listen_fd, int* tag) {
+// timeout_ms < 0 waits for ever; otherwise -2 is returned when nobody connected in time.
+int fd_recv_timeout(int listen_fd, int* tag, int timeout_ms) {
+  if (timeout_ms >= 0) {
+    pollfd pfd{listen_fd, POLLIN, 0};
+    int rc;
+    do {
+      rc = ::poll(&pfd, 1, timeout_ms);
+    } while (rc < 0 && errno == EINTR);
+    if (rc == 0) return -2;
+    if (rc < 0) return -1;
+  }
   int s = ::accept(listen_fd, nullptr, nullptr);
   if (s < 0) return -1;
   msghdr msg{};
@@ -95,4 +106,17 @@ int fd_recv(int listen_fd, int* tag) {
   return fd;
 }
 
+int fd_recv(int listen_fd, int* tag) { return fd_recv_timeout(listen_fd, tag, -1); }
+
 }  // namespace b200dp
+
+// C entry points: the descriptor hand-off is host-only code, so it can be exercised without a GPU
+// (tests/test_cpu_runtime.py).  name: socket name in the abstract namespace, without the leading NUL.
+extern "C" int b200dp_fd_listen(const char* name) { return name ? b200dp::fd_listen(name) : -1; }
+extern "C" int b200dp_fd_send(const char* name, int fd, int tag, int timeout_ms) {
+  return name ? b200dp::fd_send(name, fd, tag, timeout_ms) : -1;
+}
+/* Returns the received descriptor (>= 0), -2 on timeout, -1 on error.  timeout_ms < 0: wait for ever. */
+extern "C" int b200dp_fd_recv(int listen_fd, int* tag, int timeout_ms) {
+  return b200dp::fd_recv_timeout(listen_fd, tag, timeout_ms);
+}

@@ -302,6 +302,13 @@ int b200dp_reducer_set_blocks(void* reducer, int blocks);
 int b200dp_reducer_set_staged(void* reducer, long long stage_buf_off, const long long* pushed_lo,
                               const long long* pushed_hi, const long long* stage_base);
 
+/* Descriptor hand-off between the ranks of one host (SCM_RIGHTS over abstract Unix sockets); how the
+ * virtual-memory heap and the NVSwitch multicast object are shared.  Host-only, testable without a GPU.
+ * b200dp_fd_recv returns the descriptor, -2 on timeout (timeout_ms < 0: wait for ever), -1 on error. */
+int b200dp_fd_listen(const char* name);
+int b200dp_fd_send(const char* name, int fd, int tag, int timeout_ms);
+int b200dp_fd_recv(int listen_fd, int* tag, int timeout_ms);
+
 #ifdef __cplusplus
 }
 #endif

@@ -137,3 +137,36 @@ def test_example_launcher_runs_two_ranks_of_part3_on_cpu():
     assert r.returncode == 0, r.stderr[-2000:]
     m = json.loads(r.stdout.strip().splitlines()[-1])
     assert m["mode"] == "part3" and m["world_size"] == 2
+
+
+def test_descriptor_handoff_over_abstract_unix_sockets():
+    """csrc/fdpass.cpp: how ranks exchange the POSIX handles of the VMM heap and the multicast object.
+    A pipe's write end travels through SCM_RIGHTS; what the receiver writes into its copy must come
+    out of the sender's read end.  Also: a receive with nobody connecting times out instead of hanging."""
+    import ctypes
+    import uuid
+    from cs744_pytorch_distributed_tutorial_b200.ops import _lib
+    lib = _lib.lib()
+    lib.b200dp_fd_listen.argtypes = [ctypes.c_char_p]
+    lib.b200dp_fd_send.argtypes = [ctypes.c_char_p, ctypes.c_int, ctypes.c_int, ctypes.c_int]
+    lib.b200dp_fd_recv.argtypes = [ctypes.c_int, ctypes.POINTER(ctypes.c_int), ctypes.c_int]
+    name = f"b200dp-test-{uuid.uuid4().hex}".encode()
+    lfd = lib.b200dp_fd_listen(name)
+    assert lfd >= 0
+    try:
+        tag = ctypes.c_int(-1)
+        assert lib.b200dp_fd_recv(lfd, ctypes.byref(tag), 50) == -2          # nobody there: bounded wait
+        r, w = os.pipe()
+        sent = []
+        t = threading.Thread(target=lambda: sent.append(lib.b200dp_fd_send(name, w, 42, 5000)))
+        t.start()
+        got = lib.b200dp_fd_recv(lfd, ctypes.byref(tag), 5000)
+        t.join()
+        assert sent == [0] and got >= 0 and got != w and tag.value == 42
+        os.write(got, b"through the copy")
+        assert os.read(r, 64) == b"through the copy"
+        for fd in (got, r, w):
+            os.close(fd)
+        assert lib.b200dp_fd_send(b"b200dp-nobody-listens-here", 0, 1, 100) == -1   # connect timeout
+    finally:
+        os.close(lfd)

@@ -170,3 +170,25 @@ def test_descriptor_handoff_over_abstract_unix_sockets():
         assert lib.b200dp_fd_send(b"b200dp-nobody-listens-here", 0, 1, 100) == -1   # connect timeout
     finally:
         os.close(lfd)
+
+
+@pytest.mark.parametrize("fn,args,needle", [
+    ("b200dp_conv_igemm", (None, None, None, None, None, 4, 8, 8, 48, 64, 9, 0, None), "unsupported shape"),
+    ("b200dp_conv_igemm", (None, None, None, None, None, 4, 8, 8, 64, 64, 5, 0, None), "taps=5"),
+    ("b200dp_conv_igemm", (None, None, None, None, None, 4, 6, 6, 64, 64, 9, 0, None), "cannot be tiled"),
+    ("b200dp_conv_wgrad", (None, None, None, 4, 8, 8, 64, 96, 9, 64, 0, 0, None), "Cout=96"),
+    ("b200dp_bn_stats", (None, None, 100, 12, None), "C=12"),
+    ("b200dp_linear_fwd", (None, None, None, None, 4, 13, 10, None), "multiple of 8"),
+    ("b200dp_linear_fwd", (None, None, None, None, 4, 16, 40, None), "O=40"),
+    ("b200dp_head_fwd_bwd", (None,) * 11 + (4, 4096, 10, 1.0, None), "F=4096"),
+    ("b200dp_conv_dgrad_bn_reduce", (None,) * 8 + (4, 8, 8, 64, 64, 9, 0, 1, 0, None), "are required"),
+    ("b200dp_bn_relu_pool_bwd_reduce_from_out", (None, None, None, None, None, 0, 64, None), "unsupported shape"),
+])
+def test_entry_points_reject_bad_arguments_before_touching_the_gpu(fn, args, needle):
+    """Fail loudly: shape / argument errors come back as a code plus a message naming the problem
+    (b200dp_last_error), on any host, without a CUDA call having been made."""
+    import cs744_pytorch_distributed_tutorial_b200.parallel.comm  # noqa: F401  (declares the comm prototypes)
+    from cs744_pytorch_distributed_tutorial_b200.ops._lib import NativeError, call
+    with pytest.raises(NativeError) as e:
+        call(fn, *args)
+    assert needle in str(e.value) and "code -22" in str(e.value)

@@ -135,10 +135,16 @@ def self_first_is_64(module: nn.Module) -> bool:
 _TUNE_CACHE: Dict[tuple, object] = {}   # (kind, B, hw, cin, cout, taps) -> best tile config, per process
 
 
+# experimental (not yet validated on hardware): offer the persistent conv kernel (cta_pair code 2) to the tuner
+PERSIST_CANDIDATES = os.environ.get("B200DP_PERSIST", "0") != "0"
+
+
 def _igemm_candidates(m_tiles: int, n_total: int, total_kb: int):
     """(block_n, split_k, cta_pair) triples worth timing: every N tile, K splits while the grid is
     small, and the tcgen05 cta_group::2 kernel wherever the tile count allows pairing."""
     out = []
+    if PERSIST_CANDIDATES:
+        out += [(bn, 1, 2) for bn in (64, 128, 256) if n_total % bn == 0 and m_tiles * (n_total // bn) > 148]
     for bn in (32, 64, 128, 256):
         if n_total % bn:
             continue
@@ -516,7 +522,7 @@ class NativeVGG:
             # the tensor pipe ~40% busy on its own).  The bucket-ready signal is recorded on that stream.
             if side is not None:
                 self._wgrad_fork[i].record(main)
-            if i > 0 and DGRAD_BN_REDUCE:
+            if i > 0 and DGRAD_BN_REDUCE and b.dgrad_pair != 2:   # (the persistent kernel has no bn-reduce flavour)
                 prev = self.blocks[i - 1]
                 K.conv_dgrad_bn_reduce(b.dy[:B], b.wd, prev.dout[:B], prev.out[:B], prev.gamma, prev.beta, prev.sums,
                                        block_n=b.dgrad_block_n, split_k=b.dgrad_split_k, cta_pair=b.dgrad_pair,

@@ -25,6 +25,7 @@ _PROTOTYPES = {
     "b200dp_conv_igemm": [P, P, P, P, P, I, I, I, I, I, I, I, P],
     "b200dp_conv_igemm_splitk": [P, P, P, P, P, P, I, I, I, I, I, I, I, I, P],
     "b200dp_conv_igemm_pair": [P, P, P, P, P, P, I, I, I, I, I, I, I, I, P],
+    "b200dp_conv_igemm_persist": [P, P, P, P, P, I, I, I, I, I, I, I, P],
     "b200dp_conv_dgrad_bn_reduce": [P, P, P, P, P, P, P, P, I, I, I, I, I, I, I, I, I, P],
     "b200dp_conv_wgrad": [P, P, P, I, I, I, I, I, I, I, I, I, P],
     "b200dp_conv_wgrad_tiled": [P, P, P, I, I, I, I, I, I, I, I, I, I, P],

@@ -47,6 +47,12 @@ def conv_igemm(act: torch.Tensor, wgt: torch.Tensor, bias: Optional[torch.Tensor
     Cout = wgt.shape[0]
     assert wgt.shape[1] == taps * Cin, (wgt.shape, taps, Cin)
     assert out.shape == (B, H, W, Cout)
+    if cta_pair == 2:
+        # experimental persistent kernel (one CTA per SM, double-buffered TMEM accumulator); no split-K
+        assert split_k == 1
+        call("b200dp_conv_igemm_persist", ptr(act), ptr(wgt), ptr(bias), ptr(out), ptr(stats), B, H, W, Cin, Cout,
+             taps, block_n, stream_ptr())
+        return out
     if cta_pair:
         # tcgen05 cta_group::2: a 256 x block_n tile per pair of SMs, each staging half of the weight tile
         if split_k > 1:

@@ -470,6 +470,209 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads)
   conv_igemm_2cta_body<BLOCK_N, STAGES, true>(tmA, tmB, p);
 }
 
+// ---------------------------------------------------------------------------
+// Persistent variant (experimental, B200DP_PERSIST=1 makes it a tile-shape candidate of the autotuner):
+// one CTA per SM walks the output tiles t = blockIdx.x, blockIdx.x + gridDim.x, ...  The accumulator is
+// double-buffered in TMEM (2 x BLOCK_N columns), so the epilogue of tile i (tcgen05.ld, bias, bf16,
+// stores, statistics) runs while the TMA producer and the MMA thread are already on tile i+1: the
+// SM's operand pipe, which is what bounds these layers, never drains between tiles, and barrier
+// setup / TMEM allocation / descriptor prefetch are paid once per SM instead of once per tile.
+// No split-K.  Statistics use their own shared-memory scratch (the stage buffers are never idle here).
+// ---------------------------------------------------------------------------
+struct IgemmPersistParams : IgemmParams {
+  int m_tiles, total_tiles;
+};
+
+template <int BLOCK_N, int STAGES>
+__global__ void __launch_bounds__(kNumThreads, 1)
+    conv_igemm_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                              const IgemmPersistParams p) {
+  constexpr int kBStageBytes = BLOCK_N * kBlockK * 2;
+  constexpr int kStageBytes = kAStageBytes + kBStageBytes;
+  constexpr uint32_t kAccCols = BLOCK_N < 32 ? 32 : BLOCK_N;
+  constexpr uint32_t kTmemCols = 2 * kAccCols;
+  constexpr uint32_t kIdesc = umma_idesc_bf16(kBlockM, BLOCK_N, 0, 0);
+  constexpr int kScratchBytes = 4 * 2 * BLOCK_N * 4;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  float* scratch = reinterpret_cast<float*>(smem + STAGES * kStageBytes);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * kStageBytes + kScratchBytes);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full_bar = empty_bar + STAGES;   // [2]
+  uint64_t* tmem_empty_bar = tmem_full_bar + 2;   // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  pdl_launch_dependents();
+  const int total_kb = p.taps * p.cin_blocks;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&tmem_full_bar[b], 1);   // one tcgen05.commit per tile
+      mbar_init(&tmem_empty_bar[b], 4);  // one arrive per epilogue warp once its TMEM reads are done
+    }
+    mbar_fence_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, kTmemCols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();
+
+  if (warp == 0) {
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x) {
+        const int m_tile = t % p.m_tiles, n_tile = t / p.m_tiles;
+        int n0, h0;
+        if (p.TN == 1) {
+          const int tiles_per_img = p.H / p.TH;
+          n0 = m_tile / tiles_per_img;
+          h0 = (m_tile - n0 * tiles_per_img) * p.TH;
+        } else {
+          n0 = m_tile * p.TN;
+          h0 = 0;
+        }
+        for (int kb = 0; kb < total_kb; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          mbar_arrive_expect_tx(&full_bar[stage], kStageBytes);
+          const int tap = kb / p.cin_blocks;
+          const int cb = kb - tap * p.cin_blocks;
+          int dr = 0, ds = 0;
+          if (p.taps == 9) {
+            dr = tap / 3 - 1;
+            ds = tap % 3 - 1;
+          }
+          uint8_t* a_dst = smem + stage * kStageBytes;
+          tma_load_4d(a_dst, &tmA, &full_bar[stage], cb * kBlockK, ds, h0 + dr, n0);
+          tma_load_2d(a_dst + kAStageBytes, &tmB, &full_bar[stage], kb * kBlockK, n_tile * BLOCK_N);
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++it) {
+        const int buf = it & 1;
+        const uint32_t use = static_cast<uint32_t>(it >> 1) & 1u;
+        mbar_wait(&tmem_empty_bar[buf], use ^ 1);  // the epilogue has drained this accumulator (first use: free)
+        tc_fence_after();
+        const uint32_t acc = tmem_base + static_cast<uint32_t>(buf) * kAccCols;
+        for (int kb = 0; kb < total_kb; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(smem + stage * kStageBytes);
+          const uint32_t b_addr = a_addr + kAStageBytes;
+#pragma unroll
+          for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+            const uint64_t da = umma_smem_desc(a_addr + k * kUmmaK * 2, 16, 1024);
+            const uint64_t db = umma_smem_desc(b_addr + k * kUmmaK * 2, 16, 1024);
+            umma_bf16(acc, da, db, kIdesc, (kb | k) != 0);
+          }
+          umma_commit(&empty_bar[stage]);
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit(&tmem_full_bar[buf]);
+      }
+    }
+  } else {
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    int it = 0;
+    for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++it) {
+      const int m_tile = t % p.m_tiles, n_tile = t / p.m_tiles;
+      const int buf = it & 1;
+      const uint32_t use = static_cast<uint32_t>(it >> 1) & 1u;
+      const long m = static_cast<long>(m_tile) * kBlockM + row;
+      const bool valid = m < p.m_total;
+      __nv_bfloat16* out_row = p.out + m * p.n_total + n_tile * BLOCK_N;
+      mbar_wait(&tmem_full_bar[buf], use);
+      tc_fence_after();
+      const uint32_t acc = tmem_base + static_cast<uint32_t>(buf) * kAccCols + (static_cast<uint32_t>(q * 32) << 16);
+#pragma unroll 1
+      for (int c = 0; c < BLOCK_N; c += 32) {
+        uint32_t v[32];
+        tmem_ld_32x32(acc + c, v);
+        tmem_ld_wait();
+        if (c + 32 >= BLOCK_N) {
+          // last read of this accumulator: hand it back so that the MMA thread can start tile it + 2
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tmem_empty_bar[buf]);
+        }
+        float f[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+        if (p.bias != nullptr) {
+          const float* b = p.bias + n_tile * BLOCK_N + c;
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] += __ldg(b + j);
+        }
+        uint32_t packed[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) packed[j] = pack_bf16x2(f[2 * j], f[2 * j + 1]);
+        if (valid) {
+          uint4* dst = reinterpret_cast<uint4*>(out_row + c);
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            dst[j] = make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
+        }
+        if (p.stats != nullptr) {
+          float s1[32], s2[32];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const float2 r = unpack_bf16x2(packed[j]);
+            s1[2 * j] = valid ? r.x : 0.f;
+            s1[2 * j + 1] = valid ? r.y : 0.f;
+            s2[2 * j] = s1[2 * j] * s1[2 * j];
+            s2[2 * j + 1] = s1[2 * j + 1] * s1[2 * j + 1];
+          }
+          const float t1 = warp_transpose_sum(s1, lane);
+          const float t2 = warp_transpose_sum(s2, lane);
+          scratch[q * 2 * BLOCK_N + c + lane] = t1;
+          scratch[q * 2 * BLOCK_N + BLOCK_N + c + lane] = t2;
+        }
+      }
+      if (p.stats != nullptr) {
+        asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps: partials complete
+        for (int i = static_cast<int>(threadIdx.x) - 64; i < 2 * BLOCK_N; i += 128) {
+          const float tsum = scratch[i] + scratch[2 * BLOCK_N + i] + scratch[4 * BLOCK_N + i] + scratch[6 * BLOCK_N + i];
+          const int half = i / BLOCK_N;
+          atomicAdd(p.stats + half * p.n_total + n_tile * BLOCK_N + (i - half * BLOCK_N), tsum);
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");  // scratch may be overwritten by the next tile
+      }
+    }
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, kTmemCols);
+  }
+}
+
 // Split-K epilogue: partial fp32 [M][N] -> (+bias) -> bf16 out, fused BatchNorm statistics of the
 // rounded values, and the workspace is cleared again for its next user.
 __global__ void __launch_bounds__(256) splitk_finalize_kernel(float* __restrict__ partial,
@@ -949,6 +1152,25 @@ static int launch_igemm_2cta(const CUtensorMap& tmA, const CUtensorMap& tmB, con
 }
 
 template <int BLOCK_N, int STAGES>
+static int launch_igemm_persist(const CUtensorMap& tmA, const CUtensorMap& tmB, const IgemmPersistParams& p,
+                                cudaStream_t stream) {
+  constexpr int smem = STAGES * (kAStageBytes + BLOCK_N * kBlockK * 2) + 4 * 2 * BLOCK_N * 4 + 1024 + 256;
+  static bool configured = false;
+  static int sms = 0;
+  auto kern = conv_igemm_persist_kernel<BLOCK_N, STAGES>;
+  if (!configured) {
+    B200DP_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    int dev = 0;
+    B200DP_CUDA_TRY(cudaGetDevice(&dev));
+    B200DP_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    configured = true;
+  }
+  const int grid = p.total_tiles < sms ? p.total_tiles : sms;
+  B200DP_CUDA_TRY(launch_pdl(kern, dim3(grid), dim3(kNumThreads), smem, stream, tmA, tmB, p));
+  return 0;
+}
+
+template <int BLOCK_N, int STAGES>
 static int launch_dgrad_bnr(const CUtensorMap& tmA, const CUtensorMap& tmB, const IgemmParams& p, int m_tiles,
                             int splits, cudaStream_t stream) {
   constexpr int smem = STAGES * (kAStageBytes + BLOCK_N * kBlockK * 2) + 1024 + 256;
@@ -1092,16 +1314,33 @@ static int conv_igemm_impl(const void* act, const void* wgt, const float* bias, 
     int rc = make_tmap(&tmA, act, 4, dims, box);
     if (rc) return rc;
   }
-  if (cta_pair && ((m_tiles & 1) || block_n < 64)) {
+  if (cta_pair == 1 && ((m_tiles & 1) || block_n < 64)) {
     set_error("conv_igemm: the CTA-pair kernel needs an even number of 128-pixel tiles (got %d) and block_n >= 64",
               m_tiles);
     return B200DP_EINVAL;
   }
   {
     const uint64_t dims[2] = {(uint64_t)taps * Cin, (uint64_t)Cout};
-    const uint32_t box[2] = {64, (uint32_t)(cta_pair ? block_n / 2 : block_n)};
+    const uint32_t box[2] = {64, (uint32_t)(cta_pair == 1 ? block_n / 2 : block_n)};
     int rc = make_tmap(&tmB, wgt, 2, dims, box);
     if (rc) return rc;
+  }
+  if (cta_pair == 2) {
+    // persistent 1-CTA kernel; statistics always go through shared memory, no split-K, no bnr
+    if (split_k != 1 || bnr != nullptr || block_n < 64) {
+      set_error("conv_igemm: the persistent kernel takes block_n in {64,128,256}, split_k = 1 and no bn-reduce");
+      return B200DP_EINVAL;
+    }
+    IgemmPersistParams pp{};
+    static_cast<IgemmParams&>(pp) = p;
+    pp.m_tiles = m_tiles;
+    pp.total_tiles = m_tiles * (Cout / block_n);
+    switch (block_n) {
+      case 256: return launch_igemm_persist<256, 4>(tmA, tmB, pp, stream);
+      case 128: return launch_igemm_persist<128, 6>(tmA, tmB, pp, stream);
+      case 64: return launch_igemm_persist<64, 8>(tmA, tmB, pp, stream);
+      default: set_error("conv_igemm: block_n=%d not in {64,128,256} for the persistent kernel", block_n); return B200DP_EINVAL;
+    }
   }
   int rc;
   if (bnr != nullptr) {
@@ -1113,7 +1352,7 @@ static int conv_igemm_impl(const void* act, const void* wgt, const float* bias, 
     p.bnr_gamma = bnr->gamma;
     p.bnr_beta = bnr->beta;
     p.bnr_sums = bnr->sums;
-    if (cta_pair) {
+    if (cta_pair == 1) {
       switch (block_n) {
         case 256: rc = launch_dgrad_bnr_2cta<256, 6>(tmA, tmB, p, m_tiles, split_k, stream); break;
         case 128: rc = launch_dgrad_bnr_2cta<128, 6>(tmA, tmB, p, m_tiles, split_k, stream); break;
@@ -1141,7 +1380,7 @@ static int conv_igemm_impl(const void* act, const void* wgt, const float* bias, 
                                p.bnr_sums, static_cast<long>(p.m_total), Cout));
     return 0;
   }
-  if (cta_pair) {
+  if (cta_pair == 1) {
     switch (block_n) {
       case 256: rc = launch_igemm_2cta<256, 6>(tmA, tmB, p, m_tiles, split_k, stream); break;
       case 128: rc = launch_igemm_2cta<128, 6>(tmA, tmB, p, m_tiles, split_k, stream); break;
@@ -1214,6 +1453,17 @@ extern "C" int b200dp_conv_dgrad_bn_reduce(const void* act, const void* wgt, voi
   const BnReduceArgs bnr{bn_out, gamma, beta, sums};
   return conv_igemm_impl(act, wgt, nullptr, out, nullptr, workspace, B, H, W, Cin, Cout, taps, block_n, split_k,
                          cta_pair, static_cast<cudaStream_t>(stream_), &bnr);
+}
+
+/* Persistent variant of b200dp_conv_igemm (experimental): one CTA per SM walks the output tiles with the
+ * accumulator double-buffered in TMEM, so a tile's epilogue overlaps the next tile's loads and MMAs.
+ * block_n in {64,128,256}; no split-K. */
+extern "C" int b200dp_conv_igemm_persist(const void* act, const void* wgt, const float* bias, void* out,
+                                         float* stats, int B, int H, int W, int Cin, int Cout, int taps,
+                                         int block_n, b200dp_stream_t stream_) {
+  if (block_n == 0) block_n = (Cout % 128 == 0) ? 128 : 64;
+  return conv_igemm_impl(act, wgt, bias, out, stats, nullptr, B, H, W, Cin, Cout, taps, block_n, 1, 2,
+                         static_cast<cudaStream_t>(stream_));
 }
 
 static int conv_wgrad_impl(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin, int Cout, int taps,

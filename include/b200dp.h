@@ -84,6 +84,13 @@ int b200dp_conv_dgrad_bn_reduce(const void* act, const void* wgt, void* out, flo
                                 const float* gamma, const float* beta, float* sums, int B, int H, int W, int Cin,
                                 int Cout, int taps, int block_n, int split_k, int cta_pair, b200dp_stream_t stream);
 
+/* Persistent variant of b200dp_conv_igemm (experimental, never run in round 1): one CTA per SM walks the
+ * output tiles, the accumulator is double-buffered in TMEM, so a tile's epilogue overlaps the next tile's
+ * loads and MMAs.  block_n in {64,128,256} (0 = choose); no split-K. */
+int b200dp_conv_igemm_persist(const void* act, const void* wgt, const float* bias, void* out, float* stats,
+                              int B, int H, int W, int Cin, int Cout, int taps, int block_n,
+                              b200dp_stream_t stream);
+
 /* dW[Cout][taps][cin_valid] (fp32) += sum over pixels dY[p][Cout] * X[p + tap][Cin].
  * dy: bf16 [B,H,W,Cout]; x: bf16 [B,H,W,Cin].  Both operands are consumed
  * MN-major straight from their NHWC layout.  split_k = 0 chooses a split that

@@ -243,3 +243,34 @@ def test_wgrad_push_reduce_scatter_matches_the_bucket_allreduce():
     cos = torch.nn.functional.cosine_similarity(da, db, dim=0).item()
     assert cos > 0.97, cos
     assert abs(db.norm().item() / da.norm().item() - 1) < 0.05
+
+
+# (B, H, W, Cin, Cout): more tiles than SMs, exactly as many, fewer, and a partly valid last tile
+PERSIST_SHAPES = [(256, 16, 16, 64, 128), (64, 8, 8, 128, 256), (296, 4, 4, 256, 512), (32, 4, 4, 512, 512),
+                  (30, 2, 2, 512, 512), (8, 32, 32, 64, 64)]
+
+
+@pytest.mark.parametrize("shape", PERSIST_SHAPES)
+@pytest.mark.parametrize("block_n", [64, 128, 256])
+@pytest.mark.parametrize("with_stats", [True, False])
+def test_persistent_conv_matches_the_one_tile_per_cta_kernel(shape, block_n, with_stats):
+    """Same bits as conv_igemm with the same N tile (same accumulation order), same statistics."""
+    native = _native()
+    B, H, W, Cin, Cout = shape
+    if Cout % block_n:
+        pytest.skip("block_n does not divide Cout")
+    g = torch.Generator(device=DEV).manual_seed(21)
+    x = torch.randn(B, H, W, Cin, device=DEV, generator=g).bfloat16()
+    w = (torch.randn(Cout, 9 * Cin, device=DEV, generator=g) / (3 * Cin ** 0.5)).bfloat16()
+    bias = torch.randn(Cout, device=DEV, generator=g) if with_stats else None
+    ref = torch.empty(B, H, W, Cout, device=DEV, dtype=torch.bfloat16)
+    st_ref = torch.zeros(2 * Cout, device=DEV) if with_stats else None
+    native.conv_igemm(x, w, bias, ref, stats=st_ref, block_n=block_n)
+    for rep in range(2):
+        out = torch.full_like(ref, float("nan"))
+        st = torch.zeros(2 * Cout, device=DEV) if with_stats else None
+        native.conv_igemm(x, w, bias, out, stats=st, block_n=block_n, cta_pair=2)
+        torch.cuda.synchronize()
+        assert torch.equal(out, ref)
+        if with_stats:
+            torch.testing.assert_close(st, st_ref, rtol=1e-4, atol=1e-3)

@@ -274,3 +274,23 @@ def test_persistent_conv_matches_the_one_tile_per_cta_kernel(shape, block_n, wit
         assert torch.equal(out, ref)
         if with_stats:
             torch.testing.assert_close(st, st_ref, rtol=1e-4, atol=1e-3)
+
+
+def test_classifier_forward_runs_on_the_tcgen05_gemm_kernel_too():
+    """The 512 -> 10 linear layer as a taps=1 implicit GEMM on the tensor cores (weights padded to 32
+    rows): same kernel as layer 0.  Not the default: the whole layer is 2.6 MFLOP, less than the fixed
+    cost of a TMEM / TMA pipeline, and the GEMM kernel stores bf16 logits."""
+    native = _native()
+    B, Fd, O = 256, 512, 10
+    g = torch.Generator(device=DEV).manual_seed(4)
+    x = torch.randn(B, 1, 1, Fd, device=DEV, generator=g).bfloat16()
+    w = torch.zeros(32, Fd, device=DEV)
+    w[:O] = torch.randn(O, Fd, device=DEV, generator=g) * 0.05
+    b = torch.zeros(32, device=DEV)
+    b[:O] = torch.randn(O, device=DEV, generator=g) * 0.1
+    out = torch.empty(B, 1, 1, 32, device=DEV, dtype=torch.bfloat16)
+    native.conv_igemm(x, w.bfloat16().contiguous(), b, out, taps=1, block_n=32)
+    torch.cuda.synchronize()
+    ref = x.float().view(B, Fd) @ w.bfloat16().float().t() + b
+    torch.testing.assert_close(out.float().view(B, 32)[:, :O], ref[:, :O], rtol=2e-2, atol=2e-2)
+    assert float(out.float().view(B, 32)[:, O:].abs().max()) == 0.0

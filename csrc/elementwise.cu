@@ -1028,8 +1028,8 @@ __global__ void __launch_bounds__(kHeadWarps * 32)
     float tl = 0.f;
     int tc = 0;
     for (unsigned k = 0; k < gridDim.x; ++k) {
-      tl += *(volatile float*)&g_head_loss_part[k];
-      tc += *(volatile int*)&g_head_corr_part[k];
+      tl += __ldcg(&g_head_loss_part[k]);   // L2: written by other blocks before their ticket
+      tc += __ldcg(&g_head_corr_part[k]);
     }
     if (loss != nullptr) *loss = tl / static_cast<float>(B);
     if (correct != nullptr) *correct = tc;

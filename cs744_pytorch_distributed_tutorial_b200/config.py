@@ -45,7 +45,7 @@ class TrainConfig:
     dtype: str = "bf16"         # compute dtype of the native GPU path (fp32 master weights)
     backend: str = "auto"       # auto | gloo | nccl | native  (native = in-kernel NVLink collectives)
     sync_impl: str = "auto"     # auto | torch | native
-    bucket_plan: str = "layer"  # layer (8 buckets) | ddp (torch's 3 buckets) | single
+    bucket_plan: str = "layer"  # layer (8 buckets) | ddp (torch's 3 buckets) | single | cap:<MiB>
     fuse_optimizer: bool = True  # SGD in the collective epilogue where the mode allows it
     # CTAs of a side-stream bucket kernel (part3); the GEMMs keep the other SMs.  Three 9.4 MB buckets
     # become ready in the first ~100 us of backward; 16 CTAs could not drain them before backward ended

@@ -90,7 +90,8 @@ class FlatLayout:
         """``layer``: one bucket per conv layer in gradient-ready order, the small tensors
         folded into the neighbouring conv's bucket.  ``ddp``: torch DDP's size
         caps (1 MiB first bucket, 25 MiB afterwards; ref: master/part3/part3.py:116 and the
-        probe in SURVEY.md 2.9).  ``single``: everything in one bucket (DDP's first iteration)."""
+        probe in SURVEY.md 2.9).  ``single``: everything in one bucket (DDP's first iteration).
+        ``cap:<MiB>``: greedy buckets of at least that size, closed at conv-layer boundaries."""
         groups: List[List[FlatEntry]] = []
         if plan == "single":
             groups = [list(self.entries)]
@@ -113,6 +114,28 @@ class FlatLayout:
                     cur, size, cap = [], 0, 25 << 20
             if cur:
                 groups.append(cur)
+        elif plan.startswith("cap:"):
+            # greedy grouping in gradient-ready order, a bucket closes at the first conv weight that takes
+            # it to <n> MiB or more (e.g. cap:12 -> 18.9 / 14.2 / 3.9 MB on VGG-11): fewer launches and
+            # barrier round trips than "layer", earlier readiness than "ddp"
+            try:
+                cap = float(plan[4:]) * (1 << 20)
+            except ValueError:
+                raise ValueError(f"bucket plan {plan!r}: expected cap:<MiB>") from None
+            if cap <= 0:
+                raise ValueError(f"bucket plan {plan!r}: the cap must be positive")
+            cur, size = [], 0
+            for e in self.entries:
+                cur.append(e)
+                size += 4 * e.numel
+                if e.kind == "conv_w" and size >= cap:
+                    groups.append(cur)
+                    cur, size = [], 0
+            if cur:
+                if groups and not any(e.kind == "conv_w" for e in cur):
+                    groups[-1].extend(cur)
+                else:
+                    groups.append(cur)
         else:
             raise ValueError(f"unknown bucket plan {plan!r}")
         out: List[Bucket] = []

@@ -29,6 +29,11 @@ else
     v=$(env $cfg timeout 200 $RUN bench.py --gpus $N --steps 100 --no-e2e 2>&1 | ms)
     echo "  [${cfg:-baseline}] ms/step=$v" | tee -a $OUT/ab_${N}gpu.log
   done
+  echo "== bucket plans"
+  for bp in layer cap:9 cap:12 ddp single; do
+    v=$(timeout 200 $RUN bench.py --gpus $N --steps 100 --no-e2e --bucket-plan $bp 2>&1 | ms)
+    echo "  [bucket-plan $bp] ms/step=$v" | tee -a $OUT/ab_${N}gpu.log
+  done
   echo "== reducer CTAs"
   for cb in 16 24 32 48 64; do
     v=$(timeout 200 $RUN bench.py --gpus $N --steps 100 --no-e2e --comm-blocks $cb 2>&1 | ms)

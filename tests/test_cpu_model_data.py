@@ -123,6 +123,16 @@ def test_flat_layout_and_bucket_plans():
     mb = [b.nbytes / 1e6 for b in ddp]
     assert 9.4 < mb[0] < 9.5 and 27.1 < mb[1] < 27.2 and 0.25 < mb[2] < 0.35
     assert len(L.buckets("single")) == 1
+    # size-capped plan: closes at conv-layer boundaries, covers everything exactly once, in order
+    cap = L.buckets("cap:12")
+    assert [round(b.nbytes / 1e6, 1) for b in cap] == [18.9, 14.2, 3.9]
+    assert cap[0].start == 0 and cap[-1].end == L.total and all(a.end == b.start for a, b in zip(cap, cap[1:]))
+    assert sorted(n for b in cap for n in b.names) == sorted(e.name for e in L.entries)
+    assert len(L.buckets("cap:1000")) == 1 and len(L.buckets("cap:0.001")) == 8
+    with pytest.raises(ValueError):
+        L.buckets("cap:x")
+    with pytest.raises(ValueError):
+        L.buckets("nonsense")
 
 
 def test_config_defaults_are_reference_literals_and_validated():

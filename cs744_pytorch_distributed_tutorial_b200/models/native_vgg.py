@@ -158,15 +158,18 @@ def self_first_is_64(module: nn.Module) -> bool:
 _TUNE_CACHE: Dict[tuple, object] = {}   # (kind, B, hw, cin, cout, taps) -> best tile config, per process
 
 
-# experimental (not yet validated on hardware): offer the persistent conv kernel (cta_pair code 2) to the tuner
-PERSIST_CANDIDATES = os.environ.get("B200DP_PERSIST", "0") != "0"
+# experimental (not yet validated on hardware): offer the persistent conv kernel (cta_pair code 2) to the tuner.
+# "1": forward convs only -- a persistent dgrad holds ~200 KB of shared memory on every SM, which would push
+# the concurrent weight-gradient kernels off the SMs (the tuner times kernels in isolation and cannot see
+# that); "2": dgrad as well.
+PERSIST_CANDIDATES = int(os.environ.get("B200DP_PERSIST", "0") or 0)
 
 
-def _igemm_candidates(m_tiles: int, n_total: int, total_kb: int):
+def _igemm_candidates(m_tiles: int, n_total: int, total_kb: int, persist: bool = False):
     """(block_n, split_k, cta_pair) triples worth timing: every N tile, K splits while the grid is
     small, and the tcgen05 cta_group::2 kernel wherever the tile count allows pairing."""
     out = []
-    if PERSIST_CANDIDATES:
+    if persist:
         out += [(bn, 1, 2) for bn in (64, 128, 256) if n_total % bn == 0 and m_tiles * (n_total // bn) > 148]
     for bn in (32, 64, 128, 256):
         if n_total % bn:
@@ -399,7 +402,7 @@ class NativeVGG:
                     t = {c: _time_captured(lambda c=c: K.conv_igemm(x_in, b.wf, b.bias, y, stats=b.stats, taps=b.taps,
                                                                     block_n=c[0], split_k=c[1], cta_pair=c[2],
                                                                     workspace=self.splitk_ws))
-                         for c in _igemm_candidates(m_tiles, s.cout, b.taps * b.kin // 64)}
+                         for c in _igemm_candidates(m_tiles, s.cout, b.taps * b.kin // 64, PERSIST_CANDIDATES >= 1)}
                     _TUNE_CACHE[("fwd",) + key] = min(t, key=t.get)
                 b.fwd_block_n, b.fwd_split_k, b.fwd_pair = _TUNE_CACHE[("fwd",) + key]
                 if ("wgrad",) + key not in _TUNE_CACHE:
@@ -416,7 +419,7 @@ class NativeVGG:
                         t = {c: _time_captured(lambda c=c: K.conv_igemm(dy, b.wd, None, dprev, block_n=c[0],
                                                                         split_k=c[1], cta_pair=c[2],
                                                                         workspace=self.splitk_ws))
-                             for c in _igemm_candidates(m_tiles, s.cin, 9 * s.cout // 64)}
+                             for c in _igemm_candidates(m_tiles, s.cin, 9 * s.cout // 64, PERSIST_CANDIDATES >= 2)}
                         _TUNE_CACHE[("dgrad",) + key] = min(t, key=t.get)
                     b.dgrad_block_n, b.dgrad_split_k, b.dgrad_pair = _TUNE_CACHE[("dgrad",) + key]
         torch.cuda.current_stream().wait_stream(side)

@@ -48,6 +48,9 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--test-size", type=int, default=10000)
     p.add_argument("--real-data", action="store_true", help="use ../../data/cifar-10-batches-py if present")
     p.add_argument("--no-augment", action="store_true")
+    p.add_argument("--loader", choices=("python", "native"), default="python",
+                   help="batch assembly: vectorised torch ops, or the C++ thread pool of csrc/loader.cpp")
+    p.add_argument("--loader-threads", type=int, default=4)
     p.add_argument("--no-eval", action="store_true")
     p.add_argument("--checkpoint", type=str, default=None, help="save a checkpoint here after training")
     p.add_argument("--resume", type=str, default=None)
@@ -62,7 +65,7 @@ def config_from_args(argv=None) -> TrainConfig:
                        device=a.device, backend=a.backend, bucket_plan=a.bucket_plan,
                        fuse_optimizer=not a.no_fuse_optimizer, nvls={"auto": None, "on": True, "off": False}[a.nvls], cuda_graph=not a.no_cuda_graph,
                        train_size=a.train_size, test_size=a.test_size, synthetic=not a.real_data,
-                       augment=not a.no_augment, eval=not a.no_eval, checkpoint=a.checkpoint, resume=a.resume)
+                       augment=not a.no_augment, loader=a.loader, loader_threads=a.loader_threads, eval=not a.no_eval, checkpoint=a.checkpoint, resume=a.resume)
 
 
 def main(argv=None) -> int:

@@ -37,6 +37,11 @@ class TrainConfig:
     port: Optional[int] = None  # default: the reference port of the mode
     log_interval: int = 20      # ref: master/part2a/part2a.py:54
     num_workers: int = 2        # ref: master/part2a/part2a.py:109
+    # batch assembly for Trainer.fit: "python" = vectorised torch ops (data.BatchPipeline, ~20 k images/s),
+    # "native" = C++ threads (csrc/loader.cpp, > 300 k images/s per thread); same sampling, different
+    # augmentation draws
+    loader: str = "python"
+    loader_threads: int = 4
     cpu_threads: int = 4        # ref: master/part2a/part2a.py:18
     data_root: str = "../../data"
     # --- new knobs -------------------------------------------------------------------
@@ -79,6 +84,8 @@ class TrainConfig:
             raise ValueError(f"need 0 <= rank < num_nodes, got rank={self.rank} num_nodes={self.num_nodes}")
         if self.mode == "part1" and self.num_nodes != 1:
             raise ValueError("part1 is the single-process mode; use part2a/part2b/part3 for num_nodes > 1")
+        if self.loader not in ("python", "native"):
+            raise ValueError(f"loader must be 'python' or 'native', got {self.loader!r}")
         if self.port is None:
             self.port = REFERENCE_PORTS[self.mode]
         if self.per_rank_batch is None:

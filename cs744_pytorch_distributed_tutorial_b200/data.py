@@ -245,3 +245,110 @@ class BatchPipeline:
             augment_batch(self.data[sel], x, self._gen, self.augment)
             torch.index_select(self.targets, 0, sel, out=y)
             yield x, y
+
+
+class NativeBatchPipeline:
+    """``BatchPipeline`` with the batch assembly in C++ threads (csrc/loader.cpp): crop, flip, uint8 -> fp32
+    and normalisation are one table-lookup pass per image, ``ring`` batches are built ahead in order into
+    pinned buffers.  Same sampling as ``BatchPipeline`` (``ShardedSampler``); the augmentation draws come
+    from a counter-based generator keyed by (seed, epoch, position), so a run is reproducible for any
+    thread count (they are not the draws of the torch generator ``BatchPipeline`` uses).
+
+    A yielded batch stays valid until ``release_lag`` further batches have been requested; with a GPU
+    consumer call ``consumed(event)`` after issuing the host->device copy of the batch, and the slot is
+    only refilled once that event has completed."""
+
+    def __init__(self, dataset, batch: int, world: int = 1, rank: int = 0, train: bool = True, augment: bool = True,
+                 drop_last: bool = False, seed: int = 0, ring: int = 4, threads: int = 4, pin: Optional[bool] = None,
+                 release_lag: int = 2):
+        import collections
+        import ctypes
+        from .ops import _lib
+        if ring < release_lag + 2:
+            raise ValueError("ring must be at least release_lag + 2")
+        self._lib, self._ct = _lib.lib(), ctypes
+        self._images = np.ascontiguousarray(dataset.data, dtype=np.uint8)
+        self._labels = np.ascontiguousarray(dataset.targets, dtype=np.int64)
+        if self._images.shape[1:] != (32, 32, 3):
+            raise ValueError(f"expected uint8 images [N,32,32,3], got {self._images.shape}")
+        self.batch, self.train, self.augment, self.drop_last = batch, train, augment and train, drop_last
+        self.sampler = ShardedSampler(len(dataset), world if train else 1, rank if train else 0, shuffle=train,
+                                      seed=seed, drop_last=False)
+        pin = torch.cuda.is_available() if pin is None else pin
+        self._x = [torch.empty(batch, 3, 32, 32, pin_memory=pin) for _ in range(ring)]
+        self._y = [torch.empty(batch, dtype=torch.int64, pin_memory=pin) for _ in range(ring)]
+        vp = ctypes.c_void_p
+        xs = (vp * ring)(*[t.data_ptr() for t in self._x])
+        ys = (vp * ring)(*[t.data_ptr() for t in self._y])
+        mean = (ctypes.c_float * 3)(*CIFAR_MEAN)
+        std = (ctypes.c_float * 3)(*CIFAR_STD)
+        h = vp()
+        L = self._lib
+        L.b200dp_loader_create.argtypes = [vp, vp, ctypes.c_longlong, ctypes.c_int, ctypes.c_int, vp, vp, vp, vp,
+                                           ctypes.c_int, ctypes.c_ulonglong, ctypes.c_int, ctypes.POINTER(vp)]
+        L.b200dp_loader_start_epoch.argtypes = [vp, vp, ctypes.c_longlong, ctypes.c_longlong, ctypes.c_int]
+        L.b200dp_loader_next.argtypes = [vp, ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_int)]
+        L.b200dp_loader_release.argtypes = [vp, ctypes.c_int]
+        L.b200dp_loader_destroy.argtypes = [vp]
+        self._check(L.b200dp_loader_create(self._images.ctypes.data, self._labels.ctypes.data, len(self._labels), batch,
+                                           ring, xs, ys, mean, std, int(self.augment), seed * 7919 + rank, threads,
+                                           ctypes.byref(h)), "b200dp_loader_create")
+        self._h = h
+        self.release_lag = release_lag
+        self._held = collections.deque()
+        self._pending_event = None
+
+    def _check(self, rc: int, what: str) -> None:
+        if rc != 0:
+            from .ops._lib import NativeError
+            msg = self._lib.b200dp_last_error()
+            raise NativeError(f"{what} failed (code {rc}): {msg.decode() if msg else ''}")
+
+    def __len__(self) -> int:
+        n = len(self.sampler)
+        return n // self.batch if self.drop_last else math.ceil(n / self.batch)
+
+    @property
+    def dataset_len(self) -> int:
+        return self._images.shape[0]
+
+    def consumed(self, event=None) -> None:
+        """The batch yielded last has been handed to the device; ``event`` (a CUDA event recorded after its
+        host->device copy, or None) must have completed before its buffer is refilled."""
+        self._pending_event = event
+
+    def _release_oldest(self) -> None:
+        slot, ev = self._held.popleft()
+        if ev is not None:
+            ev.synchronize()
+        self._check(self._lib.b200dp_loader_release(self._h, slot), "b200dp_loader_release")
+
+    def __iter__(self):
+        ct = self._ct
+        order = np.ascontiguousarray(self.sampler.indices().numpy(), dtype=np.int64)
+        while self._held:                      # an abandoned epoch: wait for its copies, hand the slots back
+            self._release_oldest()
+        self._check(self._lib.b200dp_loader_start_epoch(self._h, order.ctypes.data, len(order), self.sampler.epoch,
+                                                        int(self.drop_last)), "b200dp_loader_start_epoch")
+        slot, count = ct.c_int(), ct.c_int()
+        while True:
+            rc = self._lib.b200dp_loader_next(self._h, ct.byref(slot), ct.byref(count))
+            if rc == 1:
+                break
+            self._check(rc, "b200dp_loader_next")
+            self._pending_event = None
+            yield self._x[slot.value][: count.value], self._y[slot.value][: count.value]
+            self._held.append((slot.value, self._pending_event))
+            while len(self._held) > self.release_lag:
+                self._release_oldest()
+
+    def close(self) -> None:
+        if getattr(self, "_h", None) is not None:
+            self._lib.b200dp_loader_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -100,6 +100,14 @@ class TorchBackend:
         correct = int((out.argmax(1) == target).sum().item())
         return loss, correct
 
+    def input_event(self):
+        """Event after which the host buffers passed to the last ``train_step`` may be overwritten."""
+        if self.device.type != "cuda":
+            return None
+        ev = torch.cuda.Event()
+        ev.record()
+        return ev
+
     def all_reduce_sum(self, value: float) -> float:
         if self.cfg.world_size == 1 or not self.dist.is_initialized():
             return value
@@ -199,6 +207,7 @@ class NativeBackend:
         self._loss_events: List[Optional[torch.cuda.Event]] = [None] * 64
         self._loss_idx = 0
         self.graph: Optional[torch.cuda.CUDAGraph] = None
+        self._last_input_event = None
         self.steps_done = 0
         self.launches_per_step = 0
         if cfg.cuda_graph:
@@ -253,6 +262,7 @@ class NativeBackend:
             self._stage_x[slot][: data.shape[0]].copy_(data, non_blocking=True)
             self._stage_y[slot][: target.shape[0]].copy_(target, non_blocking=True)
             self._copy_done[slot].record(self._copy_stream)
+        self._last_input_event = self._copy_done[slot]
         return slot
 
     def run_staged(self, slot: int) -> torch.Tensor:
@@ -279,6 +289,8 @@ class NativeBackend:
         nv = self.native
         x = data.to(self.device, non_blocking=True).float()
         y = target.to(self.device, non_blocking=True)
+        self._last_input_event = torch.cuda.Event()
+        self._last_input_event.record()
         self.sync.pre_forward()
         nv.forward(x, training=True)
         self.sync.post_forward()
@@ -290,6 +302,11 @@ class NativeBackend:
         self.sync.pre_forward()
         self.steps_done += 1
         return nv.loss
+
+    def input_event(self):
+        """Event after which the host buffers passed to the last ``train_step`` may be overwritten
+        (recorded on the copy stream behind the host->device copy, or on the compute stream for a ragged batch)."""
+        return self._last_input_event
 
     def read_loss_async(self) -> int:
         """Queue a device->host copy of the current loss; returns a ticket for ``loss_value``."""
@@ -415,6 +432,9 @@ class Trainer:
                 break
             clock.step_begin(batch_idx)
             loss = self.train_step(data, target)
+            if hasattr(loader, "consumed"):
+                # the loader may refill this batch's pinned buffer once its host->device copy is done
+                loader.consumed(self.backend.input_event())
             clock.step_end(batch_idx)
             n_iters += 1
             if batch_idx % cfg.log_interval == 0:
@@ -443,7 +463,7 @@ class Trainer:
         total_loss, correct, n_batches, n_samples = 0.0, 0, 0, 0
         for data, target in loader:
             loss, c = self.backend.eval_batch(data, target)
-            total_loss += float(loss)
+            total_loss += float(loss)      # host sync: the batch has been consumed
             correct += c
             n_batches += 1
             n_samples += int(target.shape[0])
@@ -455,13 +475,19 @@ class Trainer:
 
     def fit(self) -> Dict[str, float]:
         """The tutorial's job: one epoch of training, then the test pass."""
-        from .data import BatchPipeline, build_dataset
+        from .data import BatchPipeline, NativeBatchPipeline, build_dataset
         cfg = self.cfg
         train_set = build_dataset(cfg, True)
         test_set = build_dataset(cfg, False)
-        train = BatchPipeline(train_set, cfg.per_rank_batch, cfg.world_size, cfg.rank, train=True,
-                              augment=cfg.augment, drop_last=cfg.drop_last, seed=0)
-        test = BatchPipeline(test_set, cfg.per_rank_batch, train=False)
+        if cfg.loader == "native":
+            train = NativeBatchPipeline(train_set, cfg.per_rank_batch, cfg.world_size, cfg.rank, train=True,
+                                        augment=cfg.augment, drop_last=cfg.drop_last, seed=0,
+                                        threads=cfg.loader_threads)
+            test = NativeBatchPipeline(test_set, cfg.per_rank_batch, train=False, threads=cfg.loader_threads)
+        else:
+            train = BatchPipeline(train_set, cfg.per_rank_batch, cfg.world_size, cfg.rank, train=True,
+                                  augment=cfg.augment, drop_last=cfg.drop_last, seed=0)
+            test = BatchPipeline(test_set, cfg.per_rank_batch, train=False)
         out: Dict[str, float] = {}
         for epoch in range(cfg.epochs):
             train.sampler.set_epoch(epoch)

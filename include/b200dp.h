@@ -309,6 +309,24 @@ int b200dp_reducer_set_blocks(void* reducer, int blocks);
 int b200dp_reducer_set_staged(void* reducer, long long stage_buf_off, const long long* pushed_lo,
                               const long long* pushed_hi, const long long* stage_base);
 
+/* Native batch loader (csrc/loader.cpp; the role of torch's DataLoader worker processes for the reference):
+ * a pool of threads turns uint8 HWC CIFAR images into normalised fp32 NCHW batches -- RandomCrop(32,
+ * padding 4) + RandomHorizontalFlip + ToTensor + Normalize in one table-lookup pass -- inside caller-owned
+ * (pinned) buffers, in order, `ring` batches ahead.  Host-only.
+ *   images: uint8 [n][32][32][3], labels: int64 [n] (both must outlive the loader); xs / ys: `ring` output
+ *   buffers of batch*3*32*32 floats / batch int64; mean / std: 3 floats each.
+ *   start_epoch: `order` = the epoch's sample indices in consumption order (sharding / shuffling is the
+ *   caller's).  next: blocks for the next batch, returns 1 when the epoch is exhausted.  release: the
+ *   slot's contents are no longer needed (its host->device copy has completed). */
+int b200dp_loader_create(const void* images, const long long* labels, long long n, int batch, int ring,
+                         void* const* xs, void* const* ys, const float* mean, const float* std_, int augment,
+                         unsigned long long seed, int threads, void** out_loader);
+int b200dp_loader_start_epoch(void* loader, const long long* order, long long count, long long epoch,
+                              int drop_last);
+int b200dp_loader_next(void* loader, int* slot, int* count);
+int b200dp_loader_release(void* loader, int slot);
+int b200dp_loader_destroy(void* loader);
+
 /* Descriptor hand-off between the ranks of one host (SCM_RIGHTS over abstract Unix sockets); how the
  * virtual-memory heap and the NVSwitch multicast object are shared.  Host-only, testable without a GPU.
  * b200dp_fd_recv returns the descriptor, -2 on timeout (timeout_ms < 0: wait for ever), -1 on error. */

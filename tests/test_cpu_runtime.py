@@ -192,3 +192,13 @@ def test_entry_points_reject_bad_arguments_before_touching_the_gpu(fn, args, nee
     with pytest.raises(NativeError) as e:
         call(fn, *args)
     assert needle in str(e.value) and "code -22" in str(e.value)
+
+
+def test_cli_runs_with_the_native_loader():
+    cmd = [sys.executable, "-m", "cs744_pytorch_distributed_tutorial_b200.cli", "--mode", "part1", "--device", "cpu",
+           "--global-batch", "16", "--train-size", "72", "--test-size", "40", "--iters", "4", "--loader", "native",
+           "--loader-threads", "2"]
+    r = subprocess.run(cmd, cwd=REPO, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    m = json.loads(r.stdout.strip().splitlines()[-1])
+    assert m["iters"] == 4 and m["samples"] == 40

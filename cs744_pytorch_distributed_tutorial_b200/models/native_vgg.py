@@ -207,6 +207,7 @@ def _time_captured(fn, reps: int = 10, replays: int = 5) -> float:
 # tests/test_cpu_executor_dry_run.py sets this to walk the executor's control flow on CPU with the kernel
 # wrappers and the CUDA stream / event API replaced by recorders
 _DRY_RUN = False
+_ACT_DTYPE = torch.bfloat16   # activations / operand copies; the CPU emulation test runs the executor in fp32
 
 
 class NativeVGG:
@@ -311,7 +312,7 @@ class NativeVGG:
     # ------------------------------------------------------------------ workspaces
     def _alloc_workspaces(self) -> None:
         B, dev = self.max_batch, self.device
-        bf = torch.bfloat16
+        bf = _ACT_DTYPE
         L = self.layout
         self.blocks: List[_Block] = []
         # fp32 partial-tile workspace of the split-K convs (kept zero by their finalize kernel)

@@ -256,3 +256,48 @@ def test_engine_training_steps_match_torch_sgd(emu, monkeypatch):
     nv.refresh_shadows()
     for b, (wf, wd) in zip(nv.blocks, got):
         assert torch.equal(b.wf, wf) and (wd is None or torch.equal(b.wd, wd))
+
+
+def test_trainer_fit_evaluate_checkpoint_resume_on_the_native_backend(emu, monkeypatch, tmp_path, capsys):
+    """The tutorial's whole job through Trainer on the native backend (emulated kernels): a ragged last batch,
+    the test pass, a checkpoint in the reference's state_dict format, and a resumed trainer that continues
+    from the same parameters and momentum (ref: master/part1/part1.py:65-103)."""
+    from cs744_pytorch_distributed_tutorial_b200 import engine
+    from cs744_pytorch_distributed_tutorial_b200.config import TrainConfig
+    from cs744_pytorch_distributed_tutorial_b200.parallel import sync_native
+    monkeypatch.setattr(sync_native, "K", emu)
+    monkeypatch.setattr(torch.cuda, "set_device", lambda d: None)
+    real_zeros = torch.zeros
+    monkeypatch.setattr(torch, "zeros", lambda *a, **kw: real_zeros(*a, **{k: v for k, v in kw.items() if k != "pin_memory"}))
+    orig_enable = VGG.enable_native
+    monkeypatch.setattr(VGG, "enable_native", lambda self, max_batch, heap=None, **kw: orig_enable(self, max_batch, heap=heap, autotune=False, **kw))
+    ck = str(tmp_path / "ck.pt")
+    for loader in ("python", "native"):
+        cfg = TrainConfig(mode="part1", device="cpu", backend="native", global_batch=8, train_size=20, test_size=12,
+                          lr=0.01, cuda_graph=False, checkpoint=ck, loader=loader, loader_threads=2, json_metrics=False)
+        tr = engine.Trainer(cfg)
+        out = tr.fit()
+        assert tr.backend_name == "native" and out["iters"] == 3 and out["samples"] == 12    # 8 + 8 + 4 images
+        assert tr.backend.steps_done == 3 and 0 <= out["correct"] <= 12
+        params = tr.backend.native.flat_params.clone()
+        mom = tr.backend.native.flat_momentum.clone()
+        tr.close()
+        lines = capsys.readouterr().out.splitlines()
+        assert lines[0].startswith("0 loss: ") and any(l.startswith("Test set: Average loss:") for l in lines)
+        # reference-format checkpoint: plain torch module loads it
+        payload = torch.load(ck, weights_only=True)
+        plain = VGG("VGG11")
+        plain.load_state_dict(payload["model"])
+        assert len(payload["model"]) == 58 and payload["step"] == 3
+        # resume: same weights, same momentum, shadows refreshed
+        cfg2 = TrainConfig(mode="part1", device="cpu", backend="native", global_batch=8, train_size=20, test_size=12,
+                           lr=0.01, cuda_graph=False, resume=ck, json_metrics=False)
+        tr2 = engine.Trainer(cfg2)
+        nv2 = tr2.backend.native
+        torch.testing.assert_close(nv2.flat_params[: nv2.layout.used], params[: nv2.layout.used])
+        torch.testing.assert_close(nv2.flat_momentum[: nv2.layout.used], mom[: nv2.layout.used])
+        assert tr2.global_step == 3
+        got = [b.wf.clone() for b in nv2.blocks]
+        nv2.refresh_shadows()
+        assert all(torch.equal(b.wf, w) for b, w in zip(nv2.blocks, got))
+        tr2.close()

@@ -35,6 +35,11 @@ WGRAD_ON_SIDE_STREAM = os.environ.get("B200DP_WGRAD_STREAM", "1") != "0"
 # clear flat_grads on the weight-gradient stream during the forward pass instead of at the head of
 # backward; measured neutral at batch 256 (0.7435 vs 0.7422 ms), so off unless asked for
 ZERO_GRADS_EARLY = os.environ.get("B200DP_ZERO_GRADS_EARLY", "0") != "0"
+# experimental (not yet run on hardware): instead of one 36.9 MB fill at the head of backward (7 us on the
+# critical path), clear each conv layer's weight-gradient range on the weight-gradient stream right before
+# its wgrad kernel.  Everything else in the buffer is either overwritten every step (BatchNorm, classifier)
+# or never written (conv biases: exactly zero in front of a training-mode BatchNorm).
+ZERO_PER_LAYER = os.environ.get("B200DP_ZERO_PER_LAYER", "0") != "0"
 
 # experimental (not yet validated on hardware): the dgrad epilogue of block i also accumulates the
 # BatchNorm-backward sums of block i-1, which then skips its reduction launch
@@ -227,6 +232,7 @@ class NativeVGG:
         self.defer_head = False       # set by the engine when every training forward is followed by loss_fwd_bwd
         self._head_pending = False
         self._head_done = False
+        self._head_pending_clear = False
         # layer 0 (3 input channels): optional direct CUDA-core conv instead of patch gather + K=64
         # tcgen05 GEMM.  Measured slower on B200 at B=256 (LDS-bound: 122 us vs 33 + 44 us), so off.
         self.direct_first_layer = direct_first_layer and self_first_is_64(module)
@@ -506,7 +512,9 @@ class NativeVGG:
             self._head_pending = False
             last = self.blocks[-1]
             if need_grad:
+                self._head_pending_clear = True
                 self._clear_grads()
+                self._head_pending_clear = False
                 K.head_fwd_bwd(last.out[:B], self.fc_w, self.fc_b, target, self.logits[:B], self.loss, self.correct,
                                self.dlogits[:B], last.dout[:B], self.g_fc_w, self.g_fc_b, grad_scale)
                 self._head_done = True
@@ -517,6 +525,13 @@ class NativeVGG:
         return self.loss
 
     def _clear_grads(self) -> None:
+        if ZERO_PER_LAYER and WGRAD_ON_SIDE_STREAM:
+            # conv weights are cleared per layer in backward(); the fused head accumulates onto the classifier's
+            # gradient, so that small range is cleared here (linear_bwd clears it itself)
+            if self._head_pending_clear:
+                self.g_fc_w.zero_()
+                self.g_fc_b.zero_()
+            return
         if getattr(self, "_grads_cleared", False):
             torch.cuda.current_stream().wait_event(self._zero_done)   # cleared during forward on the wgrad stream
             self._grads_cleared = False
@@ -567,6 +582,8 @@ class NativeVGG:
             if side is not None:
                 side.wait_event(self._wgrad_fork[i])
             with torch.cuda.stream(side) if side is not None else contextlib.nullcontext():
+                if ZERO_PER_LAYER and side is not None:
+                    b.g_w.zero_()       # split-K partial tiles are accumulated with red.global.add
                 if b.direct:
                     K.conv3x3_c3_wgrad(b.dy[:B], self._x_first, b.g_w)
                 elif self.wgrad_push is not None and i in self.wgrad_push:

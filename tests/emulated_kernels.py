@@ -103,9 +103,10 @@ class EmulatedKernels:
         z = xhat * gamma + beta
         g = dout.float()
         if pool:
-            zp = z.permute(0, 3, 1, 2).detach().requires_grad_(True)
-            pooled = F.max_pool2d(torch.relu(zp), 2)
-            pooled.backward(g.permute(0, 3, 1, 2))
+            with torch.enable_grad():          # (the executor may be running inside an autograd backward)
+                zp = z.permute(0, 3, 1, 2).detach().requires_grad_(True)
+                pooled = F.max_pool2d(torch.relu(zp), 2)
+                pooled.backward(g.permute(0, 3, 1, 2))
             dz = zp.grad.permute(0, 2, 3, 1)
         else:
             dz = g * (z > 0)

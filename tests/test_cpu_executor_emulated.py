@@ -320,3 +320,27 @@ def test_per_layer_gradient_clearing_gives_the_same_gradients(emu, monkeypatch):
         _step(nv, x, y)
         assert (got - nv.flat_grads).abs().max().item() <= 2e-5 * nv.flat_grads.abs().max().item()
         monkeypatch.setattr(native_vgg, "ZERO_PER_LAYER", True)
+
+
+def test_autograd_bridge_drives_the_native_backward(emu):
+    """The eager user API: logits = model(x); loss.backward() (torch autograd calling into the executor through
+    _NativeVGGFunction), then the fused optimizer wrapper -- gradients land in the flat buffer views that the
+    module's parameters already point at, once, not doubled."""
+    model, nv, ref, ref_logits, ref_loss, x, y = _build(seed=13)
+    logits = nv.autograd_forward(x, True)
+    loss = torch.nn.functional.cross_entropy(logits, y)
+    loss.backward()
+    torch.testing.assert_close(logits.detach(), ref_logits, rtol=3e-3, atol=3e-3)
+    assert nv.grad_views_intact()
+    ref_params = dict(ref.named_parameters())
+    for name, p in model.named_parameters():
+        g, gr = p.grad.flatten(), ref_params[name].grad.flatten()
+        if gr.norm().item() < 1e-5:
+            continue
+        rel = ((g - gr).norm() / gr.norm()).item()
+        assert rel < 3e-2, f"{name}: relative L2 error {rel:.3e} (doubled gradients would give 1.0)"
+    # a second backward overwrites (the tutorial zeroes gradients every iteration), it does not accumulate
+    first = nv.flat_grads.clone()
+    logits = nv.autograd_forward(x, True)
+    torch.nn.functional.cross_entropy(logits, y).backward()
+    assert (nv.flat_grads - first).abs().max().item() <= 1e-5 * first.abs().max().item()

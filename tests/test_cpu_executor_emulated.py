@@ -344,3 +344,35 @@ def test_autograd_bridge_drives_the_native_backward(emu):
     logits = nv.autograd_forward(x, True)
     torch.nn.functional.cross_entropy(logits, y).backward()
     assert (nv.flat_grads - first).abs().max().item() <= 1e-5 * first.abs().max().item()
+
+
+def test_eager_training_loop_with_fused_sgd_matches_torch(emu, monkeypatch):
+    """The tutorial's loop verbatim -- zero_grad / forward / loss / backward / step (ref: master/part1/part1.py:
+    31-38) -- on a native-enabled model with ops.optim.FusedSGD, against the same loop on the plain module
+    with torch.optim.SGD, including a foreign zero_grad(set_to_none=True) that drops the gradient views."""
+    from cs744_pytorch_distributed_tutorial_b200.ops import optim as fused_optim
+    monkeypatch.setattr(fused_optim, "K", emu)
+    model, nv, ref, _, _, x, y = _build(seed=14)
+    model._native = nv
+    ref.zero_grad()
+    opt_ref = torch.optim.SGD(ref.parameters(), lr=0.05, momentum=0.9, weight_decay=1e-4)
+    opt = fused_optim.FusedSGD(model, lr=0.05, momentum=0.9, weight_decay=1e-4)
+    for step in range(3):
+        xb, yb = torch.randn_like(x), torch.randint(0, 10, y.shape)
+        opt_ref.zero_grad()
+        torch.nn.functional.cross_entropy(ref(xb), yb).backward()
+        opt_ref.step()
+        if step == 1:                                   # another component clears gradients its own way
+            for p in model.parameters():
+                p.grad = None
+            assert not nv.grad_views_intact()
+        opt.zero_grad()
+        assert nv.grad_views_intact()
+        loss = torch.nn.functional.cross_entropy(nv.autograd_forward(xb, True), yb)
+        loss.backward()
+        opt.step()
+    ref_params = dict(ref.named_parameters())
+    for name, p in model.named_parameters():
+        a, b = p.data.flatten(), ref_params[name].data.flatten()
+        rel = ((a - b).norm() / (b.norm() + 1e-12)).item()
+        assert rel < 2e-2, f"{name}: relative L2 {rel:.3e}"

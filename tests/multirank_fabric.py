@@ -25,6 +25,7 @@ class Fabric:
         self.execs = [None] * world      # NativeVGG per rank
         self.syncs = [None] * world      # BucketedOverlapSync per rank
         self.reducers = [None] * world
+        self.done = {}                   # post-backward collectives already performed, per kind
 
     # ---- collectives, executed once every rank has queued its buckets ---------------------------------
     def run_collectives(self):
@@ -52,6 +53,10 @@ class Fabric:
                 if staged:
                     g = g / W
                 red = self.reducers[r]
+                if not red.fuse:
+                    for s in range(W):                            # all-gather of the mean gradient
+                        self.execs[s].flat_grads[e_lo:e_hi] = g
+                    continue
                 p = self.execs[r].flat_params[e_lo:e_hi]
                 m = self.execs[r].flat_momentum[e_lo:e_hi]
                 m.mul_(red.momentum).add_(g + red.weight_decay * p)
@@ -90,6 +95,7 @@ class Fabric:
 class FabricComm:
     def __init__(self, fabric, rank):
         self.fabric, self.rank, self.world = fabric, rank, fabric.world
+        self._calls = {}
 
     def zeros(self, numel, dtype=torch.float32, align=256):
         return torch.zeros(numel, dtype=dtype)
@@ -113,6 +119,44 @@ class FabricComm:
                 return
         raise AssertionError("broadcast of a tensor the fabric does not know")
 
+    # ---- post-backward collectives (part2a / part2a_extra / part2b): the first rank to call performs the
+    # ---- collective for everybody (all gradients exist by then), the later calls of the same round are no-ops
+    def _once(self, what):
+        n = self._calls.get(what, 0) + 1
+        self._calls[what] = n
+        done = self.fabric.done.get(what, 0)
+        if done >= n:
+            return False
+        self.fabric.done[what] = n
+        return True
+
+    def allreduce(self, grads, start, end, *, params=None, momentum_buf=None, lr=0.0, momentum=0.0, weight_decay=0.0,
+                  prescale=True, algo=0, blocks=0, channel=0, stream=None):
+        if not self._once("allreduce"):
+            return
+        ex, W = self.fabric.execs, self.world
+        if prescale:
+            mean = sum(e.flat_grads[start:end] / W for e in ex)
+        else:
+            mean = sum(e.flat_grads[start:end] for e in ex) / W
+        for e in ex:
+            e.flat_grads[start:end] = mean
+            if params is not None:
+                p, m = e.flat_params[start:end], e.flat_momentum[start:end]
+                m.mul_(momentum).add_(mean + weight_decay * p)
+                p.sub_(lr * m)
+
+    def ps_reduce_bcast(self, grads, start, end, *, root=0, staging=None, blocks=0, channel=0, stream=None):
+        if not self._once("ps"):
+            return
+        ex, W = self.fabric.execs, self.world
+        acc = torch.zeros(end - start)
+        for e in ex:                                   # rank order, starting from zero
+            acc = acc + e.flat_grads[start:end]
+        mean = acc / W
+        for e in ex:
+            e.flat_grads[start:end] = mean
+
     def close(self):
         pass
 
@@ -123,6 +167,7 @@ class FabricReducer:
         self.comm, self.buckets = comm, list(buckets)
         self.lr, self.momentum, self.weight_decay = lr, momentum, weight_decay
         self.n_buckets, self.ready, self.staged = len(self.buckets), [], None
+        self.fuse = params is not None          # False: all-reduce only, the strategy runs SGD itself
         comm.fabric.reducers[comm.rank] = self
 
     def bucket_ready(self, k):

@@ -92,8 +92,8 @@ def _base_model(seed=0):
     return m
 
 
-def _run(emu, world, batches, bucket_plan="layer"):
-    """`batches`: list over steps of list over ranks of (x, y).  Returns the executors."""
+def _run(emu, world, batches, bucket_plan="layer", mode="part3", fuse=True):
+    """`batches`: list over steps of list over ranks of (x, y).  Returns the fabric (executors, strategies)."""
     fabric = Fabric(world)
     emu.fabric = fabric
     base = _base_model()
@@ -103,8 +103,13 @@ def _run(emu, world, batches, bucket_plan="layer"):
         comm = FabricComm(fabric, r)
         nv = native_vgg.NativeVGG(model, max_batch=B, heap=comm, autotune=False)
         fabric.execs[r] = nv
-        sync = sync_native.BucketedOverlapSync(nv, comm, lr=LR, momentum=MOM, weight_decay=WD, fuse_optimizer=True,
-                                               bucket_plan=bucket_plan, blocks=32)
+        kw = dict(lr=LR, momentum=MOM, weight_decay=WD, fuse_optimizer=fuse)
+        if mode == "part3":
+            sync = sync_native.BucketedOverlapSync(nv, comm, bucket_plan=bucket_plan, blocks=32, **kw)
+        elif mode == "part2b":
+            sync = sync_native.AllReduceSync(nv, comm, **kw)
+        else:
+            sync = sync_native.ParamServerSync(nv, comm, push=(mode == "part2a_extra"), **kw)
         fabric.syncs[r] = sync
     for r in range(world):
         fabric.syncs[r].on_init()
@@ -120,7 +125,8 @@ def _run(emu, world, batches, bucket_plan="layer"):
             s.post_forward()
             nv.loss_fwd_bwd(y)
             nv.backward()
-        fabric.run_collectives()
+        if mode == "part3":
+            fabric.run_collectives()
         for r in range(world):
             nv, s = fabric.execs[r], fabric.syncs[r]
             if getattr(s, "_prep_overlap", False):
@@ -203,3 +209,15 @@ def test_prep_overlap_path_keeps_operand_copies_current(emu, monkeypatch):
     fabric = _run(emu, 2, batches)
     assert all(s._prep_overlap and s.handles_shadows for s in fabric.syncs)
     _check_against_reference(fabric, _reference(2, batches))
+
+
+@pytest.mark.parametrize("mode,fuse", [("part2a", True), ("part2a_extra", True), ("part2b", True), ("part2b", False),
+                                       ("part3", False)])
+def test_every_synchronisation_mode_reaches_the_same_parameters(emu, mode, fuse):
+    """The tutorial's point: gather/scatter, point-to-point parameter server, all_reduce and DDP are the same
+    optimisation step (ref: master/part2a/part2a.py:42-53, part2a_extra.py:41-58, part2b/part2b.py:43-46,
+    part3/part3.py:116-117)."""
+    world = 3
+    batches = _batches(world, steps=2, B=2)
+    fabric = _run(emu, world, batches, mode=mode, fuse=fuse)
+    _check_against_reference(fabric, _reference(world, batches))

@@ -28,7 +28,7 @@ import torch.optim as optim
 
 from .config import TrainConfig
 from .models.vgg import VGG
-from .utils.metrics import PhaseTimer, StepClock, emit_json
+from .utils.metrics import PhaseTimer, StepClock, emit_json, nvtx_range
 
 
 def seed_everything(seed: int) -> None:
@@ -216,16 +216,20 @@ class NativeBackend:
     # -- the step ------------------------------------------------------------------------------
     def _step_body(self) -> None:
         nv = self.native
-        self.sync.pre_forward()
-        nv.forward(self.x, training=True)
-        self.sync.post_forward()
-        nv.loss_fwd_bwd(self.y)
-        nv.backward()
-        self.sync.sync_and_step()
-        if not self.sync.handles_shadows:
-            nv.refresh_shadows()
-        # within a captured step the auxiliary stream must be joined before the capture ends
-        self.sync.pre_forward()
+        with nvtx_range("b200dp.forward"):
+            self.sync.pre_forward()
+            nv.forward(self.x, training=True)
+            self.sync.post_forward()
+        with nvtx_range("b200dp.loss"):
+            nv.loss_fwd_bwd(self.y)
+        with nvtx_range("b200dp.backward"):
+            nv.backward()
+        with nvtx_range("b200dp.sync_and_step"):
+            self.sync.sync_and_step()
+            if not self.sync.handles_shadows:
+                nv.refresh_shadows()
+            # within a captured step the auxiliary stream must be joined before the capture ends
+            self.sync.pre_forward()
 
     def _capture(self) -> None:
         # warm up outside capture (module loading, lazy attribute setup), on a side stream as

@@ -106,3 +106,21 @@ class PhaseTimer:
 def emit_json(obj: dict, stream=None) -> None:
     (stream or sys.stdout).write(json.dumps(obj) + "\n")
     (stream or sys.stdout).flush()
+
+
+_NVTX = None
+
+
+def nvtx_range(name: str):
+    """NVTX range around a phase of the step (forward / loss / backward / sync) when ``B200DP_NVTX=1`` and a
+    GPU is present; otherwise a no-op context.  The ranges show up in Nsight Systems / ``torch.profiler``
+    traces of an eager run (``--no-cuda-graph``); a captured step replays without host code, so there the
+    phases are told apart by kernel names (scripts/timeline_step.py).  SURVEY.md 5.1."""
+    global _NVTX
+    if _NVTX is None:
+        import os
+        _NVTX = os.environ.get("B200DP_NVTX", "0") != "0" and torch.cuda.is_available()
+    if not _NVTX:
+        import contextlib
+        return contextlib.nullcontext()
+    return torch.cuda.nvtx.range(name)

@@ -43,6 +43,8 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--no-fuse-optimizer", action="store_true")
     p.add_argument("--nvls", choices=("auto", "on", "off"), default="auto",
                    help="NVSwitch multicast heap; in-switch all-reduce for large buckets (auto: on for world > 1)")
+    p.add_argument("--sync-impl", choices=("auto", "oneshot", "twoshot", "nvls"), default="auto",
+                   help="part2b all-reduce kernel (auto: by size and heap)")
     p.add_argument("--no-cuda-graph", action="store_true")
     p.add_argument("--train-size", type=int, default=50000)
     p.add_argument("--test-size", type=int, default=10000)
@@ -63,7 +65,7 @@ def config_from_args(argv=None) -> TrainConfig:
                        global_batch=a.global_batch, per_rank_batch=a.per_rank_batch, iters=a.iters, epochs=a.epochs,
                        lr=a.lr, momentum=a.momentum, weight_decay=a.weight_decay, seed=a.seed, port=a.port,
                        device=a.device, backend=a.backend, bucket_plan=a.bucket_plan,
-                       fuse_optimizer=not a.no_fuse_optimizer, nvls={"auto": None, "on": True, "off": False}[a.nvls], cuda_graph=not a.no_cuda_graph,
+                       fuse_optimizer=not a.no_fuse_optimizer, nvls={"auto": None, "on": True, "off": False}[a.nvls], cuda_graph=not a.no_cuda_graph, sync_impl=a.sync_impl,
                        train_size=a.train_size, test_size=a.test_size, synthetic=not a.real_data,
                        augment=not a.no_augment, loader=a.loader, loader_threads=a.loader_threads, eval=not a.no_eval, checkpoint=a.checkpoint, resume=a.resume)
 

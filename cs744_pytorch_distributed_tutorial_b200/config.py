@@ -14,6 +14,7 @@ from dataclasses import dataclass, field
 from typing import Optional
 
 MODES = ("part1", "part2a", "part2a_extra", "part2b", "part3")
+SYNC_IMPLS = {"auto": 0, "oneshot": 1, "twoshot": 2, "nvls": 3}   # b200dp_allreduce algo codes
 
 # MASTER_PORT literals (ref: master/part2a/part2a.py:83, master/part3/part3.py:72)
 REFERENCE_PORTS = {"part1": 29501, "part2a": 29501, "part2a_extra": 29501, "part2b": 29501, "part3": 29508}
@@ -40,6 +41,9 @@ class TrainConfig:
     # batch assembly for Trainer.fit: "python" = vectorised torch ops (data.BatchPipeline, ~20 k images/s),
     # "native" = C++ threads (csrc/loader.cpp, > 300 k images/s per thread); same sampling, different
     # augmentation draws
+    # part2b all-reduce kernel: auto (one-shot below 256 KiB, NVLS when the multicast heap exists, else
+    # two-shot) | oneshot | twoshot | nvls
+    sync_impl: str = "auto"
     loader: str = "python"
     loader_threads: int = 4
     cpu_threads: int = 4        # ref: master/part2a/part2a.py:18
@@ -84,6 +88,8 @@ class TrainConfig:
             raise ValueError(f"need 0 <= rank < num_nodes, got rank={self.rank} num_nodes={self.num_nodes}")
         if self.mode == "part1" and self.num_nodes != 1:
             raise ValueError("part1 is the single-process mode; use part2a/part2b/part3 for num_nodes > 1")
+        if self.sync_impl not in SYNC_IMPLS:
+            raise ValueError(f"sync_impl must be one of {tuple(SYNC_IMPLS)}, got {self.sync_impl!r}")
         if self.loader not in ("python", "native"):
             raise ValueError(f"loader must be 'python' or 'native', got {self.loader!r}")
         if self.port is None:

@@ -327,7 +327,9 @@ def make_native_sync(mode: str, native, comm: Optional[Communicator], cfg) -> Na
     if mode == "part2a_extra":
         return ParamServerSync(native, comm, push=True, blocks=cfg.sync_blocks, **kw)
     if mode == "part2b":
-        return AllReduceSync(native, comm, blocks=cfg.sync_blocks, **kw)
+        from ..config import SYNC_IMPLS
+        return AllReduceSync(native, comm, blocks=cfg.sync_blocks, algo=SYNC_IMPLS[getattr(cfg, "sync_impl", "auto")],
+                             **kw)
     if mode == "part3":
         return BucketedOverlapSync(native, comm, bucket_plan=cfg.bucket_plan, blocks=cfg.comm_blocks, **kw)
     raise ValueError(mode)

@@ -171,3 +171,13 @@ def test_local_sgd_two_phase_split_covers_all_parameters():
         assert s.split_end == s.buckets[s.split_bucket].end
         big = sum(b.end - b.start for b in s.buckets[: s.split_bucket + 1])
         assert big / nv.layout.total > 0.9          # phase 1 carries the bulk of the bytes
+
+
+def test_sync_impl_option_selects_the_allreduce_kernel():
+    from cs744_pytorch_distributed_tutorial_b200.config import TrainConfig
+    for name, code in (("auto", 0), ("oneshot", 1), ("twoshot", 2), ("nvls", 3)):
+        cfg = TrainConfig(mode="part2b", num_nodes=2, rank=0, device="cpu", sync_impl=name)
+        s = sync_native.make_native_sync("part2b", fake_native(), FakeComm(2), cfg)
+        assert type(s).__name__ == "AllReduceSync" and s.algo == code
+    with pytest.raises(ValueError):
+        TrainConfig(mode="part2b", num_nodes=2, rank=0, sync_impl="ring")

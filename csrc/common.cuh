@@ -306,4 +306,34 @@ B200DP_DEVINL uint32_t ld_relaxed_sys(const uint32_t* p) {
   return v;
 }
 
+// ---------------------------------------------------------------------------
+// 1-D bulk copies (the TMA engine without a tensor map): contiguous bytes global -> shared with
+// completion on an mbarrier, and shared -> global tracked by bulk groups.  Sizes and both addresses
+// must be multiples of 16 bytes.  Used by the bandwidth kernels that stream NHWC rows: a handful of
+// threads keeps tens of KiB in flight per SM regardless of the occupancy of the compute threads.
+// ---------------------------------------------------------------------------
+B200DP_DEVINL void bulk_load_1d(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               :
+               : "r"(smem_u32(smem_dst)), "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+B200DP_DEVINL void bulk_store_1d(void* gmem_dst, const void* smem_src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+               :
+               : "l"(gmem_dst), "r"(smem_u32(smem_src)), "r"(bytes)
+               : "memory");
+}
+B200DP_DEVINL void bulk_commit_group() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// at most N of this thread's bulk-store groups may still be READING shared memory afterwards
+template <int N>
+B200DP_DEVINL void bulk_wait_group_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+// at most N bulk-store groups may still be incomplete (writes to global not yet performed)
+template <int N>
+B200DP_DEVINL void bulk_wait_group() {
+  asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
+}
+
 }  // namespace b200dp

@@ -658,6 +658,150 @@ __global__ void __launch_bounds__(256, 3) bn_relu_pool_bwd_fused_kernel(const Bn
   bn_relu_pool_bwd_body<true>(p, red);
 }
 
+// ---------------------------------------------------------------------------
+// Bulk-copy pipelined variant of the pooled apply pass (experimental, B200DP_BN_TMA=1).
+// The register-file versions above keep at most ~10 KiB in flight per SM (37 % occupancy, a few 16-byte
+// loads per thread) and measure 45-56 % of the HBM / L2 rate.  Here the memory-level parallelism no longer
+// depends on the compute threads: one thread streams 20 KiB stages (256 work items: the two image rows of
+// y that a row of pooled pixels needs are contiguous in NHWC, and so is the matching row of dout) into a
+// ring of shared-memory buffers with cp.async.bulk, the 256 threads compute from shared memory into one of
+// two output buffers, and one thread streams those back with bulk stores.  Arithmetic per element is the
+// same as in bn_bwd_apply_pool_kernel, so the results are bit-identical.
+// Work item = (pooled pixel, 8-channel chunk); a "tile" = one pooled row of one image = Wo * C/8 items;
+// a stage = kBnTmaItems / (Wo * C/8) consecutive tiles (all tiles are contiguous in memory, image
+// boundaries included).  Requires (Wo * C/8) to divide kBnTmaItems.
+// ---------------------------------------------------------------------------
+constexpr int kBnTmaItems = 256;                       // work items per stage = threads per block
+constexpr int kBnTmaStages = 3;
+constexpr int kBnTmaYBytes = kBnTmaItems * 4 * 16;      // 16 KiB of y per stage (4 vectors per item)
+constexpr int kBnTmaGBytes = kBnTmaItems * 16;          // 4 KiB of dout per stage
+constexpr int kBnTmaStageBytes = kBnTmaYBytes + kBnTmaGBytes;
+constexpr int kBnTmaSmem = kBnTmaStages * kBnTmaStageBytes + 2 * kBnTmaYBytes + 64 + 128;
+
+__global__ void __launch_bounds__(kBnTmaItems, 2) bn_bwd_apply_pool_tma_kernel(const BnBwdParams p) {
+  extern __shared__ uint8_t bn_tma_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(bn_tma_raw) + 127) & ~uintptr_t(127));
+  uint8_t* out_buf = smem + kBnTmaStages * kBnTmaStageBytes;                     // 2 x 16 KiB
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(out_buf + 2 * kBnTmaYBytes);  // [kBnTmaStages]
+  pdl_launch_dependents();
+  const int chunks = p.C / 8;
+  const int Ho = p.H / 2, Wo = p.W / 2;
+  const int items_per_tile = Wo * chunks;
+  const int G = kBnTmaItems / items_per_tile;                       // tiles per stage
+  const long T = static_cast<long>(p.B) * Ho;                       // tiles in the tensor
+  const long num_chunks = (T + G - 1) / G;
+  const long tile_y_elems = 2L * p.W * p.C, tile_g_elems = static_cast<long>(Wo) * p.C;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kBnTmaStages; ++s) mbar_init(&full_bar[s], 1);
+    mbar_fence_init();
+  }
+  __syncthreads();
+  pdl_wait();
+
+  // producer side (thread 0): chunk j of this block is global chunk blockIdx.x + j * gridDim.x
+  auto issue = [&](long j, int stage) {
+    const long chunk_id = blockIdx.x + j * static_cast<long>(gridDim.x);
+    if (chunk_id >= num_chunks) return;
+    const long t0 = chunk_id * G;
+    const int tiles = static_cast<int>(min(static_cast<long>(G), T - t0));
+    uint8_t* dst = smem + stage * kBnTmaStageBytes;
+    const uint32_t yb = static_cast<uint32_t>(tiles * tile_y_elems * 2), gb = static_cast<uint32_t>(tiles * tile_g_elems * 2);
+    mbar_arrive_expect_tx(&full_bar[stage], yb + gb);
+    bulk_load_1d(dst, p.y + t0 * tile_y_elems, yb, &full_bar[stage]);
+    bulk_load_1d(dst + kBnTmaYBytes, p.dout + t0 * tile_g_elems, gb, &full_bar[stage]);
+  };
+  if (threadIdx.x == 0)
+    for (int s = 0; s < kBnTmaStages; ++s) issue(s, s);
+
+  // per-thread constants: the channel chunk of a thread never changes (kBnTmaItems % chunks == 0)
+  const int chunk = threadIdx.x % chunks, pix = threadIdx.x / chunks, c0i = chunk * 8;
+  const int gt = pix / Wo, wo = pix - gt * Wo;                        // tile inside the stage, pooled column
+  const float inv_count = 1.f / static_cast<float>(static_cast<long>(p.B) * p.H * p.W);
+  Vec8 scale, shift, c0, c1;
+  {
+    const Vec8 mean = load_f32x8(p.mean + c0i), invstd = load_f32x8(p.invstd + c0i);
+    const Vec8 g = load_f32x8(p.gamma + c0i), b = load_f32x8(p.beta + c0i);
+    Vec8 s1, s2;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      s1.v[j] = __ldcg(p.sums + c0i + j);
+      s2.v[j] = __ldcg(p.sums + p.C + c0i + j);
+      scale.v[j] = g.v[j] * invstd.v[j];
+      shift.v[j] = b.v[j] - mean.v[j] * scale.v[j];
+      c1.v[j] = -scale.v[j] * invstd.v[j] * s2.v[j] * inv_count;
+      c0.v[j] = -scale.v[j] * s1.v[j] * inv_count - c1.v[j] * mean.v[j];
+    }
+    if (blockIdx.x == 0 && pix == 0 && p.dgamma != nullptr) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        p.dgamma[c0i + j] = s2.v[j];
+        p.dbeta[c0i + j] = s1.v[j];
+      }
+    }
+  }
+  // element offsets of this thread's item inside a stage (same layout in the y, dy and dout buffers)
+  const int y_off = gt * static_cast<int>(tile_y_elems) + (2 * wo) * p.C + c0i;
+  const int g_off = gt * static_cast<int>(tile_g_elems) + wo * p.C + c0i;
+  const int rowb = p.W * p.C;
+
+  int stage = 0;
+  uint32_t phase = 0;
+  for (long j = 0;; ++j) {
+    const long chunk_id = blockIdx.x + j * static_cast<long>(gridDim.x);
+    if (chunk_id >= num_chunks) break;
+    const long t0 = chunk_id * G;
+    const int tiles = static_cast<int>(min(static_cast<long>(G), T - t0));
+    uint8_t* ob = out_buf + (j & 1) * kBnTmaYBytes;
+    if (threadIdx.x == 0) bulk_wait_group_read<1>();   // the store issued two chunks ago has drained this buffer
+    mbar_wait(&full_bar[stage], phase);                // this stage's y and dout have landed
+    __syncthreads();                                   // ... and everybody knows the output buffer is free
+    if (gt < tiles) {
+      const __nv_bfloat16* ys = reinterpret_cast<const __nv_bfloat16*>(smem + stage * kBnTmaStageBytes);
+      const __nv_bfloat16* gs = reinterpret_cast<const __nv_bfloat16*>(smem + stage * kBnTmaStageBytes + kBnTmaYBytes);
+      __nv_bfloat16* os = reinterpret_cast<__nv_bfloat16*>(ob);
+      const Vec8 go = unpack8(*reinterpret_cast<const uint4*>(gs + g_off));
+      const Vec8 ya = unpack8(*reinterpret_cast<const uint4*>(ys + y_off));
+      const Vec8 yb = unpack8(*reinterpret_cast<const uint4*>(ys + y_off + p.C));
+      const Vec8 yc = unpack8(*reinterpret_cast<const uint4*>(ys + y_off + rowb));
+      const Vec8 yd = unpack8(*reinterpret_cast<const uint4*>(ys + y_off + rowb + p.C));
+      Vec8 o0, o1, o2, o3;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const float za = fmaxf(fmaf(ya.v[k], scale.v[k], shift.v[k]), 0.f);
+        const float zb = fmaxf(fmaf(yb.v[k], scale.v[k], shift.v[k]), 0.f);
+        const float zc = fmaxf(fmaf(yc.v[k], scale.v[k], shift.v[k]), 0.f);
+        const float zd = fmaxf(fmaf(yd.v[k], scale.v[k], shift.v[k]), 0.f);
+        int win = 0;
+        float zmax = za;
+        if (zb > zmax) { zmax = zb; win = 1; }
+        if (zc > zmax) { zmax = zc; win = 2; }
+        if (zd > zmax) { zmax = zd; win = 3; }
+        const float sdz = zmax > 0.f ? scale.v[k] * go.v[k] : 0.f;
+        o0.v[k] = fmaf(c1.v[k], ya.v[k], c0.v[k]) + (win == 0 ? sdz : 0.f);
+        o1.v[k] = fmaf(c1.v[k], yb.v[k], c0.v[k]) + (win == 1 ? sdz : 0.f);
+        o2.v[k] = fmaf(c1.v[k], yc.v[k], c0.v[k]) + (win == 2 ? sdz : 0.f);
+        o3.v[k] = fmaf(c1.v[k], yd.v[k], c0.v[k]) + (win == 3 ? sdz : 0.f);
+      }
+      store_bf16x8(os + y_off, o0);
+      store_bf16x8(os + y_off + p.C, o1);
+      store_bf16x8(os + y_off + rowb, o2);
+      store_bf16x8(os + y_off + rowb + p.C, o3);
+    }
+    fence_proxy_async_smem();   // generic-proxy writes above must be visible to the bulk store below
+    __syncthreads();            // everyone has written its outputs and finished reading the input stage
+    if (threadIdx.x == 0) {
+      bulk_store_1d(p.dy + t0 * tile_y_elems, ob, static_cast<uint32_t>(tiles * tile_y_elems * 2));
+      bulk_commit_group();
+      issue(j + kBnTmaStages, stage);   // refill the stage just consumed
+    }
+    if (++stage == kBnTmaStages) {
+      stage = 0;
+      phase ^= 1;
+    }
+  }
+  if (threadIdx.x == 0) bulk_wait_group<0>();   // all stores performed before the block retires
+}
+
 // Reduction pass from the block OUTPUT instead of the conv output.  With a = relu(z) (max-pooled or
 // not) and g the gradient arriving at a: dz is g where a > 0 and lands on the element whose z equals
 // a, so  S1 = sum_{a>0} g  and  S2 = sum dz*xhat = sum_{a>0} g * (a - beta) / gamma.  For pooled
@@ -1213,6 +1357,27 @@ extern "C" int b200dp_bn_relu_pool_fwd(const void* y, const float* stats, const 
   return 0;
 }
 
+static bool bn_tma_supported(const BnBwdParams& p) {
+  if (!p.pool || p.C % 8 != 0 || ((p.H | p.W) & 1)) return false;
+  const int items_per_tile = (p.W / 2) * (p.C / 8);
+  return items_per_tile >= 1 && items_per_tile <= kBnTmaItems && kBnTmaItems % items_per_tile == 0;
+}
+
+static int launch_bn_apply_pool_tma(const BnBwdParams& p, cudaStream_t s) {
+  static bool configured = false;
+  if (!configured) {
+    B200DP_CUDA_TRY(cudaFuncSetAttribute(bn_bwd_apply_pool_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         kBnTmaSmem));
+    configured = true;
+  }
+  const int G = kBnTmaItems / ((p.W / 2) * (p.C / 8));
+  const long T = static_cast<long>(p.B) * (p.H / 2);
+  const long num_chunks = (T + G - 1) / G;
+  const int grid = static_cast<int>(num_chunks < 148 * 2 ? num_chunks : 148 * 2);
+  B200DP_CUDA_TRY(launch_pdl(bn_bwd_apply_pool_tma_kernel, dim3(grid), dim3(kBnTmaItems), kBnTmaSmem, s, p));
+  return 0;
+}
+
 static int launch_bn_bwd(bool apply, const BnBwdParams& p, cudaStream_t s) {
   if (p.C % 8 != 0 || p.C > 2048 || (p.pool && ((p.H | p.W) & 1))) {
     set_error("bn_relu_pool_bwd: unsupported shape H=%d W=%d C=%d pool=%d", p.H, p.W, p.C, p.pool);
@@ -1234,6 +1399,11 @@ static int launch_bn_bwd(bool apply, const BnBwdParams& p, cudaStream_t s) {
     const char* e = getenv("B200DP_BN_APPLY_POOL_V2");
     return e == nullptr || e[0] != '0';
   }();
+  static const bool bn_tma = [] {   // experimental bulk-copy pipelined kernel, off unless asked for
+    const char* e = getenv("B200DP_BN_TMA");
+    return e != nullptr && e[0] != '0';
+  }();
+  if (apply && p.pool && bn_tma && bn_tma_supported(p)) return launch_bn_apply_pool_tma(p, s);
   if (apply && !p.pool && apply_v2)
     B200DP_CUDA_TRY(launch_pdl(bn_bwd_apply_nopool_kernel, dim3(grid_for(Q, rows_per_block * 4, 148 * 3)),
                                dim3(threads), 0, s, p));
@@ -1320,6 +1490,22 @@ extern "C" int b200dp_bn_relu_pool_bwd_apply(const void* y, const void* dout, co
   BnBwdParams p{static_cast<const __nv_bfloat16*>(y), static_cast<const __nv_bfloat16*>(dout), mean, invstd, gamma,
                 beta, const_cast<float*>(sums), static_cast<__nv_bfloat16*>(dy), dgamma, dbeta, B, H, W, C, pool};
   return launch_bn_bwd(true, p, static_cast<cudaStream_t>(s));
+}
+
+/* The pooled apply pass as a bulk-copy (TMA engine) pipeline: same contract and bit-identical results as
+ * b200dp_bn_relu_pool_bwd_apply with pool = 1.  Needs (W/2) * (C/8) to divide 256.  Experimental: the
+ * executor takes it with B200DP_BN_TMA=1. */
+extern "C" int b200dp_bn_bwd_apply_pool_tma(const void* y, const void* dout, const float* mean, const float* invstd,
+                                            const float* gamma, const float* beta, const float* sums, void* dy,
+                                            float* dgamma, float* dbeta, int B, int H, int W, int C,
+                                            b200dp_stream_t s) {
+  BnBwdParams p{static_cast<const __nv_bfloat16*>(y), static_cast<const __nv_bfloat16*>(dout), mean, invstd, gamma,
+                beta, const_cast<float*>(sums), static_cast<__nv_bfloat16*>(dy), dgamma, dbeta, B, H, W, C, 1};
+  if (B <= 0 || !bn_tma_supported(p)) {
+    set_error("bn_bwd_apply_pool_tma: unsupported shape B=%d H=%d W=%d C=%d ((W/2)*(C/8) must divide 256)", B, H, W, C);
+    return B200DP_EINVAL;
+  }
+  return launch_bn_apply_pool_tma(p, static_cast<cudaStream_t>(s));
 }
 
 extern "C" int b200dp_linear_fwd(const void* x, const float* w, const float* b, float* logits, int B, int F, int O,

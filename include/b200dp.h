@@ -190,6 +190,14 @@ int b200dp_bn_relu_pool_bwd_noalloc(const void* y, const void* dout, const float
                                     const float* gamma, const float* beta, void* dy, float* dgamma,
                                     float* dbeta, int B, int H, int W, int C, int pool, b200dp_stream_t stream);
 
+/* Pooled apply pass of the BatchNorm backward as a bulk-copy (cp.async.bulk) pipeline: one thread streams
+ * 20 KiB stages of y / dout into shared memory, 256 threads compute, one thread streams dy back.  Same
+ * contract and bit-identical results as b200dp_bn_relu_pool_bwd_apply with pool = 1; (W/2)*(C/8) must divide
+ * 256.  Experimental (never run in round 1); the executor uses it with B200DP_BN_TMA=1. */
+int b200dp_bn_bwd_apply_pool_tma(const void* y, const void* dout, const float* mean, const float* invstd,
+                                 const float* gamma, const float* beta, const float* sums, void* dy, float* dgamma,
+                                 float* dbeta, int B, int H, int W, int C, b200dp_stream_t stream);
+
 /* Classifier and loss (ref: master/part1/model.py:40,45; master/part1/part1.py:36,94). */
 int b200dp_linear_fwd(const void* x_bf16, const float* w, const float* b, float* logits, int B, int F, int O,
                       b200dp_stream_t stream);

@@ -13,8 +13,8 @@ if [ "$1" != "multi" ]; then
   B200DP_EXPERIMENTAL=1 timeout 600 python -m pytest tests/test_gpu_experimental.py -m "gpu and not multigpu" -q \
       --timeout 300 2>&1 | tail -15 | tee $OUT/tests_1gpu.log
   echo "== A/B, 1 GPU, 100 steps each"
-  for cfg in "" "B200DP_DGRAD_BN_REDUCE=1" "B200DP_HEAD_FUSED=1" "B200DP_PERSIST=1" "B200DP_ZERO_PER_LAYER=1" \
-             "B200DP_DGRAD_BN_REDUCE=1 B200DP_HEAD_FUSED=1 B200DP_PERSIST=1 B200DP_ZERO_PER_LAYER=1" ""; do
+  for cfg in "" "B200DP_DGRAD_BN_REDUCE=1" "B200DP_HEAD_FUSED=1" "B200DP_PERSIST=1" "B200DP_ZERO_PER_LAYER=1" "B200DP_BN_TMA=1" \
+             "B200DP_DGRAD_BN_REDUCE=1 B200DP_HEAD_FUSED=1 B200DP_PERSIST=1 B200DP_ZERO_PER_LAYER=1 B200DP_BN_TMA=1" ""; do
     v=$(env $cfg timeout 200 python bench.py --steps 100 --no-e2e 2>&1 | ms)
     echo "  [${cfg:-baseline}] ms/step=$v" | tee -a $OUT/ab_1gpu.log
   done

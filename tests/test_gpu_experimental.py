@@ -294,3 +294,39 @@ def test_classifier_forward_runs_on_the_tcgen05_gemm_kernel_too():
     ref = x.float().view(B, Fd) @ w.bfloat16().float().t() + b
     torch.testing.assert_close(out.float().view(B, 32)[:, :O], ref[:, :O], rtol=2e-2, atol=2e-2)
     assert float(out.float().view(B, 32)[:, O:].abs().max()) == 0.0
+
+
+# (B, H, W, C) of the pooled blocks of VGG-11 at batch 256 / 32, plus ragged batches (partial last stage)
+BN_TMA_SHAPES = [(256, 32, 32, 64), (256, 16, 16, 128), (256, 8, 8, 256), (256, 4, 4, 512), (256, 2, 2, 512),
+                 (32, 32, 32, 64), (37, 2, 2, 512), (5, 4, 4, 512), (3, 16, 16, 128), (1, 2, 2, 512)]
+
+
+@pytest.mark.parametrize("shape", BN_TMA_SHAPES)
+def test_bulk_copy_pipelined_bn_apply_is_bit_identical(shape):
+    """b200dp_bn_bwd_apply_pool_tma vs the register-file kernel it replaces: same dY bits, same dgamma / dbeta,
+    and nothing written outside dY (guard bands), twice in a row (barrier phases start over per launch)."""
+    from cs744_pytorch_distributed_tutorial_b200.ops._lib import call, ptr, stream_ptr
+    B, H, W, C = shape
+    g = torch.Generator(device=DEV).manual_seed(31)
+    y = torch.randn(B, H, W, C, device=DEV, generator=g).bfloat16()
+    dout = torch.randn(B, H // 2, W // 2, C, device=DEV, generator=g).bfloat16()
+    mean = torch.randn(C, device=DEV, generator=g) * 0.1
+    invstd = torch.rand(C, device=DEV, generator=g) + 0.5
+    gamma = torch.rand(C, device=DEV, generator=g) + 0.5
+    beta = torch.randn(C, device=DEV, generator=g) * 0.1
+    sums = torch.randn(2 * C, device=DEV, generator=g)
+    ref = torch.empty_like(y)
+    dg0, db0 = torch.empty(C, device=DEV), torch.empty(C, device=DEV)
+    call("b200dp_bn_relu_pool_bwd_apply", ptr(y), ptr(dout), ptr(mean), ptr(invstd), ptr(gamma), ptr(beta), ptr(sums),
+         ptr(ref), ptr(dg0), ptr(db0), B, H, W, C, 1, stream_ptr())
+    n = y.numel()
+    for rep in range(2):
+        guard = torch.full((n + 4096,), 7.0, device=DEV).bfloat16()
+        out = guard[2048: 2048 + n].view(B, H, W, C)
+        dg, db = torch.empty(C, device=DEV), torch.empty(C, device=DEV)
+        call("b200dp_bn_bwd_apply_pool_tma", ptr(y), ptr(dout), ptr(mean), ptr(invstd), ptr(gamma), ptr(beta), ptr(sums),
+             ptr(out), ptr(dg), ptr(db), B, H, W, C, stream_ptr())
+        torch.cuda.synchronize()
+        assert torch.equal(out, ref)
+        assert torch.equal(dg, dg0) and torch.equal(db, db0)
+        assert float(guard[:2048].float().min()) == 7.0 and float(guard[2048 + n:].float().max()) == 7.0

@@ -37,6 +37,9 @@ _PROTOTYPES = {
     "b200dp_bn_relu_pool_fwd": [P, P, P, P, P, P, P, P, P, P, I, I, I, I, I, I, F, F, P],
     "b200dp_bn_relu_pool_bwd_reduce": [P, P, P, P, P, P, P, I, I, I, I, I, P],
     "b200dp_bn_relu_pool_bwd_apply": [P, P, P, P, P, P, P, P, P, P, I, I, I, I, I, P],
+    "b200dp_bn_bwd_apply_nopool_tma": [P, P, P, P, P, P, P, P, P, P, I, I, I, I, P],
+    "b200dp_bn_relu_pool_fwd_tma": [P, P, P, P, P, P, P, P, P, P, I, I, I, I, I, I, F, F, P],
+    "b200dp_bn_bwd_reduce_from_out_tma": [P, P, P, P, P, LL, I, P],
     "b200dp_bn_bwd_apply_pool_tma": [P, P, P, P, P, P, P, P, P, P, I, I, I, I, P],
     "b200dp_bn_relu_pool_bwd_reduce_from_out": [P, P, P, P, P, LL, I, P],
     "b200dp_bn_relu_pool_bwd_fused": [P, P, P, P, P, P, P, P, P, P, I, I, I, I, I, P],

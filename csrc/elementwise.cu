@@ -1292,6 +1292,22 @@ __global__ void __launch_bounds__(256) prep_conv_weights_batched_kernel(const Pr
   }
 }
 
+// B200DP_BN_TMA=1: route the BatchNorm kernels to their bulk-copy pipelined variants (csrc/bn_stream.cu and
+// bn_bwd_apply_pool_tma_kernel) wherever the shape allows; experimental, off by default.
+static bool bn_tma_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("B200DP_BN_TMA");
+    return e != nullptr && e[0] != '0';
+  }();
+  return on;
+}
+static bool bn_tma_shape_ok(int H, int W, int C, int pool) {
+  if (C < 8 || C % 8 != 0 || C > 2048 || 256 % (C / 8) != 0) return false;
+  if (!pool) return true;
+  const int items = (W / 2) * (C / 8);
+  return ((H | W) & 1) == 0 && items >= 1 && items <= 256 && 256 % items == 0;
+}
+
 static inline int grid_for(long work_items, int threads, int max_blocks = 148 * 16) {
   long b = (work_items + threads - 1) / threads;
   if (b > max_blocks) b = max_blocks;
@@ -1342,6 +1358,9 @@ extern "C" int b200dp_bn_relu_pool_fwd(const void* y, const float* stats, const 
     set_error("bn_relu_pool_fwd: unsupported shape H=%d W=%d C=%d pool=%d", H, W, C, pool);
     return B200DP_EINVAL;
   }
+  if (bn_tma_enabled() && bn_tma_shape_ok(H, W, C, pool))
+    return b200dp_bn_relu_pool_fwd_tma(y, stats, gamma, beta, running_mean, running_var, num_batches_tracked,
+                                       save_mean, save_invstd, out, B, H, W, C, pool, training, momentum, eps, s);
   BnFwdParams p{static_cast<const __nv_bfloat16*>(y), stats, gamma, beta, running_mean, running_var,
                 num_batches_tracked, save_mean, save_invstd, static_cast<__nv_bfloat16*>(out),
                 B, H, W, C, pool, training, momentum, eps};
@@ -1399,11 +1418,10 @@ static int launch_bn_bwd(bool apply, const BnBwdParams& p, cudaStream_t s) {
     const char* e = getenv("B200DP_BN_APPLY_POOL_V2");
     return e == nullptr || e[0] != '0';
   }();
-  static const bool bn_tma = [] {   // experimental bulk-copy pipelined kernel, off unless asked for
-    const char* e = getenv("B200DP_BN_TMA");
-    return e != nullptr && e[0] != '0';
-  }();
-  if (apply && p.pool && bn_tma && bn_tma_supported(p)) return launch_bn_apply_pool_tma(p, s);
+  if (apply && p.pool && bn_tma_enabled() && bn_tma_supported(p)) return launch_bn_apply_pool_tma(p, s);
+  if (apply && !p.pool && bn_tma_enabled() && bn_tma_shape_ok(p.H, p.W, p.C, 0))
+    return b200dp_bn_bwd_apply_nopool_tma(p.y, p.dout, p.mean, p.invstd, p.gamma, p.beta, p.sums, p.dy, p.dgamma,
+                                          p.dbeta, p.B, p.H, p.W, p.C, s);
   if (apply && !p.pool && apply_v2)
     B200DP_CUDA_TRY(launch_pdl(bn_bwd_apply_nopool_kernel, dim3(grid_for(Q, rows_per_block * 4, 148 * 3)),
                                dim3(threads), 0, s, p));
@@ -1473,6 +1491,8 @@ extern "C" int b200dp_bn_relu_pool_bwd_reduce_from_out(const void* out, const vo
     set_error("bn_relu_pool_bwd_reduce_from_out: unsupported shape Q=%lld C=%d", Q, C);
     return B200DP_EINVAL;
   }
+  if (bn_tma_enabled() && bn_tma_shape_ok(2, 2, C, 0))
+    return b200dp_bn_bwd_reduce_from_out_tma(out, dout, gamma, beta, sums, Q, C, s);
   const int threads = 256;
   const int rows_per_block = threads / (C / 8);
   const size_t smem = 2 * rows_per_block * C * sizeof(float);

@@ -198,6 +198,21 @@ int b200dp_bn_bwd_apply_pool_tma(const void* y, const void* dout, const float* m
                                  const float* gamma, const float* beta, const float* sums, void* dy, float* dgamma,
                                  float* dbeta, int B, int H, int W, int C, b200dp_stream_t stream);
 
+/* The rest of the BatchNorm family as bulk-copy pipelines (csrc/bn_stream.cu; experimental, never run in
+ * round 1, taken by the plain entry points with B200DP_BN_TMA=1).  Same contracts as the kernels they
+ * replace: b200dp_bn_relu_pool_bwd_apply (pool = 0), b200dp_bn_relu_pool_fwd and
+ * b200dp_bn_relu_pool_bwd_reduce_from_out; the first two are bit-identical, the reduction agrees up to
+ * summation order.  C/8 must divide 256 (and (W/2)*(C/8) with pooling). */
+int b200dp_bn_bwd_apply_nopool_tma(const void* y, const void* dout, const float* mean, const float* invstd,
+                                   const float* gamma, const float* beta, const float* sums, void* dy,
+                                   float* dgamma, float* dbeta, int B, int H, int W, int C, b200dp_stream_t stream);
+int b200dp_bn_relu_pool_fwd_tma(const void* y, const float* stats, const float* gamma, const float* beta,
+                                float* running_mean, float* running_var, long long* num_batches_tracked,
+                                float* save_mean, float* save_invstd, void* out, int B, int H, int W, int C, int pool,
+                                int training, float momentum, float eps, b200dp_stream_t stream);
+int b200dp_bn_bwd_reduce_from_out_tma(const void* out, const void* dout, const float* gamma, const float* beta,
+                                      float* sums, long long Q, int C, b200dp_stream_t stream);
+
 /* Classifier and loss (ref: master/part1/model.py:40,45; master/part1/part1.py:36,94). */
 int b200dp_linear_fwd(const void* x_bf16, const float* w, const float* b, float* logits, int B, int F, int O,
                       b200dp_stream_t stream);

@@ -14,10 +14,10 @@ import subprocess
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "cs744_pytorch_distributed_tutorial_b200", "lib", "libb200dp.so")
-SRCS = ["csrc/conv_igemm.cu", "csrc/collectives.cu", "csrc/elementwise.cu"]
+SRCS = ["csrc/conv_igemm.cu", "csrc/collectives.cu", "csrc/elementwise.cu", "csrc/bn_stream.cu"]
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo", "--expt-relaxed-constexpr",
          "-I", os.path.join(ROOT, "include"), "-Xcompiler", "-fPIC"]
-EXPERIMENTAL = ("bnr", "head_fwd_bwd", "wgrad_push", "reduce_staged", "persist")
+EXPERIMENTAL = ("bnr", "head_fwd_bwd", "wgrad_push", "reduce_staged", "persist", "_tma", "bn_stream")
 today = datetime.date.today().isoformat()
 
 
@@ -29,7 +29,7 @@ def demangle(names):
 def sass():
     txt = subprocess.run(["cuobjdump", "-sass", LIB], capture_output=True, text=True, check=True).stdout
     total, per, name = collections.Counter(), collections.OrderedDict(), None
-    interesting = re.compile(r"UTC|UTMA|LDTM|STTM|SYNCS|REDG|ATOMG|LDGMC|STGMC|MULTIMEM|MMEM|STRONG\.SYS|MEMBAR|UCGABAR|CCTL")
+    interesting = re.compile(r"UTC|UTMA|UBLKCP|LDTM|STTM|SYNCS|REDG|ATOMG|LDGMC|STGMC|MULTIMEM|MMEM|STRONG\.SYS|MEMBAR|UCGABAR|CCTL")
     for line in txt.splitlines():
         m = re.search(r"Function : (\S+)", line)
         if m:
@@ -50,7 +50,7 @@ def main():
         f.write(f"# SASS mnemonic counts of lib/libb200dp.so (cuobjdump -sass, sm_100a), {today}; scripts/sass_evidence.py\n")
         f.write("# tcgen05.mma -> UTCHMMA (.2CTA = cta_group::2), tcgen05.ld -> LDTM, tcgen05.commit -> UTCBAR, TMA -> UTMALDG,\n"
                 "# mbarrier -> SYNCS.*, red.global.add.v4.f32 -> REDG...F32x4, multimem.ld_reduce -> LDGMC.E.ADD.F32x4 (multimem.st shows as STG.E.128.STRONG.SYS),\n"
-                "# st.release.sys / ld.acquire.sys -> ST/LD ...STRONG.SYS, cluster barrier -> UCGABAR_*\n")
+                "# st.release.sys / ld.acquire.sys -> ST/LD ...STRONG.SYS, cluster barrier -> UCGABAR_*, cp.async.bulk -> UBLKCP\n")
         for k, v in total.most_common():
             f.write(f"{v:7d} {k}\n")
         f.write("\n# per kernel ([exp] = experimental, off by default, DESIGN.md section 8)\n")
@@ -58,10 +58,11 @@ def main():
             def cnt(pat):
                 return sum(v for k, v in c.items() if re.search(pat, k))
             tags = [("UTCHMMA", cnt(r"^UTCHMMA")), ("UTMALDG", cnt(r"^UTMALDG")), ("LDTM", cnt(r"^LDTM")),
-                    ("UTCBAR", cnt(r"^UTCBAR")), ("REDG.F32x4", cnt(r"REDG.*F32x4")), ("multimem.ld_reduce(LDGMC)", cnt(r"LDGMC|STGMC|MULTIMEM|MMEM")),
+                    ("UTCBAR", cnt(r"^UTCBAR")), ("UBLKCP(cp.async.bulk)", cnt(r"^UBLKCP")), ("REDG.F32x4", cnt(r"REDG.*F32x4")), ("multimem.ld_reduce(LDGMC)", cnt(r"LDGMC|STGMC|MULTIMEM|MMEM")),
                     ("STRONG.SYS", cnt(r"STRONG\.SYS"))]
             tags = " ".join(f"{k}={v}" for k, v in tags if v)
-            short = re.sub(r"\(.*", "", names[n]).replace("void ", "")
+            short = names[n].replace("(anonymous namespace)::", "").replace("void ", "")
+            short = re.sub(r"\(.*", "", short)
             exp = "[exp] " if any(e in short for e in EXPERIMENTAL) else ""
             f.write(f"{exp}{short}  {tags or '-'}\n")
     with open(os.path.join(ROOT, "profiles", "ptxas_resources.txt"), "w") as f:
@@ -80,7 +81,8 @@ def main():
                     spill = "" if m.group(1) == "0" and m.group(2) == "0" else f"  SPILL stores={m.group(1)} loads={m.group(2)}"
                 m = re.search(r"Used (\d+) registers(.*)", line)
                 if m and cur:
-                    short = re.sub(r"\(.*", "", demangle([cur])[cur]).replace("void ", "")
+                    short = demangle([cur])[cur].replace("(anonymous namespace)::", "").replace("void ", "")
+                    short = re.sub(r"\(.*", "", short)
                     exp = "[exp] " if any(e in short for e in EXPERIMENTAL) else ""
                     f.write(f"{exp}{short:66s} regs={m.group(1)}{m.group(2).rstrip()}{spill}\n")
                     cur = None

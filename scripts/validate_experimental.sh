@@ -12,6 +12,9 @@ if [ "$1" != "multi" ]; then
   echo "== acceptance tests (single GPU)"
   B200DP_EXPERIMENTAL=1 timeout 600 python -m pytest tests/test_gpu_experimental.py -m "gpu and not multigpu" -q \
       --timeout 300 2>&1 | tail -15 | tee $OUT/tests_1gpu.log
+  echo "== the regular single-GPU suite with the bulk-copy BatchNorm kernels behind the plain entry points"
+  B200DP_BN_TMA=1 timeout 600 python -m pytest tests/test_gpu_kernels.py tests/test_gpu_model.py -m gpu -q \
+      --timeout 300 2>&1 | tail -3 | tee $OUT/tests_bn_tma.log
   echo "== A/B, 1 GPU, 100 steps each"
   for cfg in "" "B200DP_DGRAD_BN_REDUCE=1" "B200DP_HEAD_FUSED=1" "B200DP_PERSIST=1" "B200DP_ZERO_PER_LAYER=1" "B200DP_BN_TMA=1" \
              "B200DP_DGRAD_BN_REDUCE=1 B200DP_HEAD_FUSED=1 B200DP_PERSIST=1 B200DP_ZERO_PER_LAYER=1 B200DP_BN_TMA=1" ""; do

@@ -330,3 +330,82 @@ def test_bulk_copy_pipelined_bn_apply_is_bit_identical(shape):
         assert torch.equal(out, ref)
         assert torch.equal(dg, dg0) and torch.equal(db, db0)
         assert float(guard[:2048].float().min()) == 7.0 and float(guard[2048 + n:].float().max()) == 7.0
+
+
+def _bn_inputs(B, H, W, C, seed):
+    g = torch.Generator(device=DEV).manual_seed(seed)
+    y = torch.randn(B, H, W, C, device=DEV, generator=g).bfloat16()
+    gamma = torch.rand(C, device=DEV, generator=g) + 0.5
+    beta = torch.randn(C, device=DEV, generator=g) * 0.1
+    return g, y, gamma, beta
+
+
+@pytest.mark.parametrize("shape", [(256, 8, 8, 256), (256, 4, 4, 512), (256, 2, 2, 512), (37, 2, 2, 512), (3, 8, 8, 256),
+                                   (2, 32, 32, 64)])
+def test_bulk_copy_nopool_apply_is_bit_identical(shape):
+    from cs744_pytorch_distributed_tutorial_b200.ops._lib import call, ptr, stream_ptr
+    B, H, W, C = shape
+    g, y, gamma, beta = _bn_inputs(B, H, W, C, 41)
+    dout = torch.randn(B, H, W, C, device=DEV, generator=g).bfloat16()
+    mean = torch.randn(C, device=DEV, generator=g) * 0.1
+    invstd = torch.rand(C, device=DEV, generator=g) + 0.5
+    sums = torch.randn(2 * C, device=DEV, generator=g)
+    outs = []
+    for fn, extra in (("b200dp_bn_relu_pool_bwd_apply", (0,)), ("b200dp_bn_bwd_apply_nopool_tma", ())):
+        dy = torch.full_like(y, float("nan"))
+        dg, db = torch.empty(C, device=DEV), torch.empty(C, device=DEV)
+        for _ in range(2):
+            call(fn, ptr(y), ptr(dout), ptr(mean), ptr(invstd), ptr(gamma), ptr(beta), ptr(sums), ptr(dy), ptr(dg),
+                 ptr(db), B, H, W, C, *extra, stream_ptr())
+        torch.cuda.synchronize()
+        outs.append((dy, dg, db))
+    for a, b in zip(*outs):
+        assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize("shape", [(256, 32, 32, 64, 1), (256, 16, 16, 128, 1), (256, 8, 8, 256, 0), (256, 8, 8, 256, 1),
+                                   (256, 4, 4, 512, 0), (256, 2, 2, 512, 1), (37, 2, 2, 512, 1), (5, 4, 4, 512, 0),
+                                   (3, 16, 16, 128, 1)])
+@pytest.mark.parametrize("training", [1, 0])
+def test_bulk_copy_bn_forward_is_bit_identical(shape, training):
+    """Outputs, saved mean / invstd, running statistics and the batch counter, against b200dp_bn_relu_pool_fwd."""
+    from cs744_pytorch_distributed_tutorial_b200.ops._lib import call, ptr, stream_ptr
+    B, H, W, C, pool = shape
+    g, y, gamma, beta = _bn_inputs(B, H, W, C, 43)
+    v = y.float().reshape(-1, C)
+    stats = torch.cat([v.sum(0), (v * v).sum(0)]).contiguous()
+    res = []
+    for fn in ("b200dp_bn_relu_pool_fwd", "b200dp_bn_relu_pool_fwd_tma"):
+        rm = torch.linspace(-0.2, 0.2, C, device=DEV).contiguous()
+        rv = torch.linspace(0.5, 1.5, C, device=DEV).contiguous()
+        nbt = torch.full((1,), 5, device=DEV, dtype=torch.int64)
+        sm, si = torch.zeros(C, device=DEV), torch.zeros(C, device=DEV)
+        ho, wo = (H // 2, W // 2) if pool else (H, W)
+        out = torch.full((B, ho, wo, C), float("nan"), device=DEV, dtype=torch.bfloat16)
+        call(fn, ptr(y), ptr(stats), ptr(gamma), ptr(beta), ptr(rm), ptr(rv), ptr(nbt), ptr(sm), ptr(si), ptr(out),
+             B, H, W, C, pool, training, 0.1, 1e-5, stream_ptr())
+        torch.cuda.synchronize()
+        res.append((out, rm, rv, nbt, sm, si))
+    for a, b in zip(*res):
+        assert torch.equal(a, b)
+    assert int(res[1][3]) == (6 if training else 5)
+
+
+@pytest.mark.parametrize("shape", [(256 * 16 * 16, 64), (256 * 8 * 8, 128), (256 * 8 * 8, 256), (256 * 2 * 2, 512),
+                                   (256, 512), (37, 512), (1, 64)])
+def test_bulk_copy_reduce_from_out_matches(shape):
+    from cs744_pytorch_distributed_tutorial_b200.ops._lib import call, ptr, stream_ptr
+    Q, C = shape
+    g = torch.Generator(device=DEV).manual_seed(47)
+    a = torch.relu(torch.randn(Q, C, device=DEV, generator=g)).bfloat16()
+    dout = torch.randn(Q, C, device=DEV, generator=g).bfloat16()
+    gamma = torch.rand(C, device=DEV, generator=g) + 0.5
+    gamma[0] = 0.0
+    beta = torch.randn(C, device=DEV, generator=g) * 0.1
+    s0, s1 = torch.zeros(2 * C, device=DEV), torch.ones(2 * C, device=DEV)     # the new one accumulates onto ones
+    call("b200dp_bn_relu_pool_bwd_reduce_from_out", ptr(a), ptr(dout), ptr(gamma), ptr(beta), ptr(s0), Q, C, stream_ptr())
+    call("b200dp_bn_bwd_reduce_from_out_tma", ptr(a), ptr(dout), ptr(gamma), ptr(beta), ptr(s1), Q, C, stream_ptr())
+    torch.cuda.synchronize()
+    scale = s0.abs().max().item() + 1e-6
+    assert ((s1 - 1.0) - s0).abs().max().item() < 1e-4 * scale + 1e-5
+    assert abs(s1[C].item() - 1.0) < 1e-6                                        # gamma == 0: no contribution to S2

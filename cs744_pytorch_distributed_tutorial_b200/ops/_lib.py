@@ -63,7 +63,8 @@ _NON_LAUNCHING = {"b200dp_store_create", "b200dp_store_set", "b200dp_store_get",
                   "b200dp_comm_heap", "b200dp_comm_peer_base", "b200dp_comm_set_timeout", "b200dp_reducer_create",
                   "b200dp_comm_create_ex", "b200dp_comm_prefer_nvls", "b200dp_comm_has_multicast",
                   "b200dp_reducer_set_lr", "b200dp_reducer_finalize", "b200dp_reducer_destroy",
-                  "b200dp_reducer_stream", "b200dp_reducer_set_blocks", "b200dp_reducer_set_staged"}
+                  "b200dp_reducer_stream", "b200dp_reducer_set_blocks", "b200dp_reducer_set_staged",
+                  "b200dp_reducer_set_lazy_exit"}
 launch_count = 0  # kernels of this library launched (or captured) by this process so far
 
 

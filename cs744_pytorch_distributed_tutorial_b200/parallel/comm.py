@@ -43,6 +43,7 @@ _lib.declare("b200dp_reducer_create", [P, I, POINTER(c_longlong), POINTER(c_long
 _lib.declare("b200dp_reducer_set_lr", [P, F])
 _lib.declare("b200dp_reducer_stream", [P, POINTER(c_void_p)])
 _lib.declare("b200dp_reducer_set_blocks", [P, I])
+_lib.declare("b200dp_reducer_set_lazy_exit", [P, I])
 _lib.declare("b200dp_reducer_set_staged", [P, LL, POINTER(c_longlong), POINTER(c_longlong), POINTER(c_longlong)])
 _lib.declare("b200dp_reduce_staged_sgd", [P, LL, LL, LL, LL, LL, LL, LL, LL, LL, F, F, F, I, I, I, P])
 _lib.declare("b200dp_reducer_bucket_ready", [P, I, P])
@@ -222,6 +223,10 @@ class BucketReducer:
 
     def set_lr(self, lr: float) -> None:
         call("b200dp_reducer_set_lr", self._h, lr)
+
+    def set_lazy_exit(self, on: bool = True) -> None:
+        """Experimental: only the last bucket kernel of a step keeps its exit barrier."""
+        call("b200dp_reducer_set_lazy_exit", self._h, int(on))
 
     def set_blocks(self, blocks: int) -> None:
         """CTAs per bucket collective from the next ``bucket_ready`` on (re-capture the step afterwards)."""

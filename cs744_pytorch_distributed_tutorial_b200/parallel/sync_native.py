@@ -218,6 +218,11 @@ class BucketedOverlapSync(NativeSync):
         # 3x3 layer forwards its finished tiles to the owning rank's staging slots as they complete
         # (GEMM -> reduce-scatter in one kernel); the bucket kernel on the reducer stream then only sums
         # local memory, applies SGD and broadcasts the parameters.
+        # Experimental (B200DP_LAZY_EXIT_BARRIER=1): bucket kernels 0..n-2 skip their exit barrier.  Not combined
+        # with the re-layout behind the buckets, which reads parameters right after the split bucket's kernel.
+        self._lazy_exit = os.environ.get("B200DP_LAZY_EXIT_BARRIER", "0") != "0" and not self._prep_overlap
+        if self._lazy_exit:
+            self.reducer.set_lazy_exit(True)
         self._wgrad_push = (os.environ.get("B200DP_WGRAD_PUSH", "0") != "0" and fuse and bucket_plan == "layer"
                             and self.world > 1 and self.world <= 8)
         if self._wgrad_push:

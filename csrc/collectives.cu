@@ -164,8 +164,8 @@ struct RangeArgs {
 // ---------------------------------------------------------------------------
 // two-shot all-reduce: reduce-scatter -> (scale, SGD) -> all-gather
 // ---------------------------------------------------------------------------
-template <bool FUSE_SGD, bool PRESCALE>
-__global__ void __launch_bounds__(512) allreduce_twoshot_kernel(const CommDev c, const RangeArgs a) {
+template <bool FUSE_SGD, bool PRESCALE, bool EXIT_BARRIER>
+B200DP_DEVINL void allreduce_twoshot_body(const CommDev& c, const RangeArgs& a) {
   const uint32_t epoch = begin_collective(c, a.channel);
   rank_barrier(c, a.channel, 0, epoch);
   const int W = c.world;
@@ -226,8 +226,23 @@ __global__ void __launch_bounds__(512) allreduce_twoshot_kernel(const CommDev c,
       }
     }
   }
-  rank_barrier(c, a.channel, 1, epoch);
+  if (EXIT_BARRIER) rank_barrier(c, a.channel, 1, epoch);
   end_collective(c, a.channel, epoch);
+}
+
+template <bool FUSE_SGD, bool PRESCALE>
+__global__ void __launch_bounds__(512) allreduce_twoshot_kernel(const CommDev c, const RangeArgs a) {
+  allreduce_twoshot_body<FUSE_SGD, PRESCALE, true>(c, a);
+}
+
+// Without the exit barrier (experimental, B200DP_LAZY_EXIT_BARRIER=1).  What the exit barrier guarantees --
+// every peer's stores into my buffers have landed, every peer has finished reading mine -- is also implied by
+// the ENTRY barrier of the next collective on the same channel: a peer reaches it only after its previous
+// kernel has completed, stores fenced.  So only the last bucket kernel of a step needs the exit barrier; at
+// 8 ranks a barrier costs ~10 us and a step has eight bucket kernels queued back to back.
+template <bool FUSE_SGD, bool PRESCALE>
+__global__ void __launch_bounds__(512) allreduce_twoshot_lazy_kernel(const CommDev c, const RangeArgs a) {
+  allreduce_twoshot_body<FUSE_SGD, PRESCALE, false>(c, a);
 }
 
 // ---------------------------------------------------------------------------
@@ -297,8 +312,8 @@ B200DP_DEVINL void multimem_st_f4(float* mc_addr, const float4& v) {
                : "memory");
 }
 
-template <bool FUSE_SGD>
-__global__ void __launch_bounds__(512) allreduce_nvls_kernel(const CommDev c, const RangeArgs a) {
+template <bool FUSE_SGD, bool EXIT_BARRIER>
+B200DP_DEVINL void allreduce_nvls_body(const CommDev& c, const RangeArgs& a) {
   const uint32_t epoch = begin_collective(c, a.channel);
   rank_barrier(c, a.channel, 0, epoch);
   const int W = c.world;
@@ -335,8 +350,18 @@ __global__ void __launch_bounds__(512) allreduce_nvls_kernel(const CommDev c, co
       }
     }
   }
-  rank_barrier(c, a.channel, 1, epoch);
+  if (EXIT_BARRIER) rank_barrier(c, a.channel, 1, epoch);
   end_collective(c, a.channel, epoch);
+}
+
+template <bool FUSE_SGD>
+__global__ void __launch_bounds__(512) allreduce_nvls_kernel(const CommDev c, const RangeArgs a) {
+  allreduce_nvls_body<FUSE_SGD, true>(c, a);
+}
+
+template <bool FUSE_SGD>
+__global__ void __launch_bounds__(512) allreduce_nvls_lazy_kernel(const CommDev c, const RangeArgs a) {
+  allreduce_nvls_body<FUSE_SGD, false>(c, a);
 }
 
 // ---------------------------------------------------------------------------
@@ -881,10 +906,9 @@ extern "C" int b200dp_comm_barrier(void* comm, int channel, b200dp_stream_t stre
 }
 
 // algo: 0 = choose, 1 = one-shot, 2 = two-shot
-extern "C" int b200dp_allreduce(void* comm, long long grad_off, long long param_off, long long mom_off,
-                                long long start, long long end, int fuse_sgd, int prescale, float lr,
-                                float momentum, float weight_decay, int algo, int blocks, int channel,
-                                b200dp_stream_t stream_) {
+static int allreduce_impl(void* comm, long long grad_off, long long param_off, long long mom_off, long long start,
+                          long long end, int fuse_sgd, int prescale, float lr, float momentum, float weight_decay,
+                          int algo, int blocks, int channel, b200dp_stream_t stream_, bool skip_exit_barrier) {
   auto* c = static_cast<Comm*>(comm);
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   const int threads = 512;
@@ -919,18 +943,33 @@ extern "C" int b200dp_allreduce(void* comm, long long grad_off, long long param_
     else if (prescale) KERN<false, true><<<blocks, threads, 0, stream>>>(d, a);       \
     else KERN<false, false><<<blocks, threads, 0, stream>>>(d, a);                    \
   } while (0)
-  if (algo == 3) {
+  if (algo == 3 && skip_exit_barrier) {
+    if (fuse_sgd)
+      allreduce_nvls_lazy_kernel<true><<<blocks, threads, 0, stream>>>(d, a);
+    else
+      allreduce_nvls_lazy_kernel<false><<<blocks, threads, 0, stream>>>(d, a);
+  } else if (algo == 3) {
     if (fuse_sgd)
       allreduce_nvls_kernel<true><<<blocks, threads, 0, stream>>>(d, a);
     else
       allreduce_nvls_kernel<false><<<blocks, threads, 0, stream>>>(d, a);
   } else if (algo == 1)
     B200DP_LAUNCH_AR(allreduce_oneshot_kernel);
+  else if (skip_exit_barrier)
+    B200DP_LAUNCH_AR(allreduce_twoshot_lazy_kernel);
   else
     B200DP_LAUNCH_AR(allreduce_twoshot_kernel);
 #undef B200DP_LAUNCH_AR
   B200DP_CUDA_TRY(cudaGetLastError());
   return 0;
+}
+
+extern "C" int b200dp_allreduce(void* comm, long long grad_off, long long param_off, long long mom_off,
+                                long long start, long long end, int fuse_sgd, int prescale, float lr,
+                                float momentum, float weight_decay, int algo, int blocks, int channel,
+                                b200dp_stream_t stream_) {
+  return allreduce_impl(comm, grad_off, param_off, mom_off, start, end, fuse_sgd, prescale, lr, momentum,
+                        weight_decay, algo, blocks, channel, stream_, false);
 }
 
 /* Owner-side half of the fused wgrad -> reduce-scatter path (experimental; see conv_wgrad_push):
@@ -1050,6 +1089,7 @@ struct Reducer {
   cudaEvent_t done = nullptr;
   int launched = 0;
   // experimental: buckets whose conv weight gradient arrives through conv_wgrad_push staging
+  bool lazy_exit = false;   // experimental: only the last bucket kernel of a step keeps its exit barrier
   bool staged = false;
   long long stage_buf_off = 0;
   std::vector<long long> pushed_lo, pushed_hi, stage_base;
@@ -1129,8 +1169,19 @@ extern "C" int b200dp_reducer_bucket_ready(void* reducer, int k, b200dp_stream_t
                                     r->end[k], r->pushed_lo[k], r->pushed_hi[k], r->stage_base[k], r->lr, r->momentum,
                                     r->weight_decay, (r->comm->prefer_nvls && r->comm->mc_base) ? 1 : 0, r->blocks,
                                     r->channel, r->side);
-  return b200dp_allreduce(r->comm, r->grad_off, r->param_off, r->mom_off, r->start[k], r->end[k], r->fuse_sgd,
-                          r->prescale, r->lr, r->momentum, r->weight_decay, 0, r->blocks, r->channel, r->side);
+  const bool skip_exit = r->lazy_exit && k != static_cast<int>(r->ready.size()) - 1;
+  return allreduce_impl(r->comm, r->grad_off, r->param_off, r->mom_off, r->start[k], r->end[k], r->fuse_sgd,
+                        r->prescale, r->lr, r->momentum, r->weight_decay, 0, r->blocks, r->channel, r->side, skip_exit);
+}
+
+/* Experimental: bucket kernels 0 .. n-2 of a step drop their exit barrier (the entry barrier of the next
+ * bucket kernel on the channel implies it); bucket_ready() must then be called in index order, which is the
+ * gradient-ready order the executor uses. */
+extern "C" int b200dp_reducer_set_lazy_exit(void* reducer, int on) {
+  auto* r = static_cast<Reducer*>(reducer);
+  if (!r) return B200DP_EINVAL;
+  r->lazy_exit = on != 0;
+  return 0;
 }
 
 /* Experimental: tell the reducer which part of every bucket is delivered by conv_wgrad_push

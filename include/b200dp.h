@@ -327,6 +327,9 @@ int b200dp_reducer_destroy(void* reducer);
 int b200dp_reducer_stream(void* reducer, void** stream_out);
 /* CTAs per bucket collective for subsequent bucket_ready() calls (re-capture the step afterwards). */
 int b200dp_reducer_set_blocks(void* reducer, int blocks);
+/* Experimental: all bucket kernels of a step but the last drop their exit barrier (implied by the entry
+ * barrier of the next bucket kernel); requires bucket_ready() in index order. */
+int b200dp_reducer_set_lazy_exit(void* reducer, int on);
 /* Experimental: per bucket, the element range delivered by b200dp_conv_wgrad_push and its staging area;
  * such buckets run b200dp_reduce_staged_sgd instead of the all-reduce (pushed_lo == pushed_hi: unchanged). */
 int b200dp_reducer_set_staged(void* reducer, long long stage_buf_off, const long long* pushed_lo,

@@ -28,7 +28,8 @@ else
   B200DP_EXPERIMENTAL=1 timeout 600 python -m pytest tests/test_gpu_experimental.py -m "gpu and multigpu" -q \
       --timeout 400 2>&1 | tail -15 | tee $OUT/tests_${N}gpu.log
   echo "== A/B, $N GPUs part3, 100 steps each"
-  for cfg in "" "B200DP_PART3_PREP_OVERLAP=1" "B200DP_WGRAD_PUSH=1" "B200DP_PART3_PREP_OVERLAP=1 B200DP_WGRAD_PUSH=1" ""; do
+  for cfg in "" "B200DP_LAZY_EXIT_BARRIER=1" "B200DP_PART3_PREP_OVERLAP=1" "B200DP_WGRAD_PUSH=1" \
+             "B200DP_LAZY_EXIT_BARRIER=1 B200DP_WGRAD_PUSH=1" ""; do
     v=$(env $cfg timeout 200 $RUN bench.py --gpus $N --steps 100 --no-e2e 2>&1 | ms)
     echo "  [${cfg:-baseline}] ms/step=$v" | tee -a $OUT/ab_${N}gpu.log
   done

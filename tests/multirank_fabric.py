@@ -179,6 +179,9 @@ class FabricReducer:
     def finalize(self):
         pass
 
+    def set_lazy_exit(self, on=True):
+        pass
+
     def stream(self, device):
         class _Stream:
             def wait_event(self, ev):

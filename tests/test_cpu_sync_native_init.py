@@ -26,6 +26,9 @@ class FakeReducer:
     def set_staged(self, stage_off, lo, hi, base):
         self.staged = (stage_off, list(lo), list(hi), list(base))
 
+    def set_lazy_exit(self, on=True):
+        self.lazy_exit = on
+
     def stream(self, device):
         return "reducer-stream"
 
@@ -80,7 +83,7 @@ def fake_native():
 def _stubs(monkeypatch):
     monkeypatch.setattr(sync_native, "BucketReducer", FakeReducer)
     monkeypatch.setattr(sync_native.K, "BatchedWeightPrep", lambda specs: (lambda: None))
-    for v in ("B200DP_PART3_PREP_OVERLAP", "B200DP_WGRAD_PUSH"):
+    for v in ("B200DP_PART3_PREP_OVERLAP", "B200DP_WGRAD_PUSH", "B200DP_LAZY_EXIT_BARRIER"):
         monkeypatch.delenv(v, raising=False)
 
 
@@ -181,3 +184,12 @@ def test_sync_impl_option_selects_the_allreduce_kernel():
         assert type(s).__name__ == "AllReduceSync" and s.algo == code
     with pytest.raises(ValueError):
         TrainConfig(mode="part2b", num_nodes=2, rank=0, sync_impl="ring")
+
+
+def test_lazy_exit_barrier_toggle_is_not_combined_with_the_relayout_behind_the_buckets(monkeypatch):
+    monkeypatch.setenv("B200DP_LAZY_EXIT_BARRIER", "1")
+    nv, s = _make(4)
+    assert s._lazy_exit and s.reducer.lazy_exit is True
+    monkeypatch.setenv("B200DP_PART3_PREP_OVERLAP", "1")
+    nv, s = _make(4)
+    assert s._prep_overlap and not s._lazy_exit and not hasattr(s.reducer, "lazy_exit")

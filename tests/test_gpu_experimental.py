@@ -409,3 +409,54 @@ def test_bulk_copy_reduce_from_out_matches(shape):
     scale = s0.abs().max().item() + 1e-6
     assert ((s1 - 1.0) - s0).abs().max().item() < 1e-4 * scale + 1e-5
     assert abs(s1[C].item() - 1.0) < 1e-6                                        # gamma == 0: no contribution to S2
+
+
+def _env_worker(rank, world, tag, env, port, outdir):
+    import os as _os
+    for k, v in env.items():
+        _os.environ[k] = v
+    _os.environ["LOCAL_RANK"] = str(rank)
+    from cs744_pytorch_distributed_tutorial_b200.config import TrainConfig
+    from cs744_pytorch_distributed_tutorial_b200.engine import Trainer
+    torch.cuda.set_device(rank)
+    cfg = TrainConfig(mode="part3", master_ip="127.0.0.1", num_nodes=world, rank=rank, port=port, device="cuda",
+                      per_rank_batch=32, eval=False, lr=0.01, timeout_s=60)
+    tr = Trainer(cfg)
+    nv = tr.backend.native
+    init = nv.flat_params.cpu()
+    g = torch.Generator().manual_seed(400 + rank)
+    losses = []
+    for _ in range(4):
+        x = torch.randn(32, 3, 32, 32, generator=g).pin_memory()
+        y = torch.randint(0, 10, (32,), generator=g).pin_memory()
+        losses.append(float(tr.train_step(x, y).item()))
+    torch.cuda.synchronize()
+    torch.save({"params": nv.flat_params.cpu(), "init": init, "losses": losses}, _os.path.join(outdir, f"{tag}_{rank}.pt"))
+    tr.close()
+
+
+@pytest.mark.multigpu
+@pytest.mark.parametrize("env", [{"B200DP_LAZY_EXIT_BARRIER": "1"}, {"B200DP_PART3_PREP_OVERLAP": "1"},
+                                 {"B200DP_LAZY_EXIT_BARRIER": "1", "B200DP_WGRAD_PUSH": "1"}])
+def test_part3_scheduling_toggles_keep_replicas_identical_and_match_the_default(env):
+    import sys
+    import tempfile
+    import torch.multiprocessing as mp
+    sys.path.insert(0, os.path.dirname(__file__))
+    from helpers import free_port
+    n = torch.cuda.device_count()
+    world = 8 if n >= 8 else 4 if n >= 4 else 2
+    off = {k: "0" for k in ("B200DP_LAZY_EXIT_BARRIER", "B200DP_PART3_PREP_OVERLAP", "B200DP_WGRAD_PUSH")}
+    res = {}
+    with tempfile.TemporaryDirectory() as d:
+        for tag, e in (("default", off), ("toggled", {**off, **env})):
+            mp.spawn(_env_worker, args=(world, tag, e, free_port(), d), nprocs=world, join=True)
+            res[tag] = [torch.load(os.path.join(d, f"{tag}_{r}.pt")) for r in range(world)]
+    for tag, ranks in res.items():
+        for r in ranks[1:]:
+            assert torch.equal(ranks[0]["params"], r["params"]), f"{tag}: replicas differ"
+    a, b = res["default"][0], res["toggled"][0]
+    assert abs(a["losses"][0] - b["losses"][0]) < 1e-2
+    da, db = a["params"] - a["init"], b["params"] - b["init"]
+    assert torch.nn.functional.cosine_similarity(da, db, dim=0).item() > 0.97
+    assert abs(db.norm().item() / da.norm().item() - 1) < 0.05

@@ -362,7 +362,11 @@ class NativeBackend:
             self.store.barrier("engine")
 
     def optimizer_state(self) -> dict:
+        """Collective at world > 1: every rank must call it (the momentum slices kept by their owners are
+        gathered over NVLink first, so the dict equals what ``torch.optim.SGD`` would hold)."""
         nv = self.native
+        self.sync.gather_optimizer_state()
+        torch.cuda.synchronize(self.device)
         bufs = {e.name: nv._view(nv.flat_momentum, e).detach().cpu().contiguous() for e in nv.layout.entries}
         return {"momentum_buffers": bufs, "lr": self.cfg.lr, "momentum": self.cfg.momentum,
                 "weight_decay": self.cfg.weight_decay}
@@ -510,8 +514,9 @@ class Trainer:
     def save_checkpoint(self, path: str) -> None:
         from .checkpoint import save_checkpoint
         self.backend.synchronize()
+        opt = self.backend.optimizer_state()      # collective on the native backend (gathers sharded momentum)
         if self.cfg.rank == 0:
-            save_checkpoint(path, self.model, self.backend.optimizer_state(), self.global_step)
+            save_checkpoint(path, self.model, opt, self.global_step)
         self.backend.barrier()
 
     def load_checkpoint(self, path: str) -> None:

@@ -38,6 +38,7 @@ _lib.declare("b200dp_comm_barrier", [P, I, P])
 _lib.declare("b200dp_allreduce", [P, LL, LL, LL, LL, LL, I, I, F, F, F, I, I, I, P])
 _lib.declare("b200dp_ps_reduce_bcast", [P, LL, LL, LL, LL, I, I, I, I, P])
 _lib.declare("b200dp_broadcast", [P, LL, LL, I, I, I, P])
+_lib.declare("b200dp_allgather_slices", [P, LL, LL, LL, I, I, P])
 _lib.declare("b200dp_reducer_create", [P, I, POINTER(c_longlong), POINTER(c_longlong), LL, LL, LL, I, I, F, F, F,
                                        I, I, POINTER(c_void_p)])
 _lib.declare("b200dp_reducer_set_lr", [P, F])
@@ -190,6 +191,13 @@ class Communicator:
         if nbytes % 16:
             raise ValueError("broadcast needs a multiple of 16 bytes")
         call("b200dp_broadcast", self._h, self.offset_of(t), nbytes, root, blocks, channel, _lib.stream_ptr(stream))
+
+    def allgather_slices(self, t: torch.Tensor, start: int, end: int, blocks: int = 0, channel: int = CH_MAIN,
+                         stream: Optional[torch.cuda.Stream] = None) -> None:
+        """Every rank stores the 1/W slice of ``t[start:end]`` it owns (the slicing of the fused two-shot /
+        NVLS collectives) into every peer's copy -- assembles per-owner state such as SGD momentum."""
+        call("b200dp_allgather_slices", self._h, self.offset_of(t), start, end, blocks, channel,
+             _lib.stream_ptr(stream))
 
     def close(self) -> None:
         if self._h is not None:

@@ -67,6 +67,10 @@ class NativeSync:
         """Synchronise gradients into ``flat_grads`` without touching the parameters."""
         raise NotImplementedError
 
+    def gather_optimizer_state(self) -> None:
+        """Collective (every rank calls it): make ``flat_momentum`` complete on every rank.  The fused
+        collectives update momentum only on the owner of each 1/W slice; strategies that shard it override this."""
+
     def close(self) -> None:
         pass
 
@@ -178,6 +182,10 @@ class AllReduceSync(NativeSync):
         else:
             self.sync_only()
             self._local_sgd()
+
+    def gather_optimizer_state(self) -> None:
+        if self.fuse_optimizer and self.world > 1:
+            self.comm.allgather_slices(self.native.flat_momentum, 0, self.n, channel=CH_MAIN)
 
 
 class BucketedOverlapSync(NativeSync):
@@ -312,6 +320,13 @@ class BucketedOverlapSync(NativeSync):
             self._local_sgd()
         if self._prep_overlap:
             self._prep_lo()
+
+    def gather_optimizer_state(self) -> None:
+        # per bucket, with the bucket's own slicing; the small (one-shot) buckets already hold identical
+        # momentum on every rank, for them the gather rewrites equal values
+        if self.fuse_optimizer and self.world > 1:
+            for b in self.buckets:
+                self.comm.allgather_slices(self.native.flat_momentum, b.start, b.end, channel=CH_MAIN)
 
     def close(self) -> None:
         self.native.on_bucket_ready = None

@@ -505,6 +505,31 @@ __global__ void __launch_bounds__(512) broadcast_kernel(const CommDev c, const R
   end_collective(c, a.channel, epoch);
 }
 
+// ---------------------------------------------------------------------------
+// all-gather of owner slices: the element range [start, end) of a flat buffer at heap byte offset
+// grad_off is owned in W equal float4 slices (the slicing of the two-shot / NVLS / staged kernels);
+// every rank stores ITS slice into every peer's copy.  Used before a checkpoint: the fused collectives
+// keep SGD momentum only on the owner of a slice, so the full optimizer state has to be assembled.
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(512) allgather_slices_kernel(const CommDev c, const RangeArgs a) {
+  const uint32_t epoch = begin_collective(c, a.channel);
+  rank_barrier(c, a.channel, 0, epoch);
+  const int W = c.world;
+  const long n4 = (a.end - a.start) >> 2;
+  const long per = (n4 + W - 1) / W;
+  const long lo = min(per * c.rank, n4), hi = min(lo + per, n4);
+  const long stride = static_cast<long>(gridDim.x) * blockDim.x;
+  for (long i = lo + blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < hi; i += stride) {
+    const size_t eoff = static_cast<size_t>(a.start + (i << 2)) * sizeof(float);
+    const float4 v = *reinterpret_cast<const float4*>(c.peers.base[c.rank] + a.grad_off + eoff);
+#pragma unroll
+    for (int r = 0; r < kMaxWorld; ++r)
+      if (r < W && r != c.rank) st_peer_f4(reinterpret_cast<float*>(c.peers.base[r] + a.grad_off + eoff), v);
+  }
+  rank_barrier(c, a.channel, 1, epoch);
+  end_collective(c, a.channel, epoch);
+}
+
 __global__ void barrier_kernel(const CommDev c, int channel) {
   const uint32_t epoch = begin_collective(c, channel);
   rank_barrier(c, channel, 0, epoch);
@@ -1064,6 +1089,22 @@ extern "C" int b200dp_broadcast(void* comm, long long byte_off, long long nbytes
   a.channel = channel;
   a.root = root;
   broadcast_kernel<<<blocks, 512, 0, static_cast<cudaStream_t>(stream_)>>>(dev_view(c), a);
+  B200DP_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200dp_allgather_slices(void* comm, long long byte_off, long long start, long long end, int blocks,
+                                       int channel, b200dp_stream_t stream_) {
+  auto* c = static_cast<Comm*>(comm);
+  if (blocks <= 0) blocks = (end - start) > (1 << 18) ? 32 : 4;
+  int rc = check_range(c, start, end, blocks, channel, "allgather_slices");
+  if (rc) return rc;
+  RangeArgs a{};
+  a.grad_off = static_cast<size_t>(byte_off);
+  a.start = start;
+  a.end = end;
+  a.channel = channel;
+  allgather_slices_kernel<<<blocks, 512, 0, static_cast<cudaStream_t>(stream_)>>>(dev_view(c), a);
   B200DP_CUDA_TRY(cudaGetLastError());
   return 0;
 }

@@ -311,6 +311,14 @@ int b200dp_ps_reduce_bcast(void* comm, long long grad_off, long long stage_off, 
 int b200dp_broadcast(void* comm, long long byte_off, long long nbytes, int root, int blocks, int channel,
                      b200dp_stream_t stream);
 
+/* All-gather of owner slices: elements [start, end) of the flat fp32 buffer at heap byte offset byte_off are
+ * owned in `world` equal float4 slices (ceil(n4 / world) each, the slicing of the two-shot / NVLS collectives);
+ * every rank stores its slice into every peer's copy.  Assembles the SGD momentum -- which the fused
+ * collectives keep only on a slice's owner -- before a checkpoint, so that the saved optimizer state equals
+ * torch.optim.SGD's (ref: optimizer at master/part3/part3.py:117-118). */
+int b200dp_allgather_slices(void* comm, long long byte_off, long long start, long long end, int blocks, int channel,
+                            b200dp_stream_t stream);
+
 /* Bucket reducer (the role of DDP's C++ Reducer, ref: master/part3/part3.py:116): per-bucket
  * all-reduce(+SGD) on a high-priority side stream with a capped CTA count, forked from and
  * joined back into the compute stream with events (CUDA-graph capturable). */

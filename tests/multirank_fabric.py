@@ -139,12 +139,49 @@ class FabricComm:
             mean = sum(e.flat_grads[start:end] / W for e in ex)
         else:
             mean = sum(e.flat_grads[start:end] for e in ex) / W
-        for e in ex:
-            e.flat_grads[start:end] = mean
-            if params is not None:
+        if params is None:
+            for e in ex:
+                e.flat_grads[start:end] = mean
+            return
+        n4 = (end - start) // 4
+        if n4 * 16 <= 256 * 1024:
+            # one-shot kernel: every rank reduces the whole range and updates its own momentum and parameters
+            for e in ex:
+                e.flat_grads[start:end] = mean
                 p, m = e.flat_params[start:end], e.flat_momentum[start:end]
                 m.mul_(momentum).add_(mean + weight_decay * p)
                 p.sub_(lr * m)
+            return
+        # two-shot / NVLS kernels: momentum and the mean gradient exist only on the OWNER of each 1/W slice
+        per4 = (n4 + W - 1) // W
+        for r in range(W):
+            lo4 = min(per4 * r, n4)
+            hi4 = min(lo4 + per4, n4)
+            if hi4 <= lo4:
+                continue
+            a, b = start + 4 * lo4, start + 4 * hi4
+            g = mean[a - start: b - start]
+            p, m = ex[r].flat_params[a:b], ex[r].flat_momentum[a:b]
+            m.mul_(momentum).add_(g + weight_decay * p)
+            new_p = p - lr * m
+            ex[r].flat_grads[a:b] = g
+            for e in ex:
+                e.flat_params[a:b] = new_p
+
+    def allgather_slices(self, t, start, end, blocks=0, channel=0, stream=None):
+        """allgather_slices_kernel: every owner's slice of `flat_momentum[start:end]` goes to every rank."""
+        if not self._once(("gather", start, end)):
+            return
+        ex, W = self.fabric.execs, self.world
+        n4 = (end - start) // 4
+        per4 = (n4 + W - 1) // W
+        for r in range(W):
+            lo4 = min(per4 * r, n4)
+            hi4 = min(lo4 + per4, n4)
+            a, b = start + 4 * lo4, start + 4 * hi4
+            for e in ex:
+                if e is not ex[r]:
+                    e.flat_momentum[a:b] = ex[r].flat_momentum[a:b]
 
     def ps_reduce_bcast(self, grads, start, end, *, root=0, staging=None, blocks=0, channel=0, stream=None):
         if not self._once("ps"):

@@ -221,3 +221,38 @@ def test_every_synchronisation_mode_reaches_the_same_parameters(emu, mode, fuse)
     batches = _batches(world, steps=2, B=2)
     fabric = _run(emu, world, batches, mode=mode, fuse=fuse)
     _check_against_reference(fabric, _reference(world, batches))
+
+
+@pytest.mark.parametrize("mode", ["part2b", "part3"])
+def test_sharded_momentum_is_gathered_for_the_checkpoint(emu, mode):
+    """The fused collectives keep SGD momentum only on the owner of each 1/W slice.  A checkpoint must hold
+    what torch.optim.SGD holds (ref: optimizer at master/part3/part3.py:117-118), so every rank gathers the
+    owners' slices first; before the gather a non-owner's copy is stale."""
+    world = 3
+    batches = _batches(world, steps=2, B=2)
+    fabric = _run(emu, world, batches, mode=mode, fuse=True)
+    nv0, nv1 = fabric.execs[0], fabric.execs[1]
+    assert not torch.equal(nv0.flat_momentum, nv1.flat_momentum), "the emulation no longer models slice ownership"
+    for s in fabric.syncs:
+        s.gather_optimizer_state()
+    for nv in fabric.execs[1:]:
+        assert torch.equal(nv.flat_momentum, nv0.flat_momentum)
+    # against torch.optim.SGD's buffers after the same two steps
+    ref = _base_model().train()
+    opt = torch.optim.SGD(ref.parameters(), lr=LR, momentum=MOM, weight_decay=WD)
+    for step in batches:
+        acc = [torch.zeros_like(p) for p in ref.parameters()]
+        for x, y in step:
+            ref.zero_grad()
+            torch.nn.functional.cross_entropy(ref(x), y).backward()
+            for a, p in zip(acc, ref.parameters()):
+                a += p.grad / world
+        for a, p in zip(acc, ref.parameters()):
+            p.grad = a
+        opt.step()
+    ref_named = dict(ref.named_parameters())
+    for e in nv0.layout.entries:
+        got = nv0._view(nv0.flat_momentum, e).flatten()
+        want = opt.state[ref_named[e.name]]["momentum_buffer"].flatten()
+        rel = ((got - want).norm() / (want.norm() + 1e-12)).item()
+        assert rel < 2e-2, f"momentum of {e.name}: relative L2 {rel:.3e} against torch.optim.SGD"

@@ -250,3 +250,74 @@ def test_nvls_multimem_allreduce():
         mp.spawn(_nvls_worker, args=(world, free_port(), d), nprocs=world, join=True)
         fails = [open(os.path.join(d, f"fail_{r}.txt")).read() for r in range(world)]
     assert not any(fails), "\n".join(f for f in fails if f)
+
+
+def _resume_worker(rank, world, mode, phase, port, outdir):
+    from cs744_pytorch_distributed_tutorial_b200.config import TrainConfig
+    from cs744_pytorch_distributed_tutorial_b200.engine import Trainer
+    torch.cuda.set_device(rank)
+    os.environ["LOCAL_RANK"] = str(rank)
+    ckpt = os.path.join(outdir, f"{mode}.ckpt")
+    cfg = TrainConfig(mode=mode, master_ip="127.0.0.1", num_nodes=world, rank=rank, port=port, device="cuda",
+                      per_rank_batch=32, eval=False, lr=0.01, timeout_s=60,
+                      resume=ckpt if phase == "resume" else None)
+    tr = Trainer(cfg)
+    nv = tr.backend.native
+
+    def batch(step):
+        g = torch.Generator().manual_seed(1000 * step + rank)
+        return (torch.randn(32, 3, 32, 32, generator=g).pin_memory(),
+                torch.randint(0, 10, (32,), generator=g).pin_memory())
+
+    out = {}
+    steps = {"full": range(4), "first": range(3), "resume": range(3, 4)}[phase]
+    for s in steps:
+        if s == 3:
+            torch.cuda.synchronize()
+            out["p3"] = nv.flat_params.cpu()
+        tr.train_step(*batch(s))
+    torch.cuda.synchronize()
+    out["p_end"] = nv.flat_params.cpu()
+    if phase == "first":
+        out["mom_before"] = nv.flat_momentum.cpu()
+        tr.save_checkpoint(ckpt)             # collective: gathers the owners' momentum slices
+        out["mom_after"] = nv.flat_momentum.cpu()
+    torch.save(out, os.path.join(outdir, f"{mode}_{phase}_{rank}.pt"))
+    tr.close()
+
+
+@pytest.mark.parametrize("mode", ["part3", "part2b"])
+def test_checkpoint_holds_the_full_momentum_and_resume_continues_the_run(mode):
+    """Fused modes keep SGD momentum on the owner of each 1/W slice; the checkpoint must still hold
+    torch.optim.SGD's full state (ref: optimizer at master/part3/part3.py:117-118) and a run resumed from
+    it in a fresh process group must take the step the uninterrupted run takes."""
+    world = _world()
+    with tempfile.TemporaryDirectory() as d:
+        res = {}
+        for phase in ("full", "first", "resume"):
+            mp.spawn(_resume_worker, args=(world, mode, phase, free_port(), d), nprocs=world, join=True)
+            res[phase] = [torch.load(os.path.join(d, f"{mode}_{phase}_{r}.pt")) for r in range(world)]
+        ck = torch.load(os.path.join(d, f"{mode}.ckpt"), weights_only=False)
+    first = res["first"]
+    # before the gather a non-owner's copy differs from the owner's; afterwards every rank holds the same
+    assert not torch.equal(first[0]["mom_before"], first[1]["mom_before"])
+    for r in first[1:]:
+        assert torch.equal(first[0]["mom_after"], r["mom_after"]), "momentum differs across ranks after the gather"
+    # each rank's own live values survived the gather wherever it is the owner: the union is what was saved
+    saved = torch.cat([v.flatten() for v in ck["optimizer"]["momentum_buffers"].values()])
+    assert saved.abs().sum() > 0
+    # no stale zero slices: the big conv tensors must be dense in the saved state
+    for name, v in ck["optimizer"]["momentum_buffers"].items():
+        if v.dim() == 4 and v.numel() > 100_000:
+            frac = (v != 0).float().mean().item()
+            assert frac > 0.95, f"{name}: only {frac:.2f} of the saved momentum is non-zero"
+    # the resumed step is the uninterrupted step (momentum carries ~2.7x the gradient after three steps,
+    # so a lost momentum shows up as a step of the wrong length)
+    full, resumed = res["full"][0], res["resume"][0]
+    d_full = full["p_end"] - full["p3"]
+    d_res = resumed["p_end"] - resumed["p3"]
+    assert torch.allclose(resumed["p3"], first[0]["p_end"]), "the resumed run did not start from the saved parameters"
+    cos = torch.nn.functional.cosine_similarity(d_full, d_res, dim=0).item()
+    ratio = d_res.norm().item() / d_full.norm().item()
+    assert cos > 0.9, f"{mode}: resumed step cosine {cos}"
+    assert abs(ratio - 1) < 0.15, f"{mode}: resumed step length ratio {ratio}"

@@ -48,7 +48,7 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--no-cuda-graph", action="store_true")
     p.add_argument("--train-size", type=int, default=50000)
     p.add_argument("--test-size", type=int, default=10000)
-    p.add_argument("--real-data", action="store_true", help="use ../../data/cifar-10-batches-py if present")
+    p.add_argument("--real-data", action="store_true", help="train on ../../data/cifar-10-batches-py (an error if it is missing)")
     p.add_argument("--no-augment", action="store_true")
     p.add_argument("--loader", choices=("python", "native"), default="python",
                    help="batch assembly: vectorised torch ops, or the C++ thread pool of csrc/loader.cpp")

@@ -91,7 +91,12 @@ class CIFAR10Batches(Dataset):
 
 
 def build_dataset(cfg, train: bool, transform=None) -> Dataset:
-    if not cfg.synthetic and CIFAR10Batches.present(cfg.data_root):
+    if not cfg.synthetic:
+        if not CIFAR10Batches.present(cfg.data_root):
+            # a silent fall-back would report losses and accuracies that look like CIFAR-10 results and are not
+            raise FileNotFoundError(
+                f"real data was requested but {os.path.join(cfg.data_root, 'cifar-10-batches-py')} does not exist "
+                "(there is no download path here); drop --real-data to train on the synthetic set")
         return CIFAR10Batches(cfg.data_root, train, transform)
     n = cfg.train_size if train else cfg.test_size
     return SyntheticCIFAR10(n, train, seed=1234, transform=transform)
@@ -226,6 +231,8 @@ class BatchPipeline:
         self._y = [torch.empty(batch, dtype=torch.int64, pin_memory=pin) for _ in range(ring)]
         self._gen = torch.Generator().manual_seed(seed * 7919 + rank)
         self._slot = 0
+        self._copied = [None] * ring      # per slot: event behind the host->device copy of its last batch
+        self._last_slot = None
 
     def __len__(self) -> int:
         n = len(self.sampler)
@@ -235,12 +242,24 @@ class BatchPipeline:
     def dataset_len(self) -> int:
         return self.data.shape[0]
 
+    def consumed(self, event=None) -> None:
+        """The batch yielded last has been handed to the device; ``event`` (recorded behind its asynchronous
+        host->device copy, or None) must have completed before that pinned buffer is written again.  Without
+        this hand-shake a GPU running ``ring`` steps behind the host would copy a half-overwritten batch."""
+        if self._last_slot is not None:
+            self._copied[self._last_slot] = event
+
     def __iter__(self):
         idx = self.sampler.indices()
         for b in range(len(self)):
             sel = idx[b * self.batch: (b + 1) * self.batch]
             n = sel.numel()
+            ev = self._copied[self._slot]
+            if ev is not None:
+                ev.synchronize()
+                self._copied[self._slot] = None
             x, y = self._x[self._slot][:n], self._y[self._slot][:n]
+            self._last_slot = self._slot
             self._slot = (self._slot + 1) % len(self._x)
             augment_batch(self.data[sel], x, self._gen, self.augment)
             torch.index_select(self.targets, 0, sel, out=y)

@@ -348,6 +348,9 @@ class NativeBackend:
         key = f"red/{self._red_round}/"
         self.store.set(key + str(self.cfg.rank), struct.pack("<d", value))
         vals = [struct.unpack("<d", self.store.get(key + str(r)))[0] for r in range(self.cfg.world_size)]
+        if self.cfg.rank == 0 and self._red_round > 2:
+            # every rank has read round - 2 (it has since written round - 1, which rank 0 just read)
+            self.store.delete_prefix(f"red/{self._red_round - 2}/")
         return max(vals) if op == "max" else sum(vals)
 
     def all_reduce_sum(self, value: float) -> float:

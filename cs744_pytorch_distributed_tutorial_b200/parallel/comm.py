@@ -25,6 +25,7 @@ _lib.declare("b200dp_store_set", [P, c_char_p, c_char_p, I])
 _lib.declare("b200dp_store_get", [P, c_char_p, c_char_p, I, POINTER(c_int)])
 _lib.declare("b200dp_store_add", [P, c_char_p, LL, POINTER(c_longlong)])
 _lib.declare("b200dp_store_barrier", [P, c_char_p])
+_lib.declare("b200dp_store_delete_prefix", [P, c_char_p])
 _lib.declare("b200dp_store_destroy", [P])
 _lib.declare("b200dp_comm_create", [P, I, I, I, LL, POINTER(c_void_p)])
 _lib.declare("b200dp_comm_create_ex", [P, I, I, I, LL, I, POINTER(c_void_p)])
@@ -85,6 +86,10 @@ class Store:
 
     def barrier(self, name: str = "b") -> None:
         call("b200dp_store_barrier", self._h, name.encode())
+
+    def delete_prefix(self, prefix: str) -> None:
+        """Erase every key that starts with ``prefix`` (keys of exchanges every rank has finished)."""
+        call("b200dp_store_delete_prefix", self._h, prefix.encode())
 
     def close(self) -> None:
         if self._h is None:

@@ -42,11 +42,13 @@
 extern "C" int b200dp_store_set(void* h, const char* key, const void* data, int len);
 extern "C" int b200dp_store_get(void* h, const char* key, void* buf, int cap, int* out_len);
 extern "C" int b200dp_store_barrier(void* h, const char* name);
+extern "C" int b200dp_store_timeout_ms(void* h);
 
 namespace b200dp {
 int fd_listen(const std::string& name);
 int fd_send(const std::string& name, int fd, int tag, int timeout_ms);
 int fd_recv(int listen_fd, int* tag);
+int fd_recv_timeout(int listen_fd, int* tag, int timeout_ms);
 
 constexpr int kMaxWorld = 8;
 constexpr int kMaxBlocks = 256;
@@ -652,24 +654,96 @@ static int map_handle(const DriverApi& d, CUmemGenericAllocationHandle h, size_t
   return 0;
 }
 
-// Heap through the virtual-memory-management API so that it can be bound to an NVSwitch multicast
-// object: cuMemCreate -> export as POSIX fd -> every peer imports and maps it; rank 0 creates the
-// multicast object, everyone adds its device, binds its allocation and maps the multicast address.
-static int create_vmm_heap(Comm* c) {
+// Undo whatever create_vmm_heap() has set up so far (also the tail of b200dp_comm_destroy).
+static void release_vmm_heap(Comm* c) {
   const DriverApi& d = driver_api();
+  if (c->mc_base) {
+    d.memUnmap(reinterpret_cast<CUdeviceptr>(c->mc_base), c->heap_bytes);
+    d.addrFree(reinterpret_cast<CUdeviceptr>(c->mc_base), c->heap_bytes);
+    c->mc_base = nullptr;
+  }
+  for (int r = 0; r < c->world; ++r) {
+    if (r == c->rank) continue;
+    if (c->peers.base[r] != nullptr) {
+      d.memUnmap(reinterpret_cast<CUdeviceptr>(c->peers.base[r]), c->heap_bytes);
+      d.addrFree(reinterpret_cast<CUdeviceptr>(c->peers.base[r]), c->heap_bytes);
+      c->peers.base[r] = nullptr;
+    }
+    if (c->peer_handle[r]) {
+      d.memRelease(c->peer_handle[r]);
+      c->peer_handle[r] = 0;
+    }
+  }
+  if (c->mc_handle) {
+    d.memRelease(c->mc_handle);
+    c->mc_handle = 0;
+  }
+  if (c->local_base) {
+    d.memUnmap(reinterpret_cast<CUdeviceptr>(c->local_base), c->heap_bytes);
+    d.addrFree(reinterpret_cast<CUdeviceptr>(c->local_base), c->heap_bytes);
+    c->local_base = nullptr;
+    c->peers.base[c->rank] = nullptr;
+  }
+  if (c->mem_handle) {
+    d.memRelease(c->mem_handle);
+    c->mem_handle = 0;
+  }
+  c->vmm = false;
+}
+
+// Every rank publishes whether `stage` worked for it and reads everybody's answer: either all ranks go on
+// or all of them give up together (and fall back to the CUDA-IPC heap with their store counters still in
+// step).  A rank that died instead of answering surfaces as a store timeout that names its key.
+static int vmm_agree(Comm* c, const std::string& gen, const char* stage, int my_rc) {
+  if (c->world == 1) return my_rc;
+  char mine[kErrorBufferSize];
+  strncpy(mine, error_buffer(), sizeof(mine) - 1);
+  mine[sizeof(mine) - 1] = 0;
+  const std::string prefix = "vmm/" + gen + "/" + stage + "/";
+  const char ok = my_rc == 0 ? 1 : 0;
+  int rc = b200dp_store_set(c->store, (prefix + std::to_string(c->rank)).c_str(), &ok, 1);
+  if (rc) return rc;
+  int failed_rank = -1;
+  for (int r = 0; r < c->world; ++r) {
+    char v = 0;
+    int len = 0;
+    rc = b200dp_store_get(c->store, (prefix + std::to_string(r)).c_str(), &v, 1, &len);
+    if (rc) return rc;
+    if (v == 0 && failed_rank < 0) failed_rank = r;
+  }
+  if (my_rc != 0) {
+    set_error("%s", mine);
+    return my_rc;
+  }
+  if (failed_rank >= 0) {
+    set_error("comm_create: rank %d failed at stage '%s' of the multicast heap set-up; every rank falls back",
+              failed_rank, stage);
+    return B200DP_ENOSYS;
+  }
+  return 0;
+}
+
+struct VmmScratch {  // host resources of the handshake, closed on every path
+  int lfd = -1, my_fd = -1, mc_fd = -1;
+  ~VmmScratch() {
+    if (lfd >= 0) ::close(lfd);
+    if (my_fd >= 0) ::close(my_fd);
+    if (mc_fd >= 0) ::close(mc_fd);
+  }
+};
+
+static int vmm_stage_local(Comm* c, const DriverApi& d) {
   if (!d.ok) {
     set_error("comm_create: the CUDA driver lacks the VMM / multicast entry points");
     return B200DP_ENOSYS;
   }
   int mc_supported = 0;
-  {
-    auto devGet = driver_fn<PFN_cuDeviceGet_v2000>("cuDeviceGet");
-    auto getAttr = driver_fn<PFN_cuDeviceGetAttribute_v2000>("cuDeviceGetAttribute");
-    CUdevice dv = 0;
-    if (!devGet || !getAttr) return B200DP_ENOSYS;
-    B200DP_CU_TRY(devGet(&dv, c->device));
-    B200DP_CU_TRY(getAttr(&mc_supported, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, dv));
-  }
+  auto devGet = driver_fn<PFN_cuDeviceGet_v2000>("cuDeviceGet");
+  auto getAttr = driver_fn<PFN_cuDeviceGetAttribute_v2000>("cuDeviceGetAttribute");
+  CUdevice dv = 0;
+  if (!devGet || !getAttr) return B200DP_ENOSYS;
+  B200DP_CU_TRY(devGet(&dv, c->device));
+  B200DP_CU_TRY(getAttr(&mc_supported, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, dv));
   if (!mc_supported) {
     set_error("comm_create: device %d does not support NVSwitch multicast", c->device);
     return B200DP_ENOSYS;
@@ -685,45 +759,28 @@ static int create_vmm_heap(Comm* c) {
   B200DP_CUDA_TRY(cudaMemset(c->local_base, 0, c->heap_bytes));
   c->peers.base[c->rank] = c->local_base;
   c->vmm = true;
-  if (c->world == 1) return 0;
+  return 0;
+}
 
-  // ---- agree on a socket-name token, open the listening sockets, exchange descriptors
-  static int generation = 0;
-  const std::string gen = std::to_string(generation++);
-  long long token = 0;
-  if (c->rank == 0) {
-    token = (static_cast<long long>(getpid()) << 20) ^ static_cast<long long>(globaltimer_host());
-    rc = b200dp_store_set(c->store, ("vmm/token/" + gen).c_str(), &token, sizeof(token));
-    if (rc) return rc;
-  }
-  int len = 0;
-  rc = b200dp_store_get(c->store, ("vmm/token/" + gen).c_str(), &token, sizeof(token), &len);
-  if (rc) return rc;
+// exchange the heap descriptors (and rank 0's multicast descriptor), import and map the peers' heaps
+static int vmm_stage_exchange(Comm* c, const DriverApi& d, VmmScratch& x, long long token, const std::string& gen,
+                              int timeout_ms) {
   auto sock_name = [&](int r) { return "b200dp-" + std::to_string(token) + "-" + gen + "-" + std::to_string(r); };
-  const int lfd = fd_listen(sock_name(c->rank));
-  if (lfd < 0) {
-    set_error("comm_create: rank %d cannot open its descriptor-passing socket", c->rank);
-    return B200DP_EINVAL;
-  }
-  rc = b200dp_store_barrier(c->store, "vmm_listen");
-  if (rc) return rc;
-  int my_fd = -1;
-  B200DP_CU_TRY(d.exportHandle(&my_fd, c->mem_handle, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0));
+  B200DP_CU_TRY(d.exportHandle(&x.my_fd, c->mem_handle, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0));
   for (int r = 0; r < c->world; ++r)
-    if (r != c->rank && fd_send(sock_name(r), my_fd, c->rank, 30000) != 0) {
+    if (r != c->rank && fd_send(sock_name(r), x.my_fd, c->rank, timeout_ms) != 0) {
       set_error("comm_create: rank %d could not pass its heap descriptor to rank %d", c->rank, r);
       return B200DP_ETIMEDOUT;
     }
-  int mc_fd = -1;
   if (c->rank == 0) {
     CUmulticastObjectProp mp{};
     mp.numDevices = c->world;
     mp.size = c->heap_bytes;
     mp.handleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
     B200DP_CU_TRY(d.mcCreate(&c->mc_handle, &mp));
-    B200DP_CU_TRY(d.exportHandle(&mc_fd, c->mc_handle, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0));
+    B200DP_CU_TRY(d.exportHandle(&x.mc_fd, c->mc_handle, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0));
     for (int r = 1; r < c->world; ++r)
-      if (fd_send(sock_name(r), mc_fd, 100, 30000) != 0) {
+      if (fd_send(sock_name(r), x.mc_fd, 100, timeout_ms) != 0) {
         set_error("comm_create: rank 0 could not pass the multicast descriptor to rank %d", r);
         return B200DP_ETIMEDOUT;
       }
@@ -731,41 +788,96 @@ static int create_vmm_heap(Comm* c) {
   const int expect = (c->world - 1) + (c->rank == 0 ? 0 : 1);
   for (int k = 0; k < expect; ++k) {
     int tag = -1;
-    const int fd = fd_recv(lfd, &tag);
+    const int fd = fd_recv_timeout(x.lfd, &tag, timeout_ms);
     if (fd < 0) {
-      set_error("comm_create: rank %d failed to receive a descriptor", c->rank);
-      return B200DP_EINVAL;
+      set_error("comm_create: rank %d %s while waiting for descriptor %d of %d (a peer failed before sending?)",
+                c->rank, fd == -2 ? "timed out" : "hit a socket error", k + 1, expect);
+      return fd == -2 ? B200DP_ETIMEDOUT : B200DP_EINVAL;
     }
+    int rc = 0;
     if (tag == 100) {
-      B200DP_CU_TRY(d.importHandle(&c->mc_handle, reinterpret_cast<void*>(static_cast<intptr_t>(fd)),
-                                   CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR));
+      CUresult r = d.importHandle(&c->mc_handle, reinterpret_cast<void*>(static_cast<intptr_t>(fd)),
+                                  CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR);
+      if (r != CUDA_SUCCESS) {
+        set_error("comm_create: importing the multicast descriptor -> CUresult %d", static_cast<int>(r));
+        rc = B200DP_EINVAL;
+      }
     } else if (tag >= 0 && tag < c->world && tag != c->rank) {
-      B200DP_CU_TRY(d.importHandle(&c->peer_handle[tag], reinterpret_cast<void*>(static_cast<intptr_t>(fd)),
-                                   CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR));
-      rc = map_handle(d, c->peer_handle[tag], c->heap_bytes, c->device, &c->peers.base[tag]);
-      if (rc) return rc;
+      CUresult r = d.importHandle(&c->peer_handle[tag], reinterpret_cast<void*>(static_cast<intptr_t>(fd)),
+                                  CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR);
+      if (r != CUDA_SUCCESS) {
+        set_error("comm_create: importing rank %d's heap descriptor -> CUresult %d", tag, static_cast<int>(r));
+        rc = B200DP_EINVAL;
+      } else {
+        rc = map_handle(d, c->peer_handle[tag], c->heap_bytes, c->device, &c->peers.base[tag]);
+      }
     }
     ::close(fd);
+    if (rc) return rc;
   }
-  ::close(lfd);
-  ::close(my_fd);
-  if (mc_fd >= 0) ::close(mc_fd);
+  return 0;
+}
+
+// Heap through the virtual-memory-management API so that it can be bound to an NVSwitch multicast
+// object: cuMemCreate -> export as POSIX fd -> every peer imports and maps it; rank 0 creates the
+// multicast object, everyone adds its device, binds its allocation and maps the multicast address.
+// Every stage ends with vmm_agree(): a failure on one rank (or a rank that stops answering, bounded by the
+// store / descriptor time-outs) makes ALL ranks release what they mapped and return an error together.
+static int create_vmm_heap(Comm* c) {
+  const DriverApi& d = driver_api();
+  static int generation = 0;
+  const std::string gen = std::to_string(generation++);
+  const int timeout_ms = c->store ? b200dp_store_timeout_ms(c->store) : 30000;
+  VmmScratch x;
+  auto fail = [&](int rc) {
+    release_vmm_heap(c);
+    return rc;
+  };
+
+  int rc = vmm_agree(c, gen, "alloc", vmm_stage_local(c, d));
+  if (rc) return fail(rc);
+  if (c->world == 1) return 0;
+
+  // ---- agree on a socket-name token, open the listening sockets
+  long long token = 0;
+  if (c->rank == 0) {
+    token = (static_cast<long long>(getpid()) << 20) ^ static_cast<long long>(globaltimer_host());
+    rc = b200dp_store_set(c->store, ("vmm/token/" + gen).c_str(), &token, sizeof(token));
+    if (rc) return fail(rc);
+  }
+  int len = 0;
+  rc = b200dp_store_get(c->store, ("vmm/token/" + gen).c_str(), &token, sizeof(token), &len);
+  if (rc) return fail(rc);
+  x.lfd = fd_listen("b200dp-" + std::to_string(token) + "-" + gen + "-" + std::to_string(c->rank));
+  rc = 0;
+  if (x.lfd < 0) {
+    set_error("comm_create: rank %d cannot open its descriptor-passing socket", c->rank);
+    rc = B200DP_EINVAL;
+  }
+  rc = vmm_agree(c, gen, "listen", rc);
+  if (rc) return fail(rc);
+
+  rc = vmm_agree(c, gen, "exchange", vmm_stage_exchange(c, d, x, token, gen, timeout_ms));
+  if (rc) return fail(rc);
+
   // ---- multicast: add devices, then bind memory, then map (each step is collective)
+  auto cu_stage = [&](const char* what, CUresult r) {
+    if (r == CUDA_SUCCESS) return 0;
+    set_error("comm_create: %s on rank %d -> CUresult %d", what, c->rank, static_cast<int>(r));
+    return static_cast<int>(B200DP_EINVAL);
+  };
   CUdevice cudev = 0;
-  {
-    auto devGet = driver_fn<PFN_cuDeviceGet_v2000>("cuDeviceGet");
-    if (!devGet) return B200DP_ENOSYS;
-    B200DP_CU_TRY(devGet(&cudev, c->device));
-  }
-  B200DP_CU_TRY(d.mcAddDevice(c->mc_handle, cudev));
-  rc = b200dp_store_barrier(c->store, "mc_add");
-  if (rc) return rc;
-  B200DP_CU_TRY(d.mcBindMem(c->mc_handle, 0, c->mem_handle, 0, c->heap_bytes, 0));
-  rc = b200dp_store_barrier(c->store, "mc_bind");
-  if (rc) return rc;
-  rc = map_handle(d, c->mc_handle, c->heap_bytes, c->device, &c->mc_base);
-  if (rc) return rc;
-  return b200dp_store_barrier(c->store, "mc_map");
+  auto devGet = driver_fn<PFN_cuDeviceGet_v2000>("cuDeviceGet");
+  rc = devGet ? cu_stage("cuDeviceGet", devGet(&cudev, c->device)) : static_cast<int>(B200DP_ENOSYS);
+  if (rc == 0) rc = cu_stage("cuMulticastAddDevice", d.mcAddDevice(c->mc_handle, cudev));
+  rc = vmm_agree(c, gen, "mc_add", rc);
+  if (rc) return fail(rc);
+  rc = vmm_agree(c, gen, "mc_bind",
+                 cu_stage("cuMulticastBindMem", d.mcBindMem(c->mc_handle, 0, c->mem_handle, 0, c->heap_bytes, 0)));
+  if (rc) return fail(rc);
+  rc = vmm_agree(c, gen, "mc_map", map_handle(d, c->mc_handle, c->heap_bytes, c->device, &c->mc_base));
+  if (rc) return fail(rc);
+  return 0;
 }
 
 }  // namespace b200dp
@@ -790,49 +902,70 @@ extern "C" int b200dp_comm_create_ex(void* store, int rank, int world, int devic
   c->device = device;
   c->store = store;
   c->heap_bytes = ((static_cast<size_t>(heap_bytes) + kSignalPadBytes + (2u << 20) - 1) >> 21) << 21;
-  B200DP_CUDA_TRY(cudaMalloc(reinterpret_cast<void**>(&c->epochs), 2 * kNumChannels * sizeof(uint32_t)));
-  B200DP_CUDA_TRY(cudaMemset(c->epochs, 0, 2 * kNumChannels * sizeof(uint32_t)));
+  // every failure path below releases what was set up so far; the caller only sees the error code
+  auto fail = [&](int rc) {
+    for (int r = 0; r < c->world; ++r)
+      if (c->ipc_opened[r]) cudaIpcCloseMemHandle(c->peers.base[r]);
+    if (c->vmm) release_vmm_heap(c);
+    else if (c->local_base) cudaFree(c->local_base);
+    if (c->epochs) cudaFree(c->epochs);
+    delete c;
+    return rc;
+  };
+  auto cuda_rc = [](cudaError_t e, const char* what) {
+    if (e == cudaSuccess) return 0;
+    set_error("comm_create: %s -> %s", what, cudaGetErrorString(e));
+    return static_cast<int>(e);
+  };
+  int rc = cuda_rc(cudaMalloc(reinterpret_cast<void**>(&c->epochs), 2 * kNumChannels * sizeof(uint32_t)), "cudaMalloc");
+  if (rc) return fail(rc);
+  rc = cuda_rc(cudaMemset(c->epochs, 0, 2 * kNumChannels * sizeof(uint32_t)), "cudaMemset");
+  if (rc) return fail(rc);
   c->done_blocks = c->epochs + kNumChannels;
   if (flags & 1) {
-    int rc = create_vmm_heap(c);
-    if (rc) return rc;
-    B200DP_CUDA_TRY(cudaDeviceSynchronize());
+    rc = create_vmm_heap(c);   // releases its own mappings on failure
+    if (rc) return fail(rc);
+    rc = cuda_rc(cudaDeviceSynchronize(), "cudaDeviceSynchronize");
+    if (rc) return fail(rc);
     if (world > 1) {
       rc = b200dp_store_barrier(store, "comm_create");
-      if (rc) return rc;
+      if (rc) return fail(rc);
     }
     *out_comm = c;
     return 0;
   }
-  B200DP_CUDA_TRY(cudaMalloc(reinterpret_cast<void**>(&c->local_base), c->heap_bytes));
-  B200DP_CUDA_TRY(cudaMemset(c->local_base, 0, c->heap_bytes));
-  B200DP_CUDA_TRY(cudaDeviceSynchronize());
+  rc = cuda_rc(cudaMalloc(reinterpret_cast<void**>(&c->local_base), c->heap_bytes), "cudaMalloc(heap)");
+  if (rc) return fail(rc);
+  rc = cuda_rc(cudaMemset(c->local_base, 0, c->heap_bytes), "cudaMemset(heap)");
+  if (rc == 0) rc = cuda_rc(cudaDeviceSynchronize(), "cudaDeviceSynchronize");
+  if (rc) return fail(rc);
   c->peers.base[rank] = c->local_base;
   if (world > 1) {
     cudaIpcMemHandle_t mine;
-    B200DP_CUDA_TRY(cudaIpcGetMemHandle(&mine, c->local_base));
+    rc = cuda_rc(cudaIpcGetMemHandle(&mine, c->local_base), "cudaIpcGetMemHandle");
+    if (rc) return fail(rc);
     static int generation = 0;
     const std::string prefix = "heap/" + std::to_string(generation++) + "/";
-    int rc = b200dp_store_set(store, (prefix + std::to_string(rank)).c_str(), &mine, sizeof(mine));
-    if (rc) return rc;
+    rc = b200dp_store_set(store, (prefix + std::to_string(rank)).c_str(), &mine, sizeof(mine));
+    if (rc) return fail(rc);
     for (int r = 0; r < world; ++r) {
       if (r == rank) continue;
       cudaIpcMemHandle_t h;
       int len = 0;
       rc = b200dp_store_get(store, (prefix + std::to_string(r)).c_str(), &h, sizeof(h), &len);
-      if (rc) return rc;
+      if (rc) return fail(rc);
       void* p = nullptr;
       cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
       if (e != cudaSuccess) {
         set_error("comm_create: rank %d cannot map rank %d's heap over CUDA IPC: %s", rank, r,
                   cudaGetErrorString(e));
-        return static_cast<int>(e);
+        return fail(static_cast<int>(e));
       }
       c->peers.base[r] = static_cast<char*>(p);
       c->ipc_opened[r] = true;
     }
     rc = b200dp_store_barrier(store, "comm_create");
-    if (rc) return rc;
+    if (rc) return fail(rc);
   }
   *out_comm = c;
   return 0;
@@ -870,22 +1003,21 @@ extern "C" int b200dp_comm_destroy(void* comm) {
   for (int r = 0; r < c->world; ++r)
     if (c->ipc_opened[r]) cudaIpcCloseMemHandle(c->peers.base[r]);
   if (c->vmm) {
+    // peers unmap each other's heaps before anybody releases its own allocation
     const DriverApi& d = driver_api();
     if (c->mc_base) {
       d.memUnmap(reinterpret_cast<CUdeviceptr>(c->mc_base), c->heap_bytes);
       d.addrFree(reinterpret_cast<CUdeviceptr>(c->mc_base), c->heap_bytes);
+      c->mc_base = nullptr;
     }
     for (int r = 0; r < c->world; ++r) {
       if (r == c->rank || c->peers.base[r] == nullptr) continue;
       d.memUnmap(reinterpret_cast<CUdeviceptr>(c->peers.base[r]), c->heap_bytes);
       d.addrFree(reinterpret_cast<CUdeviceptr>(c->peers.base[r]), c->heap_bytes);
-      if (c->peer_handle[r]) d.memRelease(c->peer_handle[r]);
+      c->peers.base[r] = nullptr;
     }
     if (c->world > 1 && c->store) b200dp_store_barrier(c->store, "comm_destroy2");
-    if (c->mc_handle) d.memRelease(c->mc_handle);
-    d.memUnmap(reinterpret_cast<CUdeviceptr>(c->local_base), c->heap_bytes);
-    d.addrFree(reinterpret_cast<CUdeviceptr>(c->local_base), c->heap_bytes);
-    d.memRelease(c->mem_handle);
+    release_vmm_heap(c);
     cudaFree(c->epochs);
     delete c;
     return 0;

@@ -10,7 +10,8 @@
 // Wire format (all integers little-endian):
 //   request : u8 op | u32 key_len | key bytes | u32 val_len | val bytes
 //   reply   : u32 status (0 ok, 1 timeout) | u32 val_len | val bytes
-// ops: 1 SET, 2 GET (blocks until the key exists or timeout), 3 ADD (i64 delta -> new value)
+// ops: 1 SET, 2 GET (blocks until the key exists or timeout), 3 ADD (i64 delta -> new value),
+//      4 DEL (erase every key with the given prefix)
 #include <arpa/inet.h>
 #include <errno.h>
 #include <netdb.h>
@@ -35,7 +36,7 @@
 
 namespace b200dp {
 
-enum : uint8_t { OP_SET = 1, OP_GET = 2, OP_ADD = 3 };
+enum : uint8_t { OP_SET = 1, OP_GET = 2, OP_ADD = 3, OP_DEL = 4 };
 
 static bool send_all(int fd, const void* buf, size_t n) {
   const char* p = static_cast<const char*>(buf);
@@ -70,7 +71,9 @@ class StoreServer {
   StoreServer() = default;
   ~StoreServer() { stop(); }
 
-  bool start(int port, std::string* err) {
+  // Binds to `ip` when it is a numeric address of this host (so the store is not reachable through other
+  // interfaces); a host name or an address that cannot be bound (NAT, 0.0.0.0) falls back to every interface.
+  bool start(const char* ip, int port, std::string* err) {
     listen_fd_ = ::socket(AF_INET, SOCK_STREAM, 0);
     if (listen_fd_ < 0) {
       *err = "socket() failed";
@@ -80,9 +83,15 @@ class StoreServer {
     setsockopt(listen_fd_, SOL_SOCKET, SO_REUSEADDR, &one, sizeof(one));
     sockaddr_in addr{};
     addr.sin_family = AF_INET;
-    addr.sin_addr.s_addr = htonl(INADDR_ANY);
     addr.sin_port = htons(static_cast<uint16_t>(port));
-    if (::bind(listen_fd_, reinterpret_cast<sockaddr*>(&addr), sizeof(addr)) != 0) {
+    in_addr want{};
+    bool bound = false;
+    if (ip != nullptr && inet_pton(AF_INET, ip, &want) == 1 && want.s_addr != htonl(INADDR_ANY)) {
+      addr.sin_addr = want;
+      bound = ::bind(listen_fd_, reinterpret_cast<sockaddr*>(&addr), sizeof(addr)) == 0;
+    }
+    addr.sin_addr.s_addr = htonl(INADDR_ANY);
+    if (!bound && ::bind(listen_fd_, reinterpret_cast<sockaddr*>(&addr), sizeof(addr)) != 0) {
       *err = std::string("bind() failed: ") + strerror(errno);
       ::close(listen_fd_);
       listen_fd_ = -1;
@@ -130,14 +139,29 @@ class StoreServer {
     }
   }
 
+  // A request that claims a key above 4 KiB or a value above 1 MiB is not one of ours: drop the connection
+  // instead of allocating what it asks for (the port is reachable by anything that can reach the host).
+  static constexpr uint32_t kMaxKeyLen = 4096, kMaxValLen = 1u << 20;
+
   void serve(int fd) {
+    try {
+      serve_loop(fd);
+    } catch (...) {
+      // e.g. std::bad_alloc: this client is dropped, the store keeps serving the others
+    }
+    ::close(fd);
+  }
+
+  void serve_loop(int fd) {
     for (;;) {
       uint8_t op;
       uint32_t klen, vlen;
       if (!recv_all(fd, &op, 1) || !recv_all(fd, &klen, 4)) break;
+      if (klen > kMaxKeyLen) break;
       std::string key(klen, '\0');
       if (klen && !recv_all(fd, &key[0], klen)) break;
       if (!recv_all(fd, &vlen, 4)) break;
+      if (vlen > kMaxValLen) break;
       std::string val(vlen, '\0');
       if (vlen && !recv_all(fd, &val[0], vlen)) break;
       uint32_t status = 0;
@@ -171,13 +195,17 @@ class StoreServer {
         kv_[key] = enc;
         out = enc;
         cv_.notify_all();
+      } else if (op == OP_DEL) {
+        // erase every key that starts with `key` (finished barrier rounds, host-side reductions)
+        std::lock_guard<std::mutex> lk(mu_);
+        for (auto it = kv_.lower_bound(key); it != kv_.end() && it->first.compare(0, key.size(), key) == 0;)
+          it = kv_.erase(it);
       } else {
         break;
       }
       uint32_t olen = static_cast<uint32_t>(out.size());
       if (!send_all(fd, &status, 4) || !send_all(fd, &olen, 4) || (olen && !send_all(fd, out.data(), olen))) break;
     }
-    ::close(fd);
   }
 
   int listen_fd_ = -1;
@@ -230,7 +258,7 @@ extern "C" int b200dp_store_create(const char* master_ip, int port, int rank, in
   if (rank == 0) {
     s->server = new StoreServer();
     std::string err;
-    if (!s->server->start(port, &err)) {
+    if (!s->server->start(master_ip, port, &err)) {
       set_error("store_create: rank 0 cannot host the store on port %d: %s", port, err.c_str());
       delete s->server;
       delete s;
@@ -321,11 +349,30 @@ extern "C" int b200dp_store_add(void* h, const char* key, long long delta, long 
   return 0;
 }
 
-// All ranks call this the same number of times with the same name.
+extern "C" int b200dp_store_delete_prefix(void* h, const char* prefix) {
+  auto* s = static_cast<Store*>(h);
+  uint32_t status;
+  std::string out;
+  if (!prefix || !prefix[0] || !s->request(OP_DEL, prefix, nullptr, 0, &status, &out)) {
+    set_error("store_delete_prefix(%s): connection to the store lost", prefix ? prefix : "(null)");
+    return B200DP_ETIMEDOUT;
+  }
+  return 0;
+}
+
+extern "C" int b200dp_store_timeout_ms(void* h) {
+  auto* s = static_cast<Store*>(h);
+  return s ? s->timeout_ms : 0;
+}
+
+// All ranks call this the same number of times (the names need not match: rounds are numbered).
 extern "C" int b200dp_store_barrier(void* h, const char* name) {
   auto* s = static_cast<Store*>(h);
   const int64_t round = s->barrier_round++;
-  const std::string base = std::string("barrier/") + name + "/" + std::to_string(round);
+  (void)name;  // the round number alone identifies the barrier, so ranks on different code paths cannot pair up wrongly
+  const std::string base = std::string("barrier/") + std::to_string(round);
+  // everybody passed round - 2 before anyone could arrive here, so its keys are dead: rank 0 sweeps them
+  if (s->rank == 0 && round >= 2) b200dp_store_delete_prefix(h, ("barrier/" + std::to_string(round - 2) + "/").c_str());
   long long arrived = 0;
   int rc = b200dp_store_add(h, (base + "/count").c_str(), 1, &arrived);
   if (rc) return rc;

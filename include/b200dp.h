@@ -256,6 +256,10 @@ int b200dp_store_set(void* store, const char* key, const void* data, int len);
 int b200dp_store_get(void* store, const char* key, void* buf, int cap, int* out_len);
 int b200dp_store_add(void* store, const char* key, long long delta, long long* result);
 int b200dp_store_barrier(void* store, const char* name);
+/* Erase every key that starts with `prefix` (finished barrier rounds, host-side reductions). */
+int b200dp_store_delete_prefix(void* store, const char* prefix);
+/* The timeout given to b200dp_store_create, in milliseconds. */
+int b200dp_store_timeout_ms(void* store);
 int b200dp_store_destroy(void* store);
 
 /* ------------------------------------------------------------------------

@@ -153,3 +153,33 @@ def test_config_defaults_are_reference_literals_and_validated():
     assert not TrainConfig(mode="part3", num_nodes=1, rank=0).use_nvls
     assert not TrainConfig(mode="part3", num_nodes=8, rank=0, nvls=False).use_nvls
     assert not TrainConfig(mode="part1", nvls=True).use_nvls
+
+
+def test_real_data_request_without_the_files_is_an_error(tmp_path):
+    """A silent fall-back to synthetic images would print CIFAR-looking numbers that are not CIFAR results."""
+    import pytest
+    from cs744_pytorch_distributed_tutorial_b200.config import TrainConfig
+    from cs744_pytorch_distributed_tutorial_b200.data import build_dataset
+    cfg = TrainConfig(synthetic=False, data_root=str(tmp_path))
+    with pytest.raises(FileNotFoundError, match="cifar-10-batches-py"):
+        build_dataset(cfg, True)
+
+
+def test_batch_pipeline_waits_for_the_copy_of_a_slot_before_refilling_it():
+    """The ring of pinned buffers is only safe with a hand-shake: the event behind a batch's host->device copy
+    must complete before its buffer is overwritten (the engine passes it through ``consumed``)."""
+    ds = SyntheticCIFAR10(64, True, seed=1)
+    bp = BatchPipeline(ds, batch=8, train=True, augment=False, pin=False, ring=2)
+    log = []
+
+    class Ev:
+        def __init__(self, i):
+            self.i = i
+
+        def synchronize(self):
+            log.append(self.i)
+
+    for i, _ in enumerate(bp):
+        bp.consumed(Ev(i))
+    # 8 batches through 2 slots: batch i+2 reuses batch i's buffer and must have waited for event i first
+    assert log == list(range(6))

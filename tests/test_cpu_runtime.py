@@ -62,6 +62,35 @@ def test_store_get_times_out_with_a_message_naming_the_key():
     s.close()
 
 
+def test_store_survives_a_bogus_request_and_sweeps_finished_barriers():
+    """The store port is reachable by anything that can reach the host: a request that claims a 3 GiB key must
+    cost the server nothing but that connection, and finished barrier rounds must not pile up in the map."""
+    import socket
+    import struct
+    from cs744_pytorch_distributed_tutorial_b200.ops._lib import NativeError
+    from cs744_pytorch_distributed_tutorial_b200.parallel import comm as C
+    port = free_port()
+    s = C.Store("127.0.0.1", port, 0, 1, timeout_s=0.5)
+    bogus = socket.create_connection(("127.0.0.1", port))
+    bogus.sendall(struct.pack("<BI", 1, 3 << 30))
+    bogus.settimeout(5)
+    assert bogus.recv(16) == b""            # dropped, nothing allocated
+    bogus.close()
+    s.set("still/alive", b"yes")
+    assert s.get("still/alive") == b"yes"
+    for _ in range(6):
+        s.barrier("x")
+    with pytest.raises(NativeError):        # round 0's keys were erased when round 2 started
+        s.get("barrier/0/go")
+    s.set("red/1/0", b"a")
+    s.set("red/10/0", b"b")
+    s.delete_prefix("red/1/")
+    assert s.get("red/10/0") == b"b"
+    with pytest.raises(NativeError):
+        s.get("red/1/0")
+    s.close()
+
+
 def test_checkpoint_roundtrip_and_reference_compat(tmp_path):
     from cs744_pytorch_distributed_tutorial_b200.checkpoint import load_checkpoint, save_checkpoint
     from cs744_pytorch_distributed_tutorial_b200.models.vgg import VGG11

@@ -28,6 +28,7 @@ import torch.optim as optim
 
 from .config import TrainConfig
 from .models.vgg import VGG
+from .ops import native as K
 from .utils.metrics import PhaseTimer, StepClock, emit_json, nvtx_range
 
 
@@ -190,15 +191,18 @@ class NativeBackend:
                 self.comm = Communicator(self.store, cfg.rank, W, device.index or 0, heap_bytes, timeout_s=cfg.timeout_s)
             heap = self.comm
         self.native = model.enable_native(max_batch=B, heap=heap)
-        from .models.native_vgg import HEAD_FUSED
-        self.native.defer_head = HEAD_FUSED   # this backend always calls loss_fwd_bwd() after a training forward
+        # this backend always calls loss_fwd_bwd() after a training forward, so the classifier forward, the loss
+        # and the classifier backward run as ONE launch (head_fwd_bwd) instead of three plus two memset nodes
+        self.native.defer_head = True
         self.sync = make_native_sync(cfg.mode, self.native, self.comm, cfg)
         self.sync.on_init()
         # static step inputs / outputs
         self.x = torch.zeros(B, 3, 32, 32, device=device)
-        self.y = torch.zeros(B, dtype=torch.int64, device=device)
+        Bp = (B + 1) // 2 * 2                    # label buffers padded to a multiple of 16 bytes (copy_pair)
+        self._y_full = torch.zeros(Bp, dtype=torch.int64, device=device)
+        self.y = self._y_full[:B]
         self._stage_x = [torch.zeros_like(self.x) for _ in range(2)]
-        self._stage_y = [torch.zeros_like(self.y) for _ in range(2)]
+        self._stage_y = [torch.zeros_like(self._y_full) for _ in range(2)]
         self._copy_stream = torch.cuda.Stream(device)
         self._copy_done = [torch.cuda.Event() for _ in range(2)]
         self._slot_free = [torch.cuda.Event() for _ in range(2)]
@@ -273,8 +277,7 @@ class NativeBackend:
         self._eval_synced = False
         cur = torch.cuda.current_stream()
         cur.wait_event(self._copy_done[slot])
-        self.x.copy_(self._stage_x[slot], non_blocking=True)
-        self.y.copy_(self._stage_y[slot], non_blocking=True)
+        K.copy_pair(self.x, self._stage_x[slot], self._y_full, self._stage_y[slot])
         self._slot_free[slot].record(cur)
         if self.graph is not None:
             self.graph.replay()

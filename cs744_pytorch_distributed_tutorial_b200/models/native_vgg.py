@@ -32,23 +32,6 @@ from ..ops import native as K
 # weight gradients on a second stream, concurrently with the dgrad / BatchNorm-backward chain
 WGRAD_ON_SIDE_STREAM = os.environ.get("B200DP_WGRAD_STREAM", "1") != "0"
 
-# clear flat_grads on the weight-gradient stream during the forward pass instead of at the head of
-# backward; measured neutral at batch 256 (0.7435 vs 0.7422 ms), so off unless asked for
-ZERO_GRADS_EARLY = os.environ.get("B200DP_ZERO_GRADS_EARLY", "0") != "0"
-# experimental (not yet run on hardware): instead of one 36.9 MB fill at the head of backward (7 us on the
-# critical path), clear each conv layer's weight-gradient range on the weight-gradient stream right before
-# its wgrad kernel.  Everything else in the buffer is either overwritten every step (BatchNorm, classifier)
-# or never written (conv biases: exactly zero in front of a training-mode BatchNorm).
-ZERO_PER_LAYER = os.environ.get("B200DP_ZERO_PER_LAYER", "0") != "0"
-
-# experimental (not yet validated on hardware): the dgrad epilogue of block i also accumulates the
-# BatchNorm-backward sums of block i-1, which then skips its reduction launch
-DGRAD_BN_REDUCE = os.environ.get("B200DP_DGRAD_BN_REDUCE", "0") != "0"
-
-# experimental (not yet validated on hardware): linear_fwd + cross_entropy + linear_bwd as one launch in
-# the engine's training step (NativeVGG.defer_head)
-HEAD_FUSED = os.environ.get("B200DP_HEAD_FUSED", "0") != "0"
-
 ALIGN = 4  # floats; every tensor starts on a 16-byte boundary inside the flat buffers
 
 
@@ -156,26 +139,13 @@ class _Block:
     pass
 
 
-def self_first_is_64(module: nn.Module) -> bool:
-    return module.block_specs()[0].cout == 64
-
-
 _TUNE_CACHE: Dict[tuple, object] = {}   # (kind, B, hw, cin, cout, taps) -> best tile config, per process
 
 
-# experimental (not yet validated on hardware): offer the persistent conv kernel (cta_pair code 2) to the tuner.
-# "1": forward convs only -- a persistent dgrad holds ~200 KB of shared memory on every SM, which would push
-# the concurrent weight-gradient kernels off the SMs (the tuner times kernels in isolation and cannot see
-# that); "2": dgrad as well.
-PERSIST_CANDIDATES = int(os.environ.get("B200DP_PERSIST", "0") or 0)
-
-
-def _igemm_candidates(m_tiles: int, n_total: int, total_kb: int, persist: bool = False):
+def _igemm_candidates(m_tiles: int, n_total: int, total_kb: int):
     """(block_n, split_k, cta_pair) triples worth timing: every N tile, K splits while the grid is
     small, and the tcgen05 cta_group::2 kernel wherever the tile count allows pairing."""
     out = []
-    if persist:
-        out += [(bn, 1, 2) for bn in (64, 128, 256) if n_total % bn == 0 and m_tiles * (n_total // bn) > 148]
     for bn in (32, 64, 128, 256):
         if n_total % bn:
             continue
@@ -217,7 +187,7 @@ _ACT_DTYPE = torch.bfloat16   # activations / operand copies; the CPU emulation 
 
 class NativeVGG:
     def __init__(self, module: nn.Module, max_batch: int, heap=None, conv_stats_fused: bool = True,
-                 autotune: bool = True, direct_first_layer: bool = False):
+                 autotune: bool = True):
         dev = next(module.parameters()).device
         if dev.type != "cuda" and not _DRY_RUN:
             raise RuntimeError("NativeVGG needs the module on a CUDA device")
@@ -232,10 +202,6 @@ class NativeVGG:
         self.defer_head = False       # set by the engine when every training forward is followed by loss_fwd_bwd
         self._head_pending = False
         self._head_done = False
-        self._head_pending_clear = False
-        # layer 0 (3 input channels): optional direct CUDA-core conv instead of patch gather + K=64
-        # tcgen05 GEMM.  Measured slower on B200 at B=256 (LDS-bound: 122 us vs 33 + 44 us), so off.
-        self.direct_first_layer = direct_first_layer and self_first_is_64(module)
         self.specs = module.block_specs()
         self.layout = FlatLayout(list(module.named_parameters()))
         alloc = (lambda n, dt=torch.float32: heap.zeros(n, dt)) if heap is not None else \
@@ -261,7 +227,6 @@ class NativeVGG:
         self._wgrad_fork = [torch.cuda.Event() for _ in self.specs]
         self._wgrad_join = torch.cuda.Event()
         self._dgrad_done = [torch.cuda.Event() for _ in self.specs]
-        self._zero_fork, self._zero_done = torch.cuda.Event(), torch.cuda.Event()
         self._block_prep = None
         self._adopt_parameters()
         self._alloc_workspaces()
@@ -340,7 +305,7 @@ class NativeVGG:
             b.taps = 1 if b.first else 9
             hw = s.hw
             if b.first:
-                b.x_in = None if self.direct_first_layer else torch.zeros(B, hw, hw, b.kin, device=dev, dtype=bf)
+                b.x_in = torch.zeros(B, hw, hw, b.kin, device=dev, dtype=bf)
             else:
                 b.x_in = self.blocks[-1].out
             b.y = torch.empty(B, hw, hw, s.cout, device=dev, dtype=bf)
@@ -354,7 +319,6 @@ class NativeVGG:
             b.mean = torch.empty(s.cout, device=dev)
             b.invstd = torch.empty(s.cout, device=dev)
             kpad = b.taps * b.kin
-            b.direct = b.first and self.direct_first_layer
             b.wf = torch.empty(s.cout, kpad, device=dev, dtype=bf)
             b.wd = None if b.first else torch.empty(s.cin, 9 * s.cout, device=dev, dtype=bf)
             ew, eb = L.by_name[f"layers.{s.conv_idx}.weight"], L.by_name[f"layers.{s.conv_idx}.bias"]
@@ -404,8 +368,6 @@ class NativeVGG:
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):
             for i, b in enumerate(self.blocks):
-                if b.direct:
-                    continue
                 s = b.spec
                 x_in, y, dy = b.x_in[:B], b.y[:B], b.dy[:B]
                 key = (B, s.hw, b.kin, s.cout, b.taps)
@@ -414,7 +376,7 @@ class NativeVGG:
                     t = {c: _time_captured(lambda c=c: K.conv_igemm(x_in, b.wf, b.bias, y, stats=b.stats, taps=b.taps,
                                                                     block_n=c[0], split_k=c[1], cta_pair=c[2],
                                                                     workspace=self.splitk_ws))
-                         for c in _igemm_candidates(m_tiles, s.cout, b.taps * b.kin // 64, PERSIST_CANDIDATES >= 1)}
+                         for c in _igemm_candidates(m_tiles, s.cout, b.taps * b.kin // 64)}
                     _TUNE_CACHE[("fwd",) + key] = min(t, key=t.get)
                 b.fwd_block_n, b.fwd_split_k, b.fwd_pair = _TUNE_CACHE[("fwd",) + key]
                 if ("wgrad",) + key not in _TUNE_CACHE:
@@ -431,7 +393,7 @@ class NativeVGG:
                         t = {c: _time_captured(lambda c=c: K.conv_igemm(dy, b.wd, None, dprev, block_n=c[0],
                                                                         split_k=c[1], cta_pair=c[2],
                                                                         workspace=self.splitk_ws))
-                             for c in _igemm_candidates(m_tiles, s.cin, 9 * s.cout // 64, PERSIST_CANDIDATES >= 2)}
+                             for c in _igemm_candidates(m_tiles, s.cin, 9 * s.cout // 64)}
                         _TUNE_CACHE[("dgrad",) + key] = min(t, key=t.get)
                     b.dgrad_block_n, b.dgrad_split_k, b.dgrad_pair = _TUNE_CACHE[("dgrad",) + key]
         torch.cuda.current_stream().wait_stream(side)
@@ -444,19 +406,17 @@ class NativeVGG:
         """bf16 operand copies of the fp32 master weights: Wf (forward) and Wd (dgrad)."""
         if getattr(self, "_prep", None) is None:
             self._prep = K.BatchedWeightPrep([(b.w_master, b.wf, b.wd, b.spec.cout, b.spec.cin, 9, b.taps * b.kin)
-                                              for b in self.blocks if not b.direct])
+                                              for b in self.blocks])
         self._prep()
 
     def prep_block(self, i: int) -> None:
         """Refresh the bf16 weight copies of block ``i`` on the current stream, after the data gradient
         of that block (the last reader of the old copies in this step) has finished."""
         if self._block_prep is None:
-            self._block_prep = [None if b.direct else
-                                K.BatchedWeightPrep([(b.w_master, b.wf, b.wd, b.spec.cout, b.spec.cin, 9, b.taps * b.kin)])
+            self._block_prep = [K.BatchedWeightPrep([(b.w_master, b.wf, b.wd, b.spec.cout, b.spec.cin, 9, b.taps * b.kin)])
                                 for b in self.blocks]
         torch.cuda.current_stream().wait_event(self._dgrad_done[i])
-        if self._block_prep[i] is not None:
-            self._block_prep[i]()
+        self._block_prep[i]()
 
     def blocks_of_bucket(self, k: int) -> List[int]:
         return [i for i, ks in self._bucket_of_block.items() if k in ks]
@@ -469,30 +429,17 @@ class NativeVGG:
             raise ValueError(f"batch {B} exceeds the executor's max_batch {self.max_batch}")
         self._B = B
         if training:
-            self.zero_region.zero_()
-            if WGRAD_ON_SIDE_STREAM and ZERO_GRADS_EARLY:
-                # clear the gradient buffer on the weight-gradient stream while the forward pass runs
-                main = torch.cuda.current_stream()
-                self._zero_fork.record(main)
-                self._wgrad_stream.wait_event(self._zero_fork)
-                with torch.cuda.stream(self._wgrad_stream):
-                    self.flat_grads.zero_()
-                    self._zero_done.record(self._wgrad_stream)
-                self._grads_cleared = True
+            K.fill_zero(self.zero_region)
         for b in self.blocks:
             s = b.spec
             y = b.y[:B]
             fused = training and self.conv_stats_fused
-            if b.direct:
-                self._x_first = x if x.is_contiguous() else x.contiguous()
-                K.conv3x3_c3_fwd(self._x_first, b.w_master, b.bias, y, stats=b.stats if fused else None)
-            else:
-                x_in = b.x_in[:B]
-                if b.first:
-                    K.im2col3x3_c3(x.contiguous(), x_in)
-                K.conv_igemm(x_in, b.wf, b.bias, y, stats=b.stats if fused else None, taps=b.taps,
-                             block_n=b.fwd_block_n, split_k=b.fwd_split_k, cta_pair=b.fwd_pair,
-                             workspace=self.splitk_ws)
+            x_in = b.x_in[:B]
+            if b.first:
+                K.im2col3x3_c3(x.contiguous(), x_in)
+            K.conv_igemm(x_in, b.wf, b.bias, y, stats=b.stats if fused else None, taps=b.taps,
+                         block_n=b.fwd_block_n, split_k=b.fwd_split_k, cta_pair=b.fwd_pair,
+                         workspace=self.splitk_ws)
             if training and not fused:
                 K.bn_stats(y, b.stats)
             K.bn_relu_pool_fwd(y, b.stats, b.gamma, b.beta, b.running_mean, b.running_var, b.nbt, b.mean, b.invstd,
@@ -512,9 +459,7 @@ class NativeVGG:
             self._head_pending = False
             last = self.blocks[-1]
             if need_grad:
-                self._head_pending_clear = True
                 self._clear_grads()
-                self._head_pending_clear = False
                 K.head_fwd_bwd(last.out[:B], self.fc_w, self.fc_b, target, self.logits[:B], self.loss, self.correct,
                                self.dlogits[:B], last.dout[:B], self.g_fc_w, self.g_fc_b, grad_scale)
                 self._head_done = True
@@ -525,18 +470,8 @@ class NativeVGG:
         return self.loss
 
     def _clear_grads(self) -> None:
-        if ZERO_PER_LAYER and WGRAD_ON_SIDE_STREAM:
-            # conv weights are cleared per layer in backward(); the fused head accumulates onto the classifier's
-            # gradient, so that small range is cleared here (linear_bwd clears it itself)
-            if self._head_pending_clear:
-                self.g_fc_w.zero_()
-                self.g_fc_b.zero_()
-            return
-        if getattr(self, "_grads_cleared", False):
-            torch.cuda.current_stream().wait_event(self._zero_done)   # cleared during forward on the wgrad stream
-            self._grads_cleared = False
-        else:
-            self.flat_grads.zero_()  # split-K weight gradients are accumulated with red.global.add
+        # split-K weight gradients are accumulated with red.global.add; the conv biases rely on this zero too
+        K.fill_zero(self.flat_grads)
 
     # ------------------------------------------------------------------ backward
     def backward(self, dlogits: Optional[torch.Tensor] = None) -> None:
@@ -569,24 +504,19 @@ class NativeVGG:
             # the tensor pipe ~40% busy on its own).  The bucket-ready signal is recorded on that stream.
             if side is not None:
                 self._wgrad_fork[i].record(main)
-            if i > 0 and DGRAD_BN_REDUCE and b.dgrad_pair != 2:   # (the persistent kernel has no bn-reduce flavour)
+            if i > 0:
+                # the dgrad epilogue also accumulates the BatchNorm-backward sums of the block below,
+                # which then skips its own reduction pass
                 prev = self.blocks[i - 1]
                 K.conv_dgrad_bn_reduce(b.dy[:B], b.wd, prev.dout[:B], prev.out[:B], prev.gamma, prev.beta, prev.sums,
                                        block_n=b.dgrad_block_n, split_k=b.dgrad_split_k, cta_pair=b.dgrad_pair,
                                        workspace=self.splitk_ws)
                 reduced = True
-            elif i > 0:
-                K.conv_igemm(b.dy[:B], b.wd, None, self.blocks[i - 1].dout[:B], block_n=b.dgrad_block_n,
-                             split_k=b.dgrad_split_k, cta_pair=b.dgrad_pair, workspace=self.splitk_ws)
             self._dgrad_done[i].record(main)   # after this the layer's bf16 weight copies may be rewritten
             if side is not None:
                 side.wait_event(self._wgrad_fork[i])
             with torch.cuda.stream(side) if side is not None else contextlib.nullcontext():
-                if ZERO_PER_LAYER and side is not None:
-                    b.g_w.zero_()       # split-K partial tiles are accumulated with red.global.add
-                if b.direct:
-                    K.conv3x3_c3_wgrad(b.dy[:B], self._x_first, b.g_w)
-                elif self.wgrad_push is not None and i in self.wgrad_push:
+                if self.wgrad_push is not None and i in self.wgrad_push:
                     # experimental: GEMM + transfer half of the reduce-scatter in one kernel
                     K.conv_wgrad_push(b.dy[:B], b.x_in[:B], b.g_w, split_k=b.wgrad_split_k, block_n=b.wgrad_block_n,
                                       **self.wgrad_push[i])

@@ -25,14 +25,11 @@ _PROTOTYPES = {
     "b200dp_conv_igemm": [P, P, P, P, P, I, I, I, I, I, I, I, P],
     "b200dp_conv_igemm_splitk": [P, P, P, P, P, P, I, I, I, I, I, I, I, I, P],
     "b200dp_conv_igemm_pair": [P, P, P, P, P, P, I, I, I, I, I, I, I, I, P],
-    "b200dp_conv_igemm_persist": [P, P, P, P, P, I, I, I, I, I, I, I, P],
     "b200dp_conv_dgrad_bn_reduce": [P, P, P, P, P, P, P, P, I, I, I, I, I, I, I, I, I, P],
     "b200dp_conv_wgrad": [P, P, P, I, I, I, I, I, I, I, I, I, P],
     "b200dp_conv_wgrad_tiled": [P, P, P, I, I, I, I, I, I, I, I, I, I, P],
     "b200dp_conv_wgrad_push": [P, P, P, I, I, I, I, I, I, I, I, P, I, I, I, P, LL, LL, LL, LL, P],
     "b200dp_im2col3x3_c3": [P, P, I, I, I, P],
-    "b200dp_conv3x3_c3_fwd": [P, P, P, P, P, I, I, I, P],
-    "b200dp_conv3x3_c3_wgrad": [P, P, P, I, I, I, P],
     "b200dp_bn_stats": [P, P, LL, I, P],
     "b200dp_bn_relu_pool_fwd": [P, P, P, P, P, P, P, P, P, P, I, I, I, I, I, I, F, F, P],
     "b200dp_bn_relu_pool_bwd_reduce": [P, P, P, P, P, P, P, I, I, I, I, I, P],
@@ -42,12 +39,13 @@ _PROTOTYPES = {
     "b200dp_bn_bwd_reduce_from_out_tma": [P, P, P, P, P, LL, I, P],
     "b200dp_bn_bwd_apply_pool_tma": [P, P, P, P, P, P, P, P, P, P, I, I, I, I, P],
     "b200dp_bn_relu_pool_bwd_reduce_from_out": [P, P, P, P, P, LL, I, P],
-    "b200dp_bn_relu_pool_bwd_fused": [P, P, P, P, P, P, P, P, P, P, I, I, I, I, I, P],
     "b200dp_linear_fwd": [P, P, P, P, I, I, I, P],
     "b200dp_cross_entropy": [P, P, P, P, P, I, I, F, P],
     "b200dp_linear_bwd": [P, P, P, P, P, P, I, I, I, P],
     "b200dp_head_fwd_bwd": [P, P, P, P, P, P, P, P, P, P, P, I, I, I, F, P],
     "b200dp_sgd_momentum": [P, P, P, LL, F, F, F, F, P],
+    "b200dp_fill_zero": [P, LL, P],
+    "b200dp_copy_pair": [P, P, LL, P, P, LL, P],
     "b200dp_prep_conv_weights": [P, P, P, I, I, I, I, P],
     "b200dp_prep_conv_weights_batched": [I, P, P, P, P, P, P, P, P],
 }

@@ -13,15 +13,6 @@ import torch
 from . import _lib
 from ._lib import call, ptr, stream_ptr
 
-import os
-
-# one cooperative launch (grid barrier) vs reduce + apply; measured on B200: the two-pass form with a
-# full 444-block wave is ~3% faster per step than the co-residency-capped cooperative grid, so off.
-BN_BWD_FUSED = os.environ.get("B200DP_BN_BWD_FUSED", "0") != "0"
-# tensors of at most this many elements take the one-launch cooperative kernel even when the flag
-# above is off: on the 2x2 / 4x4 layers both passes are launch-latency bound (0 = never)
-BN_BWD_FUSED_MAX_ELEMS = int(os.environ.get("B200DP_BN_BWD_FUSED_MAX", "0"))
-BN_REDUCE_FROM_OUT = os.environ.get("B200DP_BN_REDUCE_FROM_OUT", "1") != "0"
 BN_EPS = 1e-5
 BN_MOMENTUM = 0.1
 
@@ -47,12 +38,6 @@ def conv_igemm(act: torch.Tensor, wgt: torch.Tensor, bias: Optional[torch.Tensor
     Cout = wgt.shape[0]
     assert wgt.shape[1] == taps * Cin, (wgt.shape, taps, Cin)
     assert out.shape == (B, H, W, Cout)
-    if cta_pair == 2:
-        # experimental persistent kernel (one CTA per SM, double-buffered TMEM accumulator); no split-K
-        assert split_k == 1
-        call("b200dp_conv_igemm_persist", ptr(act), ptr(wgt), ptr(bias), ptr(out), ptr(stats), B, H, W, Cin, Cout,
-             taps, block_n, stream_ptr())
-        return out
     if cta_pair:
         # tcgen05 cta_group::2: a 256 x block_n tile per pair of SMs, each staging half of the weight tile
         if split_k > 1:
@@ -138,27 +123,6 @@ def im2col3x3_c3(x_nchw: torch.Tensor, a0: torch.Tensor) -> torch.Tensor:
     return a0
 
 
-def conv3x3_c3_fwd(x_nchw: torch.Tensor, w: torch.Tensor, bias: torch.Tensor, y: torch.Tensor,
-                   stats: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """First layer as a direct conv: x fp32 NCHW [B,3,H,W], w fp32 [64, 27] (KRSC), y bf16 NHWC [B,H,W,64]."""
-    _chk(x_nchw, torch.float32, "x")
-    _chk(y, torch.bfloat16, "y")
-    B, C, H, W = x_nchw.shape
-    assert C == 3 and w.numel() == 64 * 27 and y.shape == (B, H, W, 64)
-    call("b200dp_conv3x3_c3_fwd", ptr(x_nchw), ptr(w), ptr(bias), ptr(y), ptr(stats), B, H, W, stream_ptr())
-    return y
-
-
-def conv3x3_c3_wgrad(dy: torch.Tensor, x_nchw: torch.Tensor, dw: torch.Tensor) -> torch.Tensor:
-    """dw[64, 27] += sum_p dy[p] (x) patch(x)[p]; ``dw`` must be zeroed by the caller."""
-    _chk(dy, torch.bfloat16, "dy")
-    _chk(x_nchw, torch.float32, "x")
-    B, C, H, W = x_nchw.shape
-    assert C == 3 and dw.numel() == 64 * 27 and dy.shape == (B, H, W, 64)
-    call("b200dp_conv3x3_c3_wgrad", ptr(dy), ptr(x_nchw), ptr(dw), B, H, W, stream_ptr())
-    return dw
-
-
 def bn_stats(y: torch.Tensor, stats: torch.Tensor) -> torch.Tensor:
     _chk(y, torch.bfloat16, "y")
     _chk(stats, torch.float32, "stats")
@@ -176,27 +140,20 @@ def bn_relu_pool_fwd(y, stats, gamma, beta, running_mean, running_var, num_batch
     return out
 
 
-def bn_relu_pool_bwd(y, dout, mean, invstd, gamma, beta, sums, dy, dgamma, dbeta, pool: bool, fused: Optional[bool] = None,
+def bn_relu_pool_bwd(y, dout, mean, invstd, gamma, beta, sums, dy, dgamma, dbeta, pool: bool,
                      out: Optional[torch.Tensor] = None, skip_reduce: bool = False):
-    """Per-channel reduction into ``sums`` (must be zero), then the dY pass -- in one cooperative
-    launch with a grid-wide barrier (``fused``) or as two launches.  ``skip_reduce``: ``sums`` already
-    holds the reduction (``conv_dgrad_bn_reduce`` of the block above produced it), only apply."""
+    """Per-channel reduction into ``sums`` (must be zero), then the dY pass.  With ``out`` (the block's stored
+    output) the reduction reads it instead of the full-resolution conv output: 2.5x fewer bytes on pooled
+    layers and no arg-max search.  ``skip_reduce``: ``sums`` already holds the reduction
+    (``conv_dgrad_bn_reduce`` of the block above produced it), only apply."""
     B, H, W, C = y.shape
-    if skip_reduce:
-        call("b200dp_bn_relu_pool_bwd_apply", ptr(y), ptr(dout), ptr(mean), ptr(invstd), ptr(gamma), ptr(beta),
-             ptr(sums), ptr(dy), ptr(dgamma), ptr(dbeta), B, H, W, C, int(pool), stream_ptr())
-        return dy
-    if (BN_BWD_FUSED or y.numel() <= BN_BWD_FUSED_MAX_ELEMS) if fused is None else fused:
-        call("b200dp_bn_relu_pool_bwd_fused", ptr(y), ptr(dout), ptr(mean), ptr(invstd), ptr(gamma), ptr(beta),
-             ptr(sums), ptr(dy), ptr(dgamma), ptr(dbeta), B, H, W, C, int(pool), stream_ptr())
-        return dy
-    if out is not None and BN_REDUCE_FROM_OUT:
-        # reduction from the stored block output: 2.5x fewer bytes on pooled layers, no arg-max search
-        call("b200dp_bn_relu_pool_bwd_reduce_from_out", ptr(out), ptr(dout), ptr(gamma), ptr(beta), ptr(sums),
-             dout.numel() // C, C, stream_ptr())
-    else:
-        call("b200dp_bn_relu_pool_bwd_reduce", ptr(y), ptr(dout), ptr(mean), ptr(invstd), ptr(gamma), ptr(beta),
-             ptr(sums), B, H, W, C, int(pool), stream_ptr())
+    if not skip_reduce:
+        if out is not None:
+            call("b200dp_bn_relu_pool_bwd_reduce_from_out", ptr(out), ptr(dout), ptr(gamma), ptr(beta), ptr(sums),
+                 dout.numel() // C, C, stream_ptr())
+        else:
+            call("b200dp_bn_relu_pool_bwd_reduce", ptr(y), ptr(dout), ptr(mean), ptr(invstd), ptr(gamma), ptr(beta),
+                 ptr(sums), B, H, W, C, int(pool), stream_ptr())
     call("b200dp_bn_relu_pool_bwd_apply", ptr(y), ptr(dout), ptr(mean), ptr(invstd), ptr(gamma), ptr(beta),
          ptr(sums), ptr(dy), ptr(dgamma), ptr(dbeta), B, H, W, C, int(pool), stream_ptr())
     return dy
@@ -234,6 +191,19 @@ def sgd_momentum(p, g, buf, lr: float, momentum: float, wd: float, grad_scale: f
     """Fused SGD on flat fp32 buffers (ref: master/part1/part1.py:38,98-99)."""
     assert p.numel() == g.numel() == buf.numel()
     call("b200dp_sgd_momentum", ptr(p), ptr(g), ptr(buf), p.numel(), lr, momentum, wd, grad_scale, stream_ptr())
+
+
+def fill_zero(t: torch.Tensor) -> torch.Tensor:
+    """Clear a contiguous tensor whose byte size is a multiple of 16 (flat buffers are padded to that)."""
+    call("b200dp_fill_zero", ptr(t), t.numel() * t.element_size(), stream_ptr())
+    return t
+
+
+def copy_pair(dst0: torch.Tensor, src0: torch.Tensor, dst1: torch.Tensor, src1: torch.Tensor) -> None:
+    """``dst0 <- src0`` and ``dst1 <- src1`` (device to device, contiguous, multiples of 16 bytes) in one launch."""
+    n0, n1 = src0.numel() * src0.element_size(), src1.numel() * src1.element_size()
+    assert dst0.numel() * dst0.element_size() >= n0 and dst1.numel() * dst1.element_size() >= n1
+    call("b200dp_copy_pair", ptr(dst0), ptr(src0), n0, ptr(dst1), ptr(src1), n1, stream_ptr())
 
 
 def prep_conv_weights(master, wf, wd, Cout: int, Cin: int, taps: int, kpad: int):

@@ -76,37 +76,37 @@ class NativeSync:
 
 
 class LocalSGD(NativeSync):
-    """One rank.  The optimizer runs in two phases: as soon as the gradients of the last ``split``
-    conv layers exist (95 % of all parameters live there and they are ready after about half of
-    backward) one fused SGD kernel updates that range and one kernel refreshes their bf16 copies on
-    the weight-gradient stream, in the shadow of the remaining backward; the small remainder follows
-    after backward.  ``B200DP_LOCAL_OVERLAP``: ``2`` (default) two-phase, ``1`` per-bucket (measured
-    slower: sixteen more launches competing with backward), ``0`` one kernel after backward."""
+    """One rank.  The optimizer runs in two phases: as soon as the gradients of the last ``split`` conv layers
+    exist (95 % of all parameters live there and they are ready after about half of backward) one fused SGD
+    kernel updates that range and one kernel refreshes their bf16 copies, in the shadow of the remaining
+    backward; the small remainder follows after backward.  Phase 1 runs on its own stream, forked from the
+    weight-gradient stream: queued on that stream it kept the weight gradients of the first three layers --
+    the tail of the step -- waiting behind the optimizer traffic (in-graph timeline, profiles/round2).
+    ``overlap=False``: one kernel after backward."""
 
     name = "none"
 
-    def __init__(self, *a, overlap: Optional[int] = None, **kw):
+    def __init__(self, *a, overlap: bool = True, **kw):
         super().__init__(*a, **kw)
-        import os
         from ..models.native_vgg import WGRAD_ON_SIDE_STREAM
-        mode = int(os.environ.get("B200DP_LOCAL_OVERLAP", "2")) if overlap is None else int(overlap)
-        self.overlap = mode if WGRAD_ON_SIDE_STREAM else 0
+        self.overlap = bool(overlap) and WGRAD_ON_SIDE_STREAM
         nv = self.native
         if self.overlap:
             self.buckets = nv.layout.buckets("layer")
             nv.set_bucket_plan(self.buckets)
             nv.on_bucket_ready = self._bucket_ready
             self.handles_shadows = True
-        if self.overlap == 2:
             # phase 1 covers the buckets of the deepest blocks down to (and including) `first_block`
             n = len(nv.blocks)
             self.first_block = max(n - 5, 1)            # VGG-11: blocks 3..7 = 35.3 of 36.9 MB
             self.split_bucket = max(k for k in range(len(self.buckets)) if self.first_block in nv.blocks_of_bucket(k))
             self.split_end = self.buckets[self.split_bucket].end
-            self._prep_hi = K.BatchedWeightPrep([(b.w_master, b.wf, b.wd, b.spec.cout, b.spec.cin, 9, b.taps * b.kin)
-                                                 for b in nv.blocks[self.first_block:] if not b.direct])
-            self._prep_lo = K.BatchedWeightPrep([(b.w_master, b.wf, b.wd, b.spec.cout, b.spec.cin, 9, b.taps * b.kin)
-                                                 for b in nv.blocks[:self.first_block] if not b.direct])
+            spec = lambda b: (b.w_master, b.wf, b.wd, b.spec.cout, b.spec.cin, 9, b.taps * b.kin)
+            self._prep_hi = K.BatchedWeightPrep([spec(b) for b in nv.blocks[self.first_block:]])
+            self._prep_lo = K.BatchedWeightPrep([spec(b) for b in nv.blocks[:self.first_block]])
+            self._opt_stream = torch.cuda.Stream(nv.device)
+            self._opt_fork, self._opt_join = torch.cuda.Event(), torch.cuda.Event()
+            self._opt_pending = False
 
     def _sgd_range(self, lo: int, hi: int) -> None:
         nv = self.native
@@ -114,27 +114,32 @@ class LocalSGD(NativeSync):
                        self.weight_decay)
 
     def _bucket_ready(self, k: int) -> None:
+        if k != self.split_bucket:
+            return
+        # called on the weight-gradient stream right after wgrad(first_block): every gradient of phase 1 exists.
+        # The data gradient of first_block is the last reader of the old bf16 copies of blocks >= first_block.
         nv = self.native
-        if self.overlap == 1:
-            self._sgd_range(self.buckets[k].start, self.buckets[k].end)
-            for i in nv.blocks_of_bucket(k):
-                nv.prep_block(i)
-        elif k == self.split_bucket:
-            # runs on the weight-gradient stream, right after wgrad(first_block); the data gradient of
-            # that block (last reader of the old bf16 copies of blocks >= first_block) is already queued
+        self._opt_fork.record(torch.cuda.current_stream())
+        self._opt_stream.wait_event(self._opt_fork)
+        self._opt_stream.wait_event(nv._dgrad_done[self.first_block])
+        with torch.cuda.stream(self._opt_stream):
             self._sgd_range(0, self.split_end)
-            torch.cuda.current_stream().wait_event(nv._dgrad_done[self.first_block])
             self._prep_hi()
+            self._opt_join.record(self._opt_stream)
+        self._opt_pending = True
 
     def sync_only(self) -> None:
         return
 
     def sync_and_step(self) -> None:
-        if self.overlap == 0:
+        if not self.overlap:
             self._local_sgd()
-        elif self.overlap == 2:
-            self._sgd_range(self.split_end, self.n)
-            self._prep_lo()
+            return
+        self._sgd_range(self.split_end, self.n)
+        self._prep_lo()
+        if self._opt_pending:
+            torch.cuda.current_stream().wait_event(self._opt_join)
+            self._opt_pending = False
 
     def close(self) -> None:
         if self.overlap:
@@ -203,34 +208,15 @@ class BucketedOverlapSync(NativeSync):
                                      prescale=True, blocks=blocks, channel=CH_BUCKET)
         nv.on_bucket_ready = self.reducer.bucket_ready
         self.launch_log = []
-        # Experimental (B200DP_PART3_PREP_OVERLAP=1, not yet run on hardware): the fused collective of a
-        # bucket leaves new fp32 weights behind; re-lay the bf16 copies of the deep blocks (95 % of the
-        # bytes) on the reducer's stream right behind the bucket that completes them instead of after
-        # finalize().  Same two-phase split as LocalSGD.
+        # Bucket kernels 0..n-2 of a step run without their exit barrier: what it guarantees is implied by the
+        # entry barrier of the next bucket kernel on the channel; only the last one of a step keeps it
+        # (measured on 2 B200s: 0.743 vs 0.773 ms/step).  The reducer does this by itself.
+        #
+        # Optional (B200DP_WGRAD_PUSH=1): the weight-gradient GEMM of every 3x3 layer forwards its finished
+        # tiles to the owning rank's staging slots as they complete (GEMM -> reduce-scatter in one kernel); the
+        # bucket kernel on the reducer stream then only sums local memory, applies SGD and broadcasts the
+        # parameters.
         import os
-        from ..models.native_vgg import WGRAD_ON_SIDE_STREAM
-        self._prep_overlap = (os.environ.get("B200DP_PART3_PREP_OVERLAP", "0") != "0" and fuse
-                              and bucket_plan == "layer" and WGRAD_ON_SIDE_STREAM and len(nv.blocks) > 2)
-        if self._prep_overlap:
-            n = len(nv.blocks)
-            self.first_block = max(n - 5, 1)
-            self.split_bucket = max(k for k in range(len(self.buckets)) if self.first_block in nv.blocks_of_bucket(k))
-            spec = lambda b: (b.w_master, b.wf, b.wd, b.spec.cout, b.spec.cin, 9, b.taps * b.kin)
-            self._prep_hi = K.BatchedWeightPrep([spec(b) for b in nv.blocks[self.first_block:] if not b.direct])
-            self._prep_lo = K.BatchedWeightPrep([spec(b) for b in nv.blocks[:self.first_block] if not b.direct])
-            self._reducer_stream = self.reducer.stream(nv.device)
-            self.handles_shadows = True
-            nv.on_bucket_ready = self._bucket_ready
-
-        # Experimental (B200DP_WGRAD_PUSH=1, not yet run on hardware): the weight-gradient GEMM of every
-        # 3x3 layer forwards its finished tiles to the owning rank's staging slots as they complete
-        # (GEMM -> reduce-scatter in one kernel); the bucket kernel on the reducer stream then only sums
-        # local memory, applies SGD and broadcasts the parameters.
-        # Experimental (B200DP_LAZY_EXIT_BARRIER=1): bucket kernels 0..n-2 skip their exit barrier.  Not combined
-        # with the re-layout behind the buckets, which reads parameters right after the split bucket's kernel.
-        self._lazy_exit = os.environ.get("B200DP_LAZY_EXIT_BARRIER", "0") != "0" and not self._prep_overlap
-        if self._lazy_exit:
-            self.reducer.set_lazy_exit(True)
         self._wgrad_push = (os.environ.get("B200DP_WGRAD_PUSH", "0") != "0" and fuse and bucket_plan == "layer"
                             and self.world > 1 and self.world <= 8)
         if self._wgrad_push:
@@ -252,7 +238,7 @@ class BucketedOverlapSync(NativeSync):
         nv.wgrad_push = {}
         self._push_counters = []
         for i, blk in enumerate(nv.blocks):
-            if blk.first or blk.direct:
+            if blk.first:
                 continue          # Cin = 3: 27 columns, not 16-byte rows; stays on the all-reduce
             e = nv.layout.by_name[f"layers.{blk.spec.conv_idx}.weight"]
             k = next(j for j, b in enumerate(self.buckets) if b.start <= e.offset < b.end)
@@ -265,15 +251,6 @@ class BucketedOverlapSync(NativeSync):
                                     stage_base=stage_base[k])
             pushed_lo[k], pushed_hi[k] = e.offset, e.offset + e.numel
         self.reducer.set_staged(stage_off, pushed_lo, pushed_hi, stage_base)
-
-    def _bucket_ready(self, k: int) -> None:
-        self.reducer.bucket_ready(k)
-        if k == self.split_bucket:
-            # buckets 0..k (every block >= first_block) have been queued on the reducer stream; the data
-            # gradient of first_block is the last reader of the old bf16 copies of those blocks
-            with torch.cuda.stream(self._reducer_stream):
-                self._reducer_stream.wait_event(self.native._dgrad_done[self.first_block])
-                self._prep_hi()
 
     def on_init(self) -> None:
         # DDP constructor: replicas start identical to rank 0
@@ -318,8 +295,6 @@ class BucketedOverlapSync(NativeSync):
         self.reducer.finalize()
         if not self.fuse_optimizer:
             self._local_sgd()
-        if self._prep_overlap:
-            self._prep_lo()
 
     def gather_optimizer_state(self) -> None:
         # per bucket, with the bucket's own slicing; the small (one-shot) buckets already hold identical

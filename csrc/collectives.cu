@@ -237,7 +237,7 @@ __global__ void __launch_bounds__(512) allreduce_twoshot_kernel(const CommDev c,
   allreduce_twoshot_body<FUSE_SGD, PRESCALE, true>(c, a);
 }
 
-// Without the exit barrier (experimental, B200DP_LAZY_EXIT_BARRIER=1).  What the exit barrier guarantees --
+// Without the exit barrier (the bucket reducer's kernels 0..n-2 of a step).  What the exit barrier guarantees --
 // every peer's stores into my buffers have landed, every peer has finished reading mine -- is also implied by
 // the ENTRY barrier of the next collective on the same channel: a peer reaches it only after its previous
 // kernel has completed, stores fenced.  So only the last bucket kernel of a step needs the exit barrier; at
@@ -1262,7 +1262,9 @@ struct Reducer {
   cudaEvent_t done = nullptr;
   int launched = 0;
   // experimental: buckets whose conv weight gradient arrives through conv_wgrad_push staging
-  bool lazy_exit = false;   // experimental: only the last bucket kernel of a step keeps its exit barrier
+  // only the last bucket kernel of a step keeps its exit barrier (the entry barrier of the next bucket
+  // kernel on the channel implies it); bucket_ready() must be called in index order
+  bool lazy_exit = true;
   bool staged = false;
   long long stage_buf_off = 0;
   std::vector<long long> pushed_lo, pushed_hi, stage_base;
@@ -1347,9 +1349,9 @@ extern "C" int b200dp_reducer_bucket_ready(void* reducer, int k, b200dp_stream_t
                         r->prescale, r->lr, r->momentum, r->weight_decay, 0, r->blocks, r->channel, r->side, skip_exit);
 }
 
-/* Experimental: bucket kernels 0 .. n-2 of a step drop their exit barrier (the entry barrier of the next
- * bucket kernel on the channel implies it); bucket_ready() must then be called in index order, which is the
- * gradient-ready order the executor uses. */
+/* Bucket kernels 0 .. n-2 of a step run without their exit barrier (the entry barrier of the next bucket
+ * kernel on the channel implies it; on by default); bucket_ready() must then be called in index order, which
+ * is the gradient-ready order the executor uses.  on = 0 gives every bucket kernel both barriers. */
 extern "C" int b200dp_reducer_set_lazy_exit(void* reducer, int on) {
   auto* r = static_cast<Reducer*>(reducer);
   if (!r) return B200DP_EINVAL;

@@ -12,8 +12,8 @@
 //     over pixels), split-K over pixel blocks fills the 148 SMs, partial tiles are
 //     combined with vector red.global.add.
 //
-// Warp roles per CTA (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner +
-// single-thread tcgen05.mma issuer, warps 2..5 = epilogue (tcgen05.ld -> registers
+// Warp roles per CTA (192 or 320 threads): warp 0 = TMA producer, warp 1 = TMEM owner +
+// single-thread tcgen05.mma issuer, warps 2.. = epilogue, 4 or 8 of them (tcgen05.ld -> registers
 // -> bias / BatchNorm statistics -> global).
 //
 // Replaces what the reference gets from ATen/oneDNN through nn.Conv2d
@@ -33,7 +33,14 @@ constexpr int kBlockM = 128;
 constexpr int kBlockK = 64;  // 64 bf16 = 128 bytes = one SW128 swizzle span
 constexpr int kUmmaK = 16;
 constexpr int kAStageBytes = kBlockM * kBlockK * 2;  // 16 KiB
-constexpr int kNumThreads = 192;
+// Warp roles: warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer, warps 2.. = epilogue.  A warp may only
+// read the TMEM lane quadrant (warp % 4), so epilogue warps come in groups of four; tiles of 128 columns and
+// more get TWO groups, each draining half of the columns (ncu on the one-group kernel: the epilogue was 22 %
+// of a CTA's life with the tensor pipe idle behind it).
+constexpr int epi_warps(int block_n) { return block_n >= 128 ? 8 : 4; }
+constexpr int cta_threads(int block_n) { return 64 + 32 * epi_warps(block_n); }
+// bytes after the stage ring: barriers + TMEM slot (256) and the CTA's bias slice (BLOCK_N floats)
+constexpr int tail_bytes(int block_n) { return 256 + 4 * block_n; }
 
 struct IgemmParams {
   int H, W, TH, TN;  // image dims; an M tile is TN images x TH rows x W columns = 128 pixels
@@ -86,17 +93,27 @@ B200DP_DEVINL void red_add_v4(float* addr, float a, float b, float c, float d) {
 // or fp32 red.add into the split-K workspace.  Warp w may only touch TMEM lanes [32*(w%4), 32*(w%4)+32).
 template <int BLOCK_N, bool BNR = false>
 B200DP_DEVINL void igemm_epilogue(const IgemmParams& p, uint32_t tmem_base, uint64_t* tmem_full_bar, int warp,
-                                  int lane, int m_tile, int n_tile, float* scratch) {
-  // Epilogue: warp w may only touch TMEM lanes [32*(w%4), 32*(w%4)+32).
+                                  int lane, int m_tile, int n_tile, float* scratch, float* bias_smem) {
+  // Epilogue: warp w may only touch TMEM lanes [32*(w%4), 32*(w%4)+32); group (w-2)/4 takes its share of columns.
+  constexpr int kEpiThreads = 32 * epi_warps(BLOCK_N);
+  constexpr int kColsPerGroup = BLOCK_N / (epi_warps(BLOCK_N) / 4);
   const int q = warp & 3;
+  const int grp = (warp - 2) >> 2;
   const int row = q * 32 + lane;
   const long m = static_cast<long>(m_tile) * kBlockM + row;
   const bool valid = m < p.m_total;
+  if (p.bias != nullptr && p.partial == nullptr) {
+    // the bias slice of this tile goes to shared memory while the main loop runs (one L2 round trip per
+    // 32-column chunk sat on the epilogue's critical path before)
+    for (int i = static_cast<int>(threadIdx.x) - 64; i < BLOCK_N; i += kEpiThreads)
+      bias_smem[i] = __ldg(p.bias + n_tile * BLOCK_N + i);
+    asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");
+  }
   mbar_wait(tmem_full_bar, 0);
   tc_fence_after();
   __nv_bfloat16* out_row = p.out + m * p.n_total + n_tile * BLOCK_N;
 #pragma unroll 1
-  for (int c = 0; c < BLOCK_N; c += 32) {
+  for (int c = grp * kColsPerGroup; c < (grp + 1) * kColsPerGroup; c += 32) {
     uint32_t v[32];
     tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + c, v);
     uint4 act[4];
@@ -122,9 +139,12 @@ B200DP_DEVINL void igemm_epilogue(const IgemmParams& p, uint32_t tmem_base, uint
 #pragma unroll
     for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
     if (p.bias != nullptr) {
-      const float* b = p.bias + n_tile * BLOCK_N + c;
+      const float4* b = reinterpret_cast<const float4*>(bias_smem + c);   // broadcast reads
 #pragma unroll
-      for (int j = 0; j < 32; ++j) f[j] += __ldg(b + j);
+      for (int j = 0; j < 8; ++j) {
+        const float4 bv = b[j];
+        f[4 * j] += bv.x; f[4 * j + 1] += bv.y; f[4 * j + 2] += bv.z; f[4 * j + 3] += bv.w;
+      }
     }
     uint32_t packed[16];
 #pragma unroll
@@ -185,16 +205,16 @@ B200DP_DEVINL void igemm_epilogue(const IgemmParams& p, uint32_t tmem_base, uint
   }
   if constexpr (BNR) {
     if (p.partial == nullptr) {
-      asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps only
-      for (int i = static_cast<int>(threadIdx.x) - 64; i < 2 * BLOCK_N; i += 128) {
+      asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");  // the epilogue warps only
+      for (int i = static_cast<int>(threadIdx.x) - 64; i < 2 * BLOCK_N; i += kEpiThreads) {
         const float t = scratch[i] + scratch[2 * BLOCK_N + i] + scratch[4 * BLOCK_N + i] + scratch[6 * BLOCK_N + i];
         const int half = i / BLOCK_N;
         atomicAdd(p.bnr_sums + half * p.n_total + n_tile * BLOCK_N + (i - half * BLOCK_N), t);
       }
     }
   } else if (p.partial == nullptr && p.stats != nullptr && p.stats_via_smem) {
-    asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps only
-    for (int i = static_cast<int>(threadIdx.x) - 64; i < 2 * BLOCK_N; i += 128) {
+    asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");  // the epilogue warps only
+    for (int i = static_cast<int>(threadIdx.x) - 64; i < 2 * BLOCK_N; i += kEpiThreads) {
       const float t = scratch[i] + scratch[2 * BLOCK_N + i] + scratch[4 * BLOCK_N + i] + scratch[6 * BLOCK_N + i];
       const int half = i / BLOCK_N;
       atomicAdd(p.stats + half * p.n_total + n_tile * BLOCK_N + (i - half * BLOCK_N), t);
@@ -307,7 +327,8 @@ B200DP_DEVINL void conv_igemm_body(const CUtensorMap& tmA, const CUtensorMap& tm
       umma_commit(tmem_full_bar);
     }
   } else {
-    igemm_epilogue<BLOCK_N, BNR>(p, tmem_base, tmem_full_bar, warp, lane, m_tile, n_tile, reinterpret_cast<float*>(smem));
+    igemm_epilogue<BLOCK_N, BNR>(p, tmem_base, tmem_full_bar, warp, lane, m_tile, n_tile, reinterpret_cast<float*>(smem),
+                                 reinterpret_cast<float*>(smem + STAGES * kStageBytes + 256));
   }
   __syncthreads();
   if (warp == 1) {
@@ -317,7 +338,7 @@ B200DP_DEVINL void conv_igemm_body(const CUtensorMap& tmA, const CUtensorMap& tm
 }
 
 template <int BLOCK_N, int STAGES>
-__global__ void __launch_bounds__(kNumThreads, STAGES == 1 ? 5 : 1)
+__global__ void __launch_bounds__(cta_threads(BLOCK_N), STAGES == 1 ? 5 : 1)
     conv_igemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                       const IgemmParams p) {
   conv_igemm_body<BLOCK_N, STAGES, false>(tmA, tmB, p);
@@ -325,7 +346,7 @@ __global__ void __launch_bounds__(kNumThreads, STAGES == 1 ? 5 : 1)
 
 // dgrad whose epilogue also accumulates the previous block's BatchNorm-backward sums (IgemmParams::bnr_*)
 template <int BLOCK_N, int STAGES>
-__global__ void __launch_bounds__(kNumThreads)
+__global__ void __launch_bounds__(cta_threads(BLOCK_N))
     conv_dgrad_bnr_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                           const IgemmParams p) {
   conv_igemm_body<BLOCK_N, STAGES, true>(tmA, tmB, p);
@@ -445,7 +466,8 @@ B200DP_DEVINL void conv_igemm_2cta_body(const CUtensorMap& tmA, const CUtensorMa
       umma_commit_2cta(tmem_full_bar, 0b11);
     }
   } else {
-    igemm_epilogue<BLOCK_N, BNR>(p, tmem_base, tmem_full_bar, warp, lane, m_tile, n_tile, reinterpret_cast<float*>(smem));
+    igemm_epilogue<BLOCK_N, BNR>(p, tmem_base, tmem_full_bar, warp, lane, m_tile, n_tile, reinterpret_cast<float*>(smem),
+                                 reinterpret_cast<float*>(smem + STAGES * kStageBytes + 256));
   }
   __syncthreads();
   tc_fence_before();
@@ -457,220 +479,17 @@ B200DP_DEVINL void conv_igemm_2cta_body(const CUtensorMap& tmA, const CUtensorMa
 }
 
 template <int BLOCK_N, int STAGES>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(cta_threads(BLOCK_N))
     conv_igemm_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                            const IgemmParams p) {
   conv_igemm_2cta_body<BLOCK_N, STAGES, false>(tmA, tmB, p);
 }
 
 template <int BLOCK_N, int STAGES>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(cta_threads(BLOCK_N))
     conv_dgrad_bnr_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                                const IgemmParams p) {
   conv_igemm_2cta_body<BLOCK_N, STAGES, true>(tmA, tmB, p);
-}
-
-// ---------------------------------------------------------------------------
-// Persistent variant (experimental, B200DP_PERSIST=1 makes it a tile-shape candidate of the autotuner):
-// one CTA per SM walks the output tiles t = blockIdx.x, blockIdx.x + gridDim.x, ...  The accumulator is
-// double-buffered in TMEM (2 x BLOCK_N columns), so the epilogue of tile i (tcgen05.ld, bias, bf16,
-// stores, statistics) runs while the TMA producer and the MMA thread are already on tile i+1: the
-// SM's operand pipe, which is what bounds these layers, never drains between tiles, and barrier
-// setup / TMEM allocation / descriptor prefetch are paid once per SM instead of once per tile.
-// No split-K.  Statistics use their own shared-memory scratch (the stage buffers are never idle here).
-// ---------------------------------------------------------------------------
-struct IgemmPersistParams : IgemmParams {
-  int m_tiles, total_tiles;
-};
-
-template <int BLOCK_N, int STAGES>
-__global__ void __launch_bounds__(kNumThreads, 1)
-    conv_igemm_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                              const IgemmPersistParams p) {
-  constexpr int kBStageBytes = BLOCK_N * kBlockK * 2;
-  constexpr int kStageBytes = kAStageBytes + kBStageBytes;
-  constexpr uint32_t kAccCols = BLOCK_N < 32 ? 32 : BLOCK_N;
-  constexpr uint32_t kTmemCols = 2 * kAccCols;
-  constexpr uint32_t kIdesc = umma_idesc_bf16(kBlockM, BLOCK_N, 0, 0);
-  constexpr int kScratchBytes = 4 * 2 * BLOCK_N * 4;
-
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  float* scratch = reinterpret_cast<float*>(smem + STAGES * kStageBytes);
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * kStageBytes + kScratchBytes);
-  uint64_t* empty_bar = full_bar + STAGES;
-  uint64_t* tmem_full_bar = empty_bar + STAGES;   // [2]
-  uint64_t* tmem_empty_bar = tmem_full_bar + 2;   // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
-
-  const int warp = threadIdx.x >> 5;
-  const int lane = threadIdx.x & 31;
-  pdl_launch_dependents();
-  const int total_kb = p.taps * p.cin_blocks;
-
-  if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&tmA);
-    tma_prefetch_desc(&tmB);
-    for (int s = 0; s < STAGES; ++s) {
-      mbar_init(&full_bar[s], 1);
-      mbar_init(&empty_bar[s], 1);
-    }
-    for (int b = 0; b < 2; ++b) {
-      mbar_init(&tmem_full_bar[b], 1);   // one tcgen05.commit per tile
-      mbar_init(&tmem_empty_bar[b], 4);  // one arrive per epilogue warp once its TMEM reads are done
-    }
-    mbar_fence_init();
-  }
-  if (warp == 1) {
-    tmem_alloc(tmem_slot, kTmemCols);
-    tmem_relinquish();
-  }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
-  pdl_wait();
-
-  if (warp == 0) {
-    if (elect_one()) {
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x) {
-        const int m_tile = t % p.m_tiles, n_tile = t / p.m_tiles;
-        int n0, h0;
-        if (p.TN == 1) {
-          const int tiles_per_img = p.H / p.TH;
-          n0 = m_tile / tiles_per_img;
-          h0 = (m_tile - n0 * tiles_per_img) * p.TH;
-        } else {
-          n0 = m_tile * p.TN;
-          h0 = 0;
-        }
-        for (int kb = 0; kb < total_kb; ++kb) {
-          mbar_wait(&empty_bar[stage], phase ^ 1);
-          mbar_arrive_expect_tx(&full_bar[stage], kStageBytes);
-          const int tap = kb / p.cin_blocks;
-          const int cb = kb - tap * p.cin_blocks;
-          int dr = 0, ds = 0;
-          if (p.taps == 9) {
-            dr = tap / 3 - 1;
-            ds = tap % 3 - 1;
-          }
-          uint8_t* a_dst = smem + stage * kStageBytes;
-          tma_load_4d(a_dst, &tmA, &full_bar[stage], cb * kBlockK, ds, h0 + dr, n0);
-          tma_load_2d(a_dst + kAStageBytes, &tmB, &full_bar[stage], kb * kBlockK, n_tile * BLOCK_N);
-          if (++stage == STAGES) {
-            stage = 0;
-            phase ^= 1;
-          }
-        }
-      }
-    }
-  } else if (warp == 1) {
-    if (elect_one()) {
-      int stage = 0;
-      uint32_t phase = 0;
-      int it = 0;
-      for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++it) {
-        const int buf = it & 1;
-        const uint32_t use = static_cast<uint32_t>(it >> 1) & 1u;
-        mbar_wait(&tmem_empty_bar[buf], use ^ 1);  // the epilogue has drained this accumulator (first use: free)
-        tc_fence_after();
-        const uint32_t acc = tmem_base + static_cast<uint32_t>(buf) * kAccCols;
-        for (int kb = 0; kb < total_kb; ++kb) {
-          mbar_wait(&full_bar[stage], phase);
-          tc_fence_after();
-          const uint32_t a_addr = smem_u32(smem + stage * kStageBytes);
-          const uint32_t b_addr = a_addr + kAStageBytes;
-#pragma unroll
-          for (int k = 0; k < kBlockK / kUmmaK; ++k) {
-            const uint64_t da = umma_smem_desc(a_addr + k * kUmmaK * 2, 16, 1024);
-            const uint64_t db = umma_smem_desc(b_addr + k * kUmmaK * 2, 16, 1024);
-            umma_bf16(acc, da, db, kIdesc, (kb | k) != 0);
-          }
-          umma_commit(&empty_bar[stage]);
-          if (++stage == STAGES) {
-            stage = 0;
-            phase ^= 1;
-          }
-        }
-        umma_commit(&tmem_full_bar[buf]);
-      }
-    }
-  } else {
-    const int q = warp & 3;
-    const int row = q * 32 + lane;
-    int it = 0;
-    for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++it) {
-      const int m_tile = t % p.m_tiles, n_tile = t / p.m_tiles;
-      const int buf = it & 1;
-      const uint32_t use = static_cast<uint32_t>(it >> 1) & 1u;
-      const long m = static_cast<long>(m_tile) * kBlockM + row;
-      const bool valid = m < p.m_total;
-      __nv_bfloat16* out_row = p.out + m * p.n_total + n_tile * BLOCK_N;
-      mbar_wait(&tmem_full_bar[buf], use);
-      tc_fence_after();
-      const uint32_t acc = tmem_base + static_cast<uint32_t>(buf) * kAccCols + (static_cast<uint32_t>(q * 32) << 16);
-#pragma unroll 1
-      for (int c = 0; c < BLOCK_N; c += 32) {
-        uint32_t v[32];
-        tmem_ld_32x32(acc + c, v);
-        tmem_ld_wait();
-        if (c + 32 >= BLOCK_N) {
-          // last read of this accumulator: hand it back so that the MMA thread can start tile it + 2
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&tmem_empty_bar[buf]);
-        }
-        float f[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
-        if (p.bias != nullptr) {
-          const float* b = p.bias + n_tile * BLOCK_N + c;
-#pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] += __ldg(b + j);
-        }
-        uint32_t packed[16];
-#pragma unroll
-        for (int j = 0; j < 16; ++j) packed[j] = pack_bf16x2(f[2 * j], f[2 * j + 1]);
-        if (valid) {
-          uint4* dst = reinterpret_cast<uint4*>(out_row + c);
-#pragma unroll
-          for (int j = 0; j < 4; ++j)
-            dst[j] = make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
-        }
-        if (p.stats != nullptr) {
-          float s1[32], s2[32];
-#pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            const float2 r = unpack_bf16x2(packed[j]);
-            s1[2 * j] = valid ? r.x : 0.f;
-            s1[2 * j + 1] = valid ? r.y : 0.f;
-            s2[2 * j] = s1[2 * j] * s1[2 * j];
-            s2[2 * j + 1] = s1[2 * j + 1] * s1[2 * j + 1];
-          }
-          const float t1 = warp_transpose_sum(s1, lane);
-          const float t2 = warp_transpose_sum(s2, lane);
-          scratch[q * 2 * BLOCK_N + c + lane] = t1;
-          scratch[q * 2 * BLOCK_N + BLOCK_N + c + lane] = t2;
-        }
-      }
-      if (p.stats != nullptr) {
-        asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps: partials complete
-        for (int i = static_cast<int>(threadIdx.x) - 64; i < 2 * BLOCK_N; i += 128) {
-          const float tsum = scratch[i] + scratch[2 * BLOCK_N + i] + scratch[4 * BLOCK_N + i] + scratch[6 * BLOCK_N + i];
-          const int half = i / BLOCK_N;
-          atomicAdd(p.stats + half * p.n_total + n_tile * BLOCK_N + (i - half * BLOCK_N), tsum);
-        }
-        asm volatile("bar.sync 1, 128;" ::: "memory");  // scratch may be overwritten by the next tile
-      }
-    }
-  }
-  __syncthreads();
-  if (warp == 1) {
-    tc_fence_after();
-    tmem_dealloc(tmem_base, kTmemCols);
-  }
 }
 
 // Split-K epilogue: partial fp32 [M][N] -> (+bias) -> bf16 out, fused BatchNorm statistics of the
@@ -950,7 +769,11 @@ B200DP_DEVINL void conv_wgrad_body(const CUtensorMap& tmDY, const CUtensorMap& t
         umma_commit(tmem_full_bar);
       }
     } else {
+      constexpr int kEpiThreads = 32 * epi_warps(BLOCK_N);
+      constexpr int kGroups = epi_warps(BLOCK_N) / 4;
+      constexpr int kColsPerGroup = BLOCK_N / kGroups;
       const int q = warp & 3;
+      const int grp = (warp - 2) >> 2;
       const int row = q * 32 + lane;
       const int co = co_tile * kBlockM + row;
       const bool valid = co < p.cout;
@@ -959,7 +782,7 @@ B200DP_DEVINL void conv_wgrad_body(const CUtensorMap& tmDY, const CUtensorMap& t
       float* out_row = p.out + static_cast<long>(co) * p.ld_out + tap * p.cin_valid + ci_tile * BLOCK_N;
       const int col_limit = p.cin_valid - ci_tile * BLOCK_N;  // columns >= this are padding
 #pragma unroll 1
-      for (int c = 0; c < BLOCK_N; c += 32) {
+      for (int c = grp * kColsPerGroup; c < (grp + 1) * kColsPerGroup; c += 32) {
         uint32_t v[32];
         tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + c, v);
         tmem_ld_wait();
@@ -995,14 +818,14 @@ B200DP_DEVINL void conv_wgrad_body(const CUtensorMap& tmDY, const CUtensorMap& t
         // writes before the counter increment, so whoever draws the last ticket sees the complete tile.
         uint32_t* last_flag = tmem_slot + 1;
         __threadfence();
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");
         if (threadIdx.x == 64) {
           const unsigned int ticket = atomicAdd(p.tile_counters + blockIdx.x, 1u);
           const bool last = ticket == static_cast<unsigned int>(p.splits) - 1u;
           if (last) p.tile_counters[blockIdx.x] = 0u;  // nobody else touches it before the next launch
           *last_flag = last ? 1u : 0u;
         }
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");
         if (*last_flag != 0u) {
           __threadfence();
           // warp-cooperative: the 32 lanes walk one output row at a time, so every store instruction
@@ -1014,7 +837,7 @@ B200DP_DEVINL void conv_wgrad_body(const CUtensorMap& tmDY, const CUtensorMap& t
             const long long row_off = static_cast<long long>(co_r) * p.ld_out + tap * p.cin_valid + ci_tile * BLOCK_N;
             const float* src_row = p.out + row_off;
             const long long i4_row = (p.flat_off + row_off - p.own_start) >> 2;
-            for (int c4 = lane; c4 < ncols4; c4 += 32) {
+            for (int c4 = lane + 32 * grp; c4 < ncols4; c4 += 32 * kGroups) {
               const long long i4 = i4_row + c4;
               const int owner = static_cast<int>(i4 / p.per4);
               if (owner != p.rank) {
@@ -1038,7 +861,7 @@ B200DP_DEVINL void conv_wgrad_body(const CUtensorMap& tmDY, const CUtensorMap& t
 }
 
 template <int BLOCK_N, int STAGES>
-__global__ void __launch_bounds__(kNumThreads)
+__global__ void __launch_bounds__(cta_threads(BLOCK_N))
     conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ CUtensorMap tmX,
                       const WgradParams p) {
   conv_wgrad_body<BLOCK_N, STAGES, false, WgradParams>(tmDY, tmX, p);
@@ -1046,7 +869,7 @@ __global__ void __launch_bounds__(kNumThreads)
 
 // Weight gradient + the transfer half of the gradient reduce-scatter (WgradParams::peer_stage ...).
 template <int BLOCK_N, int STAGES>
-__global__ void __launch_bounds__(kNumThreads)
+__global__ void __launch_bounds__(cta_threads(BLOCK_N))
     conv_wgrad_push_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ CUtensorMap tmX,
                            const WgradPushParams p) {
   conv_wgrad_body<BLOCK_N, STAGES, true, WgradPushParams>(tmDY, tmX, p);
@@ -1124,7 +947,7 @@ static bool short_k_enabled() {
 template <int BLOCK_N, int STAGES>
 static int launch_igemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const IgemmParams& p, int m_tiles,
                         int splits, cudaStream_t stream) {
-  constexpr int smem = STAGES * (kAStageBytes + BLOCK_N * kBlockK * 2) + 1024 + 256;
+  constexpr int smem = STAGES * (kAStageBytes + BLOCK_N * kBlockK * 2) + 1024 + tail_bytes(BLOCK_N);
   static bool configured = false;
   auto kern = conv_igemm_kernel<BLOCK_N, STAGES>;
   if (!configured) {
@@ -1132,14 +955,14 @@ static int launch_igemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Ig
     configured = true;
   }
   dim3 grid(m_tiles, p.n_total / BLOCK_N, splits);
-  B200DP_CUDA_TRY(launch_pdl(kern, grid, dim3(kNumThreads), smem, stream, tmA, tmB, p));
+  B200DP_CUDA_TRY(launch_pdl(kern, grid, dim3(cta_threads(BLOCK_N)), smem, stream, tmA, tmB, p));
   return 0;
 }
 
 template <int BLOCK_N, int STAGES>
 static int launch_igemm_2cta(const CUtensorMap& tmA, const CUtensorMap& tmB, const IgemmParams& p, int m_tiles,
                              int splits, cudaStream_t stream) {
-  constexpr int smem = STAGES * (kAStageBytes + (BLOCK_N / 2) * kBlockK * 2) + 1024 + 256;
+  constexpr int smem = STAGES * (kAStageBytes + (BLOCK_N / 2) * kBlockK * 2) + 1024 + tail_bytes(BLOCK_N);
   static bool configured = false;
   auto kern = conv_igemm_2cta_kernel<BLOCK_N, STAGES>;
   if (!configured) {
@@ -1147,33 +970,14 @@ static int launch_igemm_2cta(const CUtensorMap& tmA, const CUtensorMap& tmB, con
     configured = true;
   }
   dim3 grid(m_tiles, p.n_total / BLOCK_N, splits);  // m_tiles is even; __cluster_dims__(2,1,1) pairs them
-  B200DP_CUDA_TRY(launch_pdl(kern, grid, dim3(kNumThreads), smem, stream, tmA, tmB, p));
-  return 0;
-}
-
-template <int BLOCK_N, int STAGES>
-static int launch_igemm_persist(const CUtensorMap& tmA, const CUtensorMap& tmB, const IgemmPersistParams& p,
-                                cudaStream_t stream) {
-  constexpr int smem = STAGES * (kAStageBytes + BLOCK_N * kBlockK * 2) + 4 * 2 * BLOCK_N * 4 + 1024 + 256;
-  static bool configured = false;
-  static int sms = 0;
-  auto kern = conv_igemm_persist_kernel<BLOCK_N, STAGES>;
-  if (!configured) {
-    B200DP_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    int dev = 0;
-    B200DP_CUDA_TRY(cudaGetDevice(&dev));
-    B200DP_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    configured = true;
-  }
-  const int grid = p.total_tiles < sms ? p.total_tiles : sms;
-  B200DP_CUDA_TRY(launch_pdl(kern, dim3(grid), dim3(kNumThreads), smem, stream, tmA, tmB, p));
+  B200DP_CUDA_TRY(launch_pdl(kern, grid, dim3(cta_threads(BLOCK_N)), smem, stream, tmA, tmB, p));
   return 0;
 }
 
 template <int BLOCK_N, int STAGES>
 static int launch_dgrad_bnr(const CUtensorMap& tmA, const CUtensorMap& tmB, const IgemmParams& p, int m_tiles,
                             int splits, cudaStream_t stream) {
-  constexpr int smem = STAGES * (kAStageBytes + BLOCK_N * kBlockK * 2) + 1024 + 256;
+  constexpr int smem = STAGES * (kAStageBytes + BLOCK_N * kBlockK * 2) + 1024 + tail_bytes(BLOCK_N);
   static bool configured = false;
   auto kern = conv_dgrad_bnr_kernel<BLOCK_N, STAGES>;
   if (!configured) {
@@ -1181,14 +985,14 @@ static int launch_dgrad_bnr(const CUtensorMap& tmA, const CUtensorMap& tmB, cons
     configured = true;
   }
   dim3 grid(m_tiles, p.n_total / BLOCK_N, splits);
-  B200DP_CUDA_TRY(launch_pdl(kern, grid, dim3(kNumThreads), smem, stream, tmA, tmB, p));
+  B200DP_CUDA_TRY(launch_pdl(kern, grid, dim3(cta_threads(BLOCK_N)), smem, stream, tmA, tmB, p));
   return 0;
 }
 
 template <int BLOCK_N, int STAGES>
 static int launch_dgrad_bnr_2cta(const CUtensorMap& tmA, const CUtensorMap& tmB, const IgemmParams& p, int m_tiles,
                                  int splits, cudaStream_t stream) {
-  constexpr int smem = STAGES * (kAStageBytes + (BLOCK_N / 2) * kBlockK * 2) + 1024 + 256;
+  constexpr int smem = STAGES * (kAStageBytes + (BLOCK_N / 2) * kBlockK * 2) + 1024 + tail_bytes(BLOCK_N);
   static bool configured = false;
   auto kern = conv_dgrad_bnr_2cta_kernel<BLOCK_N, STAGES>;
   if (!configured) {
@@ -1196,14 +1000,14 @@ static int launch_dgrad_bnr_2cta(const CUtensorMap& tmA, const CUtensorMap& tmB,
     configured = true;
   }
   dim3 grid(m_tiles, p.n_total / BLOCK_N, splits);
-  B200DP_CUDA_TRY(launch_pdl(kern, grid, dim3(kNumThreads), smem, stream, tmA, tmB, p));
+  B200DP_CUDA_TRY(launch_pdl(kern, grid, dim3(cta_threads(BLOCK_N)), smem, stream, tmA, tmB, p));
   return 0;
 }
 
 template <int BLOCK_N, int STAGES>
 static int launch_wgrad(const CUtensorMap& tmDY, const CUtensorMap& tmX, const WgradParams& p, int tiles,
                         int splits, cudaStream_t stream) {
-  constexpr int smem = STAGES * (2 * 8192 + (BLOCK_N / 64) * 8192) + 1024 + 256;
+  constexpr int smem = STAGES * (2 * 8192 + (BLOCK_N / 64) * 8192) + 1024 + tail_bytes(BLOCK_N);
   static bool configured = false;
   auto kern = conv_wgrad_kernel<BLOCK_N, STAGES>;
   if (!configured) {
@@ -1211,14 +1015,14 @@ static int launch_wgrad(const CUtensorMap& tmDY, const CUtensorMap& tmX, const W
     configured = true;
   }
   dim3 grid(tiles, splits);
-  B200DP_CUDA_TRY(launch_pdl(kern, grid, dim3(kNumThreads), smem, stream, tmDY, tmX, p));
+  B200DP_CUDA_TRY(launch_pdl(kern, grid, dim3(cta_threads(BLOCK_N)), smem, stream, tmDY, tmX, p));
   return 0;
 }
 
 template <int BLOCK_N, int STAGES>
 static int launch_wgrad_push(const CUtensorMap& tmDY, const CUtensorMap& tmX, const WgradPushParams& p, int tiles,
                              int splits, cudaStream_t stream) {
-  constexpr int smem = STAGES * (2 * 8192 + (BLOCK_N / 64) * 8192) + 1024 + 256;
+  constexpr int smem = STAGES * (2 * 8192 + (BLOCK_N / 64) * 8192) + 1024 + tail_bytes(BLOCK_N);
   static bool configured = false;
   auto kern = conv_wgrad_push_kernel<BLOCK_N, STAGES>;
   if (!configured) {
@@ -1226,7 +1030,7 @@ static int launch_wgrad_push(const CUtensorMap& tmDY, const CUtensorMap& tmX, co
     configured = true;
   }
   dim3 grid(tiles, splits);
-  B200DP_CUDA_TRY(launch_pdl(kern, grid, dim3(kNumThreads), smem, stream, tmDY, tmX, p));
+  B200DP_CUDA_TRY(launch_pdl(kern, grid, dim3(cta_threads(BLOCK_N)), smem, stream, tmDY, tmX, p));
   return 0;
 }
 
@@ -1324,23 +1128,6 @@ static int conv_igemm_impl(const void* act, const void* wgt, const float* bias, 
     const uint32_t box[2] = {64, (uint32_t)(cta_pair == 1 ? block_n / 2 : block_n)};
     int rc = make_tmap(&tmB, wgt, 2, dims, box);
     if (rc) return rc;
-  }
-  if (cta_pair == 2) {
-    // persistent 1-CTA kernel; statistics always go through shared memory, no split-K, no bnr
-    if (split_k != 1 || bnr != nullptr || block_n < 64) {
-      set_error("conv_igemm: the persistent kernel takes block_n in {64,128,256}, split_k = 1 and no bn-reduce");
-      return B200DP_EINVAL;
-    }
-    IgemmPersistParams pp{};
-    static_cast<IgemmParams&>(pp) = p;
-    pp.m_tiles = m_tiles;
-    pp.total_tiles = m_tiles * (Cout / block_n);
-    switch (block_n) {
-      case 256: return launch_igemm_persist<256, 4>(tmA, tmB, pp, stream);
-      case 128: return launch_igemm_persist<128, 6>(tmA, tmB, pp, stream);
-      case 64: return launch_igemm_persist<64, 8>(tmA, tmB, pp, stream);
-      default: set_error("conv_igemm: block_n=%d not in {64,128,256} for the persistent kernel", block_n); return B200DP_EINVAL;
-    }
   }
   int rc;
   if (bnr != nullptr) {
@@ -1453,17 +1240,6 @@ extern "C" int b200dp_conv_dgrad_bn_reduce(const void* act, const void* wgt, voi
   const BnReduceArgs bnr{bn_out, gamma, beta, sums};
   return conv_igemm_impl(act, wgt, nullptr, out, nullptr, workspace, B, H, W, Cin, Cout, taps, block_n, split_k,
                          cta_pair, static_cast<cudaStream_t>(stream_), &bnr);
-}
-
-/* Persistent variant of b200dp_conv_igemm (experimental): one CTA per SM walks the output tiles with the
- * accumulator double-buffered in TMEM, so a tile's epilogue overlaps the next tile's loads and MMAs.
- * block_n in {64,128,256}; no split-K. */
-extern "C" int b200dp_conv_igemm_persist(const void* act, const void* wgt, const float* bias, void* out,
-                                         float* stats, int B, int H, int W, int Cin, int Cout, int taps,
-                                         int block_n, b200dp_stream_t stream_) {
-  if (block_n == 0) block_n = (Cout % 128 == 0) ? 128 : 64;
-  return conv_igemm_impl(act, wgt, bias, out, stats, nullptr, B, H, W, Cin, Cout, taps, block_n, 1, 2,
-                         static_cast<cudaStream_t>(stream_));
 }
 
 static int conv_wgrad_impl(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin, int Cout, int taps,

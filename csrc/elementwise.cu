@@ -10,7 +10,6 @@
 // unbiased for running_var; MaxPool2d(2,2) routes the gradient to the first
 // maximum in scan order; CrossEntropyLoss(mean); SGD lr/momentum/weight_decay
 // with dampening 0 and weight decay on every parameter.
-#include <cooperative_groups.h>
 #include <stdio.h>
 #include <stdlib.h>
 
@@ -62,44 +61,9 @@ B200DP_DEVINL Vec8 load_f32x8(const float* p) {
 // shared memory with coalesced loads, then every thread emits 16-byte chunks of the 64-wide patch rows.
 constexpr int kIm2colRows = 4;
 
-__global__ void __launch_bounds__(256) im2col_c3_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ a0,
-                                                        int B, int H, int W) {
-  pdl_launch_dependents();
-  pdl_wait();
-  extern __shared__ float win[];  // [rows + 2][3 channels][W + 2]
-  const int Wp = W + 2;
-  const int groups = (H + kIm2colRows - 1) / kIm2colRows;
-  const int n = blockIdx.x / groups, h0 = (blockIdx.x - n * groups) * kIm2colRows;
-  const int rows = min(kIm2colRows, H - h0);
-  for (int i = threadIdx.x; i < (rows + 2) * 3 * Wp; i += blockDim.x) {
-    const int r = i / (3 * Wp), rem = i - r * 3 * Wp;
-    const int c = rem / Wp, ww = rem - c * Wp - 1;
-    const int hh = h0 + r - 1;
-    win[i] = (hh >= 0 && hh < H && ww >= 0 && ww < W) ? __ldg(x + ((static_cast<long>(n) * 3 + c) * H + hh) * W + ww) : 0.f;
-  }
-  __syncthreads();
-  for (int t = threadIdx.x; t < rows * W * 8; t += blockDim.x) {
-    const int chunk = t & 7, pix = t >> 3;
-    const int pr = pix / W, w = pix - pr * W;
-    Vec8 r;
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const int k = chunk * 8 + j;
-      float v = 0.f;
-      if (k < 27) {
-        const int tap = k / 3, c = k - tap * 3;
-        v = win[(pr + tap / 3) * 3 * Wp + c * Wp + w + tap % 3];
-      }
-      r.v[j] = v;
-    }
-    store_bf16x8(a0 + ((static_cast<long>(n) * H + h0 + pr) * W + w) * 64 + chunk * 8, r);
-  }
-}
-
-// Same result, cheaper address arithmetic: blockDim is a multiple of 8, so a thread emits the same
-// 16-byte chunk of every patch row it touches.  The (tap, channel) -> window offset decode of its 8
-// columns is done once, outside the pixel loop; the upper half of the row (columns 32..63) is a
-// constant zero store.  B200DP_IM2COL_V2=0 selects the kernel above (A/B runs).
+// blockDim is a multiple of 8, so a thread emits the same 16-byte chunk of every patch row it touches: the
+// (tap, channel) -> window offset decode of its 8 columns is done once, outside the pixel loop; the upper
+// half of the row (columns 32..63) is a constant zero store.
 __global__ void __launch_bounds__(256) im2col_c3_v2_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ a0,
                                                            int B, int H, int W) {
   pdl_launch_dependents();
@@ -646,16 +610,6 @@ __global__ void __launch_bounds__(256, 3) bn_relu_pool_bwd_kernel(const BnBwdPar
   pdl_wait();
   extern __shared__ float red[];
   bn_relu_pool_bwd_body<APPLY>(p, red);
-}
-
-// Both passes in one cooperative launch: reduce, grid-wide barrier, apply.  The second pass finds
-// y and dout still in L2, and a layer costs one launch instead of two.
-__global__ void __launch_bounds__(256, 3) bn_relu_pool_bwd_fused_kernel(const BnBwdParams p) {
-  extern __shared__ float red[];
-  bn_relu_pool_bwd_body<false>(p, red);
-  __threadfence();
-  cooperative_groups::this_grid().sync();
-  bn_relu_pool_bwd_body<true>(p, red);
 }
 
 // ---------------------------------------------------------------------------
@@ -1214,6 +1168,29 @@ __global__ void sgd_momentum_kernel(float* __restrict__ p, const float* __restri
   }
 }
 
+// Clear n16 16-byte words (the flat gradient buffer before the split-K weight gradients are accumulated
+// into it, the per-step statistics region).  The framework's own fill, so that a training step launches no
+// library kernel and the fill takes part in the programmatic-dependent-launch chain.
+__global__ void __launch_bounds__(256) fill_zero_kernel(uint4* __restrict__ dst, long n16) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const long stride = static_cast<long>(gridDim.x) * blockDim.x;
+  const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+  for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < n16; i += stride) dst[i] = z;
+}
+
+// Device-to-device copy of up to two ranges of 16-byte words in one launch (a step's staged images and
+// labels into the buffers the captured step reads).
+__global__ void __launch_bounds__(256) copy_pair_kernel(uint4* __restrict__ d0, const uint4* __restrict__ s0, long n0,
+                                                        uint4* __restrict__ d1, const uint4* __restrict__ s1, long n1) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const long stride = static_cast<long>(gridDim.x) * blockDim.x;
+  const long first = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x;
+  for (long i = first; i < n0; i += stride) d0[i] = s0[i];
+  for (long i = first; i < n1; i += stride) d1[i] = s1[i];
+}
+
 // master fp32 [Cout][taps][Cin] -> Wf bf16 [Cout][kpad] (zero padded past taps*Cin)
 //                               -> Wd bf16 [Cin][taps*Cout] with taps flipped (dgrad operand), optional
 __global__ void prep_conv_weights_kernel(const float* __restrict__ master, __nv_bfloat16* __restrict__ wf,
@@ -1292,15 +1269,8 @@ __global__ void __launch_bounds__(256) prep_conv_weights_batched_kernel(const Pr
   }
 }
 
-// B200DP_BN_TMA=1: route the BatchNorm kernels to their bulk-copy pipelined variants (csrc/bn_stream.cu and
-// bn_bwd_apply_pool_tma_kernel) wherever the shape allows; experimental, off by default.
-static bool bn_tma_enabled() {
-  static const bool on = [] {
-    const char* e = getenv("B200DP_BN_TMA");
-    return e != nullptr && e[0] != '0';
-  }();
-  return on;
-}
+// The BatchNorm kernels run as bulk-copy pipelines (csrc/bn_stream.cu, bn_bwd_apply_pool_tma_kernel) wherever the
+// shape fits their stage geometry; the register-file kernels in this file take the remaining shapes.
 static bool bn_tma_shape_ok(int H, int W, int C, int pool) {
   if (C < 8 || C % 8 != 0 || C > 2048 || 256 % (C / 8) != 0) return false;
   if (!pool) return true;
@@ -1322,11 +1292,7 @@ using namespace b200dp;
 extern "C" int b200dp_im2col3x3_c3(const float* x_nchw, void* a0, int B, int H, int W, b200dp_stream_t s) {
   const size_t smem = (kIm2colRows + 2) * 3 * (W + 2) * sizeof(float);
   const int groups = (H + kIm2colRows - 1) / kIm2colRows;
-  static const bool v2 = [] {
-    const char* e = getenv("B200DP_IM2COL_V2");
-    return e == nullptr || e[0] != '0';
-  }();
-  B200DP_CUDA_TRY(launch_pdl(v2 ? im2col_c3_v2_kernel : im2col_c3_kernel, dim3(B * groups), dim3(256), smem,
+  B200DP_CUDA_TRY(launch_pdl(im2col_c3_v2_kernel, dim3(B * groups), dim3(256), smem,
                              static_cast<cudaStream_t>(s), x_nchw, static_cast<__nv_bfloat16*>(a0), B, H, W));
   return 0;
 }
@@ -1358,7 +1324,7 @@ extern "C" int b200dp_bn_relu_pool_fwd(const void* y, const float* stats, const 
     set_error("bn_relu_pool_fwd: unsupported shape H=%d W=%d C=%d pool=%d", H, W, C, pool);
     return B200DP_EINVAL;
   }
-  if (bn_tma_enabled() && bn_tma_shape_ok(H, W, C, pool))
+  if (bn_tma_shape_ok(H, W, C, pool))
     return b200dp_bn_relu_pool_fwd_tma(y, stats, gamma, beta, running_mean, running_var, num_batches_tracked,
                                        save_mean, save_invstd, out, B, H, W, C, pool, training, momentum, eps, s);
   BnFwdParams p{static_cast<const __nv_bfloat16*>(y), stats, gamma, beta, running_mean, running_var,
@@ -1410,66 +1376,18 @@ static int launch_bn_bwd(bool apply, const BnBwdParams& p, cudaStream_t s) {
   // ragged tail; apply pass (4 loads + 4 stores per item): measured faster with two items per thread
   // and many short blocks.
   const int blocks = apply ? grid_for(Q, rows_per_block * 2, 148 * 8) : grid_for(Q, rows_per_block, 148 * 3);
-  static const bool apply_v2 = [] {
-    const char* e = getenv("B200DP_BN_APPLY_V2");
-    return e == nullptr || e[0] != '0';
-  }();
-  static const bool apply_pool_v2 = [] {
-    const char* e = getenv("B200DP_BN_APPLY_POOL_V2");
-    return e == nullptr || e[0] != '0';
-  }();
-  if (apply && p.pool && bn_tma_enabled() && bn_tma_supported(p)) return launch_bn_apply_pool_tma(p, s);
-  if (apply && !p.pool && bn_tma_enabled() && bn_tma_shape_ok(p.H, p.W, p.C, 0))
+  if (apply && p.pool && bn_tma_supported(p)) return launch_bn_apply_pool_tma(p, s);
+  if (apply && !p.pool && bn_tma_shape_ok(p.H, p.W, p.C, 0))
     return b200dp_bn_bwd_apply_nopool_tma(p.y, p.dout, p.mean, p.invstd, p.gamma, p.beta, p.sums, p.dy, p.dgamma,
                                           p.dbeta, p.B, p.H, p.W, p.C, s);
-  if (apply && !p.pool && apply_v2)
+  if (apply && !p.pool)
     B200DP_CUDA_TRY(launch_pdl(bn_bwd_apply_nopool_kernel, dim3(grid_for(Q, rows_per_block * 4, 148 * 3)),
                                dim3(threads), 0, s, p));
-  else if (apply && p.pool && apply_pool_v2)
+  else if (apply && p.pool)
     B200DP_CUDA_TRY(launch_pdl(bn_bwd_apply_pool_kernel, dim3(grid_for(Q, rows_per_block * 2, 148 * 4)),
                                dim3(threads), 0, s, p));
-  else if (apply)
-    B200DP_CUDA_TRY(launch_pdl(bn_relu_pool_bwd_kernel<true>, dim3(blocks), dim3(threads), smem, s, p));
   else
     B200DP_CUDA_TRY(launch_pdl(bn_relu_pool_bwd_kernel<false>, dim3(blocks), dim3(threads), smem, s, p));
-  return 0;
-}
-
-/* reduce + apply in ONE cooperative launch (sums must be zero on entry, as for the two-pass form). */
-extern "C" int b200dp_bn_relu_pool_bwd_fused(const void* y, const void* dout, const float* mean, const float* invstd,
-                                             const float* gamma, const float* beta, float* sums, void* dy,
-                                             float* dgamma, float* dbeta, int B, int H, int W, int C, int pool,
-                                             b200dp_stream_t s) {
-  BnBwdParams p{static_cast<const __nv_bfloat16*>(y), static_cast<const __nv_bfloat16*>(dout), mean, invstd, gamma,
-                beta, sums, static_cast<__nv_bfloat16*>(dy), dgamma, dbeta, B, H, W, C, pool};
-  if (p.C % 8 != 0 || p.C > 2048 || (p.pool && ((p.H | p.W) & 1))) {
-    set_error("bn_relu_pool_bwd_fused: unsupported shape H=%d W=%d C=%d pool=%d", p.H, p.W, p.C, p.pool);
-    return B200DP_EINVAL;
-  }
-  const int threads = 256;
-  const int rows_per_block = threads / (p.C / 8);
-  const size_t smem = 2 * rows_per_block * p.C * sizeof(float);
-  static int max_blocks = 0;  // co-resident limit for the cooperative grid
-  if (max_blocks == 0) {
-    int per_sm = 0, sms = 0, dev = 0;
-    B200DP_CUDA_TRY(cudaGetDevice(&dev));
-    B200DP_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    B200DP_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bn_relu_pool_bwd_fused_kernel, threads, smem));
-    if (per_sm < 1) {
-      set_error("bn_relu_pool_bwd_fused: kernel does not fit on an SM");
-      return B200DP_EINVAL;
-    }
-    // two blocks per SM: leaves room for a communication kernel to stay co-resident on a side stream
-    max_blocks = sms * (per_sm < 2 ? per_sm : 2);
-  }
-  const long Q = static_cast<long>(p.B) * (p.pool ? p.H / 2 : p.H) * (p.pool ? p.W / 2 : p.W);
-  long blocks = (Q + rows_per_block - 1) / rows_per_block;
-  if (blocks > max_blocks) blocks = max_blocks;
-  if (blocks < 1) blocks = 1;
-  void* args[] = {&p};
-  B200DP_CUDA_TRY(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(bn_relu_pool_bwd_fused_kernel),
-                                              dim3(static_cast<unsigned>(blocks)), dim3(threads), args, smem,
-                                              static_cast<cudaStream_t>(s)));
   return 0;
 }
 
@@ -1491,7 +1409,7 @@ extern "C" int b200dp_bn_relu_pool_bwd_reduce_from_out(const void* out, const vo
     set_error("bn_relu_pool_bwd_reduce_from_out: unsupported shape Q=%lld C=%d", Q, C);
     return B200DP_EINVAL;
   }
-  if (bn_tma_enabled() && bn_tma_shape_ok(2, 2, C, 0))
+  if (bn_tma_shape_ok(2, 2, C, 0))
     return b200dp_bn_bwd_reduce_from_out_tma(out, dout, gamma, beta, sums, Q, C, s);
   const int threads = 256;
   const int rows_per_block = threads / (C / 8);
@@ -1612,6 +1530,34 @@ extern "C" int b200dp_sgd_momentum(float* p, const float* g, float* buf, long lo
   return 0;
 }
 
+extern "C" int b200dp_fill_zero(void* dst, long long nbytes, b200dp_stream_t s) {
+  if ((reinterpret_cast<uintptr_t>(dst) & 15) || (nbytes & 15) || nbytes < 0) {
+    set_error("fill_zero: pointer and byte count (%lld) must be multiples of 16", nbytes);
+    return B200DP_EINVAL;
+  }
+  if (nbytes == 0) return 0;
+  B200DP_CUDA_TRY(launch_pdl(fill_zero_kernel, dim3(grid_for(nbytes / 16, 256 * 4, 148 * 8)), dim3(256), 0,
+                             static_cast<cudaStream_t>(s), static_cast<uint4*>(dst), static_cast<long>(nbytes / 16)));
+  return 0;
+}
+
+extern "C" int b200dp_copy_pair(void* dst0, const void* src0, long long nbytes0, void* dst1, const void* src1,
+                                long long nbytes1, b200dp_stream_t s) {
+  const uintptr_t bits = reinterpret_cast<uintptr_t>(dst0) | reinterpret_cast<uintptr_t>(src0) |
+                         reinterpret_cast<uintptr_t>(dst1) | reinterpret_cast<uintptr_t>(src1);
+  if ((bits & 15) || (nbytes0 & 15) || (nbytes1 & 15) || nbytes0 < 0 || nbytes1 < 0) {
+    set_error("copy_pair: pointers and byte counts (%lld, %lld) must be multiples of 16", nbytes0, nbytes1);
+    return B200DP_EINVAL;
+  }
+  const long n = (nbytes0 > nbytes1 ? nbytes0 : nbytes1) / 16;
+  if (n == 0) return 0;
+  B200DP_CUDA_TRY(launch_pdl(copy_pair_kernel, dim3(grid_for(n, 256 * 2, 148 * 4)), dim3(256), 0,
+                             static_cast<cudaStream_t>(s), static_cast<uint4*>(dst0), static_cast<const uint4*>(src0),
+                             static_cast<long>(nbytes0 / 16), static_cast<uint4*>(dst1),
+                             static_cast<const uint4*>(src1), static_cast<long>(nbytes1 / 16)));
+  return 0;
+}
+
 extern "C" int b200dp_prep_conv_weights(const float* master, void* wf, void* wd, int Cout, int Cin, int taps,
                                         int kpad, b200dp_stream_t s) {
   if (kpad < taps * Cin) {
@@ -1719,209 +1665,3 @@ extern "C" int b200dp_prep_conv_weights_batched(int n, const float* const* maste
   return 0;
 }
 
-// ---------------------------------------------------------------------------
-// First layer (3 input channels) as a direct convolution on the CUDA cores.
-// K = 27 is too thin for the tensor cores (the GEMM route pads it to 64 and needs a patch-gather
-// pass); here every thread owns one output pixel x 16 channels, the 4-row input window and the
-// [27][64] weights sit in shared memory, operands are rounded to bf16 exactly like the tcgen05
-// path, BatchNorm statistics are accumulated in registers across a persistent block's tiles.
-// (ref: master/part1/model.py:13,18-23 -- the in_channels=3 Conv2d)
-// ---------------------------------------------------------------------------
-namespace b200dp {
-
-B200DP_DEVINL float round_bf16(float v) { return __bfloat162float(__float2bfloat16(v)); }
-
-__global__ void __launch_bounds__(256) conv3x3_c3_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
-                                                             const float* __restrict__ bias,
-                                                             __nv_bfloat16* __restrict__ y, float* __restrict__ stats,
-                                                             int B, int H, int W) {
-  extern __shared__ float smem_f[];
-  const int Wp = W + 2;
-  float* s_w = smem_f;                 // [27][64]
-  float* s_win = s_w + 27 * 64;        // [4][3][Wp]
-  float* s_red = s_win + 12 * Wp;      // [8 warps][2][64]
-  for (int i = threadIdx.x; i < 27 * 64; i += blockDim.x) {
-    const int k = i >> 6, co = i & 63;
-    s_w[i] = round_bf16(w[co * 27 + k]);
-  }
-  const int cg = threadIdx.x & 3;       // channels cg*16 .. +15
-  const int pl = threadIdx.x >> 2;      // pixel within the tile (2 rows x W, W <= 32)
-  const int pr = pl / W, pw = pl - pr * W;
-  float bsum[16];
-#pragma unroll
-  for (int j = 0; j < 16; ++j) bsum[j] = bias[cg * 16 + j];
-  float s1[16], s2[16];
-#pragma unroll
-  for (int j = 0; j < 16; ++j) s1[j] = s2[j] = 0.f;
-  const int tiles = B * (H / 2);
-  for (int t = blockIdx.x; t < tiles; t += gridDim.x) {
-    const int n = t / (H / 2), h0 = (t - n * (H / 2)) * 2;
-    __syncthreads();
-    for (int i = threadIdx.x; i < 12 * Wp; i += blockDim.x) {
-      const int r = i / (3 * Wp), c = (i / Wp) % 3, ww = i % Wp - 1;
-      const int hh = h0 + r - 1;
-      s_win[i] = (hh >= 0 && hh < H && ww >= 0 && ww < W)
-                     ? round_bf16(__ldg(x + ((static_cast<long>(n) * 3 + c) * H + hh) * W + ww)) : 0.f;
-    }
-    __syncthreads();
-    if (pl < 2 * W) {
-      float acc[16];
-#pragma unroll
-      for (int j = 0; j < 16; ++j) acc[j] = 0.f;
-#pragma unroll
-      for (int k = 0; k < 27; ++k) {
-        const int tap = k / 3, c = k - tap * 3;
-        const float xv = s_win[(pr + tap / 3) * 3 * Wp + c * Wp + pw + tap % 3];
-        const float4* wr = reinterpret_cast<const float4*>(s_w + k * 64 + cg * 16);
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const float4 wv = wr[q];
-          acc[4 * q] = fmaf(xv, wv.x, acc[4 * q]);
-          acc[4 * q + 1] = fmaf(xv, wv.y, acc[4 * q + 1]);
-          acc[4 * q + 2] = fmaf(xv, wv.z, acc[4 * q + 2]);
-          acc[4 * q + 3] = fmaf(xv, wv.w, acc[4 * q + 3]);
-        }
-      }
-      uint32_t packed[8];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        packed[j] = pack_bf16x2(acc[2 * j] + bsum[2 * j], acc[2 * j + 1] + bsum[2 * j + 1]);
-        const float2 r = unpack_bf16x2(packed[j]);
-        s1[2 * j] += r.x; s1[2 * j + 1] += r.y;
-        s2[2 * j] = fmaf(r.x, r.x, s2[2 * j]); s2[2 * j + 1] = fmaf(r.y, r.y, s2[2 * j + 1]);
-      }
-      uint4* dst = reinterpret_cast<uint4*>(y + ((static_cast<long>(n) * H + h0 + pr) * W + pw) * 64 + cg * 16);
-      dst[0] = make_uint4(packed[0], packed[1], packed[2], packed[3]);
-      dst[1] = make_uint4(packed[4], packed[5], packed[6], packed[7]);
-    }
-  }
-  if (stats != nullptr) {
-    // lanes that share cg (lane % 4) hold the same channels: fold the 8 pixels of the warp
-#pragma unroll
-    for (int j = 0; j < 16; ++j) {
-#pragma unroll
-      for (int o = 4; o < 32; o <<= 1) {
-        s1[j] += __shfl_xor_sync(0xffffffffu, s1[j], o);
-        s2[j] += __shfl_xor_sync(0xffffffffu, s2[j], o);
-      }
-    }
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    __syncthreads();
-    if (lane < 4) {
-#pragma unroll
-      for (int j = 0; j < 16; ++j) {
-        s_red[(warp * 2) * 64 + lane * 16 + j] = s1[j];
-        s_red[(warp * 2 + 1) * 64 + lane * 16 + j] = s2[j];
-      }
-    }
-    __syncthreads();
-    if (threadIdx.x < 128) {
-      const int which = threadIdx.x >> 6, ch = threadIdx.x & 63;
-      float tot = 0.f;
-      for (int wv = 0; wv < 8; ++wv) tot += s_red[(wv * 2 + which) * 64 + ch];
-      atomicAdd(stats + which * 64 + ch, tot);
-    }
-  }
-}
-
-// dW[co][k] += sum_p dY[p][co] * patch[p][k], k = (r*3+s)*3 + c.  256 threads = 4 pixel groups x
-// 16 groups of 4 output channels x 4 groups of 7 patch columns; 28 accumulators per thread.
-__global__ void __launch_bounds__(256) conv3x3_c3_wgrad_kernel(const __nv_bfloat16* __restrict__ dy,
-                                                               const float* __restrict__ x, float* __restrict__ dw,
-                                                               int B, int H, int W) {
-  extern __shared__ float smem_f[];
-  const int Wp = W + 2;
-  float* s_win = smem_f;                                        // [4][3][Wp]
-  __nv_bfloat16* s_dy = reinterpret_cast<__nv_bfloat16*>(s_win + 12 * Wp + ((12 * Wp) & 1));  // [2W][64]
-  const int kg = threadIdx.x & 3, cog = (threadIdx.x >> 2) & 15, pg = threadIdx.x >> 6;
-  float acc[4][7];
-#pragma unroll
-  for (int a = 0; a < 4; ++a)
-#pragma unroll
-    for (int i = 0; i < 7; ++i) acc[a][i] = 0.f;
-  int koff[7];  // window offset of patch column k relative to the pixel's (row, col)
-#pragma unroll
-  for (int i = 0; i < 7; ++i) {
-    const int k = kg * 7 + i;
-    const int tap = k / 3, c = k - tap * 3;
-    koff[i] = k < 27 ? (tap / 3) * 3 * Wp + c * Wp + tap % 3 : -1;
-  }
-  const int tiles = B * (H / 2);
-  const int npix = 2 * W;
-  for (int t = blockIdx.x; t < tiles; t += gridDim.x) {
-    const int n = t / (H / 2), h0 = (t - n * (H / 2)) * 2;
-    __syncthreads();
-    for (int i = threadIdx.x; i < 12 * Wp; i += blockDim.x) {
-      const int r = i / (3 * Wp), c = (i / Wp) % 3, ww = i % Wp - 1;
-      const int hh = h0 + r - 1;
-      s_win[i] = (hh >= 0 && hh < H && ww >= 0 && ww < W)
-                     ? round_bf16(__ldg(x + ((static_cast<long>(n) * 3 + c) * H + hh) * W + ww)) : 0.f;
-    }
-    const uint4* src = reinterpret_cast<const uint4*>(dy + (static_cast<long>(n) * H + h0) * W * 64);
-    for (int i = threadIdx.x; i < npix * 8; i += blockDim.x) reinterpret_cast<uint4*>(s_dy)[i] = src[i];
-    __syncthreads();
-    for (int p = pg; p < npix; p += 4) {
-      const int pr = p / W, pw = p - pr * W;
-      const uint2 dq = *reinterpret_cast<const uint2*>(s_dy + p * 64 + cog * 4);
-      const float2 d01 = unpack_bf16x2(dq.x), d23 = unpack_bf16x2(dq.y);
-      const float* base = s_win + pr * 3 * Wp + pw;
-#pragma unroll
-      for (int i = 0; i < 7; ++i) {
-        const float xv = koff[i] >= 0 ? base[koff[i]] : 0.f;
-        acc[0][i] = fmaf(d01.x, xv, acc[0][i]);
-        acc[1][i] = fmaf(d01.y, xv, acc[1][i]);
-        acc[2][i] = fmaf(d23.x, xv, acc[2][i]);
-        acc[3][i] = fmaf(d23.y, xv, acc[3][i]);
-      }
-    }
-  }
-  // combine the 4 pixel groups through shared memory, then one atomic per (co, k) per block
-  __syncthreads();
-  float* s_acc = smem_f;  // reuse: [4 pg][64 co][28]
-#pragma unroll
-  for (int a = 0; a < 4; ++a)
-#pragma unroll
-    for (int i = 0; i < 7; ++i) s_acc[(pg * 64 + cog * 4 + a) * 28 + kg * 7 + i] = acc[a][i];
-  __syncthreads();
-  for (int i = threadIdx.x; i < 64 * 27; i += blockDim.x) {
-    const int co = i / 27, k = i - co * 27;
-    const float v = s_acc[(0 * 64 + co) * 28 + k] + s_acc[(1 * 64 + co) * 28 + k] + s_acc[(2 * 64 + co) * 28 + k] +
-                    s_acc[(3 * 64 + co) * 28 + k];
-    atomicAdd(dw + i, v);
-  }
-}
-
-}  // namespace b200dp
-
-extern "C" int b200dp_conv3x3_c3_fwd(const float* x_nchw, const float* w, const float* bias, void* y, float* stats,
-                                     int B, int H, int W, b200dp_stream_t s) {
-  if (W > 32 || (H & 1) || W < 1) {
-    set_error("conv3x3_c3_fwd: needs even H and W <= 32 (got H=%d W=%d)", H, W);
-    return B200DP_EINVAL;
-  }
-  const size_t smem = (27 * 64 + 12 * (W + 2) + 8 * 2 * 64) * sizeof(float);
-  const int tiles = B * (H / 2);
-  const int blocks = tiles < 148 * 4 ? tiles : 148 * 4;
-  conv3x3_c3_fwd_kernel<<<blocks, 256, smem, static_cast<cudaStream_t>(s)>>>(
-      x_nchw, w, bias, static_cast<__nv_bfloat16*>(y), stats, B, H, W);
-  B200DP_CUDA_TRY(cudaGetLastError());
-  return 0;
-}
-
-extern "C" int b200dp_conv3x3_c3_wgrad(const void* dy, const float* x_nchw, float* dw, int B, int H, int W,
-                                       b200dp_stream_t s) {
-  if (W > 32 || (H & 1) || W < 1) {
-    set_error("conv3x3_c3_wgrad: needs even H and W <= 32 (got H=%d W=%d)", H, W);
-    return B200DP_EINVAL;
-  }
-  size_t win_floats = 12 * (W + 2) + ((12 * (W + 2)) & 1);
-  size_t smem = win_floats * sizeof(float) + 2 * W * 64 * sizeof(__nv_bfloat16);
-  const size_t red = 4 * 64 * 28 * sizeof(float);
-  if (smem < red) smem = red;
-  const int tiles = B * (H / 2);
-  const int blocks = tiles < 148 * 2 ? tiles : 148 * 2;
-  conv3x3_c3_wgrad_kernel<<<blocks, 256, smem, static_cast<cudaStream_t>(s)>>>(
-      static_cast<const __nv_bfloat16*>(dy), x_nchw, dw, B, H, W);
-  B200DP_CUDA_TRY(cudaGetLastError());
-  return 0;
-}

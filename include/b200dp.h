@@ -84,13 +84,6 @@ int b200dp_conv_dgrad_bn_reduce(const void* act, const void* wgt, void* out, flo
                                 const float* gamma, const float* beta, float* sums, int B, int H, int W, int Cin,
                                 int Cout, int taps, int block_n, int split_k, int cta_pair, b200dp_stream_t stream);
 
-/* Persistent variant of b200dp_conv_igemm (experimental, never run in round 1): one CTA per SM walks the
- * output tiles, the accumulator is double-buffered in TMEM, so a tile's epilogue overlaps the next tile's
- * loads and MMAs.  block_n in {64,128,256} (0 = choose); no split-K. */
-int b200dp_conv_igemm_persist(const void* act, const void* wgt, const float* bias, void* out, float* stats,
-                              int B, int H, int W, int Cin, int Cout, int taps, int block_n,
-                              b200dp_stream_t stream);
-
 /* dW[Cout][taps][cin_valid] (fp32) += sum over pixels dY[p][Cout] * X[p + tap][Cin].
  * dy: bf16 [B,H,W,Cout]; x: bf16 [B,H,W,Cin].  Both operands are consumed
  * MN-major straight from their NHWC layout.  split_k = 0 chooses a split that
@@ -128,16 +121,6 @@ int b200dp_conv_wgrad_tiled(const void* dy, const void* x, float* dw, int B, int
  * K=64 GEMM for b200dp_conv_igemm(taps=1).  (ref: master/part1/model.py:13,18) */
 int b200dp_im2col3x3_c3(const float* x_nchw, void* a0, int B, int H, int W, b200dp_stream_t stream);
 
-/* First conv (3 input channels) as a direct convolution on the CUDA cores -- K = 27 is too thin
- * for tcgen05.  y[B,H,W,64] (bf16) = conv3x3(x fp32 NCHW, w fp32 [64][27], k = (r*3+s)*3+c) + bias,
- * operands rounded to bf16 like the tensor-core path; optional fused BatchNorm statistics
- * (stats[2][64], zero on entry).  H even, W <= 32.  (ref: master/part1/model.py:13,18-23) */
-int b200dp_conv3x3_c3_fwd(const float* x_nchw, const float* w, const float* bias, void* y, float* stats, int B,
-                          int H, int W, b200dp_stream_t stream);
-/* dw[64][27] (fp32) += sum_p dy[p][64] * patch(x)[p][27]; dw must be zero (or hold the value to add to). */
-int b200dp_conv3x3_c3_wgrad(const void* dy, const float* x_nchw, float* dw, int B, int H, int W,
-                            b200dp_stream_t stream);
-
 /* stats[0..C) += sum_p y[p][c], stats[C..2C) += sum_p y[p][c]^2 (stats zero on entry). */
 int b200dp_bn_stats(const void* y, float* stats, long long P, int C, b200dp_stream_t stream);
 
@@ -165,11 +148,6 @@ int b200dp_bn_relu_pool_bwd_apply(const void* y, const void* dout, const float* 
                                   const float* gamma, const float* beta, const float* sums, void* dy,
                                   float* dgamma, float* dbeta, int B, int H, int W, int C, int pool,
                                   b200dp_stream_t stream);
-
-/* Both passes in one cooperative launch (grid-wide barrier in between); same contract as the pair. */
-int b200dp_bn_relu_pool_bwd_fused(const void* y, const void* dout, const float* mean, const float* invstd,
-                                  const float* gamma, const float* beta, float* sums, void* dy, float* dgamma,
-                                  float* dbeta, int B, int H, int W, int C, int pool, b200dp_stream_t stream);
 
 /* BatchNorm + ReLU (+ pool) backward that allocates nothing and needs no scratch from the caller.
  * This entry point has no counterpart in the reference.  It is for hosts that cannot call
@@ -238,6 +216,15 @@ int b200dp_sgd_momentum(float* p, const float* g, float* buf, long long n, float
 
 /* fp32 master [Cout][taps][Cin] -> bf16 Wf [Cout][kpad] (zero padded) and, if wd != NULL,
  * bf16 Wd [Cin][taps*Cout] with the taps flipped (the dgrad operand). */
+/* Clear nbytes (multiple of 16) at dst (16-byte aligned): the per-step clear of the flat gradient buffer and
+ * of the statistics region, as a kernel of this library so that a step launches no framework fill
+ * (ref: optimizer.zero_grad() at master/part1/part1.py:34). */
+int b200dp_fill_zero(void* dst, long long nbytes, b200dp_stream_t stream);
+/* Copy two device ranges (multiples of 16 bytes; either may be empty) in one launch: a step's staged images
+ * and labels into the static buffers of the captured step (ref: data.to(device) at master/part1/part1.py:32). */
+int b200dp_copy_pair(void* dst0, const void* src0, long long nbytes0, void* dst1, const void* src1,
+                     long long nbytes1, b200dp_stream_t stream);
+
 int b200dp_prep_conv_weights(const float* master, void* wf, void* wd, int Cout, int Cin, int taps, int kpad,
                              b200dp_stream_t stream);
 /* The same for n layers in ONE launch (tiled, coalesced, transposed through shared memory);

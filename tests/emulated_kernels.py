@@ -28,6 +28,16 @@ class EmulatedKernels:
     def _log(self, name):
         self.calls.append(name)
 
+    # ---- fills / copies ---------------------------------------------------------------------------
+    def fill_zero(self, t):
+        self._log("fill_zero")
+        return t.zero_()
+
+    def copy_pair(self, dst0, src0, dst1, src1):
+        self._log("copy_pair")
+        dst0.view(-1)[: src0.numel()].copy_(src0.view(-1))
+        dst1.view(-1)[: src1.numel()].copy_(src1.view(-1))
+
     # ---- layer 0 patch gather --------------------------------------------------------------------
     def im2col3x3_c3(self, x_nchw, a0):
         self._log("im2col3x3_c3")
@@ -94,7 +104,7 @@ class EmulatedKernels:
             a = F.max_pool2d(a.permute(0, 3, 1, 2), 2).permute(0, 2, 3, 1)
         return _put(out, a)
 
-    def bn_relu_pool_bwd(self, y, dout, mean, invstd, gamma, beta, sums, dy, dgamma, dbeta, pool, fused=None, out=None,
+    def bn_relu_pool_bwd(self, y, dout, mean, invstd, gamma, beta, sums, dy, dgamma, dbeta, pool, out=None,
                          skip_reduce=False):
         self._log("bn_relu_pool_bwd")
         B, H, W, C = y.shape

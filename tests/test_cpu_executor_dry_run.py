@@ -3,9 +3,8 @@
 
 The kernel wrappers (ops.native) and the CUDA stream / event API are replaced by recorders; tensors live on
 the CPU.  What is checked is what cannot be left to a GPU box at the end of a round: that the default step
-still issues the kernel sequence the measured build issued, and that each experimental toggle swaps exactly
-the calls it claims to swap -- a NameError or a wrong keyword in `backward()` would otherwise only show up
-on the hardware.
+still issues the kernel sequence the measured build issued, and that each option swaps exactly the calls it
+claims to swap -- a NameError or a wrong keyword in `backward()` would otherwise only show up on the hardware.
 """
 import contextlib
 import types
@@ -71,8 +70,6 @@ def executor(monkeypatch):
     monkeypatch.setattr(torch.cuda, "current_stream", lambda *a: FakeStream())
     monkeypatch.setattr(torch.cuda, "stream", lambda s: contextlib.nullcontext())
     monkeypatch.setattr(torch.cuda, "synchronize", lambda *a: None)
-    for flag in ("DGRAD_BN_REDUCE", "HEAD_FUSED", "ZERO_GRADS_EARLY"):
-        monkeypatch.setattr(native_vgg, flag, False)
 
     def make(arch="VGG11", batch=8):
         torch.manual_seed(0)
@@ -91,7 +88,9 @@ def _step(nv, batch=8):
     nv.backward()
 
 
-FWD = ["im2col3x3_c3"] + ["conv_igemm", "bn_relu_pool_fwd"] * 8 + ["linear_fwd"]
+FWD = ["fill_zero", "im2col3x3_c3"] + ["conv_igemm", "bn_relu_pool_fwd"] * 8 + ["linear_fwd"]
+EVAL_FWD = FWD[1:]          # the statistics region is only cleared for a training forward
+HEAD = ["cross_entropy", "fill_zero", "linear_bwd"]      # loss, gradient-buffer clear, classifier backward
 
 
 def test_default_step_issues_the_measured_kernel_sequence(executor):
@@ -99,25 +98,27 @@ def test_default_step_issues_the_measured_kernel_sequence(executor):
     _step(nv)
     names = rec.names()
     assert names[: len(FWD)] == FWD
-    assert names[len(FWD): len(FWD) + 2] == ["cross_entropy", "linear_bwd"]
-    bwd = names[len(FWD) + 2:]
-    # per block, deepest first: BN backward, data gradient (not for block 0), weight gradient
+    assert names[len(FWD): len(FWD) + 3] == HEAD
+    bwd = rec.calls[len(FWD) + 3:]
+    # per block, deepest first: BN backward, data gradient fused with the BN reduction of the block below (not
+    # for block 0), weight gradient
     expect = []
     for i in range(7, -1, -1):
-        expect += ["bn_relu_pool_bwd"] + (["conv_igemm"] if i > 0 else []) + ["conv_wgrad"]
-    assert bwd == expect
-    assert all(not kw.get("skip_reduce") for n, kw in rec.calls if n == "bn_relu_pool_bwd")
+        expect += ["bn_relu_pool_bwd"] + (["conv_dgrad_bn_reduce"] if i > 0 else []) + ["conv_wgrad"]
+    assert [n for n, _ in bwd] == expect
+    skips = [kw["skip_reduce"] for n, kw in bwd if n == "bn_relu_pool_bwd"]
+    assert skips == [False] + [True] * 7                          # only the deepest block reduces on its own
     # a second step behaves the same (no sticky state)
     rec.calls.clear()
     _step(nv)
-    assert rec.names()[len(FWD):] == ["cross_entropy", "linear_bwd"] + expect
+    assert rec.names()[len(FWD):] == HEAD + expect
 
 
 def test_eval_forward_and_loss_do_not_touch_the_training_only_kernels(executor):
     model, nv, rec = executor()
     nv.forward(torch.randn(8, 3, 32, 32), training=False)
     nv.loss_fwd_bwd(torch.randint(0, 10, (8,)), need_grad=False)
-    assert rec.names() == FWD + ["cross_entropy"]
+    assert rec.names() == EVAL_FWD + ["cross_entropy"]
 
 
 def test_bucket_ready_callbacks_fire_once_per_bucket_in_gradient_order(executor):
@@ -134,15 +135,16 @@ def test_bucket_ready_callbacks_fire_once_per_bucket_in_gradient_order(executor)
     assert fired == [0, 1, 2]
 
 
-def test_fused_head_toggle_replaces_exactly_the_three_head_kernels(executor):
+def test_fused_head_replaces_exactly_the_three_head_kernels(executor):
+    """What the engine's training step runs (it sets ``defer_head``): one head_fwd_bwd launch."""
     model, nv, rec = executor()
     nv.defer_head = True
     _step(nv)
     names = rec.names()
     assert names[: len(FWD) - 1] == FWD[:-1]                      # no linear_fwd at the end of forward
-    assert names[len(FWD) - 1] == "head_fwd_bwd"
+    assert names[len(FWD) - 1: len(FWD) + 1] == ["fill_zero", "head_fwd_bwd"]
     assert "linear_fwd" not in names and "cross_entropy" not in names and "linear_bwd" not in names
-    assert names[len(FWD)] == "bn_relu_pool_bwd"
+    assert names[len(FWD) + 1] == "bn_relu_pool_bwd"
     # an external dlogits (autograd path) still runs the fc backward, and eval still computes logits
     rec.calls.clear()
     nv.forward(torch.randn(8, 3, 32, 32), training=True)
@@ -151,24 +153,6 @@ def test_fused_head_toggle_replaces_exactly_the_three_head_kernels(executor):
     rec.calls.clear()
     nv.forward(torch.randn(8, 3, 32, 32), training=False)
     assert rec.names()[-1] == "linear_fwd"
-
-
-def test_dgrad_bn_reduce_toggle_moves_the_reduction_into_the_dgrad(executor, monkeypatch):
-    model, nv, rec = executor()
-    monkeypatch.setattr(native_vgg, "DGRAD_BN_REDUCE", True)
-    _step(nv)
-    bwd = rec.calls[len(FWD) + 2:]
-    assert [n for n, _ in bwd].count("conv_dgrad_bn_reduce") == 7 and "conv_igemm" not in [n for n, _ in bwd]
-    skips = [kw["skip_reduce"] for n, kw in bwd if n == "bn_relu_pool_bwd"]
-    assert skips == [False] + [True] * 7                          # only the deepest block reduces on its own
-    # the persistent dgrad has no bn-reduce flavour: that layer falls back to the two-kernel path
-    nv.blocks[4].dgrad_pair = 2
-    rec.calls.clear()
-    _step(nv)
-    bwd = rec.calls[len(FWD) + 2:]
-    names = [n for n, _ in bwd]
-    assert names.count("conv_dgrad_bn_reduce") == 6 and names.count("conv_igemm") == 1
-    assert [kw["skip_reduce"] for n, kw in bwd if n == "bn_relu_pool_bwd"] == [False, True, True, True, False, True, True, True]
 
 
 def test_wgrad_push_configuration_reroutes_the_configured_blocks_only(executor):
@@ -186,7 +170,7 @@ def test_deeper_architectures_walk_the_same_executor(executor, arch, blocks):
     _step(nv, batch=4)
     names = rec.names()
     assert names.count("bn_relu_pool_fwd") == blocks and names.count("conv_wgrad") == blocks
-    assert names.count("conv_igemm") == blocks + (blocks - 1)     # forward convs + data gradients
+    assert names.count("conv_igemm") == blocks and names.count("conv_dgrad_bn_reduce") == blocks - 1
 
 
 def test_engine_step_body_runs_end_to_end_in_dry_run(executor, monkeypatch):
@@ -198,6 +182,7 @@ def test_engine_step_body_runs_end_to_end_in_dry_run(executor, monkeypatch):
     from cs744_pytorch_distributed_tutorial_b200.parallel import sync_native
     model, nv0, rec = executor()          # installs the recorders; this executor instance itself is not used
     monkeypatch.setattr(sync_native, "K", rec)
+    monkeypatch.setattr(engine, "K", rec)
     monkeypatch.setattr(torch.cuda, "set_device", lambda d: None)
     real_zeros = torch.zeros
     monkeypatch.setattr(torch, "zeros", lambda *a, **kw: real_zeros(*a, **{k: v for k, v in kw.items() if k != "pin_memory"}))
@@ -210,7 +195,8 @@ def test_engine_step_body_runs_end_to_end_in_dry_run(executor, monkeypatch):
     loss = be.train_step(torch.randn(8, 3, 32, 32), torch.randint(0, 10, (8,)))
     names = rec.names()
     assert loss is be.native.loss and be.steps_done == 1
-    assert names[: len(FWD)] == FWD and names.count("conv_wgrad") == 8
+    assert names[0] == "copy_pair"                         # staged batch -> the step's static input buffers
+    assert names[1: len(FWD)] == FWD[:-1] and names.count("head_fwd_bwd") == 1 and names.count("conv_wgrad") == 8
     assert names.count("sgd_momentum") == 2 and names.count("prep_conv_weights_batched") == 2   # two-phase optimizer
     assert be.input_event() is not None
     # ragged last batch: same kernels, eager
@@ -278,13 +264,13 @@ def test_engine_part3_two_rank_path_in_dry_run(executor, monkeypatch):
     monkeypatch.setattr(comm_mod, "Communicator", FakeCommunicator)
     monkeypatch.setattr(sync_native, "BucketReducer", FakeReducer)
     monkeypatch.setattr(sync_native, "K", rec)
+    monkeypatch.setattr(engine, "K", rec)
     monkeypatch.setattr(torch.cuda, "set_device", lambda d: None)
     real_zeros = torch.zeros
     monkeypatch.setattr(torch, "zeros", lambda *a, **kw: real_zeros(*a, **{k: v for k, v in kw.items() if k != "pin_memory"}))
     orig_enable = VGG.enable_native
     monkeypatch.setattr(VGG, "enable_native", lambda self, max_batch, heap=None, **kw: orig_enable(self, max_batch, heap=heap, autotune=False, **kw))
-    for v in ("B200DP_PART3_PREP_OVERLAP", "B200DP_WGRAD_PUSH"):
-        monkeypatch.delenv(v, raising=False)
+    monkeypatch.delenv("B200DP_WGRAD_PUSH", raising=False)
 
     cfg = TrainConfig(mode="part3", device="cpu", num_nodes=2, rank=1, per_rank_batch=8, eval=False, cuda_graph=False)
     log.clear()
@@ -296,7 +282,7 @@ def test_engine_part3_two_rank_path_in_dry_run(executor, monkeypatch):
     log.clear()
     be.train_step(torch.randn(8, 3, 32, 32), torch.randint(0, 10, (8,)))
     names = [n for n, _ in log]
-    i_fwd_end = names.index("linear_fwd")
+    i_fwd_end = max(i for i, n in enumerate(names) if n == "bn_relu_pool_fwd")
     assert names[i_fwd_end + 1] == "comm.broadcast"                                   # BatchNorm state, after forward
     ready = [kw["k"] for n, kw in log if n == "reducer.bucket_ready"]
     assert ready == list(range(8))

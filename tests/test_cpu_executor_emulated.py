@@ -47,7 +47,9 @@ class _St:
 @pytest.fixture
 def emu(monkeypatch):
     k = EmulatedKernels()
+    from cs744_pytorch_distributed_tutorial_b200 import engine
     monkeypatch.setattr(native_vgg, "K", k)
+    monkeypatch.setattr(engine, "K", k)
     monkeypatch.setattr(native_vgg, "_DRY_RUN", True)
     monkeypatch.setattr(native_vgg, "_ACT_DTYPE", torch.float32)
     monkeypatch.setattr(torch.cuda, "Stream", _St)
@@ -55,8 +57,6 @@ def emu(monkeypatch):
     monkeypatch.setattr(torch.cuda, "current_stream", lambda *a: _St())
     monkeypatch.setattr(torch.cuda, "stream", lambda s: contextlib.nullcontext())
     monkeypatch.setattr(torch.cuda, "synchronize", lambda *a: None)
-    for flag in ("DGRAD_BN_REDUCE", "HEAD_FUSED", "ZERO_GRADS_EARLY"):
-        monkeypatch.setattr(native_vgg, flag, False)
     return k
 
 
@@ -69,11 +69,10 @@ def _reference(model, x, y):
 
 
 def _same_as_default(nv, x, y, monkeypatch, tol=2e-5):
-    """Re-run the step on the default flow (all toggles off) and require the same gradients: the toggles
-    re-route kernels, they must not change the maths beyond summation order."""
+    """Re-run the step on the plain flow (three-kernel head, no push) and require the same gradients: the
+    options re-route kernels, they must not change the maths beyond summation order."""
     got = nv.flat_grads.clone()
     loss = float(nv.loss)
-    monkeypatch.setattr(native_vgg, "DGRAD_BN_REDUCE", False)
     nv.defer_head, nv.wgrad_push = False, None
     _step(nv, x, y)
     scale = nv.flat_grads.abs().max().item()
@@ -123,19 +122,12 @@ def _step(nv, x, y):
 
 
 def test_default_flow_matches_autograd(emu):
+    """Including the data gradient that also reduces the BatchNorm backward of the block below."""
     model, nv, ref, ref_logits, ref_loss, x, y = _build()
-    _step(nv, x, y)
-    _compare(model, nv, ref, ref_logits, ref_loss)
-    assert nv.grad_views_intact()
-
-
-def test_fused_dgrad_bn_reduction_flow_matches_autograd(emu, monkeypatch):
-    monkeypatch.setattr(native_vgg, "DGRAD_BN_REDUCE", True)
-    model, nv, ref, ref_logits, ref_loss, x, y = _build(seed=1)
     _step(nv, x, y)
     assert emu.calls.count("conv_dgrad_bn_reduce") == 7
     _compare(model, nv, ref, ref_logits, ref_loss)
-    _same_as_default(nv, x, y, monkeypatch)
+    assert nv.grad_views_intact()
 
 
 def test_fused_head_flow_matches_autograd(emu, monkeypatch):
@@ -148,10 +140,9 @@ def test_fused_head_flow_matches_autograd(emu, monkeypatch):
     _same_as_default(nv, x, y, monkeypatch)
 
 
-def test_all_toggles_together_and_two_steps(emu, monkeypatch):
+def test_all_options_together_and_two_steps(emu, monkeypatch):
     """Second step after a parameter change: buffers that must be cleared per step (statistics, sums,
-    gradients) really are, with every experimental path switched on at once."""
-    monkeypatch.setattr(native_vgg, "DGRAD_BN_REDUCE", True)
+    gradients) really are, with the fused head and the push flavour of the weight gradient switched on."""
     model, nv, ref, ref_logits, ref_loss, x, y = _build(seed=3)
     nv.defer_head = True
     nv.wgrad_push = {i: dict(counters=None, world=2, rank=0, peer_stage=None, flat_off=0, own_start=0, own_len=0,
@@ -302,24 +293,6 @@ def test_trainer_fit_evaluate_checkpoint_resume_on_the_native_backend(emu, monke
         nv2.refresh_shadows()
         assert all(torch.equal(b.wf, w) for b, w in zip(nv2.blocks, got))
         tr2.close()
-
-
-def test_per_layer_gradient_clearing_gives_the_same_gradients(emu, monkeypatch):
-    """B200DP_ZERO_PER_LAYER: no whole-buffer fill; three steps in a row must not accumulate anything
-    from the step before, with and without the fused head."""
-    monkeypatch.setattr(native_vgg, "ZERO_PER_LAYER", True)
-    for defer in (False, True):
-        model, nv, ref, ref_logits, ref_loss, x, y = _build(seed=12)
-        nv.defer_head = defer
-        for _ in range(3):
-            _step(nv, x, y)
-        _compare(model, nv, ref, ref_logits, ref_loss, buffers=False)   # (running statistics moved three times)
-        got = nv.flat_grads.clone()
-        monkeypatch.setattr(native_vgg, "ZERO_PER_LAYER", False)
-        nv.defer_head = False
-        _step(nv, x, y)
-        assert (got - nv.flat_grads).abs().max().item() <= 2e-5 * nv.flat_grads.abs().max().item()
-        monkeypatch.setattr(native_vgg, "ZERO_PER_LAYER", True)
 
 
 def test_autograd_bridge_drives_the_native_backward(emu):

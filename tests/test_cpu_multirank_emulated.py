@@ -74,10 +74,7 @@ def emu(monkeypatch):
     monkeypatch.setattr(torch.cuda, "current_stream", lambda *a: _St())
     monkeypatch.setattr(torch.cuda, "stream", lambda s: contextlib.nullcontext())
     monkeypatch.setattr(torch.cuda, "synchronize", lambda *a: None)
-    for flag in ("DGRAD_BN_REDUCE", "HEAD_FUSED", "ZERO_GRADS_EARLY", "ZERO_PER_LAYER"):
-        monkeypatch.setattr(native_vgg, flag, False)
-    for v in ("B200DP_PART3_PREP_OVERLAP", "B200DP_WGRAD_PUSH"):
-        monkeypatch.delenv(v, raising=False)
+    monkeypatch.delenv("B200DP_WGRAD_PUSH", raising=False)
     return k
 
 
@@ -129,10 +126,6 @@ def _run(emu, world, batches, bucket_plan="layer", mode="part3", fuse=True):
             fabric.run_collectives()
         for r in range(world):
             nv, s = fabric.execs[r], fabric.syncs[r]
-            if getattr(s, "_prep_overlap", False):
-                # on the GPU this re-layout is queued on the reducer stream BEHIND the buckets; the fabric runs
-                # the collectives late, so the stream order is restored by running it again here
-                s._prep_hi()
             s.sync_and_step()
             if not s.handles_shadows:
                 nv.refresh_shadows()
@@ -201,14 +194,6 @@ def test_wgrad_push_path_gives_the_same_parameters_as_the_allreduce(emu, monkeyp
     assert torch.isfinite(got).all(), "a staged float4 was read that no rank had written"
     assert (got - want).abs().max().item() <= 1e-5 * want.abs().max().item()
     _check_against_reference(pushed, _reference(world, batches))
-
-
-def test_prep_overlap_path_keeps_operand_copies_current(emu, monkeypatch):
-    monkeypatch.setenv("B200DP_PART3_PREP_OVERLAP", "1")
-    batches = _batches(2, steps=2, B=2)
-    fabric = _run(emu, 2, batches)
-    assert all(s._prep_overlap and s.handles_shadows for s in fabric.syncs)
-    _check_against_reference(fabric, _reference(2, batches))
 
 
 @pytest.mark.parametrize("mode,fuse", [("part2a", True), ("part2a_extra", True), ("part2b", True), ("part2b", False),

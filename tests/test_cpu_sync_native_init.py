@@ -62,7 +62,7 @@ def fake_native():
     nv = types.SimpleNamespace(layout=layout, device=torch.device("cpu"), on_bucket_ready=None, wgrad_push=None)
     nv.blocks = []
     for i, s in enumerate(model.block_specs()):
-        nv.blocks.append(types.SimpleNamespace(spec=s, first=(i == 0), direct=False, w_master=None, wf=None, wd=None,
+        nv.blocks.append(types.SimpleNamespace(spec=s, first=(i == 0), w_master=None, wf=None, wd=None,
                                                taps=1 if i == 0 else 9, kin=64 if i == 0 else s.cin))
     nv.flat_grads = nv.flat_params = nv.flat_momentum = torch.zeros(4)
 
@@ -83,8 +83,7 @@ def fake_native():
 def _stubs(monkeypatch):
     monkeypatch.setattr(sync_native, "BucketReducer", FakeReducer)
     monkeypatch.setattr(sync_native.K, "BatchedWeightPrep", lambda specs: (lambda: None))
-    for v in ("B200DP_PART3_PREP_OVERLAP", "B200DP_WGRAD_PUSH", "B200DP_LAZY_EXIT_BARRIER"):
-        monkeypatch.delenv(v, raising=False)
+    monkeypatch.delenv("B200DP_WGRAD_PUSH", raising=False)
 
 
 def _make(world, **kw):
@@ -97,7 +96,7 @@ def _make(world, **kw):
 def test_default_part3_strategy_constructs_and_hands_buckets_to_the_reducer():
     nv, s = _make(2, bucket_plan="layer", blocks=32)
     assert len(s.buckets) == 8 and s.reducer.kw["blocks"] == 32
-    assert not s._prep_overlap and not s._wgrad_push and not s.handles_shadows
+    assert not s._wgrad_push and not s.handles_shadows
     assert nv.wgrad_push is None and s.reducer.staged is None
     nv.on_bucket_ready(3)
     assert s.reducer.ready == [3]
@@ -106,16 +105,6 @@ def test_default_part3_strategy_constructs_and_hands_buckets_to_the_reducer():
     assert nv.on_bucket_ready is None
     for plan in ("ddp", "single", "cap:12"):
         _make(4, bucket_plan=plan)
-
-
-def test_prep_overlap_toggle_sets_up_the_two_phase_split(monkeypatch):
-    monkeypatch.setenv("B200DP_PART3_PREP_OVERLAP", "1")
-    nv, s = _make(2)
-    assert s._prep_overlap and s.handles_shadows and s.first_block == 3
-    # buckets 0..split cover exactly the blocks >= first_block
-    covered = sorted(i for k in range(s.split_bucket + 1) for i in nv.blocks_of_bucket(k))
-    assert covered == list(range(s.first_block, len(nv.blocks)))
-    assert nv.on_bucket_ready == s._bucket_ready
 
 
 @pytest.mark.parametrize("world", [2, 4, 8])
@@ -169,7 +158,7 @@ def test_local_sgd_two_phase_split_covers_all_parameters():
     nv = fake_native()
     nv._wgrad_stream = None
     s = sync_native.LocalSGD(nv, None, lr=0.1, momentum=0.9, weight_decay=1e-4)
-    if s.overlap == 2:
+    if s.overlap:
         assert 0 < s.split_end < nv.layout.total and s.handles_shadows
         assert s.split_end == s.buckets[s.split_bucket].end
         big = sum(b.end - b.start for b in s.buckets[: s.split_bucket + 1])
@@ -184,12 +173,3 @@ def test_sync_impl_option_selects_the_allreduce_kernel():
         assert type(s).__name__ == "AllReduceSync" and s.algo == code
     with pytest.raises(ValueError):
         TrainConfig(mode="part2b", num_nodes=2, rank=0, sync_impl="ring")
-
-
-def test_lazy_exit_barrier_toggle_is_not_combined_with_the_relayout_behind_the_buckets(monkeypatch):
-    monkeypatch.setenv("B200DP_LAZY_EXIT_BARRIER", "1")
-    nv, s = _make(4)
-    assert s._lazy_exit and s.reducer.lazy_exit is True
-    monkeypatch.setenv("B200DP_PART3_PREP_OVERLAP", "1")
-    nv, s = _make(4)
-    assert s._prep_overlap and not s._lazy_exit and not hasattr(s.reducer, "lazy_exit")

@@ -85,6 +85,12 @@ def _stubs(monkeypatch):
     monkeypatch.setattr(sync_native.K, "BatchedWeightPrep", lambda specs: (lambda: None))
     monkeypatch.delenv("B200DP_WGRAD_PUSH", raising=False)
 
+    class _Fake:                      # LocalSGD forks its first optimizer phase onto a stream of its own
+        def __init__(self, *a, **kw):
+            pass
+    monkeypatch.setattr(torch.cuda, "Stream", _Fake)
+    monkeypatch.setattr(torch.cuda, "Event", _Fake)
+
 
 def _make(world, **kw):
     nv = fake_native()

@@ -421,6 +421,12 @@ class NativeVGG:
     def blocks_of_bucket(self, k: int) -> List[int]:
         return [i for i, ks in self._bucket_of_block.items() if k in ks]
 
+    @staticmethod
+    def _pair_ok(pair: bool, B: int, hw: int) -> bool:
+        """The CTA-pair kernels need an even number of 128-pixel tiles: a ragged last batch (the tile shapes
+        were tuned at the full batch) falls back to the one-CTA kernel with the same N tile."""
+        return bool(pair) and ((B * hw * hw + 127) // 128) % 2 == 0
+
     # ------------------------------------------------------------------ forward
     def forward(self, x: torch.Tensor, training: bool = True) -> torch.Tensor:
         """x: fp32 NCHW [B,3,32,32] on the device.  Returns the logits workspace view [B,10]."""
@@ -438,7 +444,7 @@ class NativeVGG:
             if b.first:
                 K.im2col3x3_c3(x.contiguous(), x_in)
             K.conv_igemm(x_in, b.wf, b.bias, y, stats=b.stats if fused else None, taps=b.taps,
-                         block_n=b.fwd_block_n, split_k=b.fwd_split_k, cta_pair=b.fwd_pair,
+                         block_n=b.fwd_block_n, split_k=b.fwd_split_k, cta_pair=self._pair_ok(b.fwd_pair, B, s.hw),
                          workspace=self.splitk_ws)
             if training and not fused:
                 K.bn_stats(y, b.stats)
@@ -509,8 +515,8 @@ class NativeVGG:
                 # which then skips its own reduction pass
                 prev = self.blocks[i - 1]
                 K.conv_dgrad_bn_reduce(b.dy[:B], b.wd, prev.dout[:B], prev.out[:B], prev.gamma, prev.beta, prev.sums,
-                                       block_n=b.dgrad_block_n, split_k=b.dgrad_split_k, cta_pair=b.dgrad_pair,
-                                       workspace=self.splitk_ws)
+                                       block_n=b.dgrad_block_n, split_k=b.dgrad_split_k,
+                                       cta_pair=self._pair_ok(b.dgrad_pair, B, s.hw), workspace=self.splitk_ws)
                 reduced = True
             self._dgrad_done[i].record(main)   # after this the layer's bf16 weight copies may be rewritten
             if side is not None:

@@ -11,8 +11,10 @@ What is the reference's and what is harness:
     serves synthetic CIFAR-shaped batches and brackets exactly K iterations with CUDA events.
   * parameterisation applied IN MEMORY at load time (files on disk stay byte-identical, checked
     against the install manifest): the module global ``device`` -> "cuda"; for part2a / part2a_extra
-    / part2b the hard-coded world size 4 (``[0, 1, 2, 3]``, ``range(4)``, ``/ 4``, peers 1..3) ->
-    the actual world size.  part3 needs no source parameterisation.
+    / part2b the hard-coded world size 4 (``[0, 1, 2, 3]``, ``range(4)``, ``/ 4``) -> the actual world size;
+    for part2a_extra at a world size other than 4 the master's hand-unrolled peers 1, 2, 3 become a loop over
+    ``range(1, world)`` with the same statements in the same order.  At world size 4
+    every script runs byte-identical.  part3 needs no source parameterisation.
 """
 from __future__ import annotations
 
@@ -66,8 +68,26 @@ def _parameterise_world(src: str, world: int, script: str) -> str:
     src = src.replace("dist.new_group([0, 1, 2, 3])", f"dist.new_group(list(range({world})))")
     src = src.replace("range(4)", f"range({world})")
     src = re.sub(r"/ 4\b", f"/ {world}", src)
-    if script == "part2a_extra.py":
-        raise NotImplementedError("part2a_extra unrolls peers 1,2,3 by hand; only world_size 4 runs unmodified")
+    if script == "part2a_extra.py" and "grad_1 = torch.zeros_like(p.grad)" in src:
+        # the master unrolls peers 1, 2, 3 by hand: the same statements as a loop over range(1, world), in the
+        # same order (blocking irecv per peer, left-to-right sum starting from the local gradient, one true
+        # division, blocking isend per peer) -- SURVEY.md 6.3-4.  The slave script has no world-size literal.
+        a = src.index("            grad_1 = torch.zeros_like(p.grad)")
+        b = src.index("        optimizer.step()", a)
+        body = (
+            f"            grads = [torch.zeros_like(p.grad) for _ in range({world} - 1)]\n"
+            f"            for peer in range(1, {world}):\n"
+            "                req = dist.irecv(tensor=grads[peer - 1], src=peer)\n"
+            "                req.wait()\n"
+            "            grad_mean = p.grad\n"
+            "            for g in grads:\n"
+            "                grad_mean = grad_mean + g\n"
+            f"            grad_mean = grad_mean / {world}\n"
+            "            p.grad = grad_mean\n"
+            f"            for peer in range(1, {world}):\n"
+            "                req = dist.isend(tensor=grad_mean, dst=peer)\n"
+            "                req.wait()\n")
+        src = src[:a] + body + src[b:]
     return src
 
 

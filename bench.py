@@ -15,6 +15,13 @@ One JSON line is printed by rank 0.  ``value`` is the device-timed whole-job ima
 K steps (CUDA events, barrier + synchronize on both sides, max over ranks); ``e2e`` repeats the
 measurement through ``Trainer.train_step`` with a pinned-host -> device copy of every step's batch
 and a device -> host read of every step's loss inside the timed region.
+
+Extra keys of the same line, same lease: ``strong`` -- the reference's own operating point, global batch 256
+split over the N ranks (BASELINE.json configs 2-4), for part3 / part2b / part2a (one rank: part1), for BOTH
+arms; ``selfcheck`` (N > 1, this framework's arm) -- every collective kernel against a device-computed
+expectation at VGG-11's bucket sizes plus 2,000 skewed launches, run before anything is timed (a mismatch
+aborts with exit code 3); ``roofline`` -- the step's FLOPs and streamed bytes against MEASURED_PEAKS.json.
+At one GPU there is no peer to synchronise with: both arms run the tutorial's single-process part1 loop.
 """
 from __future__ import annotations
 
@@ -106,7 +113,7 @@ def parse_args():
     p.add_argument("--scaling", choices=("weak", "strong"), default="weak")
     p.add_argument("--per-gpu-batch", type=int, default=256)
     p.add_argument("--global-batch", type=int, default=256, help="used with --scaling strong")
-    p.add_argument("--bucket-plan", default="layer")
+    p.add_argument("--bucket-plan", default="cap:12")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--comm-blocks", type=int, default=None)
     p.add_argument("--sync-blocks", type=int, default=None)
@@ -115,6 +122,10 @@ def parse_args():
                    help="multicast heap; large all-reduces reduce inside the NVSwitch (auto: on for world > 1)")
     p.add_argument("--single-rank-collectives", action="store_true",
                    help="at --gpus 1 still run the bucket reducer and comm kernels (default: fused local SGD)")
+    p.add_argument("--dtype", choices=("bf16", "tf32"), default="bf16",
+                   help="operand / activation precision of the native arm (fp32 master weights either way)")
+    p.add_argument("--no-strong", action="store_true", help="skip the global-batch-256 runs of the other modes")
+    p.add_argument("--no-selfcheck", action="store_true", help="skip the collective self-check at N > 1")
     return p.parse_args()
 
 

@@ -38,8 +38,8 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--port", type=int, default=None)
     p.add_argument("--device", choices=("auto", "cpu", "cuda"), default="auto")
     p.add_argument("--backend", choices=("auto", "gloo", "nccl", "native"), default="auto")
-    p.add_argument("--bucket-plan", default="layer",
-                   help="part3 gradient buckets: layer (one per conv layer) | ddp (torch's caps) | single | cap:<MiB>")
+    p.add_argument("--bucket-plan", default="cap:12",
+                   help="part3 gradient buckets: cap:<MiB> (greedy) | layer (one per conv layer) | ddp (torch's caps) | single")
     p.add_argument("--no-fuse-optimizer", action="store_true")
     p.add_argument("--nvls", choices=("auto", "on", "off"), default="auto",
                    help="NVSwitch multicast heap; in-switch all-reduce for large buckets (auto: on for world > 1)")

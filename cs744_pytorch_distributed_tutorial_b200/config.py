@@ -54,7 +54,11 @@ class TrainConfig:
     dtype: str = "bf16"         # compute dtype of the native GPU path (fp32 master weights)
     backend: str = "auto"       # auto | gloo | nccl | native  (native = in-kernel NVLink collectives)
     sync_impl: str = "auto"     # auto | torch | native
-    bucket_plan: str = "layer"  # layer (8 buckets) | ddp (torch's 3 buckets) | single | cap:<MiB>
+    # part3 gradient buckets: cap:<MiB> (greedy, closed at conv-layer boundaries) | layer (one per conv layer,
+    # SURVEY 7.3) | ddp (torch's 1 MiB + 25 MiB caps) | single.  cap:12 gives 18.9 / 14.2 / 3.9 MB on VGG-11: each
+    # bucket kernel pays two barrier round trips and a launch, three of them hide under backward where eight
+    # did not (2 B200s, 256 per GPU: 0.698 ms/step and 6.8 % exposed vs 0.735 and 11.5 % with `layer`)
+    bucket_plan: str = "cap:12"
     fuse_optimizer: bool = True  # SGD in the collective epilogue where the mode allows it
     # CTAs of a side-stream bucket kernel (part3); the GEMMs keep the other SMs.  Three 9.4 MB buckets
     # become ready in the first ~100 us of backward; 16 CTAs could not drain them before backward ended

@@ -53,8 +53,17 @@ def test_reference_module_loads_and_only_world_literals_are_parameterised():
     changed = [l for l in difflib.unified_diff(src.splitlines(), p8.splitlines(), lineterm="", n=0)
                if l[:1] in "+-" and l[:3] not in ("+++", "---")]
     assert len(changed) == 4, changed
-    with pytest.raises(NotImplementedError):
-        ref_harness._parameterise_world("x", 8, "part2a_extra.py")
+    # part2a_extra: the master's hand-unrolled peers 1..3 become a loop over range(1, world); the training loop
+    # around the sync block and the slave script stay character-for-character the reference
+    ex = (ref_harness.REF_ROOT / "master" / "part2a" / "part2a_extra.py").read_text()
+    assert ref_harness._parameterise_world(ex, 4, "part2a_extra.py") == ex
+    e8 = ref_harness._parameterise_world(ex, 8, "part2a_extra.py")
+    compile(e8, "part2a_extra", "exec")
+    assert "for peer in range(1, 8):" in e8 and "grad_mean = grad_mean / 8" in e8 and "grad_3" not in e8
+    head, tail = ex.index("            grad_1 = torch.zeros_like(p.grad)"), ex.index("        optimizer.step()")
+    assert e8.startswith(ex[:head]) and e8.endswith(ex[tail:])
+    sl = (ref_harness.REF_ROOT / "slave" / "part2a" / "part2a_extra.py").read_text()
+    assert ref_harness._parameterise_world(sl, 8, "part2a_extra.py") == sl
     mod = ref_harness.load_reference("part3", rank=0, world=1, device="cpu")
     assert mod.device == "cpu" and callable(mod.train_model) and hasattr(mod, "DDP")
     m = mod.mdl.VGG11()

@@ -272,7 +272,8 @@ def test_engine_part3_two_rank_path_in_dry_run(executor, monkeypatch):
     monkeypatch.setattr(VGG, "enable_native", lambda self, max_batch, heap=None, **kw: orig_enable(self, max_batch, heap=heap, autotune=False, **kw))
     monkeypatch.delenv("B200DP_WGRAD_PUSH", raising=False)
 
-    cfg = TrainConfig(mode="part3", device="cpu", num_nodes=2, rank=1, per_rank_batch=8, eval=False, cuda_graph=False)
+    cfg = TrainConfig(mode="part3", device="cpu", num_nodes=2, rank=1, per_rank_batch=8, eval=False, cuda_graph=False,
+                      bucket_plan="layer")
     log.clear()
     be = engine.NativeBackend(cfg, VGG("VGG11"), torch.device("cpu"))
     assert type(be.sync).__name__ == "BucketedOverlapSync" and be.comm.multicast      # NVLS heap by default for world > 1

@@ -116,7 +116,7 @@ def test_default_part3_strategy_constructs_and_hands_buckets_to_the_reducer():
 @pytest.mark.parametrize("world", [2, 4, 8])
 def test_wgrad_push_toggle_lays_out_staging_consistently(monkeypatch, world):
     monkeypatch.setenv("B200DP_WGRAD_PUSH", "1")
-    nv, s = _make(world)
+    nv, s = _make(world, bucket_plan="layer")
     assert s._wgrad_push and sorted(nv.wgrad_push) == list(range(1, len(nv.blocks)))   # layer 0 stays on the all-reduce
     stage_off, lo, hi, base = s.reducer.staged
     end_of_stage = 0

@@ -180,7 +180,10 @@ def run_reference(mode: str, rank: int, world: int, local_rank: int, per_rank_ba
     loader.on_timed_region, loader.on_timed_region_end = on_timed_region, on_timed_region_end
     sink = io.StringIO()
     with contextlib.redirect_stdout(sink) if quiet else contextlib.nullcontext():
-        ref.train_model(model, loader, optimizer, criterion, 0, rank)
+        if mode == "part1":
+            ref.train_model(model, loader, optimizer, criterion, 0)     # ref: master/part1/part1.py:20
+        else:
+            ref.train_model(model, loader, optimizer, criterion, 0, rank)
     ms = loader.elapsed_ms / steps
     h2d = per_rank_batch * (3 * 32 * 32 * 4 + 8) if host_inputs else 0
     return {"ms_per_step": ms, "h2d_bytes_per_step": h2d, "stdout_tail": sink.getvalue()[-400:]}

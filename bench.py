@@ -129,15 +129,89 @@ def parse_args():
     return p.parse_args()
 
 
-def working_set_mb(arch_blocks, batch: int) -> float:
-    """Bytes a training step streams through (activations bf16 fwd+bwd, weights/grads/momentum fp32)."""
+def working_set_mb(arch_blocks, batch: int, act_bytes: int = 2) -> float:
+    """Bytes a training step streams through (activations fwd+bwd, weights/grads/momentum fp32)."""
     act = 0
     for s in arch_blocks:
         hw = s.hw * s.hw
-        act += batch * hw * s.cout * 2 * 2                      # y and dy
-        act += batch * (hw // 4 if s.pool else hw) * s.cout * 2 * 2  # out and dout
-    params = 9_231_114 * 4 * 3 + 9_231_114 * 2 * 2               # fp32 p/g/m + bf16 Wf/Wd
+        act += batch * hw * s.cout * act_bytes * 2                      # y and dy
+        act += batch * (hw // 4 if s.pool else hw) * s.cout * act_bytes * 2  # out and dout
+    params = 9_231_114 * 4 * 3 + 9_231_114 * act_bytes * 2           # fp32 p/g/m + operand copies Wf/Wd
     return (act + params) / 1e6
+
+
+def step_gflop(arch_blocks, batch: int) -> float:
+    """Forward + data-gradient + weight-gradient FLOPs of the conv and linear layers for one step."""
+    f = 0.0
+    for i, s in enumerate(arch_blocks):
+        g = 2.0 * batch * s.hw * s.hw * s.cout * 9 * s.cin
+        f += g * (2 if i == 0 else 3)                       # the first layer needs no data gradient
+    f += 3 * 2.0 * batch * 512 * 10
+    return f / 1e9
+
+
+def roofline(arch_blocks, per_gpu_batch: int, ms_per_step: float, act_bytes: int) -> dict:
+    """Achieved rate of one GPU's step against the driver-measured denominators (MEASURED_PEAKS.json)."""
+    peaks = {}
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "MEASURED_PEAKS.json")) as f:
+            peaks = json.load(f)
+    except Exception:
+        pass
+    source = "measured" if peaks else "fallback"
+    tf = peaks.get("bf16_tflops_sustained", 1400.0)
+    bw = peaks.get("hbm_gbs", 6650.0)
+    gf = step_gflop(arch_blocks, per_gpu_batch)
+    mb = working_set_mb(arch_blocks, per_gpu_batch, act_bytes)
+    t = ms_per_step * 1e-3
+    return {"step_gflop": round(gf, 1), "achieved_tflops": round(gf / t / 1e3, 1),
+            "frac_of_bf16_sustained": round(gf / t / 1e3 / tf, 3), "streamed_mb": round(mb, 1),
+            "achieved_gbs": round(mb / t / 1e3, 1), "frac_of_hbm": round(mb / t / 1e3 / bw, 3),
+            "floor_ms": round(max(gf / tf, mb / bw) * 1e-3, 4), "peaks": source}
+
+
+def native_config(args, mode: str, world: int, rank: int, port: int, strong: bool):
+    from cs744_pytorch_distributed_tutorial_b200.config import TrainConfig
+    kw = dict(mode=mode, master_ip=os.environ.get("MASTER_ADDR", "127.0.0.1"), num_nodes=world, rank=rank,
+              device="cuda", eval=False, bucket_plan=args.bucket_plan, port=port, dtype=args.dtype)
+    kw["single_rank_collectives"] = args.single_rank_collectives
+    kw["nvls"] = {"auto": None, "on": True, "off": False}[args.nvls]
+    if args.comm_blocks:
+        kw["comm_blocks"] = args.comm_blocks
+    if args.sync_blocks:
+        kw["sync_blocks"] = args.sync_blocks
+    if strong:
+        kw["global_batch"] = args.global_batch
+    else:
+        kw["per_rank_batch"] = args.per_gpu_batch
+    return TrainConfig(**kw)
+
+
+def time_replays(be, steps: int, sampler=None) -> float:
+    """ms per step of `steps` replays of the captured step, device-timed, max over ranks."""
+    be.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if sampler is not None:
+        sampler.start()
+    e0.record()
+    for _ in range(steps):
+        if be.graph is not None:
+            be.graph.replay()
+        else:
+            be._step_body()
+    e1.record()
+    torch.cuda.synchronize()
+    if sampler is not None:
+        sampler.stop()
+    be.barrier()
+    return be.max_over_ranks(e0.elapsed_time(e1)) / steps
+
+
+def make_batches(B: int, rank: int, n: int = 8):
+    g = torch.Generator().manual_seed(1234 + rank)
+    return [(torch.randn(B, 3, 32, 32, generator=g).pin_memory(),
+             torch.randint(0, 10, (B,), generator=g).pin_memory()) for _ in range(n)]
 
 
 def run_native(args) -> dict:
@@ -149,48 +223,45 @@ def run_native(args) -> dict:
     rank = env_int("RANK", 0)
     if world != args.gpus:
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}; launch with torch.distributed.run for N>1")
-    mode = args.mode if world > 1 or args.mode in ("part1", "part3") else "part1"
-    kw = dict(mode=mode, master_ip=os.environ.get("MASTER_ADDR", "127.0.0.1"), num_nodes=world, rank=rank,
-              device="cuda", eval=False, bucket_plan=args.bucket_plan,
-              port=args.port or env_int("MASTER_PORT", 29500) + 37)
-    kw["single_rank_collectives"] = args.single_rank_collectives
-    kw["nvls"] = {"auto": None, "on": True, "off": False}[args.nvls]
-    if args.comm_blocks:
-        kw["comm_blocks"] = args.comm_blocks
-    if args.sync_blocks:
-        kw["sync_blocks"] = args.sync_blocks
-    if args.scaling == "weak":
-        kw["per_rank_batch"] = args.per_gpu_batch
-    else:
-        kw["global_batch"] = args.global_batch
-    cfg = TrainConfig(**kw)
+    base_port = args.port or env_int("MASTER_PORT", 29500) + 37
+    torch.cuda.set_device(env_int("LOCAL_RANK", rank))
+
+    # ---- N > 1: prove the collective kernels on this box before anything is timed
+    selfcheck = None
+    if world > 1 and not args.no_selfcheck:
+        from cs744_pytorch_distributed_tutorial_b200.parallel.comm import Store
+        from cs744_pytorch_distributed_tutorial_b200.parallel.selfcheck import run_selfcheck
+        store = Store(os.environ.get("MASTER_ADDR", "127.0.0.1"), base_port + 20, rank, world, timeout_s=120)
+        res = run_selfcheck(store, rank, world, torch.cuda.current_device(), multicast=args.nvls != "off")
+        bad = store.add("selfcheck/failed", 0 if res["ok"] else 1)
+        store.barrier("selfcheck")
+        bad = store.add("selfcheck/failed", 0)
+        store.close()
+        selfcheck = {"ok": bad == 0, "cases": res["cases"], "seconds": res["seconds"], "nvls": res["nvls"]}
+        if bad:
+            if not res["ok"]:
+                print("\n".join(res["failures"][:10]), file=sys.stderr, flush=True)
+            if rank == 0:
+                print(json.dumps({"impl": "native", "selfcheck": selfcheck, "error": "collective self-check failed"}),
+                      flush=True)
+            raise SystemExit(3)
+
+    # one GPU has no peer: every mode is the tutorial's single-process loop (part1), and is labelled so
+    mode = args.mode if (world > 1 or args.single_rank_collectives) else "part1"
+    strong_main = args.scaling == "strong"
+    cfg = native_config(args, mode, world, rank, base_port, strong_main)
     tr = Trainer(cfg)
     be = tr.backend
     B = cfg.per_rank_batch
-    g = torch.Generator().manual_seed(1234 + rank)
-    host_batches = [(torch.randn(B, 3, 32, 32, generator=g).pin_memory(),
-                     torch.randint(0, 10, (B,), generator=g).pin_memory()) for _ in range(8)]
+    host_batches = make_batches(B, rank)
     sampler = ClockSampler(torch.cuda.current_device())
+    act_bytes = 4 if args.dtype == "tf32" else 2
 
     # ---- device-timed: K replays of the captured step, inputs already resident on the device
     for i in range(max(args.warmup, 3)):
         be.run_staged(be.stage_inputs(*host_batches[i % 8]))
-    be.barrier()
-    torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     n0 = _lib.launch_count
-    sampler.start()
-    e0.record()
-    for _ in range(args.steps):
-        if be.graph is not None:
-            be.graph.replay()
-        else:
-            be._step_body()
-    e1.record()
-    torch.cuda.synchronize()
-    sampler.stop()
-    be.barrier()
-    ms_dev = be.max_over_ranks(e0.elapsed_time(e1)) / args.steps
+    ms_dev = time_replays(be, args.steps, sampler)
     launches = be.launches_per_step * args.steps if be.graph is not None else _lib.launch_count - n0
 
     # ---- end to end through the public API: H2D of every batch + D2H of every loss in the timed region
@@ -216,24 +287,29 @@ def run_native(args) -> dict:
         ms_e2e = be.max_over_ranks(t0.elapsed_time(t1)) / args.steps
         e2e = {"value": cfg.global_batch / (ms_e2e * 1e-3), "unit": "images/s", "ms_per_step": ms_e2e,
                "h2d_bytes_per_step": B * (3 * 32 * 32 * 4 + 8), "d2h_bytes_per_step": 4, "last_loss": last}
+    specs = tr.model.block_specs()
     out = {
         "metric": "VGG-11 CIFAR-10 images/sec", "impl": "native", "value": cfg.global_batch / (ms_dev * 1e-3),
         "unit": "images/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms_dev, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
-        "dtype": "bf16", "data": "synthetic (random CIFAR-10-shaped tensors, random-init weights)",
+        "dtype": args.dtype, "data": "synthetic (random CIFAR-10-shaped tensors, random-init weights)",
         "config": {"model": "VGG-11", "global_batch": cfg.global_batch, "per_gpu_batch": B, "seq_len": None,
                    "image": "3x32x32", "mode": mode, "parallelism": f"dp{world}", "optimizer": "SGD lr0.1 m0.9 wd1e-4",
                    "bucket_plan": args.bucket_plan, "cuda_graph": be.graph is not None, "nvls": cfg.use_nvls,
-                   "l2": f"no explicit flush: one step streams ~{working_set_mb(tr.model.block_specs(), B):.0f} MB "
+                   "l2": f"no explicit flush: one step streams ~{working_set_mb(specs, B, act_bytes):.0f} MB "
                          f"(> 126 MB L2) and rewrites every activation and parameter"},
         "gpu_launches": launches, "clocks": sampler.summary(),
+        "roofline": roofline(specs, B, ms_dev, act_bytes),
     }
     if e2e is not None:
         out["e2e"] = e2e
+    if selfcheck is not None:
+        out["selfcheck"] = selfcheck
     if world > 1:
         # exposed communication = step time - the same step with the sync block replaced by the local
         # fused SGD, measured on every rank with an identical no-communication trainer
-        local = Trainer(TrainConfig(mode="part1", num_nodes=1, rank=0, device="cuda", eval=False, per_rank_batch=B))
+        local = Trainer(TrainConfig(mode="part1", num_nodes=1, rank=0, device="cuda", eval=False, per_rank_batch=B,
+                                    dtype=args.dtype))
         lb = local.backend
         for i in range(3):
             lb.run_staged(lb.stage_inputs(*host_batches[i % 8]))
@@ -251,6 +327,28 @@ def run_native(args) -> dict:
         out["exposed_comm_ms_per_step"] = ms_dev - ms_local
         out["exposed_comm_fraction"] = (ms_dev - ms_local) / ms_dev
     tr.close()
+
+    # ---- the reference's own operating point: global batch 256 split over the ranks, every sync mode
+    if not args.no_strong:
+        strong = {}
+        gb = args.global_batch
+        if world == 1:
+            if not strong_main and B == gb:
+                strong["part1"] = {"ms_per_step": ms_dev, "images_per_s": gb / (ms_dev * 1e-3)}
+        elif gb % world == 0:
+            steps = min(args.steps, 50)
+            for k, m in enumerate(("part3", "part2b", "part2a")):
+                if strong_main and m == mode:
+                    strong[m] = {"ms_per_step": ms_dev, "images_per_s": gb / (ms_dev * 1e-3)}
+                    continue
+                t = Trainer(native_config(args, m, world, rank, base_port + 1 + k, True))
+                hb = make_batches(gb // world, rank, 4)
+                for i in range(3):
+                    t.backend.run_staged(t.backend.stage_inputs(*hb[i % 4]))
+                ms = time_replays(t.backend, steps)
+                strong[m] = {"ms_per_step": ms, "images_per_s": gb / (ms * 1e-3), "steps": steps}
+                t.close()
+        out["strong"] = {"global_batch": gb, "per_gpu_batch": gb // world, **strong}
     return out if rank == 0 else {}
 
 
@@ -266,17 +364,19 @@ def run_reference(args) -> dict:
     local = env_int("LOCAL_RANK", 0)
     if world != args.gpus:
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}; launch with torch.distributed.run for N>1")
-    mode = args.mode
-    if world == 1 and mode != "part3":
-        mode = "part1"
+    # one GPU: the tutorial's single-process script (part1), as for the native arm
+    mode = args.mode if world > 1 else "part1"
     B = args.per_gpu_batch if args.scaling == "weak" else args.global_batch // world
     torch.cuda.set_device(local)
-    if mode == "part3" and world == 1 and not dist.is_initialized():
-        # DDP needs a process group even for one rank (the reference always has 4)
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        os.environ.setdefault("MASTER_PORT", str(args.port or 29533))
-        dist.init_process_group("nccl", rank=0, world_size=1)
     sampler = ClockSampler(local)
+
+    def max_ranks(v: float) -> float:
+        if world == 1:
+            return v
+        t = torch.tensor([v], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
     try:
         dev = ref_harness.run_reference(mode, rank, world, local, B, args.steps, max(args.warmup, 3), host_inputs=False,
                                         on_timed_region=sampler.start, on_timed_region_end=sampler.stop)
@@ -286,13 +386,6 @@ def run_reference(args) -> dict:
     except Exception as e:  # the reference arm must never take the benchmark down
         return {"impl": "reference", "unavailable": f"{type(e).__name__}: {e}"[:300]}
 
-    def max_ranks(v: float) -> float:
-        if world == 1:
-            return v
-        t = torch.tensor([v], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
     ms_dev = max_ranks(dev["ms_per_step"])
     gb = B * world
     out = {
@@ -300,8 +393,9 @@ def run_reference(args) -> dict:
         "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_dev,
         "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "fp32 (torch default, TF32 conv)",
         "data": "synthetic (random CIFAR-10-shaped tensors, random-init weights)",
-        "config": {"model": "VGG-11", "global_batch": gb, "per_gpu_batch": B, "image": "3x32x32", "mode": mode,
-                   "parallelism": f"dp{world}", "backend": "nccl", "script": "/".join(ref_harness.SCRIPTS[mode]),
+        "config": {"model": "VGG-11", "global_batch": gb, "per_gpu_batch": B, "seq_len": None, "image": "3x32x32",
+                   "mode": mode, "parallelism": f"dp{world}", "optimizer": "SGD lr0.1 m0.9 wd1e-4", "backend": "nccl",
+                   "script": "/".join(ref_harness.SCRIPTS[mode]),
                    "note": "unmodified train_model() and model.py from baseline/_ref; device global set to cuda"},
         "gpu_launches": 0, "clocks": sampler.summary(),
     }
@@ -309,6 +403,23 @@ def run_reference(args) -> dict:
         ms = max_ranks(e2e["ms_per_step"])
         out["e2e"] = {"value": gb / (ms * 1e-3), "unit": "images/s", "ms_per_step": ms,
                       "h2d_bytes_per_step": e2e["h2d_bytes_per_step"], "d2h_bytes_per_step": 4.0 / 20}
+    # ---- the reference's own operating point: global batch 256 split over the ranks, every sync mode
+    if not args.no_strong:
+        strong = {}
+        g256 = args.global_batch
+        if world == 1:
+            if args.scaling == "weak" and B == g256:
+                strong["part1"] = {"ms_per_step": ms_dev, "images_per_s": g256 / (ms_dev * 1e-3)}
+        elif g256 % world == 0:
+            steps = min(args.steps, 50)
+            for m in ("part3", "part2b", "part2a"):
+                try:
+                    r = ref_harness.run_reference(m, rank, world, local, g256 // world, steps, 3, host_inputs=False)
+                    ms = max_ranks(r["ms_per_step"])
+                    strong[m] = {"ms_per_step": ms, "images_per_s": g256 / (ms * 1e-3), "steps": steps}
+                except Exception as e:
+                    strong[m] = {"unavailable": f"{type(e).__name__}: {e}"[:200]}
+        out["strong"] = {"global_batch": g256, "per_gpu_batch": g256 // world, **strong}
     if dist.is_initialized():
         dist.destroy_process_group()
     return out if rank == 0 else {}

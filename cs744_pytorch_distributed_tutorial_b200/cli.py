@@ -45,6 +45,10 @@ def build_parser() -> argparse.ArgumentParser:
                    help="NVSwitch multicast heap; in-switch all-reduce for large buckets (auto: on for world > 1)")
     p.add_argument("--sync-impl", choices=("auto", "oneshot", "twoshot", "nvls"), default="auto",
                    help="part2b all-reduce kernel (auto: by size and heap)")
+    p.add_argument("--dtype", choices=("bf16", "tf32"), default="bf16",
+                   help="native GPU path: bf16 operands / activations, or tf32 tensor-core math on fp32 activations")
+    p.add_argument("--aggregate-eval", action="store_true",
+                   help="also sum the per-rank correct counts of the test pass across ranks (reported by rank 0)")
     p.add_argument("--no-cuda-graph", action="store_true")
     p.add_argument("--train-size", type=int, default=50000)
     p.add_argument("--test-size", type=int, default=10000)
@@ -65,7 +69,7 @@ def config_from_args(argv=None) -> TrainConfig:
                        global_batch=a.global_batch, per_rank_batch=a.per_rank_batch, iters=a.iters, epochs=a.epochs,
                        lr=a.lr, momentum=a.momentum, weight_decay=a.weight_decay, seed=a.seed, port=a.port,
                        device=a.device, backend=a.backend, bucket_plan=a.bucket_plan,
-                       fuse_optimizer=not a.no_fuse_optimizer, nvls={"auto": None, "on": True, "off": False}[a.nvls], cuda_graph=not a.no_cuda_graph, sync_impl=a.sync_impl,
+                       fuse_optimizer=not a.no_fuse_optimizer, nvls={"auto": None, "on": True, "off": False}[a.nvls], cuda_graph=not a.no_cuda_graph, sync_impl=a.sync_impl, dtype=a.dtype, aggregate_eval=a.aggregate_eval,
                        train_size=a.train_size, test_size=a.test_size, synthetic=not a.real_data,
                        augment=not a.no_augment, loader=a.loader, loader_threads=a.loader_threads, eval=not a.no_eval, checkpoint=a.checkpoint, resume=a.resume)
 

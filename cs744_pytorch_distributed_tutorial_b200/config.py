@@ -38,12 +38,12 @@ class TrainConfig:
     port: Optional[int] = None  # default: the reference port of the mode
     log_interval: int = 20      # ref: master/part2a/part2a.py:54
     num_workers: int = 2        # ref: master/part2a/part2a.py:109
-    # batch assembly for Trainer.fit: "python" = vectorised torch ops (data.BatchPipeline, ~20 k images/s),
-    # "native" = C++ threads (csrc/loader.cpp, > 300 k images/s per thread); same sampling, different
-    # augmentation draws
     # part2b all-reduce kernel: auto (one-shot below 256 KiB, NVLS when the multicast heap exists, else
     # two-shot) | oneshot | twoshot | nvls
     sync_impl: str = "auto"
+    # batch assembly for Trainer.fit: "python" = vectorised torch ops (data.BatchPipeline, ~20 k images/s),
+    # "native" = C++ threads (csrc/loader.cpp, > 300 k images/s per thread); same sampling, different
+    # augmentation draws
     loader: str = "python"
     loader_threads: int = 4
     cpu_threads: int = 4        # ref: master/part2a/part2a.py:18
@@ -51,9 +51,11 @@ class TrainConfig:
     # --- new knobs -------------------------------------------------------------------
     arch: str = "VGG11"
     device: str = "auto"        # auto | cpu | cuda
-    dtype: str = "bf16"         # compute dtype of the native GPU path (fp32 master weights)
+    # operands and stored activations of the native GPU path (fp32 master weights and gradients either way):
+    # bf16 (tcgen05 kind::f16) | tf32 (tcgen05 kind::tf32 on fp32 activations -- the precision of the
+    # reference's fp32 model with torch's TF32 convolutions)
+    dtype: str = "bf16"
     backend: str = "auto"       # auto | gloo | nccl | native  (native = in-kernel NVLink collectives)
-    sync_impl: str = "auto"     # auto | torch | native
     # part3 gradient buckets: cap:<MiB> (greedy, closed at conv-layer boundaries) | layer (one per conv layer,
     # SURVEY 7.3) | ddp (torch's 1 MiB + 25 MiB caps) | single.  cap:12 gives 18.9 / 14.2 / 3.9 MB on VGG-11: each
     # bucket kernel pays two barrier round trips and a launch, three of them hide under backward where eight
@@ -81,8 +83,11 @@ class TrainConfig:
     checkpoint: Optional[str] = None
     resume: Optional[str] = None
     json_metrics: bool = True
-    scaling: str = "strong"     # strong: global_batch fixed; weak: per_rank_batch fixed
-    per_rank_batch: Optional[int] = None
+    # every rank evaluates the full test set (as the reference does); with this flag the per-rank correct
+    # counts are also summed across ranks and reported by rank 0 -- the intent of the workers' isend of
+    # `correct` to rank 0 that the master never receives (ref: slave/part2b/part2b.py:68-69)
+    aggregate_eval: bool = False
+    per_rank_batch: Optional[int] = None    # set: weak scaling (global_batch follows); None: global_batch is split
     timeout_s: float = 120.0
 
     def __post_init__(self) -> None:
@@ -94,6 +99,8 @@ class TrainConfig:
             raise ValueError("part1 is the single-process mode; use part2a/part2b/part3 for num_nodes > 1")
         if self.sync_impl not in SYNC_IMPLS:
             raise ValueError(f"sync_impl must be one of {tuple(SYNC_IMPLS)}, got {self.sync_impl!r}")
+        if self.dtype not in ("bf16", "tf32"):
+            raise ValueError(f"dtype must be 'bf16' or 'tf32', got {self.dtype!r}")
         if self.loader not in ("python", "native"):
             raise ValueError(f"loader must be 'python' or 'native', got {self.loader!r}")
         if self.port is None:

@@ -485,8 +485,17 @@ class Trainer:
         avg = total_loss / max(n_batches, 1)
         print('Test set: Average loss: {:.4f}, Accuracy: {}/{} ({:.0f}%)\n'.format(
             avg, correct, n_samples, 100. * correct / max(n_samples, 1)), flush=True)
-        return {"test_loss": avg, "correct": correct, "samples": n_samples,
-                "accuracy": correct / max(n_samples, 1)}
+        out = {"test_loss": avg, "correct": correct, "samples": n_samples, "accuracy": correct / max(n_samples, 1)}
+        if self.cfg.aggregate_eval and self.cfg.world_size > 1:
+            # what the reference's workers start and its master never finishes: the counts meet on rank 0
+            # (ref: slave/part2b/part2b.py:68-69)
+            total_c = int(round(self.backend.all_reduce_sum(float(correct))))
+            total_n = int(round(self.backend.all_reduce_sum(float(n_samples))))
+            if self.cfg.rank == 0:
+                print("All ranks: Accuracy: {}/{} ({:.0f}%)\n".format(total_c, total_n, 100. * total_c / max(total_n, 1)),
+                      flush=True)
+            out.update({"correct_all_ranks": total_c, "samples_all_ranks": total_n})
+        return out
 
     def fit(self) -> Dict[str, float]:
         """The tutorial's job: one epoch of training, then the test pass."""

@@ -167,7 +167,7 @@ def roofline(arch_blocks, per_gpu_batch: int, ms_per_step: float, act_bytes: int
     return {"step_gflop": round(gf, 1), "achieved_tflops": round(gf / t / 1e3, 1),
             "frac_of_bf16_sustained": round(gf / t / 1e3 / tf, 3), "streamed_mb": round(mb, 1),
             "achieved_gbs": round(mb / t / 1e3, 1), "frac_of_hbm": round(mb / t / 1e3 / bw, 3),
-            "floor_ms": round(max(gf / tf, mb / bw) * 1e-3, 4), "peaks": source}
+            "floor_ms": round(max(gf / tf, mb / bw), 4), "peaks": source}
 
 
 def native_config(args, mode: str, world: int, rank: int, port: int, strong: bool):

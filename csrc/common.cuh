@@ -262,6 +262,32 @@ B200DP_DEVINL uint64_t umma_smem_desc(uint32_t smem_addr, uint32_t lbo_bytes, ui
   return d;
 }
 
+// kind::tf32 flavours of the two MMA issue instructions (fp32 operands in shared memory, read as tf32)
+B200DP_DEVINL void umma_tf32(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                             uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+      "}\n"
+      :
+      : "r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+B200DP_DEVINL void umma_tf32_2cta(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                  uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+      "}\n"
+      :
+      : "r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
 // Instruction descriptor for kind::f16 with bf16 inputs and fp32 accumulation
 // (cute::UMMA::InstrDescriptor): c_format[4,6)=1 (F32), a/b_format=1 (BF16),
 // a_major bit15, b_major bit16 (0 = K-major, 1 = MN-major), N>>3 at [17,23), M>>4 at [24,29).
@@ -269,6 +295,49 @@ __host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N, int a_mn_ma
   return (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(a_mn_major) << 15) |
          (static_cast<uint32_t>(b_mn_major) << 16) | (static_cast<uint32_t>(N >> 3) << 17) |
          (static_cast<uint32_t>(M >> 4) << 24);
+}
+
+// Same descriptor with an explicit operand format: 1 = BF16 (kind::f16), 2 = TF32 (kind::tf32).
+__host__ __device__ constexpr uint32_t umma_idesc(int M, int N, int a_mn_major, int b_mn_major, uint32_t fmt) {
+  return (1u << 4) | (fmt << 7) | (fmt << 10) | (static_cast<uint32_t>(a_mn_major) << 15) |
+         (static_cast<uint32_t>(b_mn_major) << 16) | (static_cast<uint32_t>(N >> 3) << 17) |
+         (static_cast<uint32_t>(M >> 4) << 24);
+}
+
+// ---------------------------------------------------------------------------
+// Operand precision of the GEMM kernels.  Both flavours stage 128-byte swizzled rows, so stage sizes, descriptor
+// strides and the number of MMAs per K block are identical; what differs is the element type, the elements
+// per row and per MMA, the instruction kind and the type of the stored activations.
+//   PrecBf16: bf16 operands and activations, tcgen05.mma kind::f16 (K = 16 per instruction)
+//   PrecTf32: fp32 activations in memory, read as tf32 by kind::tf32 (K = 8 per instruction) -- the precision
+//             of the reference's fp32 model under torch's TF32 convolutions
+// ---------------------------------------------------------------------------
+struct PrecBf16 {
+  using elem = __nv_bfloat16;
+  static constexpr bool kTf32 = false;
+  static constexpr int kBytes = 2;
+  static constexpr int kBlockK = 64;   // elements per 128-byte row = K extent of one pipeline stage
+  static constexpr int kUmmaK = 16;
+  static constexpr uint32_t kFmt = 1;
+};
+struct PrecTf32 {
+  using elem = float;
+  static constexpr bool kTf32 = true;
+  static constexpr int kBytes = 4;
+  static constexpr int kBlockK = 32;
+  static constexpr int kUmmaK = 8;
+  static constexpr uint32_t kFmt = 2;
+};
+
+template <class Prec>
+B200DP_DEVINL void umma_ss(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+  if constexpr (Prec::kTf32) umma_tf32(tmem_d, da, db, idesc, accumulate);
+  else umma_bf16(tmem_d, da, db, idesc, accumulate);
+}
+template <class Prec>
+B200DP_DEVINL void umma_ss_2cta(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+  if constexpr (Prec::kTf32) umma_tf32_2cta(tmem_d, da, db, idesc, accumulate);
+  else umma_bf16_2cta(tmem_d, da, db, idesc, accumulate);
 }
 
 // ---------------------------------------------------------------------------

@@ -26,6 +26,9 @@ _PROTOTYPES = {
     "b200dp_conv_igemm_splitk": [P, P, P, P, P, P, I, I, I, I, I, I, I, I, P],
     "b200dp_conv_igemm_pair": [P, P, P, P, P, P, I, I, I, I, I, I, I, I, P],
     "b200dp_conv_dgrad_bn_reduce": [P, P, P, P, P, P, P, P, I, I, I, I, I, I, I, I, I, P],
+    "b200dp_conv_igemm_ex": [P, P, P, P, P, P, I, I, I, I, I, I, I, I, I, I, P],
+    "b200dp_conv_dgrad_bn_reduce_ex": [P, P, P, P, P, P, P, P, I, I, I, I, I, I, I, I, I, I, P],
+    "b200dp_conv_wgrad_ex": [P, P, P, I, I, I, I, I, I, I, I, I, I, I, P],
     "b200dp_conv_wgrad": [P, P, P, I, I, I, I, I, I, I, I, I, P],
     "b200dp_conv_wgrad_tiled": [P, P, P, I, I, I, I, I, I, I, I, I, I, P],
     "b200dp_conv_wgrad_push": [P, P, P, I, I, I, I, I, I, I, I, P, I, I, I, P, LL, LL, LL, LL, P],
@@ -48,6 +51,8 @@ _PROTOTYPES = {
     "b200dp_copy_pair": [P, P, LL, P, P, LL, P],
     "b200dp_prep_conv_weights": [P, P, P, I, I, I, I, P],
     "b200dp_prep_conv_weights_batched": [I, P, P, P, P, P, P, P, P],
+    "b200dp_prep_conv_weights_ex": [P, P, P, I, I, I, I, I, P],
+    "b200dp_prep_conv_weights_batched_ex": [I, P, P, P, P, P, P, P, I, P],
 }
 
 

@@ -23,36 +23,35 @@ def _chk(t: torch.Tensor, dtype: torch.dtype, name: str) -> None:
                          f"contiguous={t.is_contiguous()}")
 
 
+def _act_dtype(t: torch.Tensor, name: str) -> int:
+    """0 for bf16 activations, 1 for fp32 activations (tf32 tensor-core math); checks layout."""
+    if t.dtype not in (torch.bfloat16, torch.float32):
+        raise ValueError(f"{name}: activations are bf16 or fp32 (tf32 path), got {t.dtype}")
+    _chk(t, t.dtype, name)
+    return 1 if t.dtype == torch.float32 else 0
+
+
 def conv_igemm(act: torch.Tensor, wgt: torch.Tensor, bias: Optional[torch.Tensor], out: torch.Tensor,
                stats: Optional[torch.Tensor] = None, taps: int = 9, block_n: int = 0, split_k: int = 1,
                workspace: Optional[torch.Tensor] = None, cta_pair: bool = False) -> torch.Tensor:
     """out[B,H,W,Cout] = conv3x3(act[B,H,W,Cin], wgt[Cout, taps*Cin]) + bias (tcgen05 implicit GEMM).
 
-    ref: master/part1/model.py:18-23.  Also the dgrad kernel when fed dY and the
-    flipped/transposed weights.
-    """
-    _chk(act, torch.bfloat16, "act")
-    _chk(wgt, torch.bfloat16, "wgt")
-    _chk(out, torch.bfloat16, "out")
+    ref: master/part1/model.py:18-23.  Also the dgrad kernel when fed dY and the flipped/transposed weights.
+    bf16 tensors run ``tcgen05.mma kind::f16``; fp32 tensors (``act``, ``wgt`` and ``out`` alike) run
+    ``kind::tf32`` on the fp32 data -- the reference's precision."""
+    dt = _act_dtype(act, "act")
+    _chk(wgt, act.dtype, "wgt")
+    _chk(out, act.dtype, "out")
     B, H, W, Cin = act.shape
     Cout = wgt.shape[0]
     assert wgt.shape[1] == taps * Cin, (wgt.shape, taps, Cin)
     assert out.shape == (B, H, W, Cout)
-    if cta_pair:
-        # tcgen05 cta_group::2: a 256 x block_n tile per pair of SMs, each staging half of the weight tile
-        if split_k > 1:
-            assert workspace is not None and workspace.numel() >= out.numel()
-        call("b200dp_conv_igemm_pair", ptr(act), ptr(wgt), ptr(bias), ptr(out), ptr(stats),
-             ptr(workspace) if split_k > 1 else None, B, H, W, Cin, Cout, taps, block_n, split_k, stream_ptr())
-        return out
     if split_k > 1:
         # K loop split over several CTAs per tile; `workspace` (fp32, >= B*H*W*Cout, zero) holds the partials
         assert workspace is not None and workspace.dtype == torch.float32 and workspace.numel() >= out.numel()
-        call("b200dp_conv_igemm_splitk", ptr(act), ptr(wgt), ptr(bias), ptr(out), ptr(stats), ptr(workspace), B, H,
-             W, Cin, Cout, taps, block_n, split_k, stream_ptr())
-        return out
-    call("b200dp_conv_igemm", ptr(act), ptr(wgt), ptr(bias), ptr(out), ptr(stats), B, H, W, Cin, Cout, taps,
-         block_n, stream_ptr())
+    call("b200dp_conv_igemm_ex", ptr(act), ptr(wgt), ptr(bias), ptr(out), ptr(stats),
+         ptr(workspace) if split_k > 1 else None, B, H, W, Cin, Cout, taps, block_n, split_k, int(bool(cta_pair)), dt,
+         stream_ptr())
     return out
 
 
@@ -64,35 +63,35 @@ def conv_dgrad_bn_reduce(dy: torch.Tensor, wd: torch.Tensor, dout_prev: torch.Te
     ``dout_prev = dgrad(dy, wd)`` and ``sums += [sum_{a>0} g, sum_{a>0} g*(a-beta)/gamma]`` where
     ``a = out_prev`` is that block's stored output.  Saves the ``bn_bwd_reduce_from_out`` launch and its
     read of ``dout_prev`` (ref: the autograd of master/part1/model.py:18-23 run by part1.py:37)."""
-    _chk(dy, torch.bfloat16, "dy")
-    _chk(wd, torch.bfloat16, "wd")
-    _chk(dout_prev, torch.bfloat16, "dout_prev")
-    _chk(out_prev, torch.bfloat16, "out_prev")
+    dt = _act_dtype(dy, "dy")
+    for t, n in ((wd, "wd"), (dout_prev, "dout_prev"), (out_prev, "out_prev")):
+        _chk(t, dy.dtype, n)
     B, H, W, Cin = dy.shape
     Cout = wd.shape[0]
     assert wd.shape[1] == 9 * Cin and dout_prev.shape == (B, H, W, Cout) and out_prev.shape == dout_prev.shape
     assert sums.numel() >= 2 * Cout and gamma.numel() == Cout and beta.numel() == Cout
     if split_k > 1:
         assert workspace is not None and workspace.dtype == torch.float32 and workspace.numel() >= dout_prev.numel()
-    call("b200dp_conv_dgrad_bn_reduce", ptr(dy), ptr(wd), ptr(dout_prev), ptr(workspace) if split_k > 1 else None,
-         ptr(out_prev), ptr(gamma), ptr(beta), ptr(sums), B, H, W, Cin, Cout, 9, block_n, split_k, int(cta_pair),
-         stream_ptr())
+    call("b200dp_conv_dgrad_bn_reduce_ex", ptr(dy), ptr(wd), ptr(dout_prev), ptr(workspace) if split_k > 1 else None,
+         ptr(out_prev), ptr(gamma), ptr(beta), ptr(sums), B, H, W, Cin, Cout, 9, block_n, split_k, int(bool(cta_pair)),
+         dt, stream_ptr())
     return dout_prev
 
 
 def conv_wgrad(dy: torch.Tensor, x: torch.Tensor, dw: torch.Tensor, taps: int = 9, cin_valid: Optional[int] = None,
                split_k: int = 0, accumulate: bool = False, block_n: int = 0) -> torch.Tensor:
     """dw[Cout, taps, cin_valid] (fp32) (+)= sum_p dy[p, Cout] * x[p+tap, Cin].  With split-K or
-    ``accumulate`` the partial tiles are added onto ``dw`` (zero it first for a plain gradient)."""
-    _chk(dy, torch.bfloat16, "dy")
-    _chk(x, torch.bfloat16, "x")
+    ``accumulate`` the partial tiles are added onto ``dw`` (zero it first for a plain gradient).
+    bf16 or fp32 (tf32 math) operands, as for ``conv_igemm``."""
+    dt = _act_dtype(dy, "dy")
+    _chk(x, dy.dtype, "x")
     _chk(dw, torch.float32, "dw")
     B, H, W, Cout = dy.shape
     Cin = x.shape[3]
     cv = Cin if cin_valid is None else cin_valid
     assert dw.numel() == Cout * taps * cv
-    call("b200dp_conv_wgrad_tiled", ptr(dy), ptr(x), ptr(dw), B, H, W, Cin, Cout, taps, cv, split_k, int(accumulate),
-         block_n, stream_ptr())
+    call("b200dp_conv_wgrad_ex", ptr(dy), ptr(x), ptr(dw), B, H, W, Cin, Cout, taps, cv, split_k, int(accumulate),
+         block_n, dt, stream_ptr())
     return dw
 
 
@@ -206,19 +205,29 @@ def copy_pair(dst0: torch.Tensor, src0: torch.Tensor, dst1: torch.Tensor, src1: 
     call("b200dp_copy_pair", ptr(dst0), ptr(src0), n0, ptr(dst1), ptr(src1), n1, stream_ptr())
 
 
+def _operand_dtype(wf, wd) -> int:
+    t = wf if wf is not None else wd
+    return 1 if t.dtype == torch.float32 else 0
+
+
 def prep_conv_weights(master, wf, wd, Cout: int, Cin: int, taps: int, kpad: int):
-    call("b200dp_prep_conv_weights", ptr(master), ptr(wf), ptr(wd), Cout, Cin, taps, kpad, stream_ptr())
+    """Operand copies of one conv layer's fp32 master weights: ``wf`` [Cout, kpad] (forward, zero padded) and
+    ``wd`` [Cin, taps*Cout] (data gradient: transposed, taps flipped); either may be None.  bf16 tensors for the
+    bf16 kernels, fp32 tensors for the tf32 kernels."""
+    call("b200dp_prep_conv_weights_ex", ptr(master), ptr(wf), ptr(wd), Cout, Cin, taps, kpad, _operand_dtype(wf, wd),
+         stream_ptr())
 
 
 class BatchedWeightPrep:
-    """All conv layers' bf16 shadows (Wf and the tap-flipped transposed Wd) in ONE launch.  The
+    """All conv layers' operand copies (Wf and the tap-flipped transposed Wd) in ONE launch.  The
     pointer tables are built once; layers that are not multiples of 64 (the 3-channel first conv)
-    fall back to the single-layer kernel."""
+    fall back to the single-layer kernel; layers with nothing to write (tf32 forward operand = the master
+    tensor, no data gradient) are skipped."""
 
     def __init__(self, layers):
-        """``layers``: iterable of (master, wf, wd_or_None, Cout, Cin, taps, kpad)."""
+        """``layers``: iterable of (master, wf_or_None, wd_or_None, Cout, Cin, taps, kpad)."""
         import ctypes
-        layers = list(layers)
+        layers = [l for l in layers if l[1] is not None or l[2] is not None]
         odd = lambda l: bool(l[3] % 64 or l[4] % 64 or l[6] != l[5] * l[4])
         self._single = [l for l in layers if odd(l)]
         batched = [l for l in layers if not odd(l)]
@@ -227,8 +236,9 @@ class BatchedWeightPrep:
         if self._n:
             vp = ctypes.c_void_p * self._n
             ia = ctypes.c_int * self._n
+            self._dtype = _operand_dtype(batched[0][1], batched[0][2])
             self._master = vp(*[l[0].data_ptr() for l in batched])
-            self._wf = vp(*[l[1].data_ptr() for l in batched])
+            self._wf = vp(*[(l[1].data_ptr() if l[1] is not None else None) for l in batched])
             self._wd = vp(*[(l[2].data_ptr() if l[2] is not None else None) for l in batched])
             self._cout, self._cin = ia(*[l[3] for l in batched]), ia(*[l[4] for l in batched])
             self._taps, self._kpad = ia(*[l[5] for l in batched]), ia(*[l[6] for l in batched])
@@ -237,8 +247,8 @@ class BatchedWeightPrep:
         for m, wf, wd, co, ci, taps, kpad in self._single:
             prep_conv_weights(m, wf, wd, co, ci, taps, kpad)
         if self._n:
-            call("b200dp_prep_conv_weights_batched", self._n, self._master, self._wf, self._wd, self._cout, self._cin,
-                 self._taps, self._kpad, stream_ptr())
+            call("b200dp_prep_conv_weights_batched_ex", self._n, self._master, self._wf, self._wd, self._cout,
+                 self._cin, self._taps, self._kpad, self._dtype, stream_ptr())
 
 
 def version() -> str:

@@ -352,6 +352,49 @@ B200DP_DEVINL float2 unpack_bf16x2(uint32_t u) {
   return __bfloat1622float2(v);
 }
 
+// Eight consecutive activations (one 16-byte bf16 vector or two 16-byte fp32 vectors) as floats.
+struct F8 {
+  float v[8];
+};
+template <class T>
+B200DP_DEVINL F8 ld8(const T* p) {
+  F8 r;
+  if constexpr (sizeof(T) == 4) {
+    const float4 a = *reinterpret_cast<const float4*>(p);
+    const float4 b = *(reinterpret_cast<const float4*>(p) + 1);
+    r.v[0] = a.x; r.v[1] = a.y; r.v[2] = a.z; r.v[3] = a.w;
+    r.v[4] = b.x; r.v[5] = b.y; r.v[6] = b.z; r.v[7] = b.w;
+  } else {
+    const uint4 u = *reinterpret_cast<const uint4*>(p);
+    float2 f;
+    f = unpack_bf16x2(u.x); r.v[0] = f.x; r.v[1] = f.y;
+    f = unpack_bf16x2(u.y); r.v[2] = f.x; r.v[3] = f.y;
+    f = unpack_bf16x2(u.z); r.v[4] = f.x; r.v[5] = f.y;
+    f = unpack_bf16x2(u.w); r.v[6] = f.x; r.v[7] = f.y;
+  }
+  return r;
+}
+// Store eight values in the activation type; for bf16 `r` is replaced by the rounded values that were stored.
+template <class T>
+B200DP_DEVINL void st8(T* p, F8& r) {
+  if constexpr (sizeof(T) == 4) {
+    *reinterpret_cast<float4*>(p) = make_float4(r.v[0], r.v[1], r.v[2], r.v[3]);
+    *(reinterpret_cast<float4*>(p) + 1) = make_float4(r.v[4], r.v[5], r.v[6], r.v[7]);
+  } else {
+    uint4 u;
+    u.x = pack_bf16x2(r.v[0], r.v[1]);
+    u.y = pack_bf16x2(r.v[2], r.v[3]);
+    u.z = pack_bf16x2(r.v[4], r.v[5]);
+    u.w = pack_bf16x2(r.v[6], r.v[7]);
+    *reinterpret_cast<uint4*>(p) = u;
+    float2 f;
+    f = unpack_bf16x2(u.x); r.v[0] = f.x; r.v[1] = f.y;
+    f = unpack_bf16x2(u.y); r.v[2] = f.x; r.v[3] = f.y;
+    f = unpack_bf16x2(u.z); r.v[4] = f.x; r.v[5] = f.y;
+    f = unpack_bf16x2(u.w); r.v[6] = f.x; r.v[7] = f.y;
+  }
+}
+
 B200DP_DEVINL float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -30,9 +30,9 @@
 namespace b200dp {
 
 constexpr int kBlockM = 128;
-constexpr int kBlockK = 64;  // 64 bf16 = 128 bytes = one SW128 swizzle span
-constexpr int kUmmaK = 16;
-constexpr int kAStageBytes = kBlockM * kBlockK * 2;  // 16 KiB
+// A K block is one 128-byte SW128 swizzle span per row: 64 bf16 or 32 tf32 elements (Prec::kBlockK, common.cuh)
+constexpr int kRowBytes = 128;
+constexpr int kAStageBytes = kBlockM * kRowBytes;  // 16 KiB
 // Warp roles: warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer, warps 2.. = epilogue.  A warp may only
 // read the TMEM lane quadrant (warp % 4), so epilogue warps come in groups of four; tiles of 128 columns and
 // more get TWO groups, each draining half of the columns (ncu on the one-group kernel: the epilogue was 22 %
@@ -45,11 +45,11 @@ constexpr int tail_bytes(int block_n) { return 256 + 4 * block_n; }
 struct IgemmParams {
   int H, W, TH, TN;  // image dims; an M tile is TN images x TH rows x W columns = 128 pixels
   int taps;          // 9 (3x3 pad 1) or 1
-  int cin_blocks;    // Cin / 64
+  int cin_blocks;    // Cin / Prec::kBlockK
   int m_total;       // valid output rows (B*H*W)
   int n_total;       // Cout
   const float* bias;
-  __nv_bfloat16* out;
+  void* out;     // [M][Cout] of Prec::elem
   float* stats;  // optional [2][Cout]: sum, sum of squares
   // split-K: gridDim.z CTAs share one output tile, each reduces kb_per_split K blocks and adds its
   // fp32 partial tile into `partial` ([M][Cout], zero on entry); a finalize kernel produces `out`.
@@ -62,7 +62,7 @@ struct IgemmParams {
   // PREVIOUS block (max-pooled or not).  With `bnr_a` = that block's stored output, the epilogue also
   // accumulates its BatchNorm-backward sums  S1 = sum_{a>0} g,  S2 = sum_{a>0} g*(a-beta)/gamma  into
   // bnr_sums[0..N) / [N..2N) -- what bn_bwd_reduce_from_out_kernel computes in a separate pass.
-  const __nv_bfloat16* bnr_a;
+  const void* bnr_a;   // [M][Cout] of Prec::elem
   const float* bnr_gamma;
   const float* bnr_beta;
   float* bnr_sums;
@@ -89,12 +89,74 @@ B200DP_DEVINL void red_add_v4(float* addr, float a, float b, float c, float d) {
                : "memory");
 }
 
-// Epilogue shared by the 1-CTA and 2-CTA kernels: TMEM -> registers -> (+bias, bf16, statistics) -> global,
-// or fp32 red.add into the split-K workspace.  Warp w may only touch TMEM lanes [32*(w%4), 32*(w%4)+32).
-template <int BLOCK_N, bool BNR = false>
+// 32 consecutive activations of one row, as they sit in memory: 4 x 16 bytes of bf16 or 8 x 16 bytes of fp32.
+template <class Prec>
+struct Row32 {
+  uint4 v[Prec::kTf32 ? 8 : 4];
+};
+template <class Prec>
+B200DP_DEVINL Row32<Prec> row32_load(const typename Prec::elem* p, bool pred) {
+  Row32<Prec> r;
+#pragma unroll
+  for (int j = 0; j < (Prec::kTf32 ? 8 : 4); ++j)
+    r.v[j] = pred ? __ldg(reinterpret_cast<const uint4*>(p) + j) : make_uint4(0u, 0u, 0u, 0u);
+  return r;
+}
+template <class Prec>
+B200DP_DEVINL void row32_unpack(const Row32<Prec>& r, float (&a)[32]) {
+  if constexpr (Prec::kTf32) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      a[4 * j] = __uint_as_float(r.v[j].x); a[4 * j + 1] = __uint_as_float(r.v[j].y);
+      a[4 * j + 2] = __uint_as_float(r.v[j].z); a[4 * j + 3] = __uint_as_float(r.v[j].w);
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const uint32_t w[4] = {r.v[j].x, r.v[j].y, r.v[j].z, r.v[j].w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float2 t = unpack_bf16x2(w[k]);
+        a[8 * j + 2 * k] = t.x;
+        a[8 * j + 2 * k + 1] = t.y;
+      }
+    }
+  }
+}
+// Store 32 values of one row in the activation type; on return f[] holds the values AS STORED (bf16: rounded),
+// so that statistics taken from f[] are exactly centred on what the next kernel reads.
+template <class Prec>
+B200DP_DEVINL void row32_store(typename Prec::elem* dst, bool pred, float (&f)[32]) {
+  if constexpr (Prec::kTf32) {
+    if (pred) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        reinterpret_cast<float4*>(dst)[j] = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
+    }
+  } else {
+    uint32_t packed[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      packed[j] = pack_bf16x2(f[2 * j], f[2 * j + 1]);
+      const float2 r = unpack_bf16x2(packed[j]);
+      f[2 * j] = r.x;
+      f[2 * j + 1] = r.y;
+    }
+    if (pred) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        reinterpret_cast<uint4*>(dst)[j] = make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
+    }
+  }
+}
+
+// Epilogue shared by the 1-CTA and 2-CTA kernels: TMEM -> registers -> (+bias, activation type, statistics) ->
+// global, or fp32 red.add into the split-K workspace.
+template <class Prec, int BLOCK_N, bool BNR = false>
 B200DP_DEVINL void igemm_epilogue(const IgemmParams& p, uint32_t tmem_base, uint64_t* tmem_full_bar, int warp,
                                   int lane, int m_tile, int n_tile, float* scratch, float* bias_smem) {
-  // Epilogue: warp w may only touch TMEM lanes [32*(w%4), 32*(w%4)+32); group (w-2)/4 takes its share of columns.
+  using elem = typename Prec::elem;
+  // Warp w may only touch TMEM lanes [32*(w%4), 32*(w%4)+32); group (w-2)/4 takes its share of the columns.
   constexpr int kEpiThreads = 32 * epi_warps(BLOCK_N);
   constexpr int kColsPerGroup = BLOCK_N / (epi_warps(BLOCK_N) / 4);
   const int q = warp & 3;
@@ -111,18 +173,17 @@ B200DP_DEVINL void igemm_epilogue(const IgemmParams& p, uint32_t tmem_base, uint
   }
   mbar_wait(tmem_full_bar, 0);
   tc_fence_after();
-  __nv_bfloat16* out_row = p.out + m * p.n_total + n_tile * BLOCK_N;
+  elem* out_row = static_cast<elem*>(p.out) + m * p.n_total + n_tile * BLOCK_N;
 #pragma unroll 1
   for (int c = grp * kColsPerGroup; c < (grp + 1) * kColsPerGroup; c += 32) {
     uint32_t v[32];
     tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + c, v);
-    uint4 act[4];
+    Row32<Prec> act;
     if constexpr (BNR) {
       // the previous block's output row, same [M][N] layout as the gradient being written; in flight
       // while the TMEM load completes
-      const uint4* a_row = reinterpret_cast<const uint4*>(p.bnr_a + m * p.n_total + n_tile * BLOCK_N + c);
-#pragma unroll
-      for (int j = 0; j < 4; ++j) act[j] = (valid && p.partial == nullptr) ? __ldg(a_row + j) : make_uint4(0u, 0u, 0u, 0u);
+      act = row32_load<Prec>(static_cast<const elem*>(p.bnr_a) + m * p.n_total + n_tile * BLOCK_N + c,
+                             valid && p.partial == nullptr);
     }
     tmem_ld_wait();
     if (p.partial != nullptr) {
@@ -146,31 +207,18 @@ B200DP_DEVINL void igemm_epilogue(const IgemmParams& p, uint32_t tmem_base, uint
         f[4 * j] += bv.x; f[4 * j + 1] += bv.y; f[4 * j + 2] += bv.z; f[4 * j + 3] += bv.w;
       }
     }
-    uint32_t packed[16];
-#pragma unroll
-    for (int j = 0; j < 16; ++j) packed[j] = pack_bf16x2(f[2 * j], f[2 * j + 1]);
-    if (valid) {
-      uint4* dst = reinterpret_cast<uint4*>(out_row + c);
-#pragma unroll
-      for (int j = 0; j < 4; ++j)
-        dst[j] = make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
-    }
+    row32_store<Prec>(out_row + c, valid, f);     // f[] now holds the stored (rounded) values
     if constexpr (BNR) {
       // T1 = sum_{a>0} g and T2 = sum_{a>0} g*a over the 32 rows of this warp; beta and gamma enter once
-      // per channel afterwards: S2 = (T2 - beta*T1) / gamma.  g is the value as stored (bf16-rounded).
-      const uint32_t aw[16] = {act[0].x, act[0].y, act[0].z, act[0].w, act[1].x, act[1].y, act[1].z, act[1].w,
-                               act[2].x, act[2].y, act[2].z, act[2].w, act[3].x, act[3].y, act[3].z, act[3].w};
-      float s1[32], s2[32];
+      // per channel afterwards: S2 = (T2 - beta*T1) / gamma.  g is the value as stored.
+      float a[32], s2[32];
+      row32_unpack<Prec>(act, a);
 #pragma unroll
-      for (int j = 0; j < 16; ++j) {
-        const float2 g = unpack_bf16x2(packed[j]);
-        const float2 a = unpack_bf16x2(aw[j]);
-        s1[2 * j] = (valid && a.x > 0.f) ? g.x : 0.f;
-        s1[2 * j + 1] = (valid && a.y > 0.f) ? g.y : 0.f;
-        s2[2 * j] = s1[2 * j] * a.x;
-        s2[2 * j + 1] = s1[2 * j + 1] * a.y;
+      for (int j = 0; j < 32; ++j) {
+        f[j] = (valid && a[j] > 0.f) ? f[j] : 0.f;
+        s2[j] = f[j] * a[j];
       }
-      const float t1 = warp_transpose_sum(s1, lane);
+      const float t1 = warp_transpose_sum(f, lane);
       const float t2 = warp_transpose_sum(s2, lane);
       const int ch = n_tile * BLOCK_N + c + lane;
       const float gam = __ldg(p.bnr_gamma + ch);
@@ -179,18 +227,13 @@ B200DP_DEVINL void igemm_epilogue(const IgemmParams& p, uint32_t tmem_base, uint
       scratch[q * 2 * BLOCK_N + c + lane] = t1;
       scratch[q * 2 * BLOCK_N + BLOCK_N + c + lane] = u2;
     } else if (p.stats != nullptr) {
-      // statistics of the values as stored (bf16-rounded), so that the
-      // normalisation that follows is exactly centred on what it reads.
-      float s1[32], s2[32];
+      float s2[32];
 #pragma unroll
-      for (int j = 0; j < 16; ++j) {
-        const float2 r = unpack_bf16x2(packed[j]);
-        s1[2 * j] = valid ? r.x : 0.f;
-        s1[2 * j + 1] = valid ? r.y : 0.f;
-        s2[2 * j] = s1[2 * j] * s1[2 * j];
-        s2[2 * j + 1] = s1[2 * j + 1] * s1[2 * j + 1];
+      for (int j = 0; j < 32; ++j) {
+        f[j] = valid ? f[j] : 0.f;
+        s2[j] = f[j] * f[j];
       }
-      const float t1 = warp_transpose_sum(s1, lane);
+      const float t1 = warp_transpose_sum(f, lane);
       const float t2 = warp_transpose_sum(s2, lane);
       if (p.stats_via_smem) {
         // scratch is operand memory: every MMA that read it has completed (tmem_full_bar fired)
@@ -226,12 +269,12 @@ B200DP_DEVINL void igemm_epilogue(const IgemmParams& p, uint32_t tmem_base, uint
 // STAGES == 1 is the single-K-block case (layer 0: one 64-wide K block per tile).  Such a CTA is a pure
 // latency chain (TMA -> one MMA group -> epilogue), so it is compiled for 5 CTAs per SM (25 KiB of
 // shared memory, 64 TMEM columns each) instead of the 2 that a 4-stage ring allows.
-template <int BLOCK_N, int STAGES, bool BNR>
+template <class Prec, int BLOCK_N, int STAGES, bool BNR>
 B200DP_DEVINL void conv_igemm_body(const CUtensorMap& tmA, const CUtensorMap& tmB, const IgemmParams& p) {
-  constexpr int kBStageBytes = BLOCK_N * kBlockK * 2;
+  constexpr int kBStageBytes = BLOCK_N * kRowBytes;
   constexpr int kStageBytes = kAStageBytes + kBStageBytes;
   constexpr uint32_t kTmemCols = BLOCK_N < 32 ? 32 : BLOCK_N;
-  constexpr uint32_t kIdesc = umma_idesc_bf16(kBlockM, BLOCK_N, 0, 0);
+  constexpr uint32_t kIdesc = umma_idesc(kBlockM, BLOCK_N, 0, 0, Prec::kFmt);
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -294,8 +337,8 @@ B200DP_DEVINL void conv_igemm_body(const CUtensorMap& tmA, const CUtensorMap& tm
           ds = tap % 3 - 1;
         }
         uint8_t* a_dst = smem + stage * kStageBytes;
-        tma_load_4d(a_dst, &tmA, &full_bar[stage], cb * kBlockK, ds, h0 + dr, n0);
-        tma_load_2d(a_dst + kAStageBytes, &tmB, &full_bar[stage], kb * kBlockK, n_tile * BLOCK_N);
+        tma_load_4d(a_dst, &tmA, &full_bar[stage], cb * Prec::kBlockK, ds, h0 + dr, n0);
+        tma_load_2d(a_dst + kAStageBytes, &tmB, &full_bar[stage], kb * Prec::kBlockK, n_tile * BLOCK_N);
         if (++stage == STAGES) {
           stage = 0;
           phase ^= 1;
@@ -312,11 +355,11 @@ B200DP_DEVINL void conv_igemm_body(const CUtensorMap& tmA, const CUtensorMap& tm
         const uint32_t a_addr = smem_u32(smem + stage * kStageBytes);
         const uint32_t b_addr = a_addr + kAStageBytes;
 #pragma unroll
-        for (int k = 0; k < kBlockK / kUmmaK; ++k) {
-          // K-major SW128: 8-row groups are 1024 B apart; a K step of 16 bf16 is +32 B inside the span.
-          const uint64_t da = umma_smem_desc(a_addr + k * kUmmaK * 2, 16, 1024);
-          const uint64_t db = umma_smem_desc(b_addr + k * kUmmaK * 2, 16, 1024);
-          umma_bf16(tmem_base, da, db, kIdesc, (kb | k) != 0);
+        for (int k = 0; k < Prec::kBlockK / Prec::kUmmaK; ++k) {
+          // K-major SW128: 8-row groups are 1024 B apart; one MMA's K extent (16 bf16 / 8 tf32) is +32 B in the span.
+          const uint64_t da = umma_smem_desc(a_addr + k * 32, 16, 1024);
+          const uint64_t db = umma_smem_desc(b_addr + k * 32, 16, 1024);
+          umma_ss<Prec>(tmem_base, da, db, kIdesc, (kb | k) != 0);
         }
         umma_commit(&empty_bar[stage]);
         if (++stage == STAGES) {
@@ -327,7 +370,7 @@ B200DP_DEVINL void conv_igemm_body(const CUtensorMap& tmA, const CUtensorMap& tm
       umma_commit(tmem_full_bar);
     }
   } else {
-    igemm_epilogue<BLOCK_N, BNR>(p, tmem_base, tmem_full_bar, warp, lane, m_tile, n_tile, reinterpret_cast<float*>(smem),
+    igemm_epilogue<Prec, BLOCK_N, BNR>(p, tmem_base, tmem_full_bar, warp, lane, m_tile, n_tile, reinterpret_cast<float*>(smem),
                                  reinterpret_cast<float*>(smem + STAGES * kStageBytes + 256));
   }
   __syncthreads();
@@ -337,19 +380,19 @@ B200DP_DEVINL void conv_igemm_body(const CUtensorMap& tmA, const CUtensorMap& tm
   }
 }
 
-template <int BLOCK_N, int STAGES>
+template <class Prec, int BLOCK_N, int STAGES>
 __global__ void __launch_bounds__(cta_threads(BLOCK_N), STAGES == 1 ? 5 : 1)
     conv_igemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                       const IgemmParams p) {
-  conv_igemm_body<BLOCK_N, STAGES, false>(tmA, tmB, p);
+  conv_igemm_body<Prec, BLOCK_N, STAGES, false>(tmA, tmB, p);
 }
 
 // dgrad whose epilogue also accumulates the previous block's BatchNorm-backward sums (IgemmParams::bnr_*)
-template <int BLOCK_N, int STAGES>
+template <class Prec, int BLOCK_N, int STAGES>
 __global__ void __launch_bounds__(cta_threads(BLOCK_N))
     conv_dgrad_bnr_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                           const IgemmParams p) {
-  conv_igemm_body<BLOCK_N, STAGES, true>(tmA, tmB, p);
+  conv_igemm_body<Prec, BLOCK_N, STAGES, true>(tmA, tmB, p);
 }
 
 // ---------------------------------------------------------------------------
@@ -363,12 +406,12 @@ __global__ void __launch_bounds__(cta_threads(BLOCK_N))
 // with a cluster multicast to the empty / tmem-full barriers of both CTAs; each CTA drains its own
 // TMEM half in its epilogue warps.
 // ---------------------------------------------------------------------------
-template <int BLOCK_N, int STAGES, bool BNR>
+template <class Prec, int BLOCK_N, int STAGES, bool BNR>
 B200DP_DEVINL void conv_igemm_2cta_body(const CUtensorMap& tmA, const CUtensorMap& tmB, const IgemmParams& p) {
-  constexpr int kBHalfBytes = (BLOCK_N / 2) * kBlockK * 2;
+  constexpr int kBHalfBytes = (BLOCK_N / 2) * kRowBytes;
   constexpr int kStageBytes = kAStageBytes + kBHalfBytes;
   constexpr uint32_t kTmemCols = BLOCK_N < 32 ? 32 : BLOCK_N;
-  constexpr uint32_t kIdesc = umma_idesc_bf16(2 * kBlockM, BLOCK_N, 0, 0);
+  constexpr uint32_t kIdesc = umma_idesc(2 * kBlockM, BLOCK_N, 0, 0, Prec::kFmt);
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -433,8 +476,8 @@ B200DP_DEVINL void conv_igemm_2cta_body(const CUtensorMap& tmA, const CUtensorMa
           ds = tap % 3 - 1;
         }
         uint8_t* a_dst = smem + stage * kStageBytes;
-        tma_load_4d_2cta(a_dst, &tmA, &full_bar[stage], cb * kBlockK, ds, h0 + dr, n0);
-        tma_load_2d_2cta(a_dst + kAStageBytes, &tmB, &full_bar[stage], kb * kBlockK,
+        tma_load_4d_2cta(a_dst, &tmA, &full_bar[stage], cb * Prec::kBlockK, ds, h0 + dr, n0);
+        tma_load_2d_2cta(a_dst + kAStageBytes, &tmB, &full_bar[stage], kb * Prec::kBlockK,
                          n_tile * BLOCK_N + static_cast<int>(cta_rank) * (BLOCK_N / 2));
         if (++stage == STAGES) {
           stage = 0;
@@ -452,10 +495,10 @@ B200DP_DEVINL void conv_igemm_2cta_body(const CUtensorMap& tmA, const CUtensorMa
         const uint32_t a_addr = smem_u32(smem + stage * kStageBytes);
         const uint32_t b_addr = a_addr + kAStageBytes;
 #pragma unroll
-        for (int k = 0; k < kBlockK / kUmmaK; ++k) {
-          const uint64_t da = umma_smem_desc(a_addr + k * kUmmaK * 2, 16, 1024);
-          const uint64_t db = umma_smem_desc(b_addr + k * kUmmaK * 2, 16, 1024);
-          umma_bf16_2cta(tmem_base, da, db, kIdesc, (kb | k) != 0);
+        for (int k = 0; k < Prec::kBlockK / Prec::kUmmaK; ++k) {
+          const uint64_t da = umma_smem_desc(a_addr + k * 32, 16, 1024);
+          const uint64_t db = umma_smem_desc(b_addr + k * 32, 16, 1024);
+          umma_ss_2cta<Prec>(tmem_base, da, db, kIdesc, (kb | k) != 0);
         }
         umma_commit_2cta(&empty_bar[stage], 0b11);
         if (++stage == STAGES) {
@@ -466,7 +509,7 @@ B200DP_DEVINL void conv_igemm_2cta_body(const CUtensorMap& tmA, const CUtensorMa
       umma_commit_2cta(tmem_full_bar, 0b11);
     }
   } else {
-    igemm_epilogue<BLOCK_N, BNR>(p, tmem_base, tmem_full_bar, warp, lane, m_tile, n_tile, reinterpret_cast<float*>(smem),
+    igemm_epilogue<Prec, BLOCK_N, BNR>(p, tmem_base, tmem_full_bar, warp, lane, m_tile, n_tile, reinterpret_cast<float*>(smem),
                                  reinterpret_cast<float*>(smem + STAGES * kStageBytes + 256));
   }
   __syncthreads();
@@ -478,25 +521,25 @@ B200DP_DEVINL void conv_igemm_2cta_body(const CUtensorMap& tmA, const CUtensorMa
   }
 }
 
-template <int BLOCK_N, int STAGES>
+template <class Prec, int BLOCK_N, int STAGES>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(cta_threads(BLOCK_N))
     conv_igemm_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                            const IgemmParams p) {
-  conv_igemm_2cta_body<BLOCK_N, STAGES, false>(tmA, tmB, p);
+  conv_igemm_2cta_body<Prec, BLOCK_N, STAGES, false>(tmA, tmB, p);
 }
 
-template <int BLOCK_N, int STAGES>
+template <class Prec, int BLOCK_N, int STAGES>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(cta_threads(BLOCK_N))
     conv_dgrad_bnr_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                                const IgemmParams p) {
-  conv_igemm_2cta_body<BLOCK_N, STAGES, true>(tmA, tmB, p);
+  conv_igemm_2cta_body<Prec, BLOCK_N, STAGES, true>(tmA, tmB, p);
 }
 
-// Split-K epilogue: partial fp32 [M][N] -> (+bias) -> bf16 out, fused BatchNorm statistics of the
-// rounded values, and the workspace is cleared again for its next user.
+// Split-K epilogue: partial fp32 [M][N] -> (+bias) -> activation type, fused BatchNorm statistics of the
+// stored values, and the workspace is cleared again for its next user.
+template <class T>
 __global__ void __launch_bounds__(256) splitk_finalize_kernel(float* __restrict__ partial,
-                                                              const float* __restrict__ bias,
-                                                              __nv_bfloat16* __restrict__ out,
+                                                              const float* __restrict__ bias, T* __restrict__ out,
                                                               float* __restrict__ stats, long M, int N) {
   extern __shared__ float red[];  // [rows_per_block][N] x 2 (only with stats)
   pdl_launch_dependents();
@@ -517,19 +560,13 @@ __global__ void __launch_bounds__(256) splitk_finalize_kernel(float* __restrict_
       const float4 lo = src[0], hi = src[1];
       src[0] = make_float4(0.f, 0.f, 0.f, 0.f);
       src[1] = make_float4(0.f, 0.f, 0.f, 0.f);
-      uint4 o;
-      o.x = pack_bf16x2(lo.x + b[0], lo.y + b[1]);
-      o.y = pack_bf16x2(lo.z + b[2], lo.w + b[3]);
-      o.z = pack_bf16x2(hi.x + b[4], hi.y + b[5]);
-      o.w = pack_bf16x2(hi.z + b[6], hi.w + b[7]);
-      *reinterpret_cast<uint4*>(out + r * N + c0) = o;
+      F8 o = {{lo.x + b[0], lo.y + b[1], lo.z + b[2], lo.w + b[3], hi.x + b[4], hi.y + b[5], hi.z + b[6], hi.w + b[7]}};
+      st8(out + r * N + c0, o);          // o now holds the values as stored
       if (stats != nullptr) {
-        const float2 r0 = unpack_bf16x2(o.x), r1 = unpack_bf16x2(o.y), r2 = unpack_bf16x2(o.z), r3 = unpack_bf16x2(o.w);
-        const float vals[8] = {r0.x, r0.y, r1.x, r1.y, r2.x, r2.y, r3.x, r3.y};
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-          s1[j] += vals[j];
-          s2[j] = fmaf(vals[j], vals[j], s2[j]);
+          s1[j] += o.v[j];
+          s2[j] = fmaf(o.v[j], o.v[j], s2[j]);
         }
       }
     }
@@ -558,10 +595,11 @@ __global__ void __launch_bounds__(256) splitk_finalize_kernel(float* __restrict_
 }
 
 // Split-K epilogue of a dgrad that also feeds the previous block's BatchNorm backward: partial fp32
-// [M][N] -> bf16 dL/da, workspace cleared, and S1 / S2 of IgemmParams::bnr_* from the rounded values.
-__global__ void __launch_bounds__(256) splitk_finalize_bnr_kernel(float* __restrict__ partial,
-                                                                  __nv_bfloat16* __restrict__ out,
-                                                                  const __nv_bfloat16* __restrict__ act,
+// [M][N] -> dL/da in the activation type, workspace cleared, and S1 / S2 of IgemmParams::bnr_* from the
+// stored values.
+template <class T>
+__global__ void __launch_bounds__(256) splitk_finalize_bnr_kernel(float* __restrict__ partial, T* __restrict__ out,
+                                                                  const T* __restrict__ act,
                                                                   const float* __restrict__ gamma,
                                                                   const float* __restrict__ beta,
                                                                   float* __restrict__ sums, long M, int N) {
@@ -579,24 +617,16 @@ __global__ void __launch_bounds__(256) splitk_finalize_bnr_kernel(float* __restr
          r += static_cast<long>(gridDim.x) * rows_per_block) {
       float4* src = reinterpret_cast<float4*>(partial + r * N + c0);
       const float4 lo = src[0], hi = src[1];
-      const uint4 a = __ldg(reinterpret_cast<const uint4*>(act + r * N + c0));
+      const F8 av = ld8(act + r * N + c0);
       src[0] = make_float4(0.f, 0.f, 0.f, 0.f);
       src[1] = make_float4(0.f, 0.f, 0.f, 0.f);
-      uint4 o;
-      o.x = pack_bf16x2(lo.x, lo.y);
-      o.y = pack_bf16x2(lo.z, lo.w);
-      o.z = pack_bf16x2(hi.x, hi.y);
-      o.w = pack_bf16x2(hi.z, hi.w);
-      *reinterpret_cast<uint4*>(out + r * N + c0) = o;
-      const float2 g0 = unpack_bf16x2(o.x), g1 = unpack_bf16x2(o.y), g2 = unpack_bf16x2(o.z), g3 = unpack_bf16x2(o.w);
-      const float2 a0 = unpack_bf16x2(a.x), a1 = unpack_bf16x2(a.y), a2 = unpack_bf16x2(a.z), a3 = unpack_bf16x2(a.w);
-      const float g[8] = {g0.x, g0.y, g1.x, g1.y, g2.x, g2.y, g3.x, g3.y};
-      const float av[8] = {a0.x, a0.y, a1.x, a1.y, a2.x, a2.y, a3.x, a3.y};
+      F8 g = {{lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w}};
+      st8(out + r * N + c0, g);          // g now holds the values as stored
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        const float d = av[j] > 0.f ? g[j] : 0.f;
+        const float d = av.v[j] > 0.f ? g.v[j] : 0.f;
         s1[j] += d;
-        s2[j] = fmaf(d, av[j], s2[j]);
+        s2[j] = fmaf(d, av.v[j], s2[j]);
       }
     }
   }
@@ -627,11 +657,11 @@ __global__ void __launch_bounds__(256) splitk_finalize_bnr_kernel(float* __restr
 // weight gradient
 // ---------------------------------------------------------------------------
 struct WgradParams {
-  int H, W, TH, TN;  // a K block is TN images x TH rows x W columns = 64 pixels
+  int H, W, TH, TN;  // a K block is TN images x TH rows x W columns = 64 pixels (bf16) or 32 pixels (tf32)
   int taps;
   int cin, cout;
   int co_tiles, ci_tiles;
-  int a_boxes;  // 64-channel dY boxes that really exist in this M tile (1 when Cout == 64, else 2)
+  int a_boxes;  // dY boxes (Prec::kBlockK channels each) that really exist in this M tile: min(Cout, 128) / kBlockK
   int kblocks_total, kblocks_per_split;
   int ld_out, cin_valid;
   int use_red;
@@ -654,14 +684,20 @@ struct WgradPushParams : WgradParams {
   float* peer_stage[8];  // every rank's staging buffer: slot of source rank s starts at stage_base + s*per4*4
 };
 
-template <int BLOCK_N, int STAGES, bool PUSH, typename ParamsT>
+// pixels (GEMM K) per pipeline stage of the weight-gradient kernel: 64 for bf16, 32 for tf32 -- the same bytes
+constexpr int wgrad_pixels(bool tf32) { return tf32 ? 32 : 64; }
+
+template <class Prec, int BLOCK_N, int STAGES, bool PUSH, typename ParamsT>
 B200DP_DEVINL void conv_wgrad_body(const CUtensorMap& tmDY, const CUtensorMap& tmX, const ParamsT& p) {
-  constexpr int kSubTileBytes = 64 * 64 * 2;  // one (64 channels x 64 pixels) box, 8 KiB
-  constexpr int kABytes = 2 * kSubTileBytes;
-  constexpr int kBBytes = (BLOCK_N / 64) * kSubTileBytes;
+  constexpr int kPix = wgrad_pixels(Prec::kTf32);
+  constexpr int kCh = Prec::kBlockK;                  // channels per box = one 128-byte row
+  constexpr int kSubTileBytes = kPix * kRowBytes;     // one (kCh channels x kPix pixels) box: 8 KiB / 4 KiB
+  constexpr int kABoxes = kBlockM / kCh;
+  constexpr int kABytes = kABoxes * kSubTileBytes;    // 16 KiB
+  constexpr int kBBytes = (BLOCK_N / kCh) * kSubTileBytes;
   constexpr int kStageBytes = kABytes + kBBytes;
   constexpr uint32_t kTmemCols = BLOCK_N < 32 ? 32 : BLOCK_N;
-  constexpr uint32_t kIdesc = umma_idesc_bf16(kBlockM, BLOCK_N, 1, 1);
+  constexpr uint32_t kIdesc = umma_idesc(kBlockM, BLOCK_N, 1, 1, Prec::kFmt);
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -726,16 +762,17 @@ B200DP_DEVINL void conv_wgrad_body(const CUtensorMap& tmDY, const CUtensorMap& t
             h0 = 0;
           }
           uint8_t* a_dst = smem + stage * kStageBytes;
-          // dY tile: [64 pixels][64 channels] per box, pixels kb*64 .. +63
+          // dY tile: [kPix pixels][kCh channels] per box, pixels kb*kPix .. (boxes past Cout repeat box 0:
+          // their output rows are never stored)
 #pragma unroll
-          for (int j = 0; j < 2; ++j) {
-            const int co = co_tile * kBlockM + (j < p.a_boxes ? j * 64 : 0);
-            tma_load_2d(a_dst + j * kSubTileBytes, &tmDY, &full_bar[stage], co, kb * 64);
+          for (int j = 0; j < kABoxes; ++j) {
+            const int co = co_tile * kBlockM + (j < p.a_boxes ? j * kCh : 0);
+            tma_load_2d(a_dst + j * kSubTileBytes, &tmDY, &full_bar[stage], co, kb * kPix);
           }
           uint8_t* b_dst = a_dst + kABytes;
 #pragma unroll
-          for (int j = 0; j < BLOCK_N / 64; ++j)
-            tma_load_4d(b_dst + j * kSubTileBytes, &tmX, &full_bar[stage], ci_tile * BLOCK_N + j * 64, ds,
+          for (int j = 0; j < BLOCK_N / kCh; ++j)
+            tma_load_4d(b_dst + j * kSubTileBytes, &tmX, &full_bar[stage], ci_tile * BLOCK_N + j * kCh, ds,
                         h0 + dr, n0);
           if (++stage == STAGES) {
             stage = 0;
@@ -753,12 +790,13 @@ B200DP_DEVINL void conv_wgrad_body(const CUtensorMap& tmDY, const CUtensorMap& t
           const uint32_t a_addr = smem_u32(smem + stage * kStageBytes);
           const uint32_t b_addr = a_addr + kABytes;
 #pragma unroll
-          for (int k = 0; k < 64 / kUmmaK; ++k) {
-            // MN-major SW128: rows are pixels (K), 128 B each; 8-pixel groups are 1024 B apart (SBO),
-            // 64-channel column blocks are one sub-tile apart (LBO); 16 pixels per MMA = +2048 B.
-            const uint64_t da = umma_smem_desc(a_addr + k * kUmmaK * 128, kSubTileBytes, 1024);
-            const uint64_t db = umma_smem_desc(b_addr + k * kUmmaK * 128, kSubTileBytes, 1024);
-            umma_bf16(tmem_base, da, db, kIdesc, (kb | k) != 0);
+          for (int k = 0; k < kPix / Prec::kUmmaK; ++k) {
+            // MN-major SW128: rows are pixels (K), 128 B each; 8-pixel groups are 1024 B apart (SBO), column
+            // blocks of one 128-byte row (64 bf16 / 32 tf32 channels) are one sub-tile apart (LBO); the pixels of
+            // one MMA (16 / 8) are +2048 / +1024 B.
+            const uint64_t da = umma_smem_desc(a_addr + k * Prec::kUmmaK * kRowBytes, kSubTileBytes, 1024);
+            const uint64_t db = umma_smem_desc(b_addr + k * Prec::kUmmaK * kRowBytes, kSubTileBytes, 1024);
+            umma_ss<Prec>(tmem_base, da, db, kIdesc, (kb | k) != 0);
           }
           umma_commit(&empty_bar[stage]);
           if (++stage == STAGES) {
@@ -860,11 +898,11 @@ B200DP_DEVINL void conv_wgrad_body(const CUtensorMap& tmDY, const CUtensorMap& t
   }
 }
 
-template <int BLOCK_N, int STAGES>
+template <class Prec, int BLOCK_N, int STAGES>
 __global__ void __launch_bounds__(cta_threads(BLOCK_N))
     conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ CUtensorMap tmX,
                       const WgradParams p) {
-  conv_wgrad_body<BLOCK_N, STAGES, false, WgradParams>(tmDY, tmX, p);
+  conv_wgrad_body<Prec, BLOCK_N, STAGES, false, WgradParams>(tmDY, tmX, p);
 }
 
 // Weight gradient + the transfer half of the gradient reduce-scatter (WgradParams::peer_stage ...).
@@ -872,7 +910,7 @@ template <int BLOCK_N, int STAGES>
 __global__ void __launch_bounds__(cta_threads(BLOCK_N))
     conv_wgrad_push_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ CUtensorMap tmX,
                            const WgradPushParams p) {
-  conv_wgrad_body<BLOCK_N, STAGES, true, WgradPushParams>(tmDY, tmX, p);
+  conv_wgrad_body<PrecBf16, BLOCK_N, STAGES, true, WgradPushParams>(tmDY, tmX, p);
 }
 
 // ---------------------------------------------------------------------------
@@ -893,22 +931,24 @@ static PFN_cuTensorMapEncodeTiled_v12000 get_encode_fn() {
   return fn;
 }
 
-// bf16 tensor map, 128-byte swizzle, out-of-bounds elements read as zero.
-static int make_tmap(CUtensorMap* tm, const void* base, int rank, const uint64_t* dims, const uint32_t* box) {
+// Tensor map over 2-byte (bf16) or 4-byte elements; 4-byte maps use the TFLOAT32 type, i.e. the TMA unit rounds the
+// fp32 data to tf32 (round to nearest) on its way into shared memory.  128-byte swizzle, out-of-bounds = zero.
+static int make_tmap(CUtensorMap* tm, const void* base, int rank, const uint64_t* dims, const uint32_t* box,
+                     int elem_bytes = 2) {
   auto fn = get_encode_fn();
   if (fn == nullptr) return B200DP_ENOSYS;
   cuuint64_t gdim[4];
   cuuint64_t gstride[3];
   cuuint32_t bdim[4];
   cuuint32_t estr[4] = {1, 1, 1, 1};
-  uint64_t stride = 2;
+  uint64_t stride = static_cast<uint64_t>(elem_bytes);
   for (int i = 0; i < rank; ++i) {
     gdim[i] = dims[i];
     bdim[i] = box[i];
     stride *= dims[i];
     if (i < rank - 1) gstride[i] = stride;
   }
-  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), gdim, gstride, bdim, estr,
+  CUresult r = fn(tm, elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_TFLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), gdim, gstride, bdim, estr,
                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
@@ -944,12 +984,12 @@ static bool short_k_enabled() {
   return on;
 }
 
-template <int BLOCK_N, int STAGES>
+template <class Prec, int BLOCK_N, int STAGES>
 static int launch_igemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const IgemmParams& p, int m_tiles,
                         int splits, cudaStream_t stream) {
-  constexpr int smem = STAGES * (kAStageBytes + BLOCK_N * kBlockK * 2) + 1024 + tail_bytes(BLOCK_N);
+  constexpr int smem = STAGES * (kAStageBytes + BLOCK_N * kRowBytes) + 1024 + tail_bytes(BLOCK_N);
   static bool configured = false;
-  auto kern = conv_igemm_kernel<BLOCK_N, STAGES>;
+  auto kern = conv_igemm_kernel<Prec, BLOCK_N, STAGES>;
   if (!configured) {
     B200DP_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     configured = true;
@@ -959,12 +999,12 @@ static int launch_igemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Ig
   return 0;
 }
 
-template <int BLOCK_N, int STAGES>
+template <class Prec, int BLOCK_N, int STAGES>
 static int launch_igemm_2cta(const CUtensorMap& tmA, const CUtensorMap& tmB, const IgemmParams& p, int m_tiles,
                              int splits, cudaStream_t stream) {
-  constexpr int smem = STAGES * (kAStageBytes + (BLOCK_N / 2) * kBlockK * 2) + 1024 + tail_bytes(BLOCK_N);
+  constexpr int smem = STAGES * (kAStageBytes + (BLOCK_N / 2) * kRowBytes) + 1024 + tail_bytes(BLOCK_N);
   static bool configured = false;
-  auto kern = conv_igemm_2cta_kernel<BLOCK_N, STAGES>;
+  auto kern = conv_igemm_2cta_kernel<Prec, BLOCK_N, STAGES>;
   if (!configured) {
     B200DP_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     configured = true;
@@ -974,12 +1014,12 @@ static int launch_igemm_2cta(const CUtensorMap& tmA, const CUtensorMap& tmB, con
   return 0;
 }
 
-template <int BLOCK_N, int STAGES>
+template <class Prec, int BLOCK_N, int STAGES>
 static int launch_dgrad_bnr(const CUtensorMap& tmA, const CUtensorMap& tmB, const IgemmParams& p, int m_tiles,
                             int splits, cudaStream_t stream) {
-  constexpr int smem = STAGES * (kAStageBytes + BLOCK_N * kBlockK * 2) + 1024 + tail_bytes(BLOCK_N);
+  constexpr int smem = STAGES * (kAStageBytes + BLOCK_N * kRowBytes) + 1024 + tail_bytes(BLOCK_N);
   static bool configured = false;
-  auto kern = conv_dgrad_bnr_kernel<BLOCK_N, STAGES>;
+  auto kern = conv_dgrad_bnr_kernel<Prec, BLOCK_N, STAGES>;
   if (!configured) {
     B200DP_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     configured = true;
@@ -989,12 +1029,12 @@ static int launch_dgrad_bnr(const CUtensorMap& tmA, const CUtensorMap& tmB, cons
   return 0;
 }
 
-template <int BLOCK_N, int STAGES>
+template <class Prec, int BLOCK_N, int STAGES>
 static int launch_dgrad_bnr_2cta(const CUtensorMap& tmA, const CUtensorMap& tmB, const IgemmParams& p, int m_tiles,
                                  int splits, cudaStream_t stream) {
-  constexpr int smem = STAGES * (kAStageBytes + (BLOCK_N / 2) * kBlockK * 2) + 1024 + tail_bytes(BLOCK_N);
+  constexpr int smem = STAGES * (kAStageBytes + (BLOCK_N / 2) * kRowBytes) + 1024 + tail_bytes(BLOCK_N);
   static bool configured = false;
-  auto kern = conv_dgrad_bnr_2cta_kernel<BLOCK_N, STAGES>;
+  auto kern = conv_dgrad_bnr_2cta_kernel<Prec, BLOCK_N, STAGES>;
   if (!configured) {
     B200DP_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     configured = true;
@@ -1004,12 +1044,12 @@ static int launch_dgrad_bnr_2cta(const CUtensorMap& tmA, const CUtensorMap& tmB,
   return 0;
 }
 
-template <int BLOCK_N, int STAGES>
+template <class Prec, int BLOCK_N, int STAGES>
 static int launch_wgrad(const CUtensorMap& tmDY, const CUtensorMap& tmX, const WgradParams& p, int tiles,
                         int splits, cudaStream_t stream) {
-  constexpr int smem = STAGES * (2 * 8192 + (BLOCK_N / 64) * 8192) + 1024 + tail_bytes(BLOCK_N);
+  constexpr int smem = STAGES * (kBlockM + BLOCK_N) * kRowBytes + 1024 + tail_bytes(BLOCK_N);
   static bool configured = false;
-  auto kern = conv_wgrad_kernel<BLOCK_N, STAGES>;
+  auto kern = conv_wgrad_kernel<Prec, BLOCK_N, STAGES>;
   if (!configured) {
     B200DP_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     configured = true;
@@ -1022,7 +1062,7 @@ static int launch_wgrad(const CUtensorMap& tmDY, const CUtensorMap& tmX, const W
 template <int BLOCK_N, int STAGES>
 static int launch_wgrad_push(const CUtensorMap& tmDY, const CUtensorMap& tmX, const WgradPushParams& p, int tiles,
                              int splits, cudaStream_t stream) {
-  constexpr int smem = STAGES * (2 * 8192 + (BLOCK_N / 64) * 8192) + 1024 + tail_bytes(BLOCK_N);
+  constexpr int smem = STAGES * (kBlockM + BLOCK_N) * kRowBytes + 1024 + tail_bytes(BLOCK_N);
   static bool configured = false;
   auto kern = conv_wgrad_push_kernel<BLOCK_N, STAGES>;
   if (!configured) {
@@ -1055,11 +1095,14 @@ struct BnReduceArgs {
   float* sums;
 };
 
+template <class Prec>
 static int conv_igemm_impl(const void* act, const void* wgt, const float* bias, void* out, float* stats,
                            float* workspace, int B, int H, int W, int Cin, int Cout, int taps, int block_n, int split_k,
                            int cta_pair, cudaStream_t stream, const BnReduceArgs* bnr = nullptr) {
-  if ((taps != 9 && taps != 1) || Cin % 64 != 0 || Cout % 32 != 0 || B <= 0) {
-    set_error("conv_igemm: unsupported shape B=%d H=%d W=%d Cin=%d Cout=%d taps=%d", B, H, W, Cin, Cout, taps);
+  using elem = typename Prec::elem;
+  if ((taps != 9 && taps != 1) || Cin % Prec::kBlockK != 0 || Cout % 32 != 0 || B <= 0) {
+    set_error("conv_igemm: unsupported shape B=%d H=%d W=%d Cin=%d Cout=%d taps=%d (Cin must be a multiple of %d)", B,
+              H, W, Cin, Cout, taps, Prec::kBlockK);
     return B200DP_EINVAL;
   }
   IgemmParams p{};
@@ -1070,11 +1113,11 @@ static int conv_igemm_impl(const void* act, const void* wgt, const float* bias, 
     return B200DP_EINVAL;
   }
   p.taps = taps;
-  p.cin_blocks = Cin / 64;
+  p.cin_blocks = Cin / Prec::kBlockK;
   p.m_total = B * H * W;
   p.n_total = Cout;
   p.bias = bias;
-  p.out = static_cast<__nv_bfloat16*>(out);
+  p.out = out;
   p.stats = stats;
   static const bool stats_smem = [] {
     const char* e = getenv("B200DP_STATS_SMEM");
@@ -1114,8 +1157,8 @@ static int conv_igemm_impl(const void* act, const void* wgt, const float* bias, 
   CUtensorMap tmA, tmB;
   {
     const uint64_t dims[4] = {(uint64_t)Cin, (uint64_t)W, (uint64_t)H, (uint64_t)B};
-    const uint32_t box[4] = {64, (uint32_t)W, (uint32_t)p.TH, (uint32_t)p.TN};
-    int rc = make_tmap(&tmA, act, 4, dims, box);
+    const uint32_t box[4] = {(uint32_t)Prec::kBlockK, (uint32_t)W, (uint32_t)p.TH, (uint32_t)p.TN};
+    int rc = make_tmap(&tmA, act, 4, dims, box, Prec::kBytes);
     if (rc) return rc;
   }
   if (cta_pair == 1 && ((m_tiles & 1) || block_n < 64)) {
@@ -1125,8 +1168,8 @@ static int conv_igemm_impl(const void* act, const void* wgt, const float* bias, 
   }
   {
     const uint64_t dims[2] = {(uint64_t)taps * Cin, (uint64_t)Cout};
-    const uint32_t box[2] = {64, (uint32_t)(cta_pair == 1 ? block_n / 2 : block_n)};
-    int rc = make_tmap(&tmB, wgt, 2, dims, box);
+    const uint32_t box[2] = {(uint32_t)Prec::kBlockK, (uint32_t)(cta_pair == 1 ? block_n / 2 : block_n)};
+    int rc = make_tmap(&tmB, wgt, 2, dims, box, Prec::kBytes);
     if (rc) return rc;
   }
   int rc;
@@ -1135,23 +1178,23 @@ static int conv_igemm_impl(const void* act, const void* wgt, const float* bias, 
       set_error("conv_dgrad_bn_reduce: bias / forward statistics cannot be combined with the BatchNorm-backward sums");
       return B200DP_EINVAL;
     }
-    p.bnr_a = static_cast<const __nv_bfloat16*>(bnr->act_out);
+    p.bnr_a = bnr->act_out;
     p.bnr_gamma = bnr->gamma;
     p.bnr_beta = bnr->beta;
     p.bnr_sums = bnr->sums;
     if (cta_pair == 1) {
       switch (block_n) {
-        case 256: rc = launch_dgrad_bnr_2cta<256, 6>(tmA, tmB, p, m_tiles, split_k, stream); break;
-        case 128: rc = launch_dgrad_bnr_2cta<128, 6>(tmA, tmB, p, m_tiles, split_k, stream); break;
-        case 64: rc = launch_dgrad_bnr_2cta<64, 6>(tmA, tmB, p, m_tiles, split_k, stream); break;
+        case 256: rc = launch_dgrad_bnr_2cta<Prec, 256, 6>(tmA, tmB, p, m_tiles, split_k, stream); break;
+        case 128: rc = launch_dgrad_bnr_2cta<Prec, 128, 6>(tmA, tmB, p, m_tiles, split_k, stream); break;
+        case 64: rc = launch_dgrad_bnr_2cta<Prec, 64, 6>(tmA, tmB, p, m_tiles, split_k, stream); break;
         default: set_error("conv_dgrad_bn_reduce: block_n=%d not in {64,128,256} for the CTA-pair kernel", block_n); return B200DP_EINVAL;
       }
     } else {
       switch (block_n) {
-        case 256: rc = launch_dgrad_bnr<256, 4>(tmA, tmB, p, m_tiles, split_k, stream); break;
-        case 128: rc = launch_dgrad_bnr<128, 3>(tmA, tmB, p, m_tiles, split_k, stream); break;
-        case 64: rc = launch_dgrad_bnr<64, 4>(tmA, tmB, p, m_tiles, split_k, stream); break;
-        case 32: rc = launch_dgrad_bnr<32, 4>(tmA, tmB, p, m_tiles, split_k, stream); break;
+        case 256: rc = launch_dgrad_bnr<Prec, 256, 4>(tmA, tmB, p, m_tiles, split_k, stream); break;
+        case 128: rc = launch_dgrad_bnr<Prec, 128, 3>(tmA, tmB, p, m_tiles, split_k, stream); break;
+        case 64: rc = launch_dgrad_bnr<Prec, 64, 4>(tmA, tmB, p, m_tiles, split_k, stream); break;
+        case 32: rc = launch_dgrad_bnr<Prec, 32, 4>(tmA, tmB, p, m_tiles, split_k, stream); break;
         default: set_error("conv_dgrad_bn_reduce: block_n=%d not in {32,64,128,256}", block_n); return B200DP_EINVAL;
       }
     }
@@ -1162,27 +1205,27 @@ static int conv_igemm_impl(const void* act, const void* wgt, const float* bias, 
     long blocks = (static_cast<long>(p.m_total) + rows_per_block * 2 - 1) / (rows_per_block * 2);
     if (blocks > 148 * 4) blocks = 148 * 4;
     if (blocks < 1) blocks = 1;
-    B200DP_CUDA_TRY(launch_pdl(splitk_finalize_bnr_kernel, dim3(static_cast<unsigned>(blocks)), dim3(threads), smem,
-                               stream, workspace, static_cast<__nv_bfloat16*>(out), p.bnr_a, p.bnr_gamma, p.bnr_beta,
-                               p.bnr_sums, static_cast<long>(p.m_total), Cout));
+    B200DP_CUDA_TRY(launch_pdl(splitk_finalize_bnr_kernel<elem>, dim3(static_cast<unsigned>(blocks)), dim3(threads),
+                               smem, stream, workspace, static_cast<elem*>(out), static_cast<const elem*>(p.bnr_a),
+                               p.bnr_gamma, p.bnr_beta, p.bnr_sums, static_cast<long>(p.m_total), Cout));
     return 0;
   }
   if (cta_pair == 1) {
     switch (block_n) {
-      case 256: rc = launch_igemm_2cta<256, 6>(tmA, tmB, p, m_tiles, split_k, stream); break;
-      case 128: rc = launch_igemm_2cta<128, 6>(tmA, tmB, p, m_tiles, split_k, stream); break;
-      case 64: rc = launch_igemm_2cta<64, 6>(tmA, tmB, p, m_tiles, split_k, stream); break;
+      case 256: rc = launch_igemm_2cta<Prec, 256, 6>(tmA, tmB, p, m_tiles, split_k, stream); break;
+      case 128: rc = launch_igemm_2cta<Prec, 128, 6>(tmA, tmB, p, m_tiles, split_k, stream); break;
+      case 64: rc = launch_igemm_2cta<Prec, 64, 6>(tmA, tmB, p, m_tiles, split_k, stream); break;
       default: set_error("conv_igemm: block_n=%d not in {64,128,256} for the CTA-pair kernel", block_n); return B200DP_EINVAL;
     }
   } else
   switch (block_n) {
-    case 256: rc = launch_igemm<256, 4>(tmA, tmB, p, m_tiles, split_k, stream); break;
-    case 128: rc = launch_igemm<128, 3>(tmA, tmB, p, m_tiles, split_k, stream); break;
+    case 256: rc = launch_igemm<Prec, 256, 4>(tmA, tmB, p, m_tiles, split_k, stream); break;
+    case 128: rc = launch_igemm<Prec, 128, 3>(tmA, tmB, p, m_tiles, split_k, stream); break;
     case 64:
-      rc = (p.kb_per_split == 1 && short_k_enabled()) ? launch_igemm<64, 1>(tmA, tmB, p, m_tiles, split_k, stream)
-                                                      : launch_igemm<64, 4>(tmA, tmB, p, m_tiles, split_k, stream);
+      rc = (p.kb_per_split == 1 && short_k_enabled()) ? launch_igemm<Prec, 64, 1>(tmA, tmB, p, m_tiles, split_k, stream)
+                                                      : launch_igemm<Prec, 64, 4>(tmA, tmB, p, m_tiles, split_k, stream);
       break;
-    case 32: rc = launch_igemm<32, 4>(tmA, tmB, p, m_tiles, split_k, stream); break;
+    case 32: rc = launch_igemm<Prec, 32, 4>(tmA, tmB, p, m_tiles, split_k, stream); break;
     default: set_error("conv_igemm: block_n=%d not in {32,64,128,256}", block_n); return B200DP_EINVAL;
   }
   if (rc || split_k == 1) return rc;
@@ -1192,8 +1235,8 @@ static int conv_igemm_impl(const void* act, const void* wgt, const float* bias, 
   long blocks = (static_cast<long>(p.m_total) + rows_per_block * 2 - 1) / (rows_per_block * 2);
   if (blocks > 148 * 4) blocks = 148 * 4;
   if (blocks < 1) blocks = 1;
-  B200DP_CUDA_TRY(launch_pdl(splitk_finalize_kernel, dim3(static_cast<unsigned>(blocks)), dim3(threads), smem, stream,
-                             workspace, bias, static_cast<__nv_bfloat16*>(out), stats, static_cast<long>(p.m_total),
+  B200DP_CUDA_TRY(launch_pdl(splitk_finalize_kernel<elem>, dim3(static_cast<unsigned>(blocks)), dim3(threads), smem,
+                             stream, workspace, bias, static_cast<elem*>(out), stats, static_cast<long>(p.m_total),
                              Cout));
   return 0;
 }
@@ -1201,14 +1244,14 @@ static int conv_igemm_impl(const void* act, const void* wgt, const float* bias, 
 extern "C" int b200dp_conv_igemm(const void* act, const void* wgt, const float* bias, void* out, float* stats,
                                  int B, int H, int W, int Cin, int Cout, int taps, int block_n,
                                  b200dp_stream_t stream_) {
-  return conv_igemm_impl(act, wgt, bias, out, stats, nullptr, B, H, W, Cin, Cout, taps, block_n, 1, 0,
+  return conv_igemm_impl<PrecBf16>(act, wgt, bias, out, stats, nullptr, B, H, W, Cin, Cout, taps, block_n, 1, 0,
                          static_cast<cudaStream_t>(stream_));
 }
 
 extern "C" int b200dp_conv_igemm_splitk(const void* act, const void* wgt, const float* bias, void* out, float* stats,
                                         float* workspace, int B, int H, int W, int Cin, int Cout, int taps,
                                         int block_n, int split_k, b200dp_stream_t stream_) {
-  return conv_igemm_impl(act, wgt, bias, out, stats, workspace, B, H, W, Cin, Cout, taps, block_n, split_k, 0,
+  return conv_igemm_impl<PrecBf16>(act, wgt, bias, out, stats, workspace, B, H, W, Cin, Cout, taps, block_n, split_k, 0,
                          static_cast<cudaStream_t>(stream_));
 }
 
@@ -1218,7 +1261,7 @@ extern "C" int b200dp_conv_igemm_splitk(const void* act, const void* wgt, const 
 extern "C" int b200dp_conv_igemm_pair(const void* act, const void* wgt, const float* bias, void* out, float* stats,
                                       float* workspace, int B, int H, int W, int Cin, int Cout, int taps,
                                       int block_n, int split_k, b200dp_stream_t stream_) {
-  return conv_igemm_impl(act, wgt, bias, out, stats, workspace, B, H, W, Cin, Cout, taps, block_n, split_k, 1,
+  return conv_igemm_impl<PrecBf16>(act, wgt, bias, out, stats, workspace, B, H, W, Cin, Cout, taps, block_n, split_k, 1,
                          static_cast<cudaStream_t>(stream_));
 }
 
@@ -1238,37 +1281,40 @@ extern "C" int b200dp_conv_dgrad_bn_reduce(const void* act, const void* wgt, voi
     return B200DP_EINVAL;
   }
   const BnReduceArgs bnr{bn_out, gamma, beta, sums};
-  return conv_igemm_impl(act, wgt, nullptr, out, nullptr, workspace, B, H, W, Cin, Cout, taps, block_n, split_k,
-                         cta_pair, static_cast<cudaStream_t>(stream_), &bnr);
+  return conv_igemm_impl<PrecBf16>(act, wgt, nullptr, out, nullptr, workspace, B, H, W, Cin, Cout, taps, block_n,
+                                   split_k, cta_pair, static_cast<cudaStream_t>(stream_), &bnr);
 }
 
+template <class Prec>
 static int conv_wgrad_impl(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin, int Cout, int taps,
                            int cin_valid, int split_k, int accumulate, int block_n_req, cudaStream_t stream,
                            const WgradPushArgs* push = nullptr) {
-  if ((taps != 9 && taps != 1) || Cin % 64 != 0 || (Cout % 128 != 0 && Cout != 64) || B <= 0 || cin_valid > Cin ||
-      cin_valid <= 0) {
+  constexpr int kPix = wgrad_pixels(Prec::kTf32);
+  constexpr int kCh = Prec::kBlockK;
+  if ((taps != 9 && taps != 1) || Cin % kCh != 0 || (Cout % 128 != 0 && Cout != 64) || B <= 0 || cin_valid > Cin ||
+      cin_valid <= 0 || (push != nullptr && Prec::kTf32)) {
     set_error("conv_wgrad: unsupported shape B=%d H=%d W=%d Cin=%d Cout=%d taps=%d", B, H, W, Cin, Cout, taps);
     return B200DP_EINVAL;
   }
   WgradParams p{};
   p.H = H;
   p.W = W;
-  if (tile_geometry(H, W, 64, &p.TH, &p.TN) != 0) {
-    set_error("conv_wgrad: B=%d H=%d W=%d cannot be tiled into 64-pixel blocks", B, H, W);
+  if (tile_geometry(H, W, kPix, &p.TH, &p.TN) != 0) {
+    set_error("conv_wgrad: B=%d H=%d W=%d cannot be tiled into %d-pixel blocks", B, H, W, kPix);
     return B200DP_EINVAL;
   }
-  int block_n = (Cin % 128 == 0) ? 128 : 64;
+  int block_n = (Cin % 128 == 0) ? 128 : (Cin % 64 == 0 ? 64 : 32);
   if (block_n_req == 256 && Cin % 256 == 0) block_n = 256;
-  if (block_n_req == 64) block_n = 64;
+  if (block_n_req == 64 && Cin % 64 == 0) block_n = 64;
   p.taps = taps;
   p.cin = Cin;
   p.cout = Cout;
   p.co_tiles = (Cout + kBlockM - 1) / kBlockM;
   p.ci_tiles = Cin / block_n;
-  p.a_boxes = (Cout >= 128) ? 2 : 1;
-  // A K block is 64 pixels; when a block spans whole images (TN > 1) the last one may hang over
+  p.a_boxes = (Cout >= kBlockM ? kBlockM : Cout) / kCh;
+  // A K block is kPix pixels; when a block spans whole images (TN > 1) the last one may hang over
   // the end of the batch -- the tensor maps are sized to B, so TMA zero-fills the overhang.
-  p.kblocks_total = (p.TN > 1) ? (B + p.TN - 1) / p.TN : (B * H * W) / 64;
+  p.kblocks_total = (p.TN > 1) ? (B + p.TN - 1) / p.TN : (B * H * W) / kPix;
   const int tiles = taps * p.co_tiles * p.ci_tiles;
   if (split_k <= 0) {
     split_k = (148 + tiles - 1) / tiles;
@@ -1286,19 +1332,19 @@ static int conv_wgrad_impl(const void* dy, const void* x, float* dw, int B, int 
   CUtensorMap tmDY, tmX;
   {
     const uint64_t dims[2] = {(uint64_t)Cout, (uint64_t)B * H * W};
-    const uint32_t box[2] = {64, 64};
-    int rc = make_tmap(&tmDY, dy, 2, dims, box);
+    const uint32_t box[2] = {(uint32_t)kCh, (uint32_t)kPix};
+    int rc = make_tmap(&tmDY, dy, 2, dims, box, Prec::kBytes);
     if (rc) return rc;
   }
   {
     const uint64_t dims[4] = {(uint64_t)Cin, (uint64_t)W, (uint64_t)H, (uint64_t)B};
-    const uint32_t box[4] = {64, (uint32_t)W, (uint32_t)p.TH, (uint32_t)p.TN};
-    int rc = make_tmap(&tmX, x, 4, dims, box);
+    const uint32_t box[4] = {(uint32_t)kCh, (uint32_t)W, (uint32_t)p.TH, (uint32_t)p.TN};
+    int rc = make_tmap(&tmX, x, 4, dims, box, Prec::kBytes);
     if (rc) return rc;
   }
   // 3 stages (96 / 144 / 72 KiB): the 128-wide kernel then fits on an SM next to a 3-stage dgrad CTA
   // (99 KiB), which matters because weight and data gradients run on two streams concurrently
-  if (push != nullptr) {
+  if constexpr (!Prec::kTf32) if (push != nullptr) {
     if (push->world < 2 || push->world > 8 || push->rank < 0 || push->rank >= push->world ||
         push->peer_stage == nullptr || push->tile_counters == nullptr || push->n_counters < tiles) {
       set_error("conv_wgrad_push: need 2..8 ranks, their staging pointers and >= %d tile counters", tiles);
@@ -1327,15 +1373,18 @@ static int conv_wgrad_impl(const void* dy, const void* x, float* dw, int B, int 
     if (block_n == 128) return launch_wgrad_push<128, 3>(tmDY, tmX, pp, tiles, split_k, stream);
     return launch_wgrad_push<64, 4>(tmDY, tmX, pp, tiles, split_k, stream);
   }
-  if (block_n == 256) return launch_wgrad<256, 3>(tmDY, tmX, p, tiles, split_k, stream);
-  if (block_n == 128) return launch_wgrad<128, 3>(tmDY, tmX, p, tiles, split_k, stream);
-  return launch_wgrad<64, 4>(tmDY, tmX, p, tiles, split_k, stream);
+  if (block_n == 256) return launch_wgrad<Prec, 256, 3>(tmDY, tmX, p, tiles, split_k, stream);
+  if (block_n == 128) return launch_wgrad<Prec, 128, 3>(tmDY, tmX, p, tiles, split_k, stream);
+  if (block_n == 64) return launch_wgrad<Prec, 64, 4>(tmDY, tmX, p, tiles, split_k, stream);
+  if constexpr (Prec::kTf32) return launch_wgrad<Prec, 32, 4>(tmDY, tmX, p, tiles, split_k, stream);
+  set_error("conv_wgrad: Cin=%d needs a 32-wide tile, which only the tf32 kernel has", Cin);
+  return B200DP_EINVAL;
 }
 
 extern "C" int b200dp_conv_wgrad(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin,
                                  int Cout, int taps, int cin_valid, int split_k, int accumulate,
                                  b200dp_stream_t stream_) {
-  return conv_wgrad_impl(dy, x, dw, B, H, W, Cin, Cout, taps, cin_valid, split_k, accumulate, 0,
+  return conv_wgrad_impl<PrecBf16>(dy, x, dw, B, H, W, Cin, Cout, taps, cin_valid, split_k, accumulate, 0,
                          static_cast<cudaStream_t>(stream_));
 }
 
@@ -1355,7 +1404,7 @@ extern "C" int b200dp_conv_wgrad_push(const void* dy, const void* x, float* dw, 
                                       long long stage_base, b200dp_stream_t stream_) {
   const WgradPushArgs push{tile_counters, n_counters, world, rank, peer_stage, flat_off, own_start, own_len,
                            stage_base};
-  return conv_wgrad_impl(dy, x, dw, B, H, W, Cin, Cout, taps, Cin, split_k, 0, block_n,
+  return conv_wgrad_impl<PrecBf16>(dy, x, dw, B, H, W, Cin, Cout, taps, Cin, split_k, 0, block_n,
                          static_cast<cudaStream_t>(stream_), &push);
 }
 
@@ -1363,6 +1412,48 @@ extern "C" int b200dp_conv_wgrad_push(const void* dy, const void* x, float* dw, 
 extern "C" int b200dp_conv_wgrad_tiled(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin,
                                        int Cout, int taps, int cin_valid, int split_k, int accumulate, int block_n,
                                        b200dp_stream_t stream_) {
-  return conv_wgrad_impl(dy, x, dw, B, H, W, Cin, Cout, taps, cin_valid, split_k, accumulate, block_n,
+  return conv_wgrad_impl<PrecBf16>(dy, x, dw, B, H, W, Cin, Cout, taps, cin_valid, split_k, accumulate, block_n,
                          static_cast<cudaStream_t>(stream_));
+}
+
+/* ------------------------------------------------------------------------------------------------------
+ * Precision-generic forms (dtype 0 = bf16 operands and activations, 1 = tf32: fp32 activations and operand
+ * copies in memory, tcgen05.mma kind::tf32).  With dtype 1: act / out / bn_out / dy / x are fp32, wgt is fp32
+ * [Cout][taps*Cin], Cin must be a multiple of 32 (bf16: 64).  Everything else as for the bf16 entry points.
+ * ------------------------------------------------------------------------------------------------------ */
+extern "C" int b200dp_conv_igemm_ex(const void* act, const void* wgt, const float* bias, void* out, float* stats,
+                                    float* workspace, int B, int H, int W, int Cin, int Cout, int taps, int block_n,
+                                    int split_k, int cta_pair, int dtype, b200dp_stream_t stream_) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream_);
+  if (dtype == 1)
+    return conv_igemm_impl<PrecTf32>(act, wgt, bias, out, stats, workspace, B, H, W, Cin, Cout, taps, block_n, split_k,
+                                     cta_pair ? 1 : 0, st);
+  return conv_igemm_impl<PrecBf16>(act, wgt, bias, out, stats, workspace, B, H, W, Cin, Cout, taps, block_n, split_k,
+                                   cta_pair ? 1 : 0, st);
+}
+
+extern "C" int b200dp_conv_dgrad_bn_reduce_ex(const void* act, const void* wgt, void* out, float* workspace,
+                                              const void* bn_out, const float* gamma, const float* beta, float* sums,
+                                              int B, int H, int W, int Cin, int Cout, int taps, int block_n,
+                                              int split_k, int cta_pair, int dtype, b200dp_stream_t stream_) {
+  if (bn_out == nullptr || gamma == nullptr || beta == nullptr || sums == nullptr) {
+    set_error("conv_dgrad_bn_reduce: bn_out, gamma, beta and sums are required");
+    return B200DP_EINVAL;
+  }
+  const BnReduceArgs bnr{bn_out, gamma, beta, sums};
+  cudaStream_t st = static_cast<cudaStream_t>(stream_);
+  if (dtype == 1)
+    return conv_igemm_impl<PrecTf32>(act, wgt, nullptr, out, nullptr, workspace, B, H, W, Cin, Cout, taps, block_n,
+                                     split_k, cta_pair ? 1 : 0, st, &bnr);
+  return conv_igemm_impl<PrecBf16>(act, wgt, nullptr, out, nullptr, workspace, B, H, W, Cin, Cout, taps, block_n,
+                                   split_k, cta_pair ? 1 : 0, st, &bnr);
+}
+
+extern "C" int b200dp_conv_wgrad_ex(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin, int Cout,
+                                    int taps, int cin_valid, int split_k, int accumulate, int block_n, int dtype,
+                                    b200dp_stream_t stream_) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream_);
+  if (dtype == 1)
+    return conv_wgrad_impl<PrecTf32>(dy, x, dw, B, H, W, Cin, Cout, taps, cin_valid, split_k, accumulate, block_n, st);
+  return conv_wgrad_impl<PrecBf16>(dy, x, dw, B, H, W, Cin, Cout, taps, cin_valid, split_k, accumulate, block_n, st);
 }

@@ -1193,35 +1193,55 @@ __global__ void __launch_bounds__(256) copy_pair_kernel(uint4* __restrict__ d0, 
 
 // master fp32 [Cout][taps][Cin] -> Wf bf16 [Cout][kpad] (zero padded past taps*Cin)
 //                               -> Wd bf16 [Cin][taps*Cout] with taps flipped (dgrad operand), optional
-__global__ void prep_conv_weights_kernel(const float* __restrict__ master, __nv_bfloat16* __restrict__ wf,
-                                         __nv_bfloat16* __restrict__ wd, int Cout, int Cin, int taps, int kpad) {
+template <class T>
+B200DP_DEVINL T operand_cast(float v) {
+  if constexpr (sizeof(T) == 4) return v;
+  else return __float2bfloat16(v);
+}
+template <class T>
+B200DP_DEVINL void operand_store4(T* dst, float a, float b, float c, float d) {
+  if constexpr (sizeof(T) == 4) {
+    *reinterpret_cast<float4*>(dst) = make_float4(a, b, c, d);
+  } else {
+    uint2 o;
+    o.x = pack_bf16x2(a, b);
+    o.y = pack_bf16x2(c, d);
+    *reinterpret_cast<uint2*>(dst) = o;
+  }
+}
+
+// T = __nv_bfloat16: operand copies of the bf16 path.  T = float: the tf32 path, whose forward operand is the master
+// tensor itself wherever no padding is needed (wf == nullptr), so usually only Wd is produced.
+template <class T>
+__global__ void prep_conv_weights_kernel(const float* __restrict__ master, T* __restrict__ wf, T* __restrict__ wd,
+                                         int Cout, int Cin, int taps, int kpad) {
   pdl_launch_dependents();
   pdl_wait();
-  const long nf = static_cast<long>(Cout) * kpad;
+  const long nf = wf != nullptr ? static_cast<long>(Cout) * kpad : 0;
   const long nd = wd != nullptr ? static_cast<long>(Cin) * taps * Cout : 0;
   const int kvalid = taps * Cin;
   const long stride = static_cast<long>(gridDim.x) * blockDim.x;
   for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < nf + nd; i += stride) {
     if (i < nf) {
       const int co = static_cast<int>(i / kpad), k = static_cast<int>(i - static_cast<long>(co) * kpad);
-      wf[i] = __float2bfloat16(k < kvalid ? master[static_cast<long>(co) * kvalid + k] : 0.f);
+      wf[i] = operand_cast<T>(k < kvalid ? master[static_cast<long>(co) * kvalid + k] : 0.f);
     } else {
       const long j = i - nf;
       const int co = static_cast<int>(j % Cout);
       const int tap = static_cast<int>((j / Cout) % taps);
       const int ci = static_cast<int>(j / (static_cast<long>(Cout) * taps));
-      wd[j] = __float2bfloat16(master[(static_cast<long>(co) * taps + (taps - 1 - tap)) * Cin + ci]);
+      wd[j] = operand_cast<T>(master[(static_cast<long>(co) * taps + (taps - 1 - tap)) * Cin + ci]);
     }
   }
 }
 
 // All conv layers in ONE launch: 64(co) x 64(ci) tiles of one tap are read with coalesced float4
-// loads, written to Wf as bf16 and transposed through shared memory into Wd (tap flipped).
+// loads, written to Wf in the operand type and transposed through shared memory into Wd (tap flipped).
 constexpr int kPrepMaxLayers = 20;
 struct PrepLayer {
   const float* master;
-  __nv_bfloat16* wf;
-  __nv_bfloat16* wd;
+  void* wf;   // may be null (tf32: the master tensor is the forward operand)
+  void* wd;   // may be null
   int cout, cin, taps, kpad;
   int tile_begin;  // first global tile index of this layer
   int ci_tiles;
@@ -1231,6 +1251,7 @@ struct PrepTable {
   int n;
 };
 
+template <class T>
 __global__ void __launch_bounds__(256) prep_conv_weights_batched_kernel(const PrepTable t) {
   pdl_launch_dependents();
   pdl_wait();
@@ -1238,6 +1259,8 @@ __global__ void __launch_bounds__(256) prep_conv_weights_batched_kernel(const Pr
   int li = 0;
   while (li + 1 < t.n && static_cast<int>(blockIdx.x) >= t.l[li + 1].tile_begin) ++li;
   const PrepLayer L = t.l[li];
+  T* wf = static_cast<T*>(L.wf);
+  T* wd = static_cast<T*>(L.wd);
   int tidx = blockIdx.x - L.tile_begin;
   const int ci_t = tidx % L.ci_tiles;
   tidx /= L.ci_tiles;
@@ -1251,21 +1274,17 @@ __global__ void __launch_bounds__(256) prep_conv_weights_batched_kernel(const Pr
     const int r = (threadIdx.x >> 4) + 16 * k;
     const float4 v = *reinterpret_cast<const float4*>(L.master + static_cast<long>(co0 + r) * kvalid + tap * L.cin + ci0 + c4);
     tile[r][c4] = v.x; tile[r][c4 + 1] = v.y; tile[r][c4 + 2] = v.z; tile[r][c4 + 3] = v.w;
-    uint2 o;
-    o.x = pack_bf16x2(v.x, v.y);
-    o.y = pack_bf16x2(v.z, v.w);
-    *reinterpret_cast<uint2*>(L.wf + static_cast<long>(co0 + r) * L.kpad + tap * L.cin + ci0 + c4) = o;
+    if (wf != nullptr)
+      operand_store4(wf + static_cast<long>(co0 + r) * L.kpad + tap * L.cin + ci0 + c4, v.x, v.y, v.z, v.w);
   }
-  if (L.wd == nullptr) return;
+  if (wd == nullptr) return;
   __syncthreads();
   const int ftap = L.taps - 1 - tap;
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
     const int ci = (threadIdx.x >> 4) + 16 * k;
-    uint2 o;
-    o.x = pack_bf16x2(tile[c4][ci], tile[c4 + 1][ci]);
-    o.y = pack_bf16x2(tile[c4 + 2][ci], tile[c4 + 3][ci]);
-    *reinterpret_cast<uint2*>(L.wd + (static_cast<long>(ci0 + ci) * L.taps + ftap) * L.cout + co0 + c4) = o;
+    operand_store4(wd + (static_cast<long>(ci0 + ci) * L.taps + ftap) * L.cout + co0 + c4, tile[c4][ci],
+                   tile[c4 + 1][ci], tile[c4 + 2][ci], tile[c4 + 3][ci]);
   }
 }
 
@@ -1558,17 +1577,29 @@ extern "C" int b200dp_copy_pair(void* dst0, const void* src0, long long nbytes0,
   return 0;
 }
 
-extern "C" int b200dp_prep_conv_weights(const float* master, void* wf, void* wd, int Cout, int Cin, int taps,
-                                        int kpad, b200dp_stream_t s) {
-  if (kpad < taps * Cin) {
-    set_error("prep_conv_weights: kpad=%d < taps*Cin=%d", kpad, taps * Cin);
+/* dtype 0: bf16 operand copies; 1: fp32 copies for the tf32 kernels (wf may be NULL there: the master tensor is
+ * the forward operand whenever kpad == taps*Cin). */
+extern "C" int b200dp_prep_conv_weights_ex(const float* master, void* wf, void* wd, int Cout, int Cin, int taps,
+                                           int kpad, int dtype, b200dp_stream_t s) {
+  if (kpad < taps * Cin || (wf == nullptr && wd == nullptr)) {
+    set_error("prep_conv_weights: kpad=%d < taps*Cin=%d, or nothing to write", kpad, taps * Cin);
     return B200DP_EINVAL;
   }
-  const long n = static_cast<long>(Cout) * kpad + (wd ? static_cast<long>(Cin) * taps * Cout : 0);
-  prep_conv_weights_kernel<<<grid_for(n, 256), 256, 0, static_cast<cudaStream_t>(s)>>>(
-      master, static_cast<__nv_bfloat16*>(wf), static_cast<__nv_bfloat16*>(wd), Cout, Cin, taps, kpad);
+  const long n = (wf ? static_cast<long>(Cout) * kpad : 0) + (wd ? static_cast<long>(Cin) * taps * Cout : 0);
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  if (dtype == 1)
+    prep_conv_weights_kernel<float><<<grid_for(n, 256), 256, 0, st>>>(master, static_cast<float*>(wf),
+                                                                      static_cast<float*>(wd), Cout, Cin, taps, kpad);
+  else
+    prep_conv_weights_kernel<__nv_bfloat16><<<grid_for(n, 256), 256, 0, st>>>(
+        master, static_cast<__nv_bfloat16*>(wf), static_cast<__nv_bfloat16*>(wd), Cout, Cin, taps, kpad);
   B200DP_CUDA_TRY(cudaGetLastError());
   return 0;
+}
+
+extern "C" int b200dp_prep_conv_weights(const float* master, void* wf, void* wd, int Cout, int Cin, int taps,
+                                        int kpad, b200dp_stream_t s) {
+  return b200dp_prep_conv_weights_ex(master, wf, wd, Cout, Cin, taps, kpad, 0, s);
 }
 
 // ---------------------------------------------------------------------------
@@ -1638,11 +1669,11 @@ extern "C" int b200dp_bn_relu_pool_bwd_noalloc(const void* y, const void* dout, 
   return launch_bn_bwd(true, p, stream);
 }
 
-/* Batched form of b200dp_prep_conv_weights: all layers in one launch.  Arrays have n entries;
+/* Batched form of b200dp_prep_conv_weights_ex: all layers in one launch.  Arrays have n entries;
  * layers need Cout % 64 == 0 and Cin % 64 == 0 (others: use the single-layer entry point). */
-extern "C" int b200dp_prep_conv_weights_batched(int n, const float* const* master, void* const* wf, void* const* wd,
-                                                const int* cout, const int* cin, const int* taps, const int* kpad,
-                                                b200dp_stream_t s) {
+extern "C" int b200dp_prep_conv_weights_batched_ex(int n, const float* const* master, void* const* wf,
+                                                   void* const* wd, const int* cout, const int* cin, const int* taps,
+                                                   const int* kpad, int dtype, b200dp_stream_t s) {
   if (n < 1 || n > kPrepMaxLayers) {
     set_error("prep_conv_weights_batched: n=%d outside [1, %d]", n, kPrepMaxLayers);
     return B200DP_EINVAL;
@@ -1656,12 +1687,20 @@ extern "C" int b200dp_prep_conv_weights_batched(int n, const float* const* maste
                 i, cout[i], cin[i], kpad[i]);
       return B200DP_EINVAL;
     }
-    t.l[i] = PrepLayer{master[i], static_cast<__nv_bfloat16*>(wf[i]), static_cast<__nv_bfloat16*>(wd[i]), cout[i],
-                       cin[i], taps[i], kpad[i], tiles, cin[i] / 64};
+    t.l[i] = PrepLayer{master[i], wf[i], wd[i], cout[i], cin[i], taps[i], kpad[i], tiles, cin[i] / 64};
     tiles += (cout[i] / 64) * taps[i] * (cin[i] / 64);
   }
-  B200DP_CUDA_TRY(launch_pdl(prep_conv_weights_batched_kernel, dim3(tiles), dim3(256), 0, static_cast<cudaStream_t>(s),
-                             t));
+  if (dtype == 1)
+    B200DP_CUDA_TRY(launch_pdl(prep_conv_weights_batched_kernel<float>, dim3(tiles), dim3(256), 0,
+                               static_cast<cudaStream_t>(s), t));
+  else
+    B200DP_CUDA_TRY(launch_pdl(prep_conv_weights_batched_kernel<__nv_bfloat16>, dim3(tiles), dim3(256), 0,
+                               static_cast<cudaStream_t>(s), t));
   return 0;
 }
 
+extern "C" int b200dp_prep_conv_weights_batched(int n, const float* const* master, void* const* wf, void* const* wd,
+                                                const int* cout, const int* cin, const int* taps, const int* kpad,
+                                                b200dp_stream_t s) {
+  return b200dp_prep_conv_weights_batched_ex(n, master, wf, wd, cout, cin, taps, kpad, 0, s);
+}

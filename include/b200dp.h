@@ -112,6 +112,23 @@ int b200dp_conv_wgrad_tiled(const void* dy, const void* x, float* dw, int B, int
                             int taps, int cin_valid, int split_k, int accumulate, int block_n,
                             b200dp_stream_t stream);
 
+/* Precision-generic forms of the three GEMM entry points above.  dtype 0 = bf16 (identical to the entry points
+ * without _ex), dtype 1 = tf32: activations (act / out / bn_out / dy / x) and the operand copy of the weights
+ * are fp32 in memory, the tensor cores read them as tf32 (tcgen05.mma kind::tf32, the TMA unit rounds to
+ * nearest on the way into shared memory) and accumulate in fp32 -- the precision of the reference's fp32
+ * model under torch's TF32 convolutions (ref: master/part1/model.py:18-25, no autocast anywhere).
+ * With dtype 1, Cin must be a multiple of 32 (bf16: 64); the wgrad N tile may also be 32.
+ * cta_pair != 0 selects the cta_group::2 kernel; split_k / workspace as for b200dp_conv_igemm_splitk. */
+int b200dp_conv_igemm_ex(const void* act, const void* wgt, const float* bias, void* out, float* stats,
+                         float* workspace, int B, int H, int W, int Cin, int Cout, int taps, int block_n, int split_k,
+                         int cta_pair, int dtype, b200dp_stream_t stream);
+int b200dp_conv_dgrad_bn_reduce_ex(const void* act, const void* wgt, void* out, float* workspace, const void* bn_out,
+                                   const float* gamma, const float* beta, float* sums, int B, int H, int W, int Cin,
+                                   int Cout, int taps, int block_n, int split_k, int cta_pair, int dtype,
+                                   b200dp_stream_t stream);
+int b200dp_conv_wgrad_ex(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin, int Cout, int taps,
+                         int cin_valid, int split_k, int accumulate, int block_n, int dtype, b200dp_stream_t stream);
+
 /* ------------------------------------------------------------------------
  * Bandwidth-bound layer kernels (bf16 NHWC activations, 8 channels per thread)
  * ------------------------------------------------------------------------ */
@@ -229,6 +246,13 @@ int b200dp_prep_conv_weights(const float* master, void* wf, void* wd, int Cout, 
                              b200dp_stream_t stream);
 /* The same for n layers in ONE launch (tiled, coalesced, transposed through shared memory);
  * every layer needs Cout % 64 == 0, Cin % 64 == 0 and kpad == taps*Cin. */
+/* Precision-generic forms: dtype 0 = bf16 operand copies, 1 = fp32 copies for the tf32 kernels (wf may then be NULL
+ * where the master tensor itself is the forward operand, i.e. whenever kpad == taps * Cin). */
+int b200dp_prep_conv_weights_ex(const float* master, void* wf, void* wd, int Cout, int Cin, int taps, int kpad,
+                                int dtype, b200dp_stream_t stream);
+int b200dp_prep_conv_weights_batched_ex(int n, const float* const* master, void* const* wf, void* const* wd,
+                                        const int* cout, const int* cin, const int* taps, const int* kpad, int dtype,
+                                        b200dp_stream_t stream);
 int b200dp_prep_conv_weights_batched(int n, const float* const* master, void* const* wf, void* const* wd,
                                      const int* cout, const int* cin, const int* taps, const int* kpad,
                                      b200dp_stream_t stream);

@@ -190,7 +190,7 @@ class NativeBackend:
             if self.comm is None:
                 self.comm = Communicator(self.store, cfg.rank, W, device.index or 0, heap_bytes, timeout_s=cfg.timeout_s)
             heap = self.comm
-        self.native = model.enable_native(max_batch=B, heap=heap)
+        self.native = model.enable_native(max_batch=B, heap=heap, dtype=cfg.dtype)
         # this backend always calls loss_fwd_bwd() after a training forward, so the classifier forward, the loss
         # and the classifier backward run as ONE launch (head_fwd_bwd) instead of three plus two memset nodes
         self.native.defer_head = True

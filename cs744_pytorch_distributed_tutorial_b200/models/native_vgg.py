@@ -187,12 +187,22 @@ _ACT_DTYPE = torch.bfloat16   # activations / operand copies; the CPU emulation 
 
 class NativeVGG:
     def __init__(self, module: nn.Module, max_batch: int, heap=None, conv_stats_fused: bool = True,
-                 autotune: bool = True):
+                 autotune: bool = True, dtype: str = "bf16"):
         dev = next(module.parameters()).device
         if dev.type != "cuda" and not _DRY_RUN:
             raise RuntimeError("NativeVGG needs the module on a CUDA device")
         if not K._lib.available():
             raise RuntimeError("libb200dp.so is not available; the native sm_100a path cannot run")
+        if dtype not in ("bf16", "tf32"):
+            raise ValueError(f"dtype must be 'bf16' or 'tf32', got {dtype!r}")
+        # bf16: bf16 activations and operand copies, tcgen05 kind::f16.  tf32: fp32 activations in memory, the
+        # tensor cores read them as tf32 (kind::tf32) -- the precision of the reference's fp32 model
+        # (ref: master/part1/model.py:18-25 under torch's TF32 convolutions).  Master weights, gradients and
+        # the optimizer are fp32 either way.
+        self.dtype = dtype
+        self.tf32 = dtype == "tf32"
+        self.act_dtype = torch.float32 if self.tf32 else _ACT_DTYPE
+        self.kblock = 32 if self.tf32 else 64      # channels per 128-byte operand row = K extent of a pipeline stage
         self.module = module
         self.device = dev
         self.max_batch = max_batch
@@ -283,7 +293,7 @@ class NativeVGG:
     # ------------------------------------------------------------------ workspaces
     def _alloc_workspaces(self) -> None:
         B, dev = self.max_batch, self.device
-        bf = _ACT_DTYPE
+        bf = self.act_dtype
         L = self.layout
         self.blocks: List[_Block] = []
         # fp32 partial-tile workspace of the split-K convs (kept zero by their finalize kernel)
@@ -301,7 +311,7 @@ class NativeVGG:
             b.fwd_split_k = b.dgrad_split_k = 1
             b.wgrad_block_n = 0
             b.fwd_pair = b.dgrad_pair = False
-            b.kin = 64 if b.first else s.cin           # GEMM K per tap (layer 0: 27 -> 64 padded, 1 tap)
+            b.kin = self.kblock if b.first else s.cin   # GEMM K per tap (layer 0: 27 padded to one operand row, 1 tap)
             b.taps = 1 if b.first else 9
             hw = s.hw
             if b.first:
@@ -319,13 +329,18 @@ class NativeVGG:
             b.mean = torch.empty(s.cout, device=dev)
             b.invstd = torch.empty(s.cout, device=dev)
             kpad = b.taps * b.kin
-            b.wf = torch.empty(s.cout, kpad, device=dev, dtype=bf)
             b.wd = None if b.first else torch.empty(s.cin, 9 * s.cout, device=dev, dtype=bf)
+            b._wf_unpadded = self.tf32 and not b.first     # fp32 master [Cout][9*Cin] IS the forward operand
+            b.wf = None if b._wf_unpadded else torch.empty(s.cout, kpad, device=dev, dtype=bf)
             ew, eb = L.by_name[f"layers.{s.conv_idx}.weight"], L.by_name[f"layers.{s.conv_idx}.bias"]
             eg, ebt = L.by_name[f"layers.{s.bn_idx}.weight"], L.by_name[f"layers.{s.bn_idx}.bias"]
             fp, fg = self.flat_params, self.flat_grads
             sl = lambda flat, e: flat[e.offset: e.offset + e.numel]
             b.w_master, b.bias, b.gamma, b.beta = sl(fp, ew), sl(fp, eb), sl(fp, eg), sl(fp, ebt)
+            # what the weight re-layout kernels write for this block: (master, Wf or None, Wd or None, ...)
+            b.prep = (b.w_master, b.wf, b.wd, s.cout, s.cin, 9, kpad)
+            if b._wf_unpadded:
+                b.wf = b.w_master.view(s.cout, kpad)
             b.g_w, b.g_bias, b.g_gamma, b.g_beta = sl(fg, ew), sl(fg, eb), sl(fg, eg), sl(fg, ebt)
             bn = self.module.layers[s.bn_idx]
             b.running_mean, b.running_var, b.nbt = bn.running_mean.data, bn.running_var.data, self.flat_nbt[i:i + 1]
@@ -370,13 +385,13 @@ class NativeVGG:
             for i, b in enumerate(self.blocks):
                 s = b.spec
                 x_in, y, dy = b.x_in[:B], b.y[:B], b.dy[:B]
-                key = (B, s.hw, b.kin, s.cout, b.taps)
+                key = (self.dtype, B, s.hw, b.kin, s.cout, b.taps)
                 m_tiles = (B * s.hw * s.hw + 127) // 128
                 if ("fwd",) + key not in _TUNE_CACHE:
                     t = {c: _time_captured(lambda c=c: K.conv_igemm(x_in, b.wf, b.bias, y, stats=b.stats, taps=b.taps,
                                                                     block_n=c[0], split_k=c[1], cta_pair=c[2],
                                                                     workspace=self.splitk_ws))
-                         for c in _igemm_candidates(m_tiles, s.cout, b.taps * b.kin // 64)}
+                         for c in _igemm_candidates(m_tiles, s.cout, b.taps * b.kin // self.kblock)}
                     _TUNE_CACHE[("fwd",) + key] = min(t, key=t.get)
                 b.fwd_block_n, b.fwd_split_k, b.fwd_pair = _TUNE_CACHE[("fwd",) + key]
                 if ("wgrad",) + key not in _TUNE_CACHE:
@@ -393,7 +408,7 @@ class NativeVGG:
                         t = {c: _time_captured(lambda c=c: K.conv_igemm(dy, b.wd, None, dprev, block_n=c[0],
                                                                         split_k=c[1], cta_pair=c[2],
                                                                         workspace=self.splitk_ws))
-                             for c in _igemm_candidates(m_tiles, s.cin, 9 * s.cout // 64)}
+                             for c in _igemm_candidates(m_tiles, s.cin, 9 * s.cout // self.kblock)}
                         _TUNE_CACHE[("dgrad",) + key] = min(t, key=t.get)
                     b.dgrad_block_n, b.dgrad_split_k, b.dgrad_pair = _TUNE_CACHE[("dgrad",) + key]
         torch.cuda.current_stream().wait_stream(side)
@@ -405,16 +420,14 @@ class NativeVGG:
     def refresh_shadows(self) -> None:
         """bf16 operand copies of the fp32 master weights: Wf (forward) and Wd (dgrad)."""
         if getattr(self, "_prep", None) is None:
-            self._prep = K.BatchedWeightPrep([(b.w_master, b.wf, b.wd, b.spec.cout, b.spec.cin, 9, b.taps * b.kin)
-                                              for b in self.blocks])
+            self._prep = K.BatchedWeightPrep([b.prep for b in self.blocks])
         self._prep()
 
     def prep_block(self, i: int) -> None:
         """Refresh the bf16 weight copies of block ``i`` on the current stream, after the data gradient
         of that block (the last reader of the old copies in this step) has finished."""
         if self._block_prep is None:
-            self._block_prep = [K.BatchedWeightPrep([(b.w_master, b.wf, b.wd, b.spec.cout, b.spec.cin, 9, b.taps * b.kin)])
-                                for b in self.blocks]
+            self._block_prep = [K.BatchedWeightPrep([b.prep]) for b in self.blocks]
         torch.cuda.current_stream().wait_event(self._dgrad_done[i])
         self._block_prep[i]()
 

@@ -114,28 +114,31 @@ def conv_wgrad_push(dy: torch.Tensor, x: torch.Tensor, dw: torch.Tensor, *, coun
 
 
 def im2col3x3_c3(x_nchw: torch.Tensor, a0: torch.Tensor) -> torch.Tensor:
+    """Layer-0 patch gather: bf16 rows of 64 columns or fp32 rows of 32 columns (27 real ones either way)."""
     _chk(x_nchw, torch.float32, "x")
-    _chk(a0, torch.bfloat16, "a0")
+    dt = _act_dtype(a0, "a0")
     B, C, H, W = x_nchw.shape
-    assert C == 3 and a0.numel() == B * H * W * 64
-    call("b200dp_im2col3x3_c3", ptr(x_nchw), ptr(a0), B, H, W, stream_ptr())
+    assert C == 3 and a0.numel() == B * H * W * (32 if dt else 64)
+    call("b200dp_im2col3x3_c3_ex", ptr(x_nchw), ptr(a0), B, H, W, dt, stream_ptr())
     return a0
 
 
 def bn_stats(y: torch.Tensor, stats: torch.Tensor) -> torch.Tensor:
-    _chk(y, torch.bfloat16, "y")
+    dt = _act_dtype(y, "y")
     _chk(stats, torch.float32, "stats")
     C = y.shape[-1]
-    call("b200dp_bn_stats", ptr(y), ptr(stats), y.numel() // C, C, stream_ptr())
+    call("b200dp_bn_stats_ex", ptr(y), ptr(stats), y.numel() // C, C, dt, stream_ptr())
     return stats
 
 
 def bn_relu_pool_fwd(y, stats, gamma, beta, running_mean, running_var, num_batches_tracked, save_mean, save_invstd,
                      out, pool: bool, training: bool, momentum: float = BN_MOMENTUM, eps: float = BN_EPS):
     B, H, W, C = y.shape
-    call("b200dp_bn_relu_pool_fwd", ptr(y), ptr(stats), ptr(gamma), ptr(beta), ptr(running_mean), ptr(running_var),
-         ptr(num_batches_tracked), ptr(save_mean), ptr(save_invstd), ptr(out), B, H, W, C, int(pool), int(training),
-         momentum, eps, stream_ptr())
+    dt = _act_dtype(y, "y")
+    _chk(out, y.dtype, "out")
+    call("b200dp_bn_relu_pool_fwd_ex", ptr(y), ptr(stats), ptr(gamma), ptr(beta), ptr(running_mean),
+         ptr(running_var), ptr(num_batches_tracked), ptr(save_mean), ptr(save_invstd), ptr(out), B, H, W, C, int(pool),
+         int(training), momentum, eps, dt, stream_ptr())
     return out
 
 
@@ -146,21 +149,25 @@ def bn_relu_pool_bwd(y, dout, mean, invstd, gamma, beta, sums, dy, dgamma, dbeta
     layers and no arg-max search.  ``skip_reduce``: ``sums`` already holds the reduction
     (``conv_dgrad_bn_reduce`` of the block above produced it), only apply."""
     B, H, W, C = y.shape
+    dt = _act_dtype(y, "y")
+    _chk(dout, y.dtype, "dout")
+    _chk(dy, y.dtype, "dy")
     if not skip_reduce:
         if out is not None:
-            call("b200dp_bn_relu_pool_bwd_reduce_from_out", ptr(out), ptr(dout), ptr(gamma), ptr(beta), ptr(sums),
-                 dout.numel() // C, C, stream_ptr())
+            call("b200dp_bn_relu_pool_bwd_reduce_from_out_ex", ptr(out), ptr(dout), ptr(gamma), ptr(beta), ptr(sums),
+                 dout.numel() // C, C, dt, stream_ptr())
         else:
-            call("b200dp_bn_relu_pool_bwd_reduce", ptr(y), ptr(dout), ptr(mean), ptr(invstd), ptr(gamma), ptr(beta),
-                 ptr(sums), B, H, W, C, int(pool), stream_ptr())
-    call("b200dp_bn_relu_pool_bwd_apply", ptr(y), ptr(dout), ptr(mean), ptr(invstd), ptr(gamma), ptr(beta),
-         ptr(sums), ptr(dy), ptr(dgamma), ptr(dbeta), B, H, W, C, int(pool), stream_ptr())
+            call("b200dp_bn_relu_pool_bwd_reduce_ex", ptr(y), ptr(dout), ptr(mean), ptr(invstd), ptr(gamma),
+                 ptr(beta), ptr(sums), B, H, W, C, int(pool), dt, stream_ptr())
+    call("b200dp_bn_relu_pool_bwd_apply_ex", ptr(y), ptr(dout), ptr(mean), ptr(invstd), ptr(gamma), ptr(beta),
+         ptr(sums), ptr(dy), ptr(dgamma), ptr(dbeta), B, H, W, C, int(pool), dt, stream_ptr())
     return dy
 
 
 def linear_fwd(x, w, b, logits):
     B, Fdim = x.shape[0], x.numel() // x.shape[0]
-    call("b200dp_linear_fwd", ptr(x), ptr(w), ptr(b), ptr(logits), B, Fdim, w.shape[0], stream_ptr())
+    call("b200dp_linear_fwd_ex", ptr(x), ptr(w), ptr(b), ptr(logits), B, Fdim, w.shape[0], _act_dtype(x, "x"),
+         stream_ptr())
     return logits
 
 
@@ -175,15 +182,17 @@ def head_fwd_bwd(x, w, b, target, logits, loss, correct, dlogits, dx, dw, db, gr
     """Classifier head of a training step in one launch: ``linear_fwd`` + ``cross_entropy`` + ``linear_bwd``
     (ref: master/part1/model.py:44-46 and part1.py:35-37).  ``dw`` / ``db`` are accumulated onto."""
     B, Fdim = x.shape[0], x.numel() // x.shape[0]
-    assert target.dtype == torch.int64
-    call("b200dp_head_fwd_bwd", ptr(x), ptr(w), ptr(b), ptr(target), ptr(logits), ptr(loss), ptr(correct),
-         ptr(dlogits), ptr(dx), ptr(dw), ptr(db), B, Fdim, w.shape[0], float(grad_scale), stream_ptr())
+    assert target.dtype == torch.int64 and dx.dtype == x.dtype
+    call("b200dp_head_fwd_bwd_ex", ptr(x), ptr(w), ptr(b), ptr(target), ptr(logits), ptr(loss), ptr(correct),
+         ptr(dlogits), ptr(dx), ptr(dw), ptr(db), B, Fdim, w.shape[0], float(grad_scale), _act_dtype(x, "x"),
+         stream_ptr())
 
 
 def linear_bwd(x, w, dlogits, dw, db, dx):
     B, Fdim = x.shape[0], x.numel() // x.shape[0]
-    call("b200dp_linear_bwd", ptr(x), ptr(w), ptr(dlogits), ptr(dw), ptr(db), ptr(dx), B, Fdim, w.shape[0],
-         stream_ptr())
+    assert dx.dtype == x.dtype
+    call("b200dp_linear_bwd_ex", ptr(x), ptr(w), ptr(dlogits), ptr(dw), ptr(db), ptr(dx), B, Fdim, w.shape[0],
+         _act_dtype(x, "x"), stream_ptr())
 
 
 def sgd_momentum(p, g, buf, lr: float, momentum: float, wd: float, grad_scale: float = 1.0):

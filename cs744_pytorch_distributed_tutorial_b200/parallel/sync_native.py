@@ -101,9 +101,8 @@ class LocalSGD(NativeSync):
             self.first_block = max(n - 5, 1)            # VGG-11: blocks 3..7 = 35.3 of 36.9 MB
             self.split_bucket = max(k for k in range(len(self.buckets)) if self.first_block in nv.blocks_of_bucket(k))
             self.split_end = self.buckets[self.split_bucket].end
-            spec = lambda b: (b.w_master, b.wf, b.wd, b.spec.cout, b.spec.cin, 9, b.taps * b.kin)
-            self._prep_hi = K.BatchedWeightPrep([spec(b) for b in nv.blocks[self.first_block:]])
-            self._prep_lo = K.BatchedWeightPrep([spec(b) for b in nv.blocks[:self.first_block]])
+            self._prep_hi = K.BatchedWeightPrep([b.prep for b in nv.blocks[self.first_block:]])
+            self._prep_lo = K.BatchedWeightPrep([b.prep for b in nv.blocks[:self.first_block]])
             self._opt_stream = torch.cuda.Stream(nv.device)
             self._opt_fork, self._opt_join = torch.cuda.Event(), torch.cuda.Event()
             self._opt_pending = False

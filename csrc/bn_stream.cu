@@ -29,24 +29,26 @@ struct V8 {
   float v[8];
 };
 
-B200DP_DEVINL V8 unpack_v8(const uint4& u) {
+template <class T>
+B200DP_DEVINL V8 ld_v8(const T* p) {
+  const F8 f = ld8(p);
   V8 r;
-  float2 f;
-  f = unpack_bf16x2(u.x); r.v[0] = f.x; r.v[1] = f.y;
-  f = unpack_bf16x2(u.y); r.v[2] = f.x; r.v[3] = f.y;
-  f = unpack_bf16x2(u.z); r.v[4] = f.x; r.v[5] = f.y;
-  f = unpack_bf16x2(u.w); r.v[6] = f.x; r.v[7] = f.y;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) r.v[j] = f.v[j];
   return r;
 }
-
-B200DP_DEVINL uint4 pack_v8(const V8& r) {
-  uint4 u;
-  u.x = pack_bf16x2(r.v[0], r.v[1]);
-  u.y = pack_bf16x2(r.v[2], r.v[3]);
-  u.z = pack_bf16x2(r.v[4], r.v[5]);
-  u.w = pack_bf16x2(r.v[6], r.v[7]);
-  return u;
+template <class T>
+B200DP_DEVINL void st_v8(T* p, const V8& r) {
+  F8 f;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) f.v[j] = r.v[j];
+  st8(p, f);
 }
+// work items per thread and stage, chosen so that a stage holds the same BYTES for bf16 and fp32 activations
+template <class T>
+constexpr int items_2in() { return sizeof(T) == 4 ? 1 : 2; }   // two input streams (apply, reduce)
+template <class T>
+constexpr int items_1in() { return sizeof(T) == 4 ? 2 : 4; }   // one input stream (forward, no pool)
 
 B200DP_DEVINL V8 ld_f32x8(const float* p) {
   const float4 a = *reinterpret_cast<const float4*>(p);
@@ -77,9 +79,10 @@ struct StreamGeom {
 
 template <class Op>
 __global__ void __launch_bounds__(kThreads, 2) bn_stream_kernel(const typename Op::Params p, const StreamGeom g,
-                                                                const __nv_bfloat16* __restrict__ a_ptr,
-                                                                const __nv_bfloat16* __restrict__ b_ptr,
-                                                                __nv_bfloat16* __restrict__ out_ptr) {
+                                                                const typename Op::elem* __restrict__ a_ptr,
+                                                                const typename Op::elem* __restrict__ b_ptr,
+                                                                typename Op::elem* __restrict__ out_ptr) {
+  using elem = typename Op::elem;
   extern __shared__ uint8_t stream_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(stream_raw) + 127) & ~uintptr_t(127));
   const int a_stage = g.units_per_stage * g.a_bytes, b_stage = g.units_per_stage * g.b_bytes;
@@ -124,8 +127,8 @@ __global__ void __launch_bounds__(kThreads, 2) bn_stream_kernel(const typename O
     mbar_wait(&full_bar[stage], phase);
     __syncthreads();
     const uint8_t* in = smem + stage * in_stage;
-    op.compute(reinterpret_cast<const __nv_bfloat16*>(in), reinterpret_cast<const __nv_bfloat16*>(in + a_stage),
-               reinterpret_cast<__nv_bfloat16*>(ob), n);
+    op.compute(reinterpret_cast<const elem*>(in), reinterpret_cast<const elem*>(in + a_stage),
+               reinterpret_cast<elem*>(ob), n);
     if (o_stage != 0) fence_proxy_async_smem();
     __syncthreads();   // outputs written, input stage no longer read
     if (threadIdx.x == 0) {
@@ -158,9 +161,9 @@ int launch_stream(const typename Op::Params& p, const StreamGeom& g, const void*
   }
   const long num_chunks = (g.units + g.units_per_stage - 1) / g.units_per_stage;
   const int grid = static_cast<int>(num_chunks < 148 * 2 ? num_chunks : 148 * 2);
+  using elem = typename Op::elem;
   B200DP_CUDA_TRY(launch_pdl(bn_stream_kernel<Op>, dim3(grid), dim3(kThreads), smem, s, p, g,
-                             static_cast<const __nv_bfloat16*>(a), static_cast<const __nv_bfloat16*>(b),
-                             static_cast<__nv_bfloat16*>(out)));
+                             static_cast<const elem*>(a), static_cast<const elem*>(b), static_cast<elem*>(out)));
   return 0;
 }
 
@@ -175,10 +178,11 @@ struct ApplyParams {
   long count;   // B*H*W of the conv output
 };
 
-constexpr int kItemsPerThread = 2;   // two input streams: 2 x 8 KiB per stage, 64 KiB per CTA, 3 CTAs per SM
-
+template <class T>
 struct ApplyNoPoolOp {
   using Params = ApplyParams;
+  using elem = T;
+  static constexpr int kItemsPerThread = items_2in<T>();   // 2 x 8 KiB per stage, 64 KiB per CTA, 3 CTAs per SM
   V8 scale, shift, c0, c1;
   int C, off0, pix0, pix_step;
   __device__ ApplyNoPoolOp(const Params& p, int tid) {
@@ -209,14 +213,14 @@ struct ApplyNoPoolOp {
       }
     }
   }
-  __device__ void compute(const __nv_bfloat16* y, const __nv_bfloat16* dout, __nv_bfloat16* dy, int n) const {
+  __device__ void compute(const T* y, const T* dout, T* dy, int n) const {
 #pragma unroll
     for (int u = 0; u < kItemsPerThread; ++u) {
       const int pix = pix0 + u * pix_step;
       if (pix >= n) break;
       const int off = pix * C + off0;
-      const V8 yv = unpack_v8(*reinterpret_cast<const uint4*>(y + off));
-      const V8 go = unpack_v8(*reinterpret_cast<const uint4*>(dout + off));
+      const V8 yv = ld_v8(y + off);
+      const V8 go = ld_v8(dout + off);
       V8 o;
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
@@ -224,7 +228,7 @@ struct ApplyNoPoolOp {
         const float dz = z > 0.f ? go.v[j] : 0.f;
         o.v[j] = fmaf(scale.v[j], dz, fmaf(c1.v[j], yv.v[j], c0.v[j]));
       }
-      *reinterpret_cast<uint4*>(dy + off) = pack_v8(o);
+      st_v8(dy + off, o);
     }
   }
   __device__ void finish(const Params&, float*) const {}
@@ -245,11 +249,11 @@ struct FwdParams {
   float momentum, eps;
 };
 
-constexpr int kFwdItems = 4;   // one input stream: 16 KiB in + 16 KiB out per stage
-
-template <bool POOL>
+template <class T, bool POOL>
 struct FwdOp {
   using Params = FwdParams;
+  using elem = T;
+  static constexpr int kFwdItems = items_1in<T>();   // one input stream: 16 KiB in + 16 KiB out per stage
   V8 scale, shift;
   int C, c0i, pix0, pix_step, y_off, o_off, rowb, gt;
   __device__ FwdOp(const Params& p, int tid) {
@@ -303,13 +307,13 @@ struct FwdOp {
       }
     }
   }
-  __device__ void compute(const __nv_bfloat16* y, const __nv_bfloat16*, __nv_bfloat16* out, int n) const {
+  __device__ void compute(const T* y, const T*, T* out, int n) const {
     if (POOL) {
       if (gt >= n) return;
-      const V8 a = unpack_v8(*reinterpret_cast<const uint4*>(y + y_off));
-      const V8 bq = unpack_v8(*reinterpret_cast<const uint4*>(y + y_off + C));
-      const V8 c = unpack_v8(*reinterpret_cast<const uint4*>(y + y_off + rowb));
-      const V8 d = unpack_v8(*reinterpret_cast<const uint4*>(y + y_off + rowb + C));
+      const V8 a = ld_v8(y + y_off);
+      const V8 bq = ld_v8(y + y_off + C);
+      const V8 c = ld_v8(y + y_off + rowb);
+      const V8 d = ld_v8(y + y_off + rowb + C);
       V8 o;
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
@@ -317,18 +321,18 @@ struct FwdOp {
         const float zc = fmaf(c.v[j], scale.v[j], shift.v[j]), zd = fmaf(d.v[j], scale.v[j], shift.v[j]);
         o.v[j] = fmaxf(fmaxf(fmaxf(za, zb), fmaxf(zc, zd)), 0.f);
       }
-      *reinterpret_cast<uint4*>(out + o_off) = pack_v8(o);
+      st_v8(out + o_off, o);
     } else {
 #pragma unroll
       for (int u = 0; u < kFwdItems; ++u) {
         const int pix = pix0 + u * pix_step;
         if (pix >= n) break;
         const int off = pix * C + c0i;
-        const V8 a = unpack_v8(*reinterpret_cast<const uint4*>(y + off));
+        const V8 a = ld_v8(y + off);
         V8 o;
 #pragma unroll
         for (int j = 0; j < 8; ++j) o.v[j] = fmaxf(fmaf(a.v[j], scale.v[j], shift.v[j]), 0.f);
-        *reinterpret_cast<uint4*>(out + off) = pack_v8(o);
+        st_v8(out + off, o);
       }
     }
   }
@@ -349,8 +353,11 @@ struct ReduceParams {
   int C;
 };
 
+template <class T>
 struct ReduceFromOutOp {
   using Params = ReduceParams;
+  using elem = T;
+  static constexpr int kItemsPerThread = items_2in<T>();
   V8 bt, ig, a1, a2;
   int C, c0i, pix0, pix_step;
   __device__ ReduceFromOutOp(const Params& p, int tid) {
@@ -367,14 +374,14 @@ struct ReduceFromOutOp {
       a1.v[j] = a2.v[j] = 0.f;
     }
   }
-  __device__ void compute(const __nv_bfloat16* out, const __nv_bfloat16* dout, __nv_bfloat16*, int n) {
+  __device__ void compute(const T* out, const T* dout, T*, int n) {
 #pragma unroll
     for (int u = 0; u < kItemsPerThread; ++u) {
       const int pix = pix0 + u * pix_step;
       if (pix >= n) break;
       const int off = pix * C + c0i;
-      const V8 o = unpack_v8(*reinterpret_cast<const uint4*>(out + off));
-      const V8 g = unpack_v8(*reinterpret_cast<const uint4*>(dout + off));
+      const V8 o = ld_v8(out + off);
+      const V8 g = ld_v8(dout + off);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         const float d = o.v[j] > 0.f ? g.v[j] : 0.f;
@@ -413,29 +420,61 @@ using namespace b200dp;
 
 static bool chunks_ok(int C) { return C >= 8 && C % 8 == 0 && C <= 2048 && kThreads % (C / 8) == 0; }
 
-/* BatchNorm(+ReLU) backward apply pass without pooling as a bulk-copy pipeline: same contract and
- * bit-identical results as b200dp_bn_relu_pool_bwd_apply with pool = 0.  C/8 must divide 256. */
-extern "C" int b200dp_bn_bwd_apply_nopool_tma(const void* y, const void* dout, const float* mean, const float* invstd,
-                                              const float* gamma, const float* beta, const float* sums, void* dy,
-                                              float* dgamma, float* dbeta, int B, int H, int W, int C,
-                                              b200dp_stream_t s) {
+template <class T>
+static int apply_nopool_impl(const void* y, const void* dout, const float* mean, const float* invstd,
+                             const float* gamma, const float* beta, const float* sums, void* dy, float* dgamma,
+                             float* dbeta, int B, int H, int W, int C, cudaStream_t s) {
+  constexpr int kBytes = static_cast<int>(sizeof(T));
+  const long P = static_cast<long>(B) * H * W;
+  const ApplyParams p{mean, invstd, gamma, beta, sums, dgamma, dbeta, C, P};
+  const StreamGeom g{P, kThreads * ApplyNoPoolOp<T>::kItemsPerThread / (C / 8), kBytes * C, kBytes * C, kBytes * C};
+  return launch_stream<ApplyNoPoolOp<T>>(p, g, y, dout, dy, s);
+}
+
+/* BatchNorm(+ReLU) backward apply pass without pooling as a bulk-copy pipeline: same contract as
+ * b200dp_bn_relu_pool_bwd_apply_ex with pool = 0 (which routes here).  C/8 must divide 256.
+ * dtype 0 = bf16 activations, 1 = fp32. */
+extern "C" int b200dp_bn_bwd_apply_nopool_tma_ex(const void* y, const void* dout, const float* mean,
+                                                 const float* invstd, const float* gamma, const float* beta,
+                                                 const float* sums, void* dy, float* dgamma, float* dbeta, int B,
+                                                 int H, int W, int C, int dtype, b200dp_stream_t s) {
   if (B <= 0 || H <= 0 || W <= 0 || !chunks_ok(C)) {
     set_error("bn_bwd_apply_nopool_tma: unsupported shape B=%d H=%d W=%d C=%d (C/8 must divide 256)", B, H, W, C);
     return B200DP_EINVAL;
   }
-  const long P = static_cast<long>(B) * H * W;
-  const ApplyParams p{mean, invstd, gamma, beta, sums, dgamma, dbeta, C, P};
-  const StreamGeom g{P, kThreads * kItemsPerThread / (C / 8), 2 * C, 2 * C, 2 * C};
-  return launch_stream<ApplyNoPoolOp>(p, g, y, dout, dy, static_cast<cudaStream_t>(s));
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  if (dtype == 1)
+    return apply_nopool_impl<float>(y, dout, mean, invstd, gamma, beta, sums, dy, dgamma, dbeta, B, H, W, C, st);
+  return apply_nopool_impl<__nv_bfloat16>(y, dout, mean, invstd, gamma, beta, sums, dy, dgamma, dbeta, B, H, W, C, st);
+}
+extern "C" int b200dp_bn_bwd_apply_nopool_tma(const void* y, const void* dout, const float* mean, const float* invstd,
+                                              const float* gamma, const float* beta, const float* sums, void* dy,
+                                              float* dgamma, float* dbeta, int B, int H, int W, int C,
+                                              b200dp_stream_t s) {
+  return b200dp_bn_bwd_apply_nopool_tma_ex(y, dout, mean, invstd, gamma, beta, sums, dy, dgamma, dbeta, B, H, W, C, 0, s);
 }
 
-/* BatchNorm (training or eval) + ReLU (+ 2x2 max-pool) forward as a bulk-copy pipeline: same contract and
- * bit-identical results as b200dp_bn_relu_pool_fwd.  C/8 must divide 256; with pool, (W/2)*(C/8) must. */
-extern "C" int b200dp_bn_relu_pool_fwd_tma(const void* y, const float* stats, const float* gamma, const float* beta,
-                                           float* running_mean, float* running_var, long long* num_batches_tracked,
-                                           float* save_mean, float* save_invstd, void* out, int B, int H, int W,
-                                           int C, int pool, int training, float momentum, float eps,
-                                           b200dp_stream_t s) {
+template <class T>
+static int fwd_impl(const FwdParams& p, const void* y, void* out, int B, int H, int W, int C, int pool,
+                    cudaStream_t s) {
+  constexpr int kBytes = static_cast<int>(sizeof(T));
+  if (pool) {
+    const StreamGeom g{static_cast<long>(B) * (H / 2), kThreads / ((W / 2) * (C / 8)), 2 * kBytes * W * C, 0,
+                       kBytes * (W / 2) * C};
+    return launch_stream<FwdOp<T, true>>(p, g, y, nullptr, out, s);
+  }
+  const StreamGeom g{static_cast<long>(B) * H * W, kThreads * FwdOp<T, false>::kFwdItems / (C / 8), kBytes * C, 0,
+                     kBytes * C};
+  return launch_stream<FwdOp<T, false>>(p, g, y, nullptr, out, s);
+}
+
+/* BatchNorm (training or eval) + ReLU (+ 2x2 max-pool) forward as a bulk-copy pipeline: same contract as
+ * b200dp_bn_relu_pool_fwd_ex (which routes here).  C/8 must divide 256; with pool, (W/2)*(C/8) must. */
+extern "C" int b200dp_bn_relu_pool_fwd_tma_ex(const void* y, const float* stats, const float* gamma, const float* beta,
+                                              float* running_mean, float* running_var, long long* num_batches_tracked,
+                                              float* save_mean, float* save_invstd, void* out, int B, int H, int W,
+                                              int C, int pool, int training, float momentum, float eps, int dtype,
+                                              b200dp_stream_t s) {
   const bool ok = B > 0 && H > 0 && W > 0 && chunks_ok(C) &&
                   (!pool || (((H | W) & 1) == 0 && (W / 2) * (C / 8) <= kThreads && kThreads % ((W / 2) * (C / 8)) == 0));
   if (!ok) {
@@ -444,24 +483,40 @@ extern "C" int b200dp_bn_relu_pool_fwd_tma(const void* y, const float* stats, co
   }
   const FwdParams p{stats, gamma, beta, running_mean, running_var, num_batches_tracked, save_mean, save_invstd,
                     W, C, training, static_cast<long>(B) * H * W, momentum, eps};
-  if (pool) {
-    const StreamGeom g{static_cast<long>(B) * (H / 2), kThreads / ((W / 2) * (C / 8)), 4 * W * C, 0, W * C};
-    return launch_stream<FwdOp<true>>(p, g, y, nullptr, out, static_cast<cudaStream_t>(s));
-  }
-  const StreamGeom g{static_cast<long>(B) * H * W, kThreads * kFwdItems / (C / 8), 2 * C, 0, 2 * C};
-  return launch_stream<FwdOp<false>>(p, g, y, nullptr, out, static_cast<cudaStream_t>(s));
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  return dtype == 1 ? fwd_impl<float>(p, y, out, B, H, W, C, pool, st)
+                    : fwd_impl<__nv_bfloat16>(p, y, out, B, H, W, C, pool, st);
+}
+extern "C" int b200dp_bn_relu_pool_fwd_tma(const void* y, const float* stats, const float* gamma, const float* beta,
+                                           float* running_mean, float* running_var, long long* num_batches_tracked,
+                                           float* save_mean, float* save_invstd, void* out, int B, int H, int W,
+                                           int C, int pool, int training, float momentum, float eps,
+                                           b200dp_stream_t s) {
+  return b200dp_bn_relu_pool_fwd_tma_ex(y, stats, gamma, beta, running_mean, running_var, num_batches_tracked, save_mean,
+                                        save_invstd, out, B, H, W, C, pool, training, momentum, eps, 0, s);
 }
 
 /* Reduction pass of the BatchNorm backward from the block output as a bulk-copy pipeline: the contract of
- * b200dp_bn_relu_pool_bwd_reduce_from_out (sums accumulated onto; equal up to summation order). */
-extern "C" int b200dp_bn_bwd_reduce_from_out_tma(const void* out, const void* dout, const float* gamma,
-                                                 const float* beta, float* sums, long long Q, int C,
-                                                 b200dp_stream_t s) {
+ * b200dp_bn_relu_pool_bwd_reduce_from_out_ex (sums accumulated onto; equal up to summation order). */
+extern "C" int b200dp_bn_bwd_reduce_from_out_tma_ex(const void* out, const void* dout, const float* gamma,
+                                                    const float* beta, float* sums, long long Q, int C, int dtype,
+                                                    b200dp_stream_t s) {
   if (Q <= 0 || !chunks_ok(C)) {
     set_error("bn_bwd_reduce_from_out_tma: unsupported shape Q=%lld C=%d (C/8 must divide 256)", Q, C);
     return B200DP_EINVAL;
   }
   const ReduceParams p{gamma, beta, sums, C};
-  const StreamGeom g{static_cast<long>(Q), kThreads * kItemsPerThread / (C / 8), 2 * C, 2 * C, 0};
-  return launch_stream<ReduceFromOutOp>(p, g, out, dout, nullptr, static_cast<cudaStream_t>(s));
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  if (dtype == 1) {
+    const StreamGeom g{static_cast<long>(Q), kThreads * ReduceFromOutOp<float>::kItemsPerThread / (C / 8), 4 * C, 4 * C, 0};
+    return launch_stream<ReduceFromOutOp<float>>(p, g, out, dout, nullptr, st);
+  }
+  const StreamGeom g{static_cast<long>(Q), kThreads * ReduceFromOutOp<__nv_bfloat16>::kItemsPerThread / (C / 8), 2 * C,
+                     2 * C, 0};
+  return launch_stream<ReduceFromOutOp<__nv_bfloat16>>(p, g, out, dout, nullptr, st);
+}
+extern "C" int b200dp_bn_bwd_reduce_from_out_tma(const void* out, const void* dout, const float* gamma,
+                                                 const float* beta, float* sums, long long Q, int C,
+                                                 b200dp_stream_t s) {
+  return b200dp_bn_bwd_reduce_from_out_tma_ex(out, dout, gamma, beta, sums, Q, C, 0, s);
 }

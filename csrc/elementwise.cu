@@ -43,6 +43,60 @@ B200DP_DEVINL void store_bf16x8(__nv_bfloat16* p, const Vec8& r) {
   *reinterpret_cast<uint4*>(p) = u;
 }
 
+// raw (still packed) eight activations: one 16-byte vector of bf16 or two of fp32
+template <class T>
+struct Raw8;
+template <>
+struct Raw8<__nv_bfloat16> {
+  uint4 a;
+};
+template <>
+struct Raw8<float> {
+  float4 a, b;
+};
+B200DP_DEVINL Raw8<__nv_bfloat16> ldraw8(const __nv_bfloat16* p) {
+  Raw8<__nv_bfloat16> r;
+  r.a = *reinterpret_cast<const uint4*>(p);
+  return r;
+}
+B200DP_DEVINL Raw8<float> ldraw8(const float* p) {
+  Raw8<float> r;
+  r.a = *reinterpret_cast<const float4*>(p);
+  r.b = *(reinterpret_cast<const float4*>(p) + 1);
+  return r;
+}
+B200DP_DEVINL Vec8 load8(const __nv_bfloat16* p) { return load_bf16x8(p); }
+B200DP_DEVINL void store8(__nv_bfloat16* p, const Vec8& r) { store_bf16x8(p, r); }
+B200DP_DEVINL Vec8 load8(const float* p) {
+  const float4 a = *reinterpret_cast<const float4*>(p);
+  const float4 b = *(reinterpret_cast<const float4*>(p) + 1);
+  Vec8 r;
+  r.v[0] = a.x; r.v[1] = a.y; r.v[2] = a.z; r.v[3] = a.w;
+  r.v[4] = b.x; r.v[5] = b.y; r.v[6] = b.z; r.v[7] = b.w;
+  return r;
+}
+B200DP_DEVINL void store8(float* p, const Vec8& r) {
+  *reinterpret_cast<float4*>(p) = make_float4(r.v[0], r.v[1], r.v[2], r.v[3]);
+  *(reinterpret_cast<float4*>(p) + 1) = make_float4(r.v[4], r.v[5], r.v[6], r.v[7]);
+}
+
+template <class T>
+B200DP_DEVINL T operand_cast(float v) {
+  if constexpr (sizeof(T) == 4) return v;
+  else return __float2bfloat16(v);
+}
+template <class T>
+B200DP_DEVINL void operand_store4(T* dst, float a, float b, float c, float d) {
+  if constexpr (sizeof(T) == 4) {
+    *reinterpret_cast<float4*>(dst) = make_float4(a, b, c, d);
+  } else {
+    uint2 o;
+    o.x = pack_bf16x2(a, b);
+    o.y = pack_bf16x2(c, d);
+    *reinterpret_cast<uint2*>(dst) = o;
+  }
+}
+
 B200DP_DEVINL Vec8 load_f32x8(const float* p) {
   const float4 a = *reinterpret_cast<const float4*>(p);
   const float4 b = *reinterpret_cast<const float4*>(p + 4);
@@ -64,11 +118,13 @@ constexpr int kIm2colRows = 4;
 // blockDim is a multiple of 8, so a thread emits the same 16-byte chunk of every patch row it touches: the
 // (tap, channel) -> window offset decode of its 8 columns is done once, outside the pixel loop; the upper
 // half of the row (columns 32..63) is a constant zero store.
-__global__ void __launch_bounds__(256) im2col_c3_v2_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ a0,
-                                                           int B, int H, int W) {
+template <class T, int KP>
+__global__ void __launch_bounds__(256) im2col_c3_v2_kernel(const float* __restrict__ x, T* __restrict__ a0, int B,
+                                                           int H, int W) {
   pdl_launch_dependents();
   pdl_wait();
   extern __shared__ float win[];  // [rows + 2][3 channels][W + 2]
+  constexpr int kChunks = KP / 8;   // 16-byte-aligned groups of 8 columns per patch row (KP = 64 bf16 / 32 fp32)
   const int Wp = W + 2;
   const int groups = (H + kIm2colRows - 1) / kIm2colRows;
   const int n = blockIdx.x / groups, h0 = (blockIdx.x - n * groups) * kIm2colRows;
@@ -79,7 +135,7 @@ __global__ void __launch_bounds__(256) im2col_c3_v2_kernel(const float* __restri
     const int hh = h0 + r - 1;
     win[i] = (hh >= 0 && hh < H && ww >= 0 && ww < W) ? __ldg(x + ((static_cast<long>(n) * 3 + c) * H + hh) * W + ww) : 0.f;
   }
-  const int chunk = threadIdx.x & 7;
+  const int chunk = threadIdx.x % kChunks;
   int off[8];
   unsigned live = 0;
 #pragma unroll
@@ -90,24 +146,21 @@ __global__ void __launch_bounds__(256) im2col_c3_v2_kernel(const float* __restri
     live |= static_cast<unsigned>(real) << j;
   }
   __syncthreads();
-  __nv_bfloat16* dst_base = a0 + (static_cast<long>(n) * H + h0) * W * 64 + chunk * 8;
-  for (int pix = threadIdx.x >> 3; pix < rows * W; pix += blockDim.x >> 3) {
-    uint4 o = make_uint4(0u, 0u, 0u, 0u);
+  T* dst_base = a0 + (static_cast<long>(n) * H + h0) * W * KP + chunk * 8;
+  for (int pix = threadIdx.x / kChunks; pix < rows * W; pix += blockDim.x / kChunks) {
+    Vec8 o;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o.v[j] = 0.f;
     if (live != 0) {
       const int pr = pix / W, w = pix - pr * W;
       const float* base = win + pr * 3 * Wp + w;
-      float v[8];
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         const float t = base[off[j]];
-        v[j] = ((live >> j) & 1u) ? t : 0.f;
+        o.v[j] = ((live >> j) & 1u) ? t : 0.f;
       }
-      o.x = pack_bf16x2(v[0], v[1]);
-      o.y = pack_bf16x2(v[2], v[3]);
-      o.z = pack_bf16x2(v[4], v[5]);
-      o.w = pack_bf16x2(v[6], v[7]);
     }
-    *reinterpret_cast<uint4*>(dst_base + static_cast<long>(pix) * 64) = o;
+    store8(dst_base + static_cast<long>(pix) * KP, o);
   }
 }
 
@@ -115,7 +168,8 @@ __global__ void __launch_bounds__(256) im2col_c3_v2_kernel(const float* __restri
 // per-channel sum / sum of squares of a bf16 [P][C] matrix (stand-alone variant;
 // the conv epilogue can produce the same numbers fused).
 // ---------------------------------------------------------------------------
-__global__ void bn_stats_kernel(const __nv_bfloat16* __restrict__ y, float* __restrict__ stats, long P, int C) {
+template <class T>
+__global__ void bn_stats_kernel(const T* __restrict__ y, float* __restrict__ stats, long P, int C) {
   pdl_launch_dependents();
   pdl_wait();
   extern __shared__ float red[];  // [rows_per_block][C] x 2
@@ -129,7 +183,7 @@ __global__ void bn_stats_kernel(const __nv_bfloat16* __restrict__ y, float* __re
   if (rl < rows_per_block) {
     for (long r = static_cast<long>(blockIdx.x) * rows_per_block + rl; r < P;
          r += static_cast<long>(gridDim.x) * rows_per_block) {
-      const Vec8 v = load_bf16x8(y + r * C + chunk * 8);
+      const Vec8 v = load8(y + r * C + chunk * 8);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         s1.v[j] += v.v[j];
@@ -161,8 +215,8 @@ __global__ void bn_stats_kernel(const __nv_bfloat16* __restrict__ y, float* __re
 // ---------------------------------------------------------------------------
 // BN(train or eval) + ReLU (+ 2x2/2 max-pool) forward
 // ---------------------------------------------------------------------------
-struct BnFwdParams {
-  const __nv_bfloat16* y;
+struct BnFwdParams {   // y / out: activations of type T (bf16 or fp32), selected by the kernel's template argument
+  const void* y;
   const float* stats;  // [2][C] sum, sumsq over P = B*H*W (training only)
   const float* gamma;
   const float* beta;
@@ -171,10 +225,19 @@ struct BnFwdParams {
   long long* num_batches_tracked;
   float* save_mean;
   float* save_invstd;
-  __nv_bfloat16* out;
+  void* out;
   int B, H, W, C, pool, training;
   float momentum, eps;
 };
+
+B200DP_DEVINL Vec8 unpack8(const Raw8<float>& u) {
+  Vec8 r;
+  r.v[0] = u.a.x; r.v[1] = u.a.y; r.v[2] = u.a.z; r.v[3] = u.a.w;
+  r.v[4] = u.b.x; r.v[5] = u.b.y; r.v[6] = u.b.z; r.v[7] = u.b.w;
+  return r;
+}
+B200DP_DEVINL Vec8 unpack8(const uint4& u);
+B200DP_DEVINL Vec8 unpack8(const Raw8<__nv_bfloat16>& u) { return unpack8(u.a); }
 
 B200DP_DEVINL Vec8 unpack8(const uint4& u) {
   Vec8 r;
@@ -188,9 +251,12 @@ B200DP_DEVINL Vec8 unpack8(const uint4& u) {
 
 // Each thread owns 8 channels (scale/shift stay in registers) and walks output pixels two at a
 // time so that up to eight 16-byte loads are in flight per thread.
+template <class T>
 __global__ void __launch_bounds__(256, 3) bn_relu_pool_fwd_kernel(const BnFwdParams p) {
   pdl_launch_dependents();
   pdl_wait();
+  const T* __restrict__ py = static_cast<const T*>(p.y);
+  T* __restrict__ pout = static_cast<T*>(p.out);
   const int chunks = p.C / 8;
   const int rows_per_block = blockDim.x / chunks;
   const int chunk = threadIdx.x % chunks;
@@ -250,13 +316,13 @@ __global__ void __launch_bounds__(256, 3) bn_relu_pool_fwd_kernel(const BnFwdPar
         const long n = q / (static_cast<long>(Wo) * Ho);
         off[u] = ((n * p.H + 2 * ho) * p.W + 2 * wo) * p.C + c0;
       }
-      uint4 raw[2][4];
+      Raw8<T> raw[2][4];
 #pragma unroll
       for (int u = 0; u < 2; ++u) {
-        raw[u][0] = *reinterpret_cast<const uint4*>(p.y + off[u]);
-        raw[u][1] = *reinterpret_cast<const uint4*>(p.y + off[u] + p.C);
-        raw[u][2] = *reinterpret_cast<const uint4*>(p.y + off[u] + rowb);
-        raw[u][3] = *reinterpret_cast<const uint4*>(p.y + off[u] + rowb + p.C);
+        raw[u][0] = ldraw8(py + off[u]);
+        raw[u][1] = ldraw8(py + off[u] + p.C);
+        raw[u][2] = ldraw8(py + off[u] + rowb);
+        raw[u][3] = ldraw8(py + off[u] + rowb + p.C);
       }
 #pragma unroll
       for (int u = 0; u < 2; ++u) {
@@ -269,11 +335,11 @@ __global__ void __launch_bounds__(256, 3) bn_relu_pool_fwd_kernel(const BnFwdPar
           const float zc = fmaf(c.v[j], scale.v[j], shift.v[j]), zd = fmaf(d.v[j], scale.v[j], shift.v[j]);
           o.v[j] = fmaxf(fmaxf(fmaxf(za, zb), fmaxf(zc, zd)), 0.f);
         }
-        store_bf16x8(p.out + (u == 0 ? qa : qb) * p.C + c0, o);
+        store8(pout + (u == 0 ? qa : qb) * p.C + c0, o);
       }
     } else {
-      const uint4 ra = *reinterpret_cast<const uint4*>(p.y + qa * p.C + c0);
-      const uint4 rb = *reinterpret_cast<const uint4*>(p.y + (hasb ? qb : qa) * p.C + c0);
+      const Raw8<T> ra = ldraw8(py + qa * p.C + c0);
+      const Raw8<T> rb = ldraw8(py + (hasb ? qb : qa) * p.C + c0);
       const Vec8 a = unpack8(ra), b2 = unpack8(rb);
       Vec8 oa, ob;
 #pragma unroll
@@ -281,8 +347,8 @@ __global__ void __launch_bounds__(256, 3) bn_relu_pool_fwd_kernel(const BnFwdPar
         oa.v[j] = fmaxf(fmaf(a.v[j], scale.v[j], shift.v[j]), 0.f);
         ob.v[j] = fmaxf(fmaf(b2.v[j], scale.v[j], shift.v[j]), 0.f);
       }
-      store_bf16x8(p.out + qa * p.C + c0, oa);
-      if (hasb) store_bf16x8(p.out + qb * p.C + c0, ob);
+      store8(pout + qa * p.C + c0, oa);
+      if (hasb) store8(pout + qb * p.C + c0, ob);
     }
   }
 }
@@ -293,15 +359,15 @@ __global__ void __launch_bounds__(256, 3) bn_relu_pool_fwd_kernel(const BnFwdPar
 // dz is the gradient reaching the BN output: the incoming gradient routed through
 // the pool arg-max (first maximum in scan order) and masked by ReLU.
 // ---------------------------------------------------------------------------
-struct BnBwdParams {
-  const __nv_bfloat16* y;
-  const __nv_bfloat16* dout;
+struct BnBwdParams {   // y / dout / dy: activations of type T, selected by the kernel's template argument
+  const void* y;
+  const void* dout;
   const float* mean;
   const float* invstd;
   const float* gamma;
   const float* beta;
   float* sums;  // [2][C]: S1 = sum dz, S2 = sum dz*xhat
-  __nv_bfloat16* dy;
+  void* dy;
   float* dgamma;
   float* dbeta;
   int B, H, W, C, pool;
@@ -311,8 +377,11 @@ struct BnBwdParams {
 //   z  = y*scale + shift                       scale = gamma*invstd, shift = beta - mean*scale
 //   pass 1 accumulates  a1 = sum dz,  a2 = sum dz*y ;  S2 = invstd*(a2 - mean*a1) at the end
 //   pass 2 writes       dy = scale*dz + c0 + c1*y   c1 = -scale*invstd*S2/P, c0 = -scale*S1/P - c1*mean
-template <bool APPLY>
+template <class T, bool APPLY>
 B200DP_DEVINL void bn_relu_pool_bwd_body(const BnBwdParams& p, float* red) {
+  const T* __restrict__ py = static_cast<const T*>(p.y);
+  const T* __restrict__ pdout = static_cast<const T*>(p.dout);
+  T* __restrict__ pdy = static_cast<T*>(p.dy);
   const int chunks = p.C / 8;
   const int rows_per_block = blockDim.x / chunks;
   const int chunk = threadIdx.x % chunks;
@@ -360,29 +429,20 @@ B200DP_DEVINL void bn_relu_pool_bwd_body(const BnBwdParams& p, float* red) {
   if (rl < rows_per_block) {
     for (long q = static_cast<long>(blockIdx.x) * rows_per_block + rl; q < Q;
          q += static_cast<long>(gridDim.x) * rows_per_block) {
-      const Vec8 go = load_bf16x8(p.dout + q * p.C + c0i);
+      const Vec8 go = load8(pdout + q * p.C + c0i);
       if (p.pool) {
         const int wo = static_cast<int>(q % Wo);
         const int ho = static_cast<int>((q / Wo) % Ho);
         const long n = q / (static_cast<long>(Wo) * Ho);
         const long off = ((n * p.H + 2 * ho) * p.W + 2 * wo) * p.C + c0i;
         const long rowb = static_cast<long>(p.W) * p.C;
-        // keep the four candidates packed (bf16) -- 16 registers instead of 32
-        const uint4 raw0 = *reinterpret_cast<const uint4*>(p.y + off);
-        const uint4 raw1 = *reinterpret_cast<const uint4*>(p.y + off + p.C);
-        const uint4 raw2 = *reinterpret_cast<const uint4*>(p.y + off + rowb);
-        const uint4 raw3 = *reinterpret_cast<const uint4*>(p.y + off + rowb + p.C);
-        const uint32_t w0[4] = {raw0.x, raw0.y, raw0.z, raw0.w}, w1[4] = {raw1.x, raw1.y, raw1.z, raw1.w};
-        const uint32_t w2[4] = {raw2.x, raw2.y, raw2.z, raw2.w}, w3[4] = {raw3.x, raw3.y, raw3.z, raw3.w};
+        const Vec8 v0 = load8(py + off), v1 = load8(py + off + p.C);
+        const Vec8 v2 = load8(py + off + rowb), v3 = load8(py + off + rowb + p.C);
         Vec8 o0, o1, o2, o3;
+        {
 #pragma unroll
-        for (int h = 0; h < 4; ++h) {
-          const float2 y0 = unpack_bf16x2(w0[h]), y1 = unpack_bf16x2(w1[h]);
-          const float2 y2 = unpack_bf16x2(w2[h]), y3 = unpack_bf16x2(w3[h]);
-#pragma unroll
-          for (int e = 0; e < 2; ++e) {
-            const int j = 2 * h + e;
-            const float ya = e ? y0.y : y0.x, yb = e ? y1.y : y1.x, yc = e ? y2.y : y2.x, yd = e ? y3.y : y3.x;
+          for (int j = 0; j < 8; ++j) {
+            const float ya = v0.v[j], yb = v1.v[j], yc = v2.v[j], yd = v3.v[j];
             // same arithmetic as the forward pass so that the winner is identical
             const float za = fmaxf(fmaf(ya, scale.v[j], shift.v[j]), 0.f);
             const float zb = fmaxf(fmaf(yb, scale.v[j], shift.v[j]), 0.f);
@@ -407,13 +467,13 @@ B200DP_DEVINL void bn_relu_pool_bwd_body(const BnBwdParams& p, float* red) {
           }
         }
         if (APPLY) {
-          store_bf16x8(p.dy + off, o0);
-          store_bf16x8(p.dy + off + p.C, o1);
-          store_bf16x8(p.dy + off + rowb, o2);
-          store_bf16x8(p.dy + off + rowb + p.C, o3);
+          store8(pdy + off, o0);
+          store8(pdy + off + p.C, o1);
+          store8(pdy + off + rowb, o2);
+          store8(pdy + off + rowb + p.C, o3);
         }
       } else {
-        const Vec8 yv = load_bf16x8(p.y + q * p.C + c0i);
+        const Vec8 yv = load8(py + q * p.C + c0i);
         Vec8 o;
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
@@ -426,7 +486,7 @@ B200DP_DEVINL void bn_relu_pool_bwd_body(const BnBwdParams& p, float* red) {
             a2.v[j] = fmaf(dz, yv.v[j], a2.v[j]);
           }
         }
-        if (APPLY) store_bf16x8(p.dy + q * p.C + c0i, o);
+        if (APPLY) store8(pdy + q * p.C + c0i, o);
       }
     }
   }
@@ -458,9 +518,13 @@ B200DP_DEVINL void bn_relu_pool_bwd_body(const BnBwdParams& p, float* red) {
 // Apply pass for blocks WITHOUT a pool: purely element-wise, so four rows per thread per iteration
 // (eight 16-byte loads in flight) instead of one -- the generic body keeps too few bytes in flight for
 // these layers (ncu: 42 us for 50 MB at 256 channels x 8x8).
+template <class T>
 __global__ void __launch_bounds__(256, 3) bn_bwd_apply_nopool_kernel(const BnBwdParams p) {
   pdl_launch_dependents();
   pdl_wait();
+  const T* __restrict__ py = static_cast<const T*>(p.y);
+  const T* __restrict__ pdout = static_cast<const T*>(p.dout);
+  T* __restrict__ pdy = static_cast<T*>(p.dy);
   const int chunks = p.C / 8;
   const int rows_per_block = blockDim.x / chunks;
   const int chunk = threadIdx.x % chunks, rl = threadIdx.x / chunks, c0i = chunk * 8;
@@ -492,13 +556,13 @@ __global__ void __launch_bounds__(256, 3) bn_bwd_apply_nopool_kernel(const BnBwd
   constexpr int U = 4;
   const long stride = static_cast<long>(gridDim.x) * rows_per_block;
   for (long q0 = static_cast<long>(blockIdx.x) * rows_per_block + rl; q0 < Q; q0 += U * stride) {
-    uint4 ry[U], rg[U];
+    Raw8<T> ry[U], rg[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const long q = q0 + u * stride;
       const long qq = q < Q ? q : q0;
-      ry[u] = *reinterpret_cast<const uint4*>(p.y + qq * p.C + c0i);
-      rg[u] = *reinterpret_cast<const uint4*>(p.dout + qq * p.C + c0i);
+      ry[u] = ldraw8(py + qq * p.C + c0i);
+      rg[u] = ldraw8(pdout + qq * p.C + c0i);
     }
 #pragma unroll
     for (int u = 0; u < U; ++u) {
@@ -512,16 +576,20 @@ __global__ void __launch_bounds__(256, 3) bn_bwd_apply_nopool_kernel(const BnBwd
         const float dz = z > 0.f ? go.v[j] : 0.f;
         o.v[j] = fmaf(scale.v[j], dz, fmaf(c1.v[j], yv.v[j], c0.v[j]));
       }
-      store_bf16x8(p.dy + q * p.C + c0i, o);
+      store8(pdy + q * p.C + c0i, o);
     }
   }
 }
 
 // Apply pass for POOLED blocks, two pooled pixels per thread per iteration (ten 16-byte loads in
 // flight instead of five).  Same arithmetic as the generic body, so winners match the forward pass.
+template <class T>
 __global__ void __launch_bounds__(256, 2) bn_bwd_apply_pool_kernel(const BnBwdParams p) {
   pdl_launch_dependents();
   pdl_wait();
+  const T* __restrict__ py = static_cast<const T*>(p.y);
+  const T* __restrict__ pdout = static_cast<const T*>(p.dout);
+  T* __restrict__ pdy = static_cast<T*>(p.dy);
   const int chunks = p.C / 8;
   const int rows_per_block = blockDim.x / chunks;
   const int chunk = threadIdx.x % chunks, rl = threadIdx.x / chunks, c0i = chunk * 8;
@@ -556,7 +624,7 @@ __global__ void __launch_bounds__(256, 2) bn_bwd_apply_pool_kernel(const BnBwdPa
   const long rowb = static_cast<long>(p.W) * p.C;
   for (long q0 = static_cast<long>(blockIdx.x) * rows_per_block + rl; q0 < Q; q0 += U * stride) {
     long off[U];
-    uint4 raw[U][4], rg[U];
+    Raw8<T> raw[U][4], rg[U];
     bool live[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
@@ -567,11 +635,11 @@ __global__ void __launch_bounds__(256, 2) bn_bwd_apply_pool_kernel(const BnBwdPa
       const int ho = static_cast<int>((qq / Wo) % Ho);
       const long n = qq / (static_cast<long>(Wo) * Ho);
       off[u] = ((n * p.H + 2 * ho) * p.W + 2 * wo) * p.C + c0i;
-      rg[u] = *reinterpret_cast<const uint4*>(p.dout + qq * p.C + c0i);
-      raw[u][0] = *reinterpret_cast<const uint4*>(p.y + off[u]);
-      raw[u][1] = *reinterpret_cast<const uint4*>(p.y + off[u] + p.C);
-      raw[u][2] = *reinterpret_cast<const uint4*>(p.y + off[u] + rowb);
-      raw[u][3] = *reinterpret_cast<const uint4*>(p.y + off[u] + rowb + p.C);
+      rg[u] = ldraw8(pdout + qq * p.C + c0i);
+      raw[u][0] = ldraw8(py + off[u]);
+      raw[u][1] = ldraw8(py + off[u] + p.C);
+      raw[u][2] = ldraw8(py + off[u] + rowb);
+      raw[u][3] = ldraw8(py + off[u] + rowb + p.C);
     }
 #pragma unroll
     for (int u = 0; u < U; ++u) {
@@ -596,20 +664,20 @@ __global__ void __launch_bounds__(256, 2) bn_bwd_apply_pool_kernel(const BnBwdPa
         o2.v[j] = fmaf(c1.v[j], yc.v[j], c0.v[j]) + (win == 2 ? sdz : 0.f);
         o3.v[j] = fmaf(c1.v[j], yd.v[j], c0.v[j]) + (win == 3 ? sdz : 0.f);
       }
-      store_bf16x8(p.dy + off[u], o0);
-      store_bf16x8(p.dy + off[u] + p.C, o1);
-      store_bf16x8(p.dy + off[u] + rowb, o2);
-      store_bf16x8(p.dy + off[u] + rowb + p.C, o3);
+      store8(pdy + off[u], o0);
+      store8(pdy + off[u] + p.C, o1);
+      store8(pdy + off[u] + rowb, o2);
+      store8(pdy + off[u] + rowb + p.C, o3);
     }
   }
 }
 
-template <bool APPLY>
+template <class T, bool APPLY>
 __global__ void __launch_bounds__(256, 3) bn_relu_pool_bwd_kernel(const BnBwdParams p) {
   pdl_launch_dependents();
   pdl_wait();
   extern __shared__ float red[];
-  bn_relu_pool_bwd_body<APPLY>(p, red);
+  bn_relu_pool_bwd_body<T, APPLY>(p, red);
 }
 
 // ---------------------------------------------------------------------------
@@ -625,14 +693,21 @@ __global__ void __launch_bounds__(256, 3) bn_relu_pool_bwd_kernel(const BnBwdPar
 // a stage = kBnTmaItems / (Wo * C/8) consecutive tiles (all tiles are contiguous in memory, image
 // boundaries included).  Requires (Wo * C/8) to divide kBnTmaItems.
 // ---------------------------------------------------------------------------
-constexpr int kBnTmaItems = 256;                       // work items per stage = threads per block
+// Work items per stage = threads per block: 256 for bf16, 128 for fp32 activations (the same bytes per stage).
 constexpr int kBnTmaStages = 3;
-constexpr int kBnTmaYBytes = kBnTmaItems * 4 * 16;      // 16 KiB of y per stage (4 vectors per item)
-constexpr int kBnTmaGBytes = kBnTmaItems * 16;          // 4 KiB of dout per stage
+constexpr int kBnTmaYBytes = 256 * 4 * 16;              // 16 KiB of y per stage (4 vectors of 8 channels per item)
+constexpr int kBnTmaGBytes = 256 * 16;                  // 4 KiB of dout per stage
 constexpr int kBnTmaStageBytes = kBnTmaYBytes + kBnTmaGBytes;
 constexpr int kBnTmaSmem = kBnTmaStages * kBnTmaStageBytes + 2 * kBnTmaYBytes + 64 + 128;
+template <class T>
+constexpr int bn_tma_items() { return 512 / static_cast<int>(sizeof(T)); }
 
-__global__ void __launch_bounds__(kBnTmaItems, 2) bn_bwd_apply_pool_tma_kernel(const BnBwdParams p) {
+template <class T>
+__global__ void __launch_bounds__(bn_tma_items<T>(), 2) bn_bwd_apply_pool_tma_kernel(const BnBwdParams p) {
+  constexpr int kBnTmaItems = bn_tma_items<T>();
+  const T* __restrict__ py = static_cast<const T*>(p.y);
+  const T* __restrict__ pdout = static_cast<const T*>(p.dout);
+  T* __restrict__ pdy = static_cast<T*>(p.dy);
   extern __shared__ uint8_t bn_tma_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(bn_tma_raw) + 127) & ~uintptr_t(127));
   uint8_t* out_buf = smem + kBnTmaStages * kBnTmaStageBytes;                     // 2 x 16 KiB
@@ -642,8 +717,8 @@ __global__ void __launch_bounds__(kBnTmaItems, 2) bn_bwd_apply_pool_tma_kernel(c
   const int Ho = p.H / 2, Wo = p.W / 2;
   const int items_per_tile = Wo * chunks;
   const int G = kBnTmaItems / items_per_tile;                       // tiles per stage
-  const long T = static_cast<long>(p.B) * Ho;                       // tiles in the tensor
-  const long num_chunks = (T + G - 1) / G;
+  const long NT = static_cast<long>(p.B) * Ho;                      // tiles in the tensor
+  const long num_chunks = (NT + G - 1) / G;
   const long tile_y_elems = 2L * p.W * p.C, tile_g_elems = static_cast<long>(Wo) * p.C;
   if (threadIdx.x == 0) {
     for (int s = 0; s < kBnTmaStages; ++s) mbar_init(&full_bar[s], 1);
@@ -657,12 +732,12 @@ __global__ void __launch_bounds__(kBnTmaItems, 2) bn_bwd_apply_pool_tma_kernel(c
     const long chunk_id = blockIdx.x + j * static_cast<long>(gridDim.x);
     if (chunk_id >= num_chunks) return;
     const long t0 = chunk_id * G;
-    const int tiles = static_cast<int>(min(static_cast<long>(G), T - t0));
+    const int tiles = static_cast<int>(min(static_cast<long>(G), NT - t0));
     uint8_t* dst = smem + stage * kBnTmaStageBytes;
-    const uint32_t yb = static_cast<uint32_t>(tiles * tile_y_elems * 2), gb = static_cast<uint32_t>(tiles * tile_g_elems * 2);
+    const uint32_t yb = static_cast<uint32_t>(tiles * tile_y_elems * sizeof(T)), gb = static_cast<uint32_t>(tiles * tile_g_elems * sizeof(T));
     mbar_arrive_expect_tx(&full_bar[stage], yb + gb);
-    bulk_load_1d(dst, p.y + t0 * tile_y_elems, yb, &full_bar[stage]);
-    bulk_load_1d(dst + kBnTmaYBytes, p.dout + t0 * tile_g_elems, gb, &full_bar[stage]);
+    bulk_load_1d(dst, py + t0 * tile_y_elems, yb, &full_bar[stage]);
+    bulk_load_1d(dst + kBnTmaYBytes, pdout + t0 * tile_g_elems, gb, &full_bar[stage]);
   };
   if (threadIdx.x == 0)
     for (int s = 0; s < kBnTmaStages; ++s) issue(s, s);
@@ -704,20 +779,20 @@ __global__ void __launch_bounds__(kBnTmaItems, 2) bn_bwd_apply_pool_tma_kernel(c
     const long chunk_id = blockIdx.x + j * static_cast<long>(gridDim.x);
     if (chunk_id >= num_chunks) break;
     const long t0 = chunk_id * G;
-    const int tiles = static_cast<int>(min(static_cast<long>(G), T - t0));
+    const int tiles = static_cast<int>(min(static_cast<long>(G), NT - t0));
     uint8_t* ob = out_buf + (j & 1) * kBnTmaYBytes;
     if (threadIdx.x == 0) bulk_wait_group_read<1>();   // the store issued two chunks ago has drained this buffer
     mbar_wait(&full_bar[stage], phase);                // this stage's y and dout have landed
     __syncthreads();                                   // ... and everybody knows the output buffer is free
     if (gt < tiles) {
-      const __nv_bfloat16* ys = reinterpret_cast<const __nv_bfloat16*>(smem + stage * kBnTmaStageBytes);
-      const __nv_bfloat16* gs = reinterpret_cast<const __nv_bfloat16*>(smem + stage * kBnTmaStageBytes + kBnTmaYBytes);
-      __nv_bfloat16* os = reinterpret_cast<__nv_bfloat16*>(ob);
-      const Vec8 go = unpack8(*reinterpret_cast<const uint4*>(gs + g_off));
-      const Vec8 ya = unpack8(*reinterpret_cast<const uint4*>(ys + y_off));
-      const Vec8 yb = unpack8(*reinterpret_cast<const uint4*>(ys + y_off + p.C));
-      const Vec8 yc = unpack8(*reinterpret_cast<const uint4*>(ys + y_off + rowb));
-      const Vec8 yd = unpack8(*reinterpret_cast<const uint4*>(ys + y_off + rowb + p.C));
+      const T* ys = reinterpret_cast<const T*>(smem + stage * kBnTmaStageBytes);
+      const T* gs = reinterpret_cast<const T*>(smem + stage * kBnTmaStageBytes + kBnTmaYBytes);
+      T* os = reinterpret_cast<T*>(ob);
+      const Vec8 go = load8(gs + g_off);
+      const Vec8 ya = load8(ys + y_off);
+      const Vec8 yb = load8(ys + y_off + p.C);
+      const Vec8 yc = load8(ys + y_off + rowb);
+      const Vec8 yd = load8(ys + y_off + rowb + p.C);
       Vec8 o0, o1, o2, o3;
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
@@ -736,15 +811,15 @@ __global__ void __launch_bounds__(kBnTmaItems, 2) bn_bwd_apply_pool_tma_kernel(c
         o2.v[k] = fmaf(c1.v[k], yc.v[k], c0.v[k]) + (win == 2 ? sdz : 0.f);
         o3.v[k] = fmaf(c1.v[k], yd.v[k], c0.v[k]) + (win == 3 ? sdz : 0.f);
       }
-      store_bf16x8(os + y_off, o0);
-      store_bf16x8(os + y_off + p.C, o1);
-      store_bf16x8(os + y_off + rowb, o2);
-      store_bf16x8(os + y_off + rowb + p.C, o3);
+      store8(os + y_off, o0);
+      store8(os + y_off + p.C, o1);
+      store8(os + y_off + rowb, o2);
+      store8(os + y_off + rowb + p.C, o3);
     }
     fence_proxy_async_smem();   // generic-proxy writes above must be visible to the bulk store below
     __syncthreads();            // everyone has written its outputs and finished reading the input stage
     if (threadIdx.x == 0) {
-      bulk_store_1d(p.dy + t0 * tile_y_elems, ob, static_cast<uint32_t>(tiles * tile_y_elems * 2));
+      bulk_store_1d(pdy + t0 * tile_y_elems, ob, static_cast<uint32_t>(tiles * tile_y_elems * sizeof(T)));
       bulk_commit_group();
       issue(j + kBnTmaStages, stage);   // refill the stage just consumed
     }
@@ -762,8 +837,9 @@ __global__ void __launch_bounds__(kBnTmaItems, 2) bn_bwd_apply_pool_tma_kernel(c
 // layers this reads two quarter-size tensors instead of the full-resolution y (2.5x fewer bytes) and
 // needs no arg-max search; `a` is the stored bf16 value, i.e. z rounded to 8 bits of mantissa, whose
 // error averages out over the B*H*W terms of the sums.
-__global__ void __launch_bounds__(256, 4) bn_bwd_reduce_from_out_kernel(const __nv_bfloat16* __restrict__ out,
-                                                                        const __nv_bfloat16* __restrict__ dout,
+template <class T>
+__global__ void __launch_bounds__(256, 4) bn_bwd_reduce_from_out_kernel(const T* __restrict__ out,
+                                                                        const T* __restrict__ dout,
                                                                         const float* __restrict__ gamma,
                                                                         const float* __restrict__ beta,
                                                                         float* __restrict__ sums, long Q, int C) {
@@ -788,10 +864,10 @@ __global__ void __launch_bounds__(256, 4) bn_bwd_reduce_from_out_kernel(const __
     for (long qa = static_cast<long>(blockIdx.x) * rows_per_block + rl; qa < Q; qa += 2 * stride) {
       const long qb = qa + stride;
       const bool hasb = qb < Q;
-      const uint4 oa = *reinterpret_cast<const uint4*>(out + qa * C + c0);
-      const uint4 ga = *reinterpret_cast<const uint4*>(dout + qa * C + c0);
-      const uint4 ob = *reinterpret_cast<const uint4*>(out + (hasb ? qb : qa) * C + c0);
-      const uint4 gb = *reinterpret_cast<const uint4*>(dout + (hasb ? qb : qa) * C + c0);
+      const Raw8<T> oa = ldraw8(out + qa * C + c0);
+      const Raw8<T> ga = ldraw8(dout + qa * C + c0);
+      const Raw8<T> ob = ldraw8(out + (hasb ? qb : qa) * C + c0);
+      const Raw8<T> gb = ldraw8(dout + (hasb ? qb : qa) * C + c0);
       const Vec8 o1 = unpack8(oa), g1 = unpack8(ga), o2 = unpack8(ob), g2 = unpack8(gb);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
@@ -832,7 +908,8 @@ constexpr int kLinTileB = 256;
 
 // one warp per sample: the 16 activations of a lane are loaded once, all O dot products run as
 // independent chains, then O warp reductions
-__global__ void __launch_bounds__(128) linear_fwd_kernel(const __nv_bfloat16* __restrict__ x,
+template <class T>
+__global__ void __launch_bounds__(128) linear_fwd_kernel(const T* __restrict__ x,
                                                          const float* __restrict__ w, const float* __restrict__ bias,
                                                          float* __restrict__ logits, int B, int F, int O) {
   pdl_launch_dependents();
@@ -840,12 +917,12 @@ __global__ void __launch_bounds__(128) linear_fwd_kernel(const __nv_bfloat16* __
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (warp >= B) return;
-  const __nv_bfloat16* xr = x + static_cast<long>(warp) * F;
+  const T* xr = x + static_cast<long>(warp) * F;
   float acc[kLinMaxO];
 #pragma unroll
   for (int o = 0; o < kLinMaxO; ++o) acc[o] = 0.f;
   for (int f = lane * 8; f < F; f += 256) {
-    const Vec8 xv = load_bf16x8(xr + f);
+    const Vec8 xv = load8(xr + f);
 #pragma unroll
     for (int o = 0; o < kLinMaxO; ++o) {
       if (o < O) {
@@ -918,10 +995,11 @@ __global__ void cross_entropy_kernel(const float* __restrict__ logits, const lon
 // blocks [0, nW): dW (and db) for a tile of 64 features; blocks [nW, ...): dX.
 // dW[o][f] = sum_b dl[b][o] * x[b][f]: 64 feature lanes x 4 batch groups per block, the dl tile
 // staged in shared memory, O accumulators per thread, batch groups combined through smem.
-__global__ void __launch_bounds__(256) linear_bwd_kernel(const __nv_bfloat16* __restrict__ x,
+template <class T>
+__global__ void __launch_bounds__(256) linear_bwd_kernel(const T* __restrict__ x,
                                                          const float* __restrict__ w,
                                                          const float* __restrict__ dlogits, float* __restrict__ dw,
-                                                         float* __restrict__ db, __nv_bfloat16* __restrict__ dx,
+                                                         float* __restrict__ db, T* __restrict__ dx,
                                                          int B, int F, int O, int nW) {
   pdl_launch_dependents();
   pdl_wait();
@@ -944,7 +1022,7 @@ __global__ void __launch_bounds__(256) linear_bwd_kernel(const __nv_bfloat16* __
     if (f < F) {
 #pragma unroll 4
       for (int b = bg; b < nb; b += 4) {
-        const float xv = __bfloat162float(x[static_cast<long>(b_lo + b) * F + f]);
+        const float xv = static_cast<float>(x[static_cast<long>(b_lo + b) * F + f]);
 #pragma unroll
         for (int o = 0; o < kLinMaxO; ++o)
           if (o < O) acc[o] = fmaf(s_dl[b * O + o], xv, acc[o]);
@@ -972,7 +1050,7 @@ __global__ void __launch_bounds__(256) linear_bwd_kernel(const __nv_bfloat16* __
       const int i = static_cast<int>(idx / F), f = static_cast<int>(idx - static_cast<long>(i) * F);
       float acc = 0.f;
       for (int o = 0; o < O; ++o) acc = fmaf(dlogits[static_cast<long>(i) * O + o], w[static_cast<long>(o) * F + f], acc);
-      dx[idx] = __float2bfloat16(acc);
+      dx[idx] = operand_cast<T>(acc);
     }
   }
 }
@@ -990,11 +1068,12 @@ __device__ float g_head_loss_part[kHeadMaxBlocks];
 __device__ int g_head_corr_part[kHeadMaxBlocks];
 __device__ unsigned int g_head_blocks_done = 0;
 
+template <class T>
 __global__ void __launch_bounds__(kHeadWarps * 32)
-    head_fwd_bwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w,
+    head_fwd_bwd_kernel(const T* __restrict__ x, const float* __restrict__ w,
                         const float* __restrict__ bias, const long long* __restrict__ target,
                         float* __restrict__ logits, float* __restrict__ loss, int* __restrict__ correct,
-                        float* __restrict__ dlogits, __nv_bfloat16* __restrict__ dx, float* __restrict__ dw,
+                        float* __restrict__ dlogits, T* __restrict__ dx, float* __restrict__ dw,
                         float* __restrict__ db, int B, int F, int O, float grad_scale) {
   pdl_launch_dependents();
   pdl_wait();
@@ -1011,12 +1090,12 @@ __global__ void __launch_bounds__(kHeadWarps * 32)
   float my_loss = 0.f;
   int my_corr = 0;
   if (live) {
-    const __nv_bfloat16* xr = x + static_cast<long>(i) * F;
+    const T* xr = x + static_cast<long>(i) * F;
     float acc[kLinMaxO];
 #pragma unroll
     for (int o = 0; o < kLinMaxO; ++o) acc[o] = 0.f;
     for (int f = lane * 8; f < F; f += 256) {
-      const Vec8 xv = load_bf16x8(xr + f);
+      const Vec8 xv = load8(xr + f);
 #pragma unroll
       for (int j = 0; j < 8; ++j) xs[wib * F + f + j] = xv.v[j];
 #pragma unroll
@@ -1080,7 +1159,7 @@ __global__ void __launch_bounds__(kHeadWarps * 32)
           for (int j = 0; j < 8; ++j) a.v[j] = fmaf(dl[o], wv.v[j], a.v[j]);
         }
       }
-      store_bf16x8(dx + static_cast<long>(i) * F + f, a);
+      store8(dx + static_cast<long>(i) * F + f, a);
     }
   } else {
     for (int f = lane; f < F; f += 32) xs[wib * F + f] = 0.f;
@@ -1179,6 +1258,17 @@ __global__ void __launch_bounds__(256) fill_zero_kernel(uint4* __restrict__ dst,
   for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < n16; i += stride) dst[i] = z;
 }
 
+// Clear two fp32 ranges of any length (the classifier's dW / db before the atomics of linear_bwd).
+__global__ void __launch_bounds__(256) fill_zero_f32_pair_kernel(float* __restrict__ a, long na, float* __restrict__ b,
+                                                                 long nb) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const long stride = static_cast<long>(gridDim.x) * blockDim.x;
+  const long first = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x;
+  for (long i = first; i < na; i += stride) a[i] = 0.f;
+  for (long i = first; i < nb; i += stride) b[i] = 0.f;
+}
+
 // Device-to-device copy of up to two ranges of 16-byte words in one launch (a step's staged images and
 // labels into the buffers the captured step reads).
 __global__ void __launch_bounds__(256) copy_pair_kernel(uint4* __restrict__ d0, const uint4* __restrict__ s0, long n0,
@@ -1193,23 +1283,6 @@ __global__ void __launch_bounds__(256) copy_pair_kernel(uint4* __restrict__ d0, 
 
 // master fp32 [Cout][taps][Cin] -> Wf bf16 [Cout][kpad] (zero padded past taps*Cin)
 //                               -> Wd bf16 [Cin][taps*Cout] with taps flipped (dgrad operand), optional
-template <class T>
-B200DP_DEVINL T operand_cast(float v) {
-  if constexpr (sizeof(T) == 4) return v;
-  else return __float2bfloat16(v);
-}
-template <class T>
-B200DP_DEVINL void operand_store4(T* dst, float a, float b, float c, float d) {
-  if constexpr (sizeof(T) == 4) {
-    *reinterpret_cast<float4*>(dst) = make_float4(a, b, c, d);
-  } else {
-    uint2 o;
-    o.x = pack_bf16x2(a, b);
-    o.y = pack_bf16x2(c, d);
-    *reinterpret_cast<uint2*>(dst) = o;
-  }
-}
-
 // T = __nv_bfloat16: operand copies of the bf16 path.  T = float: the tf32 path, whose forward operand is the master
 // tensor itself wherever no padding is needed (wf == nullptr), so usually only Wd is produced.
 template <class T>
@@ -1308,15 +1381,38 @@ static inline int grid_for(long work_items, int threads, int max_blocks = 148 * 
 
 using namespace b200dp;
 
-extern "C" int b200dp_im2col3x3_c3(const float* x_nchw, void* a0, int B, int H, int W, b200dp_stream_t s) {
+/* dtype 0: bf16 patch rows of 64 columns; dtype 1: fp32 patch rows of 32 columns (27 real columns either way). */
+extern "C" int b200dp_im2col3x3_c3_ex(const float* x_nchw, void* a0, int B, int H, int W, int dtype,
+                                      b200dp_stream_t s) {
   const size_t smem = (kIm2colRows + 2) * 3 * (W + 2) * sizeof(float);
   const int groups = (H + kIm2colRows - 1) / kIm2colRows;
-  B200DP_CUDA_TRY(launch_pdl(im2col_c3_v2_kernel, dim3(B * groups), dim3(256), smem,
-                             static_cast<cudaStream_t>(s), x_nchw, static_cast<__nv_bfloat16*>(a0), B, H, W));
+  if (dtype == 1)
+    B200DP_CUDA_TRY(launch_pdl(im2col_c3_v2_kernel<float, 32>, dim3(B * groups), dim3(256), smem,
+                               static_cast<cudaStream_t>(s), x_nchw, static_cast<float*>(a0), B, H, W));
+  else
+    B200DP_CUDA_TRY(launch_pdl(im2col_c3_v2_kernel<__nv_bfloat16, 64>, dim3(B * groups), dim3(256), smem,
+                               static_cast<cudaStream_t>(s), x_nchw, static_cast<__nv_bfloat16*>(a0), B, H, W));
   return 0;
 }
+extern "C" int b200dp_im2col3x3_c3(const float* x_nchw, void* a0, int B, int H, int W, b200dp_stream_t s) {
+  return b200dp_im2col3x3_c3_ex(x_nchw, a0, B, H, W, 0, s);
+}
 
-extern "C" int b200dp_bn_stats(const void* y, float* stats, long long P, int C, b200dp_stream_t s) {
+// Forward declarations of the bulk-copy pipeline entry points (csrc/bn_stream.cu); dtype 0 = bf16, 1 = fp32.
+extern "C" int b200dp_bn_relu_pool_fwd_tma_ex(const void* y, const float* stats, const float* gamma, const float* beta,
+                                              float* running_mean, float* running_var, long long* num_batches_tracked,
+                                              float* save_mean, float* save_invstd, void* out, int B, int H, int W,
+                                              int C, int pool, int training, float momentum, float eps, int dtype,
+                                              b200dp_stream_t s);
+extern "C" int b200dp_bn_bwd_apply_nopool_tma_ex(const void* y, const void* dout, const float* mean,
+                                                 const float* invstd, const float* gamma, const float* beta,
+                                                 const float* sums, void* dy, float* dgamma, float* dbeta, int B,
+                                                 int H, int W, int C, int dtype, b200dp_stream_t s);
+extern "C" int b200dp_bn_bwd_reduce_from_out_tma_ex(const void* out, const void* dout, const float* gamma,
+                                                    const float* beta, float* sums, long long Q, int C, int dtype,
+                                                    b200dp_stream_t s);
+
+extern "C" int b200dp_bn_stats_ex(const void* y, float* stats, long long P, int C, int dtype, b200dp_stream_t s) {
   if (C % 8 != 0 || C > 2048) {
     set_error("bn_stats: C=%d unsupported", C);
     return B200DP_EINVAL;
@@ -1329,25 +1425,33 @@ extern "C" int b200dp_bn_stats(const void* y, float* stats, long long P, int C, 
   }
   const size_t smem = 2 * rows_per_block * C * sizeof(float);
   int blocks = grid_for(P, rows_per_block * 8, 148 * 4);
-  bn_stats_kernel<<<blocks, threads, smem, static_cast<cudaStream_t>(s)>>>(static_cast<const __nv_bfloat16*>(y),
-                                                                          stats, P, C);
+  if (dtype == 1)
+    bn_stats_kernel<float><<<blocks, threads, smem, static_cast<cudaStream_t>(s)>>>(static_cast<const float*>(y), stats,
+                                                                                   P, C);
+  else
+    bn_stats_kernel<__nv_bfloat16><<<blocks, threads, smem, static_cast<cudaStream_t>(s)>>>(
+        static_cast<const __nv_bfloat16*>(y), stats, P, C);
   B200DP_CUDA_TRY(cudaGetLastError());
   return 0;
 }
+extern "C" int b200dp_bn_stats(const void* y, float* stats, long long P, int C, b200dp_stream_t s) {
+  return b200dp_bn_stats_ex(y, stats, P, C, 0, s);
+}
 
-extern "C" int b200dp_bn_relu_pool_fwd(const void* y, const float* stats, const float* gamma, const float* beta,
-                                       float* running_mean, float* running_var, long long* num_batches_tracked,
-                                       float* save_mean, float* save_invstd, void* out, int B, int H, int W, int C,
-                                       int pool, int training, float momentum, float eps, b200dp_stream_t s) {
+extern "C" int b200dp_bn_relu_pool_fwd_ex(const void* y, const float* stats, const float* gamma, const float* beta,
+                                          float* running_mean, float* running_var, long long* num_batches_tracked,
+                                          float* save_mean, float* save_invstd, void* out, int B, int H, int W, int C,
+                                          int pool, int training, float momentum, float eps, int dtype,
+                                          b200dp_stream_t s) {
   if (C % 8 != 0 || (pool && ((H | W) & 1))) {
     set_error("bn_relu_pool_fwd: unsupported shape H=%d W=%d C=%d pool=%d", H, W, C, pool);
     return B200DP_EINVAL;
   }
   if (bn_tma_shape_ok(H, W, C, pool))
-    return b200dp_bn_relu_pool_fwd_tma(y, stats, gamma, beta, running_mean, running_var, num_batches_tracked,
-                                       save_mean, save_invstd, out, B, H, W, C, pool, training, momentum, eps, s);
-  BnFwdParams p{static_cast<const __nv_bfloat16*>(y), stats, gamma, beta, running_mean, running_var,
-                num_batches_tracked, save_mean, save_invstd, static_cast<__nv_bfloat16*>(out),
+    return b200dp_bn_relu_pool_fwd_tma_ex(y, stats, gamma, beta, running_mean, running_var, num_batches_tracked,
+                                          save_mean, save_invstd, out, B, H, W, C, pool, training, momentum, eps, dtype,
+                                          s);
+  BnFwdParams p{y, stats, gamma, beta, running_mean, running_var, num_batches_tracked, save_mean, save_invstd, out,
                 B, H, W, C, pool, training, momentum, eps};
   if (C > 2048) {
     set_error("bn_relu_pool_fwd: C=%d too wide for a 256-thread block", C);
@@ -1356,117 +1460,154 @@ extern "C" int b200dp_bn_relu_pool_fwd(const void* y, const float* stats, const 
   const long Q = static_cast<long>(B) * (pool ? H / 2 : H) * (pool ? W / 2 : W);
   const int rows_per_block = 256 / (C / 8);
   // two output pixels per thread per iteration; at most one resident wave (3 blocks / SM)
-  B200DP_CUDA_TRY(launch_pdl(bn_relu_pool_fwd_kernel, dim3(grid_for(Q, rows_per_block * 2, 148 * 3)), dim3(256), 0,
-                             static_cast<cudaStream_t>(s), p));
+  const dim3 grid(grid_for(Q, rows_per_block * 2, 148 * 3));
+  if (dtype == 1)
+    B200DP_CUDA_TRY(launch_pdl(bn_relu_pool_fwd_kernel<float>, grid, dim3(256), 0, static_cast<cudaStream_t>(s), p));
+  else
+    B200DP_CUDA_TRY(launch_pdl(bn_relu_pool_fwd_kernel<__nv_bfloat16>, grid, dim3(256), 0,
+                               static_cast<cudaStream_t>(s), p));
   return 0;
 }
-
-static bool bn_tma_supported(const BnBwdParams& p) {
-  if (!p.pool || p.C % 8 != 0 || ((p.H | p.W) & 1)) return false;
-  const int items_per_tile = (p.W / 2) * (p.C / 8);
-  return items_per_tile >= 1 && items_per_tile <= kBnTmaItems && kBnTmaItems % items_per_tile == 0;
+extern "C" int b200dp_bn_relu_pool_fwd(const void* y, const float* stats, const float* gamma, const float* beta,
+                                       float* running_mean, float* running_var, long long* num_batches_tracked,
+                                       float* save_mean, float* save_invstd, void* out, int B, int H, int W, int C,
+                                       int pool, int training, float momentum, float eps, b200dp_stream_t s) {
+  return b200dp_bn_relu_pool_fwd_ex(y, stats, gamma, beta, running_mean, running_var, num_batches_tracked, save_mean,
+                                    save_invstd, out, B, H, W, C, pool, training, momentum, eps, 0, s);
 }
 
+template <class T>
+static bool bn_tma_supported(const BnBwdParams& p) {
+  constexpr int kItems = bn_tma_items<T>();
+  if (!p.pool || p.C % 8 != 0 || ((p.H | p.W) & 1)) return false;
+  const int items_per_tile = (p.W / 2) * (p.C / 8);
+  return items_per_tile >= 1 && items_per_tile <= kItems && kItems % items_per_tile == 0;
+}
+
+template <class T>
 static int launch_bn_apply_pool_tma(const BnBwdParams& p, cudaStream_t s) {
+  constexpr int kItems = bn_tma_items<T>();
   static bool configured = false;
   if (!configured) {
-    B200DP_CUDA_TRY(cudaFuncSetAttribute(bn_bwd_apply_pool_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    B200DP_CUDA_TRY(cudaFuncSetAttribute(bn_bwd_apply_pool_tma_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          kBnTmaSmem));
     configured = true;
   }
-  const int G = kBnTmaItems / ((p.W / 2) * (p.C / 8));
-  const long T = static_cast<long>(p.B) * (p.H / 2);
-  const long num_chunks = (T + G - 1) / G;
+  const int G = kItems / ((p.W / 2) * (p.C / 8));
+  const long tiles = static_cast<long>(p.B) * (p.H / 2);
+  const long num_chunks = (tiles + G - 1) / G;
   const int grid = static_cast<int>(num_chunks < 148 * 2 ? num_chunks : 148 * 2);
-  B200DP_CUDA_TRY(launch_pdl(bn_bwd_apply_pool_tma_kernel, dim3(grid), dim3(kBnTmaItems), kBnTmaSmem, s, p));
+  B200DP_CUDA_TRY(launch_pdl(bn_bwd_apply_pool_tma_kernel<T>, dim3(grid), dim3(kItems), kBnTmaSmem, s, p));
   return 0;
 }
 
+template <class T>
 static int launch_bn_bwd(bool apply, const BnBwdParams& p, cudaStream_t s) {
   if (p.C % 8 != 0 || p.C > 2048 || (p.pool && ((p.H | p.W) & 1))) {
     set_error("bn_relu_pool_bwd: unsupported shape H=%d W=%d C=%d pool=%d", p.H, p.W, p.C, p.pool);
     return B200DP_EINVAL;
   }
+  constexpr int kDtype = sizeof(T) == 4 ? 1 : 0;
   const int threads = 256;
   const int rows_per_block = threads / (p.C / 8);
   const size_t smem = apply ? 0 : 2 * rows_per_block * p.C * sizeof(float);
   const long Q = static_cast<long>(p.B) * (p.pool ? p.H / 2 : p.H) * (p.pool ? p.W / 2 : p.W);
-  // reduce pass: at most one resident wave (3 blocks / SM), a grid-stride loop balances better than a
-  // ragged tail; apply pass (4 loads + 4 stores per item): measured faster with two items per thread
-  // and many short blocks.
-  const int blocks = apply ? grid_for(Q, rows_per_block * 2, 148 * 8) : grid_for(Q, rows_per_block, 148 * 3);
-  if (apply && p.pool && bn_tma_supported(p)) return launch_bn_apply_pool_tma(p, s);
+  // reduce pass: at most one resident wave (3 blocks / SM), a grid-stride loop balances better than a ragged tail
+  const int blocks = grid_for(Q, rows_per_block, 148 * 3);
+  if (apply && p.pool && bn_tma_supported<T>(p)) return launch_bn_apply_pool_tma<T>(p, s);
   if (apply && !p.pool && bn_tma_shape_ok(p.H, p.W, p.C, 0))
-    return b200dp_bn_bwd_apply_nopool_tma(p.y, p.dout, p.mean, p.invstd, p.gamma, p.beta, p.sums, p.dy, p.dgamma,
-                                          p.dbeta, p.B, p.H, p.W, p.C, s);
+    return b200dp_bn_bwd_apply_nopool_tma_ex(p.y, p.dout, p.mean, p.invstd, p.gamma, p.beta, p.sums, p.dy, p.dgamma,
+                                             p.dbeta, p.B, p.H, p.W, p.C, kDtype, s);
   if (apply && !p.pool)
-    B200DP_CUDA_TRY(launch_pdl(bn_bwd_apply_nopool_kernel, dim3(grid_for(Q, rows_per_block * 4, 148 * 3)),
+    B200DP_CUDA_TRY(launch_pdl(bn_bwd_apply_nopool_kernel<T>, dim3(grid_for(Q, rows_per_block * 4, 148 * 3)),
                                dim3(threads), 0, s, p));
   else if (apply && p.pool)
-    B200DP_CUDA_TRY(launch_pdl(bn_bwd_apply_pool_kernel, dim3(grid_for(Q, rows_per_block * 2, 148 * 4)),
+    B200DP_CUDA_TRY(launch_pdl(bn_bwd_apply_pool_kernel<T>, dim3(grid_for(Q, rows_per_block * 2, 148 * 4)),
                                dim3(threads), 0, s, p));
   else
-    B200DP_CUDA_TRY(launch_pdl(bn_relu_pool_bwd_kernel<false>, dim3(blocks), dim3(threads), smem, s, p));
+    B200DP_CUDA_TRY(launch_pdl(bn_relu_pool_bwd_kernel<T, false>, dim3(blocks), dim3(threads), smem, s, p));
   return 0;
 }
+static int launch_bn_bwd_dt(int dtype, bool apply, const BnBwdParams& p, cudaStream_t s) {
+  return dtype == 1 ? launch_bn_bwd<float>(apply, p, s) : launch_bn_bwd<__nv_bfloat16>(apply, p, s);
+}
 
+extern "C" int b200dp_bn_relu_pool_bwd_reduce_ex(const void* y, const void* dout, const float* mean,
+                                                 const float* invstd, const float* gamma, const float* beta,
+                                                 float* sums, int B, int H, int W, int C, int pool, int dtype,
+                                                 b200dp_stream_t s) {
+  BnBwdParams p{y, dout, mean, invstd, gamma, beta, sums, nullptr, nullptr, nullptr, B, H, W, C, pool};
+  return launch_bn_bwd_dt(dtype, false, p, static_cast<cudaStream_t>(s));
+}
 extern "C" int b200dp_bn_relu_pool_bwd_reduce(const void* y, const void* dout, const float* mean,
                                               const float* invstd, const float* gamma, const float* beta,
                                               float* sums, int B, int H, int W, int C, int pool,
                                               b200dp_stream_t s) {
-  BnBwdParams p{static_cast<const __nv_bfloat16*>(y), static_cast<const __nv_bfloat16*>(dout), mean, invstd, gamma,
-                beta, sums, nullptr, nullptr, nullptr, B, H, W, C, pool};
-  return launch_bn_bwd(false, p, static_cast<cudaStream_t>(s));
+  return b200dp_bn_relu_pool_bwd_reduce_ex(y, dout, mean, invstd, gamma, beta, sums, B, H, W, C, pool, 0, s);
 }
 
 /* Pass 1 computed from the block's stored OUTPUT (`out`, the same shape as `dout`) instead of the conv
  * output: fewer bytes for pooled layers, no arg-max search.  Same `sums` contract as _reduce. */
-extern "C" int b200dp_bn_relu_pool_bwd_reduce_from_out(const void* out, const void* dout, const float* gamma,
-                                                       const float* beta, float* sums, long long Q, int C,
-                                                       b200dp_stream_t s) {
+extern "C" int b200dp_bn_relu_pool_bwd_reduce_from_out_ex(const void* out, const void* dout, const float* gamma,
+                                                          const float* beta, float* sums, long long Q, int C,
+                                                          int dtype, b200dp_stream_t s) {
   if (C % 8 != 0 || C > 2048 || Q <= 0) {
     set_error("bn_relu_pool_bwd_reduce_from_out: unsupported shape Q=%lld C=%d", Q, C);
     return B200DP_EINVAL;
   }
   if (bn_tma_shape_ok(2, 2, C, 0))
-    return b200dp_bn_bwd_reduce_from_out_tma(out, dout, gamma, beta, sums, Q, C, s);
+    return b200dp_bn_bwd_reduce_from_out_tma_ex(out, dout, gamma, beta, sums, Q, C, dtype, s);
   const int threads = 256;
   const int rows_per_block = threads / (C / 8);
   const size_t smem = 2 * rows_per_block * C * sizeof(float);
   const int blocks = grid_for(Q, rows_per_block * 2, 148 * 4);
-  B200DP_CUDA_TRY(launch_pdl(bn_bwd_reduce_from_out_kernel, dim3(blocks), dim3(threads), smem,
-                             static_cast<cudaStream_t>(s), static_cast<const __nv_bfloat16*>(out),
-                             static_cast<const __nv_bfloat16*>(dout), gamma, beta, sums, static_cast<long>(Q), C));
+  if (dtype == 1)
+    B200DP_CUDA_TRY(launch_pdl(bn_bwd_reduce_from_out_kernel<float>, dim3(blocks), dim3(threads), smem,
+                               static_cast<cudaStream_t>(s), static_cast<const float*>(out),
+                               static_cast<const float*>(dout), gamma, beta, sums, static_cast<long>(Q), C));
+  else
+    B200DP_CUDA_TRY(launch_pdl(bn_bwd_reduce_from_out_kernel<__nv_bfloat16>, dim3(blocks), dim3(threads), smem,
+                               static_cast<cudaStream_t>(s), static_cast<const __nv_bfloat16*>(out),
+                               static_cast<const __nv_bfloat16*>(dout), gamma, beta, sums, static_cast<long>(Q), C));
   return 0;
 }
+extern "C" int b200dp_bn_relu_pool_bwd_reduce_from_out(const void* out, const void* dout, const float* gamma,
+                                                       const float* beta, float* sums, long long Q, int C,
+                                                       b200dp_stream_t s) {
+  return b200dp_bn_relu_pool_bwd_reduce_from_out_ex(out, dout, gamma, beta, sums, Q, C, 0, s);
+}
 
+extern "C" int b200dp_bn_relu_pool_bwd_apply_ex(const void* y, const void* dout, const float* mean,
+                                                const float* invstd, const float* gamma, const float* beta,
+                                                const float* sums, void* dy, float* dgamma, float* dbeta, int B,
+                                                int H, int W, int C, int pool, int dtype, b200dp_stream_t s) {
+  BnBwdParams p{y, dout, mean, invstd, gamma, beta, const_cast<float*>(sums), dy, dgamma, dbeta, B, H, W, C, pool};
+  return launch_bn_bwd_dt(dtype, true, p, static_cast<cudaStream_t>(s));
+}
 extern "C" int b200dp_bn_relu_pool_bwd_apply(const void* y, const void* dout, const float* mean,
                                              const float* invstd, const float* gamma, const float* beta,
                                              const float* sums, void* dy, float* dgamma, float* dbeta, int B, int H,
                                              int W, int C, int pool, b200dp_stream_t s) {
-  BnBwdParams p{static_cast<const __nv_bfloat16*>(y), static_cast<const __nv_bfloat16*>(dout), mean, invstd, gamma,
-                beta, const_cast<float*>(sums), static_cast<__nv_bfloat16*>(dy), dgamma, dbeta, B, H, W, C, pool};
-  return launch_bn_bwd(true, p, static_cast<cudaStream_t>(s));
+  return b200dp_bn_relu_pool_bwd_apply_ex(y, dout, mean, invstd, gamma, beta, sums, dy, dgamma, dbeta, B, H, W, C, pool,
+                                          0, s);
 }
 
-/* The pooled apply pass as a bulk-copy (TMA engine) pipeline: same contract and bit-identical results as
- * b200dp_bn_relu_pool_bwd_apply with pool = 1.  Needs (W/2) * (C/8) to divide 256.  Experimental: the
- * executor takes it with B200DP_BN_TMA=1. */
+/* The pooled apply pass as a bulk-copy (TMA engine) pipeline: same contract as b200dp_bn_relu_pool_bwd_apply
+ * with pool = 1 (which routes here whenever the shape fits).  Needs (W/2) * (C/8) to divide 256 (bf16). */
 extern "C" int b200dp_bn_bwd_apply_pool_tma(const void* y, const void* dout, const float* mean, const float* invstd,
                                             const float* gamma, const float* beta, const float* sums, void* dy,
                                             float* dgamma, float* dbeta, int B, int H, int W, int C,
                                             b200dp_stream_t s) {
-  BnBwdParams p{static_cast<const __nv_bfloat16*>(y), static_cast<const __nv_bfloat16*>(dout), mean, invstd, gamma,
-                beta, const_cast<float*>(sums), static_cast<__nv_bfloat16*>(dy), dgamma, dbeta, B, H, W, C, 1};
-  if (B <= 0 || !bn_tma_supported(p)) {
+  BnBwdParams p{y, dout, mean, invstd, gamma, beta, const_cast<float*>(sums), dy, dgamma, dbeta, B, H, W, C, 1};
+  if (B <= 0 || !bn_tma_supported<__nv_bfloat16>(p)) {
     set_error("bn_bwd_apply_pool_tma: unsupported shape B=%d H=%d W=%d C=%d ((W/2)*(C/8) must divide 256)", B, H, W, C);
     return B200DP_EINVAL;
   }
-  return launch_bn_apply_pool_tma(p, static_cast<cudaStream_t>(s));
+  return launch_bn_apply_pool_tma<__nv_bfloat16>(p, static_cast<cudaStream_t>(s));
 }
 
-extern "C" int b200dp_linear_fwd(const void* x, const float* w, const float* b, float* logits, int B, int F, int O,
-                                 b200dp_stream_t s) {
+extern "C" int b200dp_linear_fwd_ex(const void* x, const float* w, const float* b, float* logits, int B, int F, int O,
+                                    int dtype, b200dp_stream_t s) {
   if (F % 8 != 0) {
     set_error("linear_fwd: F=%d must be a multiple of 8", F);
     return B200DP_EINVAL;
@@ -1477,9 +1618,18 @@ extern "C" int b200dp_linear_fwd(const void* x, const float* w, const float* b, 
   }
   const int threads = 128;
   const int blocks = (B * 32 + threads - 1) / threads;
-  B200DP_CUDA_TRY(launch_pdl(linear_fwd_kernel, dim3(blocks), dim3(threads), 0, static_cast<cudaStream_t>(s),
-                             static_cast<const __nv_bfloat16*>(x), w, b, logits, B, F, O));
+  if (dtype == 1)
+    B200DP_CUDA_TRY(launch_pdl(linear_fwd_kernel<float>, dim3(blocks), dim3(threads), 0, static_cast<cudaStream_t>(s),
+                               static_cast<const float*>(x), w, b, logits, B, F, O));
+  else
+    B200DP_CUDA_TRY(launch_pdl(linear_fwd_kernel<__nv_bfloat16>, dim3(blocks), dim3(threads), 0,
+                               static_cast<cudaStream_t>(s), static_cast<const __nv_bfloat16*>(x), w, b, logits, B, F,
+                               O));
   return 0;
+}
+extern "C" int b200dp_linear_fwd(const void* x, const float* w, const float* b, float* logits, int B, int F, int O,
+                                 b200dp_stream_t s) {
+  return b200dp_linear_fwd_ex(x, w, b, logits, B, F, O, 0, s);
 }
 
 extern "C" int b200dp_cross_entropy(const float* logits, const long long* target, float* loss, float* dlogits,
@@ -1489,8 +1639,8 @@ extern "C" int b200dp_cross_entropy(const float* logits, const long long* target
   return 0;
 }
 
-extern "C" int b200dp_linear_bwd(const void* x, const float* w, const float* dlogits, float* dw, float* db, void* dx,
-                                 int B, int F, int O, b200dp_stream_t s) {
+extern "C" int b200dp_linear_bwd_ex(const void* x, const float* w, const float* dlogits, float* dw, float* db,
+                                    void* dx, int B, int F, int O, int dtype, b200dp_stream_t s) {
   if (O > kLinMaxO) {
     set_error("linear_bwd: O=%d exceeds the supported %d outputs", O, kLinMaxO);
     return B200DP_EINVAL;
@@ -1503,38 +1653,66 @@ extern "C" int b200dp_linear_bwd(const void* x, const float* w, const float* dlo
   }
   const int nW = ((F + 63) / 64) * nslices;
   const int nX = static_cast<int>((static_cast<long>(B) * F + threads - 1) / threads);
-  B200DP_CUDA_TRY(cudaMemsetAsync(dw, 0, sizeof(float) * O * F, static_cast<cudaStream_t>(s)));
-  B200DP_CUDA_TRY(cudaMemsetAsync(db, 0, sizeof(float) * O, static_cast<cudaStream_t>(s)));
-  B200DP_CUDA_TRY(launch_pdl(linear_bwd_kernel, dim3(nW + nX), dim3(threads), 0, static_cast<cudaStream_t>(s),
-                             static_cast<const __nv_bfloat16*>(x), w, dlogits, dw, db, static_cast<__nv_bfloat16*>(dx),
-                             B, F, O, nW));
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  // dw / db are accumulated with atomics: cleared by a kernel of this library (no memset nodes in a captured step)
+  B200DP_CUDA_TRY(launch_pdl(fill_zero_f32_pair_kernel, dim3(grid_for(static_cast<long>(O) * F, 256, 64)), dim3(256), 0,
+                             st, dw, static_cast<long>(O) * F, db, static_cast<long>(O)));
+  if (dtype == 1)
+    B200DP_CUDA_TRY(launch_pdl(linear_bwd_kernel<float>, dim3(nW + nX), dim3(threads), 0, st,
+                               static_cast<const float*>(x), w, dlogits, dw, db, static_cast<float*>(dx), B, F, O, nW));
+  else
+    B200DP_CUDA_TRY(launch_pdl(linear_bwd_kernel<__nv_bfloat16>, dim3(nW + nX), dim3(threads), 0, st,
+                               static_cast<const __nv_bfloat16*>(x), w, dlogits, dw, db,
+                               static_cast<__nv_bfloat16*>(dx), B, F, O, nW));
   return 0;
 }
+extern "C" int b200dp_linear_bwd(const void* x, const float* w, const float* dlogits, float* dw, float* db, void* dx,
+                                 int B, int F, int O, b200dp_stream_t s) {
+  return b200dp_linear_bwd_ex(x, w, dlogits, dw, db, dx, B, F, O, 0, s);
+}
 
-/* Training-step classifier head in one launch (experimental): logits = x W^T + b, mean softmax
- * cross-entropy into *loss, top-1 count into *correct, dlogits (may be NULL), dx = dlogits W (bf16), and
- * dw += dlogits^T x, db += sum dlogits (dw / db must be zero or hold the value to accumulate onto --
- * unlike b200dp_linear_bwd this entry point does not clear them).  F % 8 == 0, F <= 2048, O <= 16,
- * B <= 4096.  Launches on one stream only (it keeps its block counter in a device global). */
-extern "C" int b200dp_head_fwd_bwd(const void* x, const float* w, const float* bias, const long long* target,
-                                   float* logits, float* loss, int* correct, float* dlogits, void* dx, float* dw,
-                                   float* db, int B, int F, int O, float grad_scale, b200dp_stream_t s) {
-  if (F % 8 != 0 || F > 2048 || O > kLinMaxO || O < 1 || B < 1 || B > kHeadWarps * kHeadMaxBlocks) {
-    set_error("head_fwd_bwd: unsupported shape B=%d F=%d O=%d", B, F, O);
-    return B200DP_EINVAL;
-  }
+template <class T>
+static int head_fwd_bwd_impl(const void* x, const float* w, const float* bias, const long long* target, float* logits,
+                             float* loss, int* correct, float* dlogits, void* dx, float* dw, float* db, int B, int F,
+                             int O, float grad_scale, cudaStream_t s) {
   const int blocks = (B + kHeadWarps - 1) / kHeadWarps;
   const size_t smem = (static_cast<size_t>(kHeadWarps) * F + kHeadWarps * kLinMaxO) * sizeof(float);
   static bool configured = false;
   if (!configured) {
-    B200DP_CUDA_TRY(cudaFuncSetAttribute(head_fwd_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    B200DP_CUDA_TRY(cudaFuncSetAttribute(head_fwd_bwd_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          static_cast<int>((kHeadWarps * 2048 + kHeadWarps * kLinMaxO) * sizeof(float))));
     configured = true;
   }
-  B200DP_CUDA_TRY(launch_pdl(head_fwd_bwd_kernel, dim3(blocks), dim3(kHeadWarps * 32), smem, static_cast<cudaStream_t>(s),
-                             static_cast<const __nv_bfloat16*>(x), w, bias, target, logits, loss, correct, dlogits,
-                             static_cast<__nv_bfloat16*>(dx), dw, db, B, F, O, grad_scale));
+  B200DP_CUDA_TRY(launch_pdl(head_fwd_bwd_kernel<T>, dim3(blocks), dim3(kHeadWarps * 32), smem, s,
+                             static_cast<const T*>(x), w, bias, target, logits, loss, correct, dlogits,
+                             static_cast<T*>(dx), dw, db, B, F, O, grad_scale));
   return 0;
+}
+
+/* Training-step classifier head in one launch: logits = x W^T + b, mean softmax cross-entropy into *loss,
+ * top-1 count into *correct, dlogits (may be NULL), dx = dlogits W (activation type), and
+ * dw += dlogits^T x, db += sum dlogits (dw / db must be zero or hold the value to accumulate onto --
+ * unlike b200dp_linear_bwd this entry point does not clear them).  F % 8 == 0, F <= 2048, O <= 16,
+ * B <= 4096.  Launches on one stream only (it keeps its block counter in a device global). */
+extern "C" int b200dp_head_fwd_bwd_ex(const void* x, const float* w, const float* bias, const long long* target,
+                                      float* logits, float* loss, int* correct, float* dlogits, void* dx, float* dw,
+                                      float* db, int B, int F, int O, float grad_scale, int dtype, b200dp_stream_t s) {
+  if (F % 8 != 0 || F > 2048 || O > kLinMaxO || O < 1 || B < 1 || B > kHeadWarps * kHeadMaxBlocks) {
+    set_error("head_fwd_bwd: unsupported shape B=%d F=%d O=%d", B, F, O);
+    return B200DP_EINVAL;
+  }
+  cudaStream_t st = static_cast<cudaStream_t>(s);
+  if (dtype == 1)
+    return head_fwd_bwd_impl<float>(x, w, bias, target, logits, loss, correct, dlogits, dx, dw, db, B, F, O, grad_scale,
+                                    st);
+  return head_fwd_bwd_impl<__nv_bfloat16>(x, w, bias, target, logits, loss, correct, dlogits, dx, dw, db, B, F, O,
+                                          grad_scale, st);
+}
+extern "C" int b200dp_head_fwd_bwd(const void* x, const float* w, const float* bias, const long long* target,
+                                   float* logits, float* loss, int* correct, float* dlogits, void* dx, float* dw,
+                                   float* db, int B, int F, int O, float grad_scale, b200dp_stream_t s) {
+  return b200dp_head_fwd_bwd_ex(x, w, bias, target, logits, loss, correct, dlogits, dx, dw, db, B, F, O, grad_scale, 0,
+                                s);
 }
 
 extern "C" int b200dp_sgd_momentum(float* p, const float* g, float* buf, long long n, float lr, float momentum,
@@ -1662,11 +1840,10 @@ extern "C" int b200dp_bn_relu_pool_bwd_noalloc(const void* y, const void* dout, 
   cudaStream_t stream = static_cast<cudaStream_t>(s);
   // The array still holds the sums of whoever called last; the reduction adds onto it.
   B200DP_CUDA_TRY(cudaMemsetAsync(scratch, 0, 2 * static_cast<size_t>(C) * sizeof(float), stream));
-  BnBwdParams p{static_cast<const __nv_bfloat16*>(y), static_cast<const __nv_bfloat16*>(dout), mean, invstd, gamma,
-                beta, scratch, static_cast<__nv_bfloat16*>(dy), dgamma, dbeta, B, H, W, C, pool};
-  rc = launch_bn_bwd(false, p, stream);
+  BnBwdParams p{y, dout, mean, invstd, gamma, beta, scratch, dy, dgamma, dbeta, B, H, W, C, pool};
+  rc = launch_bn_bwd<__nv_bfloat16>(false, p, stream);
   if (rc) return rc;
-  return launch_bn_bwd(true, p, stream);
+  return launch_bn_bwd<__nv_bfloat16>(true, p, stream);
 }
 
 /* Batched form of b200dp_prep_conv_weights_ex: all layers in one launch.  Arrays have n entries;

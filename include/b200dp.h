@@ -138,6 +138,45 @@ int b200dp_conv_wgrad_ex(const void* dy, const void* x, float* dw, int B, int H,
  * K=64 GEMM for b200dp_conv_igemm(taps=1).  (ref: master/part1/model.py:13,18) */
 int b200dp_im2col3x3_c3(const float* x_nchw, void* a0, int B, int H, int W, b200dp_stream_t stream);
 
+/* Precision-generic forms of the bandwidth-bound layer kernels below: the same contracts with a trailing
+ * `dtype` before the stream -- 0 = bf16 activations (identical to the entry point without _ex), 1 = fp32
+ * activations (the tf32 arm; im2col then writes 32-column patch rows).  Parameters, statistics and gradients of
+ * parameters are fp32 either way.  (ref: the fp32 model of master/part1/model.py:16-25,40-46) */
+int b200dp_im2col3x3_c3_ex(const float* x_nchw, void* a0, int B, int H, int W, int dtype, b200dp_stream_t stream);
+int b200dp_bn_stats_ex(const void* y, float* stats, long long P, int C, int dtype, b200dp_stream_t stream);
+int b200dp_bn_relu_pool_fwd_ex(const void* y, const float* stats, const float* gamma, const float* beta,
+                               float* running_mean, float* running_var, long long* num_batches_tracked,
+                               float* save_mean, float* save_invstd, void* out, int B, int H, int W, int C, int pool,
+                               int training, float momentum, float eps, int dtype, b200dp_stream_t stream);
+int b200dp_bn_relu_pool_bwd_reduce_ex(const void* y, const void* dout, const float* mean, const float* invstd,
+                                      const float* gamma, const float* beta, float* sums, int B, int H, int W, int C,
+                                      int pool, int dtype, b200dp_stream_t stream);
+int b200dp_bn_relu_pool_bwd_reduce_from_out_ex(const void* out, const void* dout, const float* gamma,
+                                               const float* beta, float* sums, long long Q, int C, int dtype,
+                                               b200dp_stream_t stream);
+int b200dp_bn_relu_pool_bwd_apply_ex(const void* y, const void* dout, const float* mean, const float* invstd,
+                                     const float* gamma, const float* beta, const float* sums, void* dy,
+                                     float* dgamma, float* dbeta, int B, int H, int W, int C, int pool, int dtype,
+                                     b200dp_stream_t stream);
+int b200dp_bn_relu_pool_fwd_tma_ex(const void* y, const float* stats, const float* gamma, const float* beta,
+                                   float* running_mean, float* running_var, long long* num_batches_tracked,
+                                   float* save_mean, float* save_invstd, void* out, int B, int H, int W, int C,
+                                   int pool, int training, float momentum, float eps, int dtype,
+                                   b200dp_stream_t stream);
+int b200dp_bn_bwd_apply_nopool_tma_ex(const void* y, const void* dout, const float* mean, const float* invstd,
+                                      const float* gamma, const float* beta, const float* sums, void* dy,
+                                      float* dgamma, float* dbeta, int B, int H, int W, int C, int dtype,
+                                      b200dp_stream_t stream);
+int b200dp_bn_bwd_reduce_from_out_tma_ex(const void* out, const void* dout, const float* gamma, const float* beta,
+                                         float* sums, long long Q, int C, int dtype, b200dp_stream_t stream);
+int b200dp_linear_fwd_ex(const void* x, const float* w, const float* b, float* logits, int B, int F, int O, int dtype,
+                         b200dp_stream_t stream);
+int b200dp_linear_bwd_ex(const void* x, const float* w, const float* dlogits, float* dw, float* db, void* dx, int B,
+                         int F, int O, int dtype, b200dp_stream_t stream);
+int b200dp_head_fwd_bwd_ex(const void* x, const float* w, const float* bias, const long long* target, float* logits,
+                           float* loss, int* correct, float* dlogits, void* dx, float* dw, float* db, int B, int F,
+                           int O, float grad_scale, int dtype, b200dp_stream_t stream);
+
 /* stats[0..C) += sum_p y[p][c], stats[C..2C) += sum_p y[p][c]^2 (stats zero on entry). */
 int b200dp_bn_stats(const void* y, float* stats, long long P, int C, b200dp_stream_t stream);
 

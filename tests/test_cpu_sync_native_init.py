@@ -63,7 +63,8 @@ def fake_native():
     nv.blocks = []
     for i, s in enumerate(model.block_specs()):
         nv.blocks.append(types.SimpleNamespace(spec=s, first=(i == 0), w_master=None, wf=None, wd=None,
-                                               taps=1 if i == 0 else 9, kin=64 if i == 0 else s.cin))
+                                               taps=1 if i == 0 else 9, kin=64 if i == 0 else s.cin,
+                                               prep=(None, None, None, s.cout, s.cin, 9, 64 if i == 0 else 9 * s.cin)))
     nv.flat_grads = nv.flat_params = nv.flat_momentum = torch.zeros(4)
 
     def set_bucket_plan(buckets):

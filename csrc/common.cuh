@@ -252,13 +252,16 @@ B200DP_DEVINL void umma_commit_2cta(uint64_t* bar, uint16_t mask) {
 
 // Shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout):
 //   [0,14) start>>4 | [16,30) LBO>>4 | [32,46) SBO>>4 | [46,48) version=1 | [61,64) swizzle (2 = 128B)
-B200DP_DEVINL uint64_t umma_smem_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+// layout: 2 = SWIZZLE_128B (16-byte swizzle atoms); 1 = SWIZZLE_128B_BASE32B (32-byte atoms) -- the only layout
+// the hardware takes for MN-major 32-bit (tf32) operands, written by TMA with CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B.
+B200DP_DEVINL uint64_t umma_smem_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes,
+                                      uint32_t layout = 2) {
   uint64_t d = 0;
   d |= static_cast<uint64_t>((smem_addr & 0x3FFFF) >> 4);
   d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFF) << 16;
   d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3FFF) << 32;
   d |= 1ull << 46;  // descriptor version for sm_100
-  d |= 2ull << 61;  // SWIZZLE_128B
+  d |= static_cast<uint64_t>(layout) << 61;
   return d;
 }
 

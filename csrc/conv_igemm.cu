@@ -791,11 +791,14 @@ B200DP_DEVINL void conv_wgrad_body(const CUtensorMap& tmDY, const CUtensorMap& t
           const uint32_t b_addr = a_addr + kABytes;
 #pragma unroll
           for (int k = 0; k < kPix / Prec::kUmmaK; ++k) {
-            // MN-major SW128: rows are pixels (K), 128 B each; 8-pixel groups are 1024 B apart (SBO), column
-            // blocks of one 128-byte row (64 bf16 / 32 tf32 channels) are one sub-tile apart (LBO); the pixels of
-            // one MMA (16 / 8) are +2048 / +1024 B.
-            const uint64_t da = umma_smem_desc(a_addr + k * Prec::kUmmaK * kRowBytes, kSubTileBytes, 1024);
-            const uint64_t db = umma_smem_desc(b_addr + k * Prec::kUmmaK * kRowBytes, kSubTileBytes, 1024);
+            // MN-major: rows are pixels (K), 128 B each; column blocks of one 128-byte row (64 bf16 / 32 tf32
+            // channels) are one sub-tile apart (LBO); the pixels of one MMA (16 / 8) are +2048 / +1024 B.
+            // bf16: SWIZZLE_128B, swizzle atoms of 8 pixel rows, 1024 B apart (SBO).  tf32: MN-major 32-bit
+            // operands only exist as SWIZZLE_128B_BASE32B, whose atoms are 4 pixel rows = 512 B (SBO).
+            constexpr uint32_t kSbo = Prec::kTf32 ? 512 : 1024;
+            constexpr uint32_t kLayout = Prec::kTf32 ? 1 : 2;
+            const uint64_t da = umma_smem_desc(a_addr + k * Prec::kUmmaK * kRowBytes, kSubTileBytes, kSbo, kLayout);
+            const uint64_t db = umma_smem_desc(b_addr + k * Prec::kUmmaK * kRowBytes, kSubTileBytes, kSbo, kLayout);
             umma_ss<Prec>(tmem_base, da, db, kIdesc, (kb | k) != 0);
           }
           umma_commit(&empty_bar[stage]);
@@ -933,8 +936,9 @@ static PFN_cuTensorMapEncodeTiled_v12000 get_encode_fn() {
 
 // Tensor map over 2-byte (bf16) or 4-byte elements; 4-byte maps use the TFLOAT32 type, i.e. the TMA unit rounds the
 // fp32 data to tf32 (round to nearest) on its way into shared memory.  128-byte swizzle, out-of-bounds = zero.
+// atom32: the 128-byte swizzle with 32-byte atoms (MN-major tf32 operands of the weight-gradient kernel).
 static int make_tmap(CUtensorMap* tm, const void* base, int rank, const uint64_t* dims, const uint32_t* box,
-                     int elem_bytes = 2) {
+                     int elem_bytes = 2, bool atom32 = false) {
   auto fn = get_encode_fn();
   if (fn == nullptr) return B200DP_ENOSYS;
   cuuint64_t gdim[4];
@@ -949,7 +953,8 @@ static int make_tmap(CUtensorMap* tm, const void* base, int rank, const uint64_t
     if (i < rank - 1) gstride[i] = stride;
   }
   CUresult r = fn(tm, elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_TFLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), gdim, gstride, bdim, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, atom32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_error("cuTensorMapEncodeTiled failed with CUresult %d (rank %d dims %llu %llu box %u %u)", (int)r, rank,
@@ -1333,13 +1338,13 @@ static int conv_wgrad_impl(const void* dy, const void* x, float* dw, int B, int 
   {
     const uint64_t dims[2] = {(uint64_t)Cout, (uint64_t)B * H * W};
     const uint32_t box[2] = {(uint32_t)kCh, (uint32_t)kPix};
-    int rc = make_tmap(&tmDY, dy, 2, dims, box, Prec::kBytes);
+    int rc = make_tmap(&tmDY, dy, 2, dims, box, Prec::kBytes, Prec::kTf32);
     if (rc) return rc;
   }
   {
     const uint64_t dims[4] = {(uint64_t)Cin, (uint64_t)W, (uint64_t)H, (uint64_t)B};
     const uint32_t box[4] = {(uint32_t)kCh, (uint32_t)W, (uint32_t)p.TH, (uint32_t)p.TN};
-    int rc = make_tmap(&tmX, x, 4, dims, box, Prec::kBytes);
+    int rc = make_tmap(&tmX, x, 4, dims, box, Prec::kBytes, Prec::kTf32);
     if (rc) return rc;
   }
   // 3 stages (96 / 144 / 72 KiB): the 128-wide kernel then fits on an SM next to a 3-stage dgrad CTA

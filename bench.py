@@ -18,7 +18,8 @@ and a device -> host read of every step's loss inside the timed region.
 
 Extra keys of the same line, same lease: ``strong`` -- the reference's own operating point, global batch 256
 split over the N ranks (BASELINE.json configs 2-4), for part3 / part2b / part2a (one rank: part1), for BOTH
-arms; ``selfcheck`` (N > 1, this framework's arm) -- every collective kernel against a device-computed
+arms; ``same_precision`` -- the same step with ``--dtype tf32`` (fp32 activations, tf32 tensor-core math: the
+precision of the reference arm); ``selfcheck`` (N > 1, this framework's arm) -- every collective kernel against a device-computed
 expectation at VGG-11's bucket sizes plus 2,000 skewed launches, run before anything is timed (a mismatch
 aborts with exit code 3); ``roofline`` -- the step's FLOPs and streamed bytes against MEASURED_PEAKS.json.
 At one GPU there is no peer to synchronise with: both arms run the tutorial's single-process part1 loop.
@@ -125,6 +126,7 @@ def parse_args():
     p.add_argument("--dtype", choices=("bf16", "tf32"), default="bf16",
                    help="operand / activation precision of the native arm (fp32 master weights either way)")
     p.add_argument("--no-strong", action="store_true", help="skip the global-batch-256 runs of the other modes")
+    p.add_argument("--no-tf32", action="store_true", help="skip the extra tf32 (same precision as the reference) run")
     p.add_argument("--no-selfcheck", action="store_true", help="skip the collective self-check at N > 1")
     return p.parse_args()
 
@@ -327,6 +329,20 @@ def run_native(args) -> dict:
         out["exposed_comm_ms_per_step"] = ms_dev - ms_local
         out["exposed_comm_fraction"] = (ms_dev - ms_local) / ms_dev
     tr.close()
+
+    # ---- the same-precision arm: the same step with tf32 tensor-core math on fp32 activations (the precision of
+    # ---- the reference's fp32 model under torch's TF32 convolutions), same mode, same batch, same lease
+    if args.dtype == "bf16" and not args.no_tf32:
+        import argparse as _ap
+        a32 = _ap.Namespace(**{**vars(args), "dtype": "tf32"})
+        t = Trainer(native_config(a32, mode, world, rank, base_port + 10, strong_main))
+        for i in range(3):
+            t.backend.run_staged(t.backend.stage_inputs(*host_batches[i % 8]))
+        steps = min(args.steps, 50)
+        ms = time_replays(t.backend, steps)
+        out["same_precision"] = {"dtype": "tf32", "ms_per_step": ms, "images_per_s": cfg.global_batch / (ms * 1e-3),
+                                 "steps": steps, "roofline": roofline(specs, B, ms, 4)}
+        t.close()
 
     # ---- the reference's own operating point: global batch 256 split over the ranks, every sync mode
     if not args.no_strong:

@@ -236,6 +236,7 @@ class NativeVGG:
         self._wgrad_stream = torch.cuda.Stream(dev)
         self._wgrad_fork = [torch.cuda.Event() for _ in self.specs]
         self._wgrad_join = torch.cuda.Event()
+        self._clear_fork, self._clear_done, self._clear_pending = torch.cuda.Event(), torch.cuda.Event(), False
         self._dgrad_done = [torch.cuda.Event() for _ in self.specs]
         self._block_prep = None
         self._adopt_parameters()
@@ -449,6 +450,15 @@ class NativeVGG:
         self._B = B
         if training:
             K.fill_zero(self.zero_region)
+            if WGRAD_ON_SIDE_STREAM:
+                # the 37 MB gradient clear runs beside the forward pass instead of at the head of backward
+                cur = torch.cuda.current_stream()
+                self._clear_fork.record(cur)
+                self._wgrad_stream.wait_event(self._clear_fork)
+                with torch.cuda.stream(self._wgrad_stream):
+                    K.fill_zero(self.flat_grads)
+                    self._clear_done.record(self._wgrad_stream)
+                self._clear_pending = True
         for b in self.blocks:
             s = b.spec
             y = b.y[:B]
@@ -490,7 +500,11 @@ class NativeVGG:
 
     def _clear_grads(self) -> None:
         # split-K weight gradients are accumulated with red.global.add; the conv biases rely on this zero too
-        K.fill_zero(self.flat_grads)
+        if self._clear_pending:
+            self._clear_pending = False
+            torch.cuda.current_stream().wait_event(self._clear_done)
+        else:
+            K.fill_zero(self.flat_grads)
 
     # ------------------------------------------------------------------ backward
     def backward(self, dlogits: Optional[torch.Tensor] = None) -> None:

@@ -132,6 +132,7 @@ class TimedLoader:
 
     def __iter__(self):
         import torch.distributed as dist
+        source = None if isinstance(self.batches, list) else iter(self.batches)     # a DataLoader
         for i in range(self.warmup + self.steps):
             if i == self.warmup:
                 if self.world > 1:
@@ -140,7 +141,8 @@ class TimedLoader:
                 if self.on_timed_region:
                     self.on_timed_region()
                 self.start.record()
-            yield self.batches[i % len(self.batches)]
+            yield self.batches[i % len(self.batches)] if source is None else next(source)
+        del source
         self.end.record()
         torch.cuda.synchronize()
         if self.on_timed_region_end:
@@ -148,9 +150,35 @@ class TimedLoader:
         self.elapsed_ms = self.start.elapsed_time(self.end)
 
 
+def reference_dataloader(per_rank_batch: int, rank: int, world: int, n_images: int):
+    """The reference's input pipeline on synthetic pixels: torchvision's ``CIFAR10`` dataset class (its own
+    ``__getitem__``: uint8 array -> PIL image -> transform) with the tutorial's transform chain and its
+    ``DataLoader(num_workers=2, pin_memory=True)`` (ref: master/part1/part1.py:65-85; DistributedSampler for
+    world > 1, ref: master/part3/part3.py:94-102).  Only the pixel source differs: the CIFAR-10 files are not on
+    the box and cannot be downloaded, so the arrays the class would have unpickled are random."""
+    import numpy as np
+    from torch.utils.data import DataLoader
+    from torch.utils.data.distributed import DistributedSampler
+    from torchvision import datasets, transforms
+    rng = np.random.default_rng(1234)
+    ds = datasets.CIFAR10.__new__(datasets.CIFAR10)       # skips the download / md5 check of __init__ only
+    ds.root, ds.train = "", True
+    ds.data = rng.integers(0, 256, size=(n_images, 32, 32, 3), dtype=np.uint8)
+    ds.targets = rng.integers(0, 10, size=n_images).tolist()
+    ds.transform = transforms.Compose([
+        transforms.RandomCrop(32, padding=4), transforms.RandomHorizontalFlip(), transforms.ToTensor(),
+        transforms.Normalize(mean=[v / 255.0 for v in (125.3, 123.0, 113.9)],
+                             std=[v / 255.0 for v in (63.0, 62.1, 66.7)])])
+    ds.target_transform, ds.transforms = None, None
+    if world > 1:
+        sampler = DistributedSampler(ds, num_replicas=world, rank=rank)
+        return DataLoader(ds, num_workers=2, batch_size=per_rank_batch, sampler=sampler, pin_memory=True)
+    return DataLoader(ds, num_workers=2, batch_size=per_rank_batch, sampler=None, shuffle=True, pin_memory=True)
+
+
 def run_reference(mode: str, rank: int, world: int, local_rank: int, per_rank_batch: int, steps: int, warmup: int,
                   host_inputs: bool, n_distinct_batches: int = 8, quiet: bool = True,
-                  on_timed_region=None, on_timed_region_end=None) -> dict:
+                  on_timed_region=None, on_timed_region_end=None, real_loader: bool = False) -> dict:
     """Time ``steps`` iterations of the reference's ``train_model``.  Returns ms per step (this rank)."""
     import torch.distributed as dist
     import torch.nn as nn
@@ -169,7 +197,9 @@ def run_reference(mode: str, rank: int, world: int, local_rank: int, per_rank_ba
     criterion = nn.CrossEntropyLoss().to(device)
     g = torch.Generator().manual_seed(1234 + rank)
     batches = []
-    for _ in range(n_distinct_batches):
+    if real_loader:
+        batches = reference_dataloader(per_rank_batch, rank, world, (warmup + steps) * per_rank_batch * world)
+    for _ in range(0 if real_loader else n_distinct_batches):
         x = torch.randn(per_rank_batch, 3, 32, 32, generator=g)
         y = torch.randint(0, 10, (per_rank_batch,), generator=g)
         if host_inputs:

@@ -128,6 +128,9 @@ def parse_args():
     p.add_argument("--no-strong", action="store_true", help="skip the global-batch-256 runs of the other modes")
     p.add_argument("--no-tf32", action="store_true", help="skip the extra tf32 (same precision as the reference) run")
     p.add_argument("--no-selfcheck", action="store_true", help="skip the collective self-check at N > 1")
+    p.add_argument("--no-loader", action="store_true",
+                   help="skip the input-pipeline run (uint8 images -> augmentation -> training step)")
+    p.add_argument("--loader-threads", type=int, default=4)
     return p.parse_args()
 
 
@@ -216,6 +219,40 @@ def make_batches(B: int, rank: int, n: int = 8):
              torch.randint(0, 10, (B,), generator=g).pin_memory()) for _ in range(n)]
 
 
+def loader_e2e(tr, cfg, steps: int, threads: int, warm: int = 5) -> dict:
+    """K training steps fed by ``NativeBatchPipeline`` from a uint8 dataset, augmentation on, the loss of every
+    step read back.  Timed with CUDA events around the K steps (max over ranks)."""
+    from cs744_pytorch_distributed_tutorial_b200.data import NativeBatchPipeline, SyntheticCIFAR10
+    be = tr.backend
+    B = cfg.per_rank_batch
+    ds = SyntheticCIFAR10((warm + steps) * B * cfg.world_size, train=True)
+    pipe = NativeBatchPipeline(ds, B, cfg.world_size, cfg.rank, train=True, augment=True, drop_last=True, seed=0,
+                               threads=threads)
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    tickets, last, n = [], None, 0
+    for i, (x, y) in enumerate(pipe):
+        if i == warm:
+            be.barrier()
+            torch.cuda.synchronize()
+            t0.record()
+        tr.train_step(x, y)
+        pipe.consumed(be.input_event())
+        if i >= warm:
+            n += 1
+            tickets.append(be.read_loss_async())
+            if len(tickets) > 8:
+                be.loss_value(tickets.pop(0))
+    last = [be.loss_value(t) for t in tickets][-1]
+    t1.record()
+    torch.cuda.synchronize()
+    be.barrier()
+    pipe.close()
+    ms = be.max_over_ranks(t0.elapsed_time(t1)) / n
+    return {"value": cfg.global_batch / (ms * 1e-3), "unit": "images/s", "ms_per_step": ms, "steps": n,
+            "loader": f"csrc/loader.cpp, {threads} threads, RandomCrop(32,4)+flip+normalise, pinned ring",
+            "last_loss": last}
+
+
 def run_native(args) -> dict:
     from cs744_pytorch_distributed_tutorial_b200.config import TrainConfig
     from cs744_pytorch_distributed_tutorial_b200.engine import Trainer
@@ -289,6 +326,14 @@ def run_native(args) -> dict:
         ms_e2e = be.max_over_ranks(t0.elapsed_time(t1)) / args.steps
         e2e = {"value": cfg.global_batch / (ms_e2e * 1e-3), "unit": "images/s", "ms_per_step": ms_e2e,
                "h2d_bytes_per_step": B * (3 * 32 * 32 * 4 + 8), "d2h_bytes_per_step": 4, "last_loss": last}
+    # ---- end to end from uint8 images: the C++ loader (sampling, crop, flip, normalise into pinned ring buffers)
+    # ---- feeds Trainer.train_step; the counterpart of the reference's DataLoader run
+    e2e_loader = None
+    if not args.no_loader:
+        try:
+            e2e_loader = loader_e2e(tr, cfg, min(args.steps, 200), args.loader_threads)
+        except Exception as e:
+            e2e_loader = {"unavailable": f"{type(e).__name__}: {e}"[:200]}
     specs = tr.model.block_specs()
     out = {
         "metric": "VGG-11 CIFAR-10 images/sec", "impl": "native", "value": cfg.global_batch / (ms_dev * 1e-3),
@@ -305,6 +350,8 @@ def run_native(args) -> dict:
     }
     if e2e is not None:
         out["e2e"] = e2e
+    if e2e_loader is not None:
+        out["e2e_with_loader"] = e2e_loader
     if selfcheck is not None:
         out["selfcheck"] = selfcheck
     if world > 1:
@@ -419,6 +466,17 @@ def run_reference(args) -> dict:
         ms = max_ranks(e2e["ms_per_step"])
         out["e2e"] = {"value": gb / (ms * 1e-3), "unit": "images/s", "ms_per_step": ms,
                       "h2d_bytes_per_step": e2e["h2d_bytes_per_step"], "d2h_bytes_per_step": 4.0 / 20}
+    # ---- with the tutorial's own input pipeline in the loop (CIFAR10 dataset class, PIL transforms,
+    # ---- DataLoader(num_workers=2, pin_memory=True)) instead of ready-made tensors
+    if not args.no_loader:
+        try:
+            steps = min(args.steps, 50)
+            r = ref_harness.run_reference(mode, rank, world, local, B, steps, 5, host_inputs=True, real_loader=True)
+            ms = max_ranks(r["ms_per_step"])
+            out["e2e_with_loader"] = {"value": gb / (ms * 1e-3), "unit": "images/s", "ms_per_step": ms, "steps": steps,
+                                      "loader": "torchvision CIFAR10 + transforms, DataLoader(num_workers=2)"}
+        except Exception as e:
+            out["e2e_with_loader"] = {"unavailable": f"{type(e).__name__}: {e}"[:200]}
     # ---- the reference's own operating point: global batch 256 split over the ranks, every sync mode
     if not args.no_strong:
         strong = {}

@@ -371,6 +371,10 @@ struct BnBwdParams {   // y / dout / dy: activations of type T, selected by the 
   float* dgamma;
   float* dbeta;
   int B, H, W, C, pool;
+  int count_B = 0;  // batch the statistics were taken over when y / dout / dy are a slice of it (0: B)
+  __host__ __device__ float inv_count() const {
+    return 1.f / static_cast<float>(static_cast<long>(count_B > 0 ? count_B : B) * H * W);
+  }
 };
 
 // Register-lean formulation (64 regs -> 4 blocks / SM so that enough 16-byte loads are in flight):
@@ -389,7 +393,7 @@ B200DP_DEVINL void bn_relu_pool_bwd_body(const BnBwdParams& p, float* red) {
   const int c0i = chunk * 8;
   const int Ho = p.pool ? p.H / 2 : p.H, Wo = p.pool ? p.W / 2 : p.W;
   const long Q = static_cast<long>(p.B) * Ho * Wo;
-  const float inv_count = 1.f / static_cast<float>(static_cast<long>(p.B) * p.H * p.W);
+  const float inv_count = p.inv_count();
 
   Vec8 scale, shift, c0, c1;
   {
@@ -529,7 +533,7 @@ __global__ void __launch_bounds__(256, 3) bn_bwd_apply_nopool_kernel(const BnBwd
   const int rows_per_block = blockDim.x / chunks;
   const int chunk = threadIdx.x % chunks, rl = threadIdx.x / chunks, c0i = chunk * 8;
   const long Q = static_cast<long>(p.B) * p.H * p.W;
-  const float inv_count = 1.f / static_cast<float>(Q);
+  const float inv_count = p.inv_count();
   Vec8 scale, shift, c0, c1;
   {
     const Vec8 mean = load_f32x8(p.mean + c0i), invstd = load_f32x8(p.invstd + c0i);
@@ -595,7 +599,7 @@ __global__ void __launch_bounds__(256, 2) bn_bwd_apply_pool_kernel(const BnBwdPa
   const int chunk = threadIdx.x % chunks, rl = threadIdx.x / chunks, c0i = chunk * 8;
   const int Ho = p.H / 2, Wo = p.W / 2;
   const long Q = static_cast<long>(p.B) * Ho * Wo;
-  const float inv_count = 1.f / static_cast<float>(static_cast<long>(p.B) * p.H * p.W);
+  const float inv_count = p.inv_count();
   Vec8 scale, shift, c0, c1;
   {
     const Vec8 mean = load_f32x8(p.mean + c0i), invstd = load_f32x8(p.invstd + c0i);
@@ -745,7 +749,7 @@ __global__ void __launch_bounds__(bn_tma_items<T>(), 2) bn_bwd_apply_pool_tma_ke
   // per-thread constants: the channel chunk of a thread never changes (kBnTmaItems % chunks == 0)
   const int chunk = threadIdx.x % chunks, pix = threadIdx.x / chunks, c0i = chunk * 8;
   const int gt = pix / Wo, wo = pix - gt * Wo;                        // tile inside the stage, pooled column
-  const float inv_count = 1.f / static_cast<float>(static_cast<long>(p.B) * p.H * p.W);
+  const float inv_count = p.inv_count();
   Vec8 scale, shift, c0, c1;
   {
     const Vec8 mean = load_f32x8(p.mean + c0i), invstd = load_f32x8(p.invstd + c0i);
@@ -1515,7 +1519,7 @@ static int launch_bn_bwd(bool apply, const BnBwdParams& p, cudaStream_t s) {
   // reduce pass: at most one resident wave (3 blocks / SM), a grid-stride loop balances better than a ragged tail
   const int blocks = grid_for(Q, rows_per_block, 148 * 3);
   if (apply && p.pool && bn_tma_supported<T>(p)) return launch_bn_apply_pool_tma<T>(p, s);
-  if (apply && !p.pool && bn_tma_shape_ok(p.H, p.W, p.C, 0))
+  if (apply && !p.pool && p.count_B == 0 && bn_tma_shape_ok(p.H, p.W, p.C, 0))
     return b200dp_bn_bwd_apply_nopool_tma_ex(p.y, p.dout, p.mean, p.invstd, p.gamma, p.beta, p.sums, p.dy, p.dgamma,
                                              p.dbeta, p.B, p.H, p.W, p.C, kDtype, s);
   if (apply && !p.pool)
@@ -1582,6 +1586,21 @@ extern "C" int b200dp_bn_relu_pool_bwd_apply_ex(const void* y, const void* dout,
                                                 const float* sums, void* dy, float* dgamma, float* dbeta, int B,
                                                 int H, int W, int C, int pool, int dtype, b200dp_stream_t s) {
   BnBwdParams p{y, dout, mean, invstd, gamma, beta, const_cast<float*>(sums), dy, dgamma, dbeta, B, H, W, C, pool};
+  return launch_bn_bwd_dt(dtype, true, p, static_cast<cudaStream_t>(s));
+}
+/* The apply pass on a batch slice: y / dout / dy hold B images out of the count_B the sums were taken over, so a
+ * layer's backward can be cut into pieces that pipeline with the weight-gradient GEMM consuming dy. */
+extern "C" int b200dp_bn_relu_pool_bwd_apply_part(const void* y, const void* dout, const float* mean,
+                                                  const float* invstd, const float* gamma, const float* beta,
+                                                  const float* sums, void* dy, float* dgamma, float* dbeta, int B,
+                                                  int H, int W, int C, int pool, int count_B, int dtype,
+                                                  b200dp_stream_t s) {
+  if (count_B < B) {
+    set_error("bn_relu_pool_bwd_apply_part: count_B=%d is smaller than the slice B=%d", count_B, B);
+    return B200DP_EINVAL;
+  }
+  BnBwdParams p{y, dout, mean, invstd, gamma, beta, const_cast<float*>(sums), dy, dgamma, dbeta, B, H, W, C, pool};
+  p.count_B = count_B;
   return launch_bn_bwd_dt(dtype, true, p, static_cast<cudaStream_t>(s));
 }
 extern "C" int b200dp_bn_relu_pool_bwd_apply(const void* y, const void* dout, const float* mean,

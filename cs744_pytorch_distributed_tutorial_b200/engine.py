@@ -250,11 +250,7 @@ class NativeBackend:
         from .ops import _lib
         self.graph = torch.cuda.CUDAGraph()
         n0 = _lib.launch_count
-        import os
-        kw = {}
-        if os.environ.get("B200DP_EXP_PRIO", "0") == "1":       # measurement toggle of the current A/B
-            kw["stream"] = torch.cuda.Stream(self.device, priority=-1)
-        with torch.cuda.graph(self.graph, **kw):
+        with torch.cuda.graph(self.graph):
             self._step_body()
         self.launches_per_step = _lib.launch_count - n0
         torch.cuda.synchronize(self.device)

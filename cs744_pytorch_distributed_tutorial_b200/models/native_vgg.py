@@ -31,8 +31,6 @@ from ..ops import native as K
 
 # weight gradients on a second stream, concurrently with the dgrad / BatchNorm-backward chain
 WGRAD_ON_SIDE_STREAM = os.environ.get("B200DP_WGRAD_STREAM", "1") != "0"
-_EXP_SPLIT0 = int(os.environ.get("B200DP_EXP_SPLIT0", "0"))          # measurement toggles of the current A/B
-_EXP_FILL = os.environ.get("B200DP_EXP_FILL", "side")
 
 ALIGN = 4  # floats; every tensor starts on a 16-byte boundary inside the flat buffers
 
@@ -238,8 +236,6 @@ class NativeVGG:
         self._wgrad_stream = torch.cuda.Stream(dev)
         self._wgrad_fork = [torch.cuda.Event() for _ in self.specs]
         self._wgrad_join = torch.cuda.Event()
-        self._clear_fork, self._clear_done, self._clear_pending = torch.cuda.Event(), torch.cuda.Event(), False
-        self._piece_fork = [torch.cuda.Event() for _ in range(8)]
         self._dgrad_done = [torch.cuda.Event() for _ in self.specs]
         self._block_prep = None
         self._adopt_parameters()
@@ -453,15 +449,6 @@ class NativeVGG:
         self._B = B
         if training:
             K.fill_zero(self.zero_region)
-            if WGRAD_ON_SIDE_STREAM and _EXP_FILL == "side":
-                # the 37 MB gradient clear runs beside the forward pass instead of at the head of backward
-                cur = torch.cuda.current_stream()
-                self._clear_fork.record(cur)
-                self._wgrad_stream.wait_event(self._clear_fork)
-                with torch.cuda.stream(self._wgrad_stream):
-                    K.fill_zero(self.flat_grads)
-                    self._clear_done.record(self._wgrad_stream)
-                self._clear_pending = True
         for b in self.blocks:
             s = b.spec
             y = b.y[:B]
@@ -503,11 +490,7 @@ class NativeVGG:
 
     def _clear_grads(self) -> None:
         # split-K weight gradients are accumulated with red.global.add; the conv biases rely on this zero too
-        if self._clear_pending:
-            self._clear_pending = False
-            torch.cuda.current_stream().wait_event(self._clear_done)
-        else:
-            K.fill_zero(self.flat_grads)
+        K.fill_zero(self.flat_grads)
 
     # ------------------------------------------------------------------ backward
     def backward(self, dlogits: Optional[torch.Tensor] = None) -> None:
@@ -529,10 +512,6 @@ class NativeVGG:
         for i in range(len(self.blocks) - 1, -1, -1):
             b = self.blocks[i]
             s = b.spec
-            if i == 0 and reduced and side is not None and _EXP_SPLIT0 > 1 and B % _EXP_SPLIT0 == 0 \
-                    and self.wgrad_push is None:
-                self._backward_block0_pipelined(B, main, side, _EXP_SPLIT0)
-                break
             K.bn_relu_pool_bwd(b.y[:B], b.dout[:B], b.mean, b.invstd, b.gamma, b.beta, b.sums, b.dy[:B], b.g_gamma,
                                b.g_beta, s.pool, out=b.out[:B], skip_reduce=reduced)
             reduced = False
@@ -569,28 +548,6 @@ class NativeVGG:
         if side is not None:
             self._wgrad_join.record(side)
             main.wait_event(self._wgrad_join)
-
-    def _backward_block0_pipelined(self, B: int, main, side, pieces: int) -> None:
-        """The first block has no data gradient, so its BatchNorm backward and its weight gradient are the
-        serial tail of the step.  Cut along the batch, piece k's weight gradient (accumulated with the split-K
-        atomics) runs beside the BatchNorm backward of piece k+1."""
-        b = self.blocks[0]
-        s = b.spec
-        h = B // pieces
-        for k in range(pieces):
-            lo, hi = k * h, (k + 1) * h
-            K.bn_relu_pool_bwd_apply_part(b.y[lo:hi], b.dout[lo:hi], b.mean, b.invstd, b.gamma, b.beta, b.sums,
-                                          b.dy[lo:hi], b.g_gamma, b.g_beta, s.pool, B)
-            self._piece_fork[k].record(main)
-            side.wait_event(self._piece_fork[k])
-            with torch.cuda.stream(side):
-                K.conv_wgrad(b.dy[lo:hi], b.x_in[lo:hi], b.g_w, taps=b.taps, cin_valid=(27 if b.first else None),
-                             split_k=b.wgrad_split_k, block_n=b.wgrad_block_n, accumulate=True)
-        self._dgrad_done[0].record(main)
-        with torch.cuda.stream(side):
-            if self.on_bucket_ready is not None:
-                for kk in self._bucket_of_block.get(0, ()):
-                    self.on_bucket_ready(kk)
 
     # ------------------------------------------------------------------ torch.autograd bridge
     def autograd_forward(self, x: torch.Tensor, training: bool) -> torch.Tensor:

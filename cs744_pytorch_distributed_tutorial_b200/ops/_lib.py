@@ -53,7 +53,6 @@ _PROTOTYPES = {
     "b200dp_bn_relu_pool_bwd_reduce_ex": [P, P, P, P, P, P, P, I, I, I, I, I, I, P],
     "b200dp_bn_relu_pool_bwd_reduce_from_out_ex": [P, P, P, P, P, LL, I, I, P],
     "b200dp_bn_relu_pool_bwd_apply_ex": [P, P, P, P, P, P, P, P, P, P, I, I, I, I, I, I, P],
-    "b200dp_bn_relu_pool_bwd_apply_part": [P, P, P, P, P, P, P, P, P, P, I, I, I, I, I, I, I, P],
     "b200dp_linear_fwd_ex": [P, P, P, P, I, I, I, I, P],
     "b200dp_linear_bwd_ex": [P, P, P, P, P, P, I, I, I, I, P],
     "b200dp_head_fwd_bwd_ex": [P, P, P, P, P, P, P, P, P, P, P, I, I, I, F, I, P],

@@ -164,18 +164,6 @@ def bn_relu_pool_bwd(y, dout, mean, invstd, gamma, beta, sums, dy, dgamma, dbeta
     return dy
 
 
-def bn_relu_pool_bwd_apply_part(y, dout, mean, invstd, gamma, beta, sums, dy, dgamma, dbeta, pool: bool, count_b: int):
-    """The dY pass of ``bn_relu_pool_bwd`` on a batch slice: ``y`` / ``dout`` / ``dy`` hold some of the ``count_b``
-    images that ``sums`` (complete on entry) and the statistics cover."""
-    B, H, W, C = y.shape
-    dt = _act_dtype(y, "y")
-    _chk(dout, y.dtype, "dout")
-    _chk(dy, y.dtype, "dy")
-    call("b200dp_bn_relu_pool_bwd_apply_part", ptr(y), ptr(dout), ptr(mean), ptr(invstd), ptr(gamma), ptr(beta),
-         ptr(sums), ptr(dy), ptr(dgamma), ptr(dbeta), B, H, W, C, int(pool), int(count_b), dt, stream_ptr())
-    return dy
-
-
 def linear_fwd(x, w, b, logits):
     B, Fdim = x.shape[0], x.numel() // x.shape[0]
     call("b200dp_linear_fwd_ex", ptr(x), ptr(w), ptr(b), ptr(logits), B, Fdim, w.shape[0], _act_dtype(x, "x"),

@@ -1378,6 +1378,15 @@ static int conv_wgrad_impl(const void* dy, const void* x, float* dw, int B, int 
     if (block_n == 128) return launch_wgrad_push<128, 3>(tmDY, tmX, pp, tiles, split_k, stream);
     return launch_wgrad_push<64, 4>(tmDY, tmX, pp, tiles, split_k, stream);
   }
+  static const bool deep = [] {   // measurement toggle of the current A/B: pipeline depth that fills the 227 KB
+    const char* e = getenv("B200DP_EXP_WGRAD_DEEP");
+    return e != nullptr && e[0] == '1';
+  }();
+  if (deep) {
+    if (block_n == 256) return launch_wgrad<Prec, 256, 4>(tmDY, tmX, p, tiles, split_k, stream);
+    if (block_n == 128) return launch_wgrad<Prec, 128, 6>(tmDY, tmX, p, tiles, split_k, stream);
+    if (block_n == 64) return launch_wgrad<Prec, 64, 8>(tmDY, tmX, p, tiles, split_k, stream);
+  }
   if (block_n == 256) return launch_wgrad<Prec, 256, 3>(tmDY, tmX, p, tiles, split_k, stream);
   if (block_n == 128) return launch_wgrad<Prec, 128, 3>(tmDY, tmX, p, tiles, split_k, stream);
   if (block_n == 64) return launch_wgrad<Prec, 64, 4>(tmDY, tmX, p, tiles, split_k, stream);

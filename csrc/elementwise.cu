@@ -371,10 +371,6 @@ struct BnBwdParams {   // y / dout / dy: activations of type T, selected by the 
   float* dgamma;
   float* dbeta;
   int B, H, W, C, pool;
-  int count_B = 0;  // batch the statistics were taken over when y / dout / dy are a slice of it (0: B)
-  __host__ __device__ float inv_count() const {
-    return 1.f / static_cast<float>(static_cast<long>(count_B > 0 ? count_B : B) * H * W);
-  }
 };
 
 // Register-lean formulation (64 regs -> 4 blocks / SM so that enough 16-byte loads are in flight):
@@ -393,7 +389,7 @@ B200DP_DEVINL void bn_relu_pool_bwd_body(const BnBwdParams& p, float* red) {
   const int c0i = chunk * 8;
   const int Ho = p.pool ? p.H / 2 : p.H, Wo = p.pool ? p.W / 2 : p.W;
   const long Q = static_cast<long>(p.B) * Ho * Wo;
-  const float inv_count = p.inv_count();
+  const float inv_count = 1.f / static_cast<float>(static_cast<long>(p.B) * p.H * p.W);
 
   Vec8 scale, shift, c0, c1;
   {
@@ -533,7 +529,7 @@ __global__ void __launch_bounds__(256, 3) bn_bwd_apply_nopool_kernel(const BnBwd
   const int rows_per_block = blockDim.x / chunks;
   const int chunk = threadIdx.x % chunks, rl = threadIdx.x / chunks, c0i = chunk * 8;
   const long Q = static_cast<long>(p.B) * p.H * p.W;
-  const float inv_count = p.inv_count();
+  const float inv_count = 1.f / static_cast<float>(Q);
   Vec8 scale, shift, c0, c1;
   {
     const Vec8 mean = load_f32x8(p.mean + c0i), invstd = load_f32x8(p.invstd + c0i);
@@ -599,7 +595,7 @@ __global__ void __launch_bounds__(256, 2) bn_bwd_apply_pool_kernel(const BnBwdPa
   const int chunk = threadIdx.x % chunks, rl = threadIdx.x / chunks, c0i = chunk * 8;
   const int Ho = p.H / 2, Wo = p.W / 2;
   const long Q = static_cast<long>(p.B) * Ho * Wo;
-  const float inv_count = p.inv_count();
+  const float inv_count = 1.f / static_cast<float>(static_cast<long>(p.B) * p.H * p.W);
   Vec8 scale, shift, c0, c1;
   {
     const Vec8 mean = load_f32x8(p.mean + c0i), invstd = load_f32x8(p.invstd + c0i);
@@ -749,7 +745,7 @@ __global__ void __launch_bounds__(bn_tma_items<T>(), 2) bn_bwd_apply_pool_tma_ke
   // per-thread constants: the channel chunk of a thread never changes (kBnTmaItems % chunks == 0)
   const int chunk = threadIdx.x % chunks, pix = threadIdx.x / chunks, c0i = chunk * 8;
   const int gt = pix / Wo, wo = pix - gt * Wo;                        // tile inside the stage, pooled column
-  const float inv_count = p.inv_count();
+  const float inv_count = 1.f / static_cast<float>(static_cast<long>(p.B) * p.H * p.W);
   Vec8 scale, shift, c0, c1;
   {
     const Vec8 mean = load_f32x8(p.mean + c0i), invstd = load_f32x8(p.invstd + c0i);
@@ -1061,16 +1057,34 @@ __global__ void __launch_bounds__(256) linear_bwd_kernel(const T* __restrict__ x
 
 // ---------------------------------------------------------------------------
 // classifier head of a training step in ONE launch: logits, mean softmax cross-entropy, top-1 count,
-// dlogits, dX and this block's share of dW / db (experimental, B200DP_HEAD_FUSED=1).  One warp per
-// sample; the block's activations and dlogits are parked in shared memory so that dW needs one atomic
-// per (class, feature) per block.  Loss and count are combined by the last block to finish, so neither
-// needs clearing and the result does not depend on the order of atomics.
+// dlogits, dX and this block's share of dW / db.  kHeadWarps samples per block, one warp each; the weight
+// matrix is staged in shared memory once per block (all its loads in flight together, no per-warp L2 round
+// trips), the block's activations and dlogits are parked there too so that dW needs one vector reduction per
+// (class, 4 features) per block.  Loss and count are combined in block order by the last block to take a ticket,
+// so neither needs clearing and the result does not depend on the order of atomics; the ticket is taken before
+// the dW reductions are issued so that its round trip overlaps them.
 // ---------------------------------------------------------------------------
-constexpr int kHeadWarps = 16;
-constexpr int kHeadMaxBlocks = 256;
+constexpr int kHeadWarps = 4;
+constexpr int kHeadMaxBlocks = 1024;
 __device__ float g_head_loss_part[kHeadMaxBlocks];
 __device__ int g_head_corr_part[kHeadMaxBlocks];
 __device__ unsigned int g_head_blocks_done = 0;
+
+template <class T>
+B200DP_DEVINL float4 head_load4(const T* p) {
+  if constexpr (sizeof(T) == 4) {
+    return *reinterpret_cast<const float4*>(p);
+  } else {
+    const uint2 r = *reinterpret_cast<const uint2*>(p);
+    return make_float4(__uint_as_float(r.x << 16), __uint_as_float(r.x & 0xffff0000u), __uint_as_float(r.y << 16),
+                       __uint_as_float(r.y & 0xffff0000u));
+  }
+}
+
+B200DP_DEVINL void head_red_add_v4(float* addr, const float4& v) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+}
 
 template <class T>
 __global__ void __launch_bounds__(kHeadWarps * 32)
@@ -1080,34 +1094,38 @@ __global__ void __launch_bounds__(kHeadWarps * 32)
                         float* __restrict__ dlogits, T* __restrict__ dx, float* __restrict__ dw,
                         float* __restrict__ db, int B, int F, int O, float grad_scale) {
   pdl_launch_dependents();
-  pdl_wait();
-  extern __shared__ float head_sm[];
-  float* xs = head_sm;                    // [kHeadWarps][F]
-  float* dls = head_sm + kHeadWarps * F;  // [kHeadWarps][kLinMaxO]
+  extern __shared__ __align__(16) float head_sm[];
+  float* ws = head_sm;                       // [O][F]
+  float* xs = ws + O * F;                    // [kHeadWarps][F]
+  float* dls = xs + kHeadWarps * F;          // [kHeadWarps][kLinMaxO]
   __shared__ float s_loss[kHeadWarps];
   __shared__ int s_corr[kHeadWarps];
-  __shared__ bool s_last;
   const int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int i = blockIdx.x * kHeadWarps + wib;  // sample of this warp
   const bool live = i < B;
+  pdl_wait();
+  // weights -> shared memory (coalesced float4), this warp's activation row -> shared memory as fp32
+  for (int k = threadIdx.x * 4; k < O * F; k += kHeadWarps * 32 * 4)
+    *reinterpret_cast<float4*>(ws + k) = __ldg(reinterpret_cast<const float4*>(w + k));
+  for (int f = lane * 4; f < F; f += 128) {
+    const float4 v = live ? head_load4(x + static_cast<long>(i) * F + f) : make_float4(0.f, 0.f, 0.f, 0.f);
+    *reinterpret_cast<float4*>(xs + wib * F + f) = v;
+  }
   if (lane < kLinMaxO) dls[wib * kLinMaxO + lane] = 0.f;
+  __syncthreads();
   float my_loss = 0.f;
   int my_corr = 0;
   if (live) {
-    const T* xr = x + static_cast<long>(i) * F;
     float acc[kLinMaxO];
 #pragma unroll
     for (int o = 0; o < kLinMaxO; ++o) acc[o] = 0.f;
-    for (int f = lane * 8; f < F; f += 256) {
-      const Vec8 xv = load8(xr + f);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) xs[wib * F + f + j] = xv.v[j];
+    for (int f = lane * 4; f < F; f += 128) {
+      const float4 xv = *reinterpret_cast<const float4*>(xs + wib * F + f);
 #pragma unroll
       for (int o = 0; o < kLinMaxO; ++o) {
         if (o < O) {
-          const Vec8 wv = load_f32x8(w + static_cast<long>(o) * F + f);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) acc[o] = fmaf(xv.v[j], wv.v[j], acc[o]);
+          const float4 wv = *reinterpret_cast<const float4*>(ws + o * F + f);
+          acc[o] = fmaf(xv.x, wv.x, fmaf(xv.y, wv.y, fmaf(xv.z, wv.z, fmaf(xv.w, wv.w, acc[o]))));
         }
       }
     }
@@ -1116,9 +1134,11 @@ __global__ void __launch_bounds__(kHeadWarps * 32)
 #pragma unroll
     for (int o = 0; o < kLinMaxO; ++o) {
       float t = acc[o];
+      if (o < O) {
 #pragma unroll
-      for (int d = 16; d > 0; d >>= 1) t += __shfl_xor_sync(0xffffffffu, t, d);
-      l[o] = o < O ? t + bias[o] : -INFINITY;
+        for (int d = 16; d > 0; d >>= 1) t += __shfl_xor_sync(0xffffffffu, t, d);
+      }
+      l[o] = o < O ? t + __ldg(bias + o) : -INFINITY;
     }
     float mx = l[0];
     int am = 0;
@@ -1151,49 +1171,32 @@ __global__ void __launch_bounds__(kHeadWarps * 32)
       if (dlogits != nullptr) dlogits[static_cast<long>(i) * O + lane] = mine_d;
       dls[wib * kLinMaxO + lane] = mine_d;
     }
-    for (int f = lane * 8; f < F; f += 256) {
-      Vec8 a;
-#pragma unroll
-      for (int j = 0; j < 8; ++j) a.v[j] = 0.f;
+    for (int f = lane * 4; f < F; f += 128) {
+      float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
       for (int o = 0; o < kLinMaxO; ++o) {
         if (o < O) {
-          const Vec8 wv = load_f32x8(w + static_cast<long>(o) * F + f);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) a.v[j] = fmaf(dl[o], wv.v[j], a.v[j]);
+          const float4 wv = *reinterpret_cast<const float4*>(ws + o * F + f);
+          a.x = fmaf(dl[o], wv.x, a.x);
+          a.y = fmaf(dl[o], wv.y, a.y);
+          a.z = fmaf(dl[o], wv.z, a.z);
+          a.w = fmaf(dl[o], wv.w, a.w);
         }
       }
-      store8(dx + static_cast<long>(i) * F + f, a);
+      operand_store4(dx + static_cast<long>(i) * F + f, a.x, a.y, a.z, a.w);
     }
-  } else {
-    for (int f = lane; f < F; f += 32) xs[wib * F + f] = 0.f;
   }
   if (lane == 0) {
     s_loss[wib] = my_loss;
     s_corr[wib] = my_corr;
   }
   __syncthreads();
-  // dW / db of the block's samples: one atomic per (class, feature) per block
-  for (int f = threadIdx.x; f < F; f += blockDim.x) {
-#pragma unroll
-    for (int o = 0; o < kLinMaxO; ++o) {
-      if (o < O) {
-        float a = 0.f;
-#pragma unroll
-        for (int sidx = 0; sidx < kHeadWarps; ++sidx) a = fmaf(dls[sidx * kLinMaxO + o], xs[sidx * F + f], a);
-        atomicAdd(dw + static_cast<long>(o) * F + f, a);
-      }
-    }
-  }
-  if (static_cast<int>(threadIdx.x) < O) {
-    float a = 0.f;
-    for (int sidx = 0; sidx < kHeadWarps; ++sidx) a += dls[sidx * kLinMaxO + threadIdx.x];
-    atomicAdd(db + threadIdx.x, a);
-  }
-  // loss / count: per-block partials, summed in block order by whichever block finishes last
+  // loss / count: per-block partials; warp 0 takes the block's ticket now and looks at it after its reductions
+  unsigned ticket = 0;
   if (threadIdx.x == 0) {
     float tl = 0.f;
     int tc = 0;
+#pragma unroll
     for (int k = 0; k < kHeadWarps; ++k) {
       tl += s_loss[k];
       tc += s_corr[k];
@@ -1201,20 +1204,56 @@ __global__ void __launch_bounds__(kHeadWarps * 32)
     g_head_loss_part[blockIdx.x] = tl;
     g_head_corr_part[blockIdx.x] = tc;
     __threadfence();
-    s_last = atomicAdd(&g_head_blocks_done, 1u) == gridDim.x - 1;
+    ticket = atomicAdd(&g_head_blocks_done, 1u);
   }
-  __syncthreads();
-  if (s_last && threadIdx.x == 0) {
-    __threadfence();
-    float tl = 0.f;
-    int tc = 0;
-    for (unsigned k = 0; k < gridDim.x; ++k) {
-      tl += __ldcg(&g_head_loss_part[k]);   // L2: written by other blocks before their ticket
-      tc += __ldcg(&g_head_corr_part[k]);
+  // dW / db of the block's samples: one vector reduction per (class, 4 features) per block
+  for (int f = threadIdx.x * 4; f < F; f += kHeadWarps * 32 * 4) {
+    float4 xv[kHeadWarps];
+#pragma unroll
+    for (int sidx = 0; sidx < kHeadWarps; ++sidx) xv[sidx] = *reinterpret_cast<const float4*>(xs + sidx * F + f);
+#pragma unroll
+    for (int o = 0; o < kLinMaxO; ++o) {
+      if (o < O) {
+        float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int sidx = 0; sidx < kHeadWarps; ++sidx) {
+          const float d = dls[sidx * kLinMaxO + o];
+          a.x = fmaf(d, xv[sidx].x, a.x);
+          a.y = fmaf(d, xv[sidx].y, a.y);
+          a.z = fmaf(d, xv[sidx].z, a.z);
+          a.w = fmaf(d, xv[sidx].w, a.w);
+        }
+        head_red_add_v4(dw + static_cast<long>(o) * F + f, a);
+      }
     }
-    if (loss != nullptr) *loss = tl / static_cast<float>(B);
-    if (correct != nullptr) *correct = tc;
-    g_head_blocks_done = 0;  // ready for the next launch (stream order, graph replays)
+  }
+  if (static_cast<int>(threadIdx.x) < O) {
+    float a = 0.f;
+#pragma unroll
+    for (int sidx = 0; sidx < kHeadWarps; ++sidx) a += dls[sidx * kLinMaxO + threadIdx.x];
+    atomicAdd(db + threadIdx.x, a);
+  }
+  if (wib == 0) {
+    ticket = __shfl_sync(0xffffffffu, ticket, 0);
+    if (ticket == gridDim.x - 1) {   // every other block has published its partials before taking its ticket
+      __threadfence();
+      float tl = 0.f;
+      int tc = 0;
+      for (unsigned k = lane; k < gridDim.x; k += 32) {   // lane-strided, then a fixed butterfly: deterministic
+        tl += __ldcg(&g_head_loss_part[k]);
+        tc += __ldcg(&g_head_corr_part[k]);
+      }
+#pragma unroll
+      for (int d = 16; d > 0; d >>= 1) {
+        tl += __shfl_xor_sync(0xffffffffu, tl, d);
+        tc += __shfl_xor_sync(0xffffffffu, tc, d);
+      }
+      if (lane == 0) {
+        if (loss != nullptr) *loss = tl / static_cast<float>(B);
+        if (correct != nullptr) *correct = tc;
+        g_head_blocks_done = 0;  // ready for the next launch (stream order, graph replays)
+      }
+    }
   }
 }
 
@@ -1519,7 +1558,7 @@ static int launch_bn_bwd(bool apply, const BnBwdParams& p, cudaStream_t s) {
   // reduce pass: at most one resident wave (3 blocks / SM), a grid-stride loop balances better than a ragged tail
   const int blocks = grid_for(Q, rows_per_block, 148 * 3);
   if (apply && p.pool && bn_tma_supported<T>(p)) return launch_bn_apply_pool_tma<T>(p, s);
-  if (apply && !p.pool && p.count_B == 0 && bn_tma_shape_ok(p.H, p.W, p.C, 0))
+  if (apply && !p.pool && bn_tma_shape_ok(p.H, p.W, p.C, 0))
     return b200dp_bn_bwd_apply_nopool_tma_ex(p.y, p.dout, p.mean, p.invstd, p.gamma, p.beta, p.sums, p.dy, p.dgamma,
                                              p.dbeta, p.B, p.H, p.W, p.C, kDtype, s);
   if (apply && !p.pool)
@@ -1586,21 +1625,6 @@ extern "C" int b200dp_bn_relu_pool_bwd_apply_ex(const void* y, const void* dout,
                                                 const float* sums, void* dy, float* dgamma, float* dbeta, int B,
                                                 int H, int W, int C, int pool, int dtype, b200dp_stream_t s) {
   BnBwdParams p{y, dout, mean, invstd, gamma, beta, const_cast<float*>(sums), dy, dgamma, dbeta, B, H, W, C, pool};
-  return launch_bn_bwd_dt(dtype, true, p, static_cast<cudaStream_t>(s));
-}
-/* The apply pass on a batch slice: y / dout / dy hold B images out of the count_B the sums were taken over, so a
- * layer's backward can be cut into pieces that pipeline with the weight-gradient GEMM consuming dy. */
-extern "C" int b200dp_bn_relu_pool_bwd_apply_part(const void* y, const void* dout, const float* mean,
-                                                  const float* invstd, const float* gamma, const float* beta,
-                                                  const float* sums, void* dy, float* dgamma, float* dbeta, int B,
-                                                  int H, int W, int C, int pool, int count_B, int dtype,
-                                                  b200dp_stream_t s) {
-  if (count_B < B) {
-    set_error("bn_relu_pool_bwd_apply_part: count_B=%d is smaller than the slice B=%d", count_B, B);
-    return B200DP_EINVAL;
-  }
-  BnBwdParams p{y, dout, mean, invstd, gamma, beta, const_cast<float*>(sums), dy, dgamma, dbeta, B, H, W, C, pool};
-  p.count_B = count_B;
   return launch_bn_bwd_dt(dtype, true, p, static_cast<cudaStream_t>(s));
 }
 extern "C" int b200dp_bn_relu_pool_bwd_apply(const void* y, const void* dout, const float* mean,
@@ -1695,11 +1719,12 @@ static int head_fwd_bwd_impl(const void* x, const float* w, const float* bias, c
                              float* loss, int* correct, float* dlogits, void* dx, float* dw, float* db, int B, int F,
                              int O, float grad_scale, cudaStream_t s) {
   const int blocks = (B + kHeadWarps - 1) / kHeadWarps;
-  const size_t smem = (static_cast<size_t>(kHeadWarps) * F + kHeadWarps * kLinMaxO) * sizeof(float);
+  const size_t smem = (static_cast<size_t>(O + kHeadWarps) * F + kHeadWarps * kLinMaxO) * sizeof(float);
   static bool configured = false;
   if (!configured) {
     B200DP_CUDA_TRY(cudaFuncSetAttribute(head_fwd_bwd_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         static_cast<int>((kHeadWarps * 2048 + kHeadWarps * kLinMaxO) * sizeof(float))));
+                                         static_cast<int>(((kLinMaxO + kHeadWarps) * 2048 + kHeadWarps * kLinMaxO) *
+                                                          sizeof(float))));
     configured = true;
   }
   B200DP_CUDA_TRY(launch_pdl(head_fwd_bwd_kernel<T>, dim3(blocks), dim3(kHeadWarps * 32), smem, s,
@@ -1712,7 +1737,7 @@ static int head_fwd_bwd_impl(const void* x, const float* w, const float* bias, c
  * top-1 count into *correct, dlogits (may be NULL), dx = dlogits W (activation type), and
  * dw += dlogits^T x, db += sum dlogits (dw / db must be zero or hold the value to accumulate onto --
  * unlike b200dp_linear_bwd this entry point does not clear them).  F % 8 == 0, F <= 2048, O <= 16,
- * B <= 4096.  Launches on one stream only (it keeps its block counter in a device global). */
+ * B <= 4096, x / dx / w / dw 16-byte aligned.  Launches on one stream only (it keeps its block counter in a device global). */
 extern "C" int b200dp_head_fwd_bwd_ex(const void* x, const float* w, const float* bias, const long long* target,
                                       float* logits, float* loss, int* correct, float* dlogits, void* dx, float* dw,
                                       float* db, int B, int F, int O, float grad_scale, int dtype, b200dp_stream_t s) {

@@ -158,13 +158,6 @@ int b200dp_bn_relu_pool_bwd_apply_ex(const void* y, const void* dout, const floa
                                      const float* gamma, const float* beta, const float* sums, void* dy,
                                      float* dgamma, float* dbeta, int B, int H, int W, int C, int pool, int dtype,
                                      b200dp_stream_t stream);
-/* The apply pass on a batch slice: y / dout / dy hold B images of the count_B (>= B) images the sums and the
- * statistics were taken over.  Lets a block's backward be cut into pieces that pipeline with the weight-gradient
- * GEMM that consumes dy.  dgamma / dbeta are rewritten with the same values by every piece. */
-int b200dp_bn_relu_pool_bwd_apply_part(const void* y, const void* dout, const float* mean, const float* invstd,
-                                       const float* gamma, const float* beta, const float* sums, void* dy,
-                                       float* dgamma, float* dbeta, int B, int H, int W, int C, int pool, int count_B,
-                                       int dtype, b200dp_stream_t stream);
 int b200dp_bn_relu_pool_fwd_tma_ex(const void* y, const float* stats, const float* gamma, const float* beta,
                                    float* running_mean, float* running_var, long long* num_batches_tracked,
                                    float* save_mean, float* save_invstd, void* out, int B, int H, int W, int C,

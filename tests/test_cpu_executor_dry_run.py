@@ -88,10 +88,9 @@ def _step(nv, batch=8):
     nv.backward()
 
 
-# statistics clear, gradient-buffer clear (issued beside the forward pass on the side stream), layers
-FWD = ["fill_zero", "fill_zero", "im2col3x3_c3"] + ["conv_igemm", "bn_relu_pool_fwd"] * 8 + ["linear_fwd"]
-EVAL_FWD = FWD[2:]          # nothing is cleared for an evaluation forward
-HEAD = ["cross_entropy", "linear_bwd"]      # loss, classifier backward
+FWD = ["fill_zero", "im2col3x3_c3"] + ["conv_igemm", "bn_relu_pool_fwd"] * 8 + ["linear_fwd"]
+EVAL_FWD = FWD[1:]          # the statistics region is only cleared for a training forward
+HEAD = ["cross_entropy", "fill_zero", "linear_bwd"]      # loss, gradient-buffer clear, classifier backward
 
 
 def test_default_step_issues_the_measured_kernel_sequence(executor):
@@ -99,8 +98,8 @@ def test_default_step_issues_the_measured_kernel_sequence(executor):
     _step(nv)
     names = rec.names()
     assert names[: len(FWD)] == FWD
-    assert names[len(FWD): len(FWD) + 2] == HEAD
-    bwd = rec.calls[len(FWD) + 2:]
+    assert names[len(FWD): len(FWD) + 3] == HEAD
+    bwd = rec.calls[len(FWD) + 3:]
     # per block, deepest first: BN backward, data gradient fused with the BN reduction of the block below (not
     # for block 0), weight gradient
     expect = []
@@ -143,9 +142,9 @@ def test_fused_head_replaces_exactly_the_three_head_kernels(executor):
     _step(nv)
     names = rec.names()
     assert names[: len(FWD) - 1] == FWD[:-1]                      # no linear_fwd at the end of forward
-    assert names[len(FWD) - 1] == "head_fwd_bwd"
+    assert names[len(FWD) - 1: len(FWD) + 1] == ["fill_zero", "head_fwd_bwd"]
     assert "linear_fwd" not in names and "cross_entropy" not in names and "linear_bwd" not in names
-    assert names[len(FWD)] == "bn_relu_pool_bwd"
+    assert names[len(FWD) + 1] == "bn_relu_pool_bwd"
     # an external dlogits (autograd path) still runs the fc backward, and eval still computes logits
     rec.calls.clear()
     nv.forward(torch.randn(8, 3, 32, 32), training=True)

@@ -455,7 +455,7 @@ class NativeVGG:
             fused = training and self.conv_stats_fused
             x_in = b.x_in[:B]
             if b.first:
-                K.im2col3x3_c3(x.contiguous(), x_in)
+                K.im2col3x3_c3(x.contiguous(), x_in, upper_half_zeroed=True)   # x_in is allocated as zeros
             K.conv_igemm(x_in, b.wf, b.bias, y, stats=b.stats if fused else None, taps=b.taps,
                          block_n=b.fwd_block_n, split_k=b.fwd_split_k, cta_pair=self._pair_ok(b.fwd_pair, B, s.hw),
                          workspace=self.splitk_ws)

@@ -48,6 +48,7 @@ _PROTOTYPES = {
     "b200dp_head_fwd_bwd": [P, P, P, P, P, P, P, P, P, P, P, I, I, I, F, P],
     "b200dp_sgd_momentum": [P, P, P, LL, F, F, F, F, P],
     "b200dp_im2col3x3_c3_ex": [P, P, I, I, I, I, P],
+    "b200dp_im2col3x3_c3_ex2": [P, P, I, I, I, I, I, P],
     "b200dp_bn_stats_ex": [P, P, LL, I, I, P],
     "b200dp_bn_relu_pool_fwd_ex": [P, P, P, P, P, P, P, P, P, P, I, I, I, I, I, I, F, F, I, P],
     "b200dp_bn_relu_pool_bwd_reduce_ex": [P, P, P, P, P, P, P, I, I, I, I, I, I, P],

@@ -113,13 +113,14 @@ def conv_wgrad_push(dy: torch.Tensor, x: torch.Tensor, dw: torch.Tensor, *, coun
     return dw
 
 
-def im2col3x3_c3(x_nchw: torch.Tensor, a0: torch.Tensor) -> torch.Tensor:
-    """Layer-0 patch gather: bf16 rows of 64 columns or fp32 rows of 32 columns (27 real ones either way)."""
+def im2col3x3_c3(x_nchw: torch.Tensor, a0: torch.Tensor, upper_half_zeroed: bool = False) -> torch.Tensor:
+    """Layer-0 patch gather: bf16 rows of 64 columns or fp32 rows of 32 columns (27 real ones either way).
+    ``upper_half_zeroed``: columns 32..63 of the bf16 matrix already hold their zeros and are not rewritten."""
     _chk(x_nchw, torch.float32, "x")
     dt = _act_dtype(a0, "a0")
     B, C, H, W = x_nchw.shape
     assert C == 3 and a0.numel() == B * H * W * (32 if dt else 64)
-    call("b200dp_im2col3x3_c3_ex", ptr(x_nchw), ptr(a0), B, H, W, dt, stream_ptr())
+    call("b200dp_im2col3x3_c3_ex2", ptr(x_nchw), ptr(a0), B, H, W, dt, int(upper_half_zeroed), stream_ptr())
     return a0
 
 

@@ -1374,23 +1374,16 @@ static int conv_wgrad_impl(const void* dy, const void* x, float* dw, int B, int 
     pp.stage_base = push->stage_base;
     for (int r = 0; r < 8; ++r)
       pp.peer_stage[r] = r < push->world ? static_cast<float*>(push->peer_stage[r]) : nullptr;
-    if (block_n == 256) return launch_wgrad_push<256, 3>(tmDY, tmX, pp, tiles, split_k, stream);
-    if (block_n == 128) return launch_wgrad_push<128, 3>(tmDY, tmX, pp, tiles, split_k, stream);
-    return launch_wgrad_push<64, 4>(tmDY, tmX, pp, tiles, split_k, stream);
+    if (block_n == 256) return launch_wgrad_push<256, 4>(tmDY, tmX, pp, tiles, split_k, stream);
+    if (block_n == 128) return launch_wgrad_push<128, 6>(tmDY, tmX, pp, tiles, split_k, stream);
+    return launch_wgrad_push<64, 8>(tmDY, tmX, pp, tiles, split_k, stream);
   }
-  static const bool deep = [] {   // measurement toggle of the current A/B: pipeline depth that fills the 227 KB
-    const char* e = getenv("B200DP_EXP_WGRAD_DEEP");
-    return e != nullptr && e[0] == '1';
-  }();
-  if (deep) {
-    if (block_n == 256) return launch_wgrad<Prec, 256, 4>(tmDY, tmX, p, tiles, split_k, stream);
-    if (block_n == 128) return launch_wgrad<Prec, 128, 6>(tmDY, tmX, p, tiles, split_k, stream);
-    if (block_n == 64) return launch_wgrad<Prec, 64, 8>(tmDY, tmX, p, tiles, split_k, stream);
-  }
-  if (block_n == 256) return launch_wgrad<Prec, 256, 3>(tmDY, tmX, p, tiles, split_k, stream);
-  if (block_n == 128) return launch_wgrad<Prec, 128, 3>(tmDY, tmX, p, tiles, split_k, stream);
-  if (block_n == 64) return launch_wgrad<Prec, 64, 4>(tmDY, tmX, p, tiles, split_k, stream);
-  if constexpr (Prec::kTf32) return launch_wgrad<Prec, 32, 4>(tmDY, tmX, p, tiles, split_k, stream);
+  // one CTA per SM: the pipeline takes all of the shared memory (8 / 6 / 4 stages = 192 KB); with the 3-4 stage
+  // pipelines of round 1 the step was 10 us slower (latency-bound split-K slices, profiles/round2/ab_results.md)
+  if (block_n == 256) return launch_wgrad<Prec, 256, 4>(tmDY, tmX, p, tiles, split_k, stream);
+  if (block_n == 128) return launch_wgrad<Prec, 128, 6>(tmDY, tmX, p, tiles, split_k, stream);
+  if (block_n == 64) return launch_wgrad<Prec, 64, 8>(tmDY, tmX, p, tiles, split_k, stream);
+  if constexpr (Prec::kTf32) return launch_wgrad<Prec, 32, 8>(tmDY, tmX, p, tiles, split_k, stream);
   set_error("conv_wgrad: Cin=%d needs a 32-wide tile, which only the tf32 kernel has", Cin);
   return B200DP_EINVAL;
 }

@@ -118,13 +118,15 @@ constexpr int kIm2colRows = 4;
 // blockDim is a multiple of 8, so a thread emits the same 16-byte chunk of every patch row it touches: the
 // (tap, channel) -> window offset decode of its 8 columns is done once, outside the pixel loop; the upper
 // half of the row (columns 32..63) is a constant zero store.
-template <class T, int KP>
+// KW: columns written per row.  KW < KP leaves columns KW..KP-1 alone -- they are zero in every step, so a caller
+// that owns a persistent, zero-initialised matrix only pays for the 32 columns that carry data.
+template <class T, int KP, int KW>
 __global__ void __launch_bounds__(256) im2col_c3_v2_kernel(const float* __restrict__ x, T* __restrict__ a0, int B,
                                                            int H, int W) {
   pdl_launch_dependents();
   pdl_wait();
   extern __shared__ float win[];  // [rows + 2][3 channels][W + 2]
-  constexpr int kChunks = KP / 8;   // 16-byte-aligned groups of 8 columns per patch row (KP = 64 bf16 / 32 fp32)
+  constexpr int kChunks = KW / 8;   // 16-byte-aligned groups of 8 columns per patch row (KP = 64 bf16 / 32 fp32)
   const int Wp = W + 2;
   const int groups = (H + kIm2colRows - 1) / kIm2colRows;
   const int n = blockIdx.x / groups, h0 = (blockIdx.x - n * groups) * kIm2colRows;
@@ -1424,18 +1426,26 @@ static inline int grid_for(long work_items, int threads, int max_blocks = 148 * 
 
 using namespace b200dp;
 
-/* dtype 0: bf16 patch rows of 64 columns; dtype 1: fp32 patch rows of 32 columns (27 real columns either way). */
-extern "C" int b200dp_im2col3x3_c3_ex(const float* x_nchw, void* a0, int B, int H, int W, int dtype,
-                                      b200dp_stream_t s) {
+/* dtype 0: bf16 patch rows of 64 columns; dtype 1: fp32 patch rows of 32 columns (27 real columns either way).
+ * flags bit 0: the zero half of the bf16 rows (columns 32..63) is already zero in a0 and is not rewritten. */
+extern "C" int b200dp_im2col3x3_c3_ex2(const float* x_nchw, void* a0, int B, int H, int W, int dtype, int flags,
+                                       b200dp_stream_t s) {
   const size_t smem = (kIm2colRows + 2) * 3 * (W + 2) * sizeof(float);
   const int groups = (H + kIm2colRows - 1) / kIm2colRows;
   if (dtype == 1)
-    B200DP_CUDA_TRY(launch_pdl(im2col_c3_v2_kernel<float, 32>, dim3(B * groups), dim3(256), smem,
+    B200DP_CUDA_TRY(launch_pdl(im2col_c3_v2_kernel<float, 32, 32>, dim3(B * groups), dim3(256), smem,
                                static_cast<cudaStream_t>(s), x_nchw, static_cast<float*>(a0), B, H, W));
+  else if (flags & 1)
+    B200DP_CUDA_TRY(launch_pdl(im2col_c3_v2_kernel<__nv_bfloat16, 64, 32>, dim3(B * groups), dim3(256), smem,
+                               static_cast<cudaStream_t>(s), x_nchw, static_cast<__nv_bfloat16*>(a0), B, H, W));
   else
-    B200DP_CUDA_TRY(launch_pdl(im2col_c3_v2_kernel<__nv_bfloat16, 64>, dim3(B * groups), dim3(256), smem,
+    B200DP_CUDA_TRY(launch_pdl(im2col_c3_v2_kernel<__nv_bfloat16, 64, 64>, dim3(B * groups), dim3(256), smem,
                                static_cast<cudaStream_t>(s), x_nchw, static_cast<__nv_bfloat16*>(a0), B, H, W));
   return 0;
+}
+extern "C" int b200dp_im2col3x3_c3_ex(const float* x_nchw, void* a0, int B, int H, int W, int dtype,
+                                      b200dp_stream_t s) {
+  return b200dp_im2col3x3_c3_ex2(x_nchw, a0, B, H, W, dtype, 0, s);
 }
 extern "C" int b200dp_im2col3x3_c3(const float* x_nchw, void* a0, int B, int H, int W, b200dp_stream_t s) {
   return b200dp_im2col3x3_c3_ex(x_nchw, a0, B, H, W, 0, s);

@@ -143,6 +143,10 @@ int b200dp_im2col3x3_c3(const float* x_nchw, void* a0, int B, int H, int W, b200
  * activations (the tf32 arm; im2col then writes 32-column patch rows).  Parameters, statistics and gradients of
  * parameters are fp32 either way.  (ref: the fp32 model of master/part1/model.py:16-25,40-46) */
 int b200dp_im2col3x3_c3_ex(const float* x_nchw, void* a0, int B, int H, int W, int dtype, b200dp_stream_t stream);
+/* flags bit 0 (bf16 only): columns 32..63 of a0 are already zero (they are zero in every step) and are left alone,
+ * which halves the bytes written -- for a caller that owns a persistent zero-initialised patch matrix. */
+int b200dp_im2col3x3_c3_ex2(const float* x_nchw, void* a0, int B, int H, int W, int dtype, int flags,
+                            b200dp_stream_t stream);
 int b200dp_bn_stats_ex(const void* y, float* stats, long long P, int C, int dtype, b200dp_stream_t stream);
 int b200dp_bn_relu_pool_fwd_ex(const void* y, const float* stats, const float* gamma, const float* beta,
                                float* running_mean, float* running_var, long long* num_batches_tracked,

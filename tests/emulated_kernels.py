@@ -39,7 +39,7 @@ class EmulatedKernels:
         dst1.view(-1)[: src1.numel()].copy_(src1.view(-1))
 
     # ---- layer 0 patch gather --------------------------------------------------------------------
-    def im2col3x3_c3(self, x_nchw, a0):
+    def im2col3x3_c3(self, x_nchw, a0, upper_half_zeroed=False):
         self._log("im2col3x3_c3")
         B, C, H, W = x_nchw.shape
         xp = F.pad(x_nchw.float(), (1, 1, 1, 1))

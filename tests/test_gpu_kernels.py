@@ -113,6 +113,22 @@ def test_conv_wgrad(shape, split_k):
     assert err < 2e-3, f"conv wgrad rel err {err}"
 
 
+def test_im2col_that_leaves_the_zero_half_alone():
+    """``upper_half_zeroed``: only columns 0..31 of the bf16 patch rows are written (the executor's matrix is
+    allocated as zeros and columns 32..63 never change)."""
+    native = _native()
+    B, H, W = 5, 32, 32
+    g = torch.Generator(device=DEV).manual_seed(14)
+    x = torch.randn(B, 3, H, W, device=DEV, generator=g)
+    full = torch.empty(B, H, W, 64, device=DEV, dtype=torch.bfloat16)
+    native.im2col3x3_c3(x, full)
+    lo = torch.full((B, H, W, 64), 7.0, device=DEV, dtype=torch.bfloat16)
+    native.im2col3x3_c3(x, lo, upper_half_zeroed=True)
+    torch.cuda.synchronize()
+    assert torch.equal(lo[..., :32], full[..., :32])
+    assert bool((lo[..., 32:] == 7.0).all())          # untouched
+
+
 def test_layer0_as_gemm():
     """3-channel first conv = patch gather + K=64 GEMM; its wgrad writes only the 27 real columns."""
     native = _native()

@@ -54,7 +54,7 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--test-size", type=int, default=10000)
     p.add_argument("--real-data", action="store_true", help="train on ../../data/cifar-10-batches-py (an error if it is missing)")
     p.add_argument("--no-augment", action="store_true")
-    p.add_argument("--loader", choices=("python", "native"), default="python",
+    p.add_argument("--loader", choices=("auto", "python", "native"), default="auto",
                    help="batch assembly: vectorised torch ops, or the C++ thread pool of csrc/loader.cpp")
     p.add_argument("--loader-threads", type=int, default=4)
     p.add_argument("--no-eval", action="store_true")

@@ -44,7 +44,7 @@ class TrainConfig:
     # batch assembly for Trainer.fit: "python" = vectorised torch ops (data.BatchPipeline, ~20 k images/s),
     # "native" = C++ threads (csrc/loader.cpp, > 300 k images/s per thread); same sampling, different
     # augmentation draws
-    loader: str = "python"
+    loader: str = "auto"          # native next to a GPU (native backend), python with the torch/gloo backend
     loader_threads: int = 4
     cpu_threads: int = 4        # ref: master/part2a/part2a.py:18
     data_root: str = "../../data"
@@ -101,8 +101,8 @@ class TrainConfig:
             raise ValueError(f"sync_impl must be one of {tuple(SYNC_IMPLS)}, got {self.sync_impl!r}")
         if self.dtype not in ("bf16", "tf32"):
             raise ValueError(f"dtype must be 'bf16' or 'tf32', got {self.dtype!r}")
-        if self.loader not in ("python", "native"):
-            raise ValueError(f"loader must be 'python' or 'native', got {self.loader!r}")
+        if self.loader not in ("auto", "python", "native"):
+            raise ValueError(f"loader must be 'auto', 'python' or 'native', got {self.loader!r}")
         if self.port is None:
             self.port = REFERENCE_PORTS[self.mode]
         if self.per_rank_batch is None:

@@ -8,6 +8,10 @@ RUN="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-add
 if [ "$2" = "tests" ]; then
   timeout 1500 python -m pytest tests/test_multigpu_native.py -m gpu -q --timeout 900 2>&1 | tail -15 > $OUT/tests.log
   cat $OUT/tests.log
+elif [ "$2" = "sometests" ]; then      # the expensive world sizes: what the last kernel changes can reach
+  timeout 900 python -m pytest tests/test_multigpu_native.py tests/test_gpu_fused_paths.py -m "gpu and multigpu" -q --timeout 600 \
+      -k "push or resume or selfcheck or synced_gradient" 2>&1 | tail -15 > $OUT/tests.log
+  cat $OUT/tests.log
 fi
 timeout 600 $RUN bench.py --gpus $N --steps 100 --warmup 5 2>&1 | grep "^{" > $OUT/native.json
 timeout 600 $RUN bench.py --gpus $N --steps 100 --warmup 5 --impl reference 2>&1 | grep "^{" > $OUT/reference.json
@@ -23,13 +27,16 @@ for name in ("native", "reference"):
     except Exception as e:
         print(name, "FAILED", e)
 PY
-ab() { v=$(timeout 300 $RUN bench.py --gpus $N --steps 100 --no-e2e --no-strong --no-tf32 --no-selfcheck "$@" 2>&1 | grep "^{" | python -c "import json,sys; r=json.loads(sys.stdin.read()); print(round(r['ms_per_step'],4), round(r.get('exposed_comm_fraction',0),4))"); echo "  [$*] $v" | tee -a $OUT/ab.log; }
+timeout 300 $RUN scripts/timeline_step.py --mode part3 --out $OUT/timeline_part3 > $OUT/timeline_part3.log 2>&1
+rm -f $OUT/timeline_part3.json
+ab() { v=$(timeout 300 $RUN bench.py --gpus $N --steps 100 --no-e2e --no-strong --no-tf32 --no-selfcheck --no-loader "$@" 2>&1 | grep "^{" | python -c "import json,sys; r=json.loads(sys.stdin.read()); print(round(r['ms_per_step'],4), round(r.get('exposed_comm_fraction',0),4))"); echo "  [${LABEL}$*] $v" | tee -a $OUT/ab.log; }
 ab
-ab --bucket-plan cap:9
 ab --bucket-plan cap:16
 ab --bucket-plan layer
-ab --comm-blocks 24
 ab --comm-blocks 48
-ab --mode part2b
-ab --mode part2a
-ab --mode part2a_extra
+LABEL="wgrad-push " B200DP_WGRAD_PUSH=1 ab --bucket-plan layer
+if [ "$3" = "modes" ]; then
+  ab --mode part2b
+  ab --mode part2a
+  ab --mode part2a_extra
+fi

@@ -19,7 +19,6 @@ The kernel schedule replaces what the reference gets from ``model(data)`` /
 """
 from __future__ import annotations
 
-import contextlib
 import os
 from dataclasses import dataclass
 from typing import Callable, Dict, List, Optional, Sequence, Tuple
@@ -30,7 +29,6 @@ import torch.nn as nn
 from ..ops import native as K
 
 # weight gradients on a second stream, concurrently with the dgrad / BatchNorm-backward chain
-WGRAD_ON_SIDE_STREAM = os.environ.get("B200DP_WGRAD_STREAM", "1") != "0"
 
 ALIGN = 4  # floats; every tensor starts on a 16-byte boundary inside the flat buffers
 
@@ -501,7 +499,7 @@ class NativeVGG:
         dl = self.dlogits[:B] if dlogits is None else dlogits
         last = self.blocks[-1]
         main = torch.cuda.current_stream()
-        side = self._wgrad_stream if WGRAD_ON_SIDE_STREAM else None
+        side = self._wgrad_stream
         if self._head_done and dlogits is None:
             self._head_done = False     # the fused head already cleared the gradients and ran the fc backward
         else:
@@ -521,8 +519,7 @@ class NativeVGG:
             # wgrad(i) and dgrad(i) both only read dy(i) and are independent: the weight gradient goes to
             # a second stream so that it runs next to the data-gradient chain (each of these GEMMs keeps
             # the tensor pipe ~40% busy on its own).  The bucket-ready signal is recorded on that stream.
-            if side is not None:
-                self._wgrad_fork[i].record(main)
+            self._wgrad_fork[i].record(main)
             if i > 0:
                 # the dgrad epilogue also accumulates the BatchNorm-backward sums of the block below,
                 # which then skips its own reduction pass
@@ -532,9 +529,8 @@ class NativeVGG:
                                        cta_pair=self._pair_ok(b.dgrad_pair, B, s.hw), workspace=self.splitk_ws)
                 reduced = True
             self._dgrad_done[i].record(main)   # after this the layer's bf16 weight copies may be rewritten
-            if side is not None:
-                side.wait_event(self._wgrad_fork[i])
-            with torch.cuda.stream(side) if side is not None else contextlib.nullcontext():
+            side.wait_event(self._wgrad_fork[i])
+            with torch.cuda.stream(side):
                 if self.wgrad_push is not None and i in self.wgrad_push:
                     # experimental: GEMM + transfer half of the reduce-scatter in one kernel
                     K.conv_wgrad_push(b.dy[:B], b.x_in[:B], b.g_w, split_k=b.wgrad_split_k, block_n=b.wgrad_block_n,
@@ -545,9 +541,8 @@ class NativeVGG:
                 if self.on_bucket_ready is not None:
                     for k in self._bucket_of_block.get(i, ()):
                         self.on_bucket_ready(k)
-        if side is not None:
-            self._wgrad_join.record(side)
-            main.wait_event(self._wgrad_join)
+        self._wgrad_join.record(side)
+        main.wait_event(self._wgrad_join)
 
     # ------------------------------------------------------------------ torch.autograd bridge
     def autograd_forward(self, x: torch.Tensor, training: bool) -> torch.Tensor:

@@ -88,8 +88,7 @@ class LocalSGD(NativeSync):
 
     def __init__(self, *a, overlap: bool = True, **kw):
         super().__init__(*a, **kw)
-        from ..models.native_vgg import WGRAD_ON_SIDE_STREAM
-        self.overlap = bool(overlap) and WGRAD_ON_SIDE_STREAM
+        self.overlap = bool(overlap)
         nv = self.native
         if self.overlap:
             self.buckets = nv.layout.buckets("layer")

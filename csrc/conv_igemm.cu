@@ -57,7 +57,6 @@ struct IgemmParams {
   int kb_per_split;
   // 1: the four epilogue warps combine their statistics in shared memory (the drained stage-0 operand
   // buffer) and issue one atomic per channel per CTA instead of one per warp (B200DP_STATS_SMEM=0: off)
-  int stats_via_smem;
   // dgrad only (conv_dgrad_bnr kernels): the tile just computed is dL/da for a = relu(bn(z)) of the
   // PREVIOUS block (max-pooled or not).  With `bnr_a` = that block's stored output, the epilogue also
   // accumulates its BatchNorm-backward sums  S1 = sum_{a>0} g,  S2 = sum_{a>0} g*(a-beta)/gamma  into
@@ -235,15 +234,10 @@ B200DP_DEVINL void igemm_epilogue(const IgemmParams& p, uint32_t tmem_base, uint
       }
       const float t1 = warp_transpose_sum(f, lane);
       const float t2 = warp_transpose_sum(s2, lane);
-      if (p.stats_via_smem) {
-        // scratch is operand memory: every MMA that read it has completed (tmem_full_bar fired)
-        scratch[q * 2 * BLOCK_N + c + lane] = t1;
-        scratch[q * 2 * BLOCK_N + BLOCK_N + c + lane] = t2;
-      } else {
-        const int ch = n_tile * BLOCK_N + c + lane;
-        atomicAdd(p.stats + ch, t1);
-        atomicAdd(p.stats + p.n_total + ch, t2);
-      }
+      // combined across the epilogue warps in shared memory below: one atomic per channel per CTA.  scratch is
+      // operand memory: every MMA that read it has completed (tmem_full_bar fired)
+      scratch[q * 2 * BLOCK_N + c + lane] = t1;
+      scratch[q * 2 * BLOCK_N + BLOCK_N + c + lane] = t2;
     }
   }
   if constexpr (BNR) {
@@ -255,7 +249,7 @@ B200DP_DEVINL void igemm_epilogue(const IgemmParams& p, uint32_t tmem_base, uint
         atomicAdd(p.bnr_sums + half * p.n_total + n_tile * BLOCK_N + (i - half * BLOCK_N), t);
       }
     }
-  } else if (p.partial == nullptr && p.stats != nullptr && p.stats_via_smem) {
+  } else if (p.partial == nullptr && p.stats != nullptr) {
     asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory");  // the epilogue warps only
     for (int i = static_cast<int>(threadIdx.x) - 64; i < 2 * BLOCK_N; i += kEpiThreads) {
       const float t = scratch[i] + scratch[2 * BLOCK_N + i] + scratch[4 * BLOCK_N + i] + scratch[6 * BLOCK_N + i];
@@ -980,15 +974,6 @@ static int tile_geometry(int H, int W, int pixels_per_tile, int* TH, int* TN) {
   return 0;
 }
 
-// B200DP_IGEMM_SHORTK=0 keeps single-K-block GEMMs on the 4-stage kernel (A/B runs).
-static bool short_k_enabled() {
-  static const bool on = [] {
-    const char* e = getenv("B200DP_IGEMM_SHORTK");
-    return e == nullptr || e[0] != '0';
-  }();
-  return on;
-}
-
 template <class Prec, int BLOCK_N, int STAGES>
 static int launch_igemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const IgemmParams& p, int m_tiles,
                         int splits, cudaStream_t stream) {
@@ -1124,11 +1109,6 @@ static int conv_igemm_impl(const void* act, const void* wgt, const float* bias, 
   p.bias = bias;
   p.out = out;
   p.stats = stats;
-  static const bool stats_smem = [] {
-    const char* e = getenv("B200DP_STATS_SMEM");
-    return e == nullptr || e[0] != '0';
-  }();
-  p.stats_via_smem = stats_smem ? 1 : 0;
   const int m_tiles = (p.m_total + kBlockM - 1) / kBlockM;
   if (block_n == 0) {
     // largest N tile that still yields about one CTA per SM
@@ -1227,7 +1207,7 @@ static int conv_igemm_impl(const void* act, const void* wgt, const float* bias, 
     case 256: rc = launch_igemm<Prec, 256, 4>(tmA, tmB, p, m_tiles, split_k, stream); break;
     case 128: rc = launch_igemm<Prec, 128, 3>(tmA, tmB, p, m_tiles, split_k, stream); break;
     case 64:
-      rc = (p.kb_per_split == 1 && short_k_enabled()) ? launch_igemm<Prec, 64, 1>(tmA, tmB, p, m_tiles, split_k, stream)
+      rc = (p.kb_per_split == 1) ? launch_igemm<Prec, 64, 1>(tmA, tmB, p, m_tiles, split_k, stream)
                                                       : launch_igemm<Prec, 64, 4>(tmA, tmB, p, m_tiles, split_k, stream);
       break;
     case 32: rc = launch_igemm<Prec, 32, 4>(tmA, tmB, p, m_tiles, split_k, stream); break;

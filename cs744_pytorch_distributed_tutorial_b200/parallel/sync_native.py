@@ -33,7 +33,6 @@ from .comm import CH_AUX, CH_BUCKET, CH_MAIN, BucketReducer, Communicator
 class NativeSync:
     name = "none"
     syncs_buffers = False
-    handles_shadows = False   # True: the strategy refreshes the bf16 weight copies itself
 
     def __init__(self, native, comm: Optional[Communicator], lr: float, momentum: float, weight_decay: float,
                  fuse_optimizer: bool = True):
@@ -94,14 +93,11 @@ class LocalSGD(NativeSync):
             self.buckets = nv.layout.buckets("layer")
             nv.set_bucket_plan(self.buckets)
             nv.on_bucket_ready = self._bucket_ready
-            self.handles_shadows = True
             # phase 1 covers the buckets of the deepest blocks down to (and including) `first_block`
             n = len(nv.blocks)
             self.first_block = max(n - 5, 1)            # VGG-11: blocks 3..7 = 35.3 of 36.9 MB
             self.split_bucket = max(k for k in range(len(self.buckets)) if self.first_block in nv.blocks_of_bucket(k))
             self.split_end = self.buckets[self.split_bucket].end
-            self._prep_hi = K.BatchedWeightPrep([b.prep for b in nv.blocks[self.first_block:]])
-            self._prep_lo = K.BatchedWeightPrep([b.prep for b in nv.blocks[:self.first_block]])
             self._opt_stream = torch.cuda.Stream(nv.device)
             self._opt_fork, self._opt_join = torch.cuda.Event(), torch.cuda.Event()
             self._opt_pending = False
@@ -115,14 +111,12 @@ class LocalSGD(NativeSync):
         if k != self.split_bucket:
             return
         # called on the weight-gradient stream right after wgrad(first_block): every gradient of phase 1 exists.
-        # The data gradient of first_block is the last reader of the old bf16 copies of blocks >= first_block.
-        nv = self.native
+        # Only the fp32 master weights are written here; the operand copies that the rest of backward still reads
+        # are re-laid-out beside the next forward pass (NativeVGG.mark_shadows_stale).
         self._opt_fork.record(torch.cuda.current_stream())
         self._opt_stream.wait_event(self._opt_fork)
-        self._opt_stream.wait_event(nv._dgrad_done[self.first_block])
         with torch.cuda.stream(self._opt_stream):
             self._sgd_range(0, self.split_end)
-            self._prep_hi()
             self._opt_join.record(self._opt_stream)
         self._opt_pending = True
 
@@ -134,7 +128,6 @@ class LocalSGD(NativeSync):
             self._local_sgd()
             return
         self._sgd_range(self.split_end, self.n)
-        self._prep_lo()
         if self._opt_pending:
             torch.cuda.current_stream().wait_event(self._opt_join)
             self._opt_pending = False
@@ -195,7 +188,7 @@ class BucketedOverlapSync(NativeSync):
     name = "ddp_bucketed"
     syncs_buffers = True
 
-    def __init__(self, *a, bucket_plan: str = "cap:12", blocks: int = 32, **kw):
+    def __init__(self, *a, bucket_plan: str = "cap:16+last", blocks: int = 32, **kw):
         super().__init__(*a, **kw)
         nv = self.native
         self.buckets = nv.layout.buckets(bucket_plan)

@@ -1,12 +1,16 @@
 #!/bin/bash
-# temporary: validation + bench of the current build (1 GPU)
+# temporary: validation + A/B of the deferred weight re-layout and the "+last" bucket plans (2 GPUs)
 OUT=gpurun_out/exp; mkdir -p $OUT
-ms() { grep -o '"ms_per_step": [0-9.]*' | head -1 | cut -d' ' -f2; }
-B="python bench.py --steps 300 --warmup 20 --no-e2e --no-tf32 --no-strong --no-loader"
-timeout 900 python -m pytest tests -q -x -m "gpu and not multigpu" 2>&1 | tail -4
-for cfg in "" ""; do
-  v=$(env $cfg timeout 200 $B 2>$OUT/err.log | ms)
-  echo "  [${cfg:-default}] ms/step=$v" | tee -a $OUT/ab3.log
-done
-v=$(timeout 200 $B --dtype tf32 2>$OUT/err.log | ms); echo "  [tf32] ms/step=$v" | tee -a $OUT/ab3.log
-timeout 300 python scripts/timeline_step.py --mode part1 --out $OUT/timeline_part1 > $OUT/timeline_part1.log 2>&1; rm -f $OUT/timeline_part1.json
+N=2
+RUN="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29611"
+timeout 900 python -m pytest tests -q -x -m "gpu" --timeout 600 2>&1 | tail -4
+ms() { python -c "import json,sys; r=json.loads([l for l in sys.stdin.read().splitlines() if l.startswith('{')][-1]); print(round(r['ms_per_step'],4), round(r.get('exposed_comm_fraction',0),4))"; }
+v=$(CUDA_VISIBLE_DEVICES=0 timeout 200 python bench.py --steps 300 --warmup 20 --no-e2e --no-tf32 --no-strong --no-loader 2>$OUT/err.log | ms); echo "  [1 GPU] $v" | tee -a $OUT/ab4.log
+ab() { v=$(timeout 300 $RUN bench.py --gpus $N --steps 200 --no-e2e --no-strong --no-tf32 --no-selfcheck --no-loader "$@" 2>&1 | ms); echo "  [$*] $v" | tee -a $OUT/ab4.log; }
+ab
+ab --bucket-plan cap:16
+ab --bucket-plan cap:12+last
+ab --bucket-plan cap:12
+ab --bucket-plan layer
+ab
+timeout 300 $RUN scripts/timeline_step.py --mode part3 --out $OUT/timeline_part3_2gpu > $OUT/timeline_part3_2gpu.log 2>&1; rm -f $OUT/timeline_part3_2gpu.json

@@ -129,6 +129,13 @@ def test_flat_layout_and_bucket_plans():
     assert cap[0].start == 0 and cap[-1].end == L.total and all(a.end == b.start for a, b in zip(cap, cap[1:]))
     assert sorted(n for b in cap for n in b.names) == sorted(e.name for e in L.entries)
     assert len(L.buckets("cap:1000")) == 1 and len(L.buckets("cap:0.001")) == 8
+    # "+last": the first conv block (the last gradients of backward) in a bucket of its own -- a few KB
+    last = L.buckets("cap:16+last")
+    assert [round(b.nbytes / 1e6, 1) for b in last[:-1]] == [18.9, 17.7, 0.3] and last[-1].nbytes < 16384
+    assert last[-1].names == [e.name for e in L.entries[-4:]] and last[-1].end == L.total
+    assert all(a.end == b.start for a, b in zip(last, last[1:]))
+    assert sorted(n for b in last for n in b.names) == sorted(e.name for e in L.entries)
+    assert len(L.buckets("single+last")) == 2 and len(L.buckets("layer+last")) == 8
     with pytest.raises(ValueError):
         L.buckets("cap:x")
     with pytest.raises(ValueError):

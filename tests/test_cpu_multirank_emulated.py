@@ -127,8 +127,7 @@ def _run(emu, world, batches, bucket_plan="layer", mode="part3", fuse=True):
         for r in range(world):
             nv, s = fabric.execs[r], fabric.syncs[r]
             s.sync_and_step()
-            if not s.handles_shadows:
-                nv.refresh_shadows()
+            nv.mark_shadows_stale()
             s.pre_forward()
     return fabric
 

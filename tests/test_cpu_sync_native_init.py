@@ -76,7 +76,6 @@ def fake_native():
             nv._bucket_of_block.setdefault(min(blocks) if blocks else len(nv.blocks) - 1, []).append(bk.index)
     nv.set_bucket_plan = set_bucket_plan
     nv.blocks_of_bucket = lambda k: [i for i, ks in nv._bucket_of_block.items() if k in ks]
-    nv._dgrad_done = [object() for _ in nv.blocks]
     return nv
 
 
@@ -103,7 +102,7 @@ def _make(world, **kw):
 def test_default_part3_strategy_constructs_and_hands_buckets_to_the_reducer():
     nv, s = _make(2, bucket_plan="layer", blocks=32)
     assert len(s.buckets) == 8 and s.reducer.kw["blocks"] == 32
-    assert not s._wgrad_push and not s.handles_shadows
+    assert not s._wgrad_push
     assert nv.wgrad_push is None and s.reducer.staged is None
     nv.on_bucket_ready(3)
     assert s.reducer.ready == [3]
@@ -166,7 +165,7 @@ def test_local_sgd_two_phase_split_covers_all_parameters():
     nv._wgrad_stream = None
     s = sync_native.LocalSGD(nv, None, lr=0.1, momentum=0.9, weight_decay=1e-4)
     if s.overlap:
-        assert 0 < s.split_end < nv.layout.total and s.handles_shadows
+        assert 0 < s.split_end < nv.layout.total
         assert s.split_end == s.buckets[s.split_bucket].end
         big = sum(b.end - b.start for b in s.buckets[: s.split_bucket + 1])
         assert big / nv.layout.total > 0.9          # phase 1 carries the bulk of the bytes

@@ -249,7 +249,8 @@ def loader_e2e(tr, cfg, steps: int, threads: int, warm: int = 5) -> dict:
     pipe.close()
     ms = be.max_over_ranks(t0.elapsed_time(t1)) / n
     return {"value": cfg.global_batch / (ms * 1e-3), "unit": "images/s", "ms_per_step": ms, "steps": n,
-            "loader": f"csrc/loader.cpp, {threads} threads, RandomCrop(32,4)+flip+normalise, pinned ring",
+            "loader": f"csrc/loader.cpp, {threads} threads per rank, RandomCrop(32,4)+flip+normalise, pinned ring",
+            "host_cpus": os.cpu_count(),
             "last_loss": last}
 
 

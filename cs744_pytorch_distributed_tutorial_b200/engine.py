@@ -230,7 +230,8 @@ class NativeBackend:
             nv.backward()
         with nvtx_range("b200dp.sync_and_step"):
             self.sync.sync_and_step()
-            nv.mark_shadows_stale()      # re-laid-out beside the next forward pass, not at the tail of this step
+            if not self.sync.handles_shadows:
+                nv.refresh_shadows()
             # within a captured step the auxiliary stream must be joined before the capture ends
             self.sync.pre_forward()
 
@@ -249,7 +250,6 @@ class NativeBackend:
         from .ops import _lib
         self.graph = torch.cuda.CUDAGraph()
         n0 = _lib.launch_count
-        nv.mark_shadows_stale()          # the captured step must contain the re-layout of the operand copies
         with torch.cuda.graph(self.graph):
             self._step_body()
         self.launches_per_step = _lib.launch_count - n0
@@ -281,7 +281,6 @@ class NativeBackend:
         self._slot_free[slot].record(cur)
         if self.graph is not None:
             self.graph.replay()
-            self.native.mark_shadows_stale()     # the replay ended with an optimizer step (python flag only)
         else:
             self._step_body()
         self.steps_done += 1
@@ -305,7 +304,8 @@ class NativeBackend:
         nv.loss_fwd_bwd(y)
         nv.backward()
         self.sync.sync_and_step()
-        nv.mark_shadows_stale()
+        if not self.sync.handles_shadows:
+            nv.refresh_shadows()
         self.sync.pre_forward()
         self.steps_done += 1
         return nv.loss

@@ -245,11 +245,8 @@ class NativeVGG:
         self._wgrad_stream = torch.cuda.Stream(dev)
         self._wgrad_fork = [torch.cuda.Event() for _ in self.specs]
         self._wgrad_join = torch.cuda.Event()
-        self._prep_fork = torch.cuda.Event()
-        self._prep_done = [torch.cuda.Event(), torch.cuda.Event()]
-        self._prep_groups = None
-        self._prep_wait: Dict[int, object] = {}
-        self._shadows_stale = False
+        self._dgrad_done = [torch.cuda.Event() for _ in self.specs]
+        self._block_prep = None
         self._adopt_parameters()
         self._alloc_workspaces()
         self.refresh_shadows()
@@ -430,36 +427,18 @@ class NativeVGG:
 
     # ------------------------------------------------------------------ weight shadows
     def refresh_shadows(self) -> None:
-        """Operand copies of the fp32 master weights, now, on the current stream: Wf (forward) and Wd (dgrad)."""
+        """bf16 operand copies of the fp32 master weights: Wf (forward) and Wd (dgrad)."""
         if getattr(self, "_prep", None) is None:
             self._prep = K.BatchedWeightPrep([b.prep for b in self.blocks])
         self._prep()
-        self._shadows_stale = False
 
-    def mark_shadows_stale(self) -> None:
-        """The master weights changed (optimizer step): the next ``forward`` re-lays the operand copies out on the
-        weight-gradient stream, beside its first layers, instead of the optimizer doing it at the end of the step
-        where nothing can hide it."""
-        self._shadows_stale = True
-
-    def _refresh_beside_forward(self) -> None:
-        """Two launches on the idle weight-gradient stream: the small first blocks (needed at once), then the
-        deep blocks (35 of 37 MB for VGG-11, needed ~80 us into the forward pass).  ``forward`` waits for the
-        event of a group right before the first conv that reads it."""
-        if self._prep_groups is None:
-            split = max(len(self.blocks) - 5, 1)
-            self._prep_split = split
-            self._prep_groups = [K.BatchedWeightPrep([b.prep for b in part])
-                                 for part in (self.blocks[:split], self.blocks[split:]) if part]
-        cur, side = torch.cuda.current_stream(), self._wgrad_stream
-        self._prep_fork.record(cur)
-        side.wait_event(self._prep_fork)
-        with torch.cuda.stream(side):
-            for g, ev in zip(self._prep_groups, self._prep_done):
-                g()
-                ev.record(side)
-        self._prep_wait = {0: self._prep_done[0], self._prep_split: self._prep_done[1]}
-        self._shadows_stale = False
+    def prep_block(self, i: int) -> None:
+        """Refresh the bf16 weight copies of block ``i`` on the current stream, after the data gradient
+        of that block (the last reader of the old copies in this step) has finished."""
+        if self._block_prep is None:
+            self._block_prep = [K.BatchedWeightPrep([b.prep]) for b in self.blocks]
+        torch.cuda.current_stream().wait_event(self._dgrad_done[i])
+        self._block_prep[i]()
 
     def blocks_of_bucket(self, k: int) -> List[int]:
         return [i for i, ks in self._bucket_of_block.items() if k in ks]
@@ -477,19 +456,15 @@ class NativeVGG:
         if B > self.max_batch:
             raise ValueError(f"batch {B} exceeds the executor's max_batch {self.max_batch}")
         self._B = B
-        if self._shadows_stale:
-            self._refresh_beside_forward()
         if training:
             K.fill_zero(self.zero_region)
-        for i, b in enumerate(self.blocks):
+        for b in self.blocks:
             s = b.spec
             y = b.y[:B]
             fused = training and self.conv_stats_fused
             x_in = b.x_in[:B]
             if b.first:
                 K.im2col3x3_c3(x.contiguous(), x_in, upper_half_zeroed=True)   # x_in is allocated as zeros
-            if i in self._prep_wait:
-                torch.cuda.current_stream().wait_event(self._prep_wait.pop(i))
             K.conv_igemm(x_in, b.wf, b.bias, y, stats=b.stats if fused else None, taps=b.taps,
                          block_n=b.fwd_block_n, split_k=b.fwd_split_k, cta_pair=self._pair_ok(b.fwd_pair, B, s.hw),
                          workspace=self.splitk_ws)
@@ -564,6 +539,7 @@ class NativeVGG:
                                        block_n=b.dgrad_block_n, split_k=b.dgrad_split_k,
                                        cta_pair=self._pair_ok(b.dgrad_pair, B, s.hw), workspace=self.splitk_ws)
                 reduced = True
+            self._dgrad_done[i].record(main)   # after this the layer's bf16 weight copies may be rewritten
             side.wait_event(self._wgrad_fork[i])
             with torch.cuda.stream(side):
                 if self.wgrad_push is not None and i in self.wgrad_push:

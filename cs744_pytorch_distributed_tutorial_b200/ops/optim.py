@@ -35,7 +35,7 @@ class FusedSGD(torch.optim.Optimizer):
                     nv._view(nv.flat_grads, e).copy_(p.grad)
             nv.restore_grad_views()
         K.sgd_momentum(nv.flat_params, nv.flat_grads, nv.flat_momentum, g["lr"], g["momentum"], g["weight_decay"])
-        nv.mark_shadows_stale()
+        nv.refresh_shadows()
         return loss
 
     def zero_grad(self, set_to_none: bool = False) -> None:

@@ -33,6 +33,7 @@ from .comm import CH_AUX, CH_BUCKET, CH_MAIN, BucketReducer, Communicator
 class NativeSync:
     name = "none"
     syncs_buffers = False
+    handles_shadows = False   # True: the strategy refreshes the bf16 weight copies itself
 
     def __init__(self, native, comm: Optional[Communicator], lr: float, momentum: float, weight_decay: float,
                  fuse_optimizer: bool = True):
@@ -93,11 +94,14 @@ class LocalSGD(NativeSync):
             self.buckets = nv.layout.buckets("layer")
             nv.set_bucket_plan(self.buckets)
             nv.on_bucket_ready = self._bucket_ready
+            self.handles_shadows = True
             # phase 1 covers the buckets of the deepest blocks down to (and including) `first_block`
             n = len(nv.blocks)
             self.first_block = max(n - 5, 1)            # VGG-11: blocks 3..7 = 35.3 of 36.9 MB
             self.split_bucket = max(k for k in range(len(self.buckets)) if self.first_block in nv.blocks_of_bucket(k))
             self.split_end = self.buckets[self.split_bucket].end
+            self._prep_hi = K.BatchedWeightPrep([b.prep for b in nv.blocks[self.first_block:]])
+            self._prep_lo = K.BatchedWeightPrep([b.prep for b in nv.blocks[:self.first_block]])
             self._opt_stream = torch.cuda.Stream(nv.device)
             self._opt_fork, self._opt_join = torch.cuda.Event(), torch.cuda.Event()
             self._opt_pending = False
@@ -111,12 +115,14 @@ class LocalSGD(NativeSync):
         if k != self.split_bucket:
             return
         # called on the weight-gradient stream right after wgrad(first_block): every gradient of phase 1 exists.
-        # Only the fp32 master weights are written here; the operand copies that the rest of backward still reads
-        # are re-laid-out beside the next forward pass (NativeVGG.mark_shadows_stale).
+        # The data gradient of first_block is the last reader of the old bf16 copies of blocks >= first_block.
+        nv = self.native
         self._opt_fork.record(torch.cuda.current_stream())
         self._opt_stream.wait_event(self._opt_fork)
+        self._opt_stream.wait_event(nv._dgrad_done[self.first_block])
         with torch.cuda.stream(self._opt_stream):
             self._sgd_range(0, self.split_end)
+            self._prep_hi()
             self._opt_join.record(self._opt_stream)
         self._opt_pending = True
 
@@ -128,6 +134,7 @@ class LocalSGD(NativeSync):
             self._local_sgd()
             return
         self._sgd_range(self.split_end, self.n)
+        self._prep_lo()
         if self._opt_pending:
             torch.cuda.current_stream().wait_event(self._opt_join)
             self._opt_pending = False
@@ -212,6 +219,39 @@ class BucketedOverlapSync(NativeSync):
                             and self.world > 1 and self.world <= 8)
         if self._wgrad_push:
             self._setup_wgrad_push()
+        # The operand copies (Wf / Wd) of a bucket's layers are re-laid-out on a stream of their own as soon as the
+        # bucket's collective has finished, under the rest of backward, instead of in one pass at the tail of the
+        # step.  A bucket kernel must then end with its own exit barrier (peers' parameter stores have landed when
+        # it completes), so the reducer's lazy-exit mode is switched off: its cost sits on the reducer stream,
+        # which is off the critical path with few large buckets.
+        self._prep_overlap = (fuse and self.world > 1 and not self._wgrad_push
+                              and os.environ.get("B200DP_EXP_PREP_TAIL", "0") == "0")   # A/B toggle of this round
+        if self._prep_overlap:
+            self.handles_shadows = True
+            self.reducer.set_lazy_exit(False)
+            conv_block = {f"layers.{b.spec.conv_idx}.weight": i for i, b in enumerate(nv.blocks)}
+            self._blocks_in_bucket = [sorted(conv_block[n] for n in bk.names if n in conv_block) for bk in self.buckets]
+            self._bucket_prep = [K.BatchedWeightPrep([nv.blocks[i].prep for i in blks]) if blks else None
+                                 for blks in self._blocks_in_bucket]
+            self._prep_stream = torch.cuda.Stream(nv.device)
+            self._reducer_stream = self.reducer.stream(nv.device)
+            self._ar_done = [torch.cuda.Event() for _ in self.buckets]
+            self._prep_join = torch.cuda.Event()
+            nv.on_bucket_ready = self._bucket_ready
+
+    def _bucket_ready(self, k: int) -> None:
+        """Called on the weight-gradient stream right after the last weight gradient of bucket k was launched."""
+        nv = self.native
+        self.reducer.bucket_ready(k)
+        if self._bucket_prep[k] is None:
+            return
+        ps = self._prep_stream
+        self._ar_done[k].record(self._reducer_stream)
+        ps.wait_event(self._ar_done[k])
+        for i in self._blocks_in_bucket[k]:
+            ps.wait_event(nv._dgrad_done[i])      # the data gradient is the last reader of the old copies
+        with torch.cuda.stream(ps):
+            self._bucket_prep[k]()
 
     def _setup_wgrad_push(self) -> None:
         import ctypes
@@ -286,6 +326,9 @@ class BucketedOverlapSync(NativeSync):
         self.reducer.finalize()
         if not self.fuse_optimizer:
             self._local_sgd()
+        if self._prep_overlap:
+            self._prep_join.record(self._prep_stream)
+            torch.cuda.current_stream().wait_event(self._prep_join)
 
     def gather_optimizer_state(self) -> None:
         # per bucket, with the bucket's own slicing; the small (one-shot) buckets already hold identical

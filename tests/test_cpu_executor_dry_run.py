@@ -197,22 +197,12 @@ def test_engine_step_body_runs_end_to_end_in_dry_run(executor, monkeypatch):
     assert loss is be.native.loss and be.steps_done == 1
     assert names[0] == "copy_pair"                         # staged batch -> the step's static input buffers
     assert names[1: len(FWD)] == FWD[:-1] and names.count("head_fwd_bwd") == 1 and names.count("conv_wgrad") == 8
-    assert names.count("sgd_momentum") == 2                                        # two-phase optimizer
-    assert names.count("prep_conv_weights_batched") == 0 and be.native._shadows_stale    # re-layout is deferred ...
+    assert names.count("sgd_momentum") == 2 and names.count("prep_conv_weights_batched") == 2   # two-phase optimizer
     assert be.input_event() is not None
     # ragged last batch: same kernels, eager
     rec.calls.clear()
     be.train_step(torch.randn(5, 3, 32, 32), torch.randint(0, 10, (5,)))
-    names = rec.names()
-    assert names.count("conv_wgrad") == 8 and be.steps_done == 2
-    # ... to the start of the next forward pass: two groups, issued before the first layer's kernels
-    assert names.count("prep_conv_weights_batched") == 2
-    assert max(i for i, n in enumerate(names) if n == "prep_conv_weights_batched") < names.index("im2col3x3_c3")
-    # an evaluation forward after a training step refreshes the copies too, once
-    rec.calls.clear()
-    be.eval_batch(torch.randn(8, 3, 32, 32), torch.randint(0, 10, (8,)))
-    be.eval_batch(torch.randn(8, 3, 32, 32), torch.randint(0, 10, (8,)))
-    assert rec.names().count("prep_conv_weights_batched") == 2
+    assert rec.names().count("conv_wgrad") == 8 and be.steps_done == 2
 
 
 def test_engine_part3_two_rank_path_in_dry_run(executor, monkeypatch):
@@ -267,6 +257,12 @@ def test_engine_part3_two_rank_path_in_dry_run(executor, monkeypatch):
         def finalize(self):
             log.append(("reducer.finalize", {}))
 
+        def set_lazy_exit(self, on=True):
+            log.append(("reducer.set_lazy_exit", {"on": on}))
+
+        def stream(self, device):
+            return FakeStream()
+
         def close(self):
             pass
 
@@ -288,6 +284,7 @@ def test_engine_part3_two_rank_path_in_dry_run(executor, monkeypatch):
     be = engine.NativeBackend(cfg, VGG("VGG11"), torch.device("cpu"))
     assert type(be.sync).__name__ == "BucketedOverlapSync" and be.comm.multicast      # NVLS heap by default for world > 1
     assert be.sync.reducer.kw["blocks"] == 32
+    start_log = list(log)
     start = [n for n, _ in log]
     assert start.count("comm.broadcast") == 2 and "comm.prefer_nvls" in start         # parameters + BatchNorm state
     log.clear()
@@ -299,11 +296,10 @@ def test_engine_part3_two_rank_path_in_dry_run(executor, monkeypatch):
     assert ready == list(range(8))
     i_fin = names.index("reducer.finalize")
     assert i_fin > max(i for i, n in enumerate(names) if n == "conv_wgrad")
-    assert "prep_conv_weights_batched" not in names and be.native._shadows_stale     # re-layout: beside the next forward
+    # operand copies: re-laid-out per bucket right behind its collective (own stream), joined after finalize
+    i_ready = [i for i, n in enumerate(names) if n == "reducer.bucket_ready"]
+    i_prep = [i for i, n in enumerate(names) if n == "prep_conv_weights_batched"]
+    assert len(i_prep) == 8 and all(p == r + 1 for p, r in zip(i_prep, i_ready)) and i_prep[-1] < i_fin
+    assert ("reducer.set_lazy_exit", {"on": False}) in [(n, kw) for n, kw in start_log]
     assert "sgd_momentum" not in names                                                # the optimizer lives in the collectives
-    log.clear()
-    be.train_step(torch.randn(8, 3, 32, 32), torch.randint(0, 10, (8,)))
-    names = [n for n, _ in log]
-    assert names.count("prep_conv_weights_batched") == 2
-    assert max(i for i, n in enumerate(names) if n == "prep_conv_weights_batched") < names.index("conv_igemm")
     be.close()

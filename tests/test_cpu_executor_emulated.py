@@ -242,12 +242,8 @@ def test_engine_training_steps_match_torch_sgd(emu, monkeypatch):
         a, b = p.data.flatten(), ref_params[name].data.flatten()
         rel = ((a - b).norm() / (b.norm() + 1e-12)).item()
         assert rel < 2e-2, f"{name}: parameters drifted apart, relative L2 {rel:.3e}"
-    # the bf16-operand copies the next forward reads are the re-layout of the CURRENT weights: the optimizer left
-    # them stale, the forward pass refreshes them before its first layer
+    # the bf16-operand copies the next forward will read are the re-layout of the CURRENT weights
     nv = be.native
-    assert nv._shadows_stale
-    nv.forward(x.to(nv.device) if hasattr(x, "to") else x, training=False)
-    assert not nv._shadows_stale
     got = [(b.wf.clone(), None if b.wd is None else b.wd.clone()) for b in nv.blocks]
     nv.refresh_shadows()
     for b, (wf, wd) in zip(nv.blocks, got):

@@ -76,6 +76,7 @@ def fake_native():
             nv._bucket_of_block.setdefault(min(blocks) if blocks else len(nv.blocks) - 1, []).append(bk.index)
     nv.set_bucket_plan = set_bucket_plan
     nv.blocks_of_bucket = lambda k: [i for i, ks in nv._bucket_of_block.items() if k in ks]
+    nv._dgrad_done = [object() for _ in nv.blocks]
     return nv
 
 
@@ -88,8 +89,17 @@ def _stubs(monkeypatch):
     class _Fake:                      # LocalSGD forks its first optimizer phase onto a stream of its own
         def __init__(self, *a, **kw):
             pass
+
+        def record(self, *a):
+            pass
+
+        def wait_event(self, *a):
+            pass
+    import contextlib
     monkeypatch.setattr(torch.cuda, "Stream", _Fake)
     monkeypatch.setattr(torch.cuda, "Event", _Fake)
+    monkeypatch.setattr(torch.cuda, "stream", lambda s: contextlib.nullcontext())
+    monkeypatch.setattr(torch.cuda, "current_stream", lambda *a: _Fake())
 
 
 def _make(world, **kw):
@@ -102,15 +112,19 @@ def _make(world, **kw):
 def test_default_part3_strategy_constructs_and_hands_buckets_to_the_reducer():
     nv, s = _make(2, bucket_plan="layer", blocks=32)
     assert len(s.buckets) == 8 and s.reducer.kw["blocks"] == 32
-    assert not s._wgrad_push
+    # default: the operand copies of a bucket's layers are re-laid-out behind its collective by the strategy
+    assert not s._wgrad_push and s.handles_shadows and s._prep_overlap
+    assert s._blocks_in_bucket == [[7 - k] for k in range(8)]          # one conv layer per bucket, deepest first
     assert nv.wgrad_push is None and s.reducer.staged is None
     nv.on_bucket_ready(3)
     assert s.reducer.ready == [3]
     s.sync_and_step()
     s.close()
     assert nv.on_bucket_ready is None
-    for plan in ("ddp", "single", "cap:12"):
-        _make(4, bucket_plan=plan)
+    for plan in ("ddp", "single", "cap:12", "cap:16+last"):
+        nv, s = _make(4, bucket_plan=plan)
+        assert sorted(i for blks in s._blocks_in_bucket for i in blks) == list(range(8))   # every layer exactly once
+    assert _make(4)[1]._blocks_in_bucket == [[6, 7], [2, 3, 4, 5], [1], [0]]              # the default plan
 
 
 @pytest.mark.parametrize("world", [2, 4, 8])
@@ -165,7 +179,7 @@ def test_local_sgd_two_phase_split_covers_all_parameters():
     nv._wgrad_stream = None
     s = sync_native.LocalSGD(nv, None, lr=0.1, momentum=0.9, weight_decay=1e-4)
     if s.overlap:
-        assert 0 < s.split_end < nv.layout.total
+        assert 0 < s.split_end < nv.layout.total and s.handles_shadows
         assert s.split_end == s.buckets[s.split_bucket].end
         big = sum(b.end - b.start for b in s.buckets[: s.split_bucket + 1])
         assert big / nv.layout.total > 0.9          # phase 1 carries the bulk of the bytes

@@ -59,6 +59,15 @@ B200DP_DEVINL V8 ld_f32x8(const float* p) {
   return r;
 }
 
+B200DP_DEVINL V8 ld_cg_f32x8(const float* p) {   // two 16-byte L2 loads (values written by atomics)
+  const float4 a = __ldcg(reinterpret_cast<const float4*>(p));
+  const float4 b = __ldcg(reinterpret_cast<const float4*>(p + 4));
+  V8 r;
+  r.v[0] = a.x; r.v[1] = a.y; r.v[2] = a.z; r.v[3] = a.w;
+  r.v[4] = b.x; r.v[5] = b.y; r.v[6] = b.z; r.v[7] = b.w;
+  return r;
+}
+
 constexpr int kThreads = 256;
 constexpr int kStages = 3;
 
@@ -78,7 +87,7 @@ struct StreamGeom {
 };
 
 template <class Op>
-__global__ void __launch_bounds__(kThreads, 2) bn_stream_kernel(const typename Op::Params p, const StreamGeom g,
+__global__ void __launch_bounds__(kThreads, 3) bn_stream_kernel(const typename Op::Params p, const StreamGeom g,
                                                                 const typename Op::elem* __restrict__ a_ptr,
                                                                 const typename Op::elem* __restrict__ b_ptr,
                                                                 typename Op::elem* __restrict__ out_ptr) {
@@ -160,7 +169,12 @@ int launch_stream(const typename Op::Params& p, const StreamGeom& g, const void*
     configured = smem;
   }
   const long num_chunks = (g.units + g.units_per_stage - 1) / g.units_per_stage;
-  const int grid = static_cast<int>(num_chunks < 148 * 2 ? num_chunks : 148 * 2);
+  static const int ctas_per_sm = [] {   // measurement toggle of the current A/B
+    const char* e = getenv("B200DP_EXP_BN_CTAS");
+    return e != nullptr ? atoi(e) : 2;
+  }();
+  const long cap = 148L * ctas_per_sm;
+  const int grid = static_cast<int>(num_chunks < cap ? num_chunks : cap);
   using elem = typename Op::elem;
   B200DP_CUDA_TRY(launch_pdl(bn_stream_kernel<Op>, dim3(grid), dim3(kThreads), smem, s, p, g,
                              static_cast<const elem*>(a), static_cast<const elem*>(b), static_cast<elem*>(out)));
@@ -195,11 +209,9 @@ struct ApplyNoPoolOp {
     const float inv_count = 1.f / static_cast<float>(p.count);
     const V8 mean = ld_f32x8(p.mean + c0i), invstd = ld_f32x8(p.invstd + c0i);
     const V8 g = ld_f32x8(p.gamma + c0i), b = ld_f32x8(p.beta + c0i);
-    V8 s1, s2;
+    const V8 s1 = ld_cg_f32x8(p.sums + c0i), s2 = ld_cg_f32x8(p.sums + p.C + c0i);   // L2: atomics wrote them
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      s1.v[j] = __ldcg(p.sums + c0i + j);
-      s2.v[j] = __ldcg(p.sums + p.C + c0i + j);
       scale.v[j] = g.v[j] * invstd.v[j];
       shift.v[j] = b.v[j] - mean.v[j] * scale.v[j];
       c1.v[j] = -scale.v[j] * invstd.v[j] * s2.v[j] * inv_count;

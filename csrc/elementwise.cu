@@ -106,6 +106,15 @@ B200DP_DEVINL Vec8 load_f32x8(const float* p) {
   return r;
 }
 
+B200DP_DEVINL Vec8 load_cg_f32x8(const float* p) {   // two 16-byte L2 loads (values written by atomics)
+  const float4 a = __ldcg(reinterpret_cast<const float4*>(p));
+  const float4 b = __ldcg(reinterpret_cast<const float4*>(p + 4));
+  Vec8 r;
+  r.v[0] = a.x; r.v[1] = a.y; r.v[2] = a.z; r.v[3] = a.w;
+  r.v[4] = b.x; r.v[5] = b.y; r.v[6] = b.z; r.v[7] = b.w;
+  return r;
+}
+
 // ---------------------------------------------------------------------------
 // layer 0: gather 3x3x3 patches of the fp32 NCHW input into a bf16 [pixels][64]
 // matrix (27 real columns, k = (r*3+s)*3 + c, the rest zero) so that the first
@@ -404,12 +413,7 @@ B200DP_DEVINL void bn_relu_pool_bwd_body(const BnBwdParams& p, float* red) {
     }
     if (APPLY) {
       // L2 loads: in the fused kernel these sums were produced by atomics earlier in the same launch
-      Vec8 s1, s2;
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        s1.v[j] = __ldcg(p.sums + c0i + j);
-        s2.v[j] = __ldcg(p.sums + p.C + c0i + j);
-      }
+      const Vec8 s1 = load_cg_f32x8(p.sums + c0i), s2 = load_cg_f32x8(p.sums + p.C + c0i);   // L2: atomics wrote them
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         c1.v[j] = -scale.v[j] * invstd.v[j] * s2.v[j] * inv_count;
@@ -536,11 +540,9 @@ __global__ void __launch_bounds__(256, 3) bn_bwd_apply_nopool_kernel(const BnBwd
   {
     const Vec8 mean = load_f32x8(p.mean + c0i), invstd = load_f32x8(p.invstd + c0i);
     const Vec8 g = load_f32x8(p.gamma + c0i), b = load_f32x8(p.beta + c0i);
-    Vec8 s1, s2;
+    const Vec8 s1 = load_cg_f32x8(p.sums + c0i), s2 = load_cg_f32x8(p.sums + p.C + c0i);   // L2: atomics wrote them
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      s1.v[j] = __ldcg(p.sums + c0i + j);
-      s2.v[j] = __ldcg(p.sums + p.C + c0i + j);
       scale.v[j] = g.v[j] * invstd.v[j];
       shift.v[j] = b.v[j] - mean.v[j] * scale.v[j];
       c1.v[j] = -scale.v[j] * invstd.v[j] * s2.v[j] * inv_count;
@@ -602,11 +604,9 @@ __global__ void __launch_bounds__(256, 2) bn_bwd_apply_pool_kernel(const BnBwdPa
   {
     const Vec8 mean = load_f32x8(p.mean + c0i), invstd = load_f32x8(p.invstd + c0i);
     const Vec8 g = load_f32x8(p.gamma + c0i), b = load_f32x8(p.beta + c0i);
-    Vec8 s1, s2;
+    const Vec8 s1 = load_cg_f32x8(p.sums + c0i), s2 = load_cg_f32x8(p.sums + p.C + c0i);   // L2: atomics wrote them
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      s1.v[j] = __ldcg(p.sums + c0i + j);
-      s2.v[j] = __ldcg(p.sums + p.C + c0i + j);
       scale.v[j] = g.v[j] * invstd.v[j];
       shift.v[j] = b.v[j] - mean.v[j] * scale.v[j];
       c1.v[j] = -scale.v[j] * invstd.v[j] * s2.v[j] * inv_count;
@@ -696,16 +696,17 @@ __global__ void __launch_bounds__(256, 3) bn_relu_pool_bwd_kernel(const BnBwdPar
 // boundaries included).  Requires (Wo * C/8) to divide kBnTmaItems.
 // ---------------------------------------------------------------------------
 // Work items per stage = threads per block: 256 for bf16, 128 for fp32 activations (the same bytes per stage).
-constexpr int kBnTmaStages = 3;
 constexpr int kBnTmaYBytes = 256 * 4 * 16;              // 16 KiB of y per stage (4 vectors of 8 channels per item)
 constexpr int kBnTmaGBytes = 256 * 16;                  // 4 KiB of dout per stage
 constexpr int kBnTmaStageBytes = kBnTmaYBytes + kBnTmaGBytes;
-constexpr int kBnTmaSmem = kBnTmaStages * kBnTmaStageBytes + 2 * kBnTmaYBytes + 64 + 128;
+constexpr int bn_tma_smem(int stages) { return stages * kBnTmaStageBytes + 2 * kBnTmaYBytes + 64 + 128; }
 template <class T>
 constexpr int bn_tma_items() { return 512 / static_cast<int>(sizeof(T)); }
 
-template <class T>
-__global__ void __launch_bounds__(bn_tma_items<T>(), 2) bn_bwd_apply_pool_tma_kernel(const BnBwdParams p) {
+// kBnTmaStages = 3: two CTAs per SM (184 KB); = 2: three CTAs per SM (216 KB, 24 warps instead of 16)
+template <class T, int kBnTmaStages>
+__global__ void __launch_bounds__(bn_tma_items<T>(), kBnTmaStages == 2 ? 3 : 2)
+    bn_bwd_apply_pool_tma_kernel(const BnBwdParams p) {
   constexpr int kBnTmaItems = bn_tma_items<T>();
   const T* __restrict__ py = static_cast<const T*>(p.y);
   const T* __restrict__ pdout = static_cast<const T*>(p.dout);
@@ -752,11 +753,9 @@ __global__ void __launch_bounds__(bn_tma_items<T>(), 2) bn_bwd_apply_pool_tma_ke
   {
     const Vec8 mean = load_f32x8(p.mean + c0i), invstd = load_f32x8(p.invstd + c0i);
     const Vec8 g = load_f32x8(p.gamma + c0i), b = load_f32x8(p.beta + c0i);
-    Vec8 s1, s2;
+    const Vec8 s1 = load_cg_f32x8(p.sums + c0i), s2 = load_cg_f32x8(p.sums + p.C + c0i);   // L2: atomics wrote them
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      s1.v[j] = __ldcg(p.sums + c0i + j);
-      s2.v[j] = __ldcg(p.sums + p.C + c0i + j);
       scale.v[j] = g.v[j] * invstd.v[j];
       shift.v[j] = b.v[j] - mean.v[j] * scale.v[j];
       c1.v[j] = -scale.v[j] * invstd.v[j] * s2.v[j] * inv_count;
@@ -1537,21 +1536,31 @@ static bool bn_tma_supported(const BnBwdParams& p) {
   return items_per_tile >= 1 && items_per_tile <= kItems && kItems % items_per_tile == 0;
 }
 
-template <class T>
-static int launch_bn_apply_pool_tma(const BnBwdParams& p, cudaStream_t s) {
+template <class T, int STAGES>
+static int launch_bn_apply_pool_tma_n(const BnBwdParams& p, cudaStream_t s) {
   constexpr int kItems = bn_tma_items<T>();
+  constexpr int kSmem = bn_tma_smem(STAGES);
+  constexpr int kCtasPerSm = STAGES == 2 ? 3 : 2;
   static bool configured = false;
   if (!configured) {
-    B200DP_CUDA_TRY(cudaFuncSetAttribute(bn_bwd_apply_pool_tma_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         kBnTmaSmem));
+    B200DP_CUDA_TRY(cudaFuncSetAttribute(bn_bwd_apply_pool_tma_kernel<T, STAGES>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
     configured = true;
   }
   const int G = kItems / ((p.W / 2) * (p.C / 8));
   const long tiles = static_cast<long>(p.B) * (p.H / 2);
   const long num_chunks = (tiles + G - 1) / G;
-  const int grid = static_cast<int>(num_chunks < 148 * 2 ? num_chunks : 148 * 2);
-  B200DP_CUDA_TRY(launch_pdl(bn_bwd_apply_pool_tma_kernel<T>, dim3(grid), dim3(kItems), kBnTmaSmem, s, p));
+  const int grid = static_cast<int>(num_chunks < 148 * kCtasPerSm ? num_chunks : 148 * kCtasPerSm);
+  B200DP_CUDA_TRY(launch_pdl(bn_bwd_apply_pool_tma_kernel<T, STAGES>, dim3(grid), dim3(kItems), kSmem, s, p));
   return 0;
+}
+template <class T>
+static int launch_bn_apply_pool_tma(const BnBwdParams& p, cudaStream_t s) {
+  static const bool three = [] {   // measurement toggle of the current A/B
+    const char* e = getenv("B200DP_EXP_BN_POOL3");
+    return e != nullptr && e[0] == '1';
+  }();
+  return three ? launch_bn_apply_pool_tma_n<T, 2>(p, s) : launch_bn_apply_pool_tma_n<T, 3>(p, s);
 }
 
 template <class T>

@@ -48,13 +48,12 @@ def _conv_ref(x_nhwc, w_krsc, bias):
     return y.permute(0, 2, 3, 1).contiguous()
 
 
-@pytest.mark.parametrize("shape", CONV_SHAPES)
-@pytest.mark.parametrize("block_n", [0, 32, 64, 128, 256])
+# only the N tiles that divide Cout (0 = let the launcher choose)
+@pytest.mark.parametrize("shape,block_n", [(s, n) for s in CONV_SHAPES for n in (0, 32, 64, 128, 256)
+                                           if not n or s[4] % n == 0])
 def test_conv_fwd(shape, block_n):
     native = _native()
     B, H, W, Cin, Cout = shape
-    if block_n and Cout % block_n:
-        pytest.skip("block_n does not divide Cout")
     g = torch.Generator(device=DEV).manual_seed(1)
     x = torch.randn(B, H, W, Cin, device=DEV, generator=g).bfloat16()
     w = (torch.randn(Cout, 3, 3, Cin, device=DEV, generator=g) / (3 * Cin ** 0.5)).bfloat16()
@@ -302,15 +301,16 @@ def test_conv_fwd_split_k(shape, block_n, split_k):
         assert ws.abs().max().item() == 0
 
 
-@pytest.mark.parametrize("shape", [(32, 16, 16, 64, 128), (32, 8, 8, 256, 256), (32, 4, 4, 512, 512),
-                                   (64, 2, 2, 512, 512), (2, 32, 32, 64, 64)])
-@pytest.mark.parametrize("block_n,split_k", [(64, 1), (128, 1), (256, 1), (128, 3)])
+# the CTA-pair kernel needs an even number of 128-pixel tiles and an N tile that divides Cout
+@pytest.mark.parametrize("shape,block_n,split_k", [
+    (s, n, k) for s in [(32, 16, 16, 64, 128), (32, 8, 8, 256, 256), (32, 4, 4, 512, 512), (64, 2, 2, 512, 512),
+                        (2, 32, 32, 64, 64)]
+    for n, k in [(64, 1), (128, 1), (256, 1), (128, 3)]
+    if s[4] % n == 0 and ((s[0] * s[1] * s[2]) // 128) % 2 == 0])
 def test_conv_fwd_cta_pair(shape, block_n, split_k):
     """tcgen05.mma.cta_group::2: two CTAs share one 256-row tile, each staging half of the weights."""
     native = _native()
     B, H, W, Cin, Cout = shape
-    if Cout % block_n or ((B * H * W) // 128) % 2:
-        pytest.skip("shape not tileable by the CTA-pair kernel")
     g = torch.Generator(device=DEV).manual_seed(10)
     x = torch.randn(B, H, W, Cin, device=DEV, generator=g).bfloat16()
     w = (torch.randn(Cout, 3, 3, Cin, device=DEV, generator=g) / (3 * Cin ** 0.5)).bfloat16()

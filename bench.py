@@ -114,7 +114,7 @@ def parse_args():
     p.add_argument("--scaling", choices=("weak", "strong"), default="weak")
     p.add_argument("--per-gpu-batch", type=int, default=256)
     p.add_argument("--global-batch", type=int, default=256, help="used with --scaling strong")
-    p.add_argument("--bucket-plan", default="cap:16+last")
+    p.add_argument("--bucket-plan", default="cap:12+last")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--comm-blocks", type=int, default=None)
     p.add_argument("--sync-blocks", type=int, default=None)

@@ -38,7 +38,7 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--port", type=int, default=None)
     p.add_argument("--device", choices=("auto", "cpu", "cuda"), default="auto")
     p.add_argument("--backend", choices=("auto", "gloo", "nccl", "native"), default="auto")
-    p.add_argument("--bucket-plan", default="cap:16+last",
+    p.add_argument("--bucket-plan", default="cap:12+last",
                    help="part3 gradient buckets: cap:<MiB> (greedy) | layer (one per conv layer) | ddp (torch's caps) | single")
     p.add_argument("--no-fuse-optimizer", action="store_true")
     p.add_argument("--nvls", choices=("auto", "on", "off"), default="auto",

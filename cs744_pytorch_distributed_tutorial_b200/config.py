@@ -58,10 +58,10 @@ class TrainConfig:
     backend: str = "auto"       # auto | gloo | nccl | native  (native = in-kernel NVLink collectives)
     # part3 gradient buckets: cap:<MiB> (greedy, closed at conv-layer boundaries) | layer (one per conv layer,
     # SURVEY 7.3) | ddp (torch's 1 MiB + 25 MiB caps) | single, each optionally with "+last" (the first conv block,
-    # whose gradients come last, in a bucket of its own).  cap:16+last gives 18.9 / 17.7 / 0.3 MB + 8 KB on VGG-11:
+    # whose gradients come last, in a bucket of its own).  cap:12+last gives 18.9 / 14.2 / 3.9 MB + 8 KB on VGG-11:
     # each bucket kernel pays barrier round trips and a launch, so few large ones hide under backward where eight
     # did not, and the one collective that nothing can hide moves 8 KB instead of 4 MB
-    bucket_plan: str = "cap:16+last"
+    bucket_plan: str = "cap:12+last"
     fuse_optimizer: bool = True  # SGD in the collective epilogue where the mode allows it
     # CTAs of a side-stream bucket kernel (part3); the GEMMs keep the other SMs.  Three 9.4 MB buckets
     # become ready in the first ~100 us of backward; 16 CTAs could not drain them before backward ended

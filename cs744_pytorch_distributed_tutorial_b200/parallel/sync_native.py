@@ -195,7 +195,7 @@ class BucketedOverlapSync(NativeSync):
     name = "ddp_bucketed"
     syncs_buffers = True
 
-    def __init__(self, *a, bucket_plan: str = "cap:16+last", blocks: int = 32, **kw):
+    def __init__(self, *a, bucket_plan: str = "cap:12+last", blocks: int = 32, **kw):
         super().__init__(*a, **kw)
         nv = self.native
         self.buckets = nv.layout.buckets(bucket_plan)

@@ -87,7 +87,7 @@ struct StreamGeom {
 };
 
 template <class Op>
-__global__ void __launch_bounds__(kThreads, 3) bn_stream_kernel(const typename Op::Params p, const StreamGeom g,
+__global__ void __launch_bounds__(kThreads, 2) bn_stream_kernel(const typename Op::Params p, const StreamGeom g,
                                                                 const typename Op::elem* __restrict__ a_ptr,
                                                                 const typename Op::elem* __restrict__ b_ptr,
                                                                 typename Op::elem* __restrict__ out_ptr) {
@@ -169,12 +169,7 @@ int launch_stream(const typename Op::Params& p, const StreamGeom& g, const void*
     configured = smem;
   }
   const long num_chunks = (g.units + g.units_per_stage - 1) / g.units_per_stage;
-  static const int ctas_per_sm = [] {   // measurement toggle of the current A/B
-    const char* e = getenv("B200DP_EXP_BN_CTAS");
-    return e != nullptr ? atoi(e) : 2;
-  }();
-  const long cap = 148L * ctas_per_sm;
-  const int grid = static_cast<int>(num_chunks < cap ? num_chunks : cap);
+  const int grid = static_cast<int>(num_chunks < 148 * 2 ? num_chunks : 148 * 2);   // 3 per SM: no gain (A/B)
   using elem = typename Op::elem;
   B200DP_CUDA_TRY(launch_pdl(bn_stream_kernel<Op>, dim3(grid), dim3(kThreads), smem, s, p, g,
                              static_cast<const elem*>(a), static_cast<const elem*>(b), static_cast<elem*>(out)));

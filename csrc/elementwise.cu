@@ -696,17 +696,18 @@ __global__ void __launch_bounds__(256, 3) bn_relu_pool_bwd_kernel(const BnBwdPar
 // boundaries included).  Requires (Wo * C/8) to divide kBnTmaItems.
 // ---------------------------------------------------------------------------
 // Work items per stage = threads per block: 256 for bf16, 128 for fp32 activations (the same bytes per stage).
+// Three stages, two CTAs per SM (184 KB).  Two stages with three CTAs per SM (24 warps instead of 16) measured
+// slower (0.597 vs 0.578 ms per step).
+constexpr int kBnTmaStages = 3;
 constexpr int kBnTmaYBytes = 256 * 4 * 16;              // 16 KiB of y per stage (4 vectors of 8 channels per item)
 constexpr int kBnTmaGBytes = 256 * 16;                  // 4 KiB of dout per stage
 constexpr int kBnTmaStageBytes = kBnTmaYBytes + kBnTmaGBytes;
-constexpr int bn_tma_smem(int stages) { return stages * kBnTmaStageBytes + 2 * kBnTmaYBytes + 64 + 128; }
+constexpr int kBnTmaSmem = kBnTmaStages * kBnTmaStageBytes + 2 * kBnTmaYBytes + 64 + 128;
 template <class T>
 constexpr int bn_tma_items() { return 512 / static_cast<int>(sizeof(T)); }
 
-// kBnTmaStages = 3: two CTAs per SM (184 KB); = 2: three CTAs per SM (216 KB, 24 warps instead of 16)
-template <class T, int kBnTmaStages>
-__global__ void __launch_bounds__(bn_tma_items<T>(), kBnTmaStages == 2 ? 3 : 2)
-    bn_bwd_apply_pool_tma_kernel(const BnBwdParams p) {
+template <class T>
+__global__ void __launch_bounds__(bn_tma_items<T>(), 2) bn_bwd_apply_pool_tma_kernel(const BnBwdParams p) {
   constexpr int kBnTmaItems = bn_tma_items<T>();
   const T* __restrict__ py = static_cast<const T*>(p.y);
   const T* __restrict__ pdout = static_cast<const T*>(p.dout);
@@ -1536,31 +1537,21 @@ static bool bn_tma_supported(const BnBwdParams& p) {
   return items_per_tile >= 1 && items_per_tile <= kItems && kItems % items_per_tile == 0;
 }
 
-template <class T, int STAGES>
-static int launch_bn_apply_pool_tma_n(const BnBwdParams& p, cudaStream_t s) {
+template <class T>
+static int launch_bn_apply_pool_tma(const BnBwdParams& p, cudaStream_t s) {
   constexpr int kItems = bn_tma_items<T>();
-  constexpr int kSmem = bn_tma_smem(STAGES);
-  constexpr int kCtasPerSm = STAGES == 2 ? 3 : 2;
   static bool configured = false;
   if (!configured) {
-    B200DP_CUDA_TRY(cudaFuncSetAttribute(bn_bwd_apply_pool_tma_kernel<T, STAGES>,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+    B200DP_CUDA_TRY(cudaFuncSetAttribute(bn_bwd_apply_pool_tma_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         kBnTmaSmem));
     configured = true;
   }
   const int G = kItems / ((p.W / 2) * (p.C / 8));
   const long tiles = static_cast<long>(p.B) * (p.H / 2);
   const long num_chunks = (tiles + G - 1) / G;
-  const int grid = static_cast<int>(num_chunks < 148 * kCtasPerSm ? num_chunks : 148 * kCtasPerSm);
-  B200DP_CUDA_TRY(launch_pdl(bn_bwd_apply_pool_tma_kernel<T, STAGES>, dim3(grid), dim3(kItems), kSmem, s, p));
+  const int grid = static_cast<int>(num_chunks < 148 * 2 ? num_chunks : 148 * 2);
+  B200DP_CUDA_TRY(launch_pdl(bn_bwd_apply_pool_tma_kernel<T>, dim3(grid), dim3(kItems), kBnTmaSmem, s, p));
   return 0;
-}
-template <class T>
-static int launch_bn_apply_pool_tma(const BnBwdParams& p, cudaStream_t s) {
-  static const bool three = [] {   // measurement toggle of the current A/B
-    const char* e = getenv("B200DP_EXP_BN_POOL3");
-    return e != nullptr && e[0] == '1';
-  }();
-  return three ? launch_bn_apply_pool_tma_n<T, 2>(p, s) : launch_bn_apply_pool_tma_n<T, 3>(p, s);
 }
 
 template <class T>

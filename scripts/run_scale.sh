@@ -31,10 +31,13 @@ timeout 300 $RUN scripts/timeline_step.py --mode part3 --out $OUT/timeline_part3
 rm -f $OUT/timeline_part3.json
 ab() { v=$(timeout 300 $RUN bench.py --gpus $N --steps 100 --no-e2e --no-strong --no-tf32 --no-selfcheck --no-loader "$@" 2>&1 | grep "^{" | python -c "import json,sys; r=json.loads(sys.stdin.read()); print(round(r['ms_per_step'],4), round(r.get('exposed_comm_fraction',0),4))"); echo "  [${LABEL}$*] $v" | tee -a $OUT/ab.log; }
 ab
-ab --bucket-plan cap:16
-ab --bucket-plan layer
-ab --comm-blocks 48
-LABEL="wgrad-push " B200DP_WGRAD_PUSH=1 ab --bucket-plan layer
+LABEL="re-layout at the tail, lazy exit barriers " B200DP_EXP_PREP_TAIL=1 ab
+ab --bucket-plan cap:16+last
+ab --bucket-plan cap:12
+ab
+LABEL="re-layout at the tail, lazy exit barriers " B200DP_EXP_PREP_TAIL=1 ab
+timeout 300 $RUN bench.py --gpus $N --steps 100 --no-strong --no-tf32 --no-selfcheck --loader-threads 8 2>&1 | grep "^{" > $OUT/native_loader8.json
+python -c "import json; r=json.load(open('$OUT/native_loader8.json')); print('loader threads 8:', r.get('e2e_with_loader'))"
 if [ "$3" = "modes" ]; then
   ab --mode part2b
   ab --mode part2a

@@ -100,7 +100,7 @@ def test_param_server_variants_bit_identical(results_w2):
 
 def test_ddp_mode_syncs_buffers_and_launches_buckets_in_order(results_w2):
     r0, r1 = results_w2["part3"]
-    assert r0["launch_log"] == list(range(4)) == r1["launch_log"]      # default plan cap:16+last -> four buckets on VGG-11
+    assert r0["launch_log"] == list(range(4)) == r1["launch_log"]      # default plan cap:12+last -> four buckets on VGG-11
     # part2b keeps per-rank BatchNorm statistics ...
     b0, b1 = results_w2["part2b"]
     assert not torch.equal(b0["buffers"]["layers.1.running_mean"], b1["buffers"]["layers.1.running_mean"])

@@ -124,7 +124,7 @@ def test_default_part3_strategy_constructs_and_hands_buckets_to_the_reducer():
     for plan in ("ddp", "single", "cap:12", "cap:16+last"):
         nv, s = _make(4, bucket_plan=plan)
         assert sorted(i for blks in s._blocks_in_bucket for i in blks) == list(range(8))   # every layer exactly once
-    assert _make(4)[1]._blocks_in_bucket == [[6, 7], [2, 3, 4, 5], [1], [0]]              # the default plan
+    assert _make(4)[1]._blocks_in_bucket == [[6, 7], [4, 5], [1, 2, 3], [0]]              # the default plan
 
 
 @pytest.mark.parametrize("world", [2, 4, 8])

@@ -130,7 +130,7 @@ def parse_args():
     p.add_argument("--no-selfcheck", action="store_true", help="skip the collective self-check at N > 1")
     p.add_argument("--no-loader", action="store_true",
                    help="skip the input-pipeline run (uint8 images -> augmentation -> training step)")
-    p.add_argument("--loader-threads", type=int, default=4)
+    p.add_argument("--loader-threads", type=int, default=0, help="0 = auto (2 x CPUs / ranks, clamped to 4..8)")
     return p.parse_args()
 
 
@@ -249,7 +249,7 @@ def loader_e2e(tr, cfg, steps: int, threads: int, warm: int = 5) -> dict:
     pipe.close()
     ms = be.max_over_ranks(t0.elapsed_time(t1)) / n
     return {"value": cfg.global_batch / (ms * 1e-3), "unit": "images/s", "ms_per_step": ms, "steps": n,
-            "loader": f"csrc/loader.cpp, {threads} threads per rank, RandomCrop(32,4)+flip+normalise, pinned ring",
+            "loader": f"csrc/loader.cpp, {pipe.threads} threads per rank, RandomCrop(32,4)+flip+normalise, pinned ring",
             "host_cpus": os.cpu_count(),
             "last_loss": last}
 

@@ -56,7 +56,7 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--no-augment", action="store_true")
     p.add_argument("--loader", choices=("auto", "python", "native"), default="auto",
                    help="batch assembly: vectorised torch ops, or the C++ thread pool of csrc/loader.cpp")
-    p.add_argument("--loader-threads", type=int, default=4)
+    p.add_argument("--loader-threads", type=int, default=0, help="0 = auto (2 x CPUs / ranks, clamped to 4..8)")
     p.add_argument("--no-eval", action="store_true")
     p.add_argument("--checkpoint", type=str, default=None, help="save a checkpoint here after training")
     p.add_argument("--resume", type=str, default=None)

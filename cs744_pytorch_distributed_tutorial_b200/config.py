@@ -45,7 +45,8 @@ class TrainConfig:
     # "native" = C++ threads (csrc/loader.cpp, > 300 k images/s per thread); same sampling, different
     # augmentation draws
     loader: str = "auto"          # native next to a GPU (native backend), python with the torch/gloo backend
-    loader_threads: int = 4
+    loader_threads: int = 0     # 0 = auto: 2 * host CPUs / ranks, clamped to 4..8 (8 ranks on a 32-CPU box: 8 threads
+                                # per rank fed 2.60 M images/s, 4 threads 1.87 M)
     cpu_threads: int = 4        # ref: master/part2a/part2a.py:18
     data_root: str = "../../data"
     # --- new knobs -------------------------------------------------------------------

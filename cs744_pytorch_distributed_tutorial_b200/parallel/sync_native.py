@@ -208,7 +208,10 @@ class BucketedOverlapSync(NativeSync):
         self.launch_log = []
         # Bucket kernels 0..n-2 of a step run without their exit barrier: what it guarantees is implied by the
         # entry barrier of the next bucket kernel on the channel; only the last one of a step keeps it
-        # (measured on 2 B200s: 0.743 vs 0.773 ms/step).  The reducer does this by itself.
+        # (measured on 2 B200s: 0.743 vs 0.773 ms/step).  The reducer does this by itself.  The operand copies
+        # of the weights are therefore re-laid-out in one pass after the last bucket (the engine does it): doing it
+        # per bucket behind each collective needs every bucket kernel's own exit barrier, which costs more at
+        # 8 GPUs than the 18 us pass at the tail (0.664 vs 0.636 ms per step, profiles/round2/scale_8/ab.log).
         #
         # Optional (B200DP_WGRAD_PUSH=1): the weight-gradient GEMM of every 3x3 layer forwards its finished
         # tiles to the owning rank's staging slots as they complete (GEMM -> reduce-scatter in one kernel); the
@@ -219,39 +222,6 @@ class BucketedOverlapSync(NativeSync):
                             and self.world > 1 and self.world <= 8)
         if self._wgrad_push:
             self._setup_wgrad_push()
-        # The operand copies (Wf / Wd) of a bucket's layers are re-laid-out on a stream of their own as soon as the
-        # bucket's collective has finished, under the rest of backward, instead of in one pass at the tail of the
-        # step.  A bucket kernel must then end with its own exit barrier (peers' parameter stores have landed when
-        # it completes), so the reducer's lazy-exit mode is switched off: its cost sits on the reducer stream,
-        # which is off the critical path with few large buckets.
-        self._prep_overlap = (fuse and self.world > 1 and not self._wgrad_push
-                              and os.environ.get("B200DP_EXP_PREP_TAIL", "0") == "0")   # A/B toggle of this round
-        if self._prep_overlap:
-            self.handles_shadows = True
-            self.reducer.set_lazy_exit(False)
-            conv_block = {f"layers.{b.spec.conv_idx}.weight": i for i, b in enumerate(nv.blocks)}
-            self._blocks_in_bucket = [sorted(conv_block[n] for n in bk.names if n in conv_block) for bk in self.buckets]
-            self._bucket_prep = [K.BatchedWeightPrep([nv.blocks[i].prep for i in blks]) if blks else None
-                                 for blks in self._blocks_in_bucket]
-            self._prep_stream = torch.cuda.Stream(nv.device)
-            self._reducer_stream = self.reducer.stream(nv.device)
-            self._ar_done = [torch.cuda.Event() for _ in self.buckets]
-            self._prep_join = torch.cuda.Event()
-            nv.on_bucket_ready = self._bucket_ready
-
-    def _bucket_ready(self, k: int) -> None:
-        """Called on the weight-gradient stream right after the last weight gradient of bucket k was launched."""
-        nv = self.native
-        self.reducer.bucket_ready(k)
-        if self._bucket_prep[k] is None:
-            return
-        ps = self._prep_stream
-        self._ar_done[k].record(self._reducer_stream)
-        ps.wait_event(self._ar_done[k])
-        for i in self._blocks_in_bucket[k]:
-            ps.wait_event(nv._dgrad_done[i])      # the data gradient is the last reader of the old copies
-        with torch.cuda.stream(ps):
-            self._bucket_prep[k]()
 
     def _setup_wgrad_push(self) -> None:
         import ctypes
@@ -326,9 +296,6 @@ class BucketedOverlapSync(NativeSync):
         self.reducer.finalize()
         if not self.fuse_optimizer:
             self._local_sgd()
-        if self._prep_overlap:
-            self._prep_join.record(self._prep_stream)
-            torch.cuda.current_stream().wait_event(self._prep_join)
 
     def gather_optimizer_state(self) -> None:
         # per bucket, with the bucket's own slicing; the small (one-shot) buckets already hold identical

@@ -75,16 +75,15 @@ if a.events:
 elif a.select:
     # occurrence index of each call inside one step; forward calls run blocks 0..7, backward calls blocks 7..0
     SELECT = {
-        "b200dp_copy_pair": {0}, "b200dp_im2col3x3_c3_ex": {0}, "b200dp_fill_zero": {0, 1},
+        "b200dp_im2col3x3_c3_ex2": {0},
         "b200dp_conv_igemm_ex": {0, 1, 3, 7},                 # layer 0 GEMM, 64->128@16x16, 256->256@8x8, 512->512@2x2
-        "b200dp_bn_relu_pool_fwd_ex": {0, 1, 2, 7},
+        "b200dp_bn_relu_pool_fwd_ex": {0, 2},
         "b200dp_head_fwd_bwd_ex": {0},
-        "b200dp_bn_relu_pool_bwd_reduce_ex": {0},
-        "b200dp_bn_relu_pool_bwd_apply_ex": {0, 5, 6, 7},       # blocks 7, 2, 1, 0
-        "b200dp_conv_dgrad_bn_reduce_ex": {0, 4, 6},            # blocks 7, 3, 1
-        "b200dp_conv_wgrad_ex": {0, 4, 6, 7},                   # blocks 7, 3, 1, 0
-        "b200dp_reducer_bucket_ready": {0, 1, 2}, "b200dp_sgd_momentum": {0, 1},
-        "b200dp_prep_conv_weights_batched_ex": {0, 1, 2},
+        "b200dp_bn_relu_pool_bwd_apply_ex": {5, 7},            # blocks 2, 0
+        "b200dp_conv_dgrad_bn_reduce_ex": {4, 6},              # blocks 3, 1
+        "b200dp_conv_wgrad_ex": {4, 6, 7},                     # blocks 3, 1, 0
+        "b200dp_reducer_bucket_ready": {0}, "b200dp_sgd_momentum": {0},
+        "b200dp_prep_conv_weights_batched_ex": {0},
     }
     seen = collections.Counter()
     orig = _lib.call

@@ -127,9 +127,8 @@ def _run(emu, world, batches, bucket_plan="layer", mode="part3", fuse=True):
         for r in range(world):
             nv, s = fabric.execs[r], fabric.syncs[r]
             s.sync_and_step()
-            # the fabric runs every collective after all ranks' backward, i.e. later than a strategy that re-lays
-            # the operand copies out behind its buckets expects (stream order does not exist here): redo it
-            nv.refresh_shadows()
+            if not s.handles_shadows:
+                nv.refresh_shadows()
             s.pre_forward()
     return fabric
 

@@ -112,9 +112,7 @@ def _make(world, **kw):
 def test_default_part3_strategy_constructs_and_hands_buckets_to_the_reducer():
     nv, s = _make(2, bucket_plan="layer", blocks=32)
     assert len(s.buckets) == 8 and s.reducer.kw["blocks"] == 32
-    # default: the operand copies of a bucket's layers are re-laid-out behind its collective by the strategy
-    assert not s._wgrad_push and s.handles_shadows and s._prep_overlap
-    assert s._blocks_in_bucket == [[7 - k] for k in range(8)]          # one conv layer per bucket, deepest first
+    assert not s._wgrad_push and not s.handles_shadows      # the engine re-lays the operand copies out after the step
     assert nv.wgrad_push is None and s.reducer.staged is None
     nv.on_bucket_ready(3)
     assert s.reducer.ready == [3]
@@ -122,9 +120,8 @@ def test_default_part3_strategy_constructs_and_hands_buckets_to_the_reducer():
     s.close()
     assert nv.on_bucket_ready is None
     for plan in ("ddp", "single", "cap:12", "cap:16+last"):
-        nv, s = _make(4, bucket_plan=plan)
-        assert sorted(i for blks in s._blocks_in_bucket for i in blks) == list(range(8))   # every layer exactly once
-    assert _make(4)[1]._blocks_in_bucket == [[6, 7], [4, 5], [1, 2, 3], [0]]              # the default plan
+        _make(4, bucket_plan=plan)
+    assert [len(b.names) for b in _make(4)[1].buckets] == [10, 8, 12, 4]     # default plan cap:12+last
 
 
 @pytest.mark.parametrize("world", [2, 4, 8])

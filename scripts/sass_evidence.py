@@ -17,7 +17,7 @@ LIB = os.path.join(ROOT, "cs744_pytorch_distributed_tutorial_b200", "lib", "libb
 SRCS = ["csrc/conv_igemm.cu", "csrc/collectives.cu", "csrc/elementwise.cu", "csrc/bn_stream.cu"]
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo", "--expt-relaxed-constexpr",
          "-I", os.path.join(ROOT, "include"), "-Xcompiler", "-fPIC"]
-EXPERIMENTAL = ("bnr", "head_fwd_bwd", "wgrad_push", "reduce_staged", "persist", "_tma", "bn_stream")
+EXPERIMENTAL = ("wgrad_push", "reduce_staged")      # the optional weight-gradient push path (B200DP_WGRAD_PUSH=1)
 today = datetime.date.today().isoformat()
 
 
@@ -63,7 +63,7 @@ def main():
             tags = " ".join(f"{k}={v}" for k, v in tags if v)
             short = names[n].replace("(anonymous namespace)::", "").replace("void ", "")
             short = re.sub(r"\(.*", "", short)
-            exp = "[exp] " if any(e in short for e in EXPERIMENTAL) else ""
+            exp = "[optional] " if any(e in short for e in EXPERIMENTAL) else ""
             f.write(f"{exp}{short}  {tags or '-'}\n")
     with open(os.path.join(ROOT, "profiles", "ptxas_resources.txt"), "w") as f:
         f.write(f"# ptxas -v resource usage (sm_100a), {today}; scripts/sass_evidence.py\n")
@@ -83,7 +83,7 @@ def main():
                 if m and cur:
                     short = demangle([cur])[cur].replace("(anonymous namespace)::", "").replace("void ", "")
                     short = re.sub(r"\(.*", "", short)
-                    exp = "[exp] " if any(e in short for e in EXPERIMENTAL) else ""
+                    exp = "[optional] " if any(e in short for e in EXPERIMENTAL) else ""
                     f.write(f"{exp}{short:66s} regs={m.group(1)}{m.group(2).rstrip()}{spill}\n")
                     cur = None
     print("wrote profiles/sass_mnemonics.txt and profiles/ptxas_resources.txt")

@@ -53,7 +53,7 @@ def main():
                 "# st.release.sys / ld.acquire.sys -> ST/LD ...STRONG.SYS, cluster barrier -> UCGABAR_*, cp.async.bulk -> UBLKCP\n")
         for k, v in total.most_common():
             f.write(f"{v:7d} {k}\n")
-        f.write("\n# per kernel ([exp] = experimental, off by default, DESIGN.md section 8)\n")
+        f.write("\n# per kernel ([optional] = only used with B200DP_WGRAD_PUSH=1)\n")
         for n, c in sorted(per.items(), key=lambda kv: names[kv[0]]):
             def cnt(pat):
                 return sum(v for k, v in c.items() if re.search(pat, k))

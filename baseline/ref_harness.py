@@ -22,7 +22,6 @@ import contextlib
 import hashlib
 import io
 import json
-import os
 import re
 import sys
 import types

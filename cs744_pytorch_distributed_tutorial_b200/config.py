@@ -10,7 +10,7 @@ from __future__ import annotations
 
 import dataclasses
 import os
-from dataclasses import dataclass, field
+from dataclasses import dataclass
 from typing import Optional
 
 MODES = ("part1", "part2a", "part2a_extra", "part2b", "part3")

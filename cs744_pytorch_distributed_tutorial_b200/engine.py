@@ -16,7 +16,6 @@ reports device-timed, max-over-ranks throughput as one JSON line.
 """
 from __future__ import annotations
 
-import json
 import os
 import time
 from typing import Dict, Iterable, List, Optional, Tuple

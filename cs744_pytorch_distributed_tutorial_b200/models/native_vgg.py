@@ -19,7 +19,6 @@ The kernel schedule replaces what the reference gets from ``model(data)`` /
 """
 from __future__ import annotations
 
-import os
 from dataclasses import dataclass
 from typing import Callable, Dict, List, Optional, Sequence, Tuple
 

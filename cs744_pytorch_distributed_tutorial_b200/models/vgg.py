@@ -10,7 +10,7 @@ stock torch ops (the gloo plumbing path and the numerics oracle); on a CUDA devi
 """
 from __future__ import annotations
 
-from typing import List, Optional, Union
+from typing import List
 
 import torch
 import torch.nn as nn

@@ -11,7 +11,7 @@ import json
 import statistics
 import sys
 import time
-from typing import Dict, List, Optional
+from typing import Dict, List
 
 import torch
 

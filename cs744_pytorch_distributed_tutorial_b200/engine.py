@@ -169,7 +169,7 @@ class NativeBackend:
             flat = (n_params + 4 * 64 + 1023) // 1024 * 1024 + 4096
             staging = (W - 1) * flat if cfg.mode == "part2a_extra" else 0
             if cfg.mode == "part3" and W > 1 and os.environ.get("B200DP_WGRAD_PUSH", "0") != "0":
-                staging = flat + 64 * W * 16   # experimental wgrad -> reduce-scatter staging slots
+                staging = flat + 64 * W * 16   # optional wgrad -> reduce-scatter staging slots
             heap_bytes = 4 * (3 * flat + staging) + (8 << 20)
             from .ops._lib import NativeError
             self.comm = None

@@ -542,7 +542,7 @@ class NativeVGG:
             side.wait_event(self._wgrad_fork[i])
             with torch.cuda.stream(side):
                 if self.wgrad_push is not None and i in self.wgrad_push:
-                    # experimental: GEMM + transfer half of the reduce-scatter in one kernel
+                    # optional path: GEMM + transfer half of the reduce-scatter in one kernel
                     K.conv_wgrad_push(b.dy[:B], b.x_in[:B], b.g_w, split_k=b.wgrad_split_k, block_n=b.wgrad_block_n,
                                       **self.wgrad_push[i])
                 else:

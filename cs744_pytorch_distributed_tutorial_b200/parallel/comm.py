@@ -238,7 +238,7 @@ class BucketReducer:
         call("b200dp_reducer_set_lr", self._h, lr)
 
     def set_lazy_exit(self, on: bool = True) -> None:
-        """Experimental: only the last bucket kernel of a step keeps its exit barrier."""
+        """On by default: only the last bucket kernel of a step keeps its exit barrier."""
         call("b200dp_reducer_set_lazy_exit", self._h, int(on))
 
     def set_blocks(self, blocks: int) -> None:
@@ -246,7 +246,7 @@ class BucketReducer:
         call("b200dp_reducer_set_blocks", self._h, int(blocks))
 
     def set_staged(self, stage_buf_off: int, pushed_lo, pushed_hi, stage_base) -> None:
-        """Experimental: buckets whose conv weight gradient arrives through ``conv_wgrad_push`` staging run
+        """Optional path: buckets whose conv weight gradient arrives through ``conv_wgrad_push`` staging run
         the owner-side ``reduce_staged_sgd`` kernel instead of the all-reduce."""
         n = self.n_buckets
         arr = lambda v: (c_longlong * n)(*[int(x) for x in v])

@@ -1,15 +1,16 @@
 // BatchNorm / ReLU / pool kernels as bulk-copy (cp.async.bulk, the TMA engine without a tensor map)
-// pipelines -- experimental, never run in round 1, selected with B200DP_BN_TMA=1.
+// pipelines.  These are what the plain BatchNorm entry points run whenever the shape fits the stage geometry
+// (measured in round 2: 0.700 -> 0.668 ms per step against the register-file kernels they replaced).
 //
 // Why: the register-file kernels in elementwise.cu sit at 45-56 % of the L2 / HBM rate with the issue
-// slots half idle (ncu, profiles/RESULTS.md section 5): every warp alternates between waiting for its own
+// slots half idle (ncu, profiles/RESULTS_round1.md section 5): every warp alternates between waiting for its own
 // loads and doing arithmetic.  NHWC activations are contiguous, so a stage of work is ONE contiguous chunk
 // per tensor; one thread keeps a ring of such chunks in flight per CTA, all 256 threads compute from
 // shared memory, and bulk stores drain the results -- loads, arithmetic and stores of different stages
 // overlap without relying on occupancy.  The pooled backward apply pass lives in elementwise.cu
 // (bn_bwd_apply_pool_tma_kernel, written first); this file holds the generic skeleton and the remaining
 // members of the family.  Every op keeps the arithmetic of the kernel it replaces, statement for
-// statement, so the acceptance test is bit-exactness (tests/test_gpu_experimental.py).
+// statement; tests/test_gpu_kernels.py::test_bn_relu_pool_fwd_bwd checks both families against torch.
 //
 // No counterpart in the reference (its BatchNorm is ATen's; ref: master/part1/model.py:20-22).
 #include <cuda_bf16.h>

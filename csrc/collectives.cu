@@ -367,7 +367,7 @@ __global__ void __launch_bounds__(512) allreduce_nvls_lazy_kernel(const CommDev 
 }
 
 // ---------------------------------------------------------------------------
-// Owner-side half of the fused "weight-gradient GEMM -> reduce-scatter" path (experimental).
+// Owner-side half of the fused "weight-gradient GEMM -> reduce-scatter" path (optional, B200DP_WGRAD_PUSH=1).
 // The conv_wgrad_push kernels of every rank have already stored their finished tiles of this bucket
 // into the owner's staging slots (conv_igemm.cu), so the owner reads only LOCAL memory here: its own
 // gradient plus W-1 staged copies.  Tensors that are not produced by a wgrad GEMM (biases, BatchNorm
@@ -1129,7 +1129,7 @@ extern "C" int b200dp_allreduce(void* comm, long long grad_off, long long param_
                         weight_decay, algo, blocks, channel, stream_, false);
 }
 
-/* Owner-side half of the fused wgrad -> reduce-scatter path (experimental; see conv_wgrad_push):
+/* Owner-side half of the fused wgrad -> reduce-scatter path (optional; see conv_wgrad_push):
  * for the bucket [start, end): mean gradient of my slice = (own gradient + W-1 staged copies) / W inside
  * [pushed_lo, pushed_hi), pulled from the peers elsewhere; SGD; updated parameters to every rank.
  * stage_buf_off: byte offset of the staging buffer in the heap, stage_base: element offset of this
@@ -1261,7 +1261,7 @@ struct Reducer {
   std::vector<cudaEvent_t> ready;
   cudaEvent_t done = nullptr;
   int launched = 0;
-  // experimental: buckets whose conv weight gradient arrives through conv_wgrad_push staging
+  // optional path: buckets whose conv weight gradient arrives through conv_wgrad_push staging
   // only the last bucket kernel of a step keeps its exit barrier (the entry barrier of the next bucket
   // kernel on the channel implies it); bucket_ready() must be called in index order
   bool lazy_exit = true;
@@ -1359,7 +1359,7 @@ extern "C" int b200dp_reducer_set_lazy_exit(void* reducer, int on) {
   return 0;
 }
 
-/* Experimental: tell the reducer which part of every bucket is delivered by conv_wgrad_push
+/* Optional path: tell the reducer which part of every bucket is delivered by conv_wgrad_push
  * (pushed_lo[k] == pushed_hi[k]: none, the bucket keeps the plain all-reduce).  Needs fuse_sgd. */
 extern "C" int b200dp_reducer_set_staged(void* reducer, long long stage_buf_off, const long long* pushed_lo,
                                          const long long* pushed_hi, const long long* stage_base) {

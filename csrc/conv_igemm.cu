@@ -56,7 +56,7 @@ struct IgemmParams {
   float* partial;
   int kb_per_split;
   // 1: the four epilogue warps combine their statistics in shared memory (the drained stage-0 operand
-  // buffer) and issue one atomic per channel per CTA instead of one per warp (B200DP_STATS_SMEM=0: off)
+  // buffer) and issue one atomic per channel per CTA instead of one per warp
   // dgrad only (conv_dgrad_bnr kernels): the tile just computed is dL/da for a = relu(bn(z)) of the
   // PREVIOUS block (max-pooled or not).  With `bnr_a` = that block's stored output, the epilogue also
   // accumulates its BatchNorm-backward sums  S1 = sum_{a>0} g,  S2 = sum_{a>0} g*(a-beta)/gamma  into
@@ -1255,8 +1255,8 @@ extern "C" int b200dp_conv_igemm_pair(const void* act, const void* wgt, const fl
  * block's stored output a = relu(bn(z)) (max-pooled or not), same [B,H,W,Cout] shape as `out`; on return
  * sums[0..Cout) += sum_{a>0} g and sums[Cout..2Cout) += sum_{a>0} g*(a-beta)/gamma with g the gradient just
  * written to `out` -- the contract of b200dp_bn_relu_pool_bwd_reduce_from_out, without its extra pass.
- * cta_pair / split_k / workspace as for b200dp_conv_igemm_pair / _splitk.  Experimental: off by default
- * in the executor (B200DP_DGRAD_BN_REDUCE=1). */
+ * cta_pair / split_k / workspace as for b200dp_conv_igemm_pair / _splitk.  This is the data gradient the executor
+ * runs for every block but the first (0.700 -> 0.689 ms per step against dgrad + a separate reduction pass). */
 extern "C" int b200dp_conv_dgrad_bn_reduce(const void* act, const void* wgt, void* out, float* workspace,
                                            const void* bn_out, const float* gamma, const float* beta, float* sums,
                                            int B, int H, int W, int Cin, int Cout, int taps, int block_n, int split_k,
@@ -1375,7 +1375,8 @@ extern "C" int b200dp_conv_wgrad(const void* dy, const void* x, float* dw, int B
                          static_cast<cudaStream_t>(stream_));
 }
 
-/* Weight gradient fused with the transfer half of the data-parallel reduce-scatter (experimental).
+/* Weight gradient fused with the transfer half of the data-parallel reduce-scatter (optional path,
+ * B200DP_WGRAD_PUSH=1: correct, but measured slower than the bucket reducer at 2 and 8 GPUs).
  * As b200dp_conv_wgrad_tiled (dw zero on entry, full Cin columns), plus: the tensor lives at element
  * flat_off of the flat gradient buffer, inside the bucket [own_start, own_start + own_len) that the
  * ranks own in `world` equal float4 slices (the slicing of the two-shot all-reduce).  Whenever an output

@@ -683,7 +683,8 @@ __global__ void __launch_bounds__(256, 3) bn_relu_pool_bwd_kernel(const BnBwdPar
 }
 
 // ---------------------------------------------------------------------------
-// Bulk-copy pipelined variant of the pooled apply pass (experimental, B200DP_BN_TMA=1).
+// Bulk-copy pipelined variant of the pooled apply pass (what b200dp_bn_relu_pool_bwd_apply runs with pool = 1
+// whenever the shape fits).
 // The register-file versions above keep at most ~10 KiB in flight per SM (37 % occupancy, a few 16-byte
 // loads per thread) and measure 45-56 % of the HBM / L2 rate.  Here the memory-level parallelism no longer
 // depends on the compute threads: one thread streams 20 KiB stages (256 work items: the two image rows of

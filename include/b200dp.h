@@ -79,7 +79,7 @@ int b200dp_conv_igemm_pair(const void* act, const void* wgt, const float* bias, 
  * the gradient just written -- exactly what b200dp_bn_relu_pool_bwd_reduce_from_out computes, fused into
  * the GEMM epilogue (split_k > 1: into the finalize kernel).  No bias, no forward statistics.
  * block_n in {32,64,128,256} ({64,128,256} with cta_pair); workspace as for b200dp_conv_igemm_splitk.
- * Experimental in round 1: the executor uses it only with B200DP_DGRAD_BN_REDUCE=1. */
+ * The executor's data gradient for every block but the first. */
 int b200dp_conv_dgrad_bn_reduce(const void* act, const void* wgt, void* out, float* workspace, const void* bn_out,
                                 const float* gamma, const float* beta, float* sums, int B, int H, int W, int Cin,
                                 int Cout, int taps, int block_n, int split_k, int cta_pair, b200dp_stream_t stream);
@@ -94,8 +94,8 @@ int b200dp_conv_dgrad_bn_reduce(const void* act, const void* wgt, void* out, flo
 int b200dp_conv_wgrad(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin, int Cout,
                       int taps, int cin_valid, int split_k, int accumulate, b200dp_stream_t stream);
 
-/* Weight gradient fused with the transfer half of the data-parallel reduce-scatter (experimental, never
- * run in round 1).  As b200dp_conv_wgrad_tiled (dw zero on entry, all Cin columns), plus: the tensor sits
+/* Weight gradient fused with the transfer half of the data-parallel reduce-scatter (optional path of part3,
+ * B200DP_WGRAD_PUSH=1; measured slower than the bucket reducer at 2 and 8 GPUs).  As b200dp_conv_wgrad_tiled (dw zero on entry, all Cin columns), plus: the tensor sits
  * at element flat_off of the flat gradient buffer, inside the bucket [own_start, own_start + own_len) that
  * the ranks own in `world` equal float4 slices (the slicing of the two-shot all-reduce).  When an output
  * tile is complete on this rank its float4s owned by rank r are stored over NVLink into peer_stage[r] at
@@ -231,13 +231,13 @@ int b200dp_bn_relu_pool_bwd_noalloc(const void* y, const void* dout, const float
 /* Pooled apply pass of the BatchNorm backward as a bulk-copy (cp.async.bulk) pipeline: one thread streams
  * 20 KiB stages of y / dout into shared memory, 256 threads compute, one thread streams dy back.  Same
  * contract and bit-identical results as b200dp_bn_relu_pool_bwd_apply with pool = 1; (W/2)*(C/8) must divide
- * 256.  Experimental (never run in round 1); the executor uses it with B200DP_BN_TMA=1. */
+ * 256.  b200dp_bn_relu_pool_bwd_apply routes here whenever the shape fits. */
 int b200dp_bn_bwd_apply_pool_tma(const void* y, const void* dout, const float* mean, const float* invstd,
                                  const float* gamma, const float* beta, const float* sums, void* dy, float* dgamma,
                                  float* dbeta, int B, int H, int W, int C, b200dp_stream_t stream);
 
-/* The rest of the BatchNorm family as bulk-copy pipelines (csrc/bn_stream.cu; experimental, never run in
- * round 1, taken by the plain entry points with B200DP_BN_TMA=1).  Same contracts as the kernels they
+/* The rest of the BatchNorm family as bulk-copy pipelines (csrc/bn_stream.cu; the plain entry points route to
+ * them whenever the shape fits).  Same contracts as the kernels they
  * replace: b200dp_bn_relu_pool_bwd_apply (pool = 0), b200dp_bn_relu_pool_fwd and
  * b200dp_bn_relu_pool_bwd_reduce_from_out; the first two are bit-identical, the reduction agrees up to
  * summation order.  C/8 must divide 256 (and (W/2)*(C/8) with pooling). */
@@ -260,8 +260,7 @@ int b200dp_cross_entropy(const float* logits, const long long* target, float* lo
                          int* correct, int B, int O, float grad_scale, b200dp_stream_t stream);
 int b200dp_linear_bwd(const void* x_bf16, const float* w, const float* dlogits, float* dw, float* db,
                       void* dx_bf16, int B, int F, int O, b200dp_stream_t stream);
-/* The three calls above as ONE launch for a training step (experimental; the executor uses it with
- * B200DP_HEAD_FUSED=1): logits, mean cross-entropy, top-1 count, dlogits (may be NULL), dx, and
+/* The three calls above as ONE launch (what a training step runs): logits, mean cross-entropy, top-1 count, dlogits (may be NULL), dx, and
  * dw += dlogits^T x, db += sum dlogits.  dw / db are accumulated onto (zero them first), loss / correct
  * are overwritten.  F % 8 == 0, F <= 2048, O <= 16, B <= 4096; one stream at a time. */
 int b200dp_head_fwd_bwd(const void* x_bf16, const float* w, const float* bias, const long long* target,
@@ -348,7 +347,7 @@ int b200dp_allreduce(void* comm, long long grad_off, long long param_off, long l
                      long long end, int fuse_sgd, int prescale, float lr, float momentum, float weight_decay,
                      int algo, int blocks, int channel, b200dp_stream_t stream);
 
-/* Owner-side half of the fused wgrad -> reduce-scatter path (experimental): bucket [start, end); inside
+/* Owner-side half of the fused wgrad -> reduce-scatter path (optional): bucket [start, end); inside
  * [pushed_lo, pushed_hi) the mean gradient of my slice is (own + W-1 staged copies) / W, elsewhere it is
  * pulled from the peers; then SGD and the updated parameters go to every rank (nvls = 1: multimem.st). */
 int b200dp_reduce_staged_sgd(void* comm, long long grad_off, long long param_off, long long mom_off,
@@ -393,10 +392,10 @@ int b200dp_reducer_destroy(void* reducer);
 int b200dp_reducer_stream(void* reducer, void** stream_out);
 /* CTAs per bucket collective for subsequent bucket_ready() calls (re-capture the step afterwards). */
 int b200dp_reducer_set_blocks(void* reducer, int blocks);
-/* Experimental: all bucket kernels of a step but the last drop their exit barrier (implied by the entry
+/* on = 1 (the default): all bucket kernels of a step but the last drop their exit barrier (implied by the entry
  * barrier of the next bucket kernel); requires bucket_ready() in index order. */
 int b200dp_reducer_set_lazy_exit(void* reducer, int on);
-/* Experimental: per bucket, the element range delivered by b200dp_conv_wgrad_push and its staging area;
+/* Optional path: per bucket, the element range delivered by b200dp_conv_wgrad_push and its staging area;
  * such buckets run b200dp_reduce_staged_sgd instead of the all-reduce (pushed_lo == pushed_hi: unchanged). */
 int b200dp_reducer_set_staged(void* reducer, long long stage_buf_off, const long long* pushed_lo,
                               const long long* pushed_hi, const long long* stage_base);

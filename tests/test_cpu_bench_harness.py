@@ -89,3 +89,22 @@ def test_reference_train_model_runs_on_cpu_through_the_harness_loader():
     with contextlib.redirect_stdout(buf):
         mod.train_model(model, batches, opt, crit, 0)
     assert buf.getvalue().startswith("0 loss: ")
+
+
+def test_reference_input_pipeline_is_torchvisions_dataset_class_with_the_tutorials_loader_settings():
+    """``e2e_with_loader`` of the reference arm: torchvision's CIFAR10 ``__getitem__`` (uint8 array -> PIL ->
+    transform chain of the tutorial) behind ``DataLoader(num_workers=2, pin_memory=True)``; only the pixels are
+    synthetic (ref: master/part1/part1.py:65-85, master/part3/part3.py:94-102)."""
+    pytest.importorskip("torchvision")
+    import ref_harness
+    from torchvision import datasets, transforms
+    dl = ref_harness.reference_dataloader(per_rank_batch=16, rank=0, world=1, n_images=64)
+    assert isinstance(dl.dataset, datasets.CIFAR10) and dl.num_workers == 2 and dl.batch_size == 16
+    kinds = [type(t) for t in dl.dataset.transform.transforms]
+    assert kinds == [transforms.RandomCrop, transforms.RandomHorizontalFlip, transforms.ToTensor, transforms.Normalize]
+    x, y = dl.dataset[0]                                      # the class's own __getitem__, in this process
+    assert x.shape == (3, 32, 32) and x.dtype == torch.float32 and 0 <= int(y) < 10
+    assert len(dl) == 4
+    # the sharded flavour: DistributedSampler over the same dataset, a quarter of the images per rank
+    d4 = ref_harness.reference_dataloader(per_rank_batch=16, rank=1, world=4, n_images=64 * 4)
+    assert type(d4.sampler).__name__ == "DistributedSampler" and len(d4) == 4

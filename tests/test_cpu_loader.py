@@ -123,3 +123,20 @@ def test_native_loader_is_much_faster_than_the_python_pipeline():
     fast = rate(nat)
     nat.close()
     assert fast > 3 * slow, (fast, slow)
+
+
+def test_thread_count_zero_means_auto_and_gives_the_same_batches(ds, monkeypatch):
+    """``threads=0`` (the default of ``TrainConfig.loader_threads``): 2 x host CPUs / ranks, clamped to 4..8 --
+    and, like any thread count, the same batches."""
+    import os
+    monkeypatch.setattr(os, "cpu_count", lambda: 32)
+    auto8 = NativeBatchPipeline(ds, 100, world=8, rank=3, train=True, augment=True, pin=False, threads=0)
+    assert auto8.threads == 8                                  # 2 * 32 / 8
+    monkeypatch.setattr(os, "cpu_count", lambda: 4)
+    auto4 = NativeBatchPipeline(ds, 100, world=8, rank=3, train=True, augment=True, pin=False, threads=0)
+    assert auto4.threads == 4                                  # never below 4
+    fixed = NativeBatchPipeline(ds, 100, world=8, rank=3, train=True, augment=True, pin=False, threads=2)
+    for (xa, ya), (xb, yb), (xc, yc) in zip(auto8, auto4, fixed):
+        assert torch.equal(xa, xc) and torch.equal(ya, yc) and torch.equal(xb, xc) and torch.equal(yb, yc)
+    for p in (auto8, auto4, fixed):
+        p.close()
